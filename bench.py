@@ -1,0 +1,450 @@
+#!/usr/bin/env python
+"""Benchmark of the B200-native NeuralNetworkModel hot path (contract: see DESIGN.md, section Measurement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3] [--impl native|reference]
+
+Default workload = BASELINE.json configs[1]: 784-256-128-10 MLP, relu/relu/softmax + cross-entropy,
+Adam, L2 0.001, batch 1024, fp32, one train step (forward + loss + backward + update) per "step".
+Prints ONE JSON line (rank 0).  `value` = samples/s with inputs resident in HBM; `e2e` = the same
+through the host-buffer API (pinned host batch -> device every step, cost read back every step).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+SIZES = [784, 256, 128, 10]
+ALGOS = ["linear", "relu", "linear", "relu", "linear", "softmax"]
+N_PARAMS = sum((SIZES[i] + 1) * SIZES[i + 1] for i in range(3))           # 235,146
+HP = dict(learning_rate=0.01, decay_rate=0.9, l2_lambda=0.001, beta1=0.9, beta2=0.999, epsilon=1e-8)
+# algorithmic HBM bytes of one C2 train step (X + labels + Adam read/write of P, m, v)
+C2_BATCH = 1024
+C2_STEP_BYTES = C2_BATCH * 784 * 4 + C2_BATCH * 4 + 6 * N_PARAMS * 4       # 8,858,864
+C2_STEP_FLOPS = C2_BATCH * 1_007_104
+C3_BYTES_PER_SAMPLE = 784 * 4 + 10 * 4                                     # 3,176
+C3_FLOPS_PER_SAMPLE = 469_504
+
+
+def init_params(sizes, seed=0):
+    """Synthetic xavier-scaled normal weights, zero biases (the reference's defaults,
+    neural_net_model.py:104-108,243-244)."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for l in range(len(sizes) - 1):
+        out.append(rng.standard_normal((sizes[l], sizes[l + 1])) / np.sqrt(sizes[l]))
+        out.append(np.zeros(sizes[l + 1]))
+    return out
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm_gbs=float(d["hbm_gbs"]), bf16_tflops=float(d["bf16_tflops"]),
+                    bf16_tflops_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0,
+                source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_setup(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if args.impl == "reference":
+            return world, rank, local      # rank 0 alone works; no process group needed
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    elif torch.cuda.is_available():
+        torch.cuda.set_device(0)
+    return world, rank, local
+
+
+def barrier_sync(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(ms, world):
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return ms
+
+
+def make_engine(local):
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    eng = DeviceMLP(SIZES, StackSpec.from_algos(ALGOS), True, "float32", local)
+    params = init_params(SIZES, seed=0)
+    for l in range(3):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    return eng
+
+
+def synth_pool(n_batches, batch, device, seed):
+    g = torch.Generator(device=device).manual_seed(seed)
+    xs = torch.randn((n_batches, batch, 784), generator=g, device=device, dtype=torch.float32)
+    ys = torch.randint(0, 10, (n_batches, batch), generator=g, device=device, dtype=torch.int32)
+    return xs, ys
+
+
+# ---- kernel-level algorithmic work, for the roofline of the dominant kernel ------------------------
+def kernel_work(tag, batch):
+    """(algorithmic bytes, flops) of one launch of kernel `tag` at C2 shapes (fp32)."""
+    if tag[:5] in ("fwd_l", "bwd_w", "bwd_x"):
+        l = int(tag.rsplit("l", 1)[1])
+        k, n = SIZES[l], SIZES[l + 1]
+        if tag.startswith("fwd_l"):       # read X, [W;b]; write the recorded output
+            return 4 * (batch * k + (k + 1) * n + batch * n), 2 * batch * (k + 1) * n
+        if tag.startswith("bwd_w"):       # read X, dZ; write [dW;db]
+            return 4 * (batch * k + batch * n + (k + 1) * n), 2 * batch * (k + 1) * n
+        return 4 * (batch * n + k * n + 2 * batch * k), 2 * batch * k * n     # read dZ, W, a_prev; write dZ_prev
+    if tag == "update":                   # read g, P, m, v; write P, m, v
+        return 4 * 7 * N_PARAMS, 12 * N_PARAMS
+    if tag == "loss":
+        return 4 * (3 * batch * 10 + batch), 40 * batch
+    return 0, 0
+
+
+def run_c2(args, world, rank, local):
+    from penr_oz_neural_network_torch_b200 import HostBatchFeeder, launch_count
+    dev = torch.device("cuda", local)
+    eng = make_engine(local)
+    batch = C2_BATCH
+    n_pool = 64                                    # 64 x 3.2 MB = 205 MB of inputs > 126 MB L2
+    xs, ys = synth_pool(n_pool, batch, dev, 1234 + rank)
+    total = args.warmup + args.steps
+    eng.train_begin(optimizer="adam", epochs=total + 8, **HP)
+    for i in range(args.warmup):
+        eng.train_step(xs[i % n_pool], ys[i % n_pool])
+    barrier_sync(world)
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    l0 = launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        j = (args.warmup + i) % n_pool
+        eng.train_step(xs[j], ys[j])
+    e1.record()
+    barrier_sync(world)
+    launches = launch_count() - l0
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    costs = eng.costs(args.warmup, args.steps)
+    assert np.isfinite(costs).all(), "non-finite training cost"
+
+    # ---- e2e: host buffers in, cost out, every step --------------------------------------------------
+    n_host = 8
+    hx = [torch.randn((batch, 784), dtype=torch.float32).pin_memory() for _ in range(n_host)]
+    hy = [torch.randint(0, 10, (batch,), dtype=torch.int32).pin_memory() for _ in range(n_host)]
+    e2e_steps = args.steps
+    eng.train_begin(optimizer="adam", epochs=args.warmup + e2e_steps + 8, **HP)
+    feeder = HostBatchFeeder(eng, batch)
+    feeder.stage(hx[0], hy[0])
+    for i in range(args.warmup):
+        feeder.step(i)
+        feeder.stage(hx[(i + 1) % n_host], hy[(i + 1) % n_host])
+        feeder.cost(i)
+    barrier_sync(world)
+    t0 = time.perf_counter()
+    last = 0.0
+    for i in range(e2e_steps):
+        k = args.warmup + i
+        feeder.step(k)
+        feeder.stage(hx[(k + 1) % n_host], hy[(k + 1) % n_host])
+        last = feeder.cost(k)
+    barrier_sync(world)
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
+    assert np.isfinite(last)
+    clocks = sampler.stop() if sampler else None
+
+    # ---- per-kernel timing pass (CUDA events inside the library, on the launching stream) -----------
+    roof = None
+    if rank == 0:
+        pk = peaks()
+        prof_steps = 50
+        eng.train_begin(optimizer="adam", epochs=prof_steps + 8, **HP)
+        for i in range(4):
+            eng.train_step(xs[i], ys[i])
+        eng.profile_begin()
+        for i in range(prof_steps):
+            eng.train_step(xs[(7 * i) % n_pool], ys[(7 * i) % n_pool])
+        prof = eng.profile_end()
+        tot = sum(v["ms"] for v in prof.values())
+        top = max(prof, key=lambda t: prof[t]["ms"])
+        per_launch_s = prof[top]["ms"] / prof[top]["launches"] * 1e-3
+        nbytes, flops = kernel_work(top, batch)
+        gbs = nbytes / per_launch_s / 1e9
+        roof = {"bound": "hbm", "kernel": top, "achieved": round(gbs, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": round(gbs / pk["hbm_gbs"], 4), "traffic": None, "peak_source": pk["source"],
+                "us_per_launch": round(per_launch_s * 1e6, 2), "share_of_step": round(prof[top]["ms"] / tot, 3),
+                "algorithmic_bytes_per_launch": nbytes,
+                "fp32_fma": {"achieved_tflops": round(flops / per_launch_s / 1e12, 2), "nominal_peak_tflops": 74.4,
+                             "frac": round(flops / per_launch_s / 74.4e12, 4),
+                             "note": "the binding bound of this SIMT kernel is the fp32 FMA pipe, not HBM"},
+                "step": {"algorithmic_bytes": C2_STEP_BYTES, "flops": C2_STEP_FLOPS,
+                         "hbm_frac": round(C2_STEP_BYTES / (ms / args.steps * 1e-3) / 1e9 / pk["hbm_gbs"], 4),
+                         "fp32_fma_frac": round(C2_STEP_FLOPS / (ms / args.steps * 1e-3) / 74.4e12, 4)},
+                "kernels_us": {t: round(v["ms"] / v["launches"] * 1e3, 2) for t, v in prof.items()}}
+    eng.close()
+    return dict(metric="train samples/s (fwd+bwd+step)", unit="samples/s",
+                value=world * batch * args.steps / (ms * 1e-3), ms_per_step=ms / args.steps,
+                e2e={"value": world * batch * e2e_steps / (e2e_ms * 1e-3), "unit": "samples/s",
+                     "h2d_bytes_per_step": feeder.h2d_bytes, "d2h_bytes_per_step": feeder.d2h_bytes,
+                     "ms_per_step": e2e_ms / e2e_steps},
+                gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
+                config={"workload": "c2: MLP 784-256-128-10 relu/relu/softmax + cross-entropy, Adam, L2 1e-3, "
+                                    "batch 1024, fp32 train step", "batch_per_gpu": batch,
+                        "global_batch": batch * world, "parallelism": f"replicas x{world}" if world > 1 else "single",
+                        "dropout": 0.0, "l2_flush": "inputs cycle through a 205 MB pool (> 126 MB L2); parameters "
+                                                    "stay cache-resident as in real training"})
+
+
+def run_c3(args, world, rank, local):
+    """Batched inference (BASELINE.json configs[2]) at one batch size (--batch, default 262144)."""
+    from penr_oz_neural_network_torch_b200 import launch_count
+    dev = torch.device("cuda", local)
+    eng = make_engine(local)
+    batch = args.batch or 262144
+    n_pool = max(2, int(np.ceil(260e6 / (batch * 784 * 4))))
+    n_pool = min(n_pool, 64)
+    g = torch.Generator(device=dev).manual_seed(99 + rank)
+    xs = torch.randn((n_pool, batch, 784), generator=g, device=dev, dtype=torch.float32)
+    out = torch.empty((batch, 10), device=dev, dtype=torch.float32)
+    for i in range(args.warmup):
+        eng.forward(xs[i % n_pool], out)
+    barrier_sync(world)
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    l0 = launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        eng.forward(xs[(args.warmup + i) % n_pool], out)
+    e1.record()
+    barrier_sync(world)
+    launches = launch_count() - l0
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    # e2e: pinned host batch in, probabilities out
+    hx = torch.randn((batch, 784), dtype=torch.float32).pin_memory()
+    ho = torch.empty((batch, 10), dtype=torch.float32).pin_memory()
+    xd = torch.empty((batch, 784), device=dev, dtype=torch.float32)
+    e2e_steps = max(3, min(args.steps, 20))
+    for _ in range(2):
+        xd.copy_(hx, non_blocking=True); eng.forward(xd, out); ho.copy_(out, non_blocking=True)
+    barrier_sync(world)
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        xd.copy_(hx, non_blocking=True); eng.forward(xd, out); ho.copy_(out, non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
+    clocks = sampler.stop() if sampler else None
+    roof = None
+    if rank == 0:
+        pk = peaks()
+        eng.profile_begin()
+        for i in range(5):
+            eng.forward(xs[i % n_pool], out)
+        prof = eng.profile_end()
+        tot = sum(v["ms"] for v in prof.values())
+        top = max(prof, key=lambda t: prof[t]["ms"])
+        per = ms / args.steps * 1e-3
+        roof = {"bound": "hbm", "kernel": "whole forward pass (all layer kernels of one call)",
+                "achieved": round(batch * C3_BYTES_PER_SAMPLE / per / 1e9, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": round(batch * C3_BYTES_PER_SAMPLE / per / 1e9 / pk["hbm_gbs"], 4), "traffic": None,
+                "peak_source": pk["source"], "top_kernel": top, "share_of_step": round(prof[top]["ms"] / tot, 3),
+                "fp32_fma": {"achieved_tflops": round(batch * C3_FLOPS_PER_SAMPLE / per / 1e12, 2),
+                             "nominal_peak_tflops": 74.4,
+                             "frac": round(batch * C3_FLOPS_PER_SAMPLE / per / 74.4e12, 4)},
+                "kernels_ms": {t: round(v["ms"] / 5, 4) for t, v in prof.items()}}
+    eng.close()
+    return dict(metric="infer samples/s", unit="samples/s", value=world * batch * args.steps / (ms * 1e-3),
+                ms_per_step=ms / args.steps,
+                e2e={"value": world * batch * e2e_steps / (e2e_ms * 1e-3), "unit": "samples/s",
+                     "h2d_bytes_per_step": batch * 784 * 4, "d2h_bytes_per_step": batch * 10 * 4,
+                     "ms_per_step": e2e_ms / e2e_steps},
+                gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
+                config={"workload": f"c3: batched inference 784-256-128-10, batch {batch}, fp32",
+                        "batch_per_gpu": batch, "global_batch": batch * world,
+                        "parallelism": f"replicas x{world}" if world > 1 else "single",
+                        "l2_flush": f"inputs cycle through a {n_pool * batch * 784 * 4 / 1e6:.0f} MB pool (> L2)"})
+
+
+# ---- CPU arms -------------------------------------------------------------------------------------------
+def cpu_train_c2(seconds, max_steps=None, threads=None):
+    """The reference's torch-CPU path (oracle/torch_cpu_port.py, fp64 as the reference ships) at C2
+    shapes on this box's host cores.  Returns (samples/s, steps timed, threads)."""
+    from oracle.torch_cpu_port import TorchCpuMLP
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    params = init_params(SIZES, seed=0)
+    m = TorchCpuMLP(ALGOS, params, "adam")
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn((C2_BATCH, 784), generator=g, dtype=torch.float64)
+    y = torch.randint(0, 10, (C2_BATCH,), generator=g, dtype=torch.int64)
+    for i in range(2):
+        m.train_step(x, y, 0.01, l2_lambda=0.001)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        m.train_step(x, y, 0.01 * 0.9 ** min(n, 50), l2_lambda=0.001)
+        n += 1
+        el = time.perf_counter() - t0
+        if (max_steps and n >= max_steps) or (not max_steps and el >= seconds) or el > 120:
+            break
+    return C2_BATCH * n / el, n, threads, el
+
+
+def cpu_infer_c3(batch, seconds, threads=None):
+    from oracle.torch_cpu_port import TorchCpuMLP
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    m = TorchCpuMLP(ALGOS, init_params(SIZES, seed=0), "adam")
+    b = min(batch, 65536)
+    x = torch.randn((b, 784), dtype=torch.float64)
+    m.forward(x)
+    n, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < seconds:
+        m.forward(x)       # the reference does not wrap inference in no_grad (neural_net_model.py:379-380)
+        n += 1
+    el = time.perf_counter() - t0
+    return b * n / el, n, threads, el, b
+
+
+def run_reference(args, world, rank):
+    if rank != 0:
+        return None
+    if args.workload == "c3":
+        batch = args.batch or 262144
+        v, n, thr, el, b = cpu_infer_c3(batch, 10.0)
+        return dict(impl="reference", metric="infer samples/s", unit="samples/s", value=v, n_gpus=args.gpus,
+                    steps=n, warmup=1, ms_per_step=el / n * 1e3, higher_is_better=True, scaling="weak",
+                    vs_baseline=None, dtype="f64", data="synthetic",
+                    config={"workload": f"c3: batched inference 784-256-128-10, batch {batch}, fp32"},
+                    cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
+                                  "sample": f"{n} forward passes of {b} rows, torch CPU fp64 (oracle/torch_cpu_port.py)"},
+                    e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+    steps = max(1, min(args.steps, 2000))
+    v, n, thr, el = cpu_train_c2(0, max_steps=steps)
+    return dict(impl="reference", metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v,
+                n_gpus=args.gpus, steps=n, warmup=2, ms_per_step=el / n * 1e3, higher_is_better=True,
+                scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
+                config={"workload": "c2: MLP 784-256-128-10 relu/relu/softmax + cross-entropy, Adam, L2 1e-3, "
+                                    "batch 1024, fp32 train step"},
+                cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
+                              "sample": f"{n} train steps of batch 1024, torch CPU fp64, the reference's operator "
+                                        "sequence (oracle/torch_cpu_port.py)"},
+                e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3"])
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    world, rank, local = dist_setup(args)
+
+    if args.impl == "reference":
+        line = run_reference(args, world, rank)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback); "
+                         "use --impl reference for the CPU arm")
+    res = (run_c2 if args.workload == "c2" else run_c3)(args, world, rank, local)
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            if args.workload == "c2":
+                v, n, thr, el = cpu_train_c2(12.0)
+                cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
+                       "sample": f"{n} train steps of batch 1024 in {el:.1f} s, torch CPU fp64, the reference's "
+                                 "operator sequence (oracle/torch_cpu_port.py)"}
+            else:
+                v, n, thr, el, b = cpu_infer_c3(args.batch or 262144, 10.0)
+                cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
+                       "sample": f"{n} forward passes of {b} rows in {el:.1f} s, torch CPU fp64"}
+        line = dict(metric=res["metric"], value=res["value"], unit=res["unit"], n_gpus=world, steps=args.steps,
+                    warmup=args.warmup, ms_per_step=res["ms_per_step"], higher_is_better=True, scaling="weak",
+                    vs_baseline=None, dtype=res["dtype"], data="synthetic", config=res["config"], e2e=res["e2e"],
+                    gpu_launches=res["gpu_launches"], clocks=res["clocks"], roofline=res["roofline"],
+                    cpu_baseline=cpu, impl="native")
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,141 @@
+/*
+ * pozmlp.h -- C ABI of the B200-native NeuralNetworkModel hot path.
+ *
+ * The reference (derinworks/penr-oz-neural-network-torch) is pure Python and has no FFI of its
+ * own; its hot path sits behind the methods of class NeuralNetworkModel.  Each entry point below
+ * names the reference code it replaces (file:line in the reference repository).  The Python class
+ * in penr_oz_neural_network_torch_b200/neural_net_model.py binds these with ctypes and is the
+ * only caller; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; poz_last_error() then returns a
+ *     thread-local message.  Nothing aborts the process.
+ *   - pointers are borrowed for the duration of the call; the context owns device parameters,
+ *     optimizer state and workspace.
+ *   - "stack" = n_linear Linear layers, layer l mapping sizes[l] -> sizes[l+1], each optionally
+ *     followed by one activation (POZ_ACT_*).  Weights use the reference layout W[in][out]
+ *     row-major (neural_net_model.py:104), bias[out] (:106-108).
+ *   - host parameter/optimizer images are always float64 (the reference's dtype); the context
+ *     converts to its compute dtype on upload and back on download.
+ *   - device batch buffers use the compute dtype of the context: float (POZ_DTYPE_F32), double
+ *     (POZ_DTYPE_F64) or __nv_bfloat16 (POZ_DTYPE_BF16); labels are int32.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - all entry points are re-entrant across contexts; one context must not be used from two
+ *     threads at once (the reference holds a per-model lock around train, main.py:264-283).
+ */
+#ifndef POZMLP_H
+#define POZMLP_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct poz_ctx poz_ctx;
+
+enum { POZ_ACT_NONE = 0, POZ_ACT_RELU = 1, POZ_ACT_SIGMOID = 2, POZ_ACT_TANH = 3, POZ_ACT_SOFTMAX = 4 };
+enum { POZ_LOSS_MSE = 0, POZ_LOSS_CE = 1 };
+enum { POZ_DTYPE_F32 = 0, POZ_DTYPE_F64 = 1, POZ_DTYPE_BF16 = 2 };
+enum { POZ_OPT_SGD = 0, POZ_OPT_ADAM = 1 };
+
+/* Hyper-parameters of one train() call: the keyword arguments of
+ * NeuralNetworkModel.train (neural_net_model.py:410-411) plus the optimizer choice (:279-283). */
+typedef struct poz_train_config {
+    int       optimizer;        /* POZ_OPT_* */
+    double    learning_rate;    /* lr_t = learning_rate * decay_rate**epoch, neural_net_model.py:464 */
+    double    decay_rate;
+    double    dropout_rate;     /* F.dropout p on every hidden entry, neural_net_model.py:393-395 */
+    double    l2_lambda;        /* cost += l2 * sum(w**2) over weights, neural_net_model.py:482-483 */
+    double    beta1, beta2, epsilon;   /* Adam param_groups, neural_net_model.py:445-448 */
+    long long epochs;           /* number of steps this call will run (sizes the cost ring) */
+    long long progress_stride;  /* weight-update ratio recorded when epoch % stride == 0 (:504); 0 = never */
+    unsigned long long dropout_seed;   /* Philox key for in-kernel masks (perf mode) */
+    long long global_batch;     /* data-parallel: loss mean is over this many rows; 0 = local batch */
+} poz_train_config;
+
+/* ---- library ---------------------------------------------------------------------------- */
+const char* poz_last_error(void);
+int         poz_version(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+long long   poz_launch_count(void);
+
+/* Per-kernel device timing (new; used by bench.py for the roofline of the dominant kernel).
+ * Between begin and end every kernel launch of the context is bracketed by CUDA events on the
+ * launching stream; end synchronises and writes {"<kernel tag>": {"launches": n, "ms": total}, ...}. */
+int poz_profile_begin(poz_ctx* ctx);
+int poz_profile_end(poz_ctx* ctx, char* json_out, long long cap);
+
+/* ---- context = device image of one NeuralNetworkModel -------------------------------------
+ * Replaces the parameter containers Layer.params / MultiLayerPerceptron.params
+ * (neural_net_model.py:24-31,262-267) and torch.optim.Adam's state (:279-283).
+ * drop_z[l] / drop_a[l]: the reference's `hidden` flag (neural_net_model.py:255) of the Linear
+ * entry / of the activation entry that follows it -- the places where dropout is applied. */
+int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_codes,
+                   const unsigned char* drop_z, const unsigned char* drop_a,
+                   int has_bias, int loss_code, int dtype_code, poz_ctx** out);
+int poz_ctx_destroy(poz_ctx* ctx);
+/* Grow the workspace for batches of up to max_batch rows (otherwise grown on demand). */
+int poz_ctx_reserve(poz_ctx* ctx, long long max_batch, int for_training);
+
+/* Layer.state_dict setter / getter (neural_net_model.py:33-45): float64 host images. */
+int poz_params_upload(poz_ctx* ctx, int layer, const double* w, const double* b);
+int poz_params_download(poz_ctx* ctx, int layer, double* w, double* b);
+/* torch.optim.Adam state_dict()/load_state_dict() (neural_net_model.py:338-341,351-354):
+ * exp_avg / exp_avg_sq per parameter tensor and the shared step count. */
+int poz_adam_upload(poz_ctx* ctx, int layer, const double* m_w, const double* v_w,
+                    const double* m_b, const double* v_b);
+int poz_adam_download(poz_ctx* ctx, int layer, double* m_w, double* v_w, double* m_b, double* v_b);
+int poz_adam_set_step(poz_ctx* ctx, long long step);
+int poz_adam_get_step(poz_ctx* ctx, long long* step);
+
+/* ---- inference: NeuralNetworkModel._forward without target + compute_output
+ * (neural_net_model.py:371-396; LinearLayer.forward :110-120; activations :172-188).
+ * x_dev [batch][sizes[0]] row-major, out_dev [batch][sizes[n_linear]]; both device memory. */
+int poz_forward(poz_ctx* ctx, const void* x_dev, long long batch, void* out_dev, void* stream);
+/* Same with the loss (neural_net_model.py:398-406).  target_dev: int32 labels [batch] for
+ * POZ_LOSS_CE, compute-dtype [batch][out] for POZ_LOSS_MSE.  cost_host receives the scalar
+ * (the call synchronises the stream to deliver it). */
+int poz_forward_loss(poz_ctx* ctx, const void* x_dev, const void* target_dev, long long batch,
+                     void* out_dev, double* cost_host, void* stream);
+
+/* ---- training: the loop body of NeuralNetworkModel.train (neural_net_model.py:459-500) ------
+ * poz_train_begin  = the per-call set-up (:444-448, epoch counter reset).
+ * poz_train_step   = one epoch: forward (:480), L2 (:482-483), backward (:495), optimizer
+ *                    (:496-500).  row_idx_dev (int32 [batch], may be NULL) gathers the batch rows
+ *                    from x_dev/target_dev in place of the reference's list indexing (:460-461).
+ *                    keep_masks (may be NULL): host array of 2*n_linear device pointers
+ *                    (uint8 [batch][out] keep-masks for the z and a dropout points of each layer,
+ *                    NULL entries = draw in-kernel) -- used for bit-parity with a recorded
+ *                    torch mask stream.  diagnostics != 0 keeps every entry's output, its
+ *                    gradient and the weight gradients of this step (:491-493) for download.
+ * poz_train_costs  = cost.item() of epochs [first, first+count) (:503); synchronises.
+ * poz_train_update_ratios = sum statistics behind weight_upd_ratio (:506-507). */
+int poz_train_begin(poz_ctx* ctx, const poz_train_config* cfg);
+int poz_train_step(poz_ctx* ctx, const void* x_dev, const void* target_dev, const int* row_idx_dev,
+                   long long batch, const void* const* keep_masks, int diagnostics, void* stream);
+int poz_train_costs(poz_ctx* ctx, long long first, long long count, double* costs_host, void* stream);
+/* ratios_host [count][n_linear]: std(w_new - w_old) / (std(w_new) + 1e-8), unbiased std. */
+int poz_train_update_ratios(poz_ctx* ctx, long long first_record, long long count,
+                            double* ratios_host, void* stream);
+
+/* Diagnostics of the last step run with diagnostics != 0 (feeds the unchanged
+ * _record_training_overall_progress, neural_net_model.py:532-583).  `entry` counts the
+ * reference's layer list: for linear l, which = 0 is the Linear entry, which = 1 its activation. */
+int poz_diag_activation(poz_ctx* ctx, int layer, int which, double* host_out);
+int poz_diag_activation_grad(poz_ctx* ctx, int layer, int which, double* host_out, int* has_grad);
+int poz_diag_weight_grad(poz_ctx* ctx, int layer, double* w_grad, double* b_grad);
+
+/* ---- data parallel (new: the reference is single-process) --------------------------------
+ * The flat gradient image (all layers, compute dtype... always float32/float64) that the host
+ * all-reduces with NCCL between the backward and the update of a step. */
+int poz_grad_buffer(poz_ctx* ctx, void** dev_ptr, long long* n_elems, int* dtype_code, void* stream);
+/* Split step for data parallelism: backward leaves SUM-ready local gradients (already scaled by
+ * 1/global_batch) in the flat buffer; the caller all-reduces; poz_train_apply runs the update. */
+int poz_train_backward(poz_ctx* ctx, const void* x_dev, const void* target_dev,
+                       const int* row_idx_dev, long long batch, const void* const* keep_masks,
+                       int diagnostics, void* stream);
+int poz_train_apply(poz_ctx* ctx, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POZMLP_H */

@@ -1,0 +1,9 @@
+"""B200-native hot path of derinworks/penr-oz-neural-network-torch (train step + batched inference).
+
+``from penr_oz_neural_network_torch_b200 import NeuralNetworkModel`` is the drop-in for the
+reference's ``from neural_net_model import NeuralNetworkModel``.
+"""
+from ._native import PozError, build, launch_count  # noqa: F401
+from .engine import DeviceMLP, HostBatchFeeder, StackSpec  # noqa: F401
+from .neural_net_model import (Layer, LinearLayer, MultiLayerPerceptron, NeuralNetworkModel,  # noqa: F401
+                               ReluLayer, SigmoidLayer, SoftmaxLayer, TanhLayer)

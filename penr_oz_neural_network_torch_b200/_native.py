@@ -1,0 +1,141 @@
+"""ctypes binding of libpozmlp.so (the C ABI declared in include/pozmlp.h).
+
+There is no CPU or PyTorch fallback: if the shared library is missing, or an entry point fails,
+this module raises.  ``build()`` compiles the library in-tree for sm_100a.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(_HERE, "libpozmlp.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "pozmlp.h")
+
+ACT_CODES = {"none": 0, "relu": 1, "sigmoid": 2, "tanh": 3, "softmax": 4}
+LOSS_MSE, LOSS_CE = 0, 1
+DTYPE_F32, DTYPE_F64, DTYPE_BF16 = 0, 1, 2
+OPT_SGD, OPT_ADAM = 0, 1
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+SOURCES = ["poz_api.cu"]
+
+
+class PozError(RuntimeError):
+    """A C-ABI call returned non-zero; the message is poz_last_error()."""
+
+
+class TrainConfig(C.Structure):
+    _fields_ = [
+        ("optimizer", C.c_int),
+        ("learning_rate", C.c_double),
+        ("decay_rate", C.c_double),
+        ("dropout_rate", C.c_double),
+        ("l2_lambda", C.c_double),
+        ("beta1", C.c_double),
+        ("beta2", C.c_double),
+        ("epsilon", C.c_double),
+        ("epochs", C.c_longlong),
+        ("progress_stride", C.c_longlong),
+        ("dropout_seed", C.c_ulonglong),
+        ("global_batch", C.c_longlong),
+    ]
+
+
+def _sources():
+    return [os.path.join(_CSRC, s) for s in SOURCES]
+
+
+def _stale() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    built = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC)] + [HEADER_PATH]
+    return any(os.path.getmtime(d) > built for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile libpozmlp.so in-tree with nvcc for sm_100a (cross-compiles without a GPU)."""
+    if not force and not _stale():
+        return LIB_PATH
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + _sources() + ["-o", LIB_PATH]
+    if verbose:
+        cmd.insert(1, "-Xptxas")
+        cmd.insert(2, "-v")
+    proc = subprocess.run(cmd, capture_output=True, text=True)
+    if proc.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+    if verbose:
+        print(proc.stderr)
+    return LIB_PATH
+
+
+_lib = None
+_lock = threading.Lock()
+
+_VP, _LL, _I, _DP = C.c_void_p, C.c_longlong, C.c_int, C.POINTER(C.c_double)
+
+# name -> (restype, argtypes); mirrors include/pozmlp.h one to one
+SIGNATURES = {
+    "poz_last_error": (C.c_char_p, []),
+    "poz_version": (_I, []),
+    "poz_launch_count": (_LL, []),
+    "poz_profile_begin": (_I, [_VP]),
+    "poz_profile_end": (_I, [_VP, C.c_char_p, _LL]),
+    "poz_ctx_create": (_I, [_I, _I, C.POINTER(_I), C.POINTER(_I), C.POINTER(C.c_ubyte),
+                            C.POINTER(C.c_ubyte), _I, _I, _I, C.POINTER(_VP)]),
+    "poz_ctx_destroy": (_I, [_VP]),
+    "poz_ctx_reserve": (_I, [_VP, _LL, _I]),
+    "poz_params_upload": (_I, [_VP, _I, _VP, _VP]),
+    "poz_params_download": (_I, [_VP, _I, _VP, _VP]),
+    "poz_adam_upload": (_I, [_VP, _I, _VP, _VP, _VP, _VP]),
+    "poz_adam_download": (_I, [_VP, _I, _VP, _VP, _VP, _VP]),
+    "poz_adam_set_step": (_I, [_VP, _LL]),
+    "poz_adam_get_step": (_I, [_VP, C.POINTER(_LL)]),
+    "poz_forward": (_I, [_VP, _VP, _LL, _VP, _VP]),
+    "poz_forward_loss": (_I, [_VP, _VP, _VP, _LL, _VP, _DP, _VP]),
+    "poz_train_begin": (_I, [_VP, C.POINTER(TrainConfig)]),
+    "poz_train_step": (_I, [_VP, _VP, _VP, _VP, _LL, C.POINTER(_VP), _I, _VP]),
+    "poz_train_costs": (_I, [_VP, _LL, _LL, _VP, _VP]),
+    "poz_train_update_ratios": (_I, [_VP, _LL, _LL, _VP, _VP]),
+    "poz_diag_activation": (_I, [_VP, _I, _I, _VP]),
+    "poz_diag_activation_grad": (_I, [_VP, _I, _I, _VP, C.POINTER(_I)]),
+    "poz_diag_weight_grad": (_I, [_VP, _I, _VP, _VP]),
+    "poz_grad_buffer": (_I, [_VP, C.POINTER(_VP), C.POINTER(_LL), C.POINTER(_I), _VP]),
+    "poz_train_backward": (_I, [_VP, _VP, _VP, _VP, _LL, C.POINTER(_VP), _I, _VP]),
+    "poz_train_apply": (_I, [_VP, _VP]),
+}
+
+
+def lib():
+    """The loaded library.  Raises if it has not been built -- there is no fallback path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise PozError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
+                               "g.build()'` (there is no CPU fallback for the hot path)")
+            handle = C.CDLL(LIB_PATH)
+            for name, (res, args) in SIGNATURES.items():
+                fn = getattr(handle, name)      # AttributeError if the symbol is not exported
+                fn.restype = res
+                fn.argtypes = args
+            _lib = handle
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = lib().poz_last_error()
+        raise PozError(msg.decode() if msg else f"pozmlp call failed with code {rc}")
+
+
+def launch_count() -> int:
+    return int(lib().poz_launch_count())

@@ -1,0 +1,889 @@
+// pozmlp C ABI (include/pozmlp.h): context management and the narrow SIMT path (fp32 / fp64).
+#include "../../include/pozmlp.h"
+#include "poz_ctx.h"
+#include "poz_kernels.cuh"
+#include "poz_simt_gemm.cuh"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace poz {
+
+static thread_local std::string t_error;
+void set_error(const std::string& msg) { t_error = msg; }
+static std::atomic<long long> s_launches{0};
+void count_launch(int n) { s_launches.fetch_add(n, std::memory_order_relaxed); }
+
+#define POZ_LAUNCH_CHECK()                                                                    \
+    do {                                                                                      \
+        poz::count_launch();                                                                  \
+        POZ_CUDA(cudaGetLastError());                                                         \
+    } while (0)
+
+static int num_sms(int device) {
+    static int cached[64] = {0};
+    if (device >= 0 && device < 64 && cached[device]) return cached[device];
+    int n = 148;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+    if (device >= 0 && device < 64) cached[device] = n;
+    return n;
+}
+
+// Brackets one launch with CUDA events when the context is in profiling mode (poz_profile_begin).
+struct ProfScope {
+    poz_ctx* c; cudaStream_t s; size_t idx = 0; bool on;
+    ProfScope(poz_ctx* ctx, const std::string& tag, cudaStream_t stream) : c(ctx), s(stream), on(ctx->profiling) {
+        if (!on) return;
+        poz_ctx::ProfRec r;
+        r.tag = tag;
+        cudaEventCreate(&r.a);
+        cudaEventCreate(&r.b);
+        cudaEventRecord(r.a, s);
+        c->prof.push_back(r);
+        idx = c->prof.size() - 1;
+    }
+    ~ProfScope() { if (on) cudaEventRecord(c->prof[idx].b, s); }
+};
+
+template <typename T> static Operand<T> make_operand(const T* ptr, long long ld, const int* row_idx,
+                                                     long long rows, int cols, int ones) {
+    Operand<T> o;
+    o.ptr = ptr; o.ld = ld; o.row_idx = row_idx; o.rows = rows; o.cols = cols; o.ones = ones;
+    constexpr int V = Vec16<T>::V;
+    o.vec_ok = ((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld % V) == 0) ? 1 : 0;
+    return o;
+}
+
+// ---- tile configurations -----------------------------------------------------------------------
+template <typename T> struct Tiles;
+template <> struct Tiles<float> {
+    // small: fills the GPU at batch ~1k; large: better reuse for big batches; thin: out <= 16
+    static constexpr int SM_BM = 32, SM_BN = 64, SM_BK = 16, SM_TM = 4, SM_TN = 4;
+    static constexpr int LG_BM = 128, LG_BN = 64, LG_BK = 16, LG_TM = 8, LG_TN = 4;
+    static constexpr int TH_BM = 64, TH_BN = 16, TH_BK = 16, TH_TM = 4, TH_TN = 4;
+};
+template <> struct Tiles<double> {
+    static constexpr int SM_BM = 32, SM_BN = 32, SM_BK = 8, SM_TM = 4, SM_TN = 2;
+    static constexpr int LG_BM = 64, LG_BN = 64, LG_BK = 8, LG_TM = 4, LG_TN = 4;
+    static constexpr int TH_BM = 64, TH_BN = 16, TH_BK = 8, TH_TM = 4, TH_TN = 2;
+};
+
+enum TileKind { TILE_SMALL, TILE_LARGE, TILE_THIN };
+
+template <typename T, bool A_KC, bool B_KC, class Epi>
+static int launch_gemm(TileKind kind, const Operand<T>& A, const Operand<T>& B, long long M, int N,
+                       long long Kd, int splits, long long k_chunk, const Epi& epi,
+                       cudaStream_t stream) {
+    using TL = Tiles<T>;
+    if (M <= 0 || N <= 0) return 0;
+    auto grid_for = [&](int BM, int BN) {
+        return dim3((unsigned)((N + BN - 1) / BN), (unsigned)((M + BM - 1) / BM), (unsigned)splits);
+    };
+    switch (kind) {
+        case TILE_LARGE: {
+            dim3 g = grid_for(TL::LG_BM, TL::LG_BN);
+            if (g.y > 65535) POZ_FAIL("gemm: too many row tiles for one launch");
+            gemm_simt_kernel<T, TL::LG_BM, TL::LG_BN, TL::LG_BK, TL::LG_TM, TL::LG_TN, A_KC, B_KC, Epi>
+                <<<g, (TL::LG_BM / TL::LG_TM) * (TL::LG_BN / TL::LG_TN), 0, stream>>>(A, B, M, N, Kd, k_chunk, epi);
+            break;
+        }
+        case TILE_THIN: {
+            dim3 g = grid_for(TL::TH_BM, TL::TH_BN);
+            if (g.y > 65535) POZ_FAIL("gemm: too many row tiles for one launch");
+            gemm_simt_kernel<T, TL::TH_BM, TL::TH_BN, TL::TH_BK, TL::TH_TM, TL::TH_TN, A_KC, B_KC, Epi>
+                <<<g, (TL::TH_BM / TL::TH_TM) * (TL::TH_BN / TL::TH_TN), 0, stream>>>(A, B, M, N, Kd, k_chunk, epi);
+            break;
+        }
+        default: {
+            dim3 g = grid_for(TL::SM_BM, TL::SM_BN);
+            if (g.y > 65535) POZ_FAIL("gemm: too many row tiles for one launch");
+            gemm_simt_kernel<T, TL::SM_BM, TL::SM_BN, TL::SM_BK, TL::SM_TM, TL::SM_TN, A_KC, B_KC, Epi>
+                <<<g, (TL::SM_BM / TL::SM_TM) * (TL::SM_BN / TL::SM_TN), 0, stream>>>(A, B, M, N, Kd, k_chunk, epi);
+            break;
+        }
+    }
+    POZ_LAUNCH_CHECK();
+    return 0;
+}
+
+template <typename T> static TileKind pick_tile(const poz_ctx* c, long long M, int N) {
+    using TL = Tiles<T>;
+    if (N <= 16) return TILE_THIN;
+    long long small_ctas = ((M + TL::SM_BM - 1) / TL::SM_BM) * ((N + TL::SM_BN - 1) / TL::SM_BN);
+    return small_ctas >= 8LL * num_sms(c->device) ? TILE_LARGE : TILE_SMALL;
+}
+
+// ---- memory helpers ----------------------------------------------------------------------------
+static int dev_alloc(void** p, size_t bytes) {
+    *p = nullptr;
+    if (bytes == 0) return 0;
+    POZ_CUDA(cudaMalloc(p, bytes));
+    return 0;
+}
+static void dev_free(void*& p) {
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+
+static DropPoint make_drop(const poz_ctx* c, int layer, int which, const void* const* masks) {
+    DropPoint d{};
+    const bool flag = which == 0 ? c->drop_z[layer] : c->drop_a[layer];
+    const double p = c->cfg.dropout_rate;
+    d.enabled = (flag && c->training_pass && p > 0.0) ? 1 : 0;
+    d.mask = (d.enabled && masks) ? static_cast<const uint8_t*>(masks[2 * layer + which]) : nullptr;
+    d.point = (uint32_t)(2 * layer + which);
+    d.keep_prob = (float)(1.0 - p);
+    d.scale = (float)(1.0 / (1.0 - p));
+    return d;
+}
+
+static int ensure_stage(poz_ctx* c, size_t elems) {
+    if (c->stage_elems >= elems) return 0;
+    dev_free(reinterpret_cast<void*&>(c->stage));
+    POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->stage), elems * sizeof(double)));
+    c->stage_elems = elems;
+    return 0;
+}
+
+// host float64 image -> device compute dtype at flat offset `off`
+template <typename T> static int put_f64(poz_ctx* c, void* dst_base, long long off, const double* src, long long n) {
+    if (n <= 0) return 0;
+    T* dst = static_cast<T*>(dst_base) + off;
+    if (sizeof(T) == sizeof(double)) {
+        POZ_CUDA(cudaMemcpy(dst, src, n * sizeof(double), cudaMemcpyHostToDevice));
+        return 0;
+    }
+    POZ_TRY(ensure_stage(c, (size_t)n));
+    POZ_CUDA(cudaMemcpy(c->stage, src, n * sizeof(double), cudaMemcpyHostToDevice));
+    int blocks = (int)std::min<long long>((n + 255) / 256, 4096);
+    convert_kernel<double, T><<<blocks, 256>>>(c->stage, dst, n);
+    POZ_LAUNCH_CHECK();
+    POZ_CUDA(cudaDeviceSynchronize());
+    return 0;
+}
+template <typename T> static int get_f64(poz_ctx* c, const void* src_base, long long off, double* dst, long long n) {
+    if (n <= 0) return 0;
+    const T* src = static_cast<const T*>(src_base) + off;
+    POZ_CUDA(cudaDeviceSynchronize());
+    if (sizeof(T) == sizeof(double)) {
+        POZ_CUDA(cudaMemcpy(dst, src, n * sizeof(double), cudaMemcpyDeviceToHost));
+        return 0;
+    }
+    POZ_TRY(ensure_stage(c, (size_t)n));
+    int blocks = (int)std::min<long long>((n + 255) / 256, 4096);
+    convert_kernel<T, double><<<blocks, 256>>>(src, c->stage, n);
+    POZ_LAUNCH_CHECK();
+    POZ_CUDA(cudaMemcpy(dst, c->stage, n * sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+#define POZ_DISPATCH(c, fn, ...)                                                              \
+    ((c)->dtype == POZ_DTYPE_F64 ? fn<double>(__VA_ARGS__) : fn<float>(__VA_ARGS__))
+
+// ---- workspace ---------------------------------------------------------------------------------
+static void free_workspace(poz_ctx* c) {
+    for (auto& p : c->zbuf) dev_free(p);
+    for (auto& p : c->abuf) dev_free(p);
+    for (auto& p : c->dzbuf) dev_free(p);
+    for (auto& p : c->dz_rec) dev_free(p);
+    for (auto& p : c->da_rec) dev_free(p);
+    dev_free(c->ping);
+    dev_free(c->pong);
+    c->ws_train = 0;
+    c->ws_infer = 0;
+    c->ws_diag = 0;
+}
+
+static int reserve_train(poz_ctx* c, long long batch, bool diag) {
+    const int nl = c->nl;
+    if (batch > c->ws_train) {
+        for (int l = 0; l < nl; ++l) {
+            dev_free(c->zbuf[l]); dev_free(c->abuf[l]); dev_free(c->dzbuf[l]);
+            dev_free(c->dz_rec[l]); dev_free(c->da_rec[l]);
+        }
+        c->ws_diag = 0;
+        for (int l = 0; l < nl; ++l) {
+            size_t bytes = (size_t)batch * c->sizes[l + 1] * c->esz;
+            POZ_TRY(dev_alloc(&c->abuf[l], bytes));
+            POZ_TRY(dev_alloc(&c->dzbuf[l], bytes));
+            if (c->acts[l] != ACT_NONE) POZ_TRY(dev_alloc(&c->zbuf[l], bytes));
+        }
+        c->ws_train = batch;
+    }
+    if (diag && c->ws_diag < c->ws_train) {
+        for (int l = 0; l < nl; ++l) {
+            size_t bytes = (size_t)c->ws_train * c->sizes[l + 1] * c->esz;
+            dev_free(c->dz_rec[l]); dev_free(c->da_rec[l]);
+            POZ_TRY(dev_alloc(&c->dz_rec[l], bytes));
+            if (c->acts[l] != ACT_NONE) POZ_TRY(dev_alloc(&c->da_rec[l], bytes));
+        }
+        c->ws_diag = c->ws_train;
+    }
+    return 0;
+}
+
+static int reserve_infer(poz_ctx* c, long long chunk) {
+    if (chunk <= c->ws_infer) return 0;
+    dev_free(c->ping);
+    dev_free(c->pong);
+    int widest = 0;
+    for (int l = 1; l <= c->nl; ++l) widest = std::max(widest, c->sizes[l]);
+    size_t bytes = (size_t)chunk * widest * c->esz;
+    POZ_TRY(dev_alloc(&c->ping, bytes));
+    POZ_TRY(dev_alloc(&c->pong, bytes));
+    c->ws_infer = chunk;
+    return 0;
+}
+
+static int ensure_grad_slabs(poz_ctx* c, int slabs) {
+    if (slabs <= c->g_slabs) return 0;
+    dev_free(c->G);
+    POZ_TRY(dev_alloc(&c->G, (size_t)slabs * c->p_total * c->esz));
+    c->g_slabs = slabs;
+    return 0;
+}
+
+// ---- forward of one layer ------------------------------------------------------------------------
+template <typename T>
+static int layer_forward(poz_ctx* c, int l, const T* x, const int* row_idx, long long x_rows,
+                         long long M, T* z_out, T* a_out, const void* const* masks,
+                         cudaStream_t stream) {
+    const int K = c->sizes[l], N = c->sizes[l + 1];
+    const int hb = c->has_bias;
+    (void)x_rows;
+    Operand<T> A = make_operand<T>(x, K, row_idx, M, K, hb);
+    const T* w = static_cast<const T*>(c->P) + c->off[l];
+    Operand<T> B = make_operand<T>(w, N, nullptr, K + hb, N, 0);
+    FwdEpi<T> epi;
+    epi.z_out = z_out; epi.a_out = a_out; epi.ld = N; epi.act = c->acts[l];
+    epi.dz = make_drop(c, l, 0, masks);
+    epi.da = make_drop(c, l, 1, masks);
+    epi.st = c->st;
+    ProfScope ps(c, "fwd_l" + std::to_string(l), stream);
+    return launch_gemm<T, true, false>(pick_tile<T>(c, M, N), A, B, M, N, (long long)K + hb, 1,
+                                       (long long)K + hb, epi, stream);
+}
+
+template <typename T> static int run_softmax(poz_ctx* c, const T* z, T* out, long long M, int N, cudaStream_t s) {
+    ProfScope ps(c, "softmax", s);
+    int blocks = (int)std::min<long long>((M + 7) / 8, 148 * 8);
+    softmax_kernel<T><<<std::max(blocks, 1), 256, 0, s>>>(z, out, M, N);
+    POZ_LAUNCH_CHECK();
+    return 0;
+}
+
+template <typename T>
+static int run_loss(poz_ctx* c, LossArgs<T>& a, cudaStream_t s) {
+    ProfScope ps(c, "loss", s);
+    if (c->loss == POZ_LOSS_CE) {
+        int blocks = (int)std::min<long long>((a.M + 7) / 8, 148 * 8);
+        ce_loss_kernel<T><<<std::max(blocks, 1), 256, 0, s>>>(a);
+    } else {
+        long long total = a.M * a.N;
+        int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 8);
+        mse_loss_kernel<T><<<std::max(blocks, 1), 256, 0, s>>>(a);
+    }
+    POZ_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---- inference -----------------------------------------------------------------------------------
+// Rows are processed in chunks small enough that the intermediate activations of a chunk stay in
+// the 126 MB L2 between the per-layer kernels instead of round-tripping through HBM.
+template <typename T>
+static int forward_impl(poz_ctx* c, const T* x, const void* target, long long batch, T* out,
+                        double* cost_host, cudaStream_t stream) {
+    const int nl = c->nl;
+    int widest = 0;
+    for (int l = 1; l <= nl; ++l) widest = std::max(widest, c->sizes[l]);
+    long long chunk = std::max<long long>(256, (24LL << 20) / ((long long)widest * sizeof(T)));
+    chunk = std::min(chunk, batch);
+    POZ_TRY(reserve_infer(c, chunk));
+    c->training_pass = false;
+    if (cost_host) POZ_CUDA(cudaMemsetAsync(c->scalar_cost, 0, sizeof(double), stream));
+    const int n_out = c->sizes[nl];
+    for (long long r0 = 0; r0 < batch; r0 += chunk) {
+        const long long m = std::min(chunk, batch - r0);
+        const T* cur = x + r0 * c->sizes[0];
+        T* bufs[2] = {static_cast<T*>(c->ping), static_cast<T*>(c->pong)};
+        int flip = 0;
+        for (int l = 0; l < nl; ++l) {
+            const bool last = l == nl - 1;
+            const bool softmax = c->acts[l] == ACT_SOFTMAX;
+            T* dst = (last && !softmax) ? out + r0 * n_out : bufs[flip];
+            // softmax units keep their logits; everything else only needs the activation output
+            POZ_TRY(layer_forward<T>(c, l, cur, nullptr, m, m, softmax ? dst : nullptr,
+                                     softmax ? nullptr : dst, nullptr, stream));
+            cur = dst;
+            flip ^= 1;
+        }
+        const bool softmax_last = c->acts[nl - 1] == ACT_SOFTMAX;
+        if (cost_host) {
+            LossArgs<T> a{};
+            a.z = cur;
+            a.M = m; a.N = n_out; a.act = c->acts[nl - 1];
+            a.cost_base = c->scalar_cost; a.cost_cap = 1; a.st = nullptr;
+            if (c->loss == POZ_LOSS_CE) {
+                a.target = static_cast<const int*>(target) + r0;
+                a.probs = out + r0 * n_out;
+                a.inv_count = 1.0 / (double)batch;
+            } else {
+                a.target = static_cast<const T*>(target) + r0 * n_out;
+                a.inv_count = 1.0 / ((double)batch * n_out);
+            }
+            POZ_TRY(run_loss<T>(c, a, stream));
+        } else if (softmax_last) {
+            POZ_TRY(run_softmax<T>(c, cur, out + r0 * n_out, m, n_out, stream));
+        }
+    }
+    if (cost_host) {
+        POZ_CUDA(cudaMemcpyAsync(cost_host, c->scalar_cost, sizeof(double), cudaMemcpyDeviceToHost, stream));
+        POZ_CUDA(cudaStreamSynchronize(stream));
+    }
+    return 0;
+}
+
+// ---- training step -------------------------------------------------------------------------------
+static void plan_splits(poz_ctx* c, long long batch, SegTable& seg, std::vector<long long>& kchunk) {
+    const int sms = num_sms(c->device);
+    kchunk.assign(c->nl, batch);
+    for (int l = 0; l < c->nl; ++l) {
+        const int M = c->sizes[l] + c->has_bias, N = c->sizes[l + 1];
+        long long tiles;
+        int bk;
+        if (c->dtype == POZ_DTYPE_F64) {
+            using TL = Tiles<double>;
+            tiles = (N <= 16) ? (long long)((M + TL::TH_BM - 1) / TL::TH_BM) * ((N + TL::TH_BN - 1) / TL::TH_BN)
+                              : (long long)((M + TL::SM_BM - 1) / TL::SM_BM) * ((N + TL::SM_BN - 1) / TL::SM_BN);
+            bk = TL::SM_BK;
+        } else {
+            using TL = Tiles<float>;
+            tiles = (N <= 16) ? (long long)((M + TL::TH_BM - 1) / TL::TH_BM) * ((N + TL::TH_BN - 1) / TL::TH_BN)
+                              : (long long)((M + TL::SM_BM - 1) / TL::SM_BM) * ((N + TL::SM_BN - 1) / TL::SM_BN);
+            bk = TL::SM_BK;
+        }
+        long long want = (2LL * sms + tiles - 1) / tiles;
+        long long max_by_batch = std::max<long long>(1, batch / 64);
+        long long s = std::max<long long>(1, std::min<long long>({want, max_by_batch, (long long)c->max_splits}));
+        long long kc = (batch + s - 1) / s;
+        kc = ((kc + bk - 1) / bk) * bk;
+        s = (batch + kc - 1) / kc;
+        seg.splits[l] = (int)s;
+        kchunk[l] = kc;
+    }
+}
+
+static void fill_seg(const poz_ctx* c, SegTable& seg) {
+    seg.n = c->nl;
+    for (int l = 0; l <= c->nl; ++l) seg.off[l] = c->off[l];
+    for (int l = 0; l < c->nl; ++l) {
+        seg.w_elems[l] = (long long)c->sizes[l] * c->sizes[l + 1];
+        seg.n_elems[l] = ((long long)c->sizes[l] + c->has_bias) * c->sizes[l + 1];
+        seg.splits[l] = 1;
+    }
+}
+
+template <typename T>
+static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* row_idx,
+                         long long batch, const void* const* masks, int diag, cudaStream_t stream) {
+    const int nl = c->nl;
+    if (!c->train_begun) POZ_FAIL("poz_train_step: call poz_train_begin first");
+    if (batch <= 0) POZ_FAIL("poz_train_step: empty batch");
+    POZ_TRY(reserve_train(c, batch, diag != 0));
+    SegTable seg;
+    fill_seg(c, seg);
+    std::vector<long long> kchunk;
+    plan_splits(c, batch, seg, kchunk);
+    int slabs = 1;
+    for (int l = 0; l < nl; ++l) slabs = std::max(slabs, seg.splits[l]);
+    POZ_TRY(ensure_grad_slabs(c, slabs));
+    c->seg_splits.assign(seg.splits, seg.splits + nl);
+    c->training_pass = true;
+    c->grads_reduced = false;
+    c->diag_batch = diag ? batch : 0;
+    c->last_batch = batch;
+
+    {
+        ProfScope ps(c, "step_begin", stream);
+        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, nl);
+        POZ_LAUNCH_CHECK();
+    }
+
+    // forward, keeping what the backward needs (and, for diagnostics, every entry's output)
+    const T* cur = x;
+    const int* cur_idx = row_idx;
+    for (int l = 0; l < nl; ++l) {
+        T* zb = static_cast<T*>(c->zbuf[l]);
+        T* ab = static_cast<T*>(c->abuf[l]);
+        const int act = c->acts[l];
+        T* z_out = nullptr;
+        T* a_out = ab;
+        if (act == ACT_SOFTMAX) { z_out = zb; a_out = nullptr; }
+        else if (act != ACT_NONE && diag) z_out = zb;
+        POZ_TRY(layer_forward<T>(c, l, cur, cur_idx, batch, batch, z_out, a_out, masks, stream));
+        cur = (act == ACT_SOFTMAX) ? zb : ab;
+        cur_idx = nullptr;
+    }
+
+    // loss and the gradient of the last linear's pre-dropout output
+    const long long gb = c->cfg.global_batch > 0 ? c->cfg.global_batch : batch;
+    const int last = nl - 1;
+    const int n_out = c->sizes[nl];
+    {
+        LossArgs<T> a{};
+        a.z = cur; a.target = target; a.row_idx = row_idx;
+        a.M = batch; a.N = n_out; a.act = c->acts[last];
+        a.dz_pre = static_cast<T*>(c->dzbuf[last]);
+        a.dz = make_drop(c, last, 0, masks);
+        a.cost_base = c->cost_ring; a.cost_cap = c->cost_cap; a.st = c->st;
+        if (c->loss == POZ_LOSS_CE) {
+            a.inv_count = 1.0 / (double)gb;
+            a.probs = static_cast<T*>(c->abuf[last]);
+            if (diag) a.dz_rec = static_cast<T*>(c->dz_rec[last]);
+        } else {
+            a.inv_count = 1.0 / ((double)gb * n_out);
+            if (diag) {
+                if (c->acts[last] != ACT_NONE) {
+                    a.da_rec = static_cast<T*>(c->da_rec[last]);
+                    a.dz_rec = static_cast<T*>(c->dz_rec[last]);
+                } else {
+                    a.dz_rec = static_cast<T*>(c->dz_rec[last]);
+                }
+            }
+        }
+        POZ_TRY(run_loss<T>(c, a, stream));
+    }
+
+    // backward: weight gradients (batch-split partial sums) and input gradients, last layer first
+    for (int l = last; l >= 0; --l) {
+        const int K = c->sizes[l], N = c->sizes[l + 1], hb = c->has_bias;
+        const T* dz = static_cast<const T*>(c->dzbuf[l]);
+        {
+            const T* inp = l == 0 ? x : static_cast<const T*>(c->abuf[l - 1]);
+            Operand<T> A = make_operand<T>(inp, K, l == 0 ? row_idx : nullptr, batch, K, hb);
+            Operand<T> B = make_operand<T>(dz, N, nullptr, batch, N, 0);
+            BwdWeightEpi<T> epi;
+            epi.g = static_cast<T*>(c->G); epi.slab = c->p_total; epi.off = c->off[l]; epi.ld = N;
+            TileKind kind = N <= 16 ? TILE_THIN : TILE_SMALL;
+            ProfScope ps(c, "bwd_w_l" + std::to_string(l), stream);
+            POZ_TRY((launch_gemm<T, false, false>(kind, A, B, (long long)K + hb, N, batch,
+                                                  seg.splits[l], kchunk[l], epi, stream)));
+        }
+        if (l > 0) {
+            const T* w = static_cast<const T*>(c->P) + c->off[l];
+            Operand<T> A = make_operand<T>(dz, N, nullptr, batch, N, 0);
+            Operand<T> B = make_operand<T>(w, N, nullptr, K, N, 0);
+            BwdDataEpi<T> epi;
+            epi.a_prev = static_cast<const T*>(c->abuf[l - 1]);
+            epi.dz_prev = static_cast<T*>(c->dzbuf[l - 1]);
+            epi.ld = K;
+            epi.act = c->acts[l - 1];
+            epi.dz = make_drop(c, l - 1, 0, masks);
+            epi.da = make_drop(c, l - 1, 1, masks);
+            epi.st = c->st;
+            epi.da_rec = nullptr; epi.dz_rec = nullptr;
+            if (diag) {
+                if (c->acts[l - 1] != ACT_NONE) {
+                    epi.da_rec = static_cast<T*>(c->da_rec[l - 1]);
+                    epi.dz_rec = static_cast<T*>(c->dz_rec[l - 1]);
+                } else {
+                    epi.dz_rec = static_cast<T*>(c->dz_rec[l - 1]);
+                }
+            }
+            ProfScope ps(c, "bwd_x_l" + std::to_string(l), stream);
+            POZ_TRY((launch_gemm<T, true, true>(pick_tile<T>(c, batch, K), A, B, batch, K, (long long)N, 1,
+                                                (long long)N, epi, stream)));
+        }
+    }
+    c->grads_pending = true;
+    c->diag_pending = diag != 0;
+    return 0;
+}
+
+template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream_t stream) {
+    if (!c->grads_pending) POZ_FAIL("poz_train_apply: no gradients pending");
+    SegTable seg;
+    fill_seg(c, seg);
+    if (!reduced)
+        for (int l = 0; l < c->nl; ++l) seg.splits[l] = c->seg_splits[l];
+    long long biggest = 0;
+    for (int l = 0; l < c->nl; ++l) biggest = std::max(biggest, seg.off[l + 1] - seg.off[l]);
+    int bx = (int)std::min<long long>((biggest + 255) / 256, 2LL * num_sms(c->device));
+    T* gdiag = nullptr;
+    if (c->diag_pending) {
+        if (!c->Gdiag) POZ_TRY(dev_alloc(&c->Gdiag, (size_t)c->p_total * c->esz));
+        gdiag = static_cast<T*>(c->Gdiag);
+        c->have_diag = true;
+    }
+    ProfScope ps(c, "update", stream);
+    update_kernel<T><<<dim3(std::max(bx, 1), c->nl), 256, 0, stream>>>(
+        static_cast<T*>(c->P), static_cast<T*>(c->AM), static_cast<T*>(c->AV),
+        static_cast<const T*>(c->G), c->p_total, gdiag, seg, c->st, c->cost_ring, c->cost_cap, c->stats);
+    POZ_LAUNCH_CHECK();
+    c->grads_pending = false;
+    c->diag_pending = false;
+    return 0;
+}
+
+template <typename T> static int finalize_impl(poz_ctx* c, cudaStream_t stream) {
+    SegTable seg;
+    fill_seg(c, seg);
+    bool any = false;
+    for (int l = 0; l < c->nl; ++l) { seg.splits[l] = c->seg_splits[l]; any |= seg.splits[l] > 1; }
+    if (!any) return 0;
+    long long biggest = 0;
+    for (int l = 0; l < c->nl; ++l) biggest = std::max(biggest, seg.off[l + 1] - seg.off[l]);
+    int bx = (int)std::min<long long>((biggest + 255) / 256, 2LL * num_sms(c->device));
+    ProfScope ps(c, "grad_finalize", stream);
+    grad_finalize_kernel<T><<<dim3(std::max(bx, 1), c->nl), 256, 0, stream>>>(static_cast<T*>(c->G), c->p_total, seg);
+    POZ_LAUNCH_CHECK();
+    return 0;
+}
+
+static int check_layer(poz_ctx* c, int layer, const char* who) {
+    if (!c) POZ_FAIL(std::string(who) + ": NULL context");
+    if (layer < 0 || layer >= c->nl) POZ_FAIL(std::string(who) + ": layer out of range");
+    POZ_CUDA(cudaSetDevice(c->device));
+    return 0;
+}
+
+template <typename T>
+static int put_layer(poz_ctx* c, void* base, int layer, const double* w, const double* b) {
+    long long nw = (long long)c->sizes[layer] * c->sizes[layer + 1];
+    if (w) POZ_TRY(put_f64<T>(c, base, c->off[layer], w, nw));
+    if (b && c->has_bias) POZ_TRY(put_f64<T>(c, base, c->off[layer] + nw, b, c->sizes[layer + 1]));
+    return 0;
+}
+template <typename T>
+static int get_layer(poz_ctx* c, const void* base, int layer, double* w, double* b) {
+    long long nw = (long long)c->sizes[layer] * c->sizes[layer + 1];
+    if (w) POZ_TRY(get_f64<T>(c, base, c->off[layer], w, nw));
+    if (b && c->has_bias) POZ_TRY(get_f64<T>(c, base, c->off[layer] + nw, b, c->sizes[layer + 1]));
+    return 0;
+}
+
+}  // namespace poz
+
+using namespace poz;
+
+// =================================================================================================
+extern "C" {
+
+const char* poz_last_error(void) { return t_error.c_str(); }
+int poz_version(void) { return 100; }
+long long poz_launch_count(void) { return s_launches.load(); }
+
+int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_codes,
+                   const unsigned char* drop_z, const unsigned char* drop_a, int has_bias,
+                   int loss_code, int dtype_code, poz_ctx** out) {
+    if (!out) POZ_FAIL("poz_ctx_create: out is NULL");
+    *out = nullptr;
+    if (n_linear < 1 || n_linear > MAX_LAYERS) POZ_FAIL("poz_ctx_create: n_linear must be in [1,16]");
+    if (dtype_code != POZ_DTYPE_F32 && dtype_code != POZ_DTYPE_F64)
+        POZ_FAIL("poz_ctx_create: this build supports POZ_DTYPE_F32 and POZ_DTYPE_F64 contexts");
+    for (int l = 0; l <= n_linear; ++l)
+        if (sizes[l] < 1) POZ_FAIL("poz_ctx_create: layer sizes must be positive");
+    for (int l = 0; l < n_linear; ++l) {
+        if (act_codes[l] < 0 || act_codes[l] > ACT_SOFTMAX) POZ_FAIL("poz_ctx_create: bad activation code");
+        if (act_codes[l] == ACT_SOFTMAX && l != n_linear - 1)
+            POZ_FAIL("poz_ctx_create: softmax is supported as the last activation only");
+    }
+    if ((loss_code == POZ_LOSS_CE) != (act_codes[n_linear - 1] == ACT_SOFTMAX))
+        POZ_FAIL("poz_ctx_create: cross-entropy loss goes with a trailing softmax (neural_net_model.py:400)");
+    int ndev = 0;
+    POZ_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) POZ_FAIL("poz_ctx_create: no such CUDA device");
+    POZ_CUDA(cudaSetDevice(device));
+
+    poz_ctx* c = new poz_ctx();
+    c->device = device; c->nl = n_linear; c->has_bias = has_bias ? 1 : 0;
+    c->loss = loss_code; c->dtype = dtype_code;
+    c->esz = dtype_code == POZ_DTYPE_F64 ? 8 : 4;
+    c->sizes.assign(sizes, sizes + n_linear + 1);
+    c->acts.assign(act_codes, act_codes + n_linear);
+    c->drop_z.assign(n_linear, 0); c->drop_a.assign(n_linear, 0);
+    if (drop_z) c->drop_z.assign(drop_z, drop_z + n_linear);
+    if (drop_a) c->drop_a.assign(drop_a, drop_a + n_linear);
+    c->off.assign(n_linear + 1, 0);
+    for (int l = 0; l < n_linear; ++l) {
+        long long n = ((long long)sizes[l] + c->has_bias) * sizes[l + 1];
+        n = (n + 3) & ~3LL;   // keep every layer image 16-byte aligned in the flat buffers
+        c->off[l + 1] = c->off[l] + n;
+    }
+    c->p_total = c->off[n_linear];
+    c->zbuf.assign(n_linear, nullptr); c->abuf.assign(n_linear, nullptr);
+    c->dzbuf.assign(n_linear, nullptr); c->dz_rec.assign(n_linear, nullptr);
+    c->da_rec.assign(n_linear, nullptr);
+    c->max_splits = 16;
+    auto fail = [&](void) { poz_ctx_destroy(c); return 1; };
+    size_t pbytes = (size_t)c->p_total * c->esz;
+    if (dev_alloc(&c->P, pbytes) || dev_alloc(&c->AM, pbytes) || dev_alloc(&c->AV, pbytes)) return fail();
+    if (cudaMemset(c->P, 0, pbytes) != cudaSuccess || cudaMemset(c->AM, 0, pbytes) != cudaSuccess ||
+        cudaMemset(c->AV, 0, pbytes) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
+    if (dev_alloc(reinterpret_cast<void**>(&c->st), sizeof(DevState))) return fail();
+    if (cudaMemset(c->st, 0, sizeof(DevState)) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
+    if (dev_alloc(reinterpret_cast<void**>(&c->scalar_cost), sizeof(double))) return fail();
+    std::memset(&c->cfg, 0, sizeof(c->cfg));
+    *out = c;
+    return 0;
+}
+
+int poz_ctx_destroy(poz_ctx* c) {
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_workspace(c);
+    dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
+    dev_free(reinterpret_cast<void*&>(c->st));
+    dev_free(reinterpret_cast<void*&>(c->cost_ring));
+    dev_free(reinterpret_cast<void*&>(c->stats));
+    dev_free(reinterpret_cast<void*&>(c->scalar_cost));
+    dev_free(reinterpret_cast<void*&>(c->stage));
+    delete c;
+    return 0;
+}
+
+int poz_profile_begin(poz_ctx* c) {
+    if (!c) POZ_FAIL("poz_profile_begin: NULL context");
+    POZ_CUDA(cudaSetDevice(c->device));
+    for (auto& r : c->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    c->prof.clear();
+    c->profiling = true;
+    return 0;
+}
+
+int poz_profile_end(poz_ctx* c, char* json_out, long long cap) {
+    if (!c) POZ_FAIL("poz_profile_end: NULL context");
+    POZ_CUDA(cudaSetDevice(c->device));
+    c->profiling = false;
+    POZ_CUDA(cudaDeviceSynchronize());
+    std::vector<std::string> tags;
+    std::vector<double> ms;
+    std::vector<long long> cnt;
+    for (auto& r : c->prof) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, r.a, r.b);
+        size_t i = 0;
+        for (; i < tags.size(); ++i) if (tags[i] == r.tag) break;
+        if (i == tags.size()) { tags.push_back(r.tag); ms.push_back(0.0); cnt.push_back(0); }
+        ms[i] += t; cnt[i] += 1;
+        cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+    }
+    c->prof.clear();
+    std::string js = "{";
+    for (size_t i = 0; i < tags.size(); ++i) {
+        char buf[160];
+        snprintf(buf, sizeof(buf), "%s\"%s\": {\"launches\": %lld, \"ms\": %.6f}", i ? ", " : "",
+                 tags[i].c_str(), cnt[i], ms[i]);
+        js += buf;
+    }
+    js += "}";
+    if (!json_out || cap <= (long long)js.size()) POZ_FAIL("poz_profile_end: output buffer too small");
+    std::memcpy(json_out, js.c_str(), js.size() + 1);
+    return 0;
+}
+
+int poz_ctx_reserve(poz_ctx* c, long long max_batch, int for_training) {
+    if (!c) POZ_FAIL("poz_ctx_reserve: NULL context");
+    POZ_CUDA(cudaSetDevice(c->device));
+    if (for_training) return reserve_train(c, max_batch, false);
+    return 0;
+}
+
+int poz_params_upload(poz_ctx* c, int layer, const double* w, const double* b) {
+    POZ_TRY(check_layer(c, layer, "poz_params_upload"));
+    return POZ_DISPATCH(c, put_layer, c, c->P, layer, w, b);
+}
+int poz_params_download(poz_ctx* c, int layer, double* w, double* b) {
+    POZ_TRY(check_layer(c, layer, "poz_params_download"));
+    return POZ_DISPATCH(c, get_layer, c, c->P, layer, w, b);
+}
+int poz_adam_upload(poz_ctx* c, int layer, const double* m_w, const double* v_w, const double* m_b,
+                    const double* v_b) {
+    POZ_TRY(check_layer(c, layer, "poz_adam_upload"));
+    POZ_TRY(POZ_DISPATCH(c, put_layer, c, c->AM, layer, m_w, m_b));
+    return POZ_DISPATCH(c, put_layer, c, c->AV, layer, v_w, v_b);
+}
+int poz_adam_download(poz_ctx* c, int layer, double* m_w, double* v_w, double* m_b, double* v_b) {
+    POZ_TRY(check_layer(c, layer, "poz_adam_download"));
+    POZ_TRY(POZ_DISPATCH(c, get_layer, c, c->AM, layer, m_w, m_b));
+    return POZ_DISPATCH(c, get_layer, c, c->AV, layer, v_w, v_b);
+}
+int poz_adam_set_step(poz_ctx* c, long long step) {
+    POZ_TRY(check_layer(c, 0, "poz_adam_set_step"));
+    POZ_CUDA(cudaDeviceSynchronize());
+    POZ_CUDA(cudaMemcpy(&c->st->adam_t, &step, sizeof(step), cudaMemcpyHostToDevice));
+    return 0;
+}
+int poz_adam_get_step(poz_ctx* c, long long* step) {
+    POZ_TRY(check_layer(c, 0, "poz_adam_get_step"));
+    POZ_CUDA(cudaDeviceSynchronize());
+    POZ_CUDA(cudaMemcpy(step, &c->st->adam_t, sizeof(*step), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int poz_forward(poz_ctx* c, const void* x_dev, long long batch, void* out_dev, void* stream) {
+    POZ_TRY(check_layer(c, 0, "poz_forward"));
+    if (batch <= 0) return 0;
+    if (!x_dev || !out_dev) POZ_FAIL("poz_forward: NULL buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (c->dtype == POZ_DTYPE_F64)
+        return forward_impl<double>(c, static_cast<const double*>(x_dev), nullptr, batch,
+                                    static_cast<double*>(out_dev), nullptr, s);
+    return forward_impl<float>(c, static_cast<const float*>(x_dev), nullptr, batch,
+                               static_cast<float*>(out_dev), nullptr, s);
+}
+
+int poz_forward_loss(poz_ctx* c, const void* x_dev, const void* target_dev, long long batch,
+                     void* out_dev, double* cost_host, void* stream) {
+    POZ_TRY(check_layer(c, 0, "poz_forward_loss"));
+    if (batch <= 0) POZ_FAIL("poz_forward_loss: empty batch");
+    if (!x_dev || !out_dev || !target_dev || !cost_host) POZ_FAIL("poz_forward_loss: NULL buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (c->dtype == POZ_DTYPE_F64)
+        return forward_impl<double>(c, static_cast<const double*>(x_dev), target_dev, batch,
+                                    static_cast<double*>(out_dev), cost_host, s);
+    return forward_impl<float>(c, static_cast<const float*>(x_dev), target_dev, batch,
+                               static_cast<float*>(out_dev), cost_host, s);
+}
+
+int poz_train_begin(poz_ctx* c, const poz_train_config* cfg) {
+    POZ_TRY(check_layer(c, 0, "poz_train_begin"));
+    if (!cfg) POZ_FAIL("poz_train_begin: NULL config");
+    if (cfg->dropout_rate < 0.0 || cfg->dropout_rate >= 1.0) POZ_FAIL("poz_train_begin: dropout_rate must be in [0,1)");
+    if (cfg->optimizer != POZ_OPT_SGD && cfg->optimizer != POZ_OPT_ADAM) POZ_FAIL("poz_train_begin: bad optimizer");
+    POZ_CUDA(cudaDeviceSynchronize());
+    c->cfg = *cfg;
+    long long epochs = std::max<long long>(cfg->epochs, 1);
+    if (epochs > c->cost_cap) {
+        dev_free(reinterpret_cast<void*&>(c->cost_ring));
+        POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->cost_ring), (size_t)epochs * sizeof(double)));
+        c->cost_cap = epochs;
+    }
+    long long recs = cfg->progress_stride > 0 ? (epochs + cfg->progress_stride - 1) / cfg->progress_stride + 1 : 1;
+    if (recs > c->stats_cap) {
+        dev_free(reinterpret_cast<void*&>(c->stats));
+        POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->stats), (size_t)recs * c->nl * 4 * sizeof(double)));
+        c->stats_cap = recs;
+    }
+    DevState h;
+    POZ_CUDA(cudaMemcpy(&h, c->st, sizeof(h), cudaMemcpyDeviceToHost));
+    h.lr0 = cfg->learning_rate; h.decay = cfg->decay_rate; h.beta1 = cfg->beta1; h.beta2 = cfg->beta2;
+    h.eps = cfg->epsilon; h.l2 = cfg->l2_lambda; h.seed = cfg->dropout_seed;
+    h.progress_stride = cfg->progress_stride; h.optimizer = cfg->optimizer;
+    h.next_epoch = 0; h.cur_epoch = 0; h.cur_record = -1; h.n_records = 0;
+    POZ_CUDA(cudaMemcpy(c->st, &h, sizeof(h), cudaMemcpyHostToDevice));
+    c->train_begun = true;
+    c->grads_pending = false;
+    return 0;
+}
+
+int poz_train_backward(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
+                       long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
+    POZ_TRY(check_layer(c, 0, "poz_train_backward"));
+    if (!x_dev || !target_dev) POZ_FAIL("poz_train_step: NULL buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (c->dtype == POZ_DTYPE_F64) {
+        POZ_TRY(backward_impl<double>(c, static_cast<const double*>(x_dev), target_dev, row_idx_dev, batch, keep_masks, diagnostics, s));
+        return 0;
+    }
+    return backward_impl<float>(c, static_cast<const float*>(x_dev), target_dev, row_idx_dev, batch, keep_masks, diagnostics, s);
+}
+
+int poz_train_apply(poz_ctx* c, void* stream) {
+    POZ_TRY(check_layer(c, 0, "poz_train_apply"));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    return c->dtype == POZ_DTYPE_F64 ? apply_impl<double>(c, c->grads_reduced, s)
+                                     : apply_impl<float>(c, c->grads_reduced, s);
+}
+
+int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
+                   long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
+    POZ_TRY(poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, keep_masks, diagnostics, stream));
+    return poz_train_apply(c, stream);
+}
+
+int poz_grad_buffer(poz_ctx* c, void** dev_ptr, long long* n_elems, int* dtype_code, void* stream) {
+    POZ_TRY(check_layer(c, 0, "poz_grad_buffer"));
+    if (!c->grads_pending) POZ_FAIL("poz_grad_buffer: run poz_train_backward first");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    POZ_TRY(c->dtype == POZ_DTYPE_F64 ? finalize_impl<double>(c, s) : finalize_impl<float>(c, s));
+    c->grads_reduced = true;
+    if (dev_ptr) *dev_ptr = c->G;
+    if (n_elems) *n_elems = c->p_total;
+    if (dtype_code) *dtype_code = c->dtype;
+    return 0;
+}
+
+int poz_train_costs(poz_ctx* c, long long first, long long count, double* costs_host, void* stream) {
+    POZ_TRY(check_layer(c, 0, "poz_train_costs"));
+    if (first < 0 || count < 0 || first + count > c->cost_cap) POZ_FAIL("poz_train_costs: range outside the cost ring");
+    if (count == 0) return 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    POZ_CUDA(cudaMemcpyAsync(costs_host, c->cost_ring + first, count * sizeof(double), cudaMemcpyDeviceToHost, s));
+    POZ_CUDA(cudaStreamSynchronize(s));
+    return 0;
+}
+
+int poz_train_update_ratios(poz_ctx* c, long long first_record, long long count, double* ratios_host, void* stream) {
+    POZ_TRY(check_layer(c, 0, "poz_train_update_ratios"));
+    if (first_record < 0 || count < 0 || first_record + count > c->stats_cap) POZ_FAIL("poz_train_update_ratios: range outside the record buffer");
+    if (count == 0) return 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    std::vector<double> raw((size_t)count * c->nl * 4);
+    POZ_CUDA(cudaMemcpyAsync(raw.data(), c->stats + first_record * c->nl * 4, raw.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+    POZ_CUDA(cudaStreamSynchronize(s));
+    for (long long r = 0; r < count; ++r)
+        for (int l = 0; l < c->nl; ++l) {
+            const double* q = &raw[(size_t)(r * c->nl + l) * 4];
+            const double n = (double)c->sizes[l] * c->sizes[l + 1];
+            // unbiased std from sums (neural_net_model.py:506)
+            double var_d = n > 1 ? (q[1] - q[0] * q[0] / n) / (n - 1) : NAN;
+            double var_w = n > 1 ? (q[3] - q[2] * q[2] / n) / (n - 1) : NAN;
+            double sd = std::sqrt(std::max(var_d, 0.0)), sw = std::sqrt(std::max(var_w, 0.0));
+            if (n <= 1) { sd = NAN; sw = NAN; }
+            ratios_host[r * c->nl + l] = sd / (sw + 1e-8);
+        }
+    return 0;
+}
+
+static int diag_ready(poz_ctx* c, int layer, const char* who) {
+    POZ_TRY(check_layer(c, layer, who));
+    if (c->diag_batch <= 0) POZ_FAIL(std::string(who) + ": no step was run with diagnostics enabled");
+    return 0;
+}
+
+int poz_diag_activation(poz_ctx* c, int layer, int which, double* host_out) {
+    POZ_TRY(diag_ready(c, layer, "poz_diag_activation"));
+    const int act = c->acts[layer];
+    const void* src = nullptr;
+    if (which == 0) src = act == ACT_NONE ? c->abuf[layer] : c->zbuf[layer];
+    else if (which == 1 && act != ACT_NONE) src = c->abuf[layer];
+    if (!src) POZ_FAIL("poz_diag_activation: no such entry");
+    long long n = c->diag_batch * c->sizes[layer + 1];
+    return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, n);
+}
+
+int poz_diag_activation_grad(poz_ctx* c, int layer, int which, double* host_out, int* has_grad) {
+    POZ_TRY(diag_ready(c, layer, "poz_diag_activation_grad"));
+    const int act = c->acts[layer];
+    const void* src = nullptr;
+    if (which == 0) src = c->dz_rec[layer];
+    else if (which == 1 && act != ACT_NONE && act != ACT_SOFTMAX) src = c->da_rec[layer];
+    // the trailing softmax is not on the loss graph: its .grad is None (neural_net_model.py:545)
+    if (has_grad) *has_grad = src ? 1 : 0;
+    if (!src) return 0;
+    long long n = c->diag_batch * c->sizes[layer + 1];
+    return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, n);
+}
+
+int poz_diag_weight_grad(poz_ctx* c, int layer, double* w_grad, double* b_grad) {
+    POZ_TRY(diag_ready(c, layer, "poz_diag_weight_grad"));
+    if (!c->have_diag || !c->Gdiag) POZ_FAIL("poz_diag_weight_grad: no diagnostics gradients recorded");
+    return POZ_DISPATCH(c, get_layer, c, c->Gdiag, layer, w_grad, b_grad);
+}
+
+}  // extern "C"

@@ -1,0 +1,136 @@
+// Shared device/host helpers for the pozmlp CUDA library (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+namespace poz {
+
+// ---- error plumbing: every failure becomes a message + non-zero return, never an abort -------
+void set_error(const std::string& msg);
+extern long long g_launches;   // kernels launched by this library (atomic add on host)
+void count_launch(int n = 1);
+
+#define POZ_CUDA(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            poz::set_error(std::string(#expr) + " failed: " + cudaGetErrorString(_e) +       \
+                           " (" + __FILE__ + ":" + std::to_string(__LINE__) + ")");          \
+            return 1;                                                                        \
+        }                                                                                    \
+    } while (0)
+
+#define POZ_FAIL(msg)                                                                        \
+    do {                                                                                     \
+        poz::set_error(std::string(msg));                                                    \
+        return 1;                                                                            \
+    } while (0)
+
+#define POZ_TRY(expr)                                                                        \
+    do {                                                                                     \
+        int _r = (expr);                                                                     \
+        if (_r != 0) return _r;                                                              \
+    } while (0)
+
+enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_TANH = 3, ACT_SOFTMAX = 4 };
+
+// ---- device-resident step state -----------------------------------------------------------------
+// Everything that changes from step to step lives here so that the kernel arguments of a step are
+// constant (the step can be replayed from a CUDA graph).  Written by poz_train_begin (host) and by
+// step_begin_kernel (device, one thread, first kernel of every step).
+struct DevState {
+    // hyper-parameters of the current train() call
+    double lr0, decay, beta1, beta2, eps, l2;
+    double inv_global_batch_unused;
+    unsigned long long seed;
+    long long progress_stride;
+    int optimizer;
+    int pad0;
+    // counters
+    long long next_epoch;      // epoch index the next step will use
+    long long cur_epoch;       // epoch index of the step in flight
+    long long adam_t;          // torch Adam `step`, persists across train() calls
+    long long cur_record;      // progress record slot of this step, -1 if not recorded
+    long long n_records;
+    // derived per step
+    double lr_t, step_size, bc2_sqrt;
+};
+
+// ---- Philox4x32-10 (counter-based RNG for in-kernel dropout) -------------------------------------
+__device__ __forceinline__ uint32_t philox_first(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                 uint32_t k0, uint32_t k1) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+        uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += W0; k1 += W1;
+    }
+    return c0;
+}
+
+// One dropout point (the output of one hidden entry).  keep(m, n) is a pure function of
+// (seed, epoch, point, element) so the backward pass regenerates the forward mask.
+struct DropPoint {
+    const uint8_t* mask;   // host-recorded keep mask [M][N] or nullptr
+    int enabled;           // 0 = identity
+    uint32_t point;        // unique id of this dropout point inside the stack
+    float keep_prob;       // 1 - p
+    float scale;           // 1 / (1 - p)
+};
+
+__device__ __forceinline__ bool drop_keep(const DropPoint& d, const DevState* st, long long m,
+                                          int n, int ld) {
+    long long e = m * (long long)ld + n;
+    if (d.mask) return d.mask[e] != 0;
+    uint32_t r = philox_first((uint32_t)e, (uint32_t)(e >> 32), d.point, (uint32_t)st->cur_epoch,
+                              (uint32_t)st->seed, (uint32_t)(st->seed >> 32));
+    return (r * 2.3283064365386963e-10f) < d.keep_prob;
+}
+
+// ---- activations (neural_net_model.py:172-188) and their derivatives from the OUTPUT value -------
+template <typename T> __device__ __forceinline__ T act_fwd(int act, T z) {
+    switch (act) {
+        case ACT_RELU: return z > T(0) ? z : T(0);
+        case ACT_SIGMOID: return T(1) / (T(1) + exp(-z));
+        case ACT_TANH: return tanh(z);
+        default: return z;
+    }
+}
+template <> __device__ __forceinline__ float act_fwd<float>(int act, float z) {
+    switch (act) {
+        case ACT_RELU: return fmaxf(z, 0.f);
+        case ACT_SIGMOID: return 1.f / (1.f + expf(-z));
+        case ACT_TANH: return tanhf(z);
+        default: return z;
+    }
+}
+// derivative expressed through the activation output a = act(z)
+template <typename T> __device__ __forceinline__ T act_bwd_from_out(int act, T a) {
+    switch (act) {
+        case ACT_RELU: return a > T(0) ? T(1) : T(0);
+        case ACT_SIGMOID: return a * (T(1) - a);
+        case ACT_TANH: return T(1) - a * a;     // test_torch_backward.py:170
+        default: return T(1);
+    }
+}
+
+template <typename T> __device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+template <typename T> __device__ __forceinline__ T warp_max(T v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        T u = __shfl_xor_sync(0xffffffffu, v, o);
+        v = u > v ? u : v;
+    }
+    return v;
+}
+
+}  // namespace poz

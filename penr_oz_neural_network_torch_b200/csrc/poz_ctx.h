@@ -1,0 +1,47 @@
+// Host-side context: the device image of one NeuralNetworkModel (parameters, optimizer state,
+// per-step device state, workspace).  Opaque to callers of include/pozmlp.h.
+#pragma once
+#include "../../include/pozmlp.h"
+#include "poz_common.cuh"
+#include <string>
+#include <vector>
+
+struct poz_ctx {
+    int device = 0;
+    int nl = 0;                       // linear layers
+    int has_bias = 0, loss = 0, dtype = 0;
+    size_t esz = 4;                   // bytes per element of the master parameters
+    std::vector<int> sizes, acts;
+    std::vector<unsigned char> drop_z, drop_a;
+    std::vector<long long> off;       // flat offsets of each layer's [W; b] image
+    long long p_total = 0;
+
+    void* P = nullptr;                // flat parameters
+    void* AM = nullptr;               // Adam exp_avg
+    void* AV = nullptr;               // Adam exp_avg_sq
+    void* G = nullptr;                // gradient slabs [g_slabs][p_total]
+    void* Gdiag = nullptr;            // finished gradients of the last diagnostics step
+    int g_slabs = 0, max_splits = 16;
+    std::vector<int> seg_splits;
+
+    poz::DevState* st = nullptr;
+    double* cost_ring = nullptr;  long long cost_cap = 0;
+    double* stats = nullptr;      long long stats_cap = 0;
+    double* scalar_cost = nullptr;
+    double* stage = nullptr;      size_t stage_elems = 0;
+
+    // workspace
+    long long ws_train = 0, ws_infer = 0, ws_diag = 0;
+    std::vector<void*> zbuf, abuf, dzbuf, dz_rec, da_rec;
+    void* ping = nullptr;
+    void* pong = nullptr;
+
+    struct ProfRec { std::string tag; cudaEvent_t a, b; };
+    std::vector<ProfRec> prof;
+    bool profiling = false;
+
+    poz_train_config cfg;
+    bool train_begun = false, training_pass = false;
+    bool grads_pending = false, grads_reduced = false, diag_pending = false, have_diag = false;
+    long long diag_batch = 0, last_batch = 0;
+};

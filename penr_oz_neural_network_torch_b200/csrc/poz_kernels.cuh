@@ -1,0 +1,259 @@
+// Non-GEMM kernels of the narrow path: per-step bookkeeping, loss (+ its gradient), softmax,
+// fused gradient-reduce + L2 + Adam/SGD update, dtype conversion.
+#pragma once
+#include "poz_common.cuh"
+
+namespace poz {
+
+constexpr int MAX_LAYERS = 16;
+
+struct SegTable {
+    int n;                           // linear layers
+    long long off[MAX_LAYERS + 1];   // layer l owns flat elements [off[l], off[l+1]) = [W; b]
+    long long n_elems[MAX_LAYERS];   // real elements of the image (the rest of the slot is padding)
+    long long w_elems[MAX_LAYERS];   // leading elements that are weights (L2 applies to these)
+    int splits[MAX_LAYERS];          // gradient slabs to sum for layer l
+};
+
+// First kernel of every step: advances the epoch / Adam counters and derives the step's scalars
+// (neural_net_model.py:464 lr decay; torch/optim/adam.py bias corrections).
+__global__ void step_begin_kernel(DevState* st, double* cost_ring, long long cost_cap,
+                                  double* stats, long long stats_cap, int n_layers) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    long long e = st->next_epoch;
+    st->cur_epoch = e;
+    st->next_epoch = e + 1;
+    double lr = st->lr0 * pow(st->decay, (double)e);
+    st->lr_t = lr;
+    if (st->optimizer == 1) {
+        long long t = st->adam_t + 1;
+        st->adam_t = t;
+        double bc1 = 1.0 - pow(st->beta1, (double)t);
+        double bc2 = 1.0 - pow(st->beta2, (double)t);
+        st->step_size = lr / bc1;
+        st->bc2_sqrt = sqrt(bc2);
+    }
+    cost_ring[e % cost_cap] = 0.0;
+    long long rec = -1;
+    if (st->progress_stride > 0 && (e % st->progress_stride) == 0 && st->n_records < stats_cap) {
+        rec = st->n_records;
+        st->n_records = rec + 1;
+        for (int i = 0; i < n_layers * 4; ++i) stats[rec * n_layers * 4 + i] = 0.0;
+    }
+    st->cur_record = rec;
+}
+
+template <typename T> struct LossArgs {
+    const T* z;            // CE: recorded logits [M][N];  MSE: recorded final output [M][N]
+    const void* target;    // CE: int32 labels;  MSE: T [rows][N]
+    const int* row_idx;    // gather of target rows (nullable)
+    T* probs;              // CE: softmax output (nullable)
+    T* dz_pre;             // gradient w.r.t. the last linear's pre-dropout output (nullable)
+    T* dz_rec;             // diagnostics (nullable): gradient of the recorded linear output
+    T* da_rec;             // diagnostics (nullable, MSE): gradient of the recorded final output
+    long long M;
+    int N;
+    int act;               // MSE: activation of the last unit
+    DropPoint dz;          // dropout point on the last linear's output
+    double inv_count;      // CE: 1/global_batch;  MSE: 1/(global_batch*N)
+    double* cost_base;
+    long long cost_cap;
+    const DevState* st;    // nullable: cost goes to cost_base[0]
+};
+
+__device__ __forceinline__ double* cost_slot(double* base, long long cap, const DevState* st) {
+    return st ? base + (st->cur_epoch % cap) : base;
+}
+
+__device__ __forceinline__ void block_add_double(double v, double* dst) {
+    __shared__ double red[32];
+    v = warp_sum(v);
+    int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) red[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        int nw = (blockDim.x + 31) >> 5;
+        double s = l < nw ? red[l] : 0.0;
+        s = warp_sum(s);
+        if (l == 0 && dst) atomicAdd(dst, s);
+    }
+    __syncthreads();
+}
+
+// softmax + cross-entropy + gradient, one warp per row
+// (neural_net_model.py:188,400-403; gradient test_torch_backward.py:163-164)
+template <typename T> __global__ void ce_loss_kernel(LossArgs<T> a) {
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    long long row = (long long)blockIdx.x * wpb + (threadIdx.x >> 5);
+    const long long stride = (long long)gridDim.x * wpb;
+    const int* labels = static_cast<const int*>(a.target);
+    double local = 0.0;
+    const T invb = T(a.inv_count);
+    for (; row < a.M; row += stride) {
+        const T* z = a.z + row * a.N;
+        T mx = -INFINITY;
+        for (int j = lane; j < a.N; j += 32) { T v = z[j]; mx = v > mx ? v : mx; }
+        mx = warp_max(mx);
+        T s = T(0);
+        for (int j = lane; j < a.N; j += 32) s += exp(z[j] - mx);
+        s = warp_sum(s);
+        const T inv_s = T(1) / s;
+        int y = -1;
+        if (labels) {
+            long long lr = a.row_idx ? (long long)a.row_idx[row] : row;
+            y = labels[lr];
+        }
+        for (int j = lane; j < a.N; j += 32) {
+            T p = exp(z[j] - mx) * inv_s;
+            if (a.probs) a.probs[row * a.N + j] = p;
+            if (a.dz_pre || a.dz_rec) {
+                T g = (p - (j == y ? T(1) : T(0))) * invb;
+                if (a.dz_rec) a.dz_rec[row * a.N + j] = g;
+                if (a.dz_pre) {
+                    if (a.dz.enabled) g = drop_keep(a.dz, a.st, row, j, a.N) ? g * T(a.dz.scale) : T(0);
+                    a.dz_pre[row * a.N + j] = g;
+                }
+            }
+        }
+        if (labels && lane == 0 && y >= 0 && y < a.N)
+            local += (double)(mx + log(s) - z[y]);
+    }
+    if (a.cost_base) block_add_double(local * a.inv_count, cost_slot(a.cost_base, a.cost_cap, a.st));
+}
+
+// plain row softmax for inference without a target (neural_net_model.py:188)
+template <typename T> __global__ void softmax_kernel(const T* z, T* out, long long M, int N) {
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    long long row = (long long)blockIdx.x * wpb + (threadIdx.x >> 5);
+    const long long stride = (long long)gridDim.x * wpb;
+    for (; row < M; row += stride) {
+        const T* zr = z + row * N;
+        T mx = -INFINITY;
+        for (int j = lane; j < N; j += 32) { T v = zr[j]; mx = v > mx ? v : mx; }
+        mx = warp_max(mx);
+        T s = T(0);
+        for (int j = lane; j < N; j += 32) s += exp(zr[j] - mx);
+        s = warp_sum(s);
+        const T inv_s = T(1) / s;
+        for (int j = lane; j < N; j += 32) out[row * N + j] = exp(zr[j] - mx) * inv_s;
+    }
+}
+
+// mean-squared error + gradient through the last activation (neural_net_model.py:405-406)
+template <typename T> __global__ void mse_loss_kernel(LossArgs<T> a) {
+    const long long total = a.M * a.N;
+    const T* tgt = static_cast<const T*>(a.target);
+    double local = 0.0;
+    const T two_inv = T(2.0 * a.inv_count);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        long long row = i / a.N;
+        int j = (int)(i - row * a.N);
+        long long tr = a.row_idx ? (long long)a.row_idx[row] : row;
+        T y = a.z[i];
+        T d = y - tgt[tr * a.N + j];
+        local += (double)d * (double)d;
+        if (a.dz_pre || a.dz_rec || a.da_rec) {
+            T ga = two_inv * d;
+            if (a.da_rec) a.da_rec[i] = ga;
+            T gz = ga * act_bwd_from_out<T>(a.act, y);
+            if (a.dz_rec) a.dz_rec[i] = gz;
+            if (a.dz_pre) {
+                if (a.dz.enabled) gz = drop_keep(a.dz, a.st, row, j, a.N) ? gz * T(a.dz.scale) : T(0);
+                a.dz_pre[i] = gz;
+            }
+        }
+    }
+    if (a.cost_base) block_add_double(local * a.inv_count, cost_slot(a.cost_base, a.cost_cap, a.st));
+}
+
+// Sum the batch-split gradient slabs of every layer into slab 0 (data-parallel path: slab 0 is
+// what the host all-reduces).
+template <typename T> __global__ void grad_finalize_kernel(T* g, long long slab, SegTable seg) {
+    const int l = blockIdx.y;
+    const long long n = seg.n_elems[l];
+    const int S = seg.splits[l];
+    if (S <= 1) return;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        long long idx = seg.off[l] + i;
+        T s = g[idx];
+        for (int k = 1; k < S; ++k) s += g[(long long)k * slab + idx];
+        g[idx] = s;
+    }
+}
+
+// Reduce gradient slabs, add the L2 gradient, apply Adam / SGD in place, and fold the L2 penalty
+// and the weight-update-ratio statistics into the same pass over the parameters.
+//   Adam: torch/optim/adam.py _single_tensor_adam as driven by neural_net_model.py:497
+//   SGD : neural_net_model.py:499-500
+//   L2  : neural_net_model.py:482-483 (weights only)
+//   ratio statistics: neural_net_model.py:506-507
+template <typename T>
+__global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restrict__ av,
+                              const T* __restrict__ g, long long slab, T* __restrict__ g_diag,
+                              SegTable seg, const DevState* st, double* cost_base,
+                              long long cost_cap, double* stats) {
+    const int l = blockIdx.y;
+    const long long n = seg.n_elems[l];
+    const long long nw = seg.w_elems[l];
+    const int S = seg.splits[l];
+    const bool adam = st->optimizer == 1;
+    const T l2 = T(st->l2);
+    const T lr = T(st->lr_t);
+    const T b1c = T(1.0 - st->beta1), b2 = T(st->beta2), b2c = T(1.0 - st->beta2);
+    const T step_size = T(st->step_size), bc2s = T(st->bc2_sqrt), eps = T(st->eps);
+    const long long rec = st->cur_record;
+    double l2acc = 0.0, sd = 0.0, sd2 = 0.0, sw = 0.0, sw2 = 0.0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long idx = seg.off[l] + i;
+        T gr = g[idx];
+        for (int k = 1; k < S; ++k) gr += g[(long long)k * slab + idx];
+        const T w = p[idx];
+        const bool is_w = i < nw;
+        if (is_w && st->l2 > 0.0) {
+            l2acc += (double)w * (double)w;
+            gr += T(2) * l2 * w;
+        }
+        if (g_diag) g_diag[idx] = gr;
+        T wn;
+        if (adam) {
+            T m = am[idx], v = av[idx];
+            m = m + (gr - m) * b1c;
+            v = v * b2 + b2c * gr * gr;
+            am[idx] = m;
+            av[idx] = v;
+            T denom = sqrt(v) / bc2s + eps;
+            wn = w - step_size * (m / denom);
+        } else {
+            wn = w - lr * gr;
+        }
+        p[idx] = wn;
+        if (rec >= 0 && is_w) {
+            double d = (double)wn - (double)w;
+            sd += d; sd2 += d * d; sw += (double)wn; sw2 += (double)wn * (double)wn;
+        }
+    }
+    if (st->l2 > 0.0) block_add_double(l2acc * st->l2, cost_slot(cost_base, cost_cap, st));
+    if (rec >= 0) {
+        double* s = stats + (rec * seg.n + l) * 4;
+        block_add_double(sd, s + 0);
+        block_add_double(sd2, s + 1);
+        block_add_double(sw, s + 2);
+        block_add_double(sw2, s + 3);
+    }
+}
+
+// L2 penalty for the inference-with-target path is never needed (compute_output has no L2).
+
+template <typename S, typename D>
+__global__ void convert_kernel(const S* __restrict__ src, D* __restrict__ dst, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x)
+        dst[i] = (D)src[i];
+}
+
+}  // namespace poz

@@ -1,0 +1,363 @@
+"""Tensor-level host interface to the CUDA hot path (one ``DeviceMLP`` = one ``poz_ctx``).
+
+PyTorch is used here for device memory, streams and ``torch.distributed`` only; every FLOP of the
+forward / loss / backward / optimizer path runs in the kernels of ``libpozmlp.so``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import _native as nat
+
+ACTIVATIONS = ("relu", "sigmoid", "tanh", "softmax")
+_TORCH_DTYPE = {"float32": torch.float32, "float64": torch.float64}
+_DTYPE_CODE = {"float32": nat.DTYPE_F32, "float64": nat.DTYPE_F64}
+
+
+@dataclass
+class StackSpec:
+    """Linear(+activation) units derived from the reference's expanded ``algos`` list.
+
+    ``drop_z`` / ``drop_a`` carry the reference's ``hidden`` flag (neural_net_model.py:255) of the
+    Linear entry and of the activation entry after it: the dropout points of
+    neural_net_model.py:393-395.
+    """
+    algos: list[str]
+    acts: list[str] = field(default_factory=list)
+    z_index: list[int] = field(default_factory=list)
+    a_index: list[int | None] = field(default_factory=list)
+    drop_z: list[bool] = field(default_factory=list)
+    drop_a: list[bool] = field(default_factory=list)
+
+    @property
+    def n_linear(self) -> int:
+        return len(self.acts)
+
+    @property
+    def loss(self) -> str:
+        return "ce" if self.algos and self.algos[-1] == "softmax" else "mse"
+
+    @staticmethod
+    def from_algos(algos: list[str]) -> "StackSpec":
+        spec = StackSpec(list(algos))
+        n, i = len(algos), 0
+        while i < n:
+            if algos[i] != "linear":
+                raise ValueError(f"Activation algorithm not on the B200 hot path here: {algos[i]} "
+                                 f"(stack {algos}; supported: Linear followed by relu/sigmoid/tanh/softmax)")
+            act, a_idx = "none", None
+            if i + 1 < n and algos[i + 1] in ACTIVATIONS:
+                act, a_idx = algos[i + 1], i + 1
+            if act == "softmax" and a_idx != n - 1:
+                raise ValueError("softmax is supported as the last activation only")
+            spec.acts.append(act)
+            spec.z_index.append(i)
+            spec.a_index.append(a_idx)
+            spec.drop_z.append(0 < i < n - 1)
+            spec.drop_a.append(a_idx is not None and 0 < a_idx < n - 1)
+            i += 1 if a_idx is None else 2
+        return spec
+
+
+def _arr(ctype, values):
+    return (ctype * len(values))(*values)
+
+
+def _ptr(t) -> int:
+    return 0 if t is None else int(t.data_ptr())
+
+
+def _stream_ptr(device) -> int:
+    return int(torch.cuda.current_stream(device).cuda_stream)
+
+
+class DeviceMLP:
+    """Device image of one model: parameters, Adam state, workspace; tensor-level fwd/train."""
+
+    def __init__(self, sizes, spec: StackSpec, has_bias: bool, dtype: str = "float32", device=None):
+        if not torch.cuda.is_available():
+            raise nat.PozError("no CUDA device: the NeuralNetworkModel hot path has no CPU fallback")
+        if dtype not in _DTYPE_CODE:
+            raise ValueError(f"dtype must be one of {sorted(_DTYPE_CODE)}")
+        if len(sizes) != spec.n_linear + 1:
+            raise ValueError("layer sizes do not match the stack")
+        self.lib = nat.lib()
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else
+                                   (device.index if isinstance(device, torch.device) else int(device)))
+        self.sizes = [int(s) for s in sizes]
+        self.spec = spec
+        self.has_bias = bool(has_bias)
+        self.dtype_name = dtype
+        self.tdtype = _TORCH_DTYPE[dtype]
+        self.n_linear = spec.n_linear
+        handle = C.c_void_p()
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.poz_ctx_create(
+                self.device.index, self.n_linear, _arr(C.c_int, self.sizes),
+                _arr(C.c_int, [nat.ACT_CODES[a] for a in spec.acts]),
+                _arr(C.c_ubyte, [int(b) for b in spec.drop_z]),
+                _arr(C.c_ubyte, [int(b) for b in spec.drop_a]),
+                int(self.has_bias), nat.LOSS_CE if spec.loss == "ce" else nat.LOSS_MSE,
+                _DTYPE_CODE[dtype], C.byref(handle)))
+        self.ctx = handle
+        self._epochs_declared = 0
+
+    # ---- lifetime ----
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.poz_ctx_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- parameters / optimizer state (float64 host images) ----
+    @staticmethod
+    def _f64(a):
+        if a is None:
+            return None
+        if isinstance(a, torch.Tensor):
+            a = a.detach().cpu().numpy()
+        return np.ascontiguousarray(a, dtype=np.float64)
+
+    def upload_params(self, layer: int, w, b=None):
+        w, b = self._f64(w), self._f64(b)
+        assert w.shape == (self.sizes[layer], self.sizes[layer + 1]), w.shape
+        nat.check(self.lib.poz_params_upload(self.ctx, layer, w.ctypes.data,
+                                             b.ctypes.data if b is not None else None))
+
+    def download_params(self, layer: int):
+        w = np.empty((self.sizes[layer], self.sizes[layer + 1]), dtype=np.float64)
+        b = np.empty((self.sizes[layer + 1],), dtype=np.float64) if self.has_bias else None
+        nat.check(self.lib.poz_params_download(self.ctx, layer, w.ctypes.data,
+                                               b.ctypes.data if b is not None else None))
+        return w, b
+
+    def upload_adam(self, layer: int, m_w, v_w, m_b=None, v_b=None):
+        m_w, v_w, m_b, v_b = (self._f64(t) for t in (m_w, v_w, m_b, v_b))
+        nat.check(self.lib.poz_adam_upload(
+            self.ctx, layer, m_w.ctypes.data, v_w.ctypes.data,
+            m_b.ctypes.data if m_b is not None else None, v_b.ctypes.data if v_b is not None else None))
+
+    def download_adam(self, layer: int):
+        shp = (self.sizes[layer], self.sizes[layer + 1])
+        m_w, v_w = np.empty(shp), np.empty(shp)
+        m_b = np.empty((shp[1],)) if self.has_bias else None
+        v_b = np.empty((shp[1],)) if self.has_bias else None
+        nat.check(self.lib.poz_adam_download(
+            self.ctx, layer, m_w.ctypes.data, v_w.ctypes.data,
+            m_b.ctypes.data if m_b is not None else None, v_b.ctypes.data if v_b is not None else None))
+        return m_w, v_w, m_b, v_b
+
+    def set_adam_step(self, step: int):
+        nat.check(self.lib.poz_adam_set_step(self.ctx, int(step)))
+
+    def get_adam_step(self) -> int:
+        v = C.c_longlong()
+        nat.check(self.lib.poz_adam_get_step(self.ctx, C.byref(v)))
+        return int(v.value)
+
+    # ---- helpers ----
+    def _check_x(self, x: torch.Tensor):
+        if x.device != self.device or x.dtype != self.tdtype or not x.is_contiguous():
+            raise ValueError(f"x must be a contiguous {self.tdtype} tensor on {self.device}")
+        if x.ndim != 2 or x.shape[1] != self.sizes[0]:
+            raise ValueError(f"x must be [batch, {self.sizes[0]}], got {tuple(x.shape)}")
+
+    def _check_target(self, t: torch.Tensor, rows: int | None):
+        if t.device != self.device or not t.is_contiguous():
+            raise ValueError("target must be a contiguous tensor on the model's device")
+        if self.spec.loss == "ce":
+            if t.dtype != torch.int32 or t.ndim != 1:
+                raise ValueError("cross-entropy target must be int32 labels [batch]")
+        else:
+            if t.dtype != self.tdtype or t.ndim != 2 or t.shape[1] != self.sizes[-1]:
+                raise ValueError(f"MSE target must be {self.tdtype} [batch, {self.sizes[-1]}]")
+        if rows is not None and t.shape[0] != rows:
+            raise ValueError("target rows do not match the batch")
+
+    # ---- inference (neural_net_model.py:371-396) ----
+    def forward(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        self._check_x(x)
+        batch = x.shape[0]
+        if out is None:
+            out = torch.empty((batch, self.sizes[-1]), dtype=self.tdtype, device=self.device)
+        if batch:
+            nat.check(self.lib.poz_forward(self.ctx, _ptr(x), batch, _ptr(out), _stream_ptr(self.device)))
+        return out
+
+    def forward_loss(self, x: torch.Tensor, target: torch.Tensor):
+        self._check_x(x)
+        self._check_target(target, x.shape[0])
+        out = torch.empty((x.shape[0], self.sizes[-1]), dtype=self.tdtype, device=self.device)
+        cost = C.c_double()
+        nat.check(self.lib.poz_forward_loss(self.ctx, _ptr(x), _ptr(target), x.shape[0], _ptr(out),
+                                            C.byref(cost), _stream_ptr(self.device)))
+        return out, float(cost.value)
+
+    # ---- training (neural_net_model.py:444-500) ----
+    def train_begin(self, *, optimizer: str = "adam", learning_rate=0.01, decay_rate=0.9,
+                    dropout_rate=0.0, l2_lambda=0.0, beta1=0.9, beta2=0.999, epsilon=1e-8,
+                    epochs=1, progress_stride=0, dropout_seed=0, global_batch=0):
+        cfg = nat.TrainConfig(
+            nat.OPT_ADAM if optimizer == "adam" else nat.OPT_SGD, float(learning_rate),
+            float(decay_rate), float(dropout_rate), float(l2_lambda), float(beta1), float(beta2),
+            float(epsilon), int(epochs), int(progress_stride), int(dropout_seed), int(global_batch))
+        nat.check(self.lib.poz_train_begin(self.ctx, C.byref(cfg)))
+        self._epochs_declared = int(epochs)
+
+    def _mask_array(self, masks):
+        if masks is None:
+            return None, None
+        keep = []
+        ptrs = (C.c_void_p * (2 * self.n_linear))()
+        for i in range(2 * self.n_linear):
+            m = masks.get(i) if isinstance(masks, dict) else masks[i]
+            if m is None:
+                ptrs[i] = None
+            else:
+                if m.dtype != torch.uint8 or m.device != self.device or not m.is_contiguous():
+                    raise ValueError("keep masks must be contiguous uint8 tensors on the device")
+                keep.append(m)
+                ptrs[i] = m.data_ptr()
+        return ptrs, keep
+
+    def train_step(self, x, target, row_idx=None, masks=None, diagnostics=False):
+        batch = self._check_step_args(x, target, row_idx)
+        ptrs, _keep = self._mask_array(masks)
+        nat.check(self.lib.poz_train_step(self.ctx, _ptr(x), _ptr(target), _ptr(row_idx), batch, ptrs,
+                                          int(bool(diagnostics)), _stream_ptr(self.device)))
+
+    def train_backward(self, x, target, row_idx=None, masks=None, diagnostics=False):
+        batch = self._check_step_args(x, target, row_idx)
+        ptrs, _keep = self._mask_array(masks)
+        nat.check(self.lib.poz_train_backward(self.ctx, _ptr(x), _ptr(target), _ptr(row_idx), batch, ptrs,
+                                              int(bool(diagnostics)), _stream_ptr(self.device)))
+
+    def train_apply(self):
+        nat.check(self.lib.poz_train_apply(self.ctx, _stream_ptr(self.device)))
+
+    def _check_step_args(self, x, target, row_idx) -> int:
+        self._check_x(x)
+        if row_idx is not None:
+            if row_idx.dtype != torch.int32 or row_idx.device != self.device or row_idx.ndim != 1:
+                raise ValueError("row_idx must be an int32 vector on the device")
+            self._check_target(target, None)
+            return int(row_idx.shape[0])
+        self._check_target(target, x.shape[0])
+        return int(x.shape[0])
+
+    def grad_buffer(self) -> torch.Tensor:
+        """Zero-copy torch view of the flat local gradient (valid until the next step)."""
+        p, n, dt = C.c_void_p(), C.c_longlong(), C.c_int()
+        nat.check(self.lib.poz_grad_buffer(self.ctx, C.byref(p), C.byref(n), C.byref(dt),
+                                           _stream_ptr(self.device)))
+        return _wrap_device_pointer(p.value, int(n.value), self.tdtype, self.device)
+
+    def costs(self, first: int, count: int) -> np.ndarray:
+        out = np.empty((count,), dtype=np.float64)
+        nat.check(self.lib.poz_train_costs(self.ctx, first, count, out.ctypes.data, _stream_ptr(self.device)))
+        return out
+
+    def update_ratios(self, first_record: int, count: int) -> np.ndarray:
+        out = np.empty((count, self.n_linear), dtype=np.float64)
+        nat.check(self.lib.poz_train_update_ratios(self.ctx, first_record, count, out.ctypes.data,
+                                                   _stream_ptr(self.device)))
+        return out
+
+    # ---- per-kernel timing (bench.py roofline leg) ----
+    def profile_begin(self):
+        nat.check(self.lib.poz_profile_begin(self.ctx))
+
+    def profile_end(self) -> dict:
+        import json
+        buf = C.create_string_buffer(1 << 16)
+        nat.check(self.lib.poz_profile_end(self.ctx, buf, len(buf)))
+        return json.loads(buf.value.decode())
+
+    # ---- diagnostics of the last diagnostics step (neural_net_model.py:491-493,532-583) ----
+    def diag_activation(self, layer: int, which: int, batch: int) -> np.ndarray:
+        out = np.empty((batch, self.sizes[layer + 1]), dtype=np.float64)
+        nat.check(self.lib.poz_diag_activation(self.ctx, layer, which, out.ctypes.data))
+        return out
+
+    def diag_activation_grad(self, layer: int, which: int, batch: int):
+        out = np.empty((batch, self.sizes[layer + 1]), dtype=np.float64)
+        has = C.c_int()
+        nat.check(self.lib.poz_diag_activation_grad(self.ctx, layer, which, out.ctypes.data, C.byref(has)))
+        return out if has.value else None
+
+    def diag_weight_grad(self, layer: int):
+        w = np.empty((self.sizes[layer], self.sizes[layer + 1]), dtype=np.float64)
+        b = np.empty((self.sizes[layer + 1],), dtype=np.float64) if self.has_bias else None
+        nat.check(self.lib.poz_diag_weight_grad(self.ctx, layer, w.ctypes.data,
+                                                b.ctypes.data if b is not None else None))
+        return w, b
+
+
+class _DevPtr:
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+def _wrap_device_pointer(ptr: int, n: int, dtype: torch.dtype, device) -> torch.Tensor:
+    typestr = "<f4" if dtype == torch.float32 else "<f8"
+    with torch.cuda.device(device):
+        return torch.as_tensor(_DevPtr(ptr, n, typestr), device=device)
+
+
+class HostBatchFeeder:
+    """End-to-end stepping from HOST buffers: every step copies its batch from pinned host memory
+    to the device (on a copy stream, double-buffered so the copy of step i+1 overlaps the kernels
+    of step i) and reads that step's cost back to the host, like the reference's per-epoch
+    ``cost.item()`` (neural_net_model.py:503)."""
+
+    def __init__(self, eng: DeviceMLP, batch: int):
+        self.eng = eng
+        dev = eng.device
+        self.batch = batch
+        self.x_dev = [torch.empty((batch, eng.sizes[0]), dtype=eng.tdtype, device=dev) for _ in range(2)]
+        if eng.spec.loss == "ce":
+            self.t_dev = [torch.empty((batch,), dtype=torch.int32, device=dev) for _ in range(2)]
+        else:
+            self.t_dev = [torch.empty((batch, eng.sizes[-1]), dtype=eng.tdtype, device=dev) for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.copied = [torch.cuda.Event() for _ in range(2)]
+        self.consumed = [torch.cuda.Event() for _ in range(2)]
+        self.h2d_bytes = self.x_dev[0].numel() * self.x_dev[0].element_size() + \
+            self.t_dev[0].numel() * self.t_dev[0].element_size()
+        self.d2h_bytes = 8
+        self._n = 0
+        self._staged = -1
+
+    def stage(self, x_pinned: torch.Tensor, t_pinned: torch.Tensor):
+        """Enqueue the host->device copy of the next batch (returns immediately)."""
+        slot = (self._staged + 1) % 2
+        with torch.cuda.stream(self.copy_stream):
+            if self._staged >= 1:
+                self.copy_stream.wait_event(self.consumed[slot])
+            self.x_dev[slot].copy_(x_pinned, non_blocking=True)
+            self.t_dev[slot].copy_(t_pinned, non_blocking=True)
+            self.copied[slot].record(self.copy_stream)
+        self._staged += 1
+
+    def step(self, epoch_index: int) -> None:
+        """Launch the train step on the oldest staged batch."""
+        slot = self._n % 2
+        cur = torch.cuda.current_stream(self.eng.device)
+        cur.wait_event(self.copied[slot])
+        self.eng.train_step(self.x_dev[slot], self.t_dev[slot])
+        self.consumed[slot].record(cur)
+        self._n += 1
+
+    def cost(self, epoch_index: int) -> float:
+        """Device->host read of that step's cost (synchronises on the step)."""
+        return float(self.eng.costs(epoch_index, 1)[0])

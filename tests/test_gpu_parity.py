@@ -1,0 +1,302 @@
+"""Parity of the CUDA path (through the C ABI) with the reference.
+
+Every case is checked twice: against the committed outputs of the unmodified reference
+(tests/golden/step_*.npz) and, where useful, against the numpy oracle run live on the same inputs.
+
+Stated tolerances
+  float32 context: rtol 1e-5 (BASELINE.json north_star) plus atol = 1e-5 * max|reference tensor|,
+                   which covers elements that are small because of cancellation in a K- or
+                   batch-long fp32 sum.
+  float64 context: rtol 1e-10, atol = 1e-12 * max|reference tensor|.
+  argmax of the network output: identical.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_names, load_golden
+from oracle import mlp_oracle as orc
+from oracle.detgen import det_labels, det_normalish, det_params, det_uniform
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"float32": (1e-5, 1e-5), "float64": (1e-10, 1e-12)}
+# parameters after Adam steps: m/(sqrt(v)+eps) turns a relative gradient error into an absolute
+# update error of lr * that error, so the absolute term is tied to lr rather than to |w|
+ADAM_PARAM_ATOL = {"float32": 2e-6, "float64": 1e-12}
+
+
+def close(got, want, dtype, what, rtol=None, atol=None):
+    r, a = TOL[dtype]
+    want = np.asarray(want, dtype=np.float64)
+    scale = float(np.max(np.abs(want))) if want.size else 0.0
+    np.testing.assert_allclose(np.asarray(got, dtype=np.float64), want, rtol=rtol or r,
+                               atol=atol if atol is not None else a * max(scale, 1e-30), err_msg=what)
+
+
+def expand(arrays, key, want_shape):
+    """Golden entry -> (full array | None, flat sub-sample, stride)."""
+    if key in arrays:
+        return arrays[key], None, None
+    sub = arrays[key + "__sub"]
+    n = int(np.prod(want_shape))
+    stride = next(s for s in range(1, 4096) if len(range(0, n, s)) == sub.size)
+    return None, sub, stride
+
+
+def close_golden(arrays, key, got, dtype, what=None, **kw):
+    got = np.asarray(got, dtype=np.float64)
+    full, sub, stride = expand(arrays, key, got.shape)
+    if full is not None:
+        close(got.reshape(full.shape), full, dtype, what or key, **kw)
+    else:
+        close(got.reshape(-1)[::stride], sub, dtype, (what or key) + "__sub", **kw)
+
+
+def build_case(meta, dtype):
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    algos = meta["expanded_algos"]
+    spec = StackSpec.from_algos(algos)
+    sizes = meta["sizes"]
+    has_bias = bool(meta["bias"])
+    params = det_params(sizes, has_bias, meta["salt"])
+    eng = DeviceMLP(sizes, spec, has_bias, dtype, 0)
+    per = 2 if has_bias else 1
+    for l in range(spec.n_linear):
+        eng.upload_params(l, params[per * l], params[per * l + 1] if has_bias else None)
+    x = det_normalish((meta["batch"], sizes[0]), meta["salt"] + 3)
+    tdt = torch.float32 if dtype == "float32" else torch.float64
+    xd = torch.tensor(x, dtype=tdt, device="cuda:0")
+    if spec.loss == "ce":
+        y = det_labels(meta["batch"], sizes[-1], meta["salt"] + 7)
+        td = torch.tensor(y, dtype=torch.int32, device="cuda:0")
+        target = [[int(v)] for v in y]
+    else:
+        t = det_uniform((meta["batch"], sizes[-1]), meta["salt"] + 9, 0.0, 1.0)
+        td = torch.tensor(t, dtype=tdt, device="cuda:0")
+        target = t.tolist()
+    return eng, spec, params, x, xd, target, td
+
+
+def device_masks(arrays, spec, step):
+    out = {}
+    for l in range(spec.n_linear):
+        for which, idx in ((0, spec.z_index[l]), (1, spec.a_index[l])):
+            if idx is None:
+                continue
+            key = f"mask{idx}" if step == 0 else f"mask{idx}_s{step}"
+            if key in arrays:
+                out[2 * l + which] = torch.tensor(arrays[key], dtype=torch.uint8, device="cuda:0").contiguous()
+    return out or None
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+@pytest.mark.parametrize("name", golden_names("step_"))
+def test_train_steps_match_reference_outputs(name, dtype):
+    arrays, meta = load_golden(name)
+    eng, spec, params, x, xd, target, td = build_case(meta, dtype)
+    p = meta.get("dropout", 0.0)
+    batch = meta["batch"]
+    has_bias = bool(meta["bias"])
+    per = 2 if has_bias else 1
+    eng.train_begin(optimizer=meta["optimizer"] or "sgd", learning_rate=meta["lr"],
+                    decay_rate=meta["decay"], dropout_rate=p, l2_lambda=meta["l2"], epochs=meta["steps"],
+                    progress_stride=1)
+    for step in range(meta["steps"]):
+        masks = device_masks(arrays, spec, step) if p > 0 else None
+        eng.train_step(xd, td, masks=masks, diagnostics=(step == 0))
+        if step == 0:
+            for l in range(spec.n_linear):
+                zi, ai = spec.z_index[l], spec.a_index[l]
+                close_golden(arrays, f"act{zi}", eng.diag_activation(l, 0, batch), dtype)
+                g = eng.diag_activation_grad(l, 0, batch)
+                assert g is not None
+                close_golden(arrays, f"actgrad{zi}", g, dtype)
+                if ai is not None:
+                    close_golden(arrays, f"act{ai}", eng.diag_activation(l, 1, batch), dtype)
+                    g = eng.diag_activation_grad(l, 1, batch)
+                    has = (f"actgrad{ai}" in arrays) or (f"actgrad{ai}__sub" in arrays)
+                    assert (g is not None) == has     # trailing softmax: .grad is None
+                    if g is not None:
+                        close_golden(arrays, f"actgrad{ai}", g, dtype)
+                wg, bg = eng.diag_weight_grad(l)
+                close_golden(arrays, f"grad{per * l}", wg, dtype)
+                if has_bias:
+                    close_golden(arrays, f"grad{per * l + 1}", bg, dtype)
+    close(eng.costs(0, meta["steps"]), arrays["costs"], dtype, "costs")
+    adam = meta["optimizer"] == "adam"
+    patol = ADAM_PARAM_ATOL[dtype] if adam else None
+    for l in range(spec.n_linear):
+        w, b = eng.download_params(l)
+        close_golden(arrays, f"param{per * l}", w, dtype, atol=patol)
+        if has_bias:
+            close_golden(arrays, f"param{per * l + 1}", b, dtype, atol=patol)
+    if adam:
+        assert eng.get_adam_step() == int(arrays["adam_step"])
+        for l in range(spec.n_linear):
+            m_w, v_w, m_b, v_b = eng.download_adam(l)
+            close_golden(arrays, f"adam_m{per * l}", m_w, dtype)
+            close_golden(arrays, f"adam_v{per * l}", v_w, dtype)
+            if has_bias:
+                close_golden(arrays, f"adam_m{per * l + 1}", m_b, dtype)
+                close_golden(arrays, f"adam_v{per * l + 1}", v_b, dtype)
+    # inference on the updated parameters, with and without a target
+    out, cost = eng.forward_loss(xd, td)
+    ptol = dict(rtol=1e-4) if (adam and dtype == "float32") else {}
+    close_golden(arrays, "infer_out", out.cpu().numpy(), dtype, **ptol)
+    close(cost, arrays["infer_cost"], dtype, "infer_cost", **ptol)
+    out2 = eng.forward(xd)
+    assert torch.equal(out, out2) or torch.allclose(out, out2, rtol=1e-6, atol=0)
+    one = eng.forward(xd[:1].contiguous()).cpu().numpy()[0]
+    close_golden(arrays, "infer_out_1d", one, dtype, **ptol)
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+def test_weight_update_ratio_matches_oracle(dtype):
+    arrays, meta = load_golden("step_relu_tanh_adam")
+    eng, spec, params, x, xd, target, td = build_case(meta, dtype)
+    stack = orc.parse_stack(meta["expanded_algos"])
+    eng.train_begin(optimizer="adam", learning_rate=meta["lr"], decay_rate=meta["decay"],
+                    l2_lambda=meta["l2"], epochs=3, progress_stride=1)
+    adam = orc.AdamState()
+    want = []
+    p = params
+    for step in range(3):
+        eng.train_step(xd, td)
+        newp, *_ = orc.train_step(stack, p, x, target, lr=meta["lr"] * meta["decay"] ** step,
+                                  optimizer="adam", adam=adam, l2_lambda=meta["l2"])
+        want.append([orc.weight_update_ratio(newp[2 * l], p[2 * l]) for l in range(spec.n_linear)])
+        p = newp
+    got = eng.update_ratios(0, 3)
+    np.testing.assert_allclose(got, np.asarray(want), rtol=2e-3 if dtype == "float32" else 1e-8)
+
+
+def mnist_stack():
+    sizes = [784, 256, 128, 10]
+    algos = ["linear", "relu", "linear", "relu", "linear", "softmax"]
+    return sizes, algos
+
+
+@pytest.mark.parametrize("optimizer", ["adam", "sgd"])
+def test_config2_full_size_against_live_oracle(optimizer):
+    """BASELINE.json configs[1]: 784-256-128-10, softmax + CE, batch 1024, fp32; 3 steps."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    sizes, algos = mnist_stack()
+    B = 1024
+    params = det_params(sizes, True, 77)
+    x = det_normalish((B, 784), 78)
+    y = det_labels(B, 10, 79)
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+    for l in range(3):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    xd = torch.tensor(x, dtype=torch.float32, device="cuda:0")
+    yd = torch.tensor(y, dtype=torch.int32, device="cuda:0")
+    eng.train_begin(optimizer=optimizer, learning_rate=0.01, decay_rate=0.9, l2_lambda=0.001, epochs=3)
+    for _ in range(3):
+        eng.train_step(xd, yd)
+    stack = orc.parse_stack(algos)
+    adam = orc.AdamState()
+    p, costs = params, []
+    tgt = [[int(v)] for v in y]
+    for step in range(3):
+        p, c, *_ = orc.train_step(stack, p, x, tgt, lr=0.01 * 0.9 ** step, optimizer=optimizer,
+                                  adam=adam, l2_lambda=0.001)
+        costs.append(c)
+    close(eng.costs(0, 3), costs, "float32", "costs")
+    for l in range(3):
+        w, b = eng.download_params(l)
+        atol = ADAM_PARAM_ATOL["float32"] if optimizer == "adam" else None
+        close(w, p[2 * l], "float32", f"W{l}", atol=atol)
+        close(b, p[2 * l + 1], "float32", f"b{l}", atol=atol)
+    out = eng.forward(xd).cpu().numpy()
+    ref = orc.forward(stack, p, x)[0][-1]
+    close(out, ref, "float32", "probs", rtol=1e-4)
+    # argmax identical wherever the reference's top-2 margin exceeds the stated tolerance
+    srt = np.sort(ref, axis=1)
+    decided = (srt[:, -1] - srt[:, -2]) > 1e-4
+    assert decided.mean() > 0.99
+    assert (out.argmax(1)[decided] == ref.argmax(1)[decided]).all()
+
+
+@pytest.mark.parametrize("batch", [1, 8, 64, 512, 4096, 32768, 262144])
+def test_config3_inference_sweep(batch):
+    """BASELINE.json configs[2]: batched inference on the 784-256-128-10 model.  Small batches are
+    compared with the oracle row for row; every batch must agree with a 4096-row re-run of its own
+    rows (chunking / tiling independence) and produce rows that sum to 1."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    sizes, algos = mnist_stack()
+    params = det_params(sizes, True, 5)
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+    for l in range(3):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    g = torch.Generator(device="cuda:0").manual_seed(batch)
+    xd = torch.randn((batch, 784), generator=g, device="cuda:0", dtype=torch.float32)
+    out = eng.forward(xd)
+    assert out.shape == (batch, 10)
+    assert torch.allclose(out.sum(1), torch.ones(batch, device="cuda:0"), atol=1e-5)
+    n_chk = min(batch, 2048)
+    ref = orc.forward(orc.parse_stack(algos), params, xd[:n_chk].cpu().numpy().astype(np.float64))[0][-1]
+    close(out[:n_chk].cpu().numpy(), ref, "float32", "probs", rtol=1e-4)
+    assert (out[:n_chk].cpu().numpy().argmax(1) == ref.argmax(1)).mean() > 0.999
+    if batch > 4096:
+        tail = xd[batch - 4096:].contiguous()
+        again = eng.forward(tail)
+        assert torch.allclose(out[batch - 4096:], again, rtol=1e-6, atol=1e-9)
+
+
+def test_row_gather_equals_materialised_batch():
+    """The in-kernel row gather (replacing neural_net_model.py:460-461,472) is bit-identical to
+    training on the gathered copy."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    sizes, algos = [31, 20, 7], ["linear", "tanh", "linear", "softmax"]
+    params = det_params(sizes, True, 9)
+    pool = torch.tensor(det_normalish((500, 31), 10), dtype=torch.float32, device="cuda:0")
+    labels = torch.tensor(det_labels(500, 7, 11), dtype=torch.int32, device="cuda:0")
+    idx = torch.tensor(det_labels(257, 500, 12), dtype=torch.int32, device="cuda:0")
+    res = []
+    for gather in (True, False):
+        eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+        for l in range(2):
+            eng.upload_params(l, params[2 * l], params[2 * l + 1])
+        eng.train_begin(optimizer="adam", learning_rate=0.01, l2_lambda=0.001, epochs=2)
+        for _ in range(2):
+            if gather:
+                eng.train_step(pool, labels, row_idx=idx)
+            else:
+                eng.train_step(pool[idx.long()].contiguous(), labels[idx.long()].contiguous())
+        res.append([eng.download_params(l) for l in range(2)] + [eng.costs(0, 2)])
+    for a, b in zip(res[0][:2], res[1][:2]):
+        np.testing.assert_array_equal(a[0], b[0])
+        np.testing.assert_array_equal(a[1], b[1])
+    np.testing.assert_allclose(res[0][2], res[1][2], rtol=1e-12)
+
+
+def test_in_kernel_dropout_statistics_and_determinism():
+    """Philox masks: keep-rate ~ 1-p on every hidden entry, kept values scaled by 1/(1-p),
+    backward sees the same mask as forward (zero gradient exactly where the output was dropped)."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    sizes, algos = [64, 96, 80, 10], ["linear", "sigmoid", "linear", "tanh", "linear", "softmax"]
+    spec = StackSpec.from_algos(algos)
+    params = det_params(sizes, True, 21)
+    B, p = 2048, 0.3
+    xd = torch.tensor(det_normalish((B, 64), 22), dtype=torch.float32, device="cuda:0")
+    yd = torch.tensor(det_labels(B, 10, 23), dtype=torch.int32, device="cuda:0")
+    runs = []
+    for seed in (1, 1, 2):
+        eng = DeviceMLP(sizes, spec, True, "float32", 0)
+        for l in range(3):
+            eng.upload_params(l, params[2 * l], params[2 * l + 1])
+        eng.train_begin(optimizer="sgd", learning_rate=0.01, dropout_rate=p, epochs=1, dropout_seed=seed)
+        eng.train_step(xd, yd, diagnostics=True)
+        a1 = eng.diag_activation(0, 1, B)       # sigmoid output, hidden -> dropped
+        g1 = eng.diag_activation_grad(0, 1, B)
+        z2 = eng.diag_activation(1, 0, B)       # second linear output, hidden -> dropped
+        runs.append((a1, z2, eng.costs(0, 1)[0]))
+        keep = a1 != 0.0
+        assert abs(keep.mean() - (1 - p)) < 0.01
+        assert a1[keep].min() >= 0.0 and a1[keep].max() <= 1.0 / (1 - p) + 1e-5
+        assert abs((z2 != 0.0).mean() - (1 - p)) < 0.01
+        assert g1 is not None
+    np.testing.assert_array_equal(runs[0][0], runs[1][0])       # same seed -> same masks
+    assert (runs[0][0] != runs[2][0]).any()                     # different seed -> different masks
+    assert np.isfinite(runs[0][2])

@@ -86,3 +86,21 @@ def test_oracle_train_steps_match_reference(name):
     o1t, il = orc.forward(stack, params, x[0], training=True)
     np.testing.assert_allclose(orc.loss_value(stack, o1t, il, target[0]), arrays["infer_cost_1d_t"],
                                rtol=RTOL, atol=ATOL)
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names("step_") if "dropout" not in n])
+def test_torch_cpu_port_matches_reference(name):
+    """The torch-operator port used as the timed CPU baseline gives the reference's numbers."""
+    import torch
+    from oracle.torch_cpu_port import TorchCpuMLP
+    arrays, meta = load_golden(name)
+    stack, params, x, target = case_inputs(meta)
+    m = TorchCpuMLP(meta["expanded_algos"], params, meta["optimizer"] or "sgd")
+    xt = torch.tensor(x)
+    tt = (torch.tensor([t[0] for t in target], dtype=torch.int64) if stack.loss == "ce"
+          else torch.tensor(target, dtype=torch.float64))
+    costs = [m.train_step(xt, tt, meta["lr"] * meta["decay"] ** s, l2_lambda=meta["l2"])
+             for s in range(meta["steps"])]
+    np.testing.assert_allclose(costs, arrays["costs"], rtol=RTOL, atol=ATOL)
+    for i, q in enumerate(m.params):
+        check_against(arrays, f"param{i}", q.detach().numpy(), 1e-9, 1e-12)

@@ -135,8 +135,8 @@ static DropPoint make_drop(const poz_ctx* c, int layer, int which, const void* c
     d.enabled = (flag && c->training_pass && p > 0.0) ? 1 : 0;
     d.mask = (d.enabled && masks) ? static_cast<const uint8_t*>(masks[2 * layer + which]) : nullptr;
     d.point = (uint32_t)(2 * layer + which);
-    d.keep_prob = (float)(1.0 - p);
-    d.scale = (float)(1.0 / (1.0 - p));
+    d.keep_prob = 1.0 - p;
+    d.scale = 1.0 / (1.0 - p);
     return d;
 }
 

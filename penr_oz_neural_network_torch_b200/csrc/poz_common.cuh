@@ -79,8 +79,8 @@ struct DropPoint {
     const uint8_t* mask;   // host-recorded keep mask [M][N] or nullptr
     int enabled;           // 0 = identity
     uint32_t point;        // unique id of this dropout point inside the stack
-    float keep_prob;       // 1 - p
-    float scale;           // 1 / (1 - p)
+    double keep_prob;      // 1 - p
+    double scale;          // 1 / (1 - p)
 };
 
 __device__ __forceinline__ bool drop_keep(const DropPoint& d, const DevState* st, long long m,
@@ -89,7 +89,7 @@ __device__ __forceinline__ bool drop_keep(const DropPoint& d, const DevState* st
     if (d.mask) return d.mask[e] != 0;
     uint32_t r = philox_first((uint32_t)e, (uint32_t)(e >> 32), d.point, (uint32_t)st->cur_epoch,
                               (uint32_t)st->seed, (uint32_t)(st->seed >> 32));
-    return (r * 2.3283064365386963e-10f) < d.keep_prob;
+    return (r * 2.3283064365386963e-10f) < (float)d.keep_prob;
 }
 
 // ---- activations (neural_net_model.py:172-188) and their derivatives from the OUTPUT value -------

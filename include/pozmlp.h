@@ -135,6 +135,32 @@ int poz_train_backward(poz_ctx* ctx, const void* x_dev, const void* target_dev,
                        int diagnostics, void* stream);
 int poz_train_apply(poz_ctx* ctx, void* stream);
 
+/* ---- inference without any allocation ---------------------------------------------------------
+ * No counterpart in the reference (it has no notion of device memory at all).
+ *
+ * For callers that must not allocate GPU memory when they need a prediction -- for example a server
+ * whose own memory pool already owns the device, or a loop that cannot tolerate the device-wide
+ * pause an allocation may cause -- and that therefore cannot create a poz_ctx.  The caller passes
+ * every input and output as device pointers it already holds: float32 weights W[in][out] row-major
+ * and biases b[out] per layer (biases_dev, or single entries of it, may be NULL), x_dev
+ * [batch][sizes[0]], out_dev [batch][sizes[n_linear]].  Result = poz_forward on a float32 context
+ * holding the same parameters.
+ *
+ * The hidden activations go through a fixed POZ_NOALLOC_SCRATCH_BYTES array that is part of the
+ * library image: every GPU that loads the library keeps those 8 MiB until the process ends.  Limit:
+ * no layer output wider than POZ_NOALLOC_MAX_WIDTH (larger requests fail with a message; use a
+ * context for those); any batch size (rows are processed in slices that fit the array).
+ * The array is shared by all calls and keeps the previous call's contents; nothing in it needs to be
+ * zero, so nothing is cleared.  Calls that run at the same time on one GPU overwrite each other's
+ * activations: serialise them.  The first call on a device looks up the array's device address; make
+ * that first call before starting any stream capture on that device.  The function calls no
+ * cudaMalloc / cudaFree and no allocating library routine. */
+#define POZ_NOALLOC_SCRATCH_BYTES (8ll << 20)
+#define POZ_NOALLOC_MAX_WIDTH 4096
+int poz_forward_noalloc(int device, int n_linear, const int* sizes, const int* act_codes,
+                        const float* const* weights_dev, const float* const* biases_dev,
+                        const float* x_dev, long long batch, float* out_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,7 +22,7 @@ OPT_SGD, OPT_ADAM = 0, 1
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
-SOURCES = ["poz_api.cu"]
+SOURCES = ["poz_api.cu", "poz_noalloc.cu"]
 
 
 class PozError(RuntimeError):
@@ -109,7 +109,11 @@ SIGNATURES = {
     "poz_grad_buffer": (_I, [_VP, C.POINTER(_VP), C.POINTER(_LL), C.POINTER(_I), _VP]),
     "poz_train_backward": (_I, [_VP, _VP, _VP, _VP, _LL, C.POINTER(_VP), _I, _VP]),
     "poz_train_apply": (_I, [_VP, _VP]),
+    "poz_forward_noalloc": (_I, [_I, _I, C.POINTER(_I), C.POINTER(_I), C.POINTER(_VP), C.POINTER(_VP),
+                                _VP, _LL, _VP, _VP]),
 }
+NOALLOC_MAX_WIDTH = 4096
+NOALLOC_SCRATCH_BYTES = 8 << 20
 
 
 def lib():

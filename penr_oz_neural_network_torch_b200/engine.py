@@ -302,6 +302,32 @@ class DeviceMLP:
         return w, b
 
 
+def forward_noalloc(sizes, acts, weights, biases, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """Inference through ``poz_forward_noalloc``: no context, no allocation inside the call.
+
+    Meant for code that already owns all of its device memory and may not ask for more (a server
+    whose pool has claimed the GPU, a loop that cannot stall on an allocation).  ``weights`` /
+    ``biases`` are float32 CUDA tensors ``[in, out]`` / ``[out]`` (``biases`` or its items may be
+    None), ``x`` ``[batch, sizes[0]]``, ``out`` a caller-provided ``[batch, sizes[-1]]`` tensor.
+    Layers wider than ``_native.NOALLOC_MAX_WIDTH`` are refused.  Calls on one GPU must not overlap:
+    they share one fixed scratch array inside the library.
+    """
+    lib = nat.lib()
+    n = len(acts)
+    dev = x.device
+    for t in list(weights) + [b for b in (biases or []) if b is not None] + [x, out]:
+        if t.dtype != torch.float32 or t.device != dev or not t.is_contiguous():
+            raise ValueError("forward_noalloc takes contiguous float32 tensors on one CUDA device")
+    wp = (C.c_void_p * n)(*[w.data_ptr() for w in weights])
+    bp = None
+    if biases is not None:
+        bp = (C.c_void_p * n)(*[None if b is None else b.data_ptr() for b in biases])
+    nat.check(lib.poz_forward_noalloc(dev.index, n, _arr(C.c_int, [int(v) for v in sizes]),
+                                      _arr(C.c_int, [nat.ACT_CODES[a] for a in acts]), wp, bp,
+                                      _ptr(x), x.shape[0], _ptr(out), _stream_ptr(dev)))
+    return out
+
+
 class _DevPtr:
     def __init__(self, ptr, n, typestr):
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False),

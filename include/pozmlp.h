@@ -128,6 +128,11 @@ int poz_diag_weight_grad(poz_ctx* ctx, int layer, double* w_grad, double* b_grad
  * The flat gradient image (all layers, compute dtype... always float32/float64) that the host
  * all-reduces with NCCL between the backward and the update of a step. */
 int poz_grad_buffer(poz_ctx* ctx, void** dev_ptr, long long* n_elems, int* dtype_code, void* stream);
+/* Per-layer bucket: makes `stream` wait until layer `layer`'s weight gradient of the running
+ * backward is complete, sums its batch-split slabs on `stream`, and returns the layer's [W;b] slice
+ * of the flat buffer -- so the host can all-reduce layer l on a communication stream while the
+ * backward of layers l-1..0 is still running on the compute stream. */
+int poz_grad_layer(poz_ctx* ctx, int layer, void** dev_ptr, long long* n_elems, void* stream);
 /* Split step for data parallelism: backward leaves SUM-ready local gradients (already scaled by
  * 1/global_batch) in the flat buffer; the caller all-reduces; poz_train_apply runs the update. */
 int poz_train_backward(poz_ctx* ctx, const void* x_dev, const void* target_dev,

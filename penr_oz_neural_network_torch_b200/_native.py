@@ -107,6 +107,7 @@ SIGNATURES = {
     "poz_diag_activation_grad": (_I, [_VP, _I, _I, _VP, C.POINTER(_I)]),
     "poz_diag_weight_grad": (_I, [_VP, _I, _VP, _VP]),
     "poz_grad_buffer": (_I, [_VP, C.POINTER(_VP), C.POINTER(_LL), C.POINTER(_I), _VP]),
+    "poz_grad_layer": (_I, [_VP, _I, C.POINTER(_VP), C.POINTER(_LL), _VP]),
     "poz_train_backward": (_I, [_VP, _VP, _VP, _VP, _LL, C.POINTER(_VP), _I, _VP]),
     "poz_train_apply": (_I, [_VP, _VP]),
     "poz_forward_noalloc": (_I, [_I, _I, C.POINTER(_I), C.POINTER(_I), C.POINTER(_VP), C.POINTER(_VP),

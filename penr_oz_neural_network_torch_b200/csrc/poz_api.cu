@@ -408,7 +408,8 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
 
     {
         ProfScope ps(c, "step_begin", stream);
-        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, nl);
+        const double share = c->cfg.global_batch > 0 ? (double)batch / (double)c->cfg.global_batch : 1.0;
+        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, nl, share);
         POZ_LAUNCH_CHECK();
     }
 
@@ -471,6 +472,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             ProfScope ps(c, "bwd_w_l" + std::to_string(l), stream);
             POZ_TRY((launch_gemm<T, false, false>(kind, A, B, (long long)K + hb, N, batch,
                                                   seg.splits[l], kchunk[l], epi, stream)));
+            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
         }
         if (l > 0) {
             const T* w = static_cast<const T*>(c->P) + c->off[l];
@@ -627,6 +629,12 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     if (cudaMemset(c->st, 0, sizeof(DevState)) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
     if (dev_alloc(reinterpret_cast<void**>(&c->scalar_cost), sizeof(double))) return fail();
     std::memset(&c->cfg, 0, sizeof(c->cfg));
+    c->grad_ready.assign(n_linear, nullptr);
+    for (int l = 0; l < n_linear; ++l)
+        if (cudaEventCreateWithFlags(&c->grad_ready[l], cudaEventDisableTiming) != cudaSuccess) {
+            set_error("cudaEventCreate failed");
+            return fail();
+        }
     *out = c;
     return 0;
 }
@@ -636,6 +644,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_workspace(c);
+    for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
     dev_free(reinterpret_cast<void*&>(c->st));
     dev_free(reinterpret_cast<void*&>(c->cost_ring));
@@ -815,6 +824,33 @@ int poz_grad_buffer(poz_ctx* c, void** dev_ptr, long long* n_elems, int* dtype_c
     if (dev_ptr) *dev_ptr = c->G;
     if (n_elems) *n_elems = c->p_total;
     if (dtype_code) *dtype_code = c->dtype;
+    return 0;
+}
+
+int poz_grad_layer(poz_ctx* c, int layer, void** dev_ptr, long long* n_elems, void* stream) {
+    POZ_TRY(check_layer(c, layer, "poz_grad_layer"));
+    if (!c->grads_pending) POZ_FAIL("poz_grad_layer: run poz_train_backward first");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    POZ_CUDA(cudaStreamWaitEvent(s, c->grad_ready[layer], 0));
+    const long long n = ((long long)c->sizes[layer] + c->has_bias) * c->sizes[layer + 1];
+    if (c->seg_splits[layer] > 1) {
+        SegTable seg;
+        fill_seg(c, seg);
+        for (int l = 0; l < c->nl; ++l) seg.splits[l] = l == layer ? c->seg_splits[l] : 1;
+        int bx = (int)std::min<long long>((n + 255) / 256, 2LL * num_sms(c->device));
+        ProfScope ps(c, "grad_finalize", s);
+        if (c->dtype == POZ_DTYPE_F64)
+            grad_finalize_kernel<double><<<dim3(std::max(bx, 1), c->nl), 256, 0, s>>>(static_cast<double*>(c->G), c->p_total, seg);
+        else
+            grad_finalize_kernel<float><<<dim3(std::max(bx, 1), c->nl), 256, 0, s>>>(static_cast<float*>(c->G), c->p_total, seg);
+        POZ_LAUNCH_CHECK();
+        c->seg_splits[layer] = 1;
+    }
+    bool all = true;
+    for (int l = 0; l < c->nl; ++l) all &= c->seg_splits[l] == 1;
+    if (all) c->grads_reduced = true;
+    if (dev_ptr) *dev_ptr = static_cast<char*>(c->G) + c->off[layer] * c->esz;
+    if (n_elems) *n_elems = n;
     return 0;
 }
 

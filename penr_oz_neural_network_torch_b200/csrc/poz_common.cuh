@@ -43,7 +43,7 @@ enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_TANH = 3, ACT_
 struct DevState {
     // hyper-parameters of the current train() call
     double lr0, decay, beta1, beta2, eps, l2;
-    double inv_global_batch_unused;
+    double l2_share;           // share of the L2 penalty this rank adds to the cost (local/global batch)
     unsigned long long seed;
     long long progress_stride;
     int optimizer;

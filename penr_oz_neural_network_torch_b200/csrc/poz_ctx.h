@@ -23,6 +23,7 @@ struct poz_ctx {
     void* Gdiag = nullptr;            // finished gradients of the last diagnostics step
     int g_slabs = 0, max_splits = 16;
     std::vector<int> seg_splits;
+    std::vector<cudaEvent_t> grad_ready;   // recorded when layer l's weight gradient is complete
 
     poz::DevState* st = nullptr;
     double* cost_ring = nullptr;  long long cost_cap = 0;

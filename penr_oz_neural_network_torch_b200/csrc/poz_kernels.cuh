@@ -18,9 +18,10 @@ struct SegTable {
 // First kernel of every step: advances the epoch / Adam counters and derives the step's scalars
 // (neural_net_model.py:464 lr decay; torch/optim/adam.py bias corrections).
 __global__ void step_begin_kernel(DevState* st, double* cost_ring, long long cost_cap,
-                                  double* stats, long long stats_cap, int n_layers) {
+                                  double* stats, long long stats_cap, int n_layers, double l2_share) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     long long e = st->next_epoch;
+    st->l2_share = l2_share;
     st->cur_epoch = e;
     st->next_epoch = e + 1;
     double lr = st->lr0 * pow(st->decay, (double)e);
@@ -237,7 +238,7 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
             sd += d; sd2 += d * d; sw += (double)wn; sw2 += (double)wn * (double)wn;
         }
     }
-    if (st->l2 > 0.0) block_add_double(l2acc * st->l2, cost_slot(cost_base, cost_cap, st));
+    if (st->l2 > 0.0) block_add_double(l2acc * st->l2 * st->l2_share, cost_slot(cost_base, cost_cap, st));
     if (rec >= 0) {
         double* s = stats + (rec * seg.n + l) * 4;
         block_add_double(sd, s + 0);

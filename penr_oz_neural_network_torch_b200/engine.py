@@ -261,6 +261,12 @@ class DeviceMLP:
                                            _stream_ptr(self.device)))
         return _wrap_device_pointer(p.value, int(n.value), self.tdtype, self.device)
 
+    def grad_layer(self, layer: int, stream: "torch.cuda.Stream") -> torch.Tensor:
+        """Layer ``layer``'s slice of the flat gradient, ready on ``stream`` (see poz_grad_layer)."""
+        p, n = C.c_void_p(), C.c_longlong()
+        nat.check(self.lib.poz_grad_layer(self.ctx, layer, C.byref(p), C.byref(n), int(stream.cuda_stream)))
+        return _wrap_device_pointer(p.value, int(n.value), self.tdtype, self.device)
+
     def costs(self, first: int, count: int) -> np.ndarray:
         out = np.empty((count,), dtype=np.float64)
         nat.check(self.lib.poz_train_costs(self.ctx, first, count, out.ctypes.data, _stream_ptr(self.device)))

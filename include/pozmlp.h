@@ -140,6 +140,18 @@ int poz_train_backward(poz_ctx* ctx, const void* x_dev, const void* target_dev,
                        int diagnostics, void* stream);
 int poz_train_apply(poz_ctx* ctx, void* stream);
 
+/* ---- tcgen05 GEMM building block (new; the dense contractions of LinearLayer.forward,
+ * neural_net_model.py:117, and of its autograd backward, :495, for wide layers) -----------------
+ * bf16 row-major device matrices, fp32 accumulation in tensor memory.  Exposed so that the three
+ * operand-layout variants can be tested and benchmarked in isolation; bf16 contexts call the same
+ * launchers internally.
+ *   variant 0 (forward)   out bf16 [m][n] = act(a[m][k] * b[k][n] + bias[n])         (bias may be NULL)
+ *   variant 1 (backward-x) out bf16 [m][n] = (a[m][k] * b[n][k]^T) .* act'(aux[m][n])  (aux = activation outputs)
+ *   variant 2 (backward-w) out fp32 [splits][m][n] = partial sums over k of a[k][m]^T * b[k][n]
+ * n and k (and m for variant 2) must be multiples of 8. */
+int poz_tc_gemm(int device, int variant, const void* a, const void* b, long long m, int n, long long k,
+                void* out, const float* bias, const void* aux, int act, int splits, void* stream);
+
 /* ---- inference without any allocation ---------------------------------------------------------
  * No counterpart in the reference (it has no notion of device memory at all).
  *

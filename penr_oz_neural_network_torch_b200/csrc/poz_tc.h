@@ -1,0 +1,18 @@
+// Launchers of the tcgen05 GEMM (csrc/poz_tc.cu) used by the bf16 context.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+namespace poz {
+namespace tc {
+// out[M][N] = act(x[M][K] * w[K][N] + bias[N])
+int gemm_forward(const __nv_bfloat16* x, const __nv_bfloat16* w, long long M, int N, int K, const float* bias,
+                 int act, __nv_bfloat16* out, int sms, cudaStream_t s);
+// dz_prev[M][K_in] = (dz[M][N_out] * w[K_in][N_out]^T) .* act_prev'(a_prev[M][K_in])
+int gemm_backward_data(const __nv_bfloat16* dz, const __nv_bfloat16* w, long long M, int K_in, int N_out,
+                       const __nv_bfloat16* a_prev, int act_prev, __nv_bfloat16* dz_prev, int sms, cudaStream_t s);
+// g[split][K_in][N_out] = partial sums over the batch of x[batch][K_in]^T * dz[batch][N_out]
+int gemm_backward_weight(const __nv_bfloat16* x, const __nv_bfloat16* dz, long long batch, int K_in, int N_out,
+                         float* g, long long slab, int splits, int sms, cudaStream_t s);
+}  // namespace tc
+}  // namespace poz

@@ -3,6 +3,8 @@
 #include "poz_ctx.h"
 #include "poz_kernels.cuh"
 #include "poz_simt_gemm.cuh"
+#include "poz_tc.h"
+#include "poz_wide_kernels.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -206,7 +208,7 @@ static int reserve_train(poz_ctx* c, long long batch, bool diag) {
         }
         c->ws_diag = 0;
         for (int l = 0; l < nl; ++l) {
-            size_t bytes = (size_t)batch * c->sizes[l + 1] * c->esz;
+            size_t bytes = (size_t)batch * c->sizes[l + 1] * c->act_esz;
             POZ_TRY(dev_alloc(&c->abuf[l], bytes));
             POZ_TRY(dev_alloc(&c->dzbuf[l], bytes));
             if (c->acts[l] != ACT_NONE) POZ_TRY(dev_alloc(&c->zbuf[l], bytes));
@@ -215,7 +217,7 @@ static int reserve_train(poz_ctx* c, long long batch, bool diag) {
     }
     if (diag && c->ws_diag < c->ws_train) {
         for (int l = 0; l < nl; ++l) {
-            size_t bytes = (size_t)c->ws_train * c->sizes[l + 1] * c->esz;
+            size_t bytes = (size_t)c->ws_train * c->sizes[l + 1] * c->act_esz;
             dev_free(c->dz_rec[l]); dev_free(c->da_rec[l]);
             POZ_TRY(dev_alloc(&c->dz_rec[l], bytes));
             if (c->acts[l] != ACT_NONE) POZ_TRY(dev_alloc(&c->da_rec[l], bytes));
@@ -231,7 +233,7 @@ static int reserve_infer(poz_ctx* c, long long chunk) {
     dev_free(c->pong);
     int widest = 0;
     for (int l = 1; l <= c->nl; ++l) widest = std::max(widest, c->sizes[l]);
-    size_t bytes = (size_t)chunk * widest * c->esz;
+    size_t bytes = (size_t)chunk * widest * c->act_esz;
     POZ_TRY(dev_alloc(&c->ping, bytes));
     POZ_TRY(dev_alloc(&c->pong, bytes));
     c->ws_infer = chunk;
@@ -505,6 +507,146 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     return 0;
 }
 
+
+// ---- wide (bf16 / tcgen05) path -------------------------------------------------------------------
+// fp32 master parameters + Adam state (update_kernel<float>), bf16 parameter copy `Pb`, bf16
+// activations and activation gradients, fp32 weight gradients straight from tensor memory.
+static int forward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target, long long batch,
+                        __nv_bfloat16* out, double* cost_host, cudaStream_t stream) {
+    const int nl = c->nl;
+    const int sms = num_sms(c->device);
+    long long chunk = std::min<long long>(batch, 16384);
+    POZ_TRY(reserve_infer(c, chunk));
+    c->training_pass = false;
+    if (cost_host) POZ_CUDA(cudaMemsetAsync(c->scalar_cost, 0, sizeof(double), stream));
+    const int n_out = c->sizes[nl];
+    const float* P = static_cast<const float*>(c->P);
+    const __nv_bfloat16* Pb = static_cast<const __nv_bfloat16*>(c->Pb);
+    for (long long r0 = 0; r0 < batch; r0 += chunk) {
+        const long long m = std::min(chunk, batch - r0);
+        const __nv_bfloat16* cur = x + r0 * c->sizes[0];
+        __nv_bfloat16* bufs[2] = {static_cast<__nv_bfloat16*>(c->ping), static_cast<__nv_bfloat16*>(c->pong)};
+        int flip = 0;
+        for (int l = 0; l < nl; ++l) {
+            const int K = c->sizes[l], N = c->sizes[l + 1];
+            __nv_bfloat16* dst = (l == nl - 1) ? out + r0 * n_out : bufs[flip];
+            ProfScope ps(c, "tc_fwd_l" + std::to_string(l), stream);
+            POZ_TRY(tc::gemm_forward(cur, Pb + c->off[l], m, N, K,
+                                     c->has_bias ? P + c->off[l] + (long long)K * N : nullptr, c->acts[l], dst, sms, stream));
+            cur = dst;
+            flip ^= 1;
+        }
+        if (cost_host) {
+            WideLossArgs a{};
+            a.y = cur; a.target = static_cast<const __nv_bfloat16*>(target) + r0 * n_out;
+            a.total = m * n_out; a.act = c->acts[nl - 1];
+            a.inv_count = 1.0 / ((double)batch * n_out);
+            a.cost_base = c->scalar_cost; a.cost_cap = 1; a.st = nullptr;
+            ProfScope ps(c, "loss", stream);
+            int blocks = (int)std::min<long long>((a.total / 8 + 255) / 256, 148 * 8);
+            wide_mse_loss_kernel<<<std::max(blocks, 1), 256, 0, stream>>>(a);
+            POZ_LAUNCH_CHECK();
+        }
+    }
+    if (cost_host) {
+        POZ_CUDA(cudaMemcpyAsync(cost_host, c->scalar_cost, sizeof(double), cudaMemcpyDeviceToHost, stream));
+        POZ_CUDA(cudaStreamSynchronize(stream));
+    }
+    return 0;
+}
+
+static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target, const int* row_idx,
+                         long long batch, const void* const* masks, int diag, cudaStream_t stream) {
+    const int nl = c->nl;
+    const int sms = num_sms(c->device);
+    if (!c->train_begun) POZ_FAIL("poz_train_step: call poz_train_begin first");
+    if (batch <= 0) POZ_FAIL("poz_train_step: empty batch");
+    if (row_idx) POZ_FAIL("poz_train_step: bf16 contexts take a materialised batch (no row gather: TMA reads dense tiles)");
+    if (masks || c->cfg.dropout_rate > 0.0) POZ_FAIL("poz_train_step: dropout is not available in bf16 contexts yet");
+    if (diag) POZ_FAIL("poz_train_step: diagnostics are not available in bf16 contexts yet");
+    if (batch % 8) POZ_FAIL("poz_train_step: bf16 contexts need a batch that is a multiple of 8");
+    POZ_TRY(reserve_train(c, batch, false));
+    // split the batch reduction of dW only when the output tiles alone cannot fill the GPU
+    c->seg_splits.assign(nl, 1);
+    int slabs = 1;
+    for (int l = 0; l < nl; ++l) {
+        long long tiles = (long long)((c->sizes[l] + tc_tile_m() - 1) / tc_tile_m()) * ((c->sizes[l + 1] + tc_tile_n() - 1) / tc_tile_n());
+        long long s = 1;
+        if (tiles < sms) s = std::min<long long>({(sms + tiles - 1) / tiles, std::max<long long>(1, batch / 2048), 16});
+        c->seg_splits[l] = (int)s;
+        slabs = std::max<int>(slabs, (int)s);
+    }
+    POZ_TRY(ensure_grad_slabs(c, slabs));
+    int widest = 0;
+    for (int l = 1; l <= nl; ++l) widest = std::max(widest, c->sizes[l]);
+    if (!c->colsum_scratch) POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->colsum_scratch), (size_t)COLSUM_ROWS * widest * sizeof(float)));
+    c->training_pass = true;
+    c->grads_reduced = false;
+    c->diag_batch = 0;
+    c->last_batch = batch;
+    {
+        ProfScope ps(c, "step_begin", stream);
+        const double share = c->cfg.global_batch > 0 ? (double)batch / (double)c->cfg.global_batch : 1.0;
+        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, nl, share);
+        POZ_LAUNCH_CHECK();
+    }
+    float* P = static_cast<float*>(c->P);
+    float* G = static_cast<float*>(c->G);
+    const __nv_bfloat16* Pb = static_cast<const __nv_bfloat16*>(c->Pb);
+    const __nv_bfloat16* cur = x;
+    for (int l = 0; l < nl; ++l) {
+        const int K = c->sizes[l], N = c->sizes[l + 1];
+        __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(c->abuf[l]);
+        ProfScope ps(c, "tc_fwd_l" + std::to_string(l), stream);
+        POZ_TRY(tc::gemm_forward(cur, Pb + c->off[l], batch, N, K,
+                                 c->has_bias ? P + c->off[l] + (long long)K * N : nullptr, c->acts[l], dst, sms, stream));
+        cur = dst;
+    }
+    const long long gb = c->cfg.global_batch > 0 ? c->cfg.global_batch : batch;
+    const int last = nl - 1, n_out = c->sizes[nl];
+    {
+        WideLossArgs a{};
+        a.y = cur; a.target = static_cast<const __nv_bfloat16*>(target);
+        a.dz = static_cast<__nv_bfloat16*>(c->dzbuf[last]);
+        a.total = batch * n_out; a.act = c->acts[last];
+        a.inv_count = 1.0 / ((double)gb * n_out);
+        a.cost_base = c->cost_ring; a.cost_cap = c->cost_cap; a.st = c->st;
+        ProfScope ps(c, "loss", stream);
+        int blocks = (int)std::min<long long>((a.total / 8 + 255) / 256, 148 * 8);
+        wide_mse_loss_kernel<<<std::max(blocks, 1), 256, 0, stream>>>(a);
+        POZ_LAUNCH_CHECK();
+    }
+    for (int l = last; l >= 0; --l) {
+        const int K = c->sizes[l], N = c->sizes[l + 1];
+        const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(c->dzbuf[l]);
+        const __nv_bfloat16* inp = l == 0 ? x : static_cast<const __nv_bfloat16*>(c->abuf[l - 1]);
+        {
+            ProfScope ps(c, "tc_bwd_w_l" + std::to_string(l), stream);
+            POZ_TRY(tc::gemm_backward_weight(inp, dz, batch, K, N, G + c->off[l], c->p_total, c->seg_splits[l], sms, stream));
+        }
+        if (c->has_bias) {
+            ProfScope ps(c, "bias_grad", stream);
+            float* gb_row = G + c->off[l] + (long long)K * N;
+            for (int s2 = 1; s2 < c->seg_splits[l]; ++s2)
+                POZ_CUDA(cudaMemsetAsync(gb_row + (long long)s2 * c->p_total, 0, (size_t)N * sizeof(float), stream));
+            dim3 grid((unsigned)((N + 63) / 64), COLSUM_ROWS);
+            wide_colsum_partial_kernel<<<grid, 256, 0, stream>>>(dz, batch, N, c->colsum_scratch);
+            POZ_LAUNCH_CHECK();
+            wide_colsum_final_kernel<<<(N + 255) / 256, 256, 0, stream>>>(c->colsum_scratch, N, gb_row);
+            POZ_LAUNCH_CHECK();
+        }
+        POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
+        if (l > 0) {
+            ProfScope ps(c, "tc_bwd_x_l" + std::to_string(l), stream);
+            POZ_TRY(tc::gemm_backward_data(dz, Pb + c->off[l], batch, K, N, static_cast<const __nv_bfloat16*>(c->abuf[l - 1]),
+                                           c->acts[l - 1], static_cast<__nv_bfloat16*>(c->dzbuf[l - 1]), sms, stream));
+        }
+    }
+    c->grads_pending = true;
+    c->diag_pending = false;
+    return 0;
+}
+
 template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream_t stream) {
     if (!c->grads_pending) POZ_FAIL("poz_train_apply: no gradients pending");
     SegTable seg;
@@ -523,7 +665,8 @@ template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream
     ProfScope ps(c, "update", stream);
     update_kernel<T><<<dim3(std::max(bx, 1), c->nl), 256, 0, stream>>>(
         static_cast<T*>(c->P), static_cast<T*>(c->AM), static_cast<T*>(c->AV),
-        static_cast<const T*>(c->G), c->p_total, gdiag, seg, c->st, c->cost_ring, c->cost_cap, c->stats);
+        static_cast<const T*>(c->G), c->p_total, gdiag, seg, c->st, c->cost_ring, c->cost_cap, c->stats,
+        static_cast<__nv_bfloat16*>(c->Pb));
     POZ_LAUNCH_CHECK();
     c->grads_pending = false;
     c->diag_pending = false;
@@ -584,8 +727,14 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     if (!out) POZ_FAIL("poz_ctx_create: out is NULL");
     *out = nullptr;
     if (n_linear < 1 || n_linear > MAX_LAYERS) POZ_FAIL("poz_ctx_create: n_linear must be in [1,16]");
-    if (dtype_code != POZ_DTYPE_F32 && dtype_code != POZ_DTYPE_F64)
-        POZ_FAIL("poz_ctx_create: this build supports POZ_DTYPE_F32 and POZ_DTYPE_F64 contexts");
+    if (dtype_code != POZ_DTYPE_F32 && dtype_code != POZ_DTYPE_F64 && dtype_code != POZ_DTYPE_BF16)
+        POZ_FAIL("poz_ctx_create: unknown dtype code");
+    if (dtype_code == POZ_DTYPE_BF16) {
+        // the tcgen05 path: dense layers only (TMA needs 16-byte rows), MSE stacks
+        for (int l = 0; l <= n_linear; ++l)
+            if (sizes[l] % 8) POZ_FAIL("poz_ctx_create: POZ_DTYPE_BF16 needs every layer size to be a multiple of 8");
+        if (loss_code != POZ_LOSS_MSE) POZ_FAIL("poz_ctx_create: POZ_DTYPE_BF16 supports MSE stacks (no trailing softmax)");
+    }
     for (int l = 0; l <= n_linear; ++l)
         if (sizes[l] < 1) POZ_FAIL("poz_ctx_create: layer sizes must be positive");
     for (int l = 0; l < n_linear; ++l) {
@@ -604,6 +753,7 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     c->device = device; c->nl = n_linear; c->has_bias = has_bias ? 1 : 0;
     c->loss = loss_code; c->dtype = dtype_code;
     c->esz = dtype_code == POZ_DTYPE_F64 ? 8 : 4;
+    c->act_esz = dtype_code == POZ_DTYPE_BF16 ? 2 : c->esz;
     c->sizes.assign(sizes, sizes + n_linear + 1);
     c->acts.assign(act_codes, act_codes + n_linear);
     c->drop_z.assign(n_linear, 0); c->drop_a.assign(n_linear, 0);
@@ -623,6 +773,10 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     auto fail = [&](void) { poz_ctx_destroy(c); return 1; };
     size_t pbytes = (size_t)c->p_total * c->esz;
     if (dev_alloc(&c->P, pbytes) || dev_alloc(&c->AM, pbytes) || dev_alloc(&c->AV, pbytes)) return fail();
+    if (dtype_code == POZ_DTYPE_BF16) {
+        if (dev_alloc(&c->Pb, (size_t)c->p_total * 2)) return fail();
+        if (cudaMemset(c->Pb, 0, (size_t)c->p_total * 2) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
+    }
     if (cudaMemset(c->P, 0, pbytes) != cudaSuccess || cudaMemset(c->AM, 0, pbytes) != cudaSuccess ||
         cudaMemset(c->AV, 0, pbytes) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
     if (dev_alloc(reinterpret_cast<void**>(&c->st), sizeof(DevState))) return fail();
@@ -645,6 +799,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     cudaDeviceSynchronize();
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
+    dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
     dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
     dev_free(reinterpret_cast<void*&>(c->st));
     dev_free(reinterpret_cast<void*&>(c->cost_ring));
@@ -704,7 +859,16 @@ int poz_ctx_reserve(poz_ctx* c, long long max_batch, int for_training) {
 
 int poz_params_upload(poz_ctx* c, int layer, const double* w, const double* b) {
     POZ_TRY(check_layer(c, layer, "poz_params_upload"));
-    return POZ_DISPATCH(c, put_layer, c, c->P, layer, w, b);
+    POZ_TRY(POZ_DISPATCH(c, put_layer, c, c->P, layer, w, b));
+    if (c->dtype == POZ_DTYPE_BF16) {
+        const long long n = c->off[layer + 1] - c->off[layer];
+        int blocks = (int)std::min<long long>((n + 255) / 256, 4096);
+        convert_kernel<float, __nv_bfloat16><<<blocks, 256>>>(static_cast<const float*>(c->P) + c->off[layer],
+                                                              static_cast<__nv_bfloat16*>(c->Pb) + c->off[layer], n);
+        POZ_LAUNCH_CHECK();
+        POZ_CUDA(cudaDeviceSynchronize());
+    }
+    return 0;
 }
 int poz_params_download(poz_ctx* c, int layer, double* w, double* b) {
     POZ_TRY(check_layer(c, layer, "poz_params_download"));
@@ -739,6 +903,9 @@ int poz_forward(poz_ctx* c, const void* x_dev, long long batch, void* out_dev, v
     if (batch <= 0) return 0;
     if (!x_dev || !out_dev) POZ_FAIL("poz_forward: NULL buffer");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (c->dtype == POZ_DTYPE_BF16)
+        return forward_wide(c, static_cast<const __nv_bfloat16*>(x_dev), nullptr, batch,
+                            static_cast<__nv_bfloat16*>(out_dev), nullptr, s);
     if (c->dtype == POZ_DTYPE_F64)
         return forward_impl<double>(c, static_cast<const double*>(x_dev), nullptr, batch,
                                     static_cast<double*>(out_dev), nullptr, s);
@@ -752,6 +919,9 @@ int poz_forward_loss(poz_ctx* c, const void* x_dev, const void* target_dev, long
     if (batch <= 0) POZ_FAIL("poz_forward_loss: empty batch");
     if (!x_dev || !out_dev || !target_dev || !cost_host) POZ_FAIL("poz_forward_loss: NULL buffer");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (c->dtype == POZ_DTYPE_BF16)
+        return forward_wide(c, static_cast<const __nv_bfloat16*>(x_dev), target_dev, batch,
+                            static_cast<__nv_bfloat16*>(out_dev), cost_host, s);
     if (c->dtype == POZ_DTYPE_F64)
         return forward_impl<double>(c, static_cast<const double*>(x_dev), target_dev, batch,
                                     static_cast<double*>(out_dev), cost_host, s);
@@ -795,6 +965,9 @@ int poz_train_backward(poz_ctx* c, const void* x_dev, const void* target_dev, co
     POZ_TRY(check_layer(c, 0, "poz_train_backward"));
     if (!x_dev || !target_dev) POZ_FAIL("poz_train_step: NULL buffer");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (c->dtype == POZ_DTYPE_BF16)
+        return backward_wide(c, static_cast<const __nv_bfloat16*>(x_dev), target_dev, row_idx_dev, batch, keep_masks,
+                             diagnostics, s);
     if (c->dtype == POZ_DTYPE_F64) {
         POZ_TRY(backward_impl<double>(c, static_cast<const double*>(x_dev), target_dev, row_idx_dev, batch, keep_masks, diagnostics, s));
         return 0;

@@ -16,6 +16,9 @@ struct poz_ctx {
     std::vector<long long> off;       // flat offsets of each layer's [W; b] image
     long long p_total = 0;
 
+    size_t act_esz = 4;               // bytes per element of activations (2 in bf16 contexts)
+    void* Pb = nullptr;               // bf16 copy of the parameters (bf16 contexts)
+    float* colsum_scratch = nullptr;  // partial column sums for the bias gradient (bf16 contexts)
     void* P = nullptr;                // flat parameters
     void* AM = nullptr;               // Adam exp_avg
     void* AV = nullptr;               // Adam exp_avg_sq

@@ -1,6 +1,7 @@
 // Non-GEMM kernels of the narrow path: per-step bookkeeping, loss (+ its gradient), softmax,
 // fused gradient-reduce + L2 + Adam/SGD update, dtype conversion.
 #pragma once
+#include <cuda_bf16.h>
 #include "poz_common.cuh"
 
 namespace poz {
@@ -196,7 +197,7 @@ template <typename T>
 __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restrict__ av,
                               const T* __restrict__ g, long long slab, T* __restrict__ g_diag,
                               SegTable seg, const DevState* st, double* cost_base,
-                              long long cost_cap, double* stats) {
+                              long long cost_cap, double* stats, __nv_bfloat16* __restrict__ p_bf16) {
     const int l = blockIdx.y;
     const long long n = seg.n_elems[l];
     const long long nw = seg.w_elems[l];
@@ -233,6 +234,7 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
             wn = w - lr * gr;
         }
         p[idx] = wn;
+        if (p_bf16) p_bf16[idx] = __float2bfloat16_rn((float)wn);
         if (rec >= 0 && is_w) {
             double d = (double)wn - (double)w;
             sd += d; sd2 += d * d; sw += (double)wn; sw2 += (double)wn * (double)wn;

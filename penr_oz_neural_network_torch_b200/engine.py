@@ -14,8 +14,8 @@ import torch
 from . import _native as nat
 
 ACTIVATIONS = ("relu", "sigmoid", "tanh", "softmax")
-_TORCH_DTYPE = {"float32": torch.float32, "float64": torch.float64}
-_DTYPE_CODE = {"float32": nat.DTYPE_F32, "float64": nat.DTYPE_F64}
+_TORCH_DTYPE = {"float32": torch.float32, "float64": torch.float64, "bfloat16": torch.bfloat16}
+_DTYPE_CODE = {"float32": nat.DTYPE_F32, "float64": nat.DTYPE_F64, "bfloat16": nat.DTYPE_BF16}
 
 
 @dataclass
@@ -93,6 +93,8 @@ class DeviceMLP:
         self.has_bias = bool(has_bias)
         self.dtype_name = dtype
         self.tdtype = _TORCH_DTYPE[dtype]
+        # gradients / master parameters: float32 in bfloat16 contexts
+        self.gdtype = torch.float64 if dtype == "float64" else torch.float32
         self.n_linear = spec.n_linear
         handle = C.c_void_p()
         with torch.cuda.device(self.device):
@@ -259,13 +261,13 @@ class DeviceMLP:
         p, n, dt = C.c_void_p(), C.c_longlong(), C.c_int()
         nat.check(self.lib.poz_grad_buffer(self.ctx, C.byref(p), C.byref(n), C.byref(dt),
                                            _stream_ptr(self.device)))
-        return _wrap_device_pointer(p.value, int(n.value), self.tdtype, self.device)
+        return _wrap_device_pointer(p.value, int(n.value), self.gdtype, self.device)
 
     def grad_layer(self, layer: int, stream: "torch.cuda.Stream") -> torch.Tensor:
         """Layer ``layer``'s slice of the flat gradient, ready on ``stream`` (see poz_grad_layer)."""
         p, n = C.c_void_p(), C.c_longlong()
         nat.check(self.lib.poz_grad_layer(self.ctx, layer, C.byref(p), C.byref(n), int(stream.cuda_stream)))
-        return _wrap_device_pointer(p.value, int(n.value), self.tdtype, self.device)
+        return _wrap_device_pointer(p.value, int(n.value), self.gdtype, self.device)
 
     def costs(self, first: int, count: int) -> np.ndarray:
         out = np.empty((count,), dtype=np.float64)

@@ -334,6 +334,141 @@ def run_c3(args, world, rank, local):
                         "l2_flush": f"inputs cycle through a {n_pool * batch * 784 * 4 / 1e6:.0f} MB pool (> L2)"})
 
 
+WIDE_SIZES = [4096] * 5
+WIDE_ALGOS = ["linear", "relu"] * 4
+WIDE_PARAMS = 4 * (4096 + 1) * 4096
+WIDE_FLOPS_PER_SAMPLE = 369_098_752        # fwd + dW (4 layers) + dX (3 layers)
+
+
+def wide_kernel_flops(tag, batch):
+    if tag.startswith("tc_"):
+        return 2.0 * batch * 4096 * 4096
+    return 0.0
+
+
+def run_wide(args, world, rank, local, dp):
+    """C4 (one GPU, batch 65536) / C5 (data parallel, global batch 524288 sharded over the ranks):
+    4 x Linear(4096->4096)+relu, MSE, Adam, bf16 operands / fp32 accumulate / fp32 masters."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, HostBatchFeeder, StackSpec, launch_count
+    from penr_oz_neural_network_torch_b200.dp import DataParallelTrainer, shard_bounds
+    dev = torch.device("cuda", local)
+    global_batch = (args.batch or 524288) if dp else (args.batch or 65536) * world
+    lo, hi = shard_bounds(global_batch, rank, world) if dp else (0, global_batch // world)
+    batch = hi - lo
+    eng = DeviceMLP(WIDE_SIZES, StackSpec.from_algos(WIDE_ALGOS), True, "bfloat16", local)
+    rng = np.random.default_rng(0)                       # same parameters on every rank
+    for l in range(4):
+        eng.upload_params(l, rng.standard_normal((4096, 4096)) * np.sqrt(2.0 / 4096), np.zeros(4096))
+    g = torch.Generator(device=dev).manual_seed(7 + rank)
+    x = torch.randn((batch, 4096), generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
+    t = torch.randn((batch, 4096), generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
+    total = args.warmup + args.steps
+    hp = dict(optimizer="adam", learning_rate=1e-4, decay_rate=0.999, l2_lambda=0.001, epochs=total + 4)
+    if dp and world > 1:
+        tr = DataParallelTrainer(eng)
+        tr.train_begin(global_batch=global_batch, **hp)
+        step = lambda: tr.train_step(x, t)
+    else:
+        eng.train_begin(**hp)
+        step = lambda: eng.train_step(x, t)
+    for _ in range(args.warmup):
+        step()
+    barrier_sync(world)
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    l0 = launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier_sync(world)
+    launches = launch_count() - l0
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    costs = eng.costs(args.warmup, args.steps)
+    assert np.isfinite(costs).all(), "non-finite training cost"
+    clocks = sampler.stop() if sampler else None
+    samples = global_batch * args.steps
+    # ---- e2e (single GPU only: host batch in, cost out, every step) ----
+    e2e = None
+    if world == 1:
+        hx, ht = x.cpu().pin_memory(), t.cpu().pin_memory()
+        n_e2e = max(3, min(args.steps, 10))
+        eng.train_begin(**dict(hp, epochs=n_e2e + 8))
+        feeder = HostBatchFeeder(eng, batch)
+        feeder.stage(hx, ht)
+        for i in range(2):
+            feeder.step(i); feeder.stage(hx, ht); feeder.cost(i)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(n_e2e):
+            feeder.step(2 + i); feeder.stage(hx, ht); last = feeder.cost(2 + i)
+        torch.cuda.synchronize()
+        el = time.perf_counter() - t0
+        e2e = {"value": batch * n_e2e / el, "unit": "samples/s", "h2d_bytes_per_step": feeder.h2d_bytes,
+               "d2h_bytes_per_step": feeder.d2h_bytes, "ms_per_step": el / n_e2e * 1e3}
+        del feeder, hx, ht
+    roof = None
+    if rank == 0:
+        pk = peaks()
+        if not (dp and world > 1):
+            eng.train_begin(**dict(hp, epochs=16))
+            eng.train_step(x, t)
+            eng.profile_begin()
+            for _ in range(3):
+                eng.train_step(x, t)
+            prof = eng.profile_end()
+            tot = sum(v["ms"] for v in prof.values())
+            top = max(prof, key=lambda k: prof[k]["ms"])
+            per = prof[top]["ms"] / prof[top]["launches"] * 1e-3
+            tf = wide_kernel_flops(top, batch) / per / 1e12
+            kern = {k: round(v["ms"] / v["launches"], 4) for k, v in prof.items()}
+        else:
+            top, tf, per, tot, prof, kern = "whole step", 0.0, 0.0, 1.0, {}, {}
+        step_tf = WIDE_FLOPS_PER_SAMPLE * batch / (ms / args.steps * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": top, "achieved": round(tf, 1), "peak": pk["bf16_tflops_sustained"],
+                "unit": "TFLOP/s", "frac": round(tf / pk["bf16_tflops_sustained"], 4), "traffic": None,
+                "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",
+                "frac_of_burst_peak": round(tf / pk["bf16_tflops"], 4),
+                "share_of_step": round(prof[top]["ms"] / tot, 3) if prof else None,
+                "step": {"tflops_per_gpu": round(step_tf, 1),
+                         "frac_of_sustained": round(step_tf / pk["bf16_tflops_sustained"], 4),
+                         "frac_of_burst": round(step_tf / pk["bf16_tflops"], 4)},
+                "kernels_ms": kern}
+    eng.close()
+    name = "c5" if dp else "c4"
+    return dict(metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=samples / (ms * 1e-3),
+                ms_per_step=ms / args.steps, e2e=e2e, gpu_launches=int(launches), roofline=roof, clocks=clocks,
+                dtype="bf16", scaling="strong" if dp else "weak",
+                config={"workload": f"{name}: MLP 4096x4 hidden (4 x Linear 4096->4096 + relu), MSE, Adam, bf16 "
+                                    f"operands / fp32 accumulate / fp32 master weights, train step",
+                        "batch_per_gpu": batch, "global_batch": global_batch,
+                        "parallelism": (f"dp{world} (NCCL all-reduce per layer, overlapped)" if dp else
+                                        (f"replicas x{world}" if world > 1 else "single")),
+                        "dropout": 0.0, "l2_flush": "one batch of inputs is 537 MB per GPU (> 126 MB L2)"})
+
+
+def cpu_train_wide(seconds, batch=1024, threads=None):
+    from oracle.torch_cpu_port import TorchCpuMLP
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    rng = np.random.default_rng(0)
+    params = []
+    for l in range(4):
+        params += [rng.standard_normal((4096, 4096)) * np.sqrt(2.0 / 4096), np.zeros(4096)]
+    m = TorchCpuMLP(WIDE_ALGOS, params, "adam")
+    x = torch.randn((batch, 4096), dtype=torch.float64)
+    t = torch.randn((batch, 4096), dtype=torch.float64)
+    m.train_step(x, t, 1e-4, l2_lambda=0.001)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        m.train_step(x, t, 1e-4, l2_lambda=0.001)
+        n += 1
+        el = time.perf_counter() - t0
+        if el >= seconds:
+            break
+    return batch * n / el, n, threads, el, batch
+
+
 # ---- CPU arms -------------------------------------------------------------------------------------------
 def cpu_train_c2(seconds, max_steps=None, threads=None):
     """The reference's torch-CPU path (oracle/torch_cpu_port.py, fp64 as the reference ships) at C2
@@ -387,6 +522,16 @@ def run_reference(args, world, rank):
                     cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
                                   "sample": f"{n} forward passes of {b} rows, torch CPU fp64 (oracle/torch_cpu_port.py)"},
                     e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+    if args.workload in ("c4", "c5"):
+        v, n, thr, el, b = cpu_train_wide(10.0)
+        return dict(impl="reference", metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v,
+                    n_gpus=args.gpus, steps=n, warmup=1, ms_per_step=el / n * 1e3, higher_is_better=True,
+                    scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
+                    config={"workload": f"{args.workload}: MLP 4096x4 hidden, MSE, Adam, train step"},
+                    cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
+                                  "sample": f"{n} train steps of a REDUCED batch of {b} rows, torch CPU fp64 "
+                                            "(oracle/torch_cpu_port.py); a full 65536-row step takes minutes"},
+                    e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
     steps = max(1, min(args.steps, 2000))
     v, n, thr, el = cpu_train_c2(0, max_steps=steps)
     return dict(impl="reference", metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v,
@@ -406,7 +551,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -422,11 +567,19 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback); "
                          "use --impl reference for the CPU arm")
-    res = (run_c2 if args.workload == "c2" else run_c3)(args, world, rank, local)
+    if args.workload in ("c4", "c5"):
+        res = run_wide(args, world, rank, local, dp=args.workload == "c5")
+    else:
+        res = (run_c2 if args.workload == "c2" else run_c3)(args, world, rank, local)
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            if args.workload == "c2":
+            if args.workload in ("c4", "c5"):
+                v, n, thr, el, b = cpu_train_wide(10.0)
+                cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
+                       "sample": f"{n} train steps of a REDUCED batch of {b} rows in {el:.1f} s, torch CPU fp64; "
+                                 "a full 65536-row step takes minutes"}
+            elif args.workload == "c2":
                 v, n, thr, el = cpu_train_c2(12.0)
                 cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
                        "sample": f"{n} train steps of batch 1024 in {el:.1f} s, torch CPU fp64, the reference's "
@@ -436,7 +589,8 @@ def main():
                 cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
                        "sample": f"{n} forward passes of {b} rows in {el:.1f} s, torch CPU fp64"}
         line = dict(metric=res["metric"], value=res["value"], unit=res["unit"], n_gpus=world, steps=args.steps,
-                    warmup=args.warmup, ms_per_step=res["ms_per_step"], higher_is_better=True, scaling="weak",
+                    warmup=args.warmup, ms_per_step=res["ms_per_step"], higher_is_better=True,
+                    scaling=res.get("scaling", "weak"),
                     vs_baseline=None, dtype=res["dtype"], data="synthetic", config=res["config"], e2e=res["e2e"],
                     gpu_launches=res["gpu_launches"], clocks=res["clocks"], roofline=res["roofline"],
                     cpu_baseline=cpu, impl="native")

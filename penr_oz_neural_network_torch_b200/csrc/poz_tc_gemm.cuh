@@ -292,6 +292,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 tmem_ld_wait();
                 const int n = nb * BN + c;
                 if (m < M && n < N) {
+                    // every register array below is indexed with compile-time constants only (fully
+                    // unrolled, predicated tails) so that it stays in registers
                     const bool full = (n + 32 <= N);
                     if (EPI == EPI_F32) {
                         float* out = static_cast<float*>(ep.out) + (long long)sp * ep.slab + m * ep.ldo + n;
@@ -300,7 +302,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             for (int j = 0; j < 32; j += 4)
                                 *reinterpret_cast<uint4*>(out + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                         } else {
-                            for (int j = 0; j < 32 && n + j < N; ++j) out[j] = __uint_as_float(v[j]);
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (n + j < N) out[j] = __uint_as_float(v[j]);
                         }
                     } else {
                         float f[32];
@@ -308,11 +312,26 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
                         __nv_bfloat16* out = static_cast<__nv_bfloat16*>(ep.out) + m * ep.ldo + n;
                         if (EPI == EPI_BIAS_ACT_BF16) {
+                            if (ep.bias) {
+                                const float* bp = ep.bias + n;
+                                if (full && ((reinterpret_cast<uintptr_t>(bp) & 15) == 0)) {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) {
-                                float z = f[j];
-                                if (ep.bias && n + j < N) z += __ldg(ep.bias + n + j);
-                                f[j] = act_fwd<float>(ep.act, z);
+                                    for (int j = 0; j < 32; j += 4) {
+                                        const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp + j));
+                                        f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+                                    }
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < 32; ++j)
+                                        if (n + j < N) f[j] += __ldg(bp + j);
+                                }
+                            }
+                            if (ep.act == ACT_RELU) {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+                            } else if (ep.act != ACT_NONE) {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) f[j] = act_fwd<float>(ep.act, f[j]);
                             }
                         } else {   // EPI_ACTGRAD_BF16: gradient through the previous unit's activation
                             const __nv_bfloat16* aux = ep.aux + m * ep.ldo + n;
@@ -329,8 +348,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                     }
                                 }
                             } else {
-                                for (int j = 0; j < 32 && n + j < N; ++j)
-                                    f[j] *= act_bwd_from_out<float>(ep.act, __bfloat162float(aux[j]));
+#pragma unroll
+                                for (int j = 0; j < 32; ++j)
+                                    if (n + j < N) f[j] *= act_bwd_from_out<float>(ep.act, __bfloat162float(aux[j]));
                             }
                         }
                         if (full && ((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
@@ -340,7 +360,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                     make_uint4(pack_bf16(f[j], f[j + 1]), pack_bf16(f[j + 2], f[j + 3]),
                                                pack_bf16(f[j + 4], f[j + 5]), pack_bf16(f[j + 6], f[j + 7]));
                         } else {
-                            for (int j = 0; j < 32 && n + j < N; ++j) out[j] = __float2bfloat16_rn(f[j]);
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (n + j < N) out[j] = __float2bfloat16_rn(f[j]);
                         }
                     }
                 }

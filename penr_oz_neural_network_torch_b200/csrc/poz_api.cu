@@ -3,6 +3,7 @@
 #include "poz_ctx.h"
 #include "poz_kernels.cuh"
 #include "poz_simt_gemm.cuh"
+#include "poz_simt_fast.cuh"
 #include "poz_tc.h"
 #include "poz_wide_kernels.cuh"
 
@@ -10,6 +11,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstring>
+#include <type_traits>
 #include <vector>
 
 namespace poz {
@@ -248,6 +250,53 @@ static int ensure_grad_slabs(poz_ctx* c, int slabs) {
     return 0;
 }
 
+
+// ---- pipelined fp32 kernels (poz_simt_fast.cuh): launch helpers -------------------------------------
+static fast::Op make_fast_op(const float* ptr, long long ld, const int* row_idx, long long rows, int cols) {
+    fast::Op o;
+    o.ptr = ptr; o.ld = ld; o.row_idx = row_idx; o.rows = rows; o.cols = cols;
+    o.vec4 = ((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld % 4) == 0 && (cols % 4) == 0) ? 1 : 0;
+    return o;
+}
+
+template <int BM, int BN, bool A_KC, bool B_KC, bool COLSUM, class Epi>
+static int launch_fast(const fast::Op& A, const fast::Op& B, long long M, int N, long long Kd, int splits,
+                       bool cluster, long long bias_row, const Epi& epi, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return 0;
+    long long k_chunk = (Kd + splits - 1) / splits;
+    k_chunk = ((k_chunk + fast::BK - 1) / fast::BK) * fast::BK;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)((N + BN - 1) / BN), (unsigned)((M + BM - 1) / BM), (unsigned)splits);
+    if (cfg.gridDim.y > 65535) POZ_FAIL("gemm: too many row tiles for one launch");
+    cfg.blockDim = dim3((BM / fast::TM) * (BN / fast::TN));
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (cluster && splits > 1) {
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)splits;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+    }
+    POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_f32_pipelined<BM, BN, A_KC, B_KC, COLSUM, Epi>, A, B, M, N, Kd,
+                                k_chunk, bias_row, epi));
+    count_launch();
+    return 0;
+}
+
+// cluster split-K factor for the forward / backward-x GEMMs: enough CTAs for ~4 per SM, each with
+// at least two k-tiles; a power of two that divides the 32-row tile.
+static int pick_cluster_split(const poz_ctx* c, long long tiles, long long Kd) {
+    const long long sms = num_sms(c->device);
+    const long long nk = (Kd + fast::BK - 1) / fast::BK;
+    int s = 1;
+    while (s < 8 && tiles * s * 2 <= 4 * sms && nk / (s * 2) >= 2) s *= 2;
+    return s;
+}
+
+static bool fast_large(const poz_ctx* c, long long M, int N) {
+    return ((M + 31) / 32) * ((N + 63) / 64) >= 8LL * num_sms(c->device);
+}
+
 // ---- forward of one layer ------------------------------------------------------------------------
 template <typename T>
 static int layer_forward(poz_ctx* c, int l, const T* x, const int* row_idx, long long x_rows,
@@ -256,6 +305,23 @@ static int layer_forward(poz_ctx* c, int l, const T* x, const int* row_idx, long
     const int K = c->sizes[l], N = c->sizes[l + 1];
     const int hb = c->has_bias;
     (void)x_rows;
+    if constexpr (std::is_same<T, float>::value) {
+        const float* w = static_cast<const float*>(c->P) + c->off[l];
+        fast::Op A = make_fast_op(x, K, row_idx, M, K);
+        fast::Op B = make_fast_op(w, N, nullptr, K, N);
+        fast::FwdBiasEpi epi;
+        epi.bias = hb ? w + (long long)K * N : nullptr;
+        epi.inner.z_out = z_out; epi.inner.a_out = a_out; epi.inner.ld = N; epi.inner.act = c->acts[l];
+        epi.inner.dz = make_drop(c, l, 0, masks);
+        epi.inner.da = make_drop(c, l, 1, masks);
+        epi.inner.st = c->st;
+        ProfScope ps(c, "fwd_l" + std::to_string(l), stream);
+        if (fast_large(c, M, N))
+            return launch_fast<64, 64, true, false, false>(A, B, M, N, K, 1, false, 0, epi, stream);
+        const long long tiles = ((M + 31) / 32) * ((N + 63) / 64);
+        const int split = pick_cluster_split(c, tiles, K);
+        return launch_fast<32, 64, true, false, false>(A, B, M, N, K, split, true, 0, epi, stream);
+    }
     Operand<T> A = make_operand<T>(x, K, row_idx, M, K, hb);
     const T* w = static_cast<const T*>(c->P) + c->off[l];
     Operand<T> B = make_operand<T>(w, N, nullptr, K + hb, N, 0);
@@ -464,7 +530,17 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     for (int l = last; l >= 0; --l) {
         const int K = c->sizes[l], N = c->sizes[l + 1], hb = c->has_bias;
         const T* dz = static_cast<const T*>(c->dzbuf[l]);
-        {
+        if constexpr (std::is_same<T, float>::value) {
+            const float* inp = l == 0 ? x : static_cast<const float*>(c->abuf[l - 1]);
+            fast::Op A = make_fast_op(inp, K, l == 0 ? row_idx : nullptr, batch, K);
+            fast::Op B = make_fast_op(dz, N, nullptr, batch, N);
+            BwdWeightEpi<float> epi;
+            epi.g = static_cast<float*>(c->G); epi.slab = c->p_total; epi.off = c->off[l]; epi.ld = N;
+            ProfScope ps(c, "bwd_w_l" + std::to_string(l), stream);
+            if (hb) POZ_TRY((launch_fast<32, 64, false, false, true>(A, B, K, N, batch, seg.splits[l], false, K, epi, stream)));
+            else    POZ_TRY((launch_fast<32, 64, false, false, false>(A, B, K, N, batch, seg.splits[l], false, K, epi, stream)));
+            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
+        } else {
             const T* inp = l == 0 ? x : static_cast<const T*>(c->abuf[l - 1]);
             Operand<T> A = make_operand<T>(inp, K, l == 0 ? row_idx : nullptr, batch, K, hb);
             Operand<T> B = make_operand<T>(dz, N, nullptr, batch, N, 0);
@@ -498,6 +574,13 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
                 }
             }
             ProfScope ps(c, "bwd_x_l" + std::to_string(l), stream);
+            if constexpr (std::is_same<T, float>::value) {
+                fast::Op FA = make_fast_op(dz, N, nullptr, batch, N);
+                fast::Op FB = make_fast_op(w, N, nullptr, K, N);
+                const long long tiles = ((batch + 31) / 32) * ((K + 63) / 64);
+                const int split = pick_cluster_split(c, tiles, N);
+                POZ_TRY((launch_fast<32, 64, true, true, false>(FA, FB, batch, K, N, split, true, 0, epi, stream)));
+            } else
             POZ_TRY((launch_gemm<T, true, true>(pick_tile<T>(c, batch, K), A, B, batch, K, (long long)N, 1,
                                                 (long long)N, epi, stream)));
         }

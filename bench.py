@@ -113,6 +113,8 @@ def dist_setup(args):
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"       # keep stdout to the one JSON line
         if args.impl == "reference":
             return world, rank, local      # rank 0 alone works; no process group needed
         torch.cuda.set_device(local)

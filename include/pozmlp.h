@@ -152,6 +152,15 @@ int poz_train_apply(poz_ctx* ctx, void* stream);
 int poz_tc_gemm(int device, int variant, const void* a, const void* b, long long m, int n, long long k,
                 void* out, const float* bias, const void* aux, int act, int splits, void* stream);
 
+/* Split-bf16 variant of the same building block: float32 device matrices in and out; each operand
+ * is carried as three bf16 planes (hi + mid + lo) and the six significant plane products are
+ * accumulated in tensor memory, giving float32-grade results at tensor-core rate (used by float32
+ * contexts for layers wide enough to tile).  Same variants as poz_tc_gemm; out is float32
+ * ([splits][m][n] for variant 2); aux (variant 1, may be NULL) holds activation outputs as float32.
+ * Allocates temporary plane buffers: a test / benchmark entry, not a hot-path one. */
+int poz_tc3_gemm(int device, int variant, const float* a, const float* b, long long m, int n, long long k,
+                 float* out, const float* bias, const float* aux, int act, int splits, void* stream);
+
 /* ---- inference without any allocation ---------------------------------------------------------
  * No counterpart in the reference (it has no notion of device memory at all).
  *

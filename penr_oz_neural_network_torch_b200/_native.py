@@ -22,7 +22,7 @@ OPT_SGD, OPT_ADAM = 0, 1
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
-SOURCES = ["poz_api.cu", "poz_noalloc.cu", "poz_tc.cu"]
+SOURCES = ["poz_api.cu", "poz_noalloc.cu", "poz_tc.cu", "poz_tc3.cu"]
 
 
 class PozError(RuntimeError):
@@ -111,6 +111,7 @@ SIGNATURES = {
     "poz_train_backward": (_I, [_VP, _VP, _VP, _VP, _LL, C.POINTER(_VP), _I, _VP]),
     "poz_train_apply": (_I, [_VP, _VP]),
     "poz_tc_gemm": (_I, [_I, _I, _VP, _VP, _LL, _I, _LL, _VP, _VP, _VP, _I, _I, _VP]),
+    "poz_tc3_gemm": (_I, [_I, _I, _VP, _VP, _LL, _I, _LL, _VP, _VP, _VP, _I, _I, _VP]),
     "poz_forward_noalloc": (_I, [_I, _I, C.POINTER(_I), C.POINTER(_I), C.POINTER(_VP), C.POINTER(_VP),
                                 _VP, _LL, _VP, _VP]),
 }

@@ -1,0 +1,139 @@
+// Host side of the split-bf16 tcgen05 GEMM: 3-D tensor maps over plane stacks, launchers, and the
+// fp32-in / fp32-out building-block entry point poz_tc3_gemm.
+#include "../../include/pozmlp.h"
+#include "poz_tc3.h"
+#include "poz_tc3_kernel.cuh"
+
+#include <mutex>
+
+namespace poz {
+namespace tc3 {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+static int make_map3(CUtensorMap* map, const PlaneMat& m, int box_cols, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) POZ_FAIL("tcgen05 path: cuTensorMapEncodeTiled is not available from the driver");
+    if ((reinterpret_cast<uintptr_t>(m.ptr) & 15) != 0 || (m.ld * 2) % 16 != 0 || (m.plane_stride * 2) % 16 != 0)
+        POZ_FAIL("tcgen05 path: plane base, row pitch and plane stride must be 16-byte aligned");
+    cuuint64_t gdim[3] = {(cuuint64_t)m.cols, (cuuint64_t)m.rows, 3};
+    cuuint64_t gstride[2] = {(cuuint64_t)m.ld * 2, (cuuint64_t)m.plane_stride * 2};
+    cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<__nv_bfloat16*>(m.ptr), gdim, gstride, box,
+                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) POZ_FAIL("tcgen05 path: cuTensorMapEncodeTiled (3-D) failed with code " + std::to_string((int)r));
+    return 0;
+}
+
+template <int A_MAJOR, int B_MAJOR, int BN>
+static int launch(const PlaneMat& a, const PlaneMat& b, long long M, int N, long long K, int splits, const Epi3& ep,
+                  int sms, cudaStream_t stream) {
+    using C = Cfg<BN>;
+    static bool configured = false;
+    auto kern = tc3_gemm_kernel<A_MAJOR, B_MAJOR, BN>;
+    if (!configured) {
+        POZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        configured = true;
+    }
+    CUtensorMap ma, mb;
+    POZ_TRY(make_map3(&ma, a, 64, A_MAJOR == MAJOR_K ? BM : 64));
+    POZ_TRY(make_map3(&mb, b, 64, B_MAJOR == MAJOR_K ? BN : 64));
+    long long k_per = (K + splits - 1) / splits;
+    k_per = ((k_per + BK - 1) / BK) * BK;
+    const long long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * splits;
+    const int grid = (int)(tiles < sms ? tiles : sms);
+    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, M, N, K, splits, k_per, ep);
+    count_launch();
+    POZ_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int A_MAJOR, int B_MAJOR>
+static int launch_bn(const PlaneMat& a, const PlaneMat& b, long long M, int N, long long K, int splits,
+                     const Epi3& ep, int sms, cudaStream_t stream) {
+    const long long tiles128 = ((M + BM - 1) / BM) * ((N + 127) / 128) * splits;
+    if (N <= 64 || tiles128 * 2 < sms) return launch<A_MAJOR, B_MAJOR, 64>(a, b, M, N, K, splits, ep, sms, stream);
+    return launch<A_MAJOR, B_MAJOR, 128>(a, b, M, N, K, splits, ep, sms, stream);
+}
+
+int split_planes(const float* src, long long rows, int cols, long long ld, __nv_bfloat16* dst, long long ldp,
+                 long long plane_stride, cudaStream_t stream) {
+    if (rows <= 0) return 0;
+    const long long total = rows * ldp;
+    int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    split_planes_kernel<<<blocks, 256, 0, stream>>>(src, rows, cols, ld, dst, ldp, plane_stride);
+    count_launch();
+    POZ_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms, cudaStream_t s) {
+    return launch_bn<MAJOR_K, MAJOR_MN>(x, w, M, N, K, 1, ep, sms, s);
+}
+int gemm_backward_data(const PlaneMat& dz, const PlaneMat& w, long long M, int K_in, int N_out, const Epi3& ep, int sms,
+                       cudaStream_t s) {
+    return launch_bn<MAJOR_K, MAJOR_K>(dz, w, M, K_in, N_out, 1, ep, sms, s);
+}
+int gemm_backward_weight(const PlaneMat& x, const PlaneMat& dz, long long batch, int K_in, int N_out, int splits,
+                         const Epi3& ep, int sms, cudaStream_t s) {
+    return launch_bn<MAJOR_MN, MAJOR_MN>(x, dz, K_in, N_out, batch, splits, ep, sms, s);
+}
+
+}  // namespace tc3
+}  // namespace poz
+
+// fp32 matrices in, fp32 out: splits both operands into temporary plane stacks (allocated and freed
+// here -- this is a test / benchmark building block, not the context path).
+extern "C" int poz_tc3_gemm(int device, int variant, const float* a, const float* b, long long m, int n, long long k,
+                            float* out, const float* bias, const float* aux, int act, int splits, void* stream) {
+    using namespace poz;
+    using namespace poz::tc3;
+    if (!a || !b || !out) POZ_FAIL("poz_tc3_gemm: NULL operand");
+    if (m <= 0 || n <= 0 || k <= 0) POZ_FAIL("poz_tc3_gemm: empty problem");
+    if (variant < 0 || variant > 2) POZ_FAIL("poz_tc3_gemm: unknown variant");
+    if (variant == 2 && (splits < 1 || splits > 64)) POZ_FAIL("poz_tc3_gemm: splits must be in [1,64]");
+    POZ_CUDA(cudaSetDevice(device));
+    int sms = 148;
+    POZ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // global shapes of the two operands
+    long long a_rows, b_rows; int a_cols, b_cols;
+    if (variant == 0) { a_rows = m; a_cols = (int)k; b_rows = k; b_cols = n; }          // a[m][k], b[k][n]
+    else if (variant == 1) { a_rows = m; a_cols = (int)k; b_rows = n; b_cols = (int)k; } // a[m][k], b[n][k]
+    else { a_rows = k; a_cols = (int)m; b_rows = k; b_cols = n; }                        // a[k][m], b[k][n]
+    const long long lda = (a_cols + 7) & ~7, ldb = (b_cols + 7) & ~7;
+    __nv_bfloat16 *pa = nullptr, *pb = nullptr;
+    POZ_CUDA(cudaMalloc(&pa, (size_t)3 * a_rows * lda * 2));
+    if (cudaMalloc(&pb, (size_t)3 * b_rows * ldb * 2) != cudaSuccess) { cudaFree(pa); POZ_FAIL("poz_tc3_gemm: cudaMalloc failed"); }
+    int rc = split_planes(a, a_rows, a_cols, a_cols, pa, lda, a_rows * lda, s);
+    if (!rc) rc = split_planes(b, b_rows, b_cols, b_cols, pb, ldb, b_rows * ldb, s);
+    PlaneMat A{pa, a_rows, a_cols, lda, a_rows * lda}, B{pb, b_rows, b_cols, ldb, b_rows * ldb};
+    Epi3 ep{};
+    ep.out_f32 = out; ep.ld_f32 = n; ep.slab = m * (long long)n; ep.bias = bias; ep.aux = aux; ep.ld_aux = n; ep.act = act;
+    if (!rc) {
+        if (variant == 0) { ep.mode = EPI_BIAS_ACT; rc = gemm_forward(A, B, m, n, (int)k, ep, sms, s); }
+        else if (variant == 1) { ep.mode = aux ? EPI_ACTGRAD : EPI_PLAIN; rc = gemm_backward_data(A, B, m, n, (int)k, ep, sms, s); }
+        else { ep.mode = EPI_PLAIN; rc = gemm_backward_weight(A, B, k, (int)m, n, splits, ep, sms, s); }
+    }
+    cudaStreamSynchronize(s);
+    cudaFree(pa);
+    cudaFree(pb);
+    return rc;
+}

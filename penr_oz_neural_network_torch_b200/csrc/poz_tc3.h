@@ -1,0 +1,44 @@
+// Interface of the split-bf16 tcgen05 GEMM (csrc/poz_tc3.cu): plane stacks, epilogue description,
+// launchers.  Host-only header (no device code) so that poz_api.cu can include it.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+namespace poz {
+namespace tc3 {
+
+// An fp32 matrix carried as three bf16 planes: [3][rows][ld], plane p at ptr + p * plane_stride.
+struct PlaneMat {
+    const __nv_bfloat16* ptr;
+    long long rows;
+    int cols;
+    long long ld;            // elements, multiple of 8
+    long long plane_stride;  // elements, multiple of 8
+};
+
+enum EpiMode { EPI_BIAS_ACT = 0, EPI_ACTGRAD = 1, EPI_PLAIN = 2 };
+
+struct Epi3 {
+    float* out_f32;               // nullable; [M][ld_f32] (+ split * slab)
+    long long ld_f32, slab;
+    __nv_bfloat16* out_planes;    // nullable; [3][rows][ld_planes]
+    long long ld_planes, plane_stride;
+    const float* bias;            // EPI_BIAS_ACT: [N] or null
+    const float* aux;             // EPI_ACTGRAD: recorded activation of the previous unit [M][ld_aux]
+    long long ld_aux;
+    int mode, act;
+};
+
+int split_planes(const float* src, long long rows, int cols, long long ld, __nv_bfloat16* dst, long long ldp,
+                 long long plane_stride, cudaStream_t stream);
+// out[M][N] = epilogue(x[M][K] * w[K][N])
+int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms, cudaStream_t s);
+// out[M][K_in] = epilogue(dz[M][N_out] * w[K_in][N_out]^T)
+int gemm_backward_data(const PlaneMat& dz, const PlaneMat& w, long long M, int K_in, int N_out, const Epi3& ep, int sms,
+                       cudaStream_t s);
+// out[split][K_in][N_out] = partial sums over the batch of x[batch][K_in]^T * dz[batch][N_out]
+int gemm_backward_weight(const PlaneMat& x, const PlaneMat& dz, long long batch, int K_in, int N_out, int splits,
+                         const Epi3& ep, int sms, cudaStream_t s);
+
+}  // namespace tc3
+}  // namespace poz

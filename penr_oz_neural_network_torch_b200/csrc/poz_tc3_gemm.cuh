@@ -1,0 +1,84 @@
+// Split-bf16 ("bf16x3") tcgen05 GEMM: fp32-grade matrix products on the 5th-gen tensor cores.
+//
+// Every fp32 operand x is carried as three bf16 planes hi + mid + lo (x = hi + mid + lo to ~2^-24),
+// and C = A*B is accumulated in tensor memory from the six plane products that matter
+//   hi*hi, hi*mid, mid*hi, mid*mid, hi*lo, lo*hi          (dropped terms are <= 2^-24 relative),
+// which keeps the float32 contract of the narrow configurations (rtol 1e-5 vs the float64
+// reference) while the contraction runs at tensor-core rate instead of on the fp32 FMA pipe.
+//
+// The tensor core truncates its fp32 accumulator on every tcgen05.mma, an error proportional to the
+// accumulator's magnitude and to the number of accumulation steps, so the five small products go to
+// an accumulator of their own (2^-8 of the magnitude) and only hi*hi (K/16 steps) feeds the main
+// one; the epilogue adds the two.  Measured: error/max|C| ~1.5e-6 at K = 784 instead of 5e-6.
+//
+// Tile: 128 x BN output, BK = 64, one stage = 3 A planes + 3 B planes; accumulator pairs
+// double-buffered in TMEM (2 x 2 x BN columns) so the epilogue of tile i overlaps the MMAs of
+// tile i+1.
+//   warps 0-7 : epilogue (TMEM lane quarter w%4, column half w/4)
+//   warp  8   : TMA producer       warp 9 : TMEM allocator + MMA issuer
+// Planes are stored [3][rows][pitch] and addressed through one 3-D tensor map per operand.
+#pragma once
+#include "poz_tc_gemm.cuh"
+#include "poz_tc3.h"
+
+namespace poz {
+namespace tc3 {
+
+using tc::MAJOR_K;
+using tc::MAJOR_MN;
+
+constexpr int BM = 128, BK = 64, UMMA_K = 16, PLANES = 3;
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int NUM_THREADS = (NUM_EPI_WARPS + 2) * 32;
+
+template <int BN> struct Cfg {
+    static constexpr int STAGES = BN <= 64 ? 3 : 2;
+    static constexpr int A_PLANE = BM * BK * 2;
+    static constexpr int B_PLANE = BN * BK * 2;
+    static constexpr int STAGE_BYTES = PLANES * (A_PLANE + B_PLANE);
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    // two accumulators per buffer (hi*hi, and the five small terms), two buffers
+    static constexpr int TMEM_COLS = 4 * BN;                        // 256 or 512: powers of two
+};
+
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(tc::smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1),
+        "r"(c2)
+        : "memory");
+}
+
+template <int A_MAJOR, int B_MAJOR, int BN> __device__ __forceinline__ constexpr uint32_t make_idesc3() {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)A_MAJOR << 15) | ((uint32_t)B_MAJOR << 16) |
+           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+// x -> (hi, mid, lo) bf16 with x ~= hi + mid + lo
+__device__ __forceinline__ void split3(float x, __nv_bfloat16& h, __nv_bfloat16& m, __nv_bfloat16& l) {
+    h = __float2bfloat16_rn(x);
+    const float r1 = x - __bfloat162float(h);
+    m = __float2bfloat16_rn(r1);
+    const float r2 = r1 - __bfloat162float(m);
+    l = __float2bfloat16_rn(r2);
+}
+
+// fp32 matrix [rows][cols] (pitch ld) -> planes [3][rows][ldp]; pad columns cols..ldp-1 are zeroed.
+__global__ void split_planes_kernel(const float* __restrict__ src, long long rows, int cols, long long ld,
+                                    __nv_bfloat16* __restrict__ dst, long long ldp, long long plane_stride) {
+    const long long total = rows * ldp;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / ldp;
+        const int c = (int)(i - r * ldp);
+        const float x = c < cols ? src[r * ld + c] : 0.f;
+        __nv_bfloat16 h, m, l;
+        split3(x, h, m, l);
+        dst[i] = h;
+        dst[plane_stride + i] = m;
+        dst[2 * plane_stride + i] = l;
+    }
+}
+
+}  // namespace tc3
+}  // namespace poz

@@ -5,11 +5,13 @@
 #include "poz_simt_gemm.cuh"
 #include "poz_simt_fast.cuh"
 #include "poz_tc.h"
+#include "poz_tc3.h"
 #include "poz_wide_kernels.cuh"
 
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <type_traits>
 #include <vector>
@@ -337,6 +339,12 @@ static int layer_forward(poz_ctx* c, int l, const T* x, const int* row_idx, long
 
 template <typename T> static int run_softmax(poz_ctx* c, const T* z, T* out, long long M, int N, cudaStream_t s) {
     ProfScope ps(c, "softmax", s);
+    if (N <= 32) {
+        long long b = (M + 255) / 256;
+        softmax_small_kernel<T><<<(unsigned)std::max<long long>(b, 1), 256, 0, s>>>(z, out, M, N);
+        POZ_LAUNCH_CHECK();
+        return 0;
+    }
     int blocks = (int)std::min<long long>((M + 7) / 8, 148 * 8);
     softmax_kernel<T><<<std::max(blocks, 1), 256, 0, s>>>(z, out, M, N);
     POZ_LAUNCH_CHECK();
@@ -358,6 +366,138 @@ static int run_loss(poz_ctx* c, LossArgs<T>& a, cudaStream_t s) {
     return 0;
 }
 
+// ---- float32 contexts on the tensor cores (split-bf16, csrc/poz_tc3.*) ------------------------------
+static long long round8(long long v) { return (v + 7) & ~7LL; }
+
+// every layer deep enough (K >= 64) for a 64-wide k-block to be mostly real data
+static bool tc3_stack_ok(const poz_ctx* c) {
+    if (c->dtype != POZ_DTYPE_F32) return false;
+    for (int l = 0; l < c->nl; ++l)
+        if (c->sizes[l] < 64) return false;
+    return true;
+}
+
+static int tc3_refresh_weights(poz_ctx* c, cudaStream_t stream) {
+    if (!c->Wp) {
+        c->wp_off.assign(c->nl + 1, 0);
+        c->wp_ld.assign(c->nl, 0);
+        for (int l = 0; l < c->nl; ++l) {
+            c->wp_ld[l] = round8(c->sizes[l + 1]);
+            c->wp_off[l + 1] = c->wp_off[l] + 3LL * c->sizes[l] * c->wp_ld[l];
+        }
+        c->wp_total = c->wp_off[c->nl];
+        POZ_TRY(dev_alloc(&c->Wp, (size_t)c->wp_total * 2));
+        c->wp_stale = true;
+    }
+    if (!c->wp_stale) return 0;
+    for (int l = 0; l < c->nl; ++l) {
+        const int K = c->sizes[l], N = c->sizes[l + 1];
+        ProfScope ps(c, "split_w", stream);
+        POZ_TRY(tc3::split_planes(static_cast<const float*>(c->P) + c->off[l], nullptr, K, N, N,
+                                  static_cast<__nv_bfloat16*>(c->Wp) + c->wp_off[l], c->wp_ld[l],
+                                  (long long)K * c->wp_ld[l], stream));
+    }
+    c->wp_stale = false;
+    return 0;
+}
+
+static tc3::PlaneMat tc3_weight(const poz_ctx* c, int l) {
+    tc3::PlaneMat m;
+    m.ptr = static_cast<const __nv_bfloat16*>(c->Wp) + c->wp_off[l];
+    m.rows = c->sizes[l]; m.cols = c->sizes[l + 1]; m.ld = c->wp_ld[l];
+    m.plane_stride = (long long)c->sizes[l] * c->wp_ld[l];
+    return m;
+}
+
+// Inference with every Linear layer on tcgen05: the input chunk is split into bf16 planes once,
+// each layer's epilogue writes the next layer's planes directly, and a chunk (8192 rows) of planes
+// is small enough to stay in L2 between the layer kernels.
+static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long batch, float* out,
+                       double* cost_host, cudaStream_t stream) {
+    const int nl = c->nl, sms = num_sms(c->device);
+    POZ_TRY(tc3_refresh_weights(c, stream));
+    long long widest = 0;
+    for (int l = 0; l <= nl; ++l) widest = std::max<long long>(widest, round8(c->sizes[l]));
+    // chunk: input planes + the widest hidden planes of a chunk should fit in ~100 MB of L2, and the
+    // first (dominant) layer's 128x128 tiles of a chunk should fill whole waves of the SMs
+    long long chunk = (100LL << 20) / (6 * (round8(c->sizes[0]) + widest));
+    {
+        const long long tiles_n0 = (c->sizes[1] + 127) / 128;
+        const long long rows_per_wave = std::max<long long>(1, sms / tiles_n0) * 128;
+        chunk = std::max<long long>(1, chunk / rows_per_wave) * rows_per_wave;
+    }
+    chunk = std::min<long long>(batch, chunk);
+    if (chunk > c->tc_chunk) {
+        for (auto& p : c->tc_scr) dev_free(p);
+        dev_free(reinterpret_cast<void*&>(c->tc_logits));
+        for (auto& p : c->tc_scr) POZ_TRY(dev_alloc(&p, (size_t)3 * chunk * widest * 2));
+        POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->tc_logits), (size_t)chunk * c->sizes[nl] * sizeof(float)));
+        c->tc_chunk = chunk;
+    }
+    c->training_pass = false;
+    if (cost_host) POZ_CUDA(cudaMemsetAsync(c->scalar_cost, 0, sizeof(double), stream));
+    const int n_out = c->sizes[nl];
+    const bool softmax_last = c->acts[nl - 1] == ACT_SOFTMAX;
+    const float* P = static_cast<const float*>(c->P);
+    for (long long r0 = 0; r0 < batch; r0 += chunk) {
+        const long long m = std::min(chunk, batch - r0);
+        tc3::PlaneMat cur;
+        cur.ptr = static_cast<const __nv_bfloat16*>(c->tc_scr[0]);
+        cur.rows = m; cur.cols = c->sizes[0]; cur.ld = round8(c->sizes[0]); cur.plane_stride = m * cur.ld;
+        {
+            ProfScope ps(c, "split_x", stream);
+            POZ_TRY(tc3::split_planes(x + r0 * c->sizes[0], nullptr, m, c->sizes[0], c->sizes[0],
+                                      static_cast<__nv_bfloat16*>(c->tc_scr[0]), cur.ld, cur.plane_stride, stream));
+        }
+        int flip = 1;
+        float* z_last = nullptr;
+        for (int l = 0; l < nl; ++l) {
+            const int K = c->sizes[l], N = c->sizes[l + 1];
+            const bool last = l == nl - 1;
+            tc3::Epi3 ep{};
+            ep.mode = tc3::EPI_BIAS_ACT;
+            ep.act = c->acts[l];
+            ep.bias = c->has_bias ? P + c->off[l] + (long long)K * N : nullptr;
+            tc3::PlaneMat nxt{};
+            if (last) {
+                ep.out_f32 = softmax_last ? c->tc_logits : out + r0 * n_out;
+                ep.ld_f32 = N;
+                z_last = ep.out_f32;
+            } else {
+                nxt.ptr = static_cast<const __nv_bfloat16*>(c->tc_scr[flip]);
+                nxt.rows = m; nxt.cols = N; nxt.ld = round8(N); nxt.plane_stride = m * nxt.ld;
+                ep.out_planes = static_cast<__nv_bfloat16*>(c->tc_scr[flip]);
+                ep.ld_planes = nxt.ld; ep.plane_stride = nxt.plane_stride;
+            }
+            ProfScope ps(c, "tc3_fwd_l" + std::to_string(l), stream);
+            POZ_TRY(tc3::gemm_forward(cur, tc3_weight(c, l), m, N, K, ep, sms, stream));
+            cur = nxt;
+            flip = flip == 1 ? 2 : 1;
+        }
+        if (cost_host) {
+            LossArgs<float> a{};
+            a.z = z_last; a.M = m; a.N = n_out; a.act = c->acts[nl - 1];
+            a.cost_base = c->scalar_cost; a.cost_cap = 1; a.st = nullptr;
+            if (c->loss == POZ_LOSS_CE) {
+                a.target = static_cast<const int*>(target) + r0;
+                a.probs = out + r0 * n_out;
+                a.inv_count = 1.0 / (double)batch;
+            } else {
+                a.target = static_cast<const float*>(target) + r0 * n_out;
+                a.inv_count = 1.0 / ((double)batch * n_out);
+            }
+            POZ_TRY(run_loss<float>(c, a, stream));
+        } else if (softmax_last) {
+            POZ_TRY(run_softmax<float>(c, z_last, out + r0 * n_out, m, n_out, stream));
+        }
+    }
+    if (cost_host) {
+        POZ_CUDA(cudaMemcpyAsync(cost_host, c->scalar_cost, sizeof(double), cudaMemcpyDeviceToHost, stream));
+        POZ_CUDA(cudaStreamSynchronize(stream));
+    }
+    return 0;
+}
+
 // ---- inference -----------------------------------------------------------------------------------
 // Rows are processed in chunks small enough that the intermediate activations of a chunk stay in
 // the 126 MB L2 between the per-layer kernels instead of round-tripping through HBM.
@@ -365,6 +505,10 @@ template <typename T>
 static int forward_impl(poz_ctx* c, const T* x, const void* target, long long batch, T* out,
                         double* cost_host, cudaStream_t stream) {
     const int nl = c->nl;
+    if constexpr (std::is_same<T, float>::value) {
+        // big batches of a deep-enough stack: every layer on the tensor cores
+        if (batch >= c->tc3_min_batch && tc3_stack_ok(c)) return forward_tc3(c, x, target, batch, out, cost_host, stream);
+    }
     int widest = 0;
     for (int l = 1; l <= nl; ++l) widest = std::max(widest, c->sizes[l]);
     long long chunk = std::max<long long>(256, (24LL << 20) / ((long long)widest * sizeof(T)));
@@ -753,6 +897,7 @@ template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream
     POZ_LAUNCH_CHECK();
     c->grads_pending = false;
     c->diag_pending = false;
+    c->wp_stale = true;
     return 0;
 }
 
@@ -853,6 +998,7 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     c->dzbuf.assign(n_linear, nullptr); c->dz_rec.assign(n_linear, nullptr);
     c->da_rec.assign(n_linear, nullptr);
     c->max_splits = 16;
+    if (const char* e = getenv("POZ_TC3_MIN_BATCH")) c->tc3_min_batch = atoll(e);
     auto fail = [&](void) { poz_ctx_destroy(c); return 1; };
     size_t pbytes = (size_t)c->p_total * c->esz;
     if (dev_alloc(&c->P, pbytes) || dev_alloc(&c->AM, pbytes) || dev_alloc(&c->AV, pbytes)) return fail();
@@ -883,6 +1029,8 @@ int poz_ctx_destroy(poz_ctx* c) {
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
+    dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
+    dev_free(reinterpret_cast<void*&>(c->tc_logits));
     dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
     dev_free(reinterpret_cast<void*&>(c->st));
     dev_free(reinterpret_cast<void*&>(c->cost_ring));
@@ -943,6 +1091,7 @@ int poz_ctx_reserve(poz_ctx* c, long long max_batch, int for_training) {
 int poz_params_upload(poz_ctx* c, int layer, const double* w, const double* b) {
     POZ_TRY(check_layer(c, layer, "poz_params_upload"));
     POZ_TRY(POZ_DISPATCH(c, put_layer, c, c->P, layer, w, b));
+    c->wp_stale = true;
     if (c->dtype == POZ_DTYPE_BF16) {
         const long long n = c->off[layer + 1] - c->off[layer];
         int blocks = (int)std::min<long long>((n + 255) / 256, 4096);

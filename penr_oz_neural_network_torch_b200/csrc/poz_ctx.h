@@ -19,6 +19,15 @@ struct poz_ctx {
     size_t act_esz = 4;               // bytes per element of activations (2 in bf16 contexts)
     void* Pb = nullptr;               // bf16 copy of the parameters (bf16 contexts)
     float* colsum_scratch = nullptr;  // partial column sums for the bias gradient (bf16 contexts)
+    // split-bf16 tensor-core path of float32 contexts (csrc/poz_tc3.*)
+    void* Wp = nullptr;               // weight planes, layer l at wp_off[l]: [3][in_l][wp_ld[l]] bf16
+    std::vector<long long> wp_off, wp_ld;
+    long long wp_total = 0;
+    bool wp_stale = true;             // parameters changed since the planes were built
+    void* tc_scr[3] = {nullptr, nullptr, nullptr};   // plane stacks: input chunk, ping, pong
+    float* tc_logits = nullptr;       // fp32 logits of a chunk (trailing softmax)
+    long long tc_chunk = 0;
+    long long tc3_min_batch = 2048;   // smaller batches stay on the SIMT kernels (POZ_TC3_MIN_BATCH overrides)
     void* P = nullptr;                // flat parameters
     void* AM = nullptr;               // Adam exp_avg
     void* AV = nullptr;               // Adam exp_avg_sq

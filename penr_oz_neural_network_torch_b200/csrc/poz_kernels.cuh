@@ -143,6 +143,26 @@ template <typename T> __global__ void softmax_kernel(const T* z, T* out, long lo
     }
 }
 
+// the same for narrow rows (N <= 32): one thread per row, values held in registers
+template <typename T> __global__ void softmax_small_kernel(const T* __restrict__ z, T* __restrict__ out, long long M, int N) {
+    const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= M) return;
+    const T* zr = z + row * N;
+    T v[32];
+    T mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+        if (j < N) { v[j] = zr[j]; mx = v[j] > mx ? v[j] : mx; }
+    T s = T(0);
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+        if (j < N) { v[j] = exp(v[j] - mx); s += v[j]; }
+    const T inv = T(1) / s;
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+        if (j < N) out[row * N + j] = v[j] * inv;
+}
+
 // mean-squared error + gradient through the last activation (neural_net_model.py:405-406)
 template <typename T> __global__ void mse_loss_kernel(LossArgs<T> a) {
     const long long total = a.M * a.N;

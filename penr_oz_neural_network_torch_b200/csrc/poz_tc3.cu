@@ -73,12 +73,12 @@ static int launch_bn(const PlaneMat& a, const PlaneMat& b, long long M, int N, l
     return launch<A_MAJOR, B_MAJOR, 128>(a, b, M, N, K, splits, ep, sms, stream);
 }
 
-int split_planes(const float* src, long long rows, int cols, long long ld, __nv_bfloat16* dst, long long ldp,
-                 long long plane_stride, cudaStream_t stream) {
+int split_planes(const float* src, const int* row_idx, long long rows, int cols, long long ld, __nv_bfloat16* dst,
+                 long long ldp, long long plane_stride, cudaStream_t stream) {
     if (rows <= 0) return 0;
-    const long long total = rows * ldp;
+    const long long total = rows * (ldp / 8);
     int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-    split_planes_kernel<<<blocks, 256, 0, stream>>>(src, rows, cols, ld, dst, ldp, plane_stride);
+    split_planes_kernel<<<blocks, 256, 0, stream>>>(src, row_idx, rows, cols, ld, dst, ldp, plane_stride);
     count_launch();
     POZ_CUDA(cudaGetLastError());
     return 0;
@@ -122,8 +122,8 @@ extern "C" int poz_tc3_gemm(int device, int variant, const float* a, const float
     __nv_bfloat16 *pa = nullptr, *pb = nullptr;
     POZ_CUDA(cudaMalloc(&pa, (size_t)3 * a_rows * lda * 2));
     if (cudaMalloc(&pb, (size_t)3 * b_rows * ldb * 2) != cudaSuccess) { cudaFree(pa); POZ_FAIL("poz_tc3_gemm: cudaMalloc failed"); }
-    int rc = split_planes(a, a_rows, a_cols, a_cols, pa, lda, a_rows * lda, s);
-    if (!rc) rc = split_planes(b, b_rows, b_cols, b_cols, pb, ldb, b_rows * ldb, s);
+    int rc = split_planes(a, nullptr, a_rows, a_cols, a_cols, pa, lda, a_rows * lda, s);
+    if (!rc) rc = split_planes(b, nullptr, b_rows, b_cols, b_cols, pb, ldb, b_rows * ldb, s);
     PlaneMat A{pa, a_rows, a_cols, lda, a_rows * lda}, B{pb, b_rows, b_cols, ldb, b_rows * ldb};
     Epi3 ep{};
     ep.out_f32 = out; ep.ld_f32 = n; ep.slab = m * (long long)n; ep.bias = bias; ep.aux = aux; ep.ld_aux = n; ep.act = act;

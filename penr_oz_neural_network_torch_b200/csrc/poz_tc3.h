@@ -29,8 +29,9 @@ struct Epi3 {
     int mode, act;
 };
 
-int split_planes(const float* src, long long rows, int cols, long long ld, __nv_bfloat16* dst, long long ldp,
-                 long long plane_stride, cudaStream_t stream);
+// row_idx (nullable) gathers source rows: plane row r = source row row_idx[r]
+int split_planes(const float* src, const int* row_idx, long long rows, int cols, long long ld, __nv_bfloat16* dst,
+                 long long ldp, long long plane_stride, cudaStream_t stream);
 // out[M][N] = epilogue(x[M][K] * w[K][N])
 int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms, cudaStream_t s);
 // out[M][K_in] = epilogue(dz[M][N_out] * w[K_in][N_out]^T)

@@ -63,20 +63,43 @@ __device__ __forceinline__ void split3(float x, __nv_bfloat16& h, __nv_bfloat16&
     l = __float2bfloat16_rn(r2);
 }
 
-// fp32 matrix [rows][cols] (pitch ld) -> planes [3][rows][ldp]; pad columns cols..ldp-1 are zeroed.
-__global__ void split_planes_kernel(const float* __restrict__ src, long long rows, int cols, long long ld,
-                                    __nv_bfloat16* __restrict__ dst, long long ldp, long long plane_stride) {
-    const long long total = rows * ldp;
+// fp32 matrix [rows][cols] (pitch ld, optional row gather) -> planes [3][rows][ldp]; pad columns
+// cols..ldp-1 are zeroed.  One thread converts 8 consecutive elements: two 16-byte loads when the
+// source row allows it, one 16-byte store per plane.
+__global__ void split_planes_kernel(const float* __restrict__ src, const int* __restrict__ row_idx, long long rows,
+                                    int cols, long long ld, __nv_bfloat16* __restrict__ dst, long long ldp,
+                                    long long plane_stride) {
+    const int groups = (int)(ldp / 8);
+    const long long total = rows * groups;
+    const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && (ld % 4 == 0);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
-        const long long r = i / ldp;
-        const int c = (int)(i - r * ldp);
-        const float x = c < cols ? src[r * ld + c] : 0.f;
-        __nv_bfloat16 h, m, l;
-        split3(x, h, m, l);
-        dst[i] = h;
-        dst[plane_stride + i] = m;
-        dst[2 * plane_stride + i] = l;
+        const long long r = i / groups;
+        const int c = (int)(i - r * groups) * 8;
+        const float* s = src + (row_idx ? (long long)row_idx[r] : r) * ld + c;
+        float x[8];
+        if (vec && c + 8 <= cols) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(s));
+            const float4 b = __ldg(reinterpret_cast<const float4*>(s) + 1);
+            x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w; x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) x[j] = (c + j < cols) ? s[j] : 0.f;
+        }
+        uint32_t ph[4], pm[4], pl[4];
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) {
+            __nv_bfloat16 h0, m0, l0, h1, m1, l1;
+            split3(x[j], h0, m0, l0);
+            split3(x[j + 1], h1, m1, l1);
+            ph[j / 2] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+            pm[j / 2] = (uint32_t)__bfloat16_as_ushort(m0) | ((uint32_t)__bfloat16_as_ushort(m1) << 16);
+            pl[j / 2] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+        }
+        __nv_bfloat16* o = dst + r * ldp + c;
+        *reinterpret_cast<uint4*>(o) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+        *reinterpret_cast<uint4*>(o + plane_stride) = make_uint4(pm[0], pm[1], pm[2], pm[3]);
+        *reinterpret_cast<uint4*>(o + 2 * plane_stride) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
     }
 }
 

@@ -189,6 +189,12 @@ template <typename T> static int get_f64(poz_ctx* c, const void* src_base, long 
 #define POZ_DISPATCH(c, fn, ...)                                                              \
     ((c)->dtype == POZ_DTYPE_F64 ? fn<double>(__VA_ARGS__) : fn<float>(__VA_ARGS__))
 
+static void clear_graphs(poz_ctx* c) {
+    for (auto& e : c->graphs)
+        if (e.exec) cudaGraphExecDestroy(e.exec);
+    c->graphs.clear();
+}
+
 // ---- workspace ---------------------------------------------------------------------------------
 static void free_workspace(poz_ctx* c) {
     for (auto& p : c->zbuf) dev_free(p);
@@ -218,6 +224,7 @@ static int reserve_train(poz_ctx* c, long long batch, bool diag) {
             if (c->acts[l] != ACT_NONE) POZ_TRY(dev_alloc(&c->zbuf[l], bytes));
         }
         c->ws_train = batch;
+        clear_graphs(c);
     }
     if (diag && c->ws_diag < c->ws_train) {
         for (int l = 0; l < nl; ++l) {
@@ -227,6 +234,7 @@ static int reserve_train(poz_ctx* c, long long batch, bool diag) {
             if (c->acts[l] != ACT_NONE) POZ_TRY(dev_alloc(&c->da_rec[l], bytes));
         }
         c->ws_diag = c->ws_train;
+        clear_graphs(c);
     }
     return 0;
 }
@@ -249,6 +257,7 @@ static int ensure_grad_slabs(poz_ctx* c, int slabs) {
     dev_free(c->G);
     POZ_TRY(dev_alloc(&c->G, (size_t)slabs * c->p_total * c->esz));
     c->g_slabs = slabs;
+    clear_graphs(c);
     return 0;
 }
 
@@ -999,6 +1008,7 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     c->da_rec.assign(n_linear, nullptr);
     c->max_splits = 16;
     if (const char* e = getenv("POZ_TC3_MIN_BATCH")) c->tc3_min_batch = atoll(e);
+    if (const char* e = getenv("POZ_GRAPHS")) c->graphs_enabled = atoi(e) != 0;
     auto fail = [&](void) { poz_ctx_destroy(c); return 1; };
     size_t pbytes = (size_t)c->p_total * c->esz;
     if (dev_alloc(&c->P, pbytes) || dev_alloc(&c->AM, pbytes) || dev_alloc(&c->AV, pbytes)) return fail();
@@ -1026,6 +1036,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
+    clear_graphs(c);
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
@@ -1188,6 +1199,14 @@ int poz_train_begin(poz_ctx* c, const poz_train_config* cfg) {
     h.next_epoch = 0; h.cur_epoch = 0; h.cur_record = -1; h.n_records = 0;
     POZ_CUDA(cudaMemcpy(c->st, &h, sizeof(h), cudaMemcpyHostToDevice));
     c->train_begun = true;
+    {   // captured steps bake these into kernel arguments; everything else lives in DevState
+        const double sig[6] = {cfg->dropout_rate, (double)cfg->global_batch, (double)c->cost_cap, (double)c->stats_cap,
+                               (double)reinterpret_cast<uintptr_t>(c->cost_ring), (double)reinterpret_cast<uintptr_t>(c->stats)};
+        if (std::memcmp(sig, c->graph_sig, sizeof(sig)) != 0) {
+            clear_graphs(c);
+            std::memcpy(c->graph_sig, sig, sizeof(sig));
+        }
+    }
     c->grads_pending = false;
     return 0;
 }
@@ -1214,10 +1233,62 @@ int poz_train_apply(poz_ctx* c, void* stream) {
                                      : apply_impl<float>(c, c->grads_reduced, s);
 }
 
+// A step on the same buffers and batch size launches the same kernels with the same arguments
+// (everything that changes from step to step lives in DevState on the device), so from the second
+// time a (x, target, row_idx, batch) key is seen the step is captured once into a CUDA graph and
+// replayed: one graph launch instead of ~11 kernel launches of host work per step.
 int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
                    long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
-    POZ_TRY(poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, keep_masks, diagnostics, stream));
-    return poz_train_apply(c, stream);
+    POZ_TRY(check_layer(c, 0, "poz_train_step"));
+    const bool graphable = c->graphs_enabled && !c->profiling && !diagnostics && !keep_masks &&
+                           c->dtype != POZ_DTYPE_BF16 && c->train_begun &&
+                           stream != nullptr;   // the legacy default stream cannot be captured
+    if (!graphable) {
+        POZ_TRY(poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, keep_masks, diagnostics, stream));
+        return poz_train_apply(c, stream);
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    poz_ctx::StepGraph* g = nullptr;
+    for (auto& e : c->graphs)
+        if (e.x == x_dev && e.t == target_dev && e.idx == row_idx_dev && e.batch == batch) { g = &e; break; }
+    if (g && g->exec) {
+        POZ_CUDA(cudaGraphLaunch(g->exec, s));
+        count_launch(g->launches);
+        return 0;
+    }
+    if (!g) {
+        // first sighting: run eagerly (this also performs every allocation the step needs)
+        if (c->graphs.size() >= 256) clear_graphs(c);
+        poz_ctx::StepGraph e;
+        e.x = x_dev; e.t = target_dev; e.idx = row_idx_dev; e.batch = batch;
+        c->graphs.push_back(e);
+        POZ_TRY(poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, nullptr, 0, stream));
+        return poz_train_apply(c, stream);
+    }
+    // second sighting: capture, instantiate, launch
+    const long long before = poz_launch_count();
+    POZ_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    int rc = poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, nullptr, 0, stream);
+    if (!rc) rc = poz_train_apply(c, stream);
+    cudaGraph_t graph = nullptr;
+    cudaError_t ce = cudaStreamEndCapture(s, &graph);
+    if (rc || ce != cudaSuccess || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        if (!rc) set_error(std::string("poz_train_step: graph capture failed: ") + cudaGetErrorString(ce));
+        c->graphs_enabled = false;          // fall back to plain launches for this context
+        cudaGetLastError();
+        if (rc) return rc;
+        POZ_TRY(poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, nullptr, 0, stream));
+        return poz_train_apply(c, stream);
+    }
+    cudaGraphExec_t exec = nullptr;
+    ce = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ce != cudaSuccess) POZ_FAIL(std::string("poz_train_step: cudaGraphInstantiate failed: ") + cudaGetErrorString(ce));
+    g->exec = exec;
+    g->launches = (int)(poz_launch_count() - before);
+    POZ_CUDA(cudaGraphLaunch(exec, s));
+    return 0;
 }
 
 int poz_grad_buffer(poz_ctx* c, void** dev_ptr, long long* n_elems, int* dtype_code, void* stream) {

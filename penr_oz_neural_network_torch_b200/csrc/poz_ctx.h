@@ -53,6 +53,16 @@ struct poz_ctx {
     std::vector<ProfRec> prof;
     bool profiling = false;
 
+    // CUDA-graph replay of whole train steps (same buffers, same batch): see poz_train_step
+    struct StepGraph {
+        const void* x; const void* t; const void* idx; long long batch;
+        cudaGraphExec_t exec = nullptr;   // null until the key has been seen twice
+        int launches = 0;
+    };
+    std::vector<StepGraph> graphs;
+    bool graphs_enabled = true;
+    double graph_sig[6] = {0, 0, 0, 0, 0, 0};
+
     poz_train_config cfg;
     bool train_begun = false, training_pass = false;
     bool grads_pending = false, grads_reduced = false, diag_pending = false, have_diag = false;

@@ -269,9 +269,11 @@ class DeviceMLP:
         nat.check(self.lib.poz_grad_layer(self.ctx, layer, C.byref(p), C.byref(n), int(stream.cuda_stream)))
         return _wrap_device_pointer(p.value, int(n.value), self.gdtype, self.device)
 
-    def costs(self, first: int, count: int) -> np.ndarray:
+    def costs(self, first: int, count: int, stream=None) -> np.ndarray:
+        """cost.item() of epochs [first, first+count); synchronises `stream` (default: current)."""
         out = np.empty((count,), dtype=np.float64)
-        nat.check(self.lib.poz_train_costs(self.ctx, first, count, out.ctypes.data, _stream_ptr(self.device)))
+        sp = _stream_ptr(self.device) if stream is None else int(stream.cuda_stream)
+        nat.check(self.lib.poz_train_costs(self.ctx, first, count, out.ctypes.data, sp))
         return out
 
     def update_ratios(self, first_record: int, count: int) -> np.ndarray:
@@ -392,6 +394,12 @@ class HostBatchFeeder:
         self.consumed[slot].record(cur)
         self._n += 1
 
-    def cost(self, epoch_index: int) -> float:
-        """Device->host read of that step's cost (synchronises on the step)."""
-        return float(self.eng.costs(epoch_index, 1)[0])
+    def cost(self, epoch_index: int, step_number: int | None = None) -> float:
+        """Device->host read of one step's cost.  With ``step_number`` (the 0-based count of
+        ``step()`` calls that produced it) the read runs on the copy stream behind that step's
+        completion event only, so a later step already in flight is not waited for; without it the
+        compute stream is synchronised."""
+        if step_number is None:
+            return float(self.eng.costs(epoch_index, 1)[0])
+        self.copy_stream.wait_event(self.consumed[step_number % 2])
+        return float(self.eng.costs(epoch_index, 1, stream=self.copy_stream)[0])

@@ -398,27 +398,37 @@ class NeuralNetworkModel(MultiLayerPerceptron):
                         progress_stride=stride, dropout_seed=random.getrandbits(63))
         for layer in self.layers:
             layer.training = True
+        # one persistent index buffer: every epoch reuses the same device addresses, so the
+        # library replays the step from a CUDA graph after the second epoch
+        idx_d = torch.empty((sample_size,), dtype=torch.int32, device=eng.device)
         stamps = []
         fetched = 0
         last_serialized = time.time()
-        for epoch in range(epochs):
-            idx = torch.randint(0, n_data, (sample_size,))                  # :460, same generator
-            idx_d = idx.to(torch.int32).to(eng.device, non_blocking=True)
-            if self.optimizer is not None:                                  # :467-469 (view only)
-                for group in self.optimizer.param_groups:
-                    group["lr"] = learning_rate * (decay_rate ** epoch)
-            long_training = time.time() - last_serialized >= 10             # :488
-            diagnostics = epoch + 1 == epochs or long_training              # :491
-            eng.train_step(x_all, t_all, row_idx=idx_d, diagnostics=diagnostics)
-            stamps.append(dt.now().isoformat())
-            if long_training:  # pragma: no cover
-                fetched = self._collect_progress(eng, stamps, fetched, epoch + 1, stride)
-                self._download_params()
-                if self.optimizer is not None:
-                    self._download_adam_state()
-                self._record_training_overall_progress(self._collect_diagnostics(eng, sample_size))
-                self.serialize()
-                last_serialized = time.time()
+        # a side stream: the library replays the step from a CUDA graph, which the legacy default
+        # stream does not allow
+        side = torch.cuda.Stream(device=eng.device)
+        side.wait_stream(torch.cuda.current_stream(eng.device))
+        with torch.cuda.stream(side):
+            for epoch in range(epochs):
+                idx = torch.randint(0, n_data, (sample_size,))                  # :460, same generator
+                idx_d.copy_(idx.to(torch.int32))
+                if self.optimizer is not None:                                  # :467-469 (view only)
+                    for group in self.optimizer.param_groups:
+                        group["lr"] = learning_rate * (decay_rate ** epoch)
+                long_training = time.time() - last_serialized >= 10             # :488
+                diagnostics = epoch + 1 == epochs or long_training              # :491
+                eng.train_step(x_all, t_all, row_idx=idx_d, diagnostics=diagnostics)
+                stamps.append(dt.now().isoformat())
+                if long_training:  # pragma: no cover
+                    fetched = self._collect_progress(eng, stamps, fetched, epoch + 1, stride)
+                    self._download_params()
+                    if self.optimizer is not None:
+                        self._download_adam_state()
+                    self._record_training_overall_progress(self._collect_diagnostics(eng, sample_size))
+                    self.serialize()
+                    last_serialized = time.time()
+        torch.cuda.current_stream(eng.device).wait_stream(side)
+        side.synchronize()
         self._collect_progress(eng, stamps, fetched, epochs, stride)
         self._download_params()
         if self.optimizer is not None:

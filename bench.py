@@ -213,27 +213,32 @@ def run_c2(args, world, rank, local):
     hx = [torch.randn((batch, 784), dtype=torch.float32).pin_memory() for _ in range(n_host)]
     hy = [torch.randint(0, 10, (batch,), dtype=torch.int32).pin_memory() for _ in range(n_host)]
     e2e_steps = args.steps
-    eng.train_begin(optimizer="adam", epochs=args.warmup + e2e_steps + 8, **HP)
-    feeder = HostBatchFeeder(eng, batch)
-    feeder.stage(hx[0], hy[0])
     # every step: host batch -> device, train step, that step's cost -> host.  The cost of step k is
     # read while step k+1 runs (one step of lag), so the GPU never idles on the read-back.
+    # host-side timing is exposed to host noise: three back-to-back timed regions, median reported
+    e2e_runs = []
+    k = args.warmup
+    last = 0.0
+    eng.train_begin(optimizer="adam", epochs=args.warmup + 3 * e2e_steps + 8, **HP)
+    feeder = HostBatchFeeder(eng, batch)
+    feeder.stage(hx[0], hy[0])
     for i in range(args.warmup):
         feeder.step(i)
         feeder.stage(hx[(i + 1) % n_host], hy[(i + 1) % n_host])
         if i:
             feeder.cost(i - 1, i - 1)
-    barrier_sync(world)
-    t0 = time.perf_counter()
-    last = 0.0
-    for i in range(e2e_steps):
-        k = args.warmup + i
-        feeder.step(k)
-        feeder.stage(hx[(k + 1) % n_host], hy[(k + 1) % n_host])
+    for rep in range(3):
+        barrier_sync(world)
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            feeder.step(k)
+            feeder.stage(hx[(k + 1) % n_host], hy[(k + 1) % n_host])
+            last = feeder.cost(k - 1, k - 1)
+            k += 1
         last = feeder.cost(k - 1, k - 1)
-    last = feeder.cost(args.warmup + e2e_steps - 1, args.warmup + e2e_steps - 1)
-    barrier_sync(world)
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
+        barrier_sync(world)
+        e2e_runs.append(max_over_ranks((time.perf_counter() - t0) * 1e3, world))
+    e2e_ms = float(np.median(e2e_runs))
     assert np.isfinite(last)
     clocks = sampler.stop() if sampler else None
 
@@ -270,7 +275,9 @@ def run_c2(args, world, rank, local):
                 value=world * batch * args.steps / (ms * 1e-3), ms_per_step=ms / args.steps,
                 e2e={"value": world * batch * e2e_steps / (e2e_ms * 1e-3), "unit": "samples/s",
                      "h2d_bytes_per_step": feeder.h2d_bytes, "d2h_bytes_per_step": feeder.d2h_bytes,
-                     "ms_per_step": e2e_ms / e2e_steps},
+                     "ms_per_step": e2e_ms / e2e_steps,
+                     "note": "median of 3 timed regions (host clock); cost of step k read back while step k+1 runs",
+                     "runs_ms_per_step": [round(v / e2e_steps, 5) for v in e2e_runs]},
                 gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
                 config={"workload": "c2: MLP 784-256-128-10 relu/relu/softmax + cross-entropy, Adam, L2 1e-3, "
                                     "batch 1024, fp32 train step", "batch_per_gpu": batch,

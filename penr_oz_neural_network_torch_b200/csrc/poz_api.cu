@@ -386,7 +386,8 @@ static bool tc3_stack_ok(const poz_ctx* c) {
     return true;
 }
 
-static int tc3_refresh_weights(poz_ctx* c, cudaStream_t stream) {
+static int tc3_refresh_weights(poz_ctx* c, cudaStream_t stream, int upto = -1) {
+    if (upto < 0) upto = c->nl;
     if (!c->Wp) {
         c->wp_off.assign(c->nl + 1, 0);
         c->wp_ld.assign(c->nl, 0);
@@ -398,15 +399,19 @@ static int tc3_refresh_weights(poz_ctx* c, cudaStream_t stream) {
         POZ_TRY(dev_alloc(&c->Wp, (size_t)c->wp_total * 2));
         c->wp_stale = true;
     }
-    if (!c->wp_stale) return 0;
-    for (int l = 0; l < c->nl; ++l) {
+    if (c->wp_stale || c->wp_fresh.size() != (size_t)c->nl) {
+        c->wp_fresh.assign(c->nl, 0);
+        c->wp_stale = false;
+    }
+    for (int l = 0; l < upto; ++l) {
+        if (c->wp_fresh[l]) continue;
+        c->wp_fresh[l] = 1;
         const int K = c->sizes[l], N = c->sizes[l + 1];
         ProfScope ps(c, "split_w", stream);
         POZ_TRY(tc3::split_planes(static_cast<const float*>(c->P) + c->off[l], nullptr, K, N, N,
                                   static_cast<__nv_bfloat16*>(c->Wp) + c->wp_off[l], c->wp_ld[l],
                                   (long long)K * c->wp_ld[l], stream));
     }
-    c->wp_stale = false;
     return 0;
 }
 
@@ -620,12 +625,41 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     plan_splits(c, batch, seg, kchunk);
     int slabs = 1;
     for (int l = 0; l < nl; ++l) slabs = std::max(slabs, seg.splits[l]);
+    // The first layer (the only deep contraction of a narrow stack) goes to the tensor cores
+    // (split-bf16) when nothing needs the SIMT epilogue's extras: no dropout, masks or diagnostics.
+    bool tc0 = false;
+    int tc0_splits = 1;
+    if constexpr (std::is_same<T, float>::value) {
+        tc0 = c->tc3_train && nl >= 2 && c->sizes[0] >= 256 && c->sizes[1] >= 64 && batch >= c->tc3_train_min_batch && !diag && !masks &&
+              c->cfg.dropout_rate == 0.0 && c->acts[0] != ACT_SOFTMAX;
+        if (tc0) {
+            const long long tiles = (long long)((c->sizes[0] + 127) / 128) * ((c->sizes[1] + 63) / 64);
+            while (tc0_splits < 16 && tiles * tc0_splits * 2 <= num_sms(c->device) && batch / (tc0_splits * 2) >= 128)
+                tc0_splits *= 2;
+            seg.splits[0] = tc0_splits;
+            slabs = std::max(slabs, tc0_splits);
+            if (batch > c->tc_tr_batch) {
+                dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz);
+                POZ_TRY(dev_alloc(&c->tc_tr_x, (size_t)3 * batch * round8(c->sizes[0]) * 2));
+                POZ_TRY(dev_alloc(&c->tc_tr_dz, (size_t)3 * batch * round8(c->sizes[1]) * 2));
+                c->tc_tr_batch = batch;
+                clear_graphs(c);
+            }
+            if (!c->Wp) POZ_TRY(tc3_refresh_weights(c, stream, 0));   // allocation only
+            if (!c->colsum_scratch) POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->colsum_scratch), (size_t)32 * c->sizes[1] * sizeof(float)));
+        }
+    }
     POZ_TRY(ensure_grad_slabs(c, slabs));
     c->seg_splits.assign(seg.splits, seg.splits + nl);
     c->training_pass = true;
     c->grads_reduced = false;
     c->diag_batch = diag ? batch : 0;
     c->last_batch = batch;
+    tc3::PlaneMat xp{};
+    if (tc0) {
+        xp.ptr = static_cast<const __nv_bfloat16*>(c->tc_tr_x);
+        xp.rows = batch; xp.cols = c->sizes[0]; xp.ld = round8(c->sizes[0]); xp.plane_stride = batch * xp.ld;
+    }
 
     {
         ProfScope ps(c, "step_begin", stream);
@@ -645,6 +679,26 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         T* a_out = ab;
         if (act == ACT_SOFTMAX) { z_out = zb; a_out = nullptr; }
         else if (act != ACT_NONE && diag) z_out = zb;
+        if constexpr (std::is_same<T, float>::value) {
+            if (tc0 && l == 0) {
+                const int K = c->sizes[0], N = c->sizes[1];
+                POZ_TRY(tc3_refresh_weights(c, stream, 1));
+                {
+                    ProfScope ps(c, "split_x", stream);
+                    POZ_TRY(tc3::split_planes(x, row_idx, batch, K, K, static_cast<__nv_bfloat16*>(c->tc_tr_x), xp.ld,
+                                              xp.plane_stride, stream));
+                }
+                tc3::Epi3 ep{};
+                ep.mode = tc3::EPI_BIAS_ACT; ep.act = act;
+                ep.bias = c->has_bias ? static_cast<const float*>(c->P) + c->off[0] + (long long)K * N : nullptr;
+                ep.out_f32 = ab; ep.ld_f32 = N;
+                ProfScope ps(c, "tc3_fwd_l0", stream);
+                POZ_TRY(tc3::gemm_forward(xp, tc3_weight(c, 0), batch, N, K, ep, num_sms(c->device), stream));
+                cur = ab;
+                cur_idx = nullptr;
+                continue;
+            }
+        }
         POZ_TRY(layer_forward<T>(c, l, cur, cur_idx, batch, batch, z_out, a_out, masks, stream));
         cur = (act == ACT_SOFTMAX) ? zb : ab;
         cur_idx = nullptr;
@@ -684,6 +738,35 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         const int K = c->sizes[l], N = c->sizes[l + 1], hb = c->has_bias;
         const T* dz = static_cast<const T*>(c->dzbuf[l]);
         if constexpr (std::is_same<T, float>::value) {
+          if (tc0 && l == 0) {
+            tc3::PlaneMat dzp;
+            dzp.ptr = static_cast<const __nv_bfloat16*>(c->tc_tr_dz);
+            dzp.rows = batch; dzp.cols = N; dzp.ld = round8(N); dzp.plane_stride = batch * dzp.ld;
+            {
+                ProfScope ps(c, "split_dz", stream);
+                POZ_TRY(tc3::split_planes(dz, nullptr, batch, N, N, static_cast<__nv_bfloat16*>(c->tc_tr_dz), dzp.ld,
+                                          dzp.plane_stride, stream));
+            }
+            float* G = static_cast<float*>(c->G);
+            tc3::Epi3 ep{};
+            ep.mode = tc3::EPI_PLAIN;
+            ep.out_f32 = G + c->off[0]; ep.ld_f32 = N; ep.slab = c->p_total;
+            {
+                ProfScope ps(c, "tc3_bwd_w_l0", stream);
+                POZ_TRY(tc3::gemm_backward_weight(xp, dzp, batch, K, N, tc0_splits, ep, num_sms(c->device), stream));
+            }
+            if (hb) {
+                ProfScope ps(c, "bias_grad", stream);
+                float* gb_row = G + c->off[0] + (long long)K * N;
+                for (int s2 = 1; s2 < tc0_splits; ++s2)
+                    POZ_CUDA(cudaMemsetAsync(gb_row + (long long)s2 * c->p_total, 0, (size_t)N * sizeof(float), stream));
+                colsum_f32_partial_kernel<<<dim3((N + 63) / 64, 32), 256, 0, stream>>>(dz, batch, N, c->colsum_scratch);
+                POZ_LAUNCH_CHECK();
+                colsum_f32_final_kernel<<<(N + 255) / 256, 256, 0, stream>>>(c->colsum_scratch, 32, N, gb_row);
+                POZ_LAUNCH_CHECK();
+            }
+            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
+          } else {
             const float* inp = l == 0 ? x : static_cast<const float*>(c->abuf[l - 1]);
             fast::Op A = make_fast_op(inp, K, l == 0 ? row_idx : nullptr, batch, K);
             fast::Op B = make_fast_op(dz, N, nullptr, batch, N);
@@ -693,6 +776,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             if (hb) POZ_TRY((launch_fast<32, 64, false, false, true>(A, B, K, N, batch, seg.splits[l], false, K, epi, stream)));
             else    POZ_TRY((launch_fast<32, 64, false, false, false>(A, B, K, N, batch, seg.splits[l], false, K, epi, stream)));
             if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
+          }
         } else {
             const T* inp = l == 0 ? x : static_cast<const T*>(c->abuf[l - 1]);
             Operand<T> A = make_operand<T>(inp, K, l == 0 ? row_idx : nullptr, batch, K, hb);
@@ -1009,6 +1093,8 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     c->max_splits = 16;
     if (const char* e = getenv("POZ_TC3_MIN_BATCH")) c->tc3_min_batch = atoll(e);
     if (const char* e = getenv("POZ_GRAPHS")) c->graphs_enabled = atoi(e) != 0;
+    if (const char* e = getenv("POZ_TC3_TRAIN")) c->tc3_train = atoi(e) != 0;
+    if (const char* e = getenv("POZ_TC3_TRAIN_MIN_BATCH")) c->tc3_train_min_batch = atoll(e);
     auto fail = [&](void) { poz_ctx_destroy(c); return 1; };
     size_t pbytes = (size_t)c->p_total * c->esz;
     if (dev_alloc(&c->P, pbytes) || dev_alloc(&c->AM, pbytes) || dev_alloc(&c->AV, pbytes)) return fail();
@@ -1041,6 +1127,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
     dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
+    dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz);
     dev_free(reinterpret_cast<void*&>(c->tc_logits));
     dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
     dev_free(reinterpret_cast<void*&>(c->st));

@@ -23,7 +23,15 @@ struct poz_ctx {
     void* Wp = nullptr;               // weight planes, layer l at wp_off[l]: [3][in_l][wp_ld[l]] bf16
     std::vector<long long> wp_off, wp_ld;
     long long wp_total = 0;
-    bool wp_stale = true;             // parameters changed since the planes were built
+    bool wp_stale = true;             // parameters changed since (some of) the planes were built
+    std::vector<char> wp_fresh;       // per layer: planes match the current parameters
+    void* tc_tr_x = nullptr;          // training: planes of the (gathered) input batch
+    void* tc_tr_dz = nullptr;         // training: planes of dZ of the first layer
+    long long tc_tr_batch = 0;
+    // measured at batch 1024 (C2) the plane splits cost what the tensor cores save, so the SIMT
+    // kernels keep the first layer below this batch (POZ_TC3_TRAIN_MIN_BATCH overrides)
+    long long tc3_train_min_batch = 8192;
+    bool tc3_train = true;            // first layer of float32 training on tcgen05 when it is deep enough
     void* tc_scr[3] = {nullptr, nullptr, nullptr};   // plane stacks: input chunk, ping, pong
     float* tc_logits = nullptr;       // fp32 logits of a chunk (trailing softmax)
     long long tc_chunk = 0;

@@ -270,6 +270,37 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
     }
 }
 
+// Bias gradient db[n] = sum_b dz[b][n] for float32 dz (test_torch_backward.py:166), two
+// deterministic passes: block (x, r) sums rows r*8+warp, +8*gridDim.y, ... of 64 columns into
+// partial[r][n]; the second pass adds the gridDim.y partials in a fixed order.
+__global__ void colsum_f32_partial_kernel(const float* __restrict__ dz, long long rows, int N, float* __restrict__ partial) {
+    __shared__ float red[8][64];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c0 = blockIdx.x * 64 + lane, c1 = c0 + 32;
+    float s0 = 0.f, s1 = 0.f;
+    for (long long r = (long long)blockIdx.y * 8 + warp; r < rows; r += (long long)gridDim.y * 8) {
+        if (c0 < N) s0 += dz[r * N + c0];
+        if (c1 < N) s1 += dz[r * N + c1];
+    }
+    red[warp][lane] = s0;
+    red[warp][lane + 32] = s1;
+    __syncthreads();
+    if (threadIdx.x < 64) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+        const int cc = blockIdx.x * 64 + threadIdx.x;
+        if (cc < N) partial[(long long)blockIdx.y * N + cc] = t;
+    }
+}
+__global__ void colsum_f32_final_kernel(const float* __restrict__ partial, int parts, int N, float* __restrict__ out) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float t = 0.f;
+    for (int r = 0; r < parts; ++r) t += partial[(long long)r * N + n];
+    out[n] = t;
+}
+
 // L2 penalty for the inference-with-target path is never needed (compute_output has no L2).
 
 template <typename S, typename D>

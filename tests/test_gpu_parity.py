@@ -317,3 +317,35 @@ def test_in_kernel_dropout_statistics_and_determinism():
     np.testing.assert_array_equal(runs[0][0], runs[1][0])       # same seed -> same masks
     assert (runs[0][0] != runs[2][0]).any()                     # different seed -> different masks
     assert np.isfinite(runs[0][2])
+
+
+def test_large_batch_training_with_first_layer_on_tensor_cores():
+    """Batch 8192 >= the threshold at which the first layer's forward / weight-gradient GEMMs run on
+    tcgen05 (split-bf16): three Adam steps against the live oracle, same float32 tolerance."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    sizes, algos = mnist_stack()
+    B = 8192
+    params = det_params(sizes, True, 177)
+    x = det_normalish((B, 784), 178)
+    y = det_labels(B, 10, 179)
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+    for l in range(3):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    xd = torch.tensor(x, dtype=torch.float32, device="cuda:0")
+    yd = torch.tensor(y, dtype=torch.int32, device="cuda:0")
+    eng.train_begin(optimizer="sgd", learning_rate=0.05, decay_rate=0.9, l2_lambda=0.001, epochs=3)
+    eng.profile_begin()
+    for _ in range(3):
+        eng.train_step(xd, yd)
+    assert "tc3_bwd_w_l0" in eng.profile_end()
+    stack = orc.parse_stack(algos)
+    p, costs = params, []
+    tgt = [[int(v)] for v in y]
+    for step in range(3):
+        p, c, *_ = orc.train_step(stack, p, x, tgt, lr=0.05 * 0.9 ** step, optimizer="sgd", l2_lambda=0.001)
+        costs.append(c)
+    close(eng.costs(0, 3), costs, "float32", "costs")
+    for l in range(3):
+        w, b = eng.download_params(l)
+        close(w, p[2 * l], "float32", f"W{l}", outliers=True)
+        close(b, p[2 * l + 1], "float32", f"b{l}", outliers=True)

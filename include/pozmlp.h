@@ -124,6 +124,19 @@ int poz_diag_activation(poz_ctx* ctx, int layer, int which, double* host_out);
 int poz_diag_activation_grad(poz_ctx* ctx, int layer, int which, double* host_out, int* has_grad);
 int poz_diag_weight_grad(poz_ctx* ctx, int layer, double* w_grad, double* b_grad);
 
+/* Device-side statistics of the same tensors, replacing the mean / std / saturation / 100-bin density
+ * histograms that _record_training_overall_progress computes on the host (neural_net_model.py:542-583),
+ * so that only a few hundred bytes per tensor leave the device.
+ * source: 0 = entry output, 1 = its gradient, 2 = the layer's weight matrix, 3 = its gradient.
+ * poz_diag_moments -> out6 = {count (0 if the tensor does not exist), sum, sum of squares, min, max,
+ *   saturated fraction}; rule 1: |x| > threshold (:558,:561), rule 2: x <= 0 (:559), rule 3: row maximum >
+ *   threshold (:560), 0: none.
+ * poz_diag_histogram -> counts per bin for the caller's bin edges (torch.histogram's: bin i is
+ *   [edges[i], edges[i+1]), the last one closed). */
+int poz_diag_moments(poz_ctx* ctx, int layer, int which, int source, int rule, double threshold, double* out6);
+int poz_diag_histogram(poz_ctx* ctx, int layer, int which, int source, const double* edges, int bins,
+                       double* counts);
+
 /* ---- data parallel (new: the reference is single-process) --------------------------------
  * The flat gradient image (all layers, compute dtype... always float32/float64) that the host
  * all-reduces with NCCL between the backward and the update of a step. */

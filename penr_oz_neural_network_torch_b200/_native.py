@@ -106,6 +106,8 @@ SIGNATURES = {
     "poz_diag_activation": (_I, [_VP, _I, _I, _VP]),
     "poz_diag_activation_grad": (_I, [_VP, _I, _I, _VP, C.POINTER(_I)]),
     "poz_diag_weight_grad": (_I, [_VP, _I, _VP, _VP]),
+    "poz_diag_moments": (_I, [_VP, _I, _I, _I, _I, C.c_double, _VP]),
+    "poz_diag_histogram": (_I, [_VP, _I, _I, _I, _VP, _I, _VP]),
     "poz_grad_buffer": (_I, [_VP, C.POINTER(_VP), C.POINTER(_LL), C.POINTER(_I), _VP]),
     "poz_grad_layer": (_I, [_VP, _I, C.POINTER(_VP), C.POINTER(_LL), _VP]),
     "poz_train_backward": (_I, [_VP, _VP, _VP, _VP, _LL, C.POINTER(_VP), _I, _VP]),

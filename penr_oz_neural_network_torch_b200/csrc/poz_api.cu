@@ -1479,6 +1479,82 @@ int poz_diag_activation_grad(poz_ctx* c, int layer, int which, double* host_out,
     return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, n);
 }
 
+// which tensor a diagnostics request means: activation / its gradient of an entry, weights, weight gradient
+static int diag_tensor(poz_ctx* c, int layer, int which, int source, const void** ptr, long long* rows, int* cols) {
+    *ptr = nullptr;
+    if (c->dtype == POZ_DTYPE_BF16) POZ_FAIL("diagnostics are not available in bf16 contexts");
+    const int act = c->acts[layer];
+    if (source == 0 || source == 1) {
+        if (c->diag_batch <= 0) POZ_FAIL("diagnostics: no step was run with diagnostics enabled");
+        *rows = c->diag_batch; *cols = c->sizes[layer + 1];
+        if (source == 0) {
+            if (which == 0) *ptr = act == ACT_NONE ? c->abuf[layer] : c->zbuf[layer];
+            else if (act != ACT_NONE) *ptr = c->abuf[layer];
+        } else {
+            if (which == 0) *ptr = c->dz_rec[layer];
+            else if (act != ACT_NONE && act != ACT_SOFTMAX) *ptr = c->da_rec[layer];
+        }
+    } else {
+        *rows = c->sizes[layer]; *cols = c->sizes[layer + 1];
+        if (source == 2) *ptr = static_cast<const char*>(c->P) + c->off[layer] * c->esz;
+        else if (source == 3) {
+            if (!c->have_diag || !c->Gdiag) POZ_FAIL("diagnostics: no weight gradients recorded");
+            *ptr = static_cast<const char*>(c->Gdiag) + c->off[layer] * c->esz;
+        }
+    }
+    return 0;
+}
+
+int poz_diag_moments(poz_ctx* c, int layer, int which, int source, int rule, double threshold, double* out6) {
+    POZ_TRY(check_layer(c, layer, "poz_diag_moments"));
+    const void* ptr; long long rows; int cols;
+    POZ_TRY(diag_tensor(c, layer, which, source, &ptr, &rows, &cols));
+    out6[0] = 0.0;
+    if (!ptr) return 0;                      // no such tensor (e.g. the trailing softmax has no gradient)
+    const long long n = rows * cols;
+    const int blocks = (int)std::min<long long>((n + 255) / 256, 512);
+    POZ_TRY(ensure_stage(c, (size_t)blocks * 5));
+    if (c->dtype == POZ_DTYPE_F64)
+        diag_moments_kernel<double><<<blocks, 256>>>(static_cast<const double*>(ptr), rows, cols, rule, threshold, c->stage);
+    else
+        diag_moments_kernel<float><<<blocks, 256>>>(static_cast<const float*>(ptr), rows, cols, rule, threshold, c->stage);
+    POZ_LAUNCH_CHECK();
+    std::vector<double> part((size_t)blocks * 5);
+    POZ_CUDA(cudaMemcpy(part.data(), c->stage, part.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    double s = 0, s2 = 0, mn = INFINITY, mx = -INFINITY, sat = 0;
+    for (int b = 0; b < blocks; ++b) {
+        s += part[b * 5]; s2 += part[b * 5 + 1]; sat += part[b * 5 + 4];
+        mn = std::min(mn, part[b * 5 + 2]); mx = std::max(mx, part[b * 5 + 3]);
+    }
+    out6[0] = (double)n; out6[1] = s; out6[2] = s2; out6[3] = mn; out6[4] = mx;
+    out6[5] = sat / (rule == 3 ? (double)rows : (double)n);
+    return 0;
+}
+
+int poz_diag_histogram(poz_ctx* c, int layer, int which, int source, const double* edges, int bins, double* counts) {
+    POZ_TRY(check_layer(c, layer, "poz_diag_histogram"));
+    if (bins < 1 || bins > 128) POZ_FAIL("poz_diag_histogram: bins must be in [1,128]");
+    const void* ptr; long long rows; int cols;
+    POZ_TRY(diag_tensor(c, layer, which, source, &ptr, &rows, &cols));
+    if (!ptr) POZ_FAIL("poz_diag_histogram: no such tensor");
+    const long long n = rows * cols;
+    POZ_TRY(ensure_stage(c, 512));
+    double* d_edges = c->stage;
+    unsigned long long* d_counts = reinterpret_cast<unsigned long long*>(c->stage + 256);
+    POZ_CUDA(cudaMemcpy(d_edges, edges, (size_t)(bins + 1) * sizeof(double), cudaMemcpyHostToDevice));
+    POZ_CUDA(cudaMemset(d_counts, 0, (size_t)bins * sizeof(unsigned long long)));
+    const int blocks = (int)std::min<long long>((n + 255) / 256, 1184);
+    if (c->dtype == POZ_DTYPE_F64)
+        diag_histogram_kernel<double><<<blocks, 256>>>(static_cast<const double*>(ptr), n, d_edges, bins, d_counts);
+    else
+        diag_histogram_kernel<float><<<blocks, 256>>>(static_cast<const float*>(ptr), n, d_edges, bins, d_counts);
+    POZ_LAUNCH_CHECK();
+    std::vector<unsigned long long> h(bins);
+    POZ_CUDA(cudaMemcpy(h.data(), d_counts, (size_t)bins * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < bins; ++i) counts[i] = (double)h[i];
+    return 0;
+}
+
 int poz_diag_weight_grad(poz_ctx* c, int layer, double* w_grad, double* b_grad) {
     POZ_TRY(diag_ready(c, layer, "poz_diag_weight_grad"));
     if (!c->have_diag || !c->Gdiag) POZ_FAIL("poz_diag_weight_grad: no diagnostics gradients recorded");

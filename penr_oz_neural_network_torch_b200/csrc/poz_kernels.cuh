@@ -303,6 +303,74 @@ __global__ void colsum_f32_final_kernel(const float* __restrict__ partial, int p
 
 // L2 penalty for the inference-with-target path is never needed (compute_output has no L2).
 
+// ---- device-side diagnostics (neural_net_model.py:532-583) -----------------------------------------
+// Pass 1: per-block partial moments of a tensor: [sum, sum of squares, min, max, saturated count].
+// rule 1: |x| > thr; rule 2: x <= 0; rule 3: row maximum > thr (counted per row, cols <= 1024 per warp loop).
+template <typename T>
+__global__ void diag_moments_kernel(const T* __restrict__ x, long long rows, int cols, int rule, double thr,
+                                    double* __restrict__ partial /*[gridDim.x][5]*/) {
+    const long long n = rows * cols;
+    double s = 0.0, s2 = 0.0, mn = INFINITY, mx = -INFINITY, sat = 0.0;
+    if (rule == 3) {
+        const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+        for (long long r = (long long)blockIdx.x * wpb + (threadIdx.x >> 5); r < rows; r += (long long)gridDim.x * wpb) {
+            double rmax = -INFINITY;
+            for (int j = lane; j < cols; j += 32) {
+                const double v = (double)x[r * cols + j];
+                s += v; s2 += v * v; mn = v < mn ? v : mn; mx = v > mx ? v : mx; rmax = v > rmax ? v : rmax;
+            }
+            rmax = warp_max(rmax);
+            if (lane == 0 && rmax > thr) sat += 1.0;
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+            const double v = (double)x[i];
+            s += v; s2 += v * v; mn = v < mn ? v : mn; mx = v > mx ? v : mx;
+            if (rule == 1) sat += (fabs(v) > thr) ? 1.0 : 0.0;
+            else if (rule == 2) sat += (v <= 0.0) ? 1.0 : 0.0;
+        }
+    }
+    __shared__ double red[5][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    s = warp_sum(s); s2 = warp_sum(s2); sat = warp_sum(sat);
+    mn = -warp_max(-mn); mx = warp_max(mx);
+    if (lane == 0) { red[0][w] = s; red[1][w] = s2; red[2][w] = mn; red[3][w] = mx; red[4][w] = sat; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        for (int k = 1; k < nw; ++k) {
+            red[0][0] += red[0][k]; red[1][0] += red[1][k]; red[4][0] += red[4][k];
+            red[2][0] = red[2][k] < red[2][0] ? red[2][k] : red[2][0];
+            red[3][0] = red[3][k] > red[3][0] ? red[3][k] : red[3][0];
+        }
+        for (int k = 0; k < 5; ++k) partial[blockIdx.x * 5 + k] = red[k][0];
+    }
+}
+
+// Pass 2: counts per bin for given bin edges (torch.histogram's own edges, computed by the host):
+// bin i = [edges[i], edges[i+1]), the last bin closed on the right.
+template <typename T>
+__global__ void diag_histogram_kernel(const T* __restrict__ x, long long n, const double* __restrict__ edges, int bins,
+                                      unsigned long long* __restrict__ counts) {
+    __shared__ double e[129];
+    __shared__ unsigned int h[128];
+    for (int i = threadIdx.x; i <= bins; i += blockDim.x) e[i] = edges[i];
+    for (int i = threadIdx.x; i < bins; i += blockDim.x) h[i] = 0u;
+    __syncthreads();
+    const double lo = e[0], scale = (double)bins / (e[bins] - e[0]);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double v = (double)x[i];
+        int pos = (int)((v - lo) * scale);
+        pos = pos < 0 ? 0 : (pos > bins - 1 ? bins - 1 : pos);
+        while (pos > 0 && v < e[pos]) --pos;
+        while (pos < bins - 1 && v >= e[pos + 1]) ++pos;
+        atomicAdd(&h[pos], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < bins; i += blockDim.x)
+        if (h[i]) atomicAdd(&counts[i], (unsigned long long)h[i]);
+}
+
 template <typename S, typename D>
 __global__ void convert_kernel(const S* __restrict__ src, D* __restrict__ dst, long long n) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;

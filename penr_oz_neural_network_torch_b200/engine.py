@@ -304,6 +304,34 @@ class DeviceMLP:
         nat.check(self.lib.poz_diag_activation_grad(self.ctx, layer, which, out.ctypes.data, C.byref(has)))
         return out if has.value else None
 
+    def diag_stats(self, layer: int, which: int, source: int, rule: int = 0, threshold: float = 0.0,
+                   histogram: bool = True):
+        """mean / unbiased std / saturated fraction / torch.histogram(density=True) of one diagnostics
+        tensor, computed on the device (neural_net_model.py:542-583).  Returns None if the tensor does
+        not exist (e.g. the gradient of the trailing softmax).  source: 0 output, 1 its gradient,
+        2 weights, 3 weight gradient."""
+        m = np.zeros(6)
+        nat.check(self.lib.poz_diag_moments(self.ctx, layer, which, source, rule, float(threshold), m.ctypes.data))
+        n = m[0]
+        if n == 0:
+            return None
+        mean = m[1] / n
+        var = (m[2] - n * mean * mean) / (n - 1) if n > 1 else float("nan")
+        out = {"mean": float(mean), "std": float(np.sqrt(max(var, 0.0))) if n > 1 else float("nan"),
+               "saturated": float(m[5])}
+        if histogram:
+            lo, hi = float(m[3]), float(m[4])
+            if lo == hi:                       # torch.histogram widens a degenerate range by 0.5 each side
+                lo, hi = lo - 0.5, hi + 0.5
+            edges = torch.linspace(lo, hi, 101, dtype=torch.float64)
+            e = np.ascontiguousarray(edges.numpy())
+            counts = np.zeros(100)
+            nat.check(self.lib.poz_diag_histogram(self.ctx, layer, which, source, e.ctypes.data, 100,
+                                                  counts.ctypes.data))
+            widths = np.diff(e)
+            out["histogram"] = {"x": edges[:-1].tolist(), "y": (counts / (n * widths)).tolist()}
+        return out
+
     def diag_weight_grad(self, layer: int):
         w = np.empty((self.sizes[layer], self.sizes[layer + 1]), dtype=np.float64)
         b = np.empty((self.sizes[layer + 1],), dtype=np.float64) if self.has_bias else None

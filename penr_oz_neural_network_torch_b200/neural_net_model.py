@@ -424,7 +424,7 @@ class NeuralNetworkModel(MultiLayerPerceptron):
                     self._download_params()
                     if self.optimizer is not None:
                         self._download_adam_state()
-                    self._record_training_overall_progress(self._collect_diagnostics(eng, sample_size))
+                    self._record_training_overall_progress(self._device_statistics(eng))
                     self.serialize()
                     last_serialized = time.time()
         torch.cuda.current_stream(eng.device).wait_stream(side)
@@ -435,7 +435,7 @@ class NeuralNetworkModel(MultiLayerPerceptron):
             self._download_adam_state()
         self.status = "Trained"
         log.info(f"Model {self.model_id}: Done training for {epochs} epochs.")
-        self._record_training_overall_progress(self._collect_diagnostics(eng, sample_size))
+        self._record_training_overall_progress(self._device_statistics(eng))
         self.serialize()
 
     def _collect_progress(self, eng: DeviceMLP, stamps, first: int, upto: int, stride: int) -> int:
@@ -461,68 +461,49 @@ class NeuralNetworkModel(MultiLayerPerceptron):
             log.info(f"Model {self.model_id}: Epoch {epoch + 1}, Cost: {cost:.4f}")
         return upto
 
-    def _collect_diagnostics(self, eng: DeviceMLP, batch: int) -> list[dict]:
-        """Per-entry output, its gradient and the weight gradient of the last diagnostics step."""
-        entries = []
+    _SATURATION_RULE = {"tanh": (1, 0.97), "sigmoid": (1, 0.97), "relu": (2, 0.0), "softmax": (3, 0.97)}
+
+    def _device_statistics(self, eng: DeviceMLP) -> tuple[list, list]:
+        """Statistics of the last diagnostics step (neural_net_model.py:542-583), reduced on the
+        device: per entry the output's mean / std / saturation / density histogram and the same for
+        its gradient; per weight matrix its mean / std and its gradient's mean / std / histogram."""
         spec = self.stack
+        layer_stats, weight_stats = [], []
         for i, layer in enumerate(self.layers):
             if layer.algo == "linear":
-                li = spec.z_index.index(i)
-                act = eng.diag_activation(li, 0, batch)
-                grad = eng.diag_activation_grad(li, 0, batch)
-                w_grad, _ = eng.diag_weight_grad(li)
+                li, which = spec.z_index.index(i), 0
             else:
-                li = spec.a_index.index(i)
-                act = eng.diag_activation(li, 1, batch)
-                grad = eng.diag_activation_grad(li, 1, batch)
-                w_grad = None
-            entries.append({"act": torch.from_numpy(act),
-                            "grad": None if grad is None else torch.from_numpy(grad),
-                            "w_grad": None if w_grad is None else torch.from_numpy(w_grad)})
-        return entries
+                li, which = spec.a_index.index(i), 1
+            rule, thr = self._SATURATION_RULE.get(layer.algo, (1, 5.0))          # :556-561
+            act = eng.diag_stats(li, which, 0, rule, thr)
+            grad = eng.diag_stats(li, which, 1)
+            layer_stats.append({
+                "algo": layer.algo,
+                "activation": {"mean": act["mean"], "std": act["std"], "saturated": act["saturated"],
+                               "histogram": act["histogram"]},
+                "gradient": None if grad is None else {"mean": grad["mean"], "std": grad["std"],
+                                                       "histogram": grad["histogram"]},
+            })
+            if layer.weights is None:
+                weight_stats.append(None)
+            else:
+                w = eng.diag_stats(li, 0, 2, histogram=False)
+                wg = eng.diag_stats(li, 0, 3)
+                weight_stats.append({
+                    "shape": str(tuple(layer.weights.shape)),
+                    "data": {"mean": w["mean"], "std": w["std"]},
+                    "gradient": {"mean": wg["mean"], "std": wg["std"], "histogram": wg["histogram"]},
+                })
+        return layer_stats, weight_stats
 
     # ------------------------------------------------------------------ diagnostics (:532-585)
-    def _record_training_overall_progress(self, entries: list[dict]):
+    def _record_training_overall_progress(self, statistics):
         costs = [p["cost"] for p in self.progress]
         avg_progress_cost = sum(costs) / len(self.progress)
         self.avg_cost = ((self.avg_cost or avg_progress_cost) + avg_progress_cost) / 2.0
         self.avg_cost_history.append(self.avg_cost)
         if len(self.avg_cost_history) > 100:
             self.avg_cost_history.pop(random.randint(1, 98))
-
-        def density(t: Tensor):
-            h = torch.histogram(t, density=True)
-            return {"x": h.bin_edges[:-1].tolist(), "y": h.hist.tolist()}
-
-        def saturation(algo: str, a: Tensor) -> float:
-            if algo in ("tanh", "sigmoid"):
-                flags = a.abs() > 0.97
-            elif algo == "relu":
-                flags = a <= 0
-            elif algo == "softmax":
-                flags = a.max(dim=-1).values > 0.97
-            else:
-                flags = a.abs() > 5.0
-            return flags.float().mean().item()
-
-        layer_stats, weight_stats = [], []
-        for layer, e in zip(self.layers, entries):
-            a, g = e["act"], e["grad"]
-            layer_stats.append({
-                "algo": layer.algo,
-                "activation": {"mean": a.mean().item(), "std": a.std().item(),
-                               "saturated": saturation(layer.algo, a), "histogram": density(a)},
-                "gradient": None if g is None else {"mean": g.mean().item(), "std": g.std().item(),
-                                                    "histogram": density(g)},
-            })
-            if layer.weights is None:
-                weight_stats.append(None)
-            else:
-                wg = e["w_grad"]
-                weight_stats.append({
-                    "shape": str(tuple(layer.weights.shape)),
-                    "data": {"mean": layer.weights.mean().item(), "std": layer.weights.std().item()},
-                    "gradient": {"mean": wg.mean().item(), "std": wg.std().item(), "histogram": density(wg)},
-                })
+        layer_stats, weight_stats = statistics
         self.stats = {"layers": layer_stats, "weights": weight_stats}
         log.info(f"Model {self.model_id} - Cost: {avg_progress_cost:.4f} Overall Cost: {self.avg_cost:.4f}")

@@ -349,3 +349,48 @@ def test_large_batch_training_with_first_layer_on_tensor_cores():
         w, b = eng.download_params(l)
         close(w, p[2 * l], "float32", f"W{l}", outliers=True)
         close(b, p[2 * l + 1], "float32", f"b{l}", outliers=True)
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+def test_device_statistics_equal_host_torch_statistics(dtype):
+    """The device-side reductions behind `stats` (neural_net_model.py:542-583) against the reference's
+    own host formulas (mean / unbiased std / saturation rule / torch.histogram(density=True)) applied to
+    the downloaded tensors: histogram densities identical, moments to 1e-10."""
+    arrays, meta = load_golden("step_odd_sizes_adam")          # tanh, sigmoid, softmax; batch 67
+    eng, spec, params, x, xd, target, td = build_case(meta, dtype)
+    eng.train_begin(optimizer="adam", learning_rate=0.01, l2_lambda=0.001, epochs=1)
+    eng.train_step(xd, td, diagnostics=True)
+    B = meta["batch"]
+    rules = {"tanh": (1, 0.97), "sigmoid": (1, 0.97), "relu": (2, 0.0), "softmax": (3, 0.97), "none": (1, 5.0)}
+
+    def host(t, rule, thr):
+        t = torch.from_numpy(t)
+        h = torch.histogram(t, density=True)
+        sat = ((t.abs() > thr) if rule == 1 else (t <= 0) if rule == 2 else (t.max(dim=-1).values > thr)).float().mean().item()
+        return t.mean().item(), t.std().item(), sat, h.bin_edges[:-1].tolist(), h.hist.tolist()
+
+    def check(dev, t, rule=1, thr=5.0, sat=True):
+        m, s, st, hx, hy = host(t, rule, thr)
+        np.testing.assert_allclose(dev["mean"], m, rtol=1e-10, atol=1e-14)
+        np.testing.assert_allclose(dev["std"], s, rtol=1e-10)
+        if sat:
+            np.testing.assert_allclose(dev["saturated"], st, rtol=1e-6)
+        np.testing.assert_allclose(dev["histogram"]["x"], hx, rtol=0, atol=0)
+        np.testing.assert_allclose(dev["histogram"]["y"], hy, rtol=1e-12)
+
+    for l in range(spec.n_linear):
+        check(eng.diag_stats(l, 0, 0, 1, 5.0), eng.diag_activation(l, 0, B), 1, 5.0)
+        check(eng.diag_stats(l, 0, 1), eng.diag_activation_grad(l, 0, B), sat=False)
+        act = spec.acts[l]
+        rule, thr = rules[act]
+        check(eng.diag_stats(l, 1, 0, rule, thr), eng.diag_activation(l, 1, B), rule, thr)
+        g = eng.diag_activation_grad(l, 1, B)
+        d = eng.diag_stats(l, 1, 1)
+        assert (g is None) == (d is None)
+        if g is not None:
+            check(d, g, sat=False)
+        wg, _ = eng.diag_weight_grad(l)
+        check(eng.diag_stats(l, 0, 3), wg, sat=False)
+        w, _ = eng.download_params(l)
+        dw = eng.diag_stats(l, 0, 2, histogram=False)
+        np.testing.assert_allclose([dw["mean"], dw["std"]], [w.mean(), w.std(ddof=1)], rtol=1e-10, atol=1e-14)

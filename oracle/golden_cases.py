@@ -59,3 +59,29 @@ INIT_CASES = [
     dict(name="he_nobias", sizes=[5, 6, 7, 8], algos=["tanh", "relu", "sigmoid"],
          optimizer="adam", weight_algo="he", bias="", confidence=1.0, seed=3),
 ]
+
+
+# Stacks with embedding / flatten / batchnorm entries: the remaining rows of
+# the reference's test_train table (test_neural_net_model.py:180-185), the model of
+# test_torch_backward.py:121-135, and batchnorm-only MLPs.  `tokens` = indices per sample.
+def _n(name, sizes, algos, optimizer, bias, batch, salt, tokens=0, steps=3, lr=0.01, decay=0.9, l2=0.001, **kw):
+    d = dict(name=name, sizes=sizes, algos=algos, optimizer=optimizer, bias=bias, batch=batch, salt=salt,
+             tokens=tokens, steps=steps, lr=lr, decay=decay, l2=l2)
+    d.update(kw)
+    return d
+
+
+NET_CASES = [
+    _n("bn_tanh_softmax", [12, 16, 7], ["linear", "batchnorm", "tanh", "softmax"], "adam", "random", 9, 31),
+    _n("bn_relu_bn_sig_mse", [10, 14, 9, 5], ["linear", "batchnorm", "relu", "linear", "batchnorm", "sigmoid", "linear"],
+       None, "zeros", 11, 32),
+    _n("emb_tanh_softmax", [9, 2, 6, 18, 9], ["embedding", "tanh", "softmax"], "adam", "zeros", 8, 33, tokens=3),
+    _n("emb_lin_bn_tanh_softmax", [9, 2, 6, 18, 9], ["embedding", "linear", "batchnorm", "tanh", "softmax"], None,
+       "random", 10, 34, tokens=3),
+    _n("emb_hier_flatten", [9, 2, 4, 9, 18, 9],
+       ["embedding", "linear", "batchnorm", "tanh", "flatten", "linear", "softmax"], None, "zeros", 6, 35, tokens=4),
+    _n("makemore_bn", [27, 10, 30, 64, 27], ["embedding", "linear", "batchnorm", "tanh", "linear", "softmax"], "adam",
+       "random", 32, 36, tokens=3, steps=2),
+    _n("emb_dropout", [9, 4, 12, 10, 9], ["embedding", "linear", "batchnorm", "relu", "softmax"], None, "random", 12,
+       37, tokens=3, dropout=0.25),
+]

@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, "/root/reference")
 
 from oracle.detgen import det_labels, det_normalish, det_params, det_uniform  # noqa: E402
-from oracle.golden_cases import STEP_CASES, TRAIN_API_CASES, INIT_CASES  # noqa: E402
+from oracle.golden_cases import STEP_CASES, TRAIN_API_CASES, INIT_CASES, NET_CASES  # noqa: E402
 
 import neural_net_model as ref  # noqa: E402  (the reference, unmodified)
 
@@ -230,6 +230,121 @@ def run_init_case(case):
     return arrays, meta
 
 
+def net_params(m, salt):
+    """Deterministic float32-exact parameters for every entry of a reference model, in `params` order."""
+    out = []
+    for k, layer in enumerate(m.layers):
+        if layer.algo == "embedding":
+            out.append(det_uniform(tuple(layer.weights.shape), salt * 97 + k))
+        elif layer.algo == "linear":
+            fan_in = layer.weights.shape[0]
+            out.append((det_uniform(tuple(layer.weights.shape), salt * 97 + k) * np.sqrt(3.0 / fan_in))
+                       .astype(np.float32).astype(np.float64))
+            if layer.bias is not None:
+                out.append(det_uniform(tuple(layer.bias.shape), salt * 97 + 50 + k) * 0.1)
+        elif layer.algo == "batchnorm":
+            out.append(1.0 + det_uniform(tuple(layer.gain.shape), salt * 97 + k) * 0.25)
+            out.append(det_uniform(tuple(layer.bias.shape), salt * 97 + 50 + k) * 0.1)
+    return [np.asarray(a, dtype=np.float32).astype(np.float64) for a in out]
+
+
+def run_net_case(case):
+    """Stacks with embedding / flatten / batchnorm entries, driven through the reference's own methods."""
+    m = ref.NeuralNetworkModel("golden", case["sizes"], "xavier", case["bias"], case["algos"], case["optimizer"])
+    params = net_params(m, case["salt"])
+    it = iter(params)
+    for layer in m.layers:
+        if layer.algo == "batchnorm":
+            layer.state_dict = {"params": [next(it).tolist(), next(it).tolist()], "eps": layer.eps,
+                                "momentum": layer.momentum}
+        elif layer.algo == "embedding":
+            layer.state_dict = {"params": [next(it).tolist()]}
+        elif layer.algo == "linear":
+            layer.state_dict = {"params": [next(it).tolist()] + ([next(it).tolist()] if layer.bias is not None else [])}
+    if case["optimizer"] == "adam":
+        m.optimizer = torch.optim.Adam(m.params)
+    algos = list(m.algos)
+    is_ce = algos[-1] == "softmax"
+    B = case["batch"]
+    if case["tokens"]:
+        x = det_labels(B * case["tokens"], case["sizes"][0], case["salt"] + 3).reshape(B, case["tokens"]).astype(np.float64)
+    else:
+        x = det_normalish((B, case["sizes"][0]), case["salt"] + 3)
+    n_out = case["sizes"][-1]
+    target = ([[int(v)] for v in det_labels(B, n_out, case["salt"] + 7)] if is_ce
+              else det_uniform((B, n_out), case["salt"] + 9, 0.0, 1.0).tolist())
+    xt = torch.tensor(x, dtype=torch.float64)
+    p = case.get("dropout", 0.0)
+    arrays, costs = {}, []
+    for step in range(case["steps"]):
+        lr_t = case["lr"] * (case["decay"] ** step)
+        if m.optimizer is not None:
+            for g in m.optimizer.param_groups:
+                g["lr"] = lr_t
+        for q in m.params:
+            q.requires_grad_()
+        rec = None
+        if p > 0.0:
+            rec = MaskRecorder()
+            saved = torch.nn.functional.dropout
+            torch.nn.functional.dropout = rec
+            try:
+                torch.manual_seed(4321 + step)
+                acts, cost = m._forward(xt, target, p)
+            finally:
+                torch.nn.functional.dropout = saved
+        else:
+            acts, cost = m._forward(xt, target, p)
+        if case["l2"] > 0.0:
+            cost = cost + case["l2"] * sum((w ** 2).sum() for w in m.weights)
+        for q in m.params:
+            q.grad = None
+        for a in acts:
+            a.retain_grad()
+        cost.backward()
+        if step == 0:
+            for i, a in enumerate(acts):
+                arrays[f"act{i}"] = a.detach().numpy().copy()
+                if a.grad is not None:
+                    arrays[f"actgrad{i}"] = a.grad.numpy().copy()
+            for i, q in enumerate(m.params):
+                arrays[f"grad{i}"] = q.grad.numpy().copy()
+        if rec is not None:
+            hidden_idx = [i for i, l in enumerate(m.layers) if l.hidden]
+            assert len(hidden_idx) == len(rec.masks)
+            for i, mk in zip(hidden_idx, rec.masks):
+                arrays[f"mask{i}_s{step}"] = mk.numpy().astype(np.uint8)
+        if m.optimizer is not None:
+            m.optimizer.step()
+        else:
+            for q in m.params:
+                q.data -= lr_t * q.grad
+        costs.append(cost.item())
+    arrays["costs"] = np.asarray(costs)
+    for i, q in enumerate(m.params):
+        arrays[f"param{i}"] = q.detach().numpy().copy()
+    for i, layer in enumerate(m.layers):
+        if layer.algo == "batchnorm":
+            arrays[f"bn_mean{i}"] = layer.mean.detach().numpy().reshape(-1).copy()
+            arrays[f"bn_var{i}"] = layer.variance.detach().numpy().reshape(-1).copy()
+    if m.optimizer is not None:
+        sd = m.optimizer.state_dict()["state"]
+        for i in sorted(sd):
+            arrays[f"adam_m{i}"] = sd[i]["exp_avg"].numpy().copy()
+            arrays[f"adam_v{i}"] = sd[i]["exp_avg_sq"].numpy().copy()
+    # inference on the updated model: without a target batchnorm uses its running statistics (:167-168)
+    out, c = m.compute_output(x.tolist(), None)
+    arrays["infer_out"] = np.asarray(out)
+    out1, _ = m.compute_output(x[0].tolist(), None)
+    arrays["infer_out_1d"] = np.asarray(out1)
+    meta = dict(case)
+    meta["expanded_algos"] = algos
+    meta["hidden"] = [bool(l.hidden) for l in m.layers]
+    meta["flatten_ratios"] = [getattr(l, "ratio", 0) for l in m.layers]
+    meta["num_params"] = m.num_params
+    return arrays, meta
+
+
 def save(name, arrays, meta):
     path = os.path.join(OUT, name + ".npz")
     np.savez_compressed(path, __meta__=np.asarray(json.dumps(meta)), **arrays)
@@ -250,6 +365,9 @@ def main():
                 save("train_" + case["name"], arrays, meta)
         finally:
             os.chdir(cwd)
+    for case in NET_CASES:
+        arrays, meta = run_net_case(case)
+        save("net_" + case["name"], arrays, meta)
     for case in INIT_CASES:
         arrays, meta = run_init_case(case)
         save("init_" + case["name"], arrays, meta)

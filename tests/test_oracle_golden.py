@@ -104,3 +104,91 @@ def test_torch_cpu_port_matches_reference(name):
     np.testing.assert_allclose(costs, arrays["costs"], rtol=RTOL, atol=ATOL)
     for i, q in enumerate(m.params):
         check_against(arrays, f"param{i}", q.detach().numpy(), 1e-9, 1e-12)
+
+
+# ---- general per-entry oracle (embedding / flatten / batchnorm stacks) ------------------------------
+def net_case_inputs(meta):
+    from oracle import net_oracle as no
+    algos = meta["expanded_algos"]
+    entries = no.build_entries(meta["sizes"], algos, has_bias=bool(meta["bias"]))
+    B = meta["batch"]
+    if meta["tokens"]:
+        x = det_labels(B * meta["tokens"], meta["sizes"][0], meta["salt"] + 3).reshape(B, meta["tokens"]).astype(np.float64)
+    else:
+        x = det_normalish((B, meta["sizes"][0]), meta["salt"] + 3)
+    n_out = meta["sizes"][-1]
+    if algos[-1] == "softmax":
+        target = [[int(v)] for v in det_labels(B, n_out, meta["salt"] + 7)]
+    else:
+        target = det_uniform((B, n_out), meta["salt"] + 9, 0.0, 1.0).tolist()
+    return entries, x, target
+
+
+def net_det_params(entries, salt):
+    """Same construction as oracle/make_golden.py:net_params."""
+    out = []
+    for k, e in enumerate(entries):
+        if e.algo == "embedding":
+            out.append(det_uniform(e.weights.shape, salt * 97 + k))
+        elif e.algo == "linear":
+            out.append((det_uniform(e.weights.shape, salt * 97 + k) * np.sqrt(3.0 / e.weights.shape[0]))
+                       .astype(np.float32).astype(np.float64))
+            if e.bias is not None:
+                out.append(det_uniform(e.bias.shape, salt * 97 + 50 + k) * 0.1)
+        elif e.algo == "batchnorm":
+            out.append(1.0 + det_uniform(e.gain.shape, salt * 97 + k) * 0.25)
+            out.append(det_uniform(e.bn_bias.shape, salt * 97 + 50 + k) * 0.1)
+    return [np.asarray(a, dtype=np.float32).astype(np.float64) for a in out]
+
+
+@pytest.mark.parametrize("name", golden_names("net_"))
+def test_net_oracle_matches_reference(name):
+    from oracle import net_oracle as no
+    arrays, meta = load_golden(name)
+    algos = meta["algos"]
+    assert no.expand_algos(algos) == meta["expanded_algos"]
+    entries, x, target = net_case_inputs(meta)
+    assert [e.hidden for e in entries] == meta["hidden"]
+    assert [e.ratio if e.algo == "flatten" else 0 for e in entries] == [r or 0 for r in meta["flatten_ratios"]]
+    params = net_det_params(entries, meta["salt"])
+    no.set_params(entries, params)
+    assert sum(p.size for p in no.get_params(entries)) == meta["num_params"]
+    p = meta.get("dropout", 0.0)
+    adam = orc.AdamState()
+    costs = []
+    for step in range(meta["steps"]):
+        masks = None
+        if p > 0:
+            masks = {int(k[4:].split("_")[0]): v.astype(np.float64) for k, v in arrays.items()
+                     if k.startswith("mask") and k.endswith(f"_s{step}")}
+        outs, into_last, tape = no.forward(entries, x, training=True, dropout_rate=p, masks=masks)
+        cost = no.loss_value(entries, outs, into_last, target) + no.l2_penalty(entries, meta["l2"])
+        grads, out_grads = no.backward(entries, outs, into_last, tape, target, dropout_rate=p, masks=masks,
+                                       l2_lambda=meta["l2"])
+        if step == 0:
+            for i, o in enumerate(outs):
+                check_against(arrays, f"act{i}", o, RTOL, ATOL)
+            for i, g in enumerate(out_grads):
+                assert (f"actgrad{i}" in arrays) == (g is not None), f"actgrad{i}"
+                if g is not None:
+                    check_against(arrays, f"actgrad{i}", g, 1e-10, 1e-13)
+            for i, g in enumerate(grads):
+                check_against(arrays, f"grad{i}", g, 1e-10, 1e-13)
+        lr_t = meta["lr"] * meta["decay"] ** step
+        cur = no.get_params(entries)
+        new = (orc.adam_update(cur, grads, adam, lr_t) if meta["optimizer"] == "adam" else orc.sgd_update(cur, grads, lr_t))
+        no.set_params(entries, new)
+        costs.append(cost)
+    np.testing.assert_allclose(costs, arrays["costs"], rtol=1e-10)
+    for i, q in enumerate(no.get_params(entries)):
+        check_against(arrays, f"param{i}", q, 1e-8, 1e-9)
+    for i, e in enumerate(entries):
+        if e.algo == "batchnorm":
+            # the bias in front of a batchnorm has a mathematically zero gradient; Adam turns its
+            # round-off noise into ~1e-11 drifts of that bias, which the running mean follows
+            np.testing.assert_allclose(e.mean.reshape(-1), arrays[f"bn_mean{i}"], rtol=1e-9, atol=1e-9)
+            np.testing.assert_allclose(e.variance.reshape(-1), arrays[f"bn_var{i}"], rtol=1e-10, atol=1e-13)
+    outs, _, _ = no.forward(entries, x, training=False)
+    check_against(arrays, "infer_out", outs[-1], 1e-9, 1e-12)
+    outs1, _, _ = no.forward(entries, x[0], training=False)
+    check_against(arrays, "infer_out_1d", outs1[-1], 1e-9, 1e-12)

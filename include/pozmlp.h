@@ -72,6 +72,35 @@ int poz_profile_end(poz_ctx* ctx, char* json_out, long long cap);
 int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_codes,
                    const unsigned char* drop_z, const unsigned char* drop_a,
                    int has_bias, int loss_code, int dtype_code, poz_ctx** out);
+/* General stacks: an optional EmbeddingLayer head
+ * (neural_net_model.py:55-68), FlattenLayer entries (:70-91, a pure reinterpretation of the rows),
+ * and an optional BatchNormLayer (:122-170) between a Linear and its activation.
+ * row_mult: rows of the layer's input and output = batch * row_mult (flatten entries merge `ratio`
+ * rows into one); the last layer must have row_mult 1.  drop_*: how many dropout applications
+ * (hidden entries, including the flatten entries folded into the tensor) hit the recorded tensor.
+ * With an embedding head x_dev of every entry point is int32 indices [batch][tokens]. */
+typedef struct poz_layer_desc {
+    int    in, out;              /* Linear in -> out */
+    int    act;                  /* POZ_ACT_* */
+    int    has_bn;
+    double bn_eps, bn_momentum;
+    int    drop_z, drop_bn, drop_a;
+    int    row_mult;
+} poz_layer_desc;
+typedef struct poz_stack_desc {
+    int n_linear;
+    const poz_layer_desc* layers;
+    int has_bias, loss_code, dtype_code;
+    int emb_vocab, emb_dim;      /* 0, 0 = no embedding head */
+    int emb_drop;                /* dropout applications on the (flattened) embedding output */
+    int tokens;                  /* indices per sample; rows of the embedding output = batch * tokens */
+} poz_stack_desc;
+int poz_ctx_create_ex(int device, const poz_stack_desc* desc, poz_ctx** out);
+/* Upload (download = 0) or download (1) one tensor as a float64 host image.
+ * kind: 0 Linear weights, 1 Linear bias, 2 embedding table, 3 batchnorm gain, 4 batchnorm bias,
+ *       5 batchnorm running mean, 6 batchnorm running variance (kinds 5-6: buffer 0 only).
+ * buffer: 0 value, 1 Adam exp_avg, 2 Adam exp_avg_sq, 3 gradient of the last diagnostics step (download). */
+int poz_tensor_io(poz_ctx* ctx, int kind, int layer, int buffer, int download, double* host);
 int poz_ctx_destroy(poz_ctx* ctx);
 /* Grow the workspace for batches of up to max_batch rows (otherwise grown on demand). */
 int poz_ctx_reserve(poz_ctx* ctx, long long max_batch, int for_training);
@@ -119,7 +148,8 @@ int poz_train_update_ratios(poz_ctx* ctx, long long first_record, long long coun
 
 /* Diagnostics of the last step run with diagnostics != 0 (feeds the unchanged
  * _record_training_overall_progress, neural_net_model.py:532-583).  `entry` counts the
- * reference's layer list: for linear l, which = 0 is the Linear entry, which = 1 its activation. */
+ * reference's layer list: for linear l, which = 0 is the Linear entry, which = 1 its activation,
+ * which = 2 its batchnorm; layer = -1 is the embedding head (and the flatten entries after it). */
 int poz_diag_activation(poz_ctx* ctx, int layer, int which, double* host_out);
 int poz_diag_activation_grad(poz_ctx* ctx, int layer, int which, double* host_out, int* has_grad);
 int poz_diag_weight_grad(poz_ctx* ctx, int layer, double* w_grad, double* b_grad);

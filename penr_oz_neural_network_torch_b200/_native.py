@@ -29,6 +29,18 @@ class PozError(RuntimeError):
     """A C-ABI call returned non-zero; the message is poz_last_error()."""
 
 
+class LayerDesc(C.Structure):
+    _fields_ = [("in_", C.c_int), ("out", C.c_int), ("act", C.c_int), ("has_bn", C.c_int),
+                ("bn_eps", C.c_double), ("bn_momentum", C.c_double),
+                ("drop_z", C.c_int), ("drop_bn", C.c_int), ("drop_a", C.c_int), ("row_mult", C.c_int)]
+
+
+class StackDesc(C.Structure):
+    _fields_ = [("n_linear", C.c_int), ("layers", C.POINTER(LayerDesc)),
+                ("has_bias", C.c_int), ("loss_code", C.c_int), ("dtype_code", C.c_int),
+                ("emb_vocab", C.c_int), ("emb_dim", C.c_int), ("emb_drop", C.c_int), ("tokens", C.c_int)]
+
+
 class TrainConfig(C.Structure):
     _fields_ = [
         ("optimizer", C.c_int),
@@ -89,6 +101,8 @@ SIGNATURES = {
     "poz_profile_end": (_I, [_VP, C.c_char_p, _LL]),
     "poz_ctx_create": (_I, [_I, _I, C.POINTER(_I), C.POINTER(_I), C.POINTER(C.c_ubyte),
                             C.POINTER(C.c_ubyte), _I, _I, _I, C.POINTER(_VP)]),
+    "poz_ctx_create_ex": (_I, [_I, C.POINTER(StackDesc), C.POINTER(_VP)]),
+    "poz_tensor_io": (_I, [_VP, _I, _I, _I, _I, _VP]),
     "poz_ctx_destroy": (_I, [_VP]),
     "poz_ctx_reserve": (_I, [_VP, _LL, _I]),
     "poz_params_upload": (_I, [_VP, _I, _VP, _VP]),

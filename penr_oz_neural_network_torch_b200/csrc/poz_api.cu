@@ -2,6 +2,7 @@
 #include "../../include/pozmlp.h"
 #include "poz_ctx.h"
 #include "poz_kernels.cuh"
+#include "poz_net_kernels.cuh"
 #include "poz_simt_gemm.cuh"
 #include "poz_simt_fast.cuh"
 #include "poz_tc.h"
@@ -516,9 +517,14 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
 // Rows are processed in chunks small enough that the intermediate activations of a chunk stay in
 // the 126 MB L2 between the per-layer kernels instead of round-tripping through HBM.
 template <typename T>
+static int forward_general_dispatch(poz_ctx* c, const void* x, const void* target, long long batch, T* out,
+                                    double* cost_host, cudaStream_t stream);
+
+template <typename T>
 static int forward_impl(poz_ctx* c, const T* x, const void* target, long long batch, T* out,
                         double* cost_host, cudaStream_t stream) {
     const int nl = c->nl;
+    if (c->general) return forward_general_dispatch<T>(c, x, target, batch, out, cost_host, stream);
     if constexpr (std::is_same<T, float>::value) {
         // big batches of a deep-enough stack: every layer on the tensor cores
         if (batch >= c->tc3_min_batch && tc3_stack_ok(c)) return forward_tc3(c, x, target, batch, out, cost_host, stream);
@@ -602,14 +608,41 @@ static void plan_splits(poz_ctx* c, long long batch, SegTable& seg, std::vector<
     }
 }
 
+static int n_stat_slots(const poz_ctx* c) { return c->nl + (c->emb_vocab > 0 ? 1 : 0); }
+
 static void fill_seg(const poz_ctx* c, SegTable& seg) {
+    const int e = c->emb_vocab > 0 ? 1 : 0;
     seg.n = c->nl;
-    for (int l = 0; l <= c->nl; ++l) seg.off[l] = c->off[l];
+    seg.n_stat = n_stat_slots(c);
     for (int l = 0; l < c->nl; ++l) {
-        seg.w_elems[l] = (long long)c->sizes[l] * c->sizes[l + 1];
-        seg.n_elems[l] = ((long long)c->sizes[l] + c->has_bias) * c->sizes[l + 1];
+        seg.off[l] = c->off[l];
+        seg.w_elems[l] = (long long)c->kin[l] * c->sizes[l + 1];
+        seg.n_elems[l] = ((long long)c->kin[l] + c->has_bias) * c->sizes[l + 1];
         seg.splits[l] = 1;
+        seg.stat_slot[l] = e + l;
     }
+    if (e) {
+        const int k = seg.n++;
+        seg.off[k] = c->off_emb;
+        seg.n_elems[k] = seg.w_elems[k] = (long long)c->emb_vocab * c->emb_dim;
+        seg.splits[k] = 1;
+        seg.stat_slot[k] = 0;
+    }
+    for (int l = 0; l < c->nl; ++l)
+        if (!c->has_bn.empty() && c->has_bn[l]) {
+            const int k = seg.n++;
+            seg.off[k] = c->off_bn[l];
+            seg.n_elems[k] = 2LL * c->sizes[l + 1];
+            seg.w_elems[k] = 0;
+            seg.splits[k] = 1;
+            seg.stat_slot[k] = -1;
+        }
+}
+
+static long long biggest_seg(const SegTable& seg) {
+    long long b = 0;
+    for (int k = 0; k < seg.n; ++k) b = std::max(b, seg.n_elems[k]);
+    return b;
 }
 
 template <typename T>
@@ -664,7 +697,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     {
         ProfScope ps(c, "step_begin", stream);
         const double share = c->cfg.global_batch > 0 ? (double)batch / (double)c->cfg.global_batch : 1.0;
-        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, nl, share);
+        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, n_stat_slots(c), share);
         POZ_LAUNCH_CHECK();
     }
 
@@ -907,7 +940,7 @@ static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target,
     {
         ProfScope ps(c, "step_begin", stream);
         const double share = c->cfg.global_batch > 0 ? (double)batch / (double)c->cfg.global_batch : 1.0;
-        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, nl, share);
+        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, n_stat_slots(c), share);
         POZ_LAUNCH_CHECK();
     }
     float* P = static_cast<float*>(c->P);
@@ -967,14 +1000,21 @@ static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target,
     return 0;
 }
 
+#include "poz_general.inc"
+
+template <typename T>
+static int forward_general_dispatch(poz_ctx* c, const void* x, const void* target, long long batch, T* out,
+                                    double* cost_host, cudaStream_t stream) {
+    return forward_general<T>(c, x, target, batch, out, cost_host, stream);
+}
+
 template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream_t stream) {
     if (!c->grads_pending) POZ_FAIL("poz_train_apply: no gradients pending");
     SegTable seg;
     fill_seg(c, seg);
     if (!reduced)
         for (int l = 0; l < c->nl; ++l) seg.splits[l] = c->seg_splits[l];
-    long long biggest = 0;
-    for (int l = 0; l < c->nl; ++l) biggest = std::max(biggest, seg.off[l + 1] - seg.off[l]);
+    const long long biggest = biggest_seg(seg);
     int bx = (int)std::min<long long>((biggest + 255) / 256, 2LL * num_sms(c->device));
     T* gdiag = nullptr;
     if (c->diag_pending) {
@@ -983,7 +1023,7 @@ template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream
         c->have_diag = true;
     }
     ProfScope ps(c, "update", stream);
-    update_kernel<T><<<dim3(std::max(bx, 1), c->nl), 256, 0, stream>>>(
+    update_kernel<T><<<dim3(std::max(bx, 1), seg.n), 256, 0, stream>>>(
         static_cast<T*>(c->P), static_cast<T*>(c->AM), static_cast<T*>(c->AV),
         static_cast<const T*>(c->G), c->p_total, gdiag, seg, c->st, c->cost_ring, c->cost_cap, c->stats,
         static_cast<__nv_bfloat16*>(c->Pb));
@@ -1000,11 +1040,10 @@ template <typename T> static int finalize_impl(poz_ctx* c, cudaStream_t stream) 
     bool any = false;
     for (int l = 0; l < c->nl; ++l) { seg.splits[l] = c->seg_splits[l]; any |= seg.splits[l] > 1; }
     if (!any) return 0;
-    long long biggest = 0;
-    for (int l = 0; l < c->nl; ++l) biggest = std::max(biggest, seg.off[l + 1] - seg.off[l]);
+    const long long biggest = biggest_seg(seg);
     int bx = (int)std::min<long long>((biggest + 255) / 256, 2LL * num_sms(c->device));
     ProfScope ps(c, "grad_finalize", stream);
-    grad_finalize_kernel<T><<<dim3(std::max(bx, 1), c->nl), 256, 0, stream>>>(static_cast<T*>(c->G), c->p_total, seg);
+    grad_finalize_kernel<T><<<dim3(std::max(bx, 1), seg.n), 256, 0, stream>>>(static_cast<T*>(c->G), c->p_total, seg);
     POZ_LAUNCH_CHECK();
     return 0;
 }
@@ -1018,14 +1057,14 @@ static int check_layer(poz_ctx* c, int layer, const char* who) {
 
 template <typename T>
 static int put_layer(poz_ctx* c, void* base, int layer, const double* w, const double* b) {
-    long long nw = (long long)c->sizes[layer] * c->sizes[layer + 1];
+    long long nw = (long long)c->kin[layer] * c->sizes[layer + 1];
     if (w) POZ_TRY(put_f64<T>(c, base, c->off[layer], w, nw));
     if (b && c->has_bias) POZ_TRY(put_f64<T>(c, base, c->off[layer] + nw, b, c->sizes[layer + 1]));
     return 0;
 }
 template <typename T>
 static int get_layer(poz_ctx* c, const void* base, int layer, double* w, double* b) {
-    long long nw = (long long)c->sizes[layer] * c->sizes[layer + 1];
+    long long nw = (long long)c->kin[layer] * c->sizes[layer + 1];
     if (w) POZ_TRY(get_f64<T>(c, base, c->off[layer], w, nw));
     if (b && c->has_bias) POZ_TRY(get_f64<T>(c, base, c->off[layer] + nw, b, c->sizes[layer + 1]));
     return 0;
@@ -1042,28 +1081,43 @@ const char* poz_last_error(void) { return t_error.c_str(); }
 int poz_version(void) { return 100; }
 long long poz_launch_count(void) { return s_launches.load(); }
 
-int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_codes,
-                   const unsigned char* drop_z, const unsigned char* drop_a, int has_bias,
-                   int loss_code, int dtype_code, poz_ctx** out) {
+int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
     if (!out) POZ_FAIL("poz_ctx_create: out is NULL");
     *out = nullptr;
+    if (!d || !d->layers) POZ_FAIL("poz_ctx_create: NULL stack description");
+    const int n_linear = d->n_linear, dtype_code = d->dtype_code, loss_code = d->loss_code;
     if (n_linear < 1 || n_linear > MAX_LAYERS) POZ_FAIL("poz_ctx_create: n_linear must be in [1,16]");
     if (dtype_code != POZ_DTYPE_F32 && dtype_code != POZ_DTYPE_F64 && dtype_code != POZ_DTYPE_BF16)
         POZ_FAIL("poz_ctx_create: unknown dtype code");
+    const bool has_emb = d->emb_vocab > 0 || d->emb_dim > 0;
+    bool general = has_emb;
+    for (int l = 0; l < n_linear; ++l) {
+        const poz_layer_desc& L = d->layers[l];
+        if (L.in < 1 || L.out < 1) POZ_FAIL("poz_ctx_create: layer sizes must be positive");
+        if (l > 0 && L.in * (long long)L.row_mult != d->layers[l - 1].out * (long long)d->layers[l - 1].row_mult)
+            POZ_FAIL("poz_ctx_create: layer input does not match the (flattened) output of the previous layer");
+        if (L.act < 0 || L.act > ACT_SOFTMAX) POZ_FAIL("poz_ctx_create: bad activation code");
+        if (L.act == ACT_SOFTMAX && l != n_linear - 1) POZ_FAIL("poz_ctx_create: softmax is supported as the last activation only");
+        if (L.row_mult < 1) POZ_FAIL("poz_ctx_create: row_mult must be >= 1");
+        if (L.has_bn && l == n_linear - 1) POZ_FAIL("poz_ctx_create: batchnorm on the last layer is not supported");
+        if (L.has_bn || L.row_mult != 1) general = true;
+    }
+    if (d->layers[n_linear - 1].row_mult != 1) POZ_FAIL("poz_ctx_create: the last layer must produce one row per sample");
+    if (has_emb) {
+        if (d->emb_vocab < 1 || d->emb_dim < 1 || d->tokens < 1) POZ_FAIL("poz_ctx_create: bad embedding description");
+        if ((long long)d->emb_dim * d->tokens != (long long)d->layers[0].in * d->layers[0].row_mult)
+            POZ_FAIL("poz_ctx_create: first layer input does not match the flattened embedding output");
+    }
+    if (general && dtype_code == POZ_DTYPE_BF16)
+        POZ_FAIL("poz_ctx_create: embedding / flatten / batchnorm stacks need a float32 or float64 context");
     if (dtype_code == POZ_DTYPE_BF16) {
         // the tcgen05 path: dense layers only (TMA needs 16-byte rows), MSE stacks
-        for (int l = 0; l <= n_linear; ++l)
-            if (sizes[l] % 8) POZ_FAIL("poz_ctx_create: POZ_DTYPE_BF16 needs every layer size to be a multiple of 8");
+        for (int l = 0; l < n_linear; ++l)
+            if (d->layers[l].in % 8 || d->layers[l].out % 8)
+                POZ_FAIL("poz_ctx_create: POZ_DTYPE_BF16 needs every layer size to be a multiple of 8");
         if (loss_code != POZ_LOSS_MSE) POZ_FAIL("poz_ctx_create: POZ_DTYPE_BF16 supports MSE stacks (no trailing softmax)");
     }
-    for (int l = 0; l <= n_linear; ++l)
-        if (sizes[l] < 1) POZ_FAIL("poz_ctx_create: layer sizes must be positive");
-    for (int l = 0; l < n_linear; ++l) {
-        if (act_codes[l] < 0 || act_codes[l] > ACT_SOFTMAX) POZ_FAIL("poz_ctx_create: bad activation code");
-        if (act_codes[l] == ACT_SOFTMAX && l != n_linear - 1)
-            POZ_FAIL("poz_ctx_create: softmax is supported as the last activation only");
-    }
-    if ((loss_code == POZ_LOSS_CE) != (act_codes[n_linear - 1] == ACT_SOFTMAX))
+    if ((loss_code == POZ_LOSS_CE) != (d->layers[n_linear - 1].act == ACT_SOFTMAX))
         POZ_FAIL("poz_ctx_create: cross-entropy loss goes with a trailing softmax (neural_net_model.py:400)");
     int ndev = 0;
     POZ_CUDA(cudaGetDeviceCount(&ndev));
@@ -1071,25 +1125,50 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     POZ_CUDA(cudaSetDevice(device));
 
     poz_ctx* c = new poz_ctx();
-    c->device = device; c->nl = n_linear; c->has_bias = has_bias ? 1 : 0;
+    c->device = device; c->nl = n_linear; c->has_bias = d->has_bias ? 1 : 0;
     c->loss = loss_code; c->dtype = dtype_code;
     c->esz = dtype_code == POZ_DTYPE_F64 ? 8 : 4;
     c->act_esz = dtype_code == POZ_DTYPE_BF16 ? 2 : c->esz;
-    c->sizes.assign(sizes, sizes + n_linear + 1);
-    c->acts.assign(act_codes, act_codes + n_linear);
+    c->general = general;
+    c->sizes.assign(n_linear + 1, 0);
+    c->acts.assign(n_linear, 0);
     c->drop_z.assign(n_linear, 0); c->drop_a.assign(n_linear, 0);
-    if (drop_z) c->drop_z.assign(drop_z, drop_z + n_linear);
-    if (drop_a) c->drop_a.assign(drop_a, drop_a + n_linear);
+    c->rmul.assign(n_linear, 1); c->has_bn.assign(n_linear, 0);
+    c->kz.assign(n_linear, 0); c->kbn.assign(n_linear, 0); c->ka.assign(n_linear, 0);
+    c->bn_eps.assign(n_linear, 1e-5); c->bn_mom.assign(n_linear, 0.1);
+    c->off_bn.assign(n_linear, -1);
+    c->sizes[0] = d->layers[0].in;
+    c->kin.assign(n_linear, 0);
+    for (int l = 0; l < n_linear; ++l) {
+        const poz_layer_desc& L = d->layers[l];
+        c->sizes[l + 1] = L.out;
+        c->kin[l] = L.in;
+        c->acts[l] = L.act;
+        c->kz[l] = L.drop_z; c->kbn[l] = L.drop_bn; c->ka[l] = L.drop_a;
+        c->drop_z[l] = L.drop_z > 0; c->drop_a[l] = L.drop_a > 0;
+        c->rmul[l] = L.row_mult; c->has_bn[l] = L.has_bn ? 1 : 0;
+        c->bn_eps[l] = L.bn_eps; c->bn_mom[l] = L.bn_momentum;
+    }
+    c->emb_vocab = has_emb ? d->emb_vocab : 0; c->emb_dim = has_emb ? d->emb_dim : 0;
+    c->emb_drop = d->emb_drop; c->tokens = has_emb ? d->tokens : 1;
+    // flat parameter layout in the reference's `params` order: embedding table, then per Linear
+    // layer [W; b] followed by its batchnorm [gain; bias]; every image 16-byte aligned
+    auto pad4 = [](long long n) { return (n + 3) & ~3LL; };
+    long long cursor = 0;
+    if (has_emb) { c->off_emb = 0; cursor = pad4((long long)c->emb_vocab * c->emb_dim); }
     c->off.assign(n_linear + 1, 0);
     for (int l = 0; l < n_linear; ++l) {
-        long long n = ((long long)sizes[l] + c->has_bias) * sizes[l + 1];
-        n = (n + 3) & ~3LL;   // keep every layer image 16-byte aligned in the flat buffers
-        c->off[l + 1] = c->off[l] + n;
+        c->off[l] = cursor;
+        cursor += pad4(((long long)c->kin[l] + c->has_bias) * c->sizes[l + 1]);
+        if (c->has_bn[l]) { c->off_bn[l] = cursor; cursor += pad4(2LL * c->sizes[l + 1]); }
     }
-    c->p_total = c->off[n_linear];
+    c->off[n_linear] = cursor;
+    c->p_total = cursor;
     c->zbuf.assign(n_linear, nullptr); c->abuf.assign(n_linear, nullptr);
     c->dzbuf.assign(n_linear, nullptr); c->dz_rec.assign(n_linear, nullptr);
     c->da_rec.assign(n_linear, nullptr);
+    c->bn_run.assign(n_linear, nullptr); c->bn_stat.assign(n_linear, nullptr); c->bn_sums.assign(n_linear, nullptr);
+    c->ybuf.assign(n_linear, nullptr); c->dybuf.assign(n_linear, nullptr); c->dy_rec.assign(n_linear, nullptr);
     c->max_splits = 16;
     if (const char* e = getenv("POZ_TC3_MIN_BATCH")) c->tc3_min_batch = atoll(e);
     if (const char* e = getenv("POZ_GRAPHS")) c->graphs_enabled = atoi(e) != 0;
@@ -1104,10 +1183,21 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     }
     if (cudaMemset(c->P, 0, pbytes) != cudaSuccess || cudaMemset(c->AM, 0, pbytes) != cudaSuccess ||
         cudaMemset(c->AV, 0, pbytes) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
+    for (int l = 0; l < n_linear; ++l)
+        if (c->has_bn[l]) {
+            const size_t nb = (size_t)2 * c->sizes[l + 1] * c->esz;
+            if (dev_alloc(&c->bn_run[l], nb) || dev_alloc(&c->bn_stat[l], nb) || dev_alloc(&c->bn_sums[l], nb)) return fail();
+            if (cudaMemset(c->bn_run[l], 0, nb) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
+        }
     if (dev_alloc(reinterpret_cast<void**>(&c->st), sizeof(DevState))) return fail();
     if (cudaMemset(c->st, 0, sizeof(DevState)) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
     if (dev_alloc(reinterpret_cast<void**>(&c->scalar_cost), sizeof(double))) return fail();
     std::memset(&c->cfg, 0, sizeof(c->cfg));
+    for (int l = 0; l < n_linear; ++l)
+        if (c->has_bn[l]) {     // BatchNormLayer starts with gain 1, variance 1 (neural_net_model.py:128-131)
+            std::vector<double> ones(c->sizes[l + 1], 1.0);
+            if (poz_tensor_io(c, 3, l, 0, 0, ones.data()) || poz_tensor_io(c, 6, l, 0, 0, ones.data())) return fail();
+        }
     c->grad_ready.assign(n_linear, nullptr);
     for (int l = 0; l < n_linear; ++l)
         if (cudaEventCreateWithFlags(&c->grad_ready[l], cudaEventDisableTiming) != cudaSuccess) {
@@ -1118,6 +1208,27 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     return 0;
 }
 
+int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_codes,
+                   const unsigned char* drop_z, const unsigned char* drop_a, int has_bias,
+                   int loss_code, int dtype_code, poz_ctx** out) {
+    if (!out) POZ_FAIL("poz_ctx_create: out is NULL");
+    *out = nullptr;
+    if (n_linear < 1 || n_linear > MAX_LAYERS) POZ_FAIL("poz_ctx_create: n_linear must be in [1,16]");
+    if (!sizes || !act_codes) POZ_FAIL("poz_ctx_create: NULL argument");
+    std::vector<poz_layer_desc> L(n_linear);
+    for (int l = 0; l < n_linear; ++l) {
+        L[l] = poz_layer_desc{};
+        L[l].in = sizes[l]; L[l].out = sizes[l + 1]; L[l].act = act_codes[l];
+        L[l].drop_z = drop_z ? (drop_z[l] ? 1 : 0) : 0;
+        L[l].drop_a = drop_a ? (drop_a[l] ? 1 : 0) : 0;
+        L[l].row_mult = 1; L[l].bn_eps = 1e-5; L[l].bn_momentum = 0.1;
+    }
+    poz_stack_desc d{};
+    d.n_linear = n_linear; d.layers = L.data(); d.has_bias = has_bias; d.loss_code = loss_code; d.dtype_code = dtype_code;
+    d.tokens = 1;
+    return poz_ctx_create_ex(device, &d, out);
+}
+
 int poz_ctx_destroy(poz_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
@@ -1125,6 +1236,13 @@ int poz_ctx_destroy(poz_ctx* c) {
     clear_graphs(c);
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
+    for (auto& p : c->bn_run) dev_free(p);
+    for (auto& p : c->bn_stat) dev_free(p);
+    for (auto& p : c->bn_sums) dev_free(p);
+    for (auto& p : c->ybuf) dev_free(p);
+    for (auto& p : c->dybuf) dev_free(p);
+    for (auto& p : c->dy_rec) dev_free(p);
+    dev_free(c->ebuf); dev_free(c->debuf); dev_free(c->de_rec);
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
     dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
     dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz);
@@ -1215,6 +1333,25 @@ int poz_adam_download(poz_ctx* c, int layer, double* m_w, double* v_w, double* m
     POZ_TRY(POZ_DISPATCH(c, get_layer, c, c->AM, layer, m_w, m_b));
     return POZ_DISPATCH(c, get_layer, c, c->AV, layer, v_w, v_b);
 }
+int poz_tensor_io(poz_ctx* c, int kind, int layer, int buffer, int download, double* host) {
+    POZ_TRY(check_layer(c, 0, "poz_tensor_io"));
+    if (!host) POZ_FAIL("poz_tensor_io: NULL host buffer");
+    void* base; long long off, n;
+    POZ_TRY(tensor_locate(c, kind, layer, buffer, &base, &off, &n));
+    if (download) return POZ_DISPATCH(c, get_f64, c, base, off, host, n);
+    if (buffer == 3) POZ_FAIL("poz_tensor_io: the diagnostics gradient is read-only");
+    c->wp_stale = true;
+    POZ_TRY(POZ_DISPATCH(c, put_f64, c, base, off, host, n));
+    if (c->dtype == POZ_DTYPE_BF16 && buffer == 0 && kind <= 1) {
+        int blocks = (int)std::min<long long>((n + 255) / 256, 4096);
+        convert_kernel<float, __nv_bfloat16><<<blocks, 256>>>(static_cast<const float*>(c->P) + off,
+                                                              static_cast<__nv_bfloat16*>(c->Pb) + off, n);
+        POZ_LAUNCH_CHECK();
+        POZ_CUDA(cudaDeviceSynchronize());
+    }
+    return 0;
+}
+
 int poz_adam_set_step(poz_ctx* c, long long step) {
     POZ_TRY(check_layer(c, 0, "poz_adam_set_step"));
     POZ_CUDA(cudaDeviceSynchronize());
@@ -1275,7 +1412,7 @@ int poz_train_begin(poz_ctx* c, const poz_train_config* cfg) {
     long long recs = cfg->progress_stride > 0 ? (epochs + cfg->progress_stride - 1) / cfg->progress_stride + 1 : 1;
     if (recs > c->stats_cap) {
         dev_free(reinterpret_cast<void*&>(c->stats));
-        POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->stats), (size_t)recs * c->nl * 4 * sizeof(double)));
+        POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->stats), (size_t)recs * n_stat_slots(c) * 4 * sizeof(double)));
         c->stats_cap = recs;
     }
     DevState h;
@@ -1306,6 +1443,9 @@ int poz_train_backward(poz_ctx* c, const void* x_dev, const void* target_dev, co
     if (c->dtype == POZ_DTYPE_BF16)
         return backward_wide(c, static_cast<const __nv_bfloat16*>(x_dev), target_dev, row_idx_dev, batch, keep_masks,
                              diagnostics, s);
+    if (c->general)
+        return c->dtype == POZ_DTYPE_F64 ? backward_general<double>(c, x_dev, target_dev, row_idx_dev, batch, keep_masks, diagnostics, s)
+                                         : backward_general<float>(c, x_dev, target_dev, row_idx_dev, batch, keep_masks, diagnostics, s);
     if (c->dtype == POZ_DTYPE_F64) {
         POZ_TRY(backward_impl<double>(c, static_cast<const double*>(x_dev), target_dev, row_idx_dev, batch, keep_masks, diagnostics, s));
         return 0;
@@ -1395,7 +1535,7 @@ int poz_grad_layer(poz_ctx* c, int layer, void** dev_ptr, long long* n_elems, vo
     if (!c->grads_pending) POZ_FAIL("poz_grad_layer: run poz_train_backward first");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     POZ_CUDA(cudaStreamWaitEvent(s, c->grad_ready[layer], 0));
-    const long long n = ((long long)c->sizes[layer] + c->has_bias) * c->sizes[layer + 1];
+    const long long n = ((long long)c->kin[layer] + c->has_bias) * c->sizes[layer + 1];
     if (c->seg_splits[layer] > 1) {
         SegTable seg;
         fill_seg(c, seg);
@@ -1403,9 +1543,9 @@ int poz_grad_layer(poz_ctx* c, int layer, void** dev_ptr, long long* n_elems, vo
         int bx = (int)std::min<long long>((n + 255) / 256, 2LL * num_sms(c->device));
         ProfScope ps(c, "grad_finalize", s);
         if (c->dtype == POZ_DTYPE_F64)
-            grad_finalize_kernel<double><<<dim3(std::max(bx, 1), c->nl), 256, 0, s>>>(static_cast<double*>(c->G), c->p_total, seg);
+            grad_finalize_kernel<double><<<dim3(std::max(bx, 1), seg.n), 256, 0, s>>>(static_cast<double*>(c->G), c->p_total, seg);
         else
-            grad_finalize_kernel<float><<<dim3(std::max(bx, 1), c->nl), 256, 0, s>>>(static_cast<float*>(c->G), c->p_total, seg);
+            grad_finalize_kernel<float><<<dim3(std::max(bx, 1), seg.n), 256, 0, s>>>(static_cast<float*>(c->G), c->p_total, seg);
         POZ_LAUNCH_CHECK();
         c->seg_splits[layer] = 1;
     }
@@ -1432,81 +1572,95 @@ int poz_train_update_ratios(poz_ctx* c, long long first_record, long long count,
     if (first_record < 0 || count < 0 || first_record + count > c->stats_cap) POZ_FAIL("poz_train_update_ratios: range outside the record buffer");
     if (count == 0) return 0;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    std::vector<double> raw((size_t)count * c->nl * 4);
-    POZ_CUDA(cudaMemcpyAsync(raw.data(), c->stats + first_record * c->nl * 4, raw.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+    const int ns = n_stat_slots(c), e = c->emb_vocab > 0 ? 1 : 0;
+    std::vector<double> raw((size_t)count * ns * 4);
+    POZ_CUDA(cudaMemcpyAsync(raw.data(), c->stats + first_record * ns * 4, raw.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
     POZ_CUDA(cudaStreamSynchronize(s));
     for (long long r = 0; r < count; ++r)
-        for (int l = 0; l < c->nl; ++l) {
-            const double* q = &raw[(size_t)(r * c->nl + l) * 4];
-            const double n = (double)c->sizes[l] * c->sizes[l + 1];
+        for (int k = 0; k < ns; ++k) {
+            const double* q = &raw[(size_t)(r * ns + k) * 4];
+            const double n = (e && k == 0) ? (double)c->emb_vocab * c->emb_dim
+                                           : (double)c->kin[k - e] * c->sizes[k - e + 1];
             // unbiased std from sums (neural_net_model.py:506)
             double var_d = n > 1 ? (q[1] - q[0] * q[0] / n) / (n - 1) : NAN;
             double var_w = n > 1 ? (q[3] - q[2] * q[2] / n) / (n - 1) : NAN;
             double sd = std::sqrt(std::max(var_d, 0.0)), sw = std::sqrt(std::max(var_w, 0.0));
             if (n <= 1) { sd = NAN; sw = NAN; }
-            ratios_host[r * c->nl + l] = sd / (sw + 1e-8);
+            ratios_host[r * ns + k] = sd / (sw + 1e-8);
         }
     return 0;
 }
 
 static int diag_ready(poz_ctx* c, int layer, const char* who) {
-    POZ_TRY(check_layer(c, layer, who));
+    POZ_TRY(check_layer(c, layer < 0 ? 0 : layer, who));
     if (c->diag_batch <= 0) POZ_FAIL(std::string(who) + ": no step was run with diagnostics enabled");
     return 0;
 }
 
-int poz_diag_activation(poz_ctx* c, int layer, int which, double* host_out) {
-    POZ_TRY(diag_ready(c, layer, "poz_diag_activation"));
-    const int act = c->acts[layer];
-    const void* src = nullptr;
-    if (which == 0) src = act == ACT_NONE ? c->abuf[layer] : c->zbuf[layer];
-    else if (which == 1 && act != ACT_NONE) src = c->abuf[layer];
-    if (!src) POZ_FAIL("poz_diag_activation: no such entry");
-    long long n = c->diag_batch * c->sizes[layer + 1];
-    return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, n);
-}
-
-int poz_diag_activation_grad(poz_ctx* c, int layer, int which, double* host_out, int* has_grad) {
-    POZ_TRY(diag_ready(c, layer, "poz_diag_activation_grad"));
-    const int act = c->acts[layer];
-    const void* src = nullptr;
-    if (which == 0) src = c->dz_rec[layer];
-    else if (which == 1 && act != ACT_NONE && act != ACT_SOFTMAX) src = c->da_rec[layer];
-    // the trailing softmax is not on the loss graph: its .grad is None (neural_net_model.py:545)
-    if (has_grad) *has_grad = src ? 1 : 0;
-    if (!src) return 0;
-    long long n = c->diag_batch * c->sizes[layer + 1];
-    return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, n);
-}
-
-// which tensor a diagnostics request means: activation / its gradient of an entry, weights, weight gradient
 static int diag_tensor(poz_ctx* c, int layer, int which, int source, const void** ptr, long long* rows, int* cols) {
     *ptr = nullptr;
     if (c->dtype == POZ_DTYPE_BF16) POZ_FAIL("diagnostics are not available in bf16 contexts");
+    if (layer < -1 || layer >= c->nl) POZ_FAIL("diagnostics: layer out of range");
+    if ((source == 0 || source == 1) && c->diag_batch <= 0) POZ_FAIL("diagnostics: no step was run with diagnostics enabled");
+    if (source == 3 && (!c->have_diag || !c->Gdiag)) POZ_FAIL("diagnostics: no weight gradients recorded");
+    if (layer == -1) {                                  // the embedding head (and the flatten entries after it)
+        if (c->emb_vocab <= 0) POZ_FAIL("diagnostics: the stack has no embedding");
+        if (source <= 1) {
+            *rows = c->diag_batch * c->tokens; *cols = c->emb_dim;
+            *ptr = source == 0 ? c->ebuf : c->de_rec;
+        } else {
+            *rows = c->emb_vocab; *cols = c->emb_dim;
+            *ptr = static_cast<const char*>(source == 2 ? c->P : c->Gdiag) + c->off_emb * c->esz;
+        }
+        return 0;
+    }
     const int act = c->acts[layer];
-    if (source == 0 || source == 1) {
-        if (c->diag_batch <= 0) POZ_FAIL("diagnostics: no step was run with diagnostics enabled");
-        *rows = c->diag_batch; *cols = c->sizes[layer + 1];
+    const bool bn = !c->has_bn.empty() && c->has_bn[layer];
+    if (source <= 1) {
+        *rows = c->diag_batch * (c->rmul.empty() ? 1 : c->rmul[layer]); *cols = c->sizes[layer + 1];
         if (source == 0) {
-            if (which == 0) *ptr = act == ACT_NONE ? c->abuf[layer] : c->zbuf[layer];
-            else if (act != ACT_NONE) *ptr = c->abuf[layer];
+            if (which == 0) *ptr = (act == ACT_NONE && !bn) ? c->abuf[layer] : c->zbuf[layer];
+            else if (which == 1 && act != ACT_NONE) *ptr = c->abuf[layer];
+            else if (which == 2 && bn) *ptr = act == ACT_NONE ? c->abuf[layer] : c->ybuf[layer];
         } else {
             if (which == 0) *ptr = c->dz_rec[layer];
-            else if (act != ACT_NONE && act != ACT_SOFTMAX) *ptr = c->da_rec[layer];
+            else if (which == 1 && act != ACT_NONE && act != ACT_SOFTMAX) *ptr = c->da_rec[layer];
+            else if (which == 2 && bn) *ptr = c->dy_rec[layer];
         }
     } else {
-        *rows = c->sizes[layer]; *cols = c->sizes[layer + 1];
-        if (source == 2) *ptr = static_cast<const char*>(c->P) + c->off[layer] * c->esz;
-        else if (source == 3) {
-            if (!c->have_diag || !c->Gdiag) POZ_FAIL("diagnostics: no weight gradients recorded");
-            *ptr = static_cast<const char*>(c->Gdiag) + c->off[layer] * c->esz;
+        *rows = c->kin[layer]; *cols = c->sizes[layer + 1];
+        if (which == 2) {                                 // batchnorm [gain; bias]
+            if (!bn) POZ_FAIL("diagnostics: the layer has no batchnorm");
+            *rows = 2;
+            *ptr = static_cast<const char*>(source == 2 ? c->P : c->Gdiag) + c->off_bn[layer] * c->esz;
+        } else {
+            *ptr = static_cast<const char*>(source == 2 ? c->P : c->Gdiag) + c->off[layer] * c->esz;
         }
     }
     return 0;
 }
 
+int poz_diag_activation(poz_ctx* c, int layer, int which, double* host_out) {
+    POZ_TRY(diag_ready(c, layer, "poz_diag_activation"));
+    const void* src; long long rows; int cols;
+    POZ_TRY(diag_tensor(c, layer, which, 0, &src, &rows, &cols));
+    if (!src) POZ_FAIL("poz_diag_activation: no such entry");
+    return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, rows * cols);
+}
+
+int poz_diag_activation_grad(poz_ctx* c, int layer, int which, double* host_out, int* has_grad) {
+    POZ_TRY(diag_ready(c, layer, "poz_diag_activation_grad"));
+    const void* src; long long rows; int cols;
+    POZ_TRY(diag_tensor(c, layer, which, 1, &src, &rows, &cols));
+    // the trailing softmax is not on the loss graph: its .grad is None (neural_net_model.py:545)
+    if (has_grad) *has_grad = src ? 1 : 0;
+    if (!src) return 0;
+    return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, rows * cols);
+}
+
+// which tensor a diagnostics request means: activation / its gradient of an entry, weights, weight gradient
 int poz_diag_moments(poz_ctx* c, int layer, int which, int source, int rule, double threshold, double* out6) {
-    POZ_TRY(check_layer(c, layer, "poz_diag_moments"));
+    POZ_TRY(check_layer(c, layer < 0 ? 0 : layer, "poz_diag_moments"));
     const void* ptr; long long rows; int cols;
     POZ_TRY(diag_tensor(c, layer, which, source, &ptr, &rows, &cols));
     out6[0] = 0.0;
@@ -1532,7 +1686,7 @@ int poz_diag_moments(poz_ctx* c, int layer, int which, int source, int rule, dou
 }
 
 int poz_diag_histogram(poz_ctx* c, int layer, int which, int source, const double* edges, int bins, double* counts) {
-    POZ_TRY(check_layer(c, layer, "poz_diag_histogram"));
+    POZ_TRY(check_layer(c, layer < 0 ? 0 : layer, "poz_diag_histogram"));
     if (bins < 1 || bins > 128) POZ_FAIL("poz_diag_histogram: bins must be in [1,128]");
     const void* ptr; long long rows; int cols;
     POZ_TRY(diag_tensor(c, layer, which, source, &ptr, &rows, &cols));

@@ -36,6 +36,23 @@ struct poz_ctx {
     float* tc_logits = nullptr;       // fp32 logits of a chunk (trailing softmax)
     long long tc_chunk = 0;
     long long tc3_min_batch = 2048;   // smaller batches stay on the SIMT kernels (POZ_TC3_MIN_BATCH overrides)
+    // general stacks: embedding head, flatten row multipliers, batchnorm (csrc/poz_general.inc)
+    bool general = false;             // any of the above present -> the general path runs the stack
+    int emb_vocab = 0, emb_dim = 0, emb_drop = 0, tokens = 1;
+    long long off_emb = -1;           // flat offset of the embedding table
+    std::vector<int> kin;             // input width of layer l (= sizes[l] unless a flatten sits in front of it)
+    std::vector<int> rmul;            // rows of layer l = batch * rmul[l]
+    std::vector<int> has_bn, kz, kbn, ka;
+    std::vector<double> bn_eps, bn_mom;
+    std::vector<long long> off_bn;    // flat offset of [gain; bias] of layer l, -1 if none
+    std::vector<void*> bn_run;        // running [mean; variance] of layer l
+    std::vector<void*> bn_stat;       // [mean; 1/std] used by the current step
+    std::vector<void*> bn_sums;       // backward column sums
+    std::vector<void*> ybuf, dybuf, dy_rec;   // batchnorm output (diagnostics), its pre-dropout gradient
+    void* ebuf = nullptr;             // embedding output [batch*tokens][emb_dim]
+    void* debuf = nullptr;            // its gradient
+    void* de_rec = nullptr;           // diagnostics: gradient of the recorded embedding output
+    long long ws_gen = 0;
     void* P = nullptr;                // flat parameters
     void* AM = nullptr;               // Adam exp_avg
     void* AV = nullptr;               // Adam exp_avg_sq

@@ -8,12 +8,18 @@ namespace poz {
 
 constexpr int MAX_LAYERS = 16;
 
+constexpr int MAX_SEGS = 2 * MAX_LAYERS + 2;
+
+// Parameter segments of the flat buffers.  Segments 0..n_linear-1 are the Linear layers' [W; b]
+// images (segment index == layer index); an embedding table and batchnorm [gain; bias] pairs follow.
 struct SegTable {
-    int n;                           // linear layers
-    long long off[MAX_LAYERS + 1];   // layer l owns flat elements [off[l], off[l+1]) = [W; b]
-    long long n_elems[MAX_LAYERS];   // real elements of the image (the rest of the slot is padding)
-    long long w_elems[MAX_LAYERS];   // leading elements that are weights (L2 applies to these)
-    int splits[MAX_LAYERS];          // gradient slabs to sum for layer l
+    int n;                           // segments
+    int n_stat;                      // tensors the reference calls `weights` (update-ratio slots)
+    long long off[MAX_SEGS];         // first flat element of the segment
+    long long n_elems[MAX_SEGS];     // elements of the segment
+    long long w_elems[MAX_SEGS];     // leading elements that get L2 and update-ratio statistics
+    int splits[MAX_SEGS];            // gradient slabs to sum
+    int stat_slot[MAX_SEGS];         // update-ratio slot, -1 if none
 };
 
 // First kernel of every step: advances the epoch / Adam counters and derives the step's scalars
@@ -261,8 +267,8 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
         }
     }
     if (st->l2 > 0.0) block_add_double(l2acc * st->l2 * st->l2_share, cost_slot(cost_base, cost_cap, st));
-    if (rec >= 0) {
-        double* s = stats + (rec * seg.n + l) * 4;
+    if (rec >= 0 && seg.stat_slot[l] >= 0) {
+        double* s = stats + (rec * seg.n_stat + (seg.stat_slot[l] < 0 ? 0 : seg.stat_slot[l])) * 4;
         block_add_double(sd, s + 0);
         block_add_double(sd2, s + 1);
         block_add_double(sw, s + 2);

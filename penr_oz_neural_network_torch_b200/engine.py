@@ -20,18 +20,30 @@ _DTYPE_CODE = {"float32": nat.DTYPE_F32, "float64": nat.DTYPE_F64, "bfloat16": n
 
 @dataclass
 class StackSpec:
-    """Linear(+activation) units derived from the reference's expanded ``algos`` list.
+    """Units derived from the reference's expanded ``algos`` list.
 
-    ``drop_z`` / ``drop_a`` carry the reference's ``hidden`` flag (neural_net_model.py:255) of the
-    Linear entry and of the activation entry after it: the dropout points of
-    neural_net_model.py:393-395.
+    A unit is one Linear entry with an optional BatchNorm and an optional activation after it.
+    ``drop_z`` / ``drop_a`` (and ``kz`` / ``kbn`` / ``ka``) carry the reference's ``hidden`` flag
+    (neural_net_model.py:255) of the entries: the dropout points of neural_net_model.py:393-395.
+    Flatten entries (pure reshapes) fold their dropout into the tensor in front of them and divide
+    the row count: ``rmul[l]`` = rows of unit l per sample.  An embedding entry may lead the stack.
     """
     algos: list[str]
     acts: list[str] = field(default_factory=list)
     z_index: list[int] = field(default_factory=list)
     a_index: list[int | None] = field(default_factory=list)
+    bn_index: list[int | None] = field(default_factory=list)
     drop_z: list[bool] = field(default_factory=list)
     drop_a: list[bool] = field(default_factory=list)
+    kz: list[int] = field(default_factory=list)
+    kbn: list[int] = field(default_factory=list)
+    ka: list[int] = field(default_factory=list)
+    rmul: list[int] = field(default_factory=list)
+    flat_after: list[list[int]] = field(default_factory=list)   # flatten entries folded into unit l
+    emb_index: int | None = None
+    emb_drop: int = 0
+    emb_flat: list[int] = field(default_factory=list)           # flatten entries right after the embedding
+    tokens: int = 1
 
     @property
     def n_linear(self) -> int:
@@ -41,25 +53,79 @@ class StackSpec:
     def loss(self) -> str:
         return "ce" if self.algos and self.algos[-1] == "softmax" else "mse"
 
+    @property
+    def general(self) -> bool:
+        return (self.emb_index is not None or any(b is not None for b in self.bn_index)
+                or any(m != 1 for m in self.rmul))
+
     @staticmethod
-    def from_algos(algos: list[str]) -> "StackSpec":
+    def from_algos(algos: list[str], ratios: dict | None = None) -> "StackSpec":
+        """``ratios`` maps the index of every flatten entry to its ratio (known once the layers
+        hold their sizes); without it only the structure is validated."""
         spec = StackSpec(list(algos))
         n, i = len(algos), 0
+        hidden = lambda k: 0 < k < n - 1
+        ratio_of = lambda k: int((ratios or {}).get(k, 1)) or 1
+        divs = []                     # cumulative flatten ratio in front of each unit
+        div = 1
+        if n and algos[0] == "embedding":
+            spec.emb_index = 0
+            i = 1
+            while i < n and algos[i] == "flatten":
+                spec.emb_flat.append(i)
+                spec.emb_drop += int(hidden(i))
+                div *= ratio_of(i)
+                i += 1
         while i < n:
             if algos[i] != "linear":
-                raise ValueError(f"Activation algorithm not on the B200 hot path here: {algos[i]} "
-                                 f"(stack {algos}; supported: Linear followed by relu/sigmoid/tanh/softmax)")
-            act, a_idx = "none", None
-            if i + 1 < n and algos[i + 1] in ACTIVATIONS:
-                act, a_idx = algos[i + 1], i + 1
+                raise ValueError(f"Activation algorithm not on the B200 hot path here: {algos[i]} at entry {i} of "
+                                 f"{algos} (a stack is [embedding] then Linear [batchnorm] [relu|sigmoid|tanh|softmax] "
+                                 f"units, with flatten entries between them)")
+            z = i
+            kz, kbn, ka = int(hidden(z)), 0, 0
+            bn_idx = a_idx = None
+            act = "none"
+            i += 1
+            if i < n and algos[i] == "batchnorm":
+                bn_idx, kbn = i, int(hidden(i))
+                i += 1
+            if i < n and algos[i] in ACTIVATIONS:
+                act, a_idx, ka = algos[i], i, int(hidden(i))
+                i += 1
             if act == "softmax" and a_idx != n - 1:
                 raise ValueError("softmax is supported as the last activation only")
+            flats = []
+            divs.append(div)
+            while i < n and algos[i] == "flatten":
+                flats.append(i)
+                k = int(hidden(i))
+                if a_idx is not None:
+                    ka += k
+                elif bn_idx is not None:
+                    kbn += k
+                else:
+                    kz += k
+                div *= ratio_of(i)
+                i += 1
             spec.acts.append(act)
-            spec.z_index.append(i)
+            spec.z_index.append(z)
             spec.a_index.append(a_idx)
-            spec.drop_z.append(0 < i < n - 1)
-            spec.drop_a.append(a_idx is not None and 0 < a_idx < n - 1)
-            i += 1 if a_idx is None else 2
+            spec.bn_index.append(bn_idx)
+            spec.kz.append(kz); spec.kbn.append(kbn); spec.ka.append(ka)
+            spec.drop_z.append(kz > 0)
+            spec.drop_a.append(ka > 0)
+            spec.flat_after.append(flats)
+        if not spec.acts and n:
+            raise ValueError(f"stack {algos} has no Linear layer")
+        spec.tokens = div
+        spec.rmul = [div // d for d in divs]
+        if ratios is not None:
+            if spec.emb_index is None and div != 1:
+                raise ValueError("flatten entries need an embedding head on the device path")
+            if spec.rmul and spec.rmul[-1] != 1:
+                raise ValueError("the stack must end with one row per sample (flatten ratios do not use up the tokens)")
+            if spec.bn_index and spec.bn_index[-1] is not None:
+                raise ValueError("batchnorm on the last Linear layer is not supported on the device path")
         return spec
 
 
@@ -78,17 +144,26 @@ def _stream_ptr(device) -> int:
 class DeviceMLP:
     """Device image of one model: parameters, Adam state, workspace; tensor-level fwd/train."""
 
-    def __init__(self, sizes, spec: StackSpec, has_bias: bool, dtype: str = "float32", device=None):
+    def __init__(self, sizes, spec: StackSpec, has_bias: bool, dtype: str = "float32", device=None, *,
+                 embedding: tuple[int, int] | None = None, batchnorm: list | None = None):
+        """``sizes``: the chained layer widths of a plain stack, or a list of (in, out) pairs when
+        flatten entries make consecutive widths differ.  ``embedding`` = (vocab, dim);
+        ``batchnorm[l]`` = (eps, momentum) or None per Linear layer."""
         if not torch.cuda.is_available():
             raise nat.PozError("no CUDA device: the NeuralNetworkModel hot path has no CPU fallback")
         if dtype not in _DTYPE_CODE:
             raise ValueError(f"dtype must be one of {sorted(_DTYPE_CODE)}")
-        if len(sizes) != spec.n_linear + 1:
+        if sizes and isinstance(sizes[0], (tuple, list)):
+            dims = [(int(a), int(b)) for a, b in sizes]
+        else:
+            dims = [(int(a), int(b)) for a, b in zip(sizes[:-1], sizes[1:])]
+        if len(dims) != spec.n_linear:
             raise ValueError("layer sizes do not match the stack")
         self.lib = nat.lib()
         self.device = torch.device("cuda", torch.cuda.current_device() if device is None else
                                    (device.index if isinstance(device, torch.device) else int(device)))
-        self.sizes = [int(s) for s in sizes]
+        self.dims = dims
+        self.sizes = [dims[0][0]] + [d[1] for d in dims]      # chained widths (plain stacks)
         self.spec = spec
         self.has_bias = bool(has_bias)
         self.dtype_name = dtype
@@ -96,15 +171,33 @@ class DeviceMLP:
         # gradients / master parameters: float32 in bfloat16 contexts
         self.gdtype = torch.float64 if dtype == "float64" else torch.float32
         self.n_linear = spec.n_linear
+        self.embedding = tuple(embedding) if embedding else None
+        self.batchnorm = list(batchnorm) if batchnorm else [None] * self.n_linear
+        self.general = spec.general
+        self.tokens = spec.tokens if self.embedding else 1
+        self.in_features = self.tokens if self.embedding else dims[0][0]
+        self.out_features = dims[-1][1]
         handle = C.c_void_p()
+        loss = nat.LOSS_CE if spec.loss == "ce" else nat.LOSS_MSE
         with torch.cuda.device(self.device):
-            nat.check(self.lib.poz_ctx_create(
-                self.device.index, self.n_linear, _arr(C.c_int, self.sizes),
-                _arr(C.c_int, [nat.ACT_CODES[a] for a in spec.acts]),
-                _arr(C.c_ubyte, [int(b) for b in spec.drop_z]),
-                _arr(C.c_ubyte, [int(b) for b in spec.drop_a]),
-                int(self.has_bias), nat.LOSS_CE if spec.loss == "ce" else nat.LOSS_MSE,
-                _DTYPE_CODE[dtype], C.byref(handle)))
+            if not self.general:
+                nat.check(self.lib.poz_ctx_create(
+                    self.device.index, self.n_linear, _arr(C.c_int, self.sizes),
+                    _arr(C.c_int, [nat.ACT_CODES[a] for a in spec.acts]),
+                    _arr(C.c_ubyte, [int(b) for b in spec.drop_z]),
+                    _arr(C.c_ubyte, [int(b) for b in spec.drop_a]),
+                    int(self.has_bias), loss, _DTYPE_CODE[dtype], C.byref(handle)))
+            else:
+                layers = (nat.LayerDesc * self.n_linear)()
+                for l, (k_in, k_out) in enumerate(dims):
+                    bn = self.batchnorm[l]
+                    layers[l] = nat.LayerDesc(k_in, k_out, nat.ACT_CODES[spec.acts[l]], int(bn is not None),
+                                              float(bn[0]) if bn else 1e-5, float(bn[1]) if bn else 0.1,
+                                              spec.kz[l], spec.kbn[l], spec.ka[l], spec.rmul[l])
+                desc = nat.StackDesc(self.n_linear, layers, int(self.has_bias), loss, _DTYPE_CODE[dtype],
+                                     self.embedding[0] if self.embedding else 0,
+                                     self.embedding[1] if self.embedding else 0, spec.emb_drop, self.tokens)
+                nat.check(self.lib.poz_ctx_create_ex(self.device.index, C.byref(desc), C.byref(handle)))
         self.ctx = handle
         self._epochs_declared = 0
 
@@ -131,13 +224,13 @@ class DeviceMLP:
 
     def upload_params(self, layer: int, w, b=None):
         w, b = self._f64(w), self._f64(b)
-        assert w.shape == (self.sizes[layer], self.sizes[layer + 1]), w.shape
+        assert w.shape == self.dims[layer], w.shape
         nat.check(self.lib.poz_params_upload(self.ctx, layer, w.ctypes.data,
                                              b.ctypes.data if b is not None else None))
 
     def download_params(self, layer: int):
-        w = np.empty((self.sizes[layer], self.sizes[layer + 1]), dtype=np.float64)
-        b = np.empty((self.sizes[layer + 1],), dtype=np.float64) if self.has_bias else None
+        w = np.empty(self.dims[layer], dtype=np.float64)
+        b = np.empty((self.dims[layer][1],), dtype=np.float64) if self.has_bias else None
         nat.check(self.lib.poz_params_download(self.ctx, layer, w.ctypes.data,
                                                b.ctypes.data if b is not None else None))
         return w, b
@@ -149,7 +242,7 @@ class DeviceMLP:
             m_b.ctypes.data if m_b is not None else None, v_b.ctypes.data if v_b is not None else None))
 
     def download_adam(self, layer: int):
-        shp = (self.sizes[layer], self.sizes[layer + 1])
+        shp = self.dims[layer]
         m_w, v_w = np.empty(shp), np.empty(shp)
         m_b = np.empty((shp[1],)) if self.has_bias else None
         v_b = np.empty((shp[1],)) if self.has_bias else None
@@ -157,6 +250,27 @@ class DeviceMLP:
             self.ctx, layer, m_w.ctypes.data, v_w.ctypes.data,
             m_b.ctypes.data if m_b is not None else None, v_b.ctypes.data if v_b is not None else None))
         return m_w, v_w, m_b, v_b
+
+    # generic tensor <-> float64 host image (poz_tensor_io): kinds and buffers as in include/pozmlp.h
+    KIND = {"weight": 0, "bias": 1, "embedding": 2, "bn_gain": 3, "bn_bias": 4, "bn_mean": 5, "bn_var": 6}
+    BUFFER = {"value": 0, "adam_m": 1, "adam_v": 2, "diag_grad": 3}
+
+    def tensor_shape(self, kind: str, layer: int):
+        if kind == "embedding":
+            return tuple(self.embedding)
+        if kind == "weight":
+            return self.dims[layer]
+        return (self.dims[layer][1],)
+
+    def upload_tensor(self, kind: str, layer: int, values, buffer: str = "value"):
+        a = self._f64(values)
+        assert a.shape == self.tensor_shape(kind, layer), (kind, layer, a.shape)
+        nat.check(self.lib.poz_tensor_io(self.ctx, self.KIND[kind], layer, self.BUFFER[buffer], 0, a.ctypes.data))
+
+    def download_tensor(self, kind: str, layer: int, buffer: str = "value") -> np.ndarray:
+        out = np.empty(self.tensor_shape(kind, layer), dtype=np.float64)
+        nat.check(self.lib.poz_tensor_io(self.ctx, self.KIND[kind], layer, self.BUFFER[buffer], 1, out.ctypes.data))
+        return out
 
     def set_adam_step(self, step: int):
         nat.check(self.lib.poz_adam_set_step(self.ctx, int(step)))
@@ -168,10 +282,11 @@ class DeviceMLP:
 
     # ---- helpers ----
     def _check_x(self, x: torch.Tensor):
-        if x.device != self.device or x.dtype != self.tdtype or not x.is_contiguous():
-            raise ValueError(f"x must be a contiguous {self.tdtype} tensor on {self.device}")
-        if x.ndim != 2 or x.shape[1] != self.sizes[0]:
-            raise ValueError(f"x must be [batch, {self.sizes[0]}], got {tuple(x.shape)}")
+        want = torch.int32 if self.embedding else self.tdtype
+        if x.device != self.device or x.dtype != want or not x.is_contiguous():
+            raise ValueError(f"x must be a contiguous {want} tensor on {self.device}")
+        if x.ndim != 2 or x.shape[1] != self.in_features:
+            raise ValueError(f"x must be [batch, {self.in_features}], got {tuple(x.shape)}")
 
     def _check_target(self, t: torch.Tensor, rows: int | None):
         if t.device != self.device or not t.is_contiguous():
@@ -180,8 +295,8 @@ class DeviceMLP:
             if t.dtype != torch.int32 or t.ndim != 1:
                 raise ValueError("cross-entropy target must be int32 labels [batch]")
         else:
-            if t.dtype != self.tdtype or t.ndim != 2 or t.shape[1] != self.sizes[-1]:
-                raise ValueError(f"MSE target must be {self.tdtype} [batch, {self.sizes[-1]}]")
+            if t.dtype != self.tdtype or t.ndim != 2 or t.shape[1] != self.out_features:
+                raise ValueError(f"MSE target must be {self.tdtype} [batch, {self.out_features}]")
         if rows is not None and t.shape[0] != rows:
             raise ValueError("target rows do not match the batch")
 
@@ -190,7 +305,7 @@ class DeviceMLP:
         self._check_x(x)
         batch = x.shape[0]
         if out is None:
-            out = torch.empty((batch, self.sizes[-1]), dtype=self.tdtype, device=self.device)
+            out = torch.empty((batch, self.out_features), dtype=self.tdtype, device=self.device)
         if batch:
             nat.check(self.lib.poz_forward(self.ctx, _ptr(x), batch, _ptr(out), _stream_ptr(self.device)))
         return out
@@ -198,7 +313,7 @@ class DeviceMLP:
     def forward_loss(self, x: torch.Tensor, target: torch.Tensor):
         self._check_x(x)
         self._check_target(target, x.shape[0])
-        out = torch.empty((x.shape[0], self.sizes[-1]), dtype=self.tdtype, device=self.device)
+        out = torch.empty((x.shape[0], self.out_features), dtype=self.tdtype, device=self.device)
         cost = C.c_double()
         nat.check(self.lib.poz_forward_loss(self.ctx, _ptr(x), _ptr(target), x.shape[0], _ptr(out),
                                             C.byref(cost), _stream_ptr(self.device)))
@@ -219,8 +334,11 @@ class DeviceMLP:
         if masks is None:
             return None, None
         keep = []
-        ptrs = (C.c_void_p * (2 * self.n_linear))()
-        for i in range(2 * self.n_linear):
+        # slots: plain stacks 2*l + {0: z, 1: a}; general stacks 3*l + {0: z, 1: a, 2: bn} and 3*n for the
+        # embedding output
+        n_slots = 3 * self.n_linear + 1 if self.general else 2 * self.n_linear
+        ptrs = (C.c_void_p * n_slots)()
+        for i in range(n_slots):
             m = masks.get(i) if isinstance(masks, dict) else masks[i]
             if m is None:
                 ptrs[i] = None
@@ -277,7 +395,7 @@ class DeviceMLP:
         return out
 
     def update_ratios(self, first_record: int, count: int) -> np.ndarray:
-        out = np.empty((count, self.n_linear), dtype=np.float64)
+        out = np.empty((count, self.n_linear + (1 if self.embedding else 0)), dtype=np.float64)
         nat.check(self.lib.poz_train_update_ratios(self.ctx, first_record, count, out.ctypes.data,
                                                    _stream_ptr(self.device)))
         return out
@@ -293,13 +411,20 @@ class DeviceMLP:
         return json.loads(buf.value.decode())
 
     # ---- diagnostics of the last diagnostics step (neural_net_model.py:491-493,532-583) ----
+    def _diag_shape(self, layer: int, batch: int):
+        if layer < 0:
+            return (batch * self.tokens, self.embedding[1])
+        return (batch * self.spec.rmul[layer], self.dims[layer][1])
+
     def diag_activation(self, layer: int, which: int, batch: int) -> np.ndarray:
-        out = np.empty((batch, self.sizes[layer + 1]), dtype=np.float64)
+        """Recorded output of one entry of the last diagnostics step: layer l, which 0 = Linear,
+        1 = activation, 2 = batchnorm; layer -1 = the embedding head."""
+        out = np.empty(self._diag_shape(layer, batch), dtype=np.float64)
         nat.check(self.lib.poz_diag_activation(self.ctx, layer, which, out.ctypes.data))
         return out
 
     def diag_activation_grad(self, layer: int, which: int, batch: int):
-        out = np.empty((batch, self.sizes[layer + 1]), dtype=np.float64)
+        out = np.empty(self._diag_shape(layer, batch), dtype=np.float64)
         has = C.c_int()
         nat.check(self.lib.poz_diag_activation_grad(self.ctx, layer, which, out.ctypes.data, C.byref(has)))
         return out if has.value else None
@@ -333,8 +458,8 @@ class DeviceMLP:
         return out
 
     def diag_weight_grad(self, layer: int):
-        w = np.empty((self.sizes[layer], self.sizes[layer + 1]), dtype=np.float64)
-        b = np.empty((self.sizes[layer + 1],), dtype=np.float64) if self.has_bias else None
+        w = np.empty(self.dims[layer], dtype=np.float64)
+        b = np.empty((self.dims[layer][1],), dtype=np.float64) if self.has_bias else None
         nat.check(self.lib.poz_diag_weight_grad(self.ctx, layer, w.ctypes.data,
                                                 b.ctypes.data if b is not None else None))
         return w, b

@@ -160,7 +160,7 @@ int poz_diag_weight_grad(poz_ctx* ctx, int layer, double* w_grad, double* b_grad
  * source: 0 = entry output, 1 = its gradient, 2 = the layer's weight matrix, 3 = its gradient.
  * poz_diag_moments -> out6 = {count (0 if the tensor does not exist), sum, sum of squares, min, max,
  *   saturated fraction}; rule 1: |x| > threshold (:558,:561), rule 2: x <= 0 (:559), rule 3: row maximum >
- *   threshold (:560), 0: none.
+ *   threshold (:560), rule 4: row L2 norm > threshold (:556), 0: none.
  * poz_diag_histogram -> counts per bin for the caller's bin edges (torch.histogram's: bin i is
  *   [edges[i], edges[i+1]), the last one closed). */
 int poz_diag_moments(poz_ctx* ctx, int layer, int which, int source, int rule, double threshold, double* out6);

@@ -58,6 +58,11 @@ INIT_CASES = [
          optimizer="adam", weight_algo="gaussian", bias="random", confidence=0.7, seed=2),
     dict(name="he_nobias", sizes=[5, 6, 7, 8], algos=["tanh", "relu", "sigmoid"],
          optimizer="adam", weight_algo="he", bias="", confidence=1.0, seed=3),
+    dict(name="emb_bn_he", sizes=[27, 10, 30, 64, 27], algos=["embedding", "linear", "batchnorm", "tanh", "linear", "softmax"],
+         optimizer="adam", weight_algo="he", bias="random", confidence=0.1, seed=4),
+    dict(name="emb_hier_xavier", sizes=[9, 2, 4, 9, 18, 9],
+         algos=["embedding", "linear", "batchnorm", "tanh", "flatten", "linear", "softmax"],
+         optimizer=None, weight_algo="xavier", bias="zeros", confidence=1.0, seed=5),
 ]
 
 

@@ -1681,7 +1681,7 @@ int poz_diag_moments(poz_ctx* c, int layer, int which, int source, int rule, dou
         mn = std::min(mn, part[b * 5 + 2]); mx = std::max(mx, part[b * 5 + 3]);
     }
     out6[0] = (double)n; out6[1] = s; out6[2] = s2; out6[3] = mn; out6[4] = mx;
-    out6[5] = sat / (rule == 3 ? (double)rows : (double)n);
+    out6[5] = sat / ((rule == 3 || rule == 4) ? (double)rows : (double)n);
     return 0;
 }
 

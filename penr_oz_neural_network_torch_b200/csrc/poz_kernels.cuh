@@ -311,22 +311,24 @@ __global__ void colsum_f32_final_kernel(const float* __restrict__ partial, int p
 
 // ---- device-side diagnostics (neural_net_model.py:532-583) -----------------------------------------
 // Pass 1: per-block partial moments of a tensor: [sum, sum of squares, min, max, saturated count].
-// rule 1: |x| > thr; rule 2: x <= 0; rule 3: row maximum > thr (counted per row, cols <= 1024 per warp loop).
+// rule 1: |x| > thr; rule 2: x <= 0; rule 3: row maximum > thr; rule 4: row L2 norm > thr (rules 3-4 count rows).
 template <typename T>
 __global__ void diag_moments_kernel(const T* __restrict__ x, long long rows, int cols, int rule, double thr,
                                     double* __restrict__ partial /*[gridDim.x][5]*/) {
     const long long n = rows * cols;
     double s = 0.0, s2 = 0.0, mn = INFINITY, mx = -INFINITY, sat = 0.0;
-    if (rule == 3) {
+    if (rule == 3 || rule == 4) {
         const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
         for (long long r = (long long)blockIdx.x * wpb + (threadIdx.x >> 5); r < rows; r += (long long)gridDim.x * wpb) {
-            double rmax = -INFINITY;
+            double rmax = -INFINITY, rsq = 0.0;
             for (int j = lane; j < cols; j += 32) {
                 const double v = (double)x[r * cols + j];
                 s += v; s2 += v * v; mn = v < mn ? v : mn; mx = v > mx ? v : mx; rmax = v > rmax ? v : rmax;
+                rsq += v * v;
             }
             rmax = warp_max(rmax);
-            if (lane == 0 && rmax > thr) sat += 1.0;
+            rsq = warp_sum(rsq);
+            if (lane == 0 && (rule == 3 ? rmax > thr : sqrt(rsq) > thr)) sat += 1.0;
         }
     } else {
         for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {

@@ -9,9 +9,9 @@ activation stack, the loss, the backward pass and the Adam / SGD update run thro
 *view* the reference exposes (``params``, ``weights``, ``state_dict``, ``optimizer.state_dict()``)
 and synchronises them with the device image at the boundaries of ``train`` / ``compute_output``.
 
-Scope: stacks made of Linear layers each optionally followed by
-relu / sigmoid / tanh, with an optional trailing softmax.  ``embedding`` / ``flatten`` /
-``batchnorm`` entries raise ``ValueError`` -- there is deliberately no CPU fallback.
+Scope: an optional embedding head, then Linear layers each optionally followed
+by a batchnorm and by relu / sigmoid / tanh, with flatten entries between them and an optional
+trailing softmax.  Anything else raises ``ValueError`` -- there is deliberately no CPU fallback.
 """
 from __future__ import annotations
 
@@ -32,8 +32,7 @@ from .engine import ACTIVATIONS, DeviceMLP, StackSpec
 
 log = logging.getLogger(__name__)
 
-_KNOWN_ALGOS = ("linear",) + ACTIVATIONS
-_OFF_PATH_ALGOS = ("embedding", "flatten", "batchnorm")
+_KNOWN_ALGOS = ("linear", "embedding", "flatten", "batchnorm") + ACTIVATIONS
 _GAIN = {"relu": math.sqrt(2.0), "tanh": 5.0 / 3.0}     # neural_net_model.py:178,183
 
 DEFAULT_DTYPE = os.environ.get("POZ_DTYPE", "float32")
@@ -81,6 +80,67 @@ class LinearLayer(Layer):
                              else torch.randn(output_size)).double()
 
 
+class EmbeddingLayer(Layer):
+    """Lookup table (neural_net_model.py:55-68); the gather / scatter-add run in emb_*_kernel."""
+    algo = "embedding"
+
+    def __init__(self, vocab_size: int = 0, embedding_size: int = 0):
+        super().__init__()
+        if vocab_size > 0 and embedding_size > 0:
+            self.weights = torch.randn(vocab_size, embedding_size).double()
+
+
+class FlattenLayer(Layer):
+    """Merges `ratio` rows into one (neural_net_model.py:70-91): a reinterpretation on the device."""
+    algo = "flatten"
+
+    def __init__(self, ratio: int):
+        super().__init__()
+        self.ratio = ratio
+
+    @property
+    def state_dict(self) -> dict:
+        return {"ratio": self.ratio}
+
+    @state_dict.setter
+    def state_dict(self, new_state: dict):
+        self.ratio = new_state["ratio"]
+
+
+class BatchNormLayer(Layer):
+    """Parameters and running statistics of a batchnorm entry (neural_net_model.py:122-170)."""
+    algo = "batchnorm"
+
+    def __init__(self, dim_size: int, eps=1e-5, momentum=0.1):
+        super().__init__()
+        self.eps = eps
+        self.momentum = momentum
+        self.gain = torch.ones(dim_size, dtype=torch.float64) if dim_size > 0 else None
+        self.bias = torch.zeros(dim_size, dtype=torch.float64) if dim_size > 0 else None
+        self.variance = torch.ones(dim_size, dtype=torch.float64) if dim_size > 0 else None
+        self.mean = torch.zeros(dim_size, dtype=torch.float64) if dim_size > 0 else None
+
+    @property
+    def params(self) -> list[Tensor]:
+        return [t for t in (self.gain, self.bias) if t is not None]
+
+    @property
+    def state_dict(self) -> dict:
+        return {"params": [t.tolist() for t in self.params], "eps": self.eps, "momentum": self.momentum}
+
+    @state_dict.setter
+    def state_dict(self, new_state: dict):
+        values = new_state["params"]
+        if len(values) > 0:                      # running statistics are not persisted (:146-156)
+            self.gain = torch.tensor(values[0], dtype=torch.float64)
+            self.variance = torch.ones_like(self.gain)
+        if len(values) > 1:
+            self.bias = torch.tensor(values[1], dtype=torch.float64)
+            self.mean = torch.zeros_like(self.bias)
+        self.eps = new_state["eps"]
+        self.momentum = new_state["momentum"]
+
+
 class SigmoidLayer(Layer):
     algo = "sigmoid"
 
@@ -103,15 +163,19 @@ _LAYER_TYPES = {"sigmoid": SigmoidLayer, "relu": ReluLayer, "tanh": TanhLayer, "
 
 
 def expand_algos(activation_algos: list[str]) -> list[str]:
-    """The reference's "linear sandwich" (neural_net_model.py:202-212): a Linear entry is put in
-    front of every activation that does not already follow one."""
+    """The reference's entry-list expansion (neural_net_model.py:202-212): a Linear entry goes in
+    front of every activation that does not already follow a Linear / batchnorm, and a flatten entry
+    behind an embedding that has none.  Walks the list from the back, as the reference does, so
+    that the insertion positions agree in every case."""
+    requested = list(activation_algos)
     expanded: list[str] = []
-    prev = None
-    for algo in activation_algos:
-        if algo in ACTIVATIONS and prev not in ("linear", "batchnorm"):
-            expanded.append("linear")
-        expanded.append(algo)
-        prev = algo
+    for i in range(len(requested) - 1, -1, -1):
+        algo = requested[i]
+        expanded.insert(0, algo)
+        if algo in ACTIVATIONS and (i == 0 or requested[i - 1] not in ("batchnorm", "linear")):
+            expanded.insert(0, "linear")
+        elif algo == "embedding" and requested[i + 1] != "flatten":
+            expanded.insert(i + 1, "flatten")
     return expanded
 
 
@@ -120,30 +184,44 @@ class MultiLayerPerceptron:
                  activation_algos: list[str] = None, batchnorm=(1e-5, 0.1)):
         requested = activation_algos or ["relu"] * (len(layer_sizes) - 1)
         for algo in requested:
-            if algo not in _KNOWN_ALGOS and algo not in _OFF_PATH_ALGOS:
+            if algo not in _KNOWN_ALGOS:
                 raise ValueError(f"Unsupported activation algorithm: {algo}")   # neural_net_model.py:241
         self.algos = expand_algos(requested)
-        self.stack = StackSpec.from_algos(self.algos)       # raises ValueError for off-path entries
+        StackSpec.from_algos(self.algos)                    # structure check: ValueError if off the device path
         self.layers: list[Layer] = []
         n_entries = len(self.algos)
         n_sizes = len(layer_sizes)
         size_idx = 0
         pending_gain: LinearLayer | None = None
         for i, algo in enumerate(self.algos):
-            if algo == "linear":
-                in_sz = layer_sizes[size_idx] if size_idx < n_sizes else 0
-                out_sz = layer_sizes[size_idx + 1] if size_idx + 1 < n_sizes else 0
+            in_sz = layer_sizes[size_idx] if size_idx < n_sizes else 0
+            out_sz = layer_sizes[size_idx + 1] if size_idx + 1 < n_sizes else 0
+            if algo == "embedding":
+                layer = EmbeddingLayer(in_sz, out_sz)
+            elif algo == "flatten":
+                layer = FlattenLayer(out_sz // max(1, in_sz))                  # :227
+            elif algo == "linear":
                 layer = LinearLayer(in_sz, out_sz, bias_algo)
                 if in_sz > 0 and layer.weights is not None and weight_algo in ("xavier", "he"):
                     layer.weights /= math.sqrt(in_sz)                          # :243-244
                 pending_gain = layer if weight_algo == "he" else None          # :246-247
-                size_idx += 1
+            elif algo == "batchnorm":
+                layer = BatchNormLayer(in_sz, *batchnorm)                      # :231
             else:
                 layer = _LAYER_TYPES[algo]()
                 if pending_gain is not None and pending_gain.weights is not None and algo in _GAIN:
                     pending_gain.weights *= _GAIN[algo]                        # :249-253
             layer.hidden = 0 < i < n_entries - 1                               # :255
             self.layers.append(layer)
+            if algo in ("embedding", "flatten", "linear"):                     # :259-260
+                size_idx += 1
+
+    @property
+    def stack(self) -> StackSpec:
+        """Units, dropout points and row multipliers, from the entries as they are now (flatten
+        ratios are only known once the layers hold their sizes / their persisted state)."""
+        ratios = {i: layer.ratio for i, layer in enumerate(self.layers) if layer.algo == "flatten"}
+        return StackSpec.from_algos(self.algos, ratios)
 
     @property
     def params(self) -> list[Tensor]:
@@ -173,6 +251,7 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         self._dtype = dtype or DEFAULT_DTYPE
         self._device = device
         self._engine: DeviceMLP | None = None
+        self._engine_signature = None
         self._synced_versions = None
 
     # ------------------------------------------------------------------ containers
@@ -251,76 +330,104 @@ class NeuralNetworkModel(MultiLayerPerceptron):
             log.warning(f"Failed to delete: {str(e)}")
 
     # ------------------------------------------------------------------ device image
-    def _linear_layers(self) -> list[Layer]:
-        return [layer for layer in self.layers if layer.algo == "linear"]
-
     def _drop_engine(self):
         if self._engine is not None:
             self._engine.close()
         self._engine = None
         self._synced_versions = None
 
-    def _versions(self):
-        return [(id(p), p._version) for p in self.params]
+    def _param_slots(self, spec: StackSpec) -> list[tuple[Tensor, str, int]]:
+        """Every parameter tensor in the reference's `params` order with its device location."""
+        slots = []
+        for i, layer in enumerate(self.layers):
+            if layer.algo == "embedding":
+                slots.append((layer.weights, "embedding", 0))
+            elif layer.algo == "linear":
+                l = spec.z_index.index(i)
+                slots.append((layer.weights, "weight", l))
+                if layer.bias is not None:
+                    slots.append((layer.bias, "bias", l))
+            elif layer.algo == "batchnorm":
+                l = spec.bn_index.index(i)
+                slots += [(layer.gain, "bn_gain", l), (layer.bias, "bn_bias", l)]
+        return slots
+
+    def _running_slots(self, spec: StackSpec):
+        return [(layer, spec.bn_index.index(i)) for i, layer in enumerate(self.layers) if layer.algo == "batchnorm"]
+
+    def _versions(self, spec: StackSpec):
+        v = [(id(t), t._version) for t, _, _ in self._param_slots(spec)]
+        for layer, _ in self._running_slots(spec):
+            v += [(id(layer.mean), layer.mean._version), (id(layer.variance), layer.variance._version)]
+        return v
 
     def _ensure_engine(self) -> DeviceMLP:
-        linears = self._linear_layers()
+        spec = self.stack
+        linears = [self.layers[i] for i in spec.z_index]
         if not linears or any(l.weights is None for l in linears):
             raise ValueError("model has no parameters")
-        sizes = [linears[0].weights.shape[0]] + [l.weights.shape[1] for l in linears]
+        dims = [tuple(l.weights.shape) for l in linears]
         has_bias = linears[0].bias is not None
         if any((l.bias is not None) != has_bias for l in linears):
             raise ValueError("mixed bias / no-bias layers are not supported on the device path")
+        emb = tuple(self.layers[0].weights.shape) if spec.emb_index is not None else None
+        bn = [None if i is None else (self.layers[i].eps, self.layers[i].momentum) for i in spec.bn_index]
+        signature = (dims, has_bias, emb, bn, spec.rmul, spec.kz, spec.kbn, spec.ka, spec.emb_drop)
         eng = self._engine
-        if eng is None or eng.sizes != sizes or eng.has_bias != has_bias:
+        if eng is None or self._engine_signature != signature:
             self._drop_engine()
-            eng = DeviceMLP(sizes, self.stack, has_bias, self._dtype, self._device)
-            self._engine = eng
-        versions = self._versions()
+            eng = DeviceMLP(dims, spec, has_bias, self._dtype, self._device, embedding=emb, batchnorm=bn)
+            self._engine, self._engine_signature = eng, signature
+        versions = self._versions(spec)
         if versions != self._synced_versions:
-            for i, layer in enumerate(linears):
-                eng.upload_params(i, layer.weights, layer.bias)
+            for t, kind, l in self._param_slots(spec):
+                eng.upload_tensor(kind, l, t)
+            for layer, l in self._running_slots(spec):
+                eng.upload_tensor("bn_mean", l, layer.mean.reshape(-1))
+                eng.upload_tensor("bn_var", l, layer.variance.reshape(-1))
             self._synced_versions = versions
         return eng
 
+    def _download_running_stats(self):
+        eng, spec = self._engine, self.stack
+        for layer, l in self._running_slots(spec):
+            layer.mean = torch.from_numpy(eng.download_tensor("bn_mean", l))
+            layer.variance = torch.from_numpy(eng.download_tensor("bn_var", l))
+        self._synced_versions = self._versions(spec)
+
     def _download_params(self):
-        eng = self._engine
+        eng, spec = self._engine, self.stack
         with torch.no_grad():
-            for i, layer in enumerate(self._linear_layers()):
-                w, b = eng.download_params(i)
-                layer.weights.copy_(torch.from_numpy(w))
-                if layer.bias is not None:
-                    layer.bias.copy_(torch.from_numpy(b))
-        self._synced_versions = self._versions()
+            for t, kind, l in self._param_slots(spec):
+                t.copy_(torch.from_numpy(eng.download_tensor(kind, l)))
+        self._download_running_stats()
 
     def _upload_adam_state(self):
         """torch.optim.Adam.state -> device (state persists across train() calls and .pth files)."""
         eng, opt = self._engine, self.optimizer
         step = 0
-        for i, layer in enumerate(self._linear_layers()):
-            sw = opt.state.get(layer.weights, {})
-            sb = opt.state.get(layer.bias, {}) if layer.bias is not None else {}
-            zw = torch.zeros_like(layer.weights)
-            zb = torch.zeros_like(layer.bias) if layer.bias is not None else None
-            eng.upload_adam(i, sw.get("exp_avg", zw), sw.get("exp_avg_sq", zw),
-                            sb.get("exp_avg", zb) if zb is not None else None,
-                            sb.get("exp_avg_sq", zb) if zb is not None else None)
-            if "step" in sw:
-                step = int(float(sw["step"]))
+        for t, kind, l in self._param_slots(self.stack):
+            st = opt.state.get(t, {})
+            zero = torch.zeros_like(t)
+            eng.upload_tensor(kind, l, st.get("exp_avg", zero), "adam_m")
+            eng.upload_tensor(kind, l, st.get("exp_avg_sq", zero), "adam_v")
+            if "step" in st:
+                step = int(float(st["step"]))
         eng.set_adam_step(step)
 
     def _download_adam_state(self):
         eng, opt = self._engine, self.optimizer
         step = eng.get_adam_step()
-        for i, layer in enumerate(self._linear_layers()):
-            m_w, v_w, m_b, v_b = eng.download_adam(i)
-            pairs = [(layer.weights, m_w, v_w)]
-            if layer.bias is not None:
-                pairs.append((layer.bias, m_b, v_b))
-            for p, m, v in pairs:
-                opt.state[p] = {"step": torch.tensor(float(step)),
-                                "exp_avg": torch.from_numpy(m).clone(),
-                                "exp_avg_sq": torch.from_numpy(v).clone()}
+        for t, kind, l in self._param_slots(self.stack):
+            opt.state[t] = {"step": torch.tensor(float(step)),
+                            "exp_avg": torch.from_numpy(eng.download_tensor(kind, l, "adam_m")).clone(),
+                            "exp_avg_sq": torch.from_numpy(eng.download_tensor(kind, l, "adam_v")).clone()}
+
+    def _inputs_to_device(self, eng: DeviceMLP, x: Tensor) -> Tensor:
+        """float64 host tensor (features, or token indices for an embedding head) -> device batch."""
+        if eng.embedding:
+            return x.long().to(torch.int32).to(eng.device).contiguous()      # :68 `input_tensor.long()`
+        return x.to(eng.tdtype).to(eng.device).contiguous()
 
     # ------------------------------------------------------------------ forward (:371-408)
     def _targets_to_device(self, eng: DeviceMLP, target, batched: bool):
@@ -340,13 +447,15 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         eng = self._ensure_engine()
         x = torch.as_tensor(input_tensor, dtype=torch.float64)
         batched = x.ndim == 2
-        xd = (x if batched else x.unsqueeze(0)).to(eng.tdtype).to(eng.device).contiguous()
+        xd = self._inputs_to_device(eng, x if batched else x.unsqueeze(0))
         for layer in self.layers:
             layer.training = target_specified                        # :390
         if target_specified:
             td = self._targets_to_device(eng, target, batched)
             out, cost = eng.forward_loss(xd, td)
             cost_t = torch.tensor(cost, dtype=torch.float64)
+            if eng.general:          # layer.training = True moves the batchnorm running statistics (:161-166)
+                self._download_running_stats()
         else:
             out = eng.forward(xd)
             cost_t = torch.empty(0)
@@ -388,8 +497,7 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         n_data = len(training_data)
         # One upload of the whole buffer; each epoch's sample is a device-side row gather inside
         # the first-layer kernels instead of the reference's per-epoch list -> tensor copy (:472).
-        x_all = torch.tensor([x for x, _ in training_data], dtype=torch.float64)
-        x_all = x_all.to(eng.tdtype).to(eng.device).contiguous()
+        x_all = self._inputs_to_device(eng, torch.tensor([x for x, _ in training_data], dtype=torch.float64))
         t_all = self._targets_to_device(eng, [t for _, t in training_data], True)
         stride = max(1, epochs // 100)                                      # :504
         eng.train_begin(optimizer="adam" if self.optimizer is not None else "sgd",
@@ -461,20 +569,38 @@ class NeuralNetworkModel(MultiLayerPerceptron):
             log.info(f"Model {self.model_id}: Epoch {epoch + 1}, Cost: {cost:.4f}")
         return upto
 
-    _SATURATION_RULE = {"tanh": (1, 0.97), "sigmoid": (1, 0.97), "relu": (2, 0.0), "softmax": (3, 0.97)}
+    # saturation rule per entry type (neural_net_model.py:556-561): (rule code, threshold)
+    _SATURATION_RULE = {"tanh": (1, 0.97), "sigmoid": (1, 0.97), "relu": (2, 0.0), "softmax": (3, 0.97),
+                        "batchnorm": (1, 3.0), "embedding": (4, 5.0)}
+
+    def _entry_locations(self, spec: StackSpec) -> dict:
+        """entry index -> (layer, which) of the device tensor holding its recorded output.  A
+        flatten entry is a view of the tensor in front of it."""
+        loc = {}
+        if spec.emb_index is not None:
+            loc[spec.emb_index] = (-1, 0)
+            for i in spec.emb_flat:
+                loc[i] = (-1, 0)
+        for l in range(spec.n_linear):
+            loc[spec.z_index[l]] = last = (l, 0)
+            if spec.bn_index[l] is not None:
+                loc[spec.bn_index[l]] = last = (l, 2)
+            if spec.a_index[l] is not None:
+                loc[spec.a_index[l]] = last = (l, 1)
+            for i in spec.flat_after[l]:
+                loc[i] = last
+        return loc
 
     def _device_statistics(self, eng: DeviceMLP) -> tuple[list, list]:
         """Statistics of the last diagnostics step (neural_net_model.py:542-583), reduced on the
         device: per entry the output's mean / std / saturation / density histogram and the same for
-        its gradient; per weight matrix its mean / std and its gradient's mean / std / histogram."""
+        its gradient; per weight tensor its mean / std and its gradient's mean / std / histogram."""
         spec = self.stack
+        loc = self._entry_locations(spec)
         layer_stats, weight_stats = [], []
         for i, layer in enumerate(self.layers):
-            if layer.algo == "linear":
-                li, which = spec.z_index.index(i), 0
-            else:
-                li, which = spec.a_index.index(i), 1
-            rule, thr = self._SATURATION_RULE.get(layer.algo, (1, 5.0))          # :556-561
+            li, which = loc[i]
+            rule, thr = self._SATURATION_RULE.get(layer.algo, (1, 5.0))
             act = eng.diag_stats(li, which, 0, rule, thr)
             grad = eng.diag_stats(li, which, 1)
             layer_stats.append({

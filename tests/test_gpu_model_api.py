@@ -152,3 +152,27 @@ def test_params_edited_on_host_are_picked_up():
     model.layers[0].state_dict = {"params": [[[1.0] * 3] * 4, [0.0] * 3]}
     c, _ = model.compute_output(x)
     np.testing.assert_allclose(c, [1 / (1 + np.exp(-1.0))] * 3, rtol=1e-5)
+
+
+NET_TRAIN_TABLE = [   # the remaining rows of test_neural_net_model.py:180-185 and the model of test_torch_backward.py
+    ([9, 2, 6, 18, 9], ["embedding", "tanh", "softmax"], "adam", 1.0, [0, 5, 7], [5]),
+    ([9, 2, 6, 18, 9], ["embedding", "linear", "batchnorm", "tanh", "softmax"], None, 1.0, [0, 5, 7], [5]),
+    ([9, 2, 4, 9, 18, 9], ["embedding", "linear", "batchnorm", "tanh", "flatten", "linear", "softmax"], None, 0.1,
+     [0, 5, 7, 8], [5]),
+    ([27, 10, 30, 64, 27], ["embedding", "linear", "batchnorm", "tanh", "linear", "softmax"], "adam", 1.0, [1, 2, 3], [4]),
+]
+
+
+@pytest.mark.parametrize("sizes,algos,optimizer,confidence,sample_input,target", NET_TRAIN_TABLE)
+def test_reference_test_train_flow_with_embedding_and_batchnorm(sizes, algos, optimizer, confidence, sample_input,
+                                                                target, workdir):
+    test_reference_test_train_flow(sizes, algos, optimizer, confidence, sample_input, target, workdir)
+
+
+@pytest.mark.parametrize("sizes,algos,sample_input,target", [
+    ([9, 2, 6, 18, 9], ["embedding", "tanh", "softmax"], [0, 5, 8], [2]),
+    ([9, 2, 6, 18, 9], ["embedding", "tanh", "softmax"], [[0, 5, 8], [1, 3, 7]], [[2], [4]]),
+    ([9, 2, 4, 9, 18, 9], ["embedding", "tanh", "flatten", "linear", "softmax"], [[0, 5, 8, 2], [1, 3, 7, 4]], [[2], [4]]),
+])
+def test_reference_test_compute_output_flow_with_embedding(sizes, algos, sample_input, target):
+    test_reference_test_compute_output_flow(sizes, algos, sample_input, target)

@@ -490,6 +490,126 @@ def cpu_train_wide(seconds, batch=1024, threads=None):
     return batch * n / el, n, threads, el, batch
 
 
+EMB_SIZES = [27, 10, 30, 200, 27]
+EMB_ALGOS = ["embedding", "flatten", "linear", "batchnorm", "tanh", "linear", "softmax"]
+EMB_TOKENS, EMB_BATCH = 3, 32768
+
+
+def emb_params(seed=0):
+    rng = np.random.default_rng(seed)
+    return [rng.standard_normal((27, 10)), rng.standard_normal((30, 200)) / np.sqrt(30), np.zeros(200),
+            np.ones(200), np.zeros(200), rng.standard_normal((200, 27)) / np.sqrt(200), np.zeros(27)]
+
+
+def run_emb(args, world, rank, local):
+    """character-level model of the reference's own gradient test
+    (test_torch_backward.py:121-135, hidden width 200): embedding -> Linear -> batchnorm -> tanh -> Linear ->
+    softmax + cross-entropy, Adam, batch 32768 x 3 tokens, fp32 train step."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec, launch_count
+    dev = torch.device("cuda", local)
+    spec = StackSpec.from_algos(EMB_ALGOS, {1: 3})
+    eng = DeviceMLP([(30, 200), (200, 27)], spec, True, "float32", local, embedding=(27, 10), batchnorm=[(1e-5, 0.1), None])
+    p = emb_params()
+    eng.upload_tensor("embedding", 0, p[0])
+    eng.upload_tensor("weight", 0, p[1]); eng.upload_tensor("bias", 0, p[2])
+    eng.upload_tensor("bn_gain", 0, p[3]); eng.upload_tensor("bn_bias", 0, p[4])
+    eng.upload_tensor("weight", 1, p[5]); eng.upload_tensor("bias", 1, p[6])
+    batch, n_pool = args.batch or EMB_BATCH, 8
+    g = torch.Generator(device=dev).manual_seed(5 + rank)
+    xs = torch.randint(0, 27, (n_pool, batch, EMB_TOKENS), generator=g, device=dev, dtype=torch.int32)
+    ys = torch.randint(0, 27, (n_pool, batch), generator=g, device=dev, dtype=torch.int32)
+    side = torch.cuda.Stream(device=dev)
+    torch.cuda.synchronize()
+    torch.cuda.set_stream(side)
+    pre = 2 * n_pool
+    eng.train_begin(optimizer="adam", epochs=pre + args.warmup + args.steps + 8, **HP)
+    for i in range(pre + args.warmup):
+        eng.train_step(xs[i % n_pool], ys[i % n_pool])
+    barrier_sync(world)
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    l0 = launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        eng.train_step(xs[i % n_pool], ys[i % n_pool])
+    e1.record()
+    barrier_sync(world)
+    launches = launch_count() - l0
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    assert np.isfinite(eng.costs(pre + args.warmup, args.steps)).all()
+    # e2e: pinned host indices + labels in, cost out, per step
+    hx, hy = xs[0].cpu().pin_memory(), ys[0].cpu().pin_memory()
+    xd, yd = torch.empty_like(xs[0]), torch.empty_like(ys[0])
+    n_e2e = max(10, min(args.steps, 100))
+    eng.train_begin(optimizer="adam", epochs=n_e2e + 16, **HP)
+    for i in range(4):
+        xd.copy_(hx, non_blocking=True); yd.copy_(hy, non_blocking=True); eng.train_step(xd, yd)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(n_e2e):
+        xd.copy_(hx, non_blocking=True); yd.copy_(hy, non_blocking=True)
+        eng.train_step(xd, yd)
+    last = float(eng.costs(4 + n_e2e - 1, 1)[0])
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    assert np.isfinite(last)
+    clocks = sampler.stop() if sampler else None
+    roof = None
+    if rank == 0:
+        pk = peaks()
+        eng.train_begin(optimizer="adam", epochs=32, **HP)
+        eng.train_step(xs[0], ys[0])
+        eng.profile_begin()
+        for i in range(10):
+            eng.train_step(xs[i % n_pool], ys[i % n_pool])
+        prof = eng.profile_end()
+        tot = sum(v["ms"] for v in prof.values())
+        top = max(prof, key=lambda k: prof[k]["ms"])
+        # algorithmic HBM bytes of a step: indices + labels in, Adam read/write of all parameters
+        n_par = 27 * 10 + 31 * 200 + 400 + 201 * 27
+        step_bytes = batch * (EMB_TOKENS * 4 + 4) + 6 * n_par * 4
+        per = ms / args.steps * 1e-3
+        roof = {"bound": "hbm", "kernel": "whole step (11 kernels; activations of one batch stay in L2)",
+                "achieved": round(step_bytes / per / 1e9, 2), "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": round(step_bytes / per / 1e9 / pk["hbm_gbs"], 5), "traffic": None, "peak_source": pk["source"],
+                "top_kernel": top, "share_of_step": round(prof[top]["ms"] / tot, 3),
+                "algorithmic_bytes_per_step": step_bytes,
+                "fp32_fma": {"flops_per_sample": 2 * 3 * (31 * 200 + 201 * 27),
+                             "achieved_tflops": round(batch * 6 * (31 * 200 + 201 * 27) / per / 1e12, 2),
+                             "nominal_peak_tflops": 74.4},
+                "kernels_us": {k: round(v["ms"] / v["launches"] * 1e3, 2) for k, v in prof.items()}}
+    eng.close()
+    return dict(metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=world * batch * args.steps / (ms * 1e-3),
+                ms_per_step=ms / args.steps,
+                e2e={"value": world * batch * n_e2e / (e2e_ms * 1e-3), "unit": "samples/s",
+                     "h2d_bytes_per_step": batch * (EMB_TOKENS + 1) * 4, "d2h_bytes_per_step": 8,
+                     "ms_per_step": e2e_ms / n_e2e},
+                gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
+                config={"workload": "emb: embedding(27x10) -> Linear 30->200 -> batchnorm -> tanh -> Linear 200->27 -> softmax + "
+                                    "cross-entropy, Adam, L2 1e-3, batch 32768 x 3 tokens, fp32 train step",
+                        "batch_per_gpu": batch, "global_batch": batch * world,
+                        "parallelism": f"replicas x{world}" if world > 1 else "single", "dropout": 0.0,
+                        "l2_flush": "inputs are 0.5 MB per step; the step is bound by its ~90 MB of activation traffic, "
+                                    "which stays in L2"})
+
+
+def cpu_train_emb(seconds, batch=EMB_BATCH, threads=None):
+    from oracle.torch_cpu_port import TorchCpuMLP
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    m = TorchCpuMLP(EMB_ALGOS, emb_params(), "adam", flatten_ratios=[3])
+    x = torch.randint(0, 27, (batch, EMB_TOKENS)).double()
+    y = torch.randint(0, 27, (batch,), dtype=torch.int64)
+    m.train_step(x, y, 0.01, l2_lambda=0.001)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        m.train_step(x, y, 0.01, l2_lambda=0.001)
+        n += 1
+        el = time.perf_counter() - t0
+        if el >= seconds:
+            break
+    return batch * n / el, n, threads, el, batch
+
+
 # ---- CPU arms -------------------------------------------------------------------------------------------
 def cpu_train_c2(seconds, max_steps=None, threads=None):
     """The reference's torch-CPU path (oracle/torch_cpu_port.py, fp64 as the reference ships) at C2
@@ -543,6 +663,15 @@ def run_reference(args, world, rank):
                     cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
                                   "sample": f"{n} forward passes of {b} rows, torch CPU fp64 (oracle/torch_cpu_port.py)"},
                     e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+    if args.workload == "emb":
+        v, n, thr, el, b = cpu_train_emb(10.0, args.batch or EMB_BATCH)
+        return dict(impl="reference", metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v,
+                    n_gpus=args.gpus, steps=n, warmup=1, ms_per_step=el / n * 1e3, higher_is_better=True,
+                    scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
+                    config={"workload": "emb: embedding + batchnorm character model, train step"},
+                    cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
+                                  "sample": f"{n} train steps of batch {b}, torch CPU fp64 (oracle/torch_cpu_port.py)"},
+                    e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
     if args.workload in ("c4", "c5"):
         v, n, thr, el, b = cpu_train_wide(10.0)
         return dict(impl="reference", metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v,
@@ -572,7 +701,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "emb"])
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -588,14 +717,20 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback); "
                          "use --impl reference for the CPU arm")
-    if args.workload in ("c4", "c5"):
+    if args.workload == "emb":
+        res = run_emb(args, world, rank, local)
+    elif args.workload in ("c4", "c5"):
         res = run_wide(args, world, rank, local, dp=args.workload == "c5")
     else:
         res = (run_c2 if args.workload == "c2" else run_c3)(args, world, rank, local)
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            if args.workload in ("c4", "c5"):
+            if args.workload == "emb":
+                v, n, thr, el, b = cpu_train_emb(10.0, args.batch or EMB_BATCH)
+                cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
+                       "sample": f"{n} train steps of batch {b} in {el:.1f} s, torch CPU fp64 (oracle/torch_cpu_port.py)"}
+            elif args.workload in ("c4", "c5"):
                 v, n, thr, el, b = cpu_train_wide(10.0)
                 cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
                        "sample": f"{n} train steps of a REDUCED batch of {b} rows in {el:.1f} s, torch CPU fp64; "

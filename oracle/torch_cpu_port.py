@@ -17,28 +17,70 @@ import torch.nn.functional as F
 
 
 class TorchCpuMLP:
-    def __init__(self, algos, params, optimizer="adam"):
-        """algos: expanded entry list; params: flat [W0,(b0),W1,(b1)...] float64 arrays/tensors."""
+    def __init__(self, algos, params, optimizer="adam", flatten_ratios=None, batchnorm=(1e-5, 0.1)):
+        """algos: expanded entry list; params: flat list in the reference's `params` order (embedding
+        table, Linear W (b), batchnorm gain, bias ...) as float64 arrays/tensors; flatten_ratios: ratio
+        per flatten entry, in order."""
         self.algos = list(algos)
         n = len(self.algos)
         self.hidden = [0 < i < n - 1 for i in range(n)]                     # :255
         self.params = [torch.as_tensor(p, dtype=torch.float64).clone() for p in params]
         n_lin = sum(1 for a in self.algos if a == "linear")
-        self.has_bias = len(self.params) == 2 * n_lin
+        n_other = sum(1 for a in self.algos if a == "embedding") + 2 * sum(1 for a in self.algos if a == "batchnorm")
+        self.has_bias = len(self.params) - n_other == 2 * n_lin
+        self.ratios = list(flatten_ratios or [])
+        self.eps, self.momentum = batchnorm
+        self.running = {}                                                   # entry index -> [mean, variance]
+        self.weight_idx = []
+        k = 0
+        for i, a in enumerate(self.algos):
+            if a == "embedding":
+                self.weight_idx.append(k); k += 1
+            elif a == "linear":
+                self.weight_idx.append(k); k += 2 if self.has_bias else 1
+            elif a == "batchnorm":
+                dim = self.params[k].shape[0]
+                self.running[i] = [torch.zeros(dim, dtype=torch.float64), torch.ones(dim, dtype=torch.float64)]
+                k += 2
         self.optimizer = torch.optim.Adam(self.params) if optimizer == "adam" else None   # :281-282
 
     @property
     def weights(self):
-        return self.params[::2] if self.has_bias else self.params
+        return [self.params[k] for k in self.weight_idx]
 
     def forward(self, x, target=None, dropout_rate=0.0):
         """:384-408 -- returns (entry outputs, cost)."""
         training = target is not None
         outs, cur, logits = [], x, x
         it = iter(self.params)
-        for algo, hidden in zip(self.algos, self.hidden):
+        ratios = iter(self.ratios)
+        for i, (algo, hidden) in enumerate(zip(self.algos, self.hidden)):
             logits = cur
-            if algo == "linear":
+            if algo == "embedding":                                          # :68
+                cur = next(it)[logits.long()]
+            elif algo == "flatten":                                          # :82-91
+                ratio = next(ratios)
+                if logits.ndim > 1:
+                    shp = list(logits.shape)
+                    shp[-2] //= ratio
+                    shp[-1] *= ratio
+                    cur = logits.view(*shp)
+                    if shp[-2] == 1:
+                        cur = cur.squeeze(len(shp) - 2)
+            elif algo == "batchnorm":                                        # :158-170
+                gain, bias = next(it), next(it)
+                if training:
+                    dim = tuple(range(logits.ndim - 1))
+                    mean = logits.mean(dim, keepdim=True)
+                    var = logits.var(dim, keepdim=True)
+                    with torch.no_grad():
+                        run = self.running[i]
+                        run[0] = (1 - self.momentum) * run[0] + self.momentum * mean
+                        run[1] = (1 - self.momentum) * run[1] + self.momentum * var
+                else:
+                    mean, var = self.running[i]
+                cur = gain * (logits - mean) / torch.sqrt(var + self.eps) + bias
+            elif algo == "linear":
                 cur = logits @ next(it)
                 if self.has_bias:
                     cur += next(it)

@@ -1183,6 +1183,12 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
     }
     if (cudaMemset(c->P, 0, pbytes) != cudaSuccess || cudaMemset(c->AM, 0, pbytes) != cudaSuccess ||
         cudaMemset(c->AV, 0, pbytes) != cudaSuccess) { set_error("cudaMemset failed"); return fail(); }
+    {
+        int widest_bn = 0;
+        for (int l = 0; l < n_linear; ++l) if (c->has_bn[l]) widest_bn = std::max(widest_bn, c->sizes[l + 1]);
+        if (widest_bn && dev_alloc(reinterpret_cast<void**>(&c->bn_part), (size_t)BN_ROW_SPLITS * 2 * widest_bn * sizeof(double)))
+            return fail();
+    }
     for (int l = 0; l < n_linear; ++l)
         if (c->has_bn[l]) {
             const size_t nb = (size_t)2 * c->sizes[l + 1] * c->esz;
@@ -1243,6 +1249,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     for (auto& p : c->dybuf) dev_free(p);
     for (auto& p : c->dy_rec) dev_free(p);
     dev_free(c->ebuf); dev_free(c->debuf); dev_free(c->de_rec);
+    dev_free(reinterpret_cast<void*&>(c->bn_part));
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
     dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
     dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz);

@@ -48,6 +48,7 @@ struct poz_ctx {
     std::vector<void*> bn_run;        // running [mean; variance] of layer l
     std::vector<void*> bn_stat;       // [mean; 1/std] used by the current step
     std::vector<void*> bn_sums;       // backward column sums
+    double* bn_part = nullptr;        // partial column sums [BN_ROW_SPLITS][2][widest batchnorm]
     std::vector<void*> ybuf, dybuf, dy_rec;   // batchnorm output (diagnostics), its pre-dropout gradient
     void* ebuf = nullptr;             // embedding output [batch*tokens][emb_dim]
     void* debuf = nullptr;            // its gradient

@@ -50,45 +50,76 @@ __global__ void emb_scatter_kernel(const T* __restrict__ dE, const int* __restri
     }
 }
 
-// Batch statistics of z [R][N] per column: stat[n] = mean, stat[N+n] = 1/sqrt(var_unbiased + eps);
-// with `update` the running statistics follow (neural_net_model.py:161-166).  With `use_running`
-// the running statistics are used instead (inference, :167-168).  One block per 32 columns;
-// 8 warps stride over the rows, each reading 32 consecutive columns.
+constexpr int BN_ROW_SPLITS = 128;   // row splits of the batchnorm column reductions
+
+// Column reductions over the rows of a [R][N] matrix, two deterministic passes.  Pass 1: block
+// (x, y) covers 32 columns and the rows y*8+warp, +8*gridDim.y, ...; each warp reads 32 consecutive
+// columns of a row.  mode 0: partial sums of z and z^2; mode 1: partial sums of gy and gy * xhat.
 template <typename T>
-__global__ void bn_stats_kernel(const T* __restrict__ z, long long R, int N, T* __restrict__ stat,
-                                T* __restrict__ run_mean, T* __restrict__ run_var, double eps, double momentum,
-                                int use_running, int update) {
+__global__ void bn_col_partial_kernel(const T* __restrict__ a, const T* __restrict__ z, const T* __restrict__ stat,
+                                      long long R, int N, int mode, double* __restrict__ partial /*[gridDim.y][2][N]*/) {
     __shared__ double s1[8][32], s2[8][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = blockIdx.x * 32 + lane;
-    if (use_running) {
-        if (warp == 0 && n < N) {
-            stat[n] = run_mean[n];
-            stat[N + n] = (T)(1.0 / sqrt((double)run_var[n] + eps));
+    double p = 0.0, q = 0.0;
+    if (n < N) {
+        const double mean = mode ? (double)stat[n] : 0.0, inv = mode ? (double)stat[N + n] : 0.0;
+        for (long long r = (long long)blockIdx.y * 8 + warp; r < R; r += (long long)gridDim.y * 8) {
+            const double v = (double)a[r * N + n];
+            p += v;
+            q += mode ? v * (((double)z[r * N + n] - mean) * inv) : v * v;
         }
-        return;
     }
-    double a = 0.0, b = 0.0;
-    if (n < N)
-        for (long long r = warp; r < R; r += 8) {
-            const double v = (double)z[r * N + n];
-            a += v; b += v * v;
-        }
-    s1[warp][lane] = a; s2[warp][lane] = b;
+    s1[warp][lane] = p; s2[warp][lane] = q;
     __syncthreads();
     if (warp == 0 && n < N) {
         double sa = 0.0, sb = 0.0;
 #pragma unroll
         for (int w = 0; w < 8; ++w) { sa += s1[w][lane]; sb += s2[w][lane]; }
-        const double mean = sa / (double)R;
-        const double var = (sb - (double)R * mean * mean) / (double)(R - 1);   // unbiased (:162)
-        stat[n] = (T)mean;
-        stat[N + n] = (T)(1.0 / sqrt(var + eps));
-        if (update) {
-            run_mean[n] = (T)((1.0 - momentum) * (double)run_mean[n] + momentum * mean);
-            run_var[n] = (T)((1.0 - momentum) * (double)run_var[n] + momentum * var);
-        }
+        partial[((long long)blockIdx.y * 2) * N + n] = sa;
+        partial[((long long)blockIdx.y * 2 + 1) * N + n] = sb;
     }
+}
+
+// Pass 2 of the forward statistics: stat[n] = mean, stat[N+n] = 1/sqrt(var_unbiased + eps); with
+// `update` the running statistics follow (neural_net_model.py:161-166); with `use_running` the running
+// statistics are used instead (inference, :167-168).
+template <typename T>
+__global__ void bn_stats_final_kernel(const double* __restrict__ partial, int parts, long long R, int N,
+                                      T* __restrict__ stat, T* __restrict__ run_mean, T* __restrict__ run_var,
+                                      double eps, double momentum, int use_running, int update) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    if (use_running) {
+        stat[n] = run_mean[n];
+        stat[N + n] = (T)(1.0 / sqrt((double)run_var[n] + eps));
+        return;
+    }
+    double sa = 0.0, sb = 0.0;
+    for (int k = 0; k < parts; ++k) { sa += partial[((long long)k * 2) * N + n]; sb += partial[((long long)k * 2 + 1) * N + n]; }
+    const double mean = sa / (double)R;
+    const double var = (sb - (double)R * mean * mean) / (double)(R - 1);   // unbiased (:162)
+    stat[n] = (T)mean;
+    stat[N + n] = (T)(1.0 / sqrt(var + eps));
+    if (update) {
+        run_mean[n] = (T)((1.0 - momentum) * (double)run_mean[n] + momentum * mean);
+        run_var[n] = (T)((1.0 - momentum) * (double)run_var[n] + momentum * var);
+    }
+}
+
+// Pass 2 of the backward reductions: sums[n] = sum_r gy, sums[N+n] = sum_r gy * xhat; they are also
+// d_bias and d_gain (test_torch_backward.py:172-173), written to grad_out = [d_gain; d_bias].
+template <typename T>
+__global__ void bn_bwd_final_kernel(const double* __restrict__ partial, int parts, int N, T* __restrict__ sums,
+                                    T* __restrict__ grad_out) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    double sa = 0.0, sb = 0.0;
+    for (int k = 0; k < parts; ++k) { sa += partial[((long long)k * 2) * N + n]; sb += partial[((long long)k * 2 + 1) * N + n]; }
+    sums[n] = (T)sa;
+    sums[N + n] = (T)sb;
+    grad_out[n] = (T)sb;          // d_gain
+    grad_out[N + n] = (T)sa;      // d_bias
 }
 
 // y = gain * (z - mean) * inv + bias -> dropout -> recorded y -> activation -> dropout -> recorded a
@@ -107,36 +138,6 @@ __global__ void bn_apply_kernel(const T* __restrict__ z, const T* __restrict__ s
         T a = act_fwd<T>(act, y);
         if (da.enabled) a = drop_keep(da, st, r, n, N) ? a * T(da.scale) : T(0);
         if (a_out) a_out[i] = a;
-    }
-}
-
-// Column reductions of the batchnorm backward: sums[n] = sum_r gy, sums[N+n] = sum_r gy * xhat;
-// they are also d_bias and d_gain (test_torch_backward.py:172-173), written to grad_out = [d_gain; d_bias].
-template <typename T>
-__global__ void bn_bwd_reduce_kernel(const T* __restrict__ gy, const T* __restrict__ z, const T* __restrict__ stat,
-                                     long long R, int N, T* __restrict__ sums, T* __restrict__ grad_out) {
-    __shared__ double s1[8][32], s2[8][32];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int n = blockIdx.x * 32 + lane;
-    double a = 0.0, b = 0.0;
-    if (n < N) {
-        const double mean = (double)stat[n], inv = (double)stat[N + n];
-        for (long long r = warp; r < R; r += 8) {
-            const double g = (double)gy[r * N + n];
-            a += g;
-            b += g * (((double)z[r * N + n] - mean) * inv);
-        }
-    }
-    s1[warp][lane] = a; s2[warp][lane] = b;
-    __syncthreads();
-    if (warp == 0 && n < N) {
-        double sa = 0.0, sb = 0.0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) { sa += s1[w][lane]; sb += s2[w][lane]; }
-        sums[n] = (T)sa;
-        sums[N + n] = (T)sb;
-        grad_out[n] = (T)sb;          // d_gain
-        grad_out[N + n] = (T)sa;      // d_bias
     }
 }
 

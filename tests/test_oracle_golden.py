@@ -192,3 +192,22 @@ def test_net_oracle_matches_reference(name):
     check_against(arrays, "infer_out", outs[-1], 1e-9, 1e-12)
     outs1, _, _ = no.forward(entries, x[0], training=False)
     check_against(arrays, "infer_out_1d", outs1[-1], 1e-9, 1e-12)
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names("net_") if "dropout" not in n])
+def test_torch_cpu_port_general_stacks_match_reference(name):
+    import torch
+    from oracle import net_oracle as no
+    from oracle.torch_cpu_port import TorchCpuMLP
+    arrays, meta = load_golden(name)
+    entries, x, target = net_case_inputs(meta)
+    params = net_det_params(entries, meta["salt"])
+    ratios = [e.ratio for e in entries if e.algo == "flatten"]
+    m = TorchCpuMLP(meta["expanded_algos"], params, meta["optimizer"] or "sgd", flatten_ratios=ratios)
+    xt = torch.tensor(x)
+    tt = (torch.tensor([t[0] for t in target], dtype=torch.int64) if meta["expanded_algos"][-1] == "softmax"
+          else torch.tensor(target, dtype=torch.float64))
+    costs = [m.train_step(xt, tt, meta["lr"] * meta["decay"] ** s, l2_lambda=meta["l2"]) for s in range(meta["steps"])]
+    np.testing.assert_allclose(costs, arrays["costs"], rtol=1e-10)
+    for i, q in enumerate(m.params):
+        check_against(arrays, f"param{i}", q.detach().numpy(), 1e-8, 1e-9)

@@ -45,6 +45,12 @@ def init_params(sizes, seed=0):
     return out
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures committed under
+# profiles/ncu/ (r01_c2_simt_full_raw.csv, r01_c4_tc_fwd_full_raw.csv); null where no capture exists.
+NCU_TRAFFIC = {"fwd_l0": 4_081_152, "bwd_w_l0": 4_301_568, "fwd_l1": 1_246_208, "bwd_w_l1": 1_614_592,
+               "bwd_x_l1": 1_769_472, "tc_fwd": 1_204_000_000}
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -260,7 +266,9 @@ def run_c2(args, world, rank, local):
         nbytes, flops = kernel_work(top, batch)
         gbs = nbytes / per_launch_s / 1e9
         roof = {"bound": "hbm", "kernel": top, "achieved": round(gbs, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
-                "frac": round(gbs / pk["hbm_gbs"], 4), "traffic": None, "peak_source": pk["source"],
+                "frac": round(gbs / pk["hbm_gbs"], 4), "traffic": NCU_TRAFFIC.get(top),
+                "traffic_source": "ncu --set full, profiles/ncu/r01_c2_simt_full_raw.csv" if top in NCU_TRAFFIC else None,
+                "peak_source": pk["source"],
                 "us_per_launch": round(per_launch_s * 1e6, 2), "share_of_step": round(prof[top]["ms"] / tot, 3),
                 "algorithmic_bytes_per_launch": nbytes,
                 "fp32_fma": {"achieved_tflops": round(flops / per_launch_s / 1e12, 2), "nominal_peak_tflops": 74.4,
@@ -447,7 +455,9 @@ def run_wide(args, world, rank, local, dp):
             top, tf, per, tot, prof, kern = "whole step", 0.0, 0.0, 1.0, {}, {}
         step_tf = WIDE_FLOPS_PER_SAMPLE * batch / (ms / args.steps * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": top, "achieved": round(tf, 1), "peak": pk["bf16_tflops_sustained"],
-                "unit": "TFLOP/s", "frac": round(tf / pk["bf16_tflops_sustained"], 4), "traffic": None,
+                "unit": "TFLOP/s", "frac": round(tf / pk["bf16_tflops_sustained"], 4),
+                "traffic": NCU_TRAFFIC["tc_fwd"] if top.startswith("tc_fwd") else None,
+                "traffic_source": "ncu --set full, profiles/ncu/r01_c4_tc_fwd_full_raw.csv (algorithmic 1.107e9 B)",
                 "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",
                 "frac_of_burst_peak": round(tf / pk["bf16_tflops"], 4),
                 "share_of_step": round(prof[top]["ms"] / tot, 3) if prof else None,

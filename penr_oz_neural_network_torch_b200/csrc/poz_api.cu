@@ -701,10 +701,15 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         POZ_LAUNCH_CHECK();
     }
 
+    // narrow classifier head: last Linear + softmax/CE + its backward-x in one kernel (head_ce_kernel)
+    const int head_K = c->sizes[nl - 1], head_N = c->sizes[nl];
+    const size_t head_smem = ((size_t)head_K * (head_N | 1) + 32 + 8 * (size_t)head_K) * sizeof(T);
+    const bool fuse_head = c->fuse_head && nl >= 2 && c->loss == POZ_LOSS_CE && head_N <= 32 && head_smem <= 96 * 1024;
+
     // forward, keeping what the backward needs (and, for diagnostics, every entry's output)
     const T* cur = x;
     const int* cur_idx = row_idx;
-    for (int l = 0; l < nl; ++l) {
+    for (int l = 0; l < (fuse_head ? nl - 1 : nl); ++l) {
         T* zb = static_cast<T*>(c->zbuf[l]);
         T* ab = static_cast<T*>(c->abuf[l]);
         const int act = c->acts[l];
@@ -741,7 +746,36 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     const long long gb = c->cfg.global_batch > 0 ? c->cfg.global_batch : batch;
     const int last = nl - 1;
     const int n_out = c->sizes[nl];
-    {
+    if (fuse_head) {
+        const int p = last - 1;
+        HeadArgs<T> h{};
+        h.a_prev = cur;
+        h.wb = static_cast<const T*>(c->P) + c->off[last];
+        h.labels = static_cast<const int*>(target); h.row_idx = row_idx;
+        h.dz_pre = static_cast<T*>(c->dzbuf[last]);
+        h.dprev_pre = static_cast<T*>(c->dzbuf[p]);
+        if (diag) {
+            h.z_rec = static_cast<T*>(c->zbuf[last]); h.probs = static_cast<T*>(c->abuf[last]);
+            h.dz_rec = static_cast<T*>(c->dz_rec[last]);
+            if (c->acts[p] != ACT_NONE) { h.da_rec = static_cast<T*>(c->da_rec[p]); h.dzprev_rec = static_cast<T*>(c->dz_rec[p]); }
+            else h.dzprev_rec = static_cast<T*>(c->dz_rec[p]);
+        }
+        h.M = batch; h.K = head_K; h.N = head_N; h.has_bias = c->has_bias; h.act_prev = c->acts[p];
+        h.dz_last = make_drop(c, last, 0, masks);
+        h.da_prev = make_drop(c, p, 1, masks);
+        h.dz_prev = make_drop(c, p, 0, masks);
+        h.inv_batch = 1.0 / (double)gb;
+        h.cost_base = c->cost_ring; h.cost_cap = c->cost_cap; h.st = c->st;
+        static bool configured[2] = {false, false};
+        if (!configured[sizeof(T) == 8]) {
+            POZ_CUDA(cudaFuncSetAttribute(head_ce_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+            configured[sizeof(T) == 8] = true;
+        }
+        ProfScope ps(c, "head", stream);
+        const int blocks = (int)std::max<long long>(1, std::min<long long>((batch + 7) / 8, 2LL * num_sms(c->device)));
+        head_ce_kernel<T><<<blocks, 256, head_smem, stream>>>(h);
+        POZ_LAUNCH_CHECK();
+    } else {
         LossArgs<T> a{};
         a.z = cur; a.target = target; a.row_idx = row_idx;
         a.M = batch; a.N = n_out; a.act = c->acts[last];
@@ -822,7 +856,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
                                                   seg.splits[l], kchunk[l], epi, stream)));
             if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
         }
-        if (l > 0) {
+        if (l > 0 && !(fuse_head && l == last)) {
             const T* w = static_cast<const T*>(c->P) + c->off[l];
             Operand<T> A = make_operand<T>(dz, N, nullptr, batch, N, 0);
             Operand<T> B = make_operand<T>(w, N, nullptr, K, N, 0);
@@ -1172,6 +1206,7 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
     c->max_splits = 16;
     if (const char* e = getenv("POZ_TC3_MIN_BATCH")) c->tc3_min_batch = atoll(e);
     if (const char* e = getenv("POZ_GRAPHS")) c->graphs_enabled = atoi(e) != 0;
+    if (const char* e = getenv("POZ_FUSE_HEAD")) c->fuse_head = atoi(e) != 0;
     if (const char* e = getenv("POZ_TC3_TRAIN")) c->tc3_train = atoi(e) != 0;
     if (const char* e = getenv("POZ_TC3_TRAIN_MIN_BATCH")) c->tc3_train_min_batch = atoll(e);
     auto fail = [&](void) { poz_ctx_destroy(c); return 1; };

@@ -87,6 +87,7 @@ struct poz_ctx {
     };
     std::vector<StepGraph> graphs;
     bool graphs_enabled = true;
+    bool fuse_head = true;            // narrow softmax head in one kernel (POZ_FUSE_HEAD=0 disables)
     double graph_sig[6] = {0, 0, 0, 0, 0, 0};
 
     poz_train_config cfg;

@@ -387,3 +387,98 @@ __global__ void convert_kernel(const S* __restrict__ src, D* __restrict__ dst, l
 }
 
 }  // namespace poz
+
+namespace poz {
+
+// ---- fused classifier head -----------------------------------------------------------------------------
+// For stacks that end in a narrow Linear + softmax (out <= 32) one kernel does, per batch row, what would
+// otherwise be three launches at a few percent occupancy: the last Linear (neural_net_model.py:117-119),
+// softmax + cross-entropy + its gradient (:188,:400-403, test_torch_backward.py:163-164) and the
+// backward-x of that Linear pushed through the previous unit's dropout / activation
+// (test_torch_backward.py:168-170).  The last layer's [W; b] lives in shared memory (row pitch made odd
+// so that the backward's column walk is bank-conflict free); one warp owns one row: lane n accumulates
+// logit n over k with the row broadcast from shared memory, then lanes take k = lane, lane+32, ... for dA.
+template <typename T> struct HeadArgs {
+    const T* a_prev;       // recorded output of the previous unit [M][K]
+    const T* wb;           // [K+1][N] = [W; b] of the last layer (bias row only if has_bias)
+    const int* labels;     // int32 labels
+    const int* row_idx;    // gather of label rows (nullable)
+    T* z_rec;              // recorded logits (nullable)
+    T* probs;              // softmax output (nullable)
+    T* dz_pre;             // gradient of the last Linear's pre-dropout output [M][N]
+    T* dz_rec;             // diagnostics (nullable)
+    T* dprev_pre;          // gradient of the previous unit's pre-dropout linear output [M][K]
+    T* da_rec;             // diagnostics (nullable): gradient of the previous unit's recorded activation
+    T* dzprev_rec;         // diagnostics (nullable): gradient of the previous unit's recorded linear output
+    long long M;
+    int K, N, has_bias, act_prev;
+    DropPoint dz_last, da_prev, dz_prev;
+    double inv_batch;
+    double* cost_base;
+    long long cost_cap;
+    const DevState* st;
+};
+
+template <typename T> __global__ void __launch_bounds__(256) head_ce_kernel(HeadArgs<T> a) {
+    extern __shared__ __align__(16) unsigned char head_smem[];
+    T* W = reinterpret_cast<T*>(head_smem);
+    const int Ns = a.N | 1;                                  // odd row pitch
+    T* bias = W + (long long)a.K * Ns;
+    T* rows = bias + 32;                                     // [8 warps][K]
+    for (int i = threadIdx.x; i < a.K * a.N; i += blockDim.x) W[(i / a.N) * Ns + (i % a.N)] = a.wb[i];
+    for (int i = threadIdx.x; i < 32; i += blockDim.x) bias[i] = (a.has_bias && i < a.N) ? a.wb[(long long)a.K * a.N + i] : T(0);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    T* arow = rows + (long long)warp * a.K;
+    const T invb = T(a.inv_batch);
+    double local = 0.0;
+    for (long long m = (long long)blockIdx.x * wpb + warp; m < a.M; m += (long long)gridDim.x * wpb) {
+        const T* ap = a.a_prev + m * a.K;
+        for (int k = lane; k < a.K; k += 32) arow[k] = ap[k];
+        __syncwarp();
+        // logits: lane n < N owns logit n
+        T z = bias[lane];
+        if (lane < a.N)
+            for (int k = 0; k < a.K; ++k) z = fma(arow[k], W[k * Ns + lane], z);
+        if (a.dz_last.enabled && lane < a.N) z = drop_keep(a.dz_last, a.st, m, lane, a.N) ? z * T(a.dz_last.scale) : T(0);
+        if (a.z_rec && lane < a.N) a.z_rec[m * a.N + lane] = z;
+        T zm = lane < a.N ? z : T(-INFINITY);
+        const T mx = warp_max(zm);
+        const T e = lane < a.N ? exp(z - mx) : T(0);
+        const T s = warp_sum(e);
+        const T p = e / s;
+        if (a.probs && lane < a.N) a.probs[m * a.N + lane] = p;
+        const int y = a.labels[a.row_idx ? (long long)a.row_idx[m] : m];
+        T g = lane < a.N ? (p - (lane == y ? T(1) : T(0))) * invb : T(0);
+        if (a.dz_rec && lane < a.N) a.dz_rec[m * a.N + lane] = g;
+        if (a.dz_last.enabled && lane < a.N) g = drop_keep(a.dz_last, a.st, m, lane, a.N) ? g * T(a.dz_last.scale) : T(0);
+        if (lane < a.N) a.dz_pre[m * a.N + lane] = g;
+        const T zy = __shfl_sync(0xffffffffu, z, (y >= 0 && y < a.N) ? y : 0);
+        if (lane == 0 && y >= 0 && y < a.N) local += (double)(mx + log(s) - zy);
+        // backward-x: lanes take k = lane, lane + 32, ...; g of lane n is broadcast with shuffles
+        for (int k0 = 0; k0 < a.K; k0 += 32) {
+            const int k = k0 + lane;
+            T d = T(0);
+            for (int n = 0; n < a.N; ++n) {
+                const T gn = __shfl_sync(0xffffffffu, g, n);
+                if (k < a.K) d = fma(gn, W[k * Ns + n], d);
+            }
+            if (k < a.K) {
+                if (a.da_rec) a.da_rec[m * a.K + k] = d;
+                T ga = d, av = arow[k];
+                if (a.da_prev.enabled) {
+                    ga = drop_keep(a.da_prev, a.st, m, k, a.K) ? d * T(a.da_prev.scale) : T(0);
+                    av = av * T(a.da_prev.keep_prob);
+                }
+                T gz = ga * act_bwd_from_out<T>(a.act_prev, av);
+                if (a.dzprev_rec) a.dzprev_rec[m * a.K + k] = gz;
+                if (a.dz_prev.enabled) gz = drop_keep(a.dz_prev, a.st, m, k, a.K) ? gz * T(a.dz_prev.scale) : T(0);
+                a.dprev_pre[m * a.K + k] = gz;
+            }
+        }
+        __syncwarp();
+    }
+    if (a.cost_base) block_add_double(local * a.inv_batch, cost_slot(a.cost_base, a.cost_cap, a.st));
+}
+
+}  // namespace poz

@@ -801,9 +801,19 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     }
 
     // backward: weight gradients (batch-split partial sums) and input gradients, last layer first
+    // The weight-gradient GEMM of a layer >= 1 only needs that layer's dZ, so it is forked onto a side
+    // stream and runs beside the backward-x chain (each of these launches fills a fraction of the GPU);
+    // the compute stream joins again before the update.  Inside a graph capture this becomes a fork/join.
+    const bool fork = c->fork_dw && c->side_stream && nl >= 2;
     for (int l = last; l >= 0; --l) {
         const int K = c->sizes[l], N = c->sizes[l + 1], hb = c->has_bias;
         const T* dz = static_cast<const T*>(c->dzbuf[l]);
+        cudaStream_t ws = stream;
+        if (fork && l >= 1) {
+            ws = c->side_stream;
+            POZ_CUDA(cudaEventRecord(c->dz_ready[l], stream));
+            POZ_CUDA(cudaStreamWaitEvent(ws, c->dz_ready[l], 0));
+        }
         if constexpr (std::is_same<T, float>::value) {
           if (tc0 && l == 0) {
             tc3::PlaneMat dzp;
@@ -839,10 +849,10 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             fast::Op B = make_fast_op(dz, N, nullptr, batch, N);
             BwdWeightEpi<float> epi;
             epi.g = static_cast<float*>(c->G); epi.slab = c->p_total; epi.off = c->off[l]; epi.ld = N;
-            ProfScope ps(c, "bwd_w_l" + std::to_string(l), stream);
-            if (hb) POZ_TRY((launch_fast<32, 64, false, false, true>(A, B, K, N, batch, seg.splits[l], false, K, epi, stream)));
-            else    POZ_TRY((launch_fast<32, 64, false, false, false>(A, B, K, N, batch, seg.splits[l], false, K, epi, stream)));
-            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
+            ProfScope ps(c, "bwd_w_l" + std::to_string(l), ws);
+            if (hb) POZ_TRY((launch_fast<32, 64, false, false, true>(A, B, K, N, batch, seg.splits[l], false, K, epi, ws)));
+            else    POZ_TRY((launch_fast<32, 64, false, false, false>(A, B, K, N, batch, seg.splits[l], false, K, epi, ws)));
+            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], ws));
           }
         } else {
             const T* inp = l == 0 ? x : static_cast<const T*>(c->abuf[l - 1]);
@@ -851,10 +861,10 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             BwdWeightEpi<T> epi;
             epi.g = static_cast<T*>(c->G); epi.slab = c->p_total; epi.off = c->off[l]; epi.ld = N;
             TileKind kind = N <= 16 ? TILE_THIN : TILE_SMALL;
-            ProfScope ps(c, "bwd_w_l" + std::to_string(l), stream);
+            ProfScope ps(c, "bwd_w_l" + std::to_string(l), ws);
             POZ_TRY((launch_gemm<T, false, false>(kind, A, B, (long long)K + hb, N, batch,
-                                                  seg.splits[l], kchunk[l], epi, stream)));
-            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
+                                                  seg.splits[l], kchunk[l], epi, ws)));
+            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], ws));
         }
         if (l > 0 && !(fuse_head && l == last)) {
             const T* w = static_cast<const T*>(c->P) + c->off[l];
@@ -889,6 +899,8 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
                                                 (long long)N, epi, stream)));
         }
     }
+    if (fork)
+        for (int l = 1; l < nl; ++l) POZ_CUDA(cudaStreamWaitEvent(stream, c->grad_ready[l], 0));
     c->grads_pending = true;
     c->diag_pending = diag != 0;
     return 0;
@@ -1240,11 +1252,18 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
             if (poz_tensor_io(c, 3, l, 0, 0, ones.data()) || poz_tensor_io(c, 6, l, 0, 0, ones.data())) return fail();
         }
     c->grad_ready.assign(n_linear, nullptr);
+    c->dz_ready.assign(n_linear, nullptr);
     for (int l = 0; l < n_linear; ++l)
-        if (cudaEventCreateWithFlags(&c->grad_ready[l], cudaEventDisableTiming) != cudaSuccess) {
+        if (cudaEventCreateWithFlags(&c->grad_ready[l], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&c->dz_ready[l], cudaEventDisableTiming) != cudaSuccess) {
             set_error("cudaEventCreate failed");
             return fail();
         }
+    if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        set_error("cudaStreamCreate failed");
+        return fail();
+    }
+    if (const char* e = getenv("POZ_FORK_DW")) c->fork_dw = atoi(e) != 0;
     *out = c;
     return 0;
 }
@@ -1277,6 +1296,8 @@ int poz_ctx_destroy(poz_ctx* c) {
     clear_graphs(c);
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
+    for (auto e : c->dz_ready) if (e) cudaEventDestroy(e);
+    if (c->side_stream) cudaStreamDestroy(c->side_stream);
     for (auto& p : c->bn_run) dev_free(p);
     for (auto& p : c->bn_stat) dev_free(p);
     for (auto& p : c->bn_sums) dev_free(p);

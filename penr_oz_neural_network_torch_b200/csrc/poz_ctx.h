@@ -62,6 +62,9 @@ struct poz_ctx {
     int g_slabs = 0, max_splits = 16;
     std::vector<int> seg_splits;
     std::vector<cudaEvent_t> grad_ready;   // recorded when layer l's weight gradient is complete
+    std::vector<cudaEvent_t> dz_ready;     // recorded (compute stream) when layer l's dZ is complete
+    cudaStream_t side_stream = nullptr;    // weight-gradient GEMMs of layers >= 1 run here, beside the backward-x chain
+    bool fork_dw = true;
 
     poz::DevState* st = nullptr;
     double* cost_ring = nullptr;  long long cost_cap = 0;

@@ -75,6 +75,59 @@ __device__ __forceinline__ void load_tile(float* S, const Op& op, long long mn0,
     }
 }
 
+// The same tile copy with everything that does not depend on the k-tile hoisted out of the main
+// loop: each thread owns a fixed set of 16-byte chunks, so their shared-memory offsets, source
+// pointers (at the first k-tile) and row validity are computed once; per k-tile only the k bound
+// is re-checked and the pointer advanced.  Used when the operand allows 16-byte copies and its
+// gather (if any) is not along k.
+template <int MN, int NT, bool KC> struct TileCopier {
+    static constexpr int LD = KC ? BK + 4 : MN + 4;
+    static constexpr int ROWS = KC ? MN : BK;
+    static constexpr int CV = (KC ? BK : MN) / 4;
+    static constexpr int N = (ROWS * CV + NT - 1) / NT;
+    const float* src[N];
+    int soff[N];
+    int kofs[N];
+    bool ok[N];
+    long long step;      // elements to advance per k-tile
+    long long k_lim;     // exclusive bound on the global k index
+    long long k_first;
+
+    __device__ __forceinline__ void init(const Op& op, long long mn0, long long k_begin, long long k_end, int tid) {
+        k_first = k_begin;
+        if (KC) { k_lim = k_end < op.cols ? k_end : (long long)op.cols; step = BK; }
+        else    { k_lim = k_end < op.rows ? k_end : op.rows; step = (long long)BK * op.ld; }
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            const int c = tid + i * NT;
+            const int r = c / CV, cc = (c % CV) * 4;
+            soff[i] = r * LD + cc;
+            ok[i] = c < ROWS * CV;
+            if (KC) {
+                const long long gr = mn0 + r;
+                ok[i] = ok[i] && gr < op.rows;
+                kofs[i] = cc;
+                src[i] = ok[i] ? op.ptr + (op.row_idx ? (long long)op.row_idx[gr] : gr) * op.ld + k_begin + cc : op.ptr;
+            } else {
+                const long long gc = mn0 + cc;
+                ok[i] = ok[i] && gc < op.cols;
+                kofs[i] = r;
+                src[i] = ok[i] ? op.ptr + (k_begin + r) * op.ld + gc : op.ptr;
+            }
+        }
+    }
+    __device__ __forceinline__ void issue(float* S, int t) const {
+        const long long kt = k_first + (long long)t * BK;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            if ((ROWS * CV) % NT != 0 && tid_out_of_range(i)) continue;
+            const bool v = ok[i] && (kt + kofs[i] < k_lim);
+            cp_async16(S + soff[i], v ? src[i] + (long long)t * step : src[i], v ? 16 : 0);
+        }
+    }
+    __device__ __forceinline__ bool tid_out_of_range(int i) const { return (int)threadIdx.x + i * NT >= ROWS * CV; }
+};
+
 // C[M][N] = A * B over this CTA's k range; z = blockIdx.z selects the range.  When the launch forms
 // clusters along z the partial tiles are reduced through distributed shared memory and every CTA
 // of the cluster runs the epilogue for its share of the tile rows; otherwise (dW) each z writes its
@@ -109,12 +162,19 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
     float bsum[TN] = {0.f, 0.f, 0.f, 0.f};
 
+    // hoisted copy descriptors when the operands allow it (block-uniform conditions)
+    const bool a_fast = A.vec4 && (A_KC || !A.row_idx);
+    const bool b_fast = B.vec4 && (B_KC || !B.row_idx);
+    TileCopier<BM, NT, A_KC> ca;
+    TileCopier<BN, NT, B_KC> cb;
+    if (a_fast) ca.init(A, m0, k_begin, k_end, tid);
+    if (b_fast) cb.init(B, n0, k_begin, k_end, tid);
     auto issue = [&](int t) {
         float* sa = smem + (t % STAGES) * STAGE_ELEMS;
         float* sb = sa + A_ELEMS;
         const long long k0 = k_begin + (long long)t * BK;
-        load_tile<BM, NT, A_KC>(sa, A, m0, k0, k_end, tid);
-        load_tile<BN, NT, B_KC>(sb, B, n0, k0, k_end, tid);
+        if (a_fast) ca.issue(sa, t); else load_tile<BM, NT, A_KC>(sa, A, m0, k0, k_end, tid);
+        if (b_fast) cb.issue(sb, t); else load_tile<BN, NT, B_KC>(sb, B, n0, k0, k_end, tid);
     };
 #pragma unroll
     for (int s = 0; s < STAGES - 1; ++s) {

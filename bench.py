@@ -181,7 +181,7 @@ def kernel_work(tag, batch):
 
 
 def run_c2(args, world, rank, local):
-    from penr_oz_neural_network_torch_b200 import HostBatchFeeder, launch_count
+    from penr_oz_neural_network_torch_b200 import launch_count
     dev = torch.device("cuda", local)
     eng = make_engine(local)
     batch = C2_BATCH
@@ -221,30 +221,26 @@ def run_c2(args, world, rank, local):
     e2e_steps = args.steps
     # every step: host batch -> device, train step, that step's cost -> host.  The cost of step k is
     # read while step k+1 runs (one step of lag), so the GPU never idles on the read-back.
-    # host-side timing is exposed to host noise: three back-to-back timed regions, median reported
+    # Through the C-ABI host-buffer call (poz_train_step_host): one call per step copies the pinned
+    # host batch to the device, runs the step and reads back the previous step's cost.  Host-side
+    # timing is exposed to host noise: three back-to-back timed regions, median reported.
     e2e_runs = []
-    k = args.warmup
     last = 0.0
     eng.train_begin(optimizer="adam", epochs=args.warmup + 3 * e2e_steps + 8, **HP)
-    feeder = HostBatchFeeder(eng, batch)
-    feeder.stage(hx[0], hy[0])
+    k = 0
     for i in range(args.warmup):
-        feeder.step(i)
-        feeder.stage(hx[(i + 1) % n_host], hy[(i + 1) % n_host])
-        if i:
-            feeder.cost(i - 1, i - 1)
+        eng.train_step_host(hx[k % n_host], hy[k % n_host]); k += 1
     for rep in range(3):
+        eng.train_host_flush()
         barrier_sync(world)
         t0 = time.perf_counter()
         for i in range(e2e_steps):
-            feeder.step(k)
-            feeder.stage(hx[(k + 1) % n_host], hy[(k + 1) % n_host])
-            last = feeder.cost(k - 1, k - 1)
-            k += 1
-        last = feeder.cost(k - 1, k - 1)
+            last = eng.train_step_host(hx[k % n_host], hy[k % n_host]); k += 1
+        last = eng.train_host_flush()
         barrier_sync(world)
         e2e_runs.append(max_over_ranks((time.perf_counter() - t0) * 1e3, world))
     e2e_ms = float(np.median(e2e_runs))
+    h2d_bytes, d2h_bytes = batch * 784 * 4 + batch * 4, 8
     assert np.isfinite(last)
     clocks = sampler.stop() if sampler else None
 
@@ -282,9 +278,10 @@ def run_c2(args, world, rank, local):
     return dict(metric="train samples/s (fwd+bwd+step)", unit="samples/s",
                 value=world * batch * args.steps / (ms * 1e-3), ms_per_step=ms / args.steps,
                 e2e={"value": world * batch * e2e_steps / (e2e_ms * 1e-3), "unit": "samples/s",
-                     "h2d_bytes_per_step": feeder.h2d_bytes, "d2h_bytes_per_step": feeder.d2h_bytes,
+                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                      "ms_per_step": e2e_ms / e2e_steps,
-                     "note": "median of 3 timed regions (host clock); cost of step k read back while step k+1 runs",
+                     "note": "poz_train_step_host per step (pinned host batch in, cost out); median of 3 timed "
+                             "regions (host clock); the cost of step k is read back while step k+1 runs",
                      "runs_ms_per_step": [round(v / e2e_steps, 5) for v in e2e_runs]},
                 gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
                 config={"workload": "c2: MLP 784-256-128-10 relu/relu/softmax + cross-entropy, Adam, L2 1e-3, "
@@ -727,6 +724,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback); "
                          "use --impl reference for the CPU arm")
+    from penr_oz_neural_network_torch_b200 import bind_host_to_gpu_numa_node
+    numa = bind_host_to_gpu_numa_node(local)        # before any pinned allocation
     if args.workload == "emb":
         res = run_emb(args, world, rank, local)
     elif args.workload in ("c4", "c5"):
@@ -735,6 +734,10 @@ def main():
         res = (run_c2 if args.workload == "c2" else run_c3)(args, world, rank, local)
     if rank == 0:
         cpu = None
+        try:
+            os.sched_setaffinity(0, range(os.cpu_count() or 1))      # the CPU baseline uses every host core
+        except Exception:
+            pass
         if world == 1 and not args.no_cpu_baseline:
             if args.workload == "emb":
                 v, n, thr, el, b = cpu_train_emb(10.0, args.batch or EMB_BATCH)
@@ -759,7 +762,7 @@ def main():
                     scaling=res.get("scaling", "weak"),
                     vs_baseline=None, dtype=res["dtype"], data="synthetic", config=res["config"], e2e=res["e2e"],
                     gpu_launches=res["gpu_launches"], clocks=res["clocks"], roofline=res["roofline"],
-                    cpu_baseline=cpu, impl="native")
+                    cpu_baseline=cpu, impl="native", host_numa=numa)
         print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist

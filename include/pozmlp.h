@@ -142,6 +142,19 @@ int poz_train_begin(poz_ctx* ctx, const poz_train_config* cfg);
 int poz_train_step(poz_ctx* ctx, const void* x_dev, const void* target_dev, const int* row_idx_dev,
                    long long batch, const void* const* keep_masks, int diagnostics, void* stream);
 int poz_train_costs(poz_ctx* ctx, long long first, long long count, double* costs_host, void* stream);
+/* The same step from HOST buffers -- the tensor copy of neural_net_model.py:472 plus the step plus the
+ * cost.item() of :503 in one call.  x_host [batch][in] in the context's compute dtype (int32 token indices
+ * for an embedding head), target_host int32 labels [batch] or [batch][out]; both should be pinned so the
+ * copies are asynchronous.  The batch goes to one of two device slots on an internal copy stream, so
+ * the copy of this call overlaps the kernels of the previous step; the step itself runs on `stream`
+ * (replayed from a CUDA graph once a slot has been seen twice; use a non-default stream for that).
+ * *prev_cost receives the cost of the PREVIOUS host step (NaN on the first call), read back on its own
+ * stream without waiting for the step just launched.  The host buffers of a call may be reused once the
+ * next call (or poz_train_host_flush) has returned.  poz_train_host_flush waits for the last step and
+ * returns its cost. */
+int poz_train_step_host(poz_ctx* ctx, const void* x_host, const void* target_host, long long batch,
+                        double* prev_cost, void* stream);
+int poz_train_host_flush(poz_ctx* ctx, double* last_cost);
 /* ratios_host [count][n_linear]: std(w_new - w_old) / (std(w_new) + 1e-8), unbiased std. */
 int poz_train_update_ratios(poz_ctx* ctx, long long first_record, long long count,
                             double* ratios_host, void* stream);

@@ -4,6 +4,6 @@
 reference's ``from neural_net_model import NeuralNetworkModel``.
 """
 from ._native import PozError, build, launch_count  # noqa: F401
-from .engine import DeviceMLP, HostBatchFeeder, StackSpec  # noqa: F401
+from .engine import DeviceMLP, HostBatchFeeder, StackSpec, bind_host_to_gpu_numa_node  # noqa: F401
 from .neural_net_model import (Layer, LinearLayer, MultiLayerPerceptron, NeuralNetworkModel,  # noqa: F401
                                ReluLayer, SigmoidLayer, SoftmaxLayer, TanhLayer)

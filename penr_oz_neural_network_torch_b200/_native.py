@@ -115,6 +115,8 @@ SIGNATURES = {
     "poz_forward_loss": (_I, [_VP, _VP, _VP, _LL, _VP, _DP, _VP]),
     "poz_train_begin": (_I, [_VP, C.POINTER(TrainConfig)]),
     "poz_train_step": (_I, [_VP, _VP, _VP, _VP, _LL, C.POINTER(_VP), _I, _VP]),
+    "poz_train_step_host": (_I, [_VP, _VP, _VP, _LL, _DP, _VP]),
+    "poz_train_host_flush": (_I, [_VP, _DP]),
     "poz_train_costs": (_I, [_VP, _LL, _LL, _VP, _VP]),
     "poz_train_update_ratios": (_I, [_VP, _LL, _LL, _VP, _VP]),
     "poz_diag_activation": (_I, [_VP, _I, _I, _VP]),

@@ -1294,6 +1294,14 @@ int poz_ctx_destroy(poz_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     clear_graphs(c);
+    for (int i = 0; i < 2; ++i) {
+        dev_free(c->feed.x[i]); dev_free(c->feed.t[i]);
+        if (c->feed.copied[i]) cudaEventDestroy(c->feed.copied[i]);
+        if (c->feed.consumed[i]) cudaEventDestroy(c->feed.consumed[i]);
+    }
+    if (c->feed.copy_stream) cudaStreamDestroy(c->feed.copy_stream);
+    if (c->feed.read_stream) cudaStreamDestroy(c->feed.read_stream);
+    if (c->feed.cost_pinned) cudaFreeHost(c->feed.cost_pinned);
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     for (auto e : c->dz_ready) if (e) cudaEventDestroy(e);
@@ -1486,6 +1494,9 @@ int poz_train_begin(poz_ctx* c, const poz_train_config* cfg) {
     h.next_epoch = 0; h.cur_epoch = 0; h.cur_record = -1; h.n_records = 0;
     POZ_CUDA(cudaMemcpy(c->st, &h, sizeof(h), cudaMemcpyHostToDevice));
     c->train_begun = true;
+    c->epoch_host = 0;
+    c->feed.calls = 0;
+    c->feed.prev_epoch = -1;
     {   // captured steps bake these into kernel arguments; everything else lives in DevState
         const double sig[6] = {cfg->dropout_rate, (double)cfg->global_batch, (double)c->cost_cap, (double)c->stats_cap,
                                (double)reinterpret_cast<uintptr_t>(c->cost_ring), (double)reinterpret_cast<uintptr_t>(c->stats)};
@@ -1498,9 +1509,19 @@ int poz_train_begin(poz_ctx* c, const poz_train_config* cfg) {
     return 0;
 }
 
+static int train_backward_inner(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
+                                long long batch, const void* const* keep_masks, int diagnostics, void* stream);
+
 int poz_train_backward(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
                        long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
     POZ_TRY(check_layer(c, 0, "poz_train_backward"));
+    POZ_TRY(train_backward_inner(c, x_dev, target_dev, row_idx_dev, batch, keep_masks, diagnostics, stream));
+    c->epoch_host += 1;
+    return 0;
+}
+
+static int train_backward_inner(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
+                                long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
     if (!x_dev || !target_dev) POZ_FAIL("poz_train_step: NULL buffer");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (c->dtype == POZ_DTYPE_BF16)
@@ -1544,6 +1565,7 @@ int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const 
     if (g && g->exec) {
         POZ_CUDA(cudaGraphLaunch(g->exec, s));
         count_launch(g->launches);
+        c->epoch_host += 1;
         return 0;
     }
     if (!g) {
@@ -1567,6 +1589,7 @@ int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const 
         if (!rc) set_error(std::string("poz_train_step: graph capture failed: ") + cudaGetErrorString(ce));
         c->graphs_enabled = false;          // fall back to plain launches for this context
         cudaGetLastError();
+        c->epoch_host -= 1;                 // the captured (never executed) attempt does not count
         if (rc) return rc;
         POZ_TRY(poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, nullptr, 0, stream));
         return poz_train_apply(c, stream);
@@ -1578,6 +1601,91 @@ int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const 
     g->exec = exec;
     g->launches = (int)(poz_launch_count() - before);
     POZ_CUDA(cudaGraphLaunch(exec, s));
+    return 0;
+}
+
+// ---- host-buffer stepping ---------------------------------------------------------------------------
+static long long feed_x_row_bytes(const poz_ctx* c) {
+    if (c->emb_vocab > 0) return (long long)c->tokens * 4;            // int32 token indices
+    return (long long)c->sizes[0] * (long long)c->act_esz;
+}
+static long long feed_t_row_bytes(const poz_ctx* c) {
+    return c->loss == POZ_LOSS_CE ? 4 : (long long)c->sizes[c->nl] * (long long)c->act_esz;
+}
+
+static int feed_reserve(poz_ctx* c, long long batch) {
+    poz_ctx::HostFeed& f = c->feed;
+    if (!f.copy_stream) {
+        POZ_CUDA(cudaStreamCreateWithFlags(&f.copy_stream, cudaStreamNonBlocking));
+        POZ_CUDA(cudaStreamCreateWithFlags(&f.read_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            POZ_CUDA(cudaEventCreateWithFlags(&f.copied[i], cudaEventDisableTiming));
+            POZ_CUDA(cudaEventCreateWithFlags(&f.consumed[i], cudaEventDisableTiming));
+        }
+        POZ_CUDA(cudaMallocHost(reinterpret_cast<void**>(&f.cost_pinned), sizeof(double)));
+    }
+    if (batch > f.batch) {
+        POZ_CUDA(cudaDeviceSynchronize());
+        for (int i = 0; i < 2; ++i) {
+            dev_free(f.x[i]); dev_free(f.t[i]);
+            POZ_TRY(dev_alloc(&f.x[i], (size_t)(batch * feed_x_row_bytes(c))));
+            POZ_TRY(dev_alloc(&f.t[i], (size_t)(batch * feed_t_row_bytes(c))));
+        }
+        f.batch = batch;
+        f.calls = 0;
+        f.prev_epoch = -1;
+        clear_graphs(c);
+    }
+    return 0;
+}
+
+static int feed_read_cost(poz_ctx* c, int slot, long long epoch, double* out) {
+    poz_ctx::HostFeed& f = c->feed;
+    POZ_CUDA(cudaStreamWaitEvent(f.read_stream, f.consumed[slot], 0));
+    POZ_CUDA(cudaMemcpyAsync(f.cost_pinned, c->cost_ring + (epoch % c->cost_cap), sizeof(double), cudaMemcpyDeviceToHost,
+                             f.read_stream));
+    POZ_CUDA(cudaStreamSynchronize(f.read_stream));
+    *out = *f.cost_pinned;
+    return 0;
+}
+
+int poz_train_step_host(poz_ctx* c, const void* x_host, const void* target_host, long long batch, double* prev_cost,
+                        void* stream) {
+    POZ_TRY(check_layer(c, 0, "poz_train_step_host"));
+    if (!x_host || !target_host) POZ_FAIL("poz_train_step_host: NULL buffer");
+    if (!c->train_begun) POZ_FAIL("poz_train_step_host: call poz_train_begin first");
+    if (batch <= 0) POZ_FAIL("poz_train_step_host: empty batch");
+    POZ_TRY(feed_reserve(c, batch));
+    poz_ctx::HostFeed& f = c->feed;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int slot = (int)(f.calls & 1);
+    // host -> device on the copy stream; the slot is free once the step that last used it has run
+    if (f.calls >= 2) POZ_CUDA(cudaStreamWaitEvent(f.copy_stream, f.consumed[slot], 0));
+    POZ_CUDA(cudaMemcpyAsync(f.x[slot], x_host, (size_t)(batch * feed_x_row_bytes(c)), cudaMemcpyHostToDevice, f.copy_stream));
+    POZ_CUDA(cudaMemcpyAsync(f.t[slot], target_host, (size_t)(batch * feed_t_row_bytes(c)), cudaMemcpyHostToDevice, f.copy_stream));
+    POZ_CUDA(cudaEventRecord(f.copied[slot], f.copy_stream));
+    POZ_CUDA(cudaStreamWaitEvent(s, f.copied[slot], 0));
+    const long long epoch = c->epoch_host;
+    POZ_TRY(poz_train_step(c, f.x[slot], f.t[slot], nullptr, batch, nullptr, 0, stream));
+    POZ_CUDA(cudaEventRecord(f.consumed[slot], s));
+    // the previous step's cost: only that step is waited for, the one just launched keeps running
+    if (prev_cost) {
+        *prev_cost = NAN;
+        if (f.calls >= 1 && f.prev_epoch >= 0) POZ_TRY(feed_read_cost(c, slot ^ 1, f.prev_epoch, prev_cost));
+    }
+    f.prev_epoch = epoch;
+    f.calls += 1;
+    return 0;
+}
+
+int poz_train_host_flush(poz_ctx* c, double* last_cost) {
+    POZ_TRY(check_layer(c, 0, "poz_train_host_flush"));
+    poz_ctx::HostFeed& f = c->feed;
+    if (last_cost) *last_cost = NAN;
+    if (!f.copy_stream || f.calls == 0 || f.prev_epoch < 0) return 0;
+    if (last_cost) POZ_TRY(feed_read_cost(c, (int)((f.calls - 1) & 1), f.prev_epoch, last_cost));
+    else POZ_CUDA(cudaEventSynchronize(f.consumed[(f.calls - 1) & 1]));
+    f.prev_epoch = -1;
     return 0;
 }
 

@@ -93,6 +93,19 @@ struct poz_ctx {
     bool fuse_head = true;            // narrow softmax head in one kernel (POZ_FUSE_HEAD=0 disables)
     double graph_sig[6] = {0, 0, 0, 0, 0, 0};
 
+    // host-buffer stepping (poz_train_step_host): two device slots, copy + read-back streams
+    struct HostFeed {
+        void* x[2] = {nullptr, nullptr};
+        void* t[2] = {nullptr, nullptr};
+        cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr};
+        cudaStream_t copy_stream = nullptr, read_stream = nullptr;
+        double* cost_pinned = nullptr;
+        long long batch = 0;           // capacity of the slots
+        long long calls = 0;           // host steps since poz_train_begin
+        long long prev_epoch = -1;     // epoch index of the previous host step
+    } feed;
+    long long epoch_host = 0;          // steps launched since poz_train_begin (mirrors DevState::next_epoch)
+
     poz_train_config cfg;
     bool train_begun = false, training_pass = false;
     bool grads_pending = false, grads_reduced = false, diag_pending = false, have_diag = false;

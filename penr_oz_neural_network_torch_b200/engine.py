@@ -355,6 +355,25 @@ class DeviceMLP:
         nat.check(self.lib.poz_train_step(self.ctx, _ptr(x), _ptr(target), _ptr(row_idx), batch, ptrs,
                                           int(bool(diagnostics)), _stream_ptr(self.device)))
 
+    def train_step_host(self, x_host: torch.Tensor, target_host: torch.Tensor) -> float:
+        """One step from (pinned) HOST tensors through poz_train_step_host: copy, step and the
+        read-back of the previous step's cost in a single C call.  Returns the cost of the previous
+        host step (NaN on the first call); ``train_host_flush`` returns the last one."""
+        if x_host.is_cuda or target_host.is_cuda or not x_host.is_contiguous() or not target_host.is_contiguous():
+            raise ValueError("train_step_host takes contiguous CPU tensors (pinned for asynchronous copies)")
+        want = torch.int32 if self.embedding else self.tdtype
+        if x_host.dtype != want or x_host.ndim != 2 or x_host.shape[1] != self.in_features:
+            raise ValueError(f"x_host must be {want} [batch, {self.in_features}]")
+        prev = C.c_double()
+        nat.check(self.lib.poz_train_step_host(self.ctx, x_host.data_ptr(), target_host.data_ptr(), x_host.shape[0],
+                                               C.byref(prev), _stream_ptr(self.device)))
+        return float(prev.value)
+
+    def train_host_flush(self) -> float:
+        last = C.c_double()
+        nat.check(self.lib.poz_train_host_flush(self.ctx, C.byref(last)))
+        return float(last.value)
+
     def train_backward(self, x, target, row_idx=None, masks=None, diagnostics=False):
         batch = self._check_step_args(x, target, row_idx)
         ptrs, _keep = self._mask_array(masks)
@@ -503,6 +522,39 @@ def _wrap_device_pointer(ptr: int, n: int, dtype: torch.dtype, device) -> torch.
         return torch.as_tensor(_DevPtr(ptr, n, typestr), device=device)
 
 
+def bind_host_to_gpu_numa_node(device) -> dict:
+    """Pin this process (and therefore the pinned buffers it allocates next) to the CPUs of the NUMA
+    node the GPU hangs off, so that host->device copies and launches of a feeder do not cross the
+    inter-socket link on a multi-socket box.  A no-op where the platform reports no NUMA node for the
+    GPU (e.g. single-node VMs).  Best effort: returns what it did, never raises."""
+    import os
+    info = {"bound": False}
+    try:
+        idx = device.index if isinstance(device, torch.device) else int(device)
+        pr = torch.cuda.get_device_properties(idx)
+        bus = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        info["pci"] = bus
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            info["bound"] = True
+            info["cpus"] = len(allowed)
+    except Exception as e:          # no sysfs, no permission, not Linux ...
+        info["error"] = str(e)
+    return info
+
+
 class HostBatchFeeder:
     """End-to-end stepping from HOST buffers: every step copies its batch from pinned host memory
     to the device (on a copy stream, double-buffered so the copy of step i+1 overlaps the kernels
@@ -519,6 +571,7 @@ class HostBatchFeeder:
         else:
             self.t_dev = [torch.empty((batch, eng.sizes[-1]), dtype=eng.tdtype, device=dev) for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=dev)
+        self.read_stream = torch.cuda.Stream(device=dev)     # cost read-back, never queued behind a batch copy
         self.copied = [torch.cuda.Event() for _ in range(2)]
         self.consumed = [torch.cuda.Event() for _ in range(2)]
         self.h2d_bytes = self.x_dev[0].numel() * self.x_dev[0].element_size() + \
@@ -549,10 +602,10 @@ class HostBatchFeeder:
 
     def cost(self, epoch_index: int, step_number: int | None = None) -> float:
         """Device->host read of one step's cost.  With ``step_number`` (the 0-based count of
-        ``step()`` calls that produced it) the read runs on the copy stream behind that step's
+        ``step()`` calls that produced it) the read runs on its own stream behind that step's
         completion event only, so a later step already in flight is not waited for; without it the
         compute stream is synchronised."""
         if step_number is None:
             return float(self.eng.costs(epoch_index, 1)[0])
-        self.copy_stream.wait_event(self.consumed[step_number % 2])
-        return float(self.eng.costs(epoch_index, 1, stream=self.copy_stream)[0])
+        self.read_stream.wait_event(self.consumed[step_number % 2])
+        return float(self.eng.costs(epoch_index, 1, stream=self.read_stream)[0])

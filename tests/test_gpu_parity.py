@@ -394,3 +394,32 @@ def test_device_statistics_equal_host_torch_statistics(dtype):
         w, _ = eng.download_params(l)
         dw = eng.diag_stats(l, 0, 2, histogram=False)
         np.testing.assert_allclose([dw["mean"], dw["std"]], [w.mean(), w.std(ddof=1)], rtol=1e-10, atol=1e-14)
+
+
+def test_host_buffer_steps_equal_device_buffer_steps():
+    """poz_train_step_host (pinned host batch in, previous cost out) trains exactly like
+    poz_train_step on device-resident copies of the same batches."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    sizes, algos = [40, 24, 6], ["linear", "relu", "linear", "softmax"]
+    params = det_params(sizes, True, 301)
+    batches = [(torch.tensor(det_normalish((96, 40), 310 + i), dtype=torch.float32).pin_memory(),
+                torch.tensor(det_labels(96, 6, 320 + i), dtype=torch.int32).pin_memory()) for i in range(5)]
+    runs = []
+    for host in (True, False):
+        eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+        for l in range(2):
+            eng.upload_params(l, params[2 * l], params[2 * l + 1])
+        eng.train_begin(optimizer="adam", learning_rate=0.01, l2_lambda=0.001, epochs=5)
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            if host:
+                got = [eng.train_step_host(x, y) for x, y in batches]
+                got = got[1:] + [eng.train_host_flush()]
+            else:
+                for x, y in batches:
+                    eng.train_step(x.cuda(), y.cuda())
+                got = list(eng.costs(0, 5))
+        side.synchronize()
+        runs.append((got, eng.costs(0, 5), [eng.download_params(l) for l in range(2)]))
+    np.testing.assert_allclose(runs[0][0], runs[1][0], rtol=1e-12)
+    np.testing.assert_allclose(runs[0][1], runs[1][1], rtol=1e-12)

@@ -302,6 +302,11 @@ def run_c3(args, world, rank, local):
     g = torch.Generator(device=dev).manual_seed(99 + rank)
     xs = torch.randn((n_pool, batch, 784), generator=g, device=dev, dtype=torch.float32)
     out = torch.empty((batch, 10), device=dev, dtype=torch.float32)
+    side = torch.cuda.Stream(device=dev)
+    torch.cuda.synchronize()
+    torch.cuda.set_stream(side)          # small calls are replayed from CUDA graphs; not possible on the legacy stream
+    for i in range(2 * n_pool):          # every pool buffer seen twice (eager, then captured), untimed
+        eng.forward(xs[i % n_pool], out)
     for i in range(args.warmup):
         eng.forward(xs[i % n_pool], out)
     barrier_sync(world)

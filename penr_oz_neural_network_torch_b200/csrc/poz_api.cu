@@ -194,6 +194,9 @@ static void clear_graphs(poz_ctx* c) {
     for (auto& e : c->graphs)
         if (e.exec) cudaGraphExecDestroy(e.exec);
     c->graphs.clear();
+    for (auto& e : c->fwd_graphs)
+        if (e.exec) cudaGraphExecDestroy(e.exec);
+    c->fwd_graphs.clear();
 }
 
 // ---- workspace ---------------------------------------------------------------------------------
@@ -250,6 +253,7 @@ static int reserve_infer(poz_ctx* c, long long chunk) {
     POZ_TRY(dev_alloc(&c->ping, bytes));
     POZ_TRY(dev_alloc(&c->pong, bytes));
     c->ws_infer = chunk;
+    clear_graphs(c);
     return 0;
 }
 
@@ -1436,11 +1440,61 @@ int poz_adam_get_step(poz_ctx* c, long long* step) {
     return 0;
 }
 
+static int forward_launch(poz_ctx* c, const void* x_dev, long long batch, void* out_dev, cudaStream_t s);
+
+// Small inference calls are launch-bound (a handful of tiny kernels), so a call on the same buffers and
+// batch size is captured into a CUDA graph the second time it is seen and replayed afterwards.  The
+// weight planes / workspace a call needs are set up by the first, eager, call; uploads of new
+// parameters go to the same device addresses, so a captured call stays valid.
 int poz_forward(poz_ctx* c, const void* x_dev, long long batch, void* out_dev, void* stream) {
     POZ_TRY(check_layer(c, 0, "poz_forward"));
     if (batch <= 0) return 0;
     if (!x_dev || !out_dev) POZ_FAIL("poz_forward: NULL buffer");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bool graphable = c->graphs_enabled && !c->profiling && stream != nullptr && batch <= 4096 &&
+                           !(c->dtype == POZ_DTYPE_F32 && batch >= c->tc3_min_batch && !c->general);
+    if (!graphable) return forward_launch(c, x_dev, batch, out_dev, s);
+    poz_ctx::StepGraph* g = nullptr;
+    for (auto& e : c->fwd_graphs)
+        if (e.x == x_dev && e.t == out_dev && e.batch == batch) { g = &e; break; }
+    if (g && g->exec) {
+        POZ_CUDA(cudaGraphLaunch(g->exec, s));
+        count_launch(g->launches);
+        return 0;
+    }
+    if (!g) {
+        if (c->fwd_graphs.size() >= 64) {
+            for (auto& e : c->fwd_graphs) if (e.exec) cudaGraphExecDestroy(e.exec);
+            c->fwd_graphs.clear();
+        }
+        poz_ctx::StepGraph e;
+        e.x = x_dev; e.t = out_dev; e.idx = nullptr; e.batch = batch;
+        c->fwd_graphs.push_back(e);
+        return forward_launch(c, x_dev, batch, out_dev, s);
+    }
+    const long long before = poz_launch_count();
+    POZ_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    int rc = forward_launch(c, x_dev, batch, out_dev, s);
+    cudaGraph_t graph = nullptr;
+    cudaError_t ce = cudaStreamEndCapture(s, &graph);
+    if (rc || ce != cudaSuccess || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        c->graphs_enabled = false;
+        if (rc) return rc;
+        return forward_launch(c, x_dev, batch, out_dev, s);
+    }
+    cudaGraphExec_t exec = nullptr;
+    ce = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ce != cudaSuccess) POZ_FAIL(std::string("poz_forward: cudaGraphInstantiate failed: ") + cudaGetErrorString(ce));
+    g->exec = exec;
+    g->launches = (int)(poz_launch_count() - before);
+    POZ_CUDA(cudaGraphLaunch(exec, s));
+    return 0;
+}
+
+static int forward_launch(poz_ctx* c, const void* x_dev, long long batch, void* out_dev, cudaStream_t s) {
     if (c->dtype == POZ_DTYPE_BF16)
         return forward_wide(c, static_cast<const __nv_bfloat16*>(x_dev), nullptr, batch,
                             static_cast<__nv_bfloat16*>(out_dev), nullptr, s);

@@ -89,6 +89,7 @@ struct poz_ctx {
         int launches = 0;
     };
     std::vector<StepGraph> graphs;
+    std::vector<StepGraph> fwd_graphs;   // inference calls: x = input, t = output buffer
     bool graphs_enabled = true;
     bool fuse_head = true;            // narrow softmax head in one kernel (POZ_FUSE_HEAD=0 disables)
     double graph_sig[6] = {0, 0, 0, 0, 0, 0};

@@ -5,6 +5,8 @@
 #include "poz_net_kernels.cuh"
 #include "poz_simt_gemm.cuh"
 #include "poz_simt_fast.cuh"
+#include "poz_narrow_step.cuh"
+#include "poz_tf32x3_gemm.cuh"
 #include "poz_tc.h"
 #include "poz_tc3.h"
 #include "poz_wide_kernels.cuh"
@@ -267,12 +269,45 @@ static int ensure_grad_slabs(poz_ctx* c, int slabs) {
 }
 
 
+// ---- programmatic dependent launch (poz_common.cuh: pdl_trigger / pdl_wait) ----------------------------
+// Only kernels that call pdl_wait() before touching global memory are launched this way.  Measured on
+// B200 inside the step's CUDA graph the programmatic edges made the C2 step slower (108-114 us against
+// 82 us with plain edges), so the attribute is opt-in: POZ_PDL=1.
+static bool pdl_enabled() {
+    static const bool on = getenv("POZ_PDL") && atoi(getenv("POZ_PDL")) != 0;
+    return on;
+}
+
+template <typename... P, typename... A>
+static int launch_pdl(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (pdl_enabled()) {
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+    }
+    POZ_CUDA(cudaLaunchKernelEx(&cfg, kern, std::forward<A>(args)...));
+    count_launch();
+    return 0;
+}
+
 // ---- pipelined fp32 kernels (poz_simt_fast.cuh): launch helpers -------------------------------------
 static fast::Op make_fast_op(const float* ptr, long long ld, const int* row_idx, long long rows, int cols) {
     fast::Op o;
     o.ptr = ptr; o.ld = ld; o.row_idx = row_idx; o.rows = rows; o.cols = cols;
     o.vec4 = ((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld % 4) == 0 && (cols % 4) == 0) ? 1 : 0;
     return o;
+}
+
+// POZ_TF32X3=1 runs the 32x64-tile GEMMs of float32 contexts on the warp-level tensor-core instruction
+// with the error-compensated split (poz_tf32x3_gemm.cuh).  It passes the same parity tests, but measured
+// on B200 the C2 step does not get faster (the main loops of these GEMMs wait for operand tiles, not
+// for arithmetic: DESIGN.md section 4g), so the exact-fp32 FFMA kernel stays the default.
+static bool tf32x3_enabled() {
+    static const bool on = getenv("POZ_TF32X3") && atoi(getenv("POZ_TF32X3")) != 0;
+    return on;
 }
 
 template <int BM, int BN, bool A_KC, bool B_KC, bool COLSUM, class Epi>
@@ -287,14 +322,25 @@ static int launch_fast(const fast::Op& A, const fast::Op& B, long long M, int N,
     cfg.blockDim = dim3((BM / fast::TM) * (BN / fast::TN));
     cfg.dynamicSmemBytes = 0;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
+    unsigned na = 0;
     if (cluster && splits > 1) {
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)splits;
-        cfg.attrs = attr; cfg.numAttrs = 1;
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = 1; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = (unsigned)splits;
+        ++na;
     }
-    POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_f32_pipelined<BM, BN, A_KC, B_KC, COLSUM, Epi>, A, B, M, N, Kd,
-                                k_chunk, bias_row, epi));
+    if (pdl_enabled()) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (na) { cfg.attrs = attr; cfg.numAttrs = na; }
+    if (BM == 32 && BN == 64 && tf32x3_enabled())
+        POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_tf32x3_pipelined<A_KC, B_KC, COLSUM, Epi>, A, B, M, N, Kd, k_chunk,
+                                    bias_row, epi));
+    else
+        POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_f32_pipelined<BM, BN, A_KC, B_KC, COLSUM, Epi>, A, B, M, N, Kd,
+                                    k_chunk, bias_row, epi));
     count_launch();
     return 0;
 }
@@ -304,8 +350,9 @@ static int launch_fast(const fast::Op& A, const fast::Op& B, long long M, int N,
 static int pick_cluster_split(const poz_ctx* c, long long tiles, long long Kd) {
     const long long sms = num_sms(c->device);
     const long long nk = (Kd + fast::BK - 1) / fast::BK;
+    static const long long per_sm = getenv("POZ_FWD_CTAS_PER_SM") ? std::max(1, atoi(getenv("POZ_FWD_CTAS_PER_SM"))) : 4;
     int s = 1;
-    while (s < 8 && tiles * s * 2 <= 4 * sms && nk / (s * 2) >= 2) s *= 2;
+    while (s < 8 && tiles * s * 2 <= per_sm * sms && nk / (s * 2) >= 2) s *= 2;
     return s;
 }
 
@@ -355,14 +402,10 @@ template <typename T> static int run_softmax(poz_ctx* c, const T* z, T* out, lon
     ProfScope ps(c, "softmax", s);
     if (N <= 32) {
         long long b = (M + 255) / 256;
-        softmax_small_kernel<T><<<(unsigned)std::max<long long>(b, 1), 256, 0, s>>>(z, out, M, N);
-        POZ_LAUNCH_CHECK();
-        return 0;
+        return launch_pdl(softmax_small_kernel<T>, dim3((unsigned)std::max<long long>(b, 1)), dim3(256), 0, s, z, out, M, N);
     }
     int blocks = (int)std::min<long long>((M + 7) / 8, 148 * 8);
-    softmax_kernel<T><<<std::max(blocks, 1), 256, 0, s>>>(z, out, M, N);
-    POZ_LAUNCH_CHECK();
-    return 0;
+    return launch_pdl(softmax_kernel<T>, dim3(std::max(blocks, 1)), dim3(256), 0, s, z, out, M, N);
 }
 
 template <typename T>
@@ -370,14 +413,12 @@ static int run_loss(poz_ctx* c, LossArgs<T>& a, cudaStream_t s) {
     ProfScope ps(c, "loss", s);
     if (c->loss == POZ_LOSS_CE) {
         int blocks = (int)std::min<long long>((a.M + 7) / 8, 148 * 8);
-        ce_loss_kernel<T><<<std::max(blocks, 1), 256, 0, s>>>(a);
+        return launch_pdl(ce_loss_kernel<T>, dim3(std::max(blocks, 1)), dim3(256), 0, s, a);
     } else {
         long long total = a.M * a.N;
         int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 8);
-        mse_loss_kernel<T><<<std::max(blocks, 1), 256, 0, s>>>(a);
+        return launch_pdl(mse_loss_kernel<T>, dim3(std::max(blocks, 1)), dim3(256), 0, s, a);
     }
-    POZ_LAUNCH_CHECK();
-    return 0;
 }
 
 // ---- float32 contexts on the tensor cores (split-bf16, csrc/poz_tc3.*) ------------------------------
@@ -601,7 +642,8 @@ static void plan_splits(poz_ctx* c, long long batch, SegTable& seg, std::vector<
                               : (long long)((M + TL::SM_BM - 1) / TL::SM_BM) * ((N + TL::SM_BN - 1) / TL::SM_BN);
             bk = TL::SM_BK;
         }
-        long long want = (2LL * sms + tiles - 1) / tiles;
+        static const long long per_sm = getenv("POZ_DW_CTAS_PER_SM") ? std::max(1, atoi(getenv("POZ_DW_CTAS_PER_SM"))) : 4;
+        long long want = (per_sm * sms + tiles - 1) / tiles;
         long long max_by_batch = std::max<long long>(1, batch / 64);
         long long s = std::max<long long>(1, std::min<long long>({want, max_by_batch, (long long)c->max_splits}));
         long long kc = (batch + s - 1) / s;
@@ -701,8 +743,8 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     {
         ProfScope ps(c, "step_begin", stream);
         const double share = c->cfg.global_batch > 0 ? (double)batch / (double)c->cfg.global_batch : 1.0;
-        step_begin_kernel<<<1, 32, 0, stream>>>(c->st, c->cost_ring, c->cost_cap, c->stats, c->stats_cap, n_stat_slots(c), share);
-        POZ_LAUNCH_CHECK();
+        POZ_TRY(launch_pdl(step_begin_kernel, dim3(1), dim3(32), 0, stream, c->st, c->cost_ring, c->cost_cap, c->stats,
+                           c->stats_cap, n_stat_slots(c), share));
     }
 
     // narrow classifier head: last Linear + softmax/CE + its backward-x in one kernel (head_ce_kernel)
@@ -777,8 +819,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         }
         ProfScope ps(c, "head", stream);
         const int blocks = (int)std::max<long long>(1, std::min<long long>((batch + 7) / 8, 2LL * num_sms(c->device)));
-        head_ce_kernel<T><<<blocks, 256, head_smem, stream>>>(h);
-        POZ_LAUNCH_CHECK();
+        POZ_TRY(launch_pdl(head_ce_kernel<T>, dim3(blocks), dim3(256), head_smem, stream, h));
     } else {
         LossArgs<T> a{};
         a.z = cur; a.target = target; a.row_idx = row_idx;
@@ -1051,6 +1092,7 @@ static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target,
 }
 
 #include "poz_general.inc"
+#include "poz_narrow_step_host.inc"
 
 template <typename T>
 static int forward_general_dispatch(poz_ctx* c, const void* x, const void* target, long long batch, T* out,
@@ -1073,11 +1115,10 @@ template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream
         c->have_diag = true;
     }
     ProfScope ps(c, "update", stream);
-    update_kernel<T><<<dim3(std::max(bx, 1), seg.n), 256, 0, stream>>>(
-        static_cast<T*>(c->P), static_cast<T*>(c->AM), static_cast<T*>(c->AV),
-        static_cast<const T*>(c->G), c->p_total, gdiag, seg, c->st, c->cost_ring, c->cost_cap, c->stats,
-        static_cast<__nv_bfloat16*>(c->Pb));
-    POZ_LAUNCH_CHECK();
+    POZ_TRY(launch_pdl(update_kernel<T>, dim3(std::max(bx, 1), seg.n), dim3(256), 0, stream,
+                       static_cast<T*>(c->P), static_cast<T*>(c->AM), static_cast<T*>(c->AV),
+                       static_cast<const T*>(c->G), c->p_total, gdiag, seg, static_cast<const DevState*>(c->st), c->cost_ring,
+                       c->cost_cap, c->stats, static_cast<__nv_bfloat16*>(c->Pb)));
     c->grads_pending = false;
     c->diag_pending = false;
     c->wp_stale = true;
@@ -1223,6 +1264,16 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
     if (const char* e = getenv("POZ_TC3_MIN_BATCH")) c->tc3_min_batch = atoll(e);
     if (const char* e = getenv("POZ_GRAPHS")) c->graphs_enabled = atoi(e) != 0;
     if (const char* e = getenv("POZ_FUSE_HEAD")) c->fuse_head = atoi(e) != 0;
+    if (getenv("POZ_KERNEL_TRACE") && atoi(getenv("POZ_KERNEL_TRACE")) != 0) {
+        fast::KernelTraceRec* buf = nullptr;
+        POZ_CUDA(cudaMemcpyFromSymbol(&buf, fast::d_ktrace, sizeof(buf)));
+        if (!buf) {
+            POZ_CUDA(cudaMalloc(&buf, sizeof(fast::KernelTraceRec) * (size_t)fast::KTRACE_CAP));
+            POZ_CUDA(cudaMemcpyToSymbol(fast::d_ktrace, &buf, sizeof(buf)));
+        }
+    }
+    if (const char* e = getenv("POZ_FUSED_STEP")) c->fused_step = atoi(e) != 0;
+    if (const char* e = getenv("POZ_FUSED_STEP_MAX_BATCH")) c->fused_step_max_batch = atoll(e);
     if (const char* e = getenv("POZ_TC3_TRAIN")) c->tc3_train = atoi(e) != 0;
     if (const char* e = getenv("POZ_TC3_TRAIN_MIN_BATCH")) c->tc3_train_min_batch = atoll(e);
     auto fail = [&](void) { poz_ctx_destroy(c); return 1; };
@@ -1293,6 +1344,52 @@ int poz_ctx_create(int device, int n_linear, const int* sizes, const int* act_co
     return poz_ctx_create_ex(device, &d, out);
 }
 
+// POZ_KERNEL_TRACE=1: print, for the last launch of every pipelined-GEMM shape, when its CTAs reached the
+// instrumented points (ns after the first CTA of that launch started).
+static void dump_kernel_trace() {
+    fast::KernelTraceRec* buf = nullptr;
+    if (cudaMemcpyFromSymbol(&buf, fast::d_ktrace, sizeof(buf)) != cudaSuccess || !buf) return;
+    cudaDeviceSynchronize();
+    unsigned int n = 0;
+    cudaMemcpyFromSymbol(&n, fast::d_ktrace_n, sizeof(n));
+    n = std::min(n, fast::KTRACE_CAP);
+    if (!n) return;
+    std::vector<fast::KernelTraceRec> h(n);
+    cudaMemcpy(h.data(), buf, sizeof(fast::KernelTraceRec) * n, cudaMemcpyDeviceToHost);
+    // walk backwards: group consecutive records of one launch (same tag and shape)
+    size_t end = n;
+    int shown = 0;
+    while (end > 0 && shown < 12) {
+        size_t beg = end;
+        const fast::KernelTraceRec& r0 = h[end - 1];
+        while (beg > 0 && h[beg - 1].tag == r0.tag && h[beg - 1].m == r0.m && h[beg - 1].n == r0.n && h[beg - 1].k == r0.k) --beg;
+        unsigned long long t0 = ~0ull;
+        for (size_t i = beg; i < end; ++i) t0 = std::min(t0, h[i].t[0]);
+        // keep only the CTAs of the LAST launch of this run of records: those that started within 200 us of the latest
+        unsigned long long latest = 0;
+        for (size_t i = beg; i < end; ++i) latest = std::max(latest, h[i].t[0]);
+        double mean[6] = {0, 0, 0, 0, 0, 0};
+        unsigned long long mx[6] = {0, 0, 0, 0, 0, 0};
+        unsigned long long first = ~0ull;
+        size_t cnt = 0;
+        for (size_t i = beg; i < end; ++i)
+            if (latest - h[i].t[0] < 30000) first = std::min(first, h[i].t[0]);
+        for (size_t i = beg; i < end; ++i) {
+            if (latest - h[i].t[0] >= 30000) continue;
+            ++cnt;
+            for (int q = 0; q < 6; ++q) { mean[q] += (double)(h[i].t[q] - first); mx[q] = std::max(mx[q], h[i].t[q] - first); }
+        }
+        fprintf(stderr, "[poz kernel trace] tag %d M %d N %d K %d: %zu CTAs; mean (max) ns after first CTA start: entry %.0f (%llu) "
+                        "setup+prologue %.0f (%llu) first tile ready %.0f (%llu) main loop done %.0f (%llu) epilogue done %.0f (%llu) exit %.0f (%llu)\n",
+                r0.tag, r0.m, r0.n, r0.k, cnt, mean[0] / cnt, mx[0], mean[1] / cnt, mx[1], mean[2] / cnt, mx[2], mean[3] / cnt, mx[3],
+                mean[4] / cnt, mx[4], mean[5] / cnt, mx[5]);
+        end = beg;
+        ++shown;
+    }
+    unsigned int zero = 0;
+    cudaMemcpyToSymbol(fast::d_ktrace_n, &zero, sizeof(zero));
+}
+
 int poz_ctx_destroy(poz_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
@@ -1306,6 +1403,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     if (c->feed.copy_stream) cudaStreamDestroy(c->feed.copy_stream);
     if (c->feed.read_stream) cudaStreamDestroy(c->feed.read_stream);
     if (c->feed.cost_pinned) cudaFreeHost(c->feed.cost_pinned);
+    if (getenv("POZ_KERNEL_TRACE") && atoi(getenv("POZ_KERNEL_TRACE")) != 0) dump_kernel_trace();
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     for (auto e : c->dz_ready) if (e) cudaEventDestroy(e);
@@ -1321,6 +1419,9 @@ int poz_ctx_destroy(poz_ctx* c) {
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
     dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
     dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz);
+    for (auto& p : c->step_plans) dev_free(p.d_tasks);
+    dev_free(reinterpret_cast<void*&>(c->step_barrier));
+    dev_free(reinterpret_cast<void*&>(c->step_trace));
     dev_free(reinterpret_cast<void*&>(c->tc_logits));
     dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
     dev_free(reinterpret_cast<void*&>(c->st));
@@ -1605,6 +1706,14 @@ int poz_train_apply(poz_ctx* c, void* stream) {
 int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
                    long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
     POZ_TRY(check_layer(c, 0, "poz_train_step"));
+    if (x_dev && target_dev && c->fused_step && c->step_grid == 0) POZ_TRY(fused_step_probe(c));
+    if (x_dev && target_dev && fused_step_eligible(c, batch, keep_masks, diagnostics)) {
+        // narrow fp32 stack: the whole step is one persistent kernel (no graph needed: it is one launch)
+        POZ_TRY(fused_step_launch(c, static_cast<const float*>(x_dev), target_dev, row_idx_dev, batch,
+                                  static_cast<cudaStream_t>(stream)));
+        c->epoch_host += 1;
+        return 0;
+    }
     const bool graphable = c->graphs_enabled && !c->profiling && !diagnostics && !keep_masks &&
                            c->dtype != POZ_DTYPE_BF16 && c->train_begun &&
                            stream != nullptr;   // the legacy default stream cannot be captured

@@ -119,6 +119,15 @@ template <typename T> __device__ __forceinline__ T act_bwd_from_out(int act, T a
     }
 }
 
+// ---- programmatic dependent launch ------------------------------------------------------------------
+// The kernels of a step form a dependent chain of launches that each fill the GPU for a few
+// microseconds.  Launched with the programmatic-stream-serialization attribute, a kernel's CTAs are
+// scheduled as soon as every CTA of its predecessor has passed pdl_trigger(), run whatever does not
+// touch the predecessor's results, and block in pdl_wait() until the predecessor grid has completed
+// and its memory is visible.  Both are no-ops for a launch without the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 template <typename T> __device__ __forceinline__ T warp_sum(T v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

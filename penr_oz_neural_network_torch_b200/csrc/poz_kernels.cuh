@@ -26,6 +26,8 @@ struct SegTable {
 // (neural_net_model.py:464 lr decay; torch/optim/adam.py bias corrections).
 __global__ void step_begin_kernel(DevState* st, double* cost_ring, long long cost_cap,
                                   double* stats, long long stats_cap, int n_layers, double l2_share) {
+    pdl_trigger();
+    pdl_wait();
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     long long e = st->next_epoch;
     st->l2_share = l2_share;
@@ -91,6 +93,8 @@ __device__ __forceinline__ void block_add_double(double v, double* dst) {
 // softmax + cross-entropy + gradient, one warp per row
 // (neural_net_model.py:188,400-403; gradient test_torch_backward.py:163-164)
 template <typename T> __global__ void ce_loss_kernel(LossArgs<T> a) {
+    pdl_trigger();
+    pdl_wait();
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     long long row = (long long)blockIdx.x * wpb + (threadIdx.x >> 5);
@@ -132,6 +136,8 @@ template <typename T> __global__ void ce_loss_kernel(LossArgs<T> a) {
 
 // plain row softmax for inference without a target (neural_net_model.py:188)
 template <typename T> __global__ void softmax_kernel(const T* z, T* out, long long M, int N) {
+    pdl_trigger();
+    pdl_wait();
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     long long row = (long long)blockIdx.x * wpb + (threadIdx.x >> 5);
@@ -151,6 +157,8 @@ template <typename T> __global__ void softmax_kernel(const T* z, T* out, long lo
 
 // the same for narrow rows (N <= 32): one thread per row, values held in registers
 template <typename T> __global__ void softmax_small_kernel(const T* __restrict__ z, T* __restrict__ out, long long M, int N) {
+    pdl_trigger();
+    pdl_wait();
     const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= M) return;
     const T* zr = z + row * N;
@@ -171,6 +179,8 @@ template <typename T> __global__ void softmax_small_kernel(const T* __restrict__
 
 // mean-squared error + gradient through the last activation (neural_net_model.py:405-406)
 template <typename T> __global__ void mse_loss_kernel(LossArgs<T> a) {
+    pdl_trigger();
+    pdl_wait();
     const long long total = a.M * a.N;
     const T* tgt = static_cast<const T*>(a.target);
     double local = 0.0;
@@ -219,12 +229,15 @@ template <typename T> __global__ void grad_finalize_kernel(T* g, long long slab,
 //   SGD : neural_net_model.py:499-500
 //   L2  : neural_net_model.py:482-483 (weights only)
 //   ratio statistics: neural_net_model.py:506-507
+// `part` of `parts` cooperating blocks works on segment l (a kernel passes blockIdx.x / gridDim.x; the
+// fused narrow step passes its own task split).  The gradient slabs may have been written earlier in
+// the same launch, so g is not marked read-only.
 template <typename T>
-__global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restrict__ av,
-                              const T* __restrict__ g, long long slab, T* __restrict__ g_diag,
-                              SegTable seg, const DevState* st, double* cost_base,
-                              long long cost_cap, double* stats, __nv_bfloat16* __restrict__ p_bf16) {
-    const int l = blockIdx.y;
+__device__ __forceinline__ void update_body(T* __restrict__ p, T* __restrict__ am, T* __restrict__ av,
+                                            const T* g, long long slab, T* __restrict__ g_diag,
+                                            const SegTable& seg, const DevState* st, double* cost_base,
+                                            long long cost_cap, double* stats, __nv_bfloat16* __restrict__ p_bf16,
+                                            int l, int part, int parts) {
     const long long n = seg.n_elems[l];
     const long long nw = seg.w_elems[l];
     const int S = seg.splits[l];
@@ -235,35 +248,61 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
     const T step_size = T(st->step_size), bc2s = T(st->bc2_sqrt), eps = T(st->eps);
     const long long rec = st->cur_record;
     double l2acc = 0.0, sd = 0.0, sd2 = 0.0, sw = 0.0, sw2 = 0.0;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-         i += (long long)gridDim.x * blockDim.x) {
-        const long long idx = seg.off[l] + i;
-        T gr = g[idx];
-        for (int k = 1; k < S; ++k) gr += g[(long long)k * slab + idx];
-        const T w = p[idx];
-        const bool is_w = i < nw;
-        if (is_w && st->l2 > 0.0) {
-            l2acc += (double)w * (double)w;
-            gr += T(2) * l2 * w;
+    // Four elements per thread and pass, all their loads issued before the first store: the stores may
+    // alias the gradient slabs as far as the compiler knows, so a one-element loop would serialise a
+    // full memory round trip per element.
+    constexpr int U = 4;
+    const long long stride = (long long)parts * blockDim.x;
+    const bool use_l2 = st->l2 > 0.0;
+    for (long long i0 = (long long)part * blockDim.x + threadIdx.x; i0 < n; i0 += U * stride) {
+        T gr[U], w[U], m[U], v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            gr[u] = T(0); w[u] = T(0); m[u] = T(0); v[u] = T(0);
+            if (i < n) {
+                const long long idx = seg.off[l] + i;
+                gr[u] = g[idx];
+                w[u] = p[idx];
+                if (adam) { m[u] = am[idx]; v[u] = av[idx]; }
+            }
         }
-        if (g_diag) g_diag[idx] = gr;
-        T wn;
-        if (adam) {
-            T m = am[idx], v = av[idx];
-            m = m + (gr - m) * b1c;
-            v = v * b2 + b2c * gr * gr;
-            am[idx] = m;
-            av[idx] = v;
-            T denom = sqrt(v) / bc2s + eps;
-            wn = w - step_size * (m / denom);
-        } else {
-            wn = w - lr * gr;
+        for (int k = 1; k < S; ++k) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const long long i = i0 + u * stride;
+                if (i < n) gr[u] += g[(long long)k * slab + seg.off[l] + i];
+            }
         }
-        p[idx] = wn;
-        if (p_bf16) p_bf16[idx] = __float2bfloat16_rn((float)wn);
-        if (rec >= 0 && is_w) {
-            double d = (double)wn - (double)w;
-            sd += d; sd2 += d * d; sw += (double)wn; sw2 += (double)wn * (double)wn;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            if (i >= n) continue;
+            const long long idx = seg.off[l] + i;
+            const bool is_w = i < nw;
+            T gu = gr[u];
+            if (is_w && use_l2) {
+                l2acc += (double)w[u] * (double)w[u];
+                gu += T(2) * l2 * w[u];
+            }
+            if (g_diag) g_diag[idx] = gu;
+            T wn;
+            if (adam) {
+                const T mu = m[u] + (gu - m[u]) * b1c;
+                const T vu = v[u] * b2 + b2c * gu * gu;
+                am[idx] = mu;
+                av[idx] = vu;
+                const T denom = sqrt(vu) / bc2s + eps;
+                wn = w[u] - step_size * (mu / denom);
+            } else {
+                wn = w[u] - lr * gu;
+            }
+            p[idx] = wn;
+            if (p_bf16) p_bf16[idx] = __float2bfloat16_rn((float)wn);
+            if (rec >= 0 && is_w) {
+                const double d = (double)wn - (double)w[u];
+                sd += d; sd2 += d * d; sw += (double)wn; sw2 += (double)wn * (double)wn;
+            }
         }
     }
     if (st->l2 > 0.0) block_add_double(l2acc * st->l2 * st->l2_share, cost_slot(cost_base, cost_cap, st));
@@ -274,6 +313,17 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
         block_add_double(sw, s + 2);
         block_add_double(sw2, s + 3);
     }
+}
+
+template <typename T>
+__global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restrict__ av,
+                              const T* __restrict__ g, long long slab, T* __restrict__ g_diag,
+                              SegTable seg, const DevState* st, double* cost_base,
+                              long long cost_cap, double* stats, __nv_bfloat16* __restrict__ p_bf16) {
+    pdl_trigger();
+    pdl_wait();
+    update_body<T>(p, am, av, g, slab, g_diag, seg, st, cost_base, cost_cap, stats, p_bf16, (int)blockIdx.y,
+                   (int)blockIdx.x, (int)gridDim.x);
 }
 
 // Bias gradient db[n] = sum_b dz[b][n] for float32 dz (test_torch_backward.py:166), two
@@ -419,27 +469,49 @@ template <typename T> struct HeadArgs {
     const DevState* st;
 };
 
-template <typename T> __global__ void __launch_bounds__(256) head_ce_kernel(HeadArgs<T> a) {
-    extern __shared__ __align__(16) unsigned char head_smem[];
+template <typename T>
+__device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char* head_smem, int part, int parts) {
     T* W = reinterpret_cast<T*>(head_smem);
     const int Ns = a.N | 1;                                  // odd row pitch
     T* bias = W + (long long)a.K * Ns;
     T* rows = bias + 32;                                     // [8 warps][K]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    T* arow = rows + (long long)warp * a.K;
+    // the first row of this warp and its label are requested before the weights, so that the three
+    // global round trips overlap
+    const long long m_first = (long long)part * wpb + warp;
+    int y_next = -1;
+    if (m_first < a.M) {
+        const T* ap = a.a_prev + m_first * a.K;
+        for (int k = lane; k < a.K; k += 32) arow[k] = ap[k];
+        y_next = a.labels[a.row_idx ? (long long)a.row_idx[m_first] : m_first];
+    }
     for (int i = threadIdx.x; i < a.K * a.N; i += blockDim.x) W[(i / a.N) * Ns + (i % a.N)] = a.wb[i];
     for (int i = threadIdx.x; i < 32; i += blockDim.x) bias[i] = (a.has_bias && i < a.N) ? a.wb[(long long)a.K * a.N + i] : T(0);
     __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-    T* arow = rows + (long long)warp * a.K;
     const T invb = T(a.inv_batch);
     double local = 0.0;
-    for (long long m = (long long)blockIdx.x * wpb + warp; m < a.M; m += (long long)gridDim.x * wpb) {
-        const T* ap = a.a_prev + m * a.K;
-        for (int k = lane; k < a.K; k += 32) arow[k] = ap[k];
+    for (long long m = m_first; m < a.M; m += (long long)parts * wpb) {
+        if (m != m_first) {
+            const T* ap = a.a_prev + m * a.K;
+            for (int k = lane; k < a.K; k += 32) arow[k] = ap[k];
+            y_next = a.labels[a.row_idx ? (long long)a.row_idx[m] : m];
+        }
         __syncwarp();
-        // logits: lane n < N owns logit n
+        // logits: lane n < N owns logit n; four partial sums keep the dependent chain short
         T z = bias[lane];
-        if (lane < a.N)
-            for (int k = 0; k < a.K; ++k) z = fma(arow[k], W[k * Ns + lane], z);
+        if (lane < a.N) {
+            T z1 = T(0), z2 = T(0), z3 = T(0);
+            int k = 0;
+            for (; k + 4 <= a.K; k += 4) {
+                z  = fma(arow[k],     W[k * Ns + lane], z);
+                z1 = fma(arow[k + 1], W[(k + 1) * Ns + lane], z1);
+                z2 = fma(arow[k + 2], W[(k + 2) * Ns + lane], z2);
+                z3 = fma(arow[k + 3], W[(k + 3) * Ns + lane], z3);
+            }
+            for (; k < a.K; ++k) z = fma(arow[k], W[k * Ns + lane], z);
+            z = (z + z1) + (z2 + z3);
+        }
         if (a.dz_last.enabled && lane < a.N) z = drop_keep(a.dz_last, a.st, m, lane, a.N) ? z * T(a.dz_last.scale) : T(0);
         if (a.z_rec && lane < a.N) a.z_rec[m * a.N + lane] = z;
         T zm = lane < a.N ? z : T(-INFINITY);
@@ -448,7 +520,7 @@ template <typename T> __global__ void __launch_bounds__(256) head_ce_kernel(Head
         const T s = warp_sum(e);
         const T p = e / s;
         if (a.probs && lane < a.N) a.probs[m * a.N + lane] = p;
-        const int y = a.labels[a.row_idx ? (long long)a.row_idx[m] : m];
+        const int y = y_next;
         T g = lane < a.N ? (p - (lane == y ? T(1) : T(0))) * invb : T(0);
         if (a.dz_rec && lane < a.N) a.dz_rec[m * a.N + lane] = g;
         if (a.dz_last.enabled && lane < a.N) g = drop_keep(a.dz_last, a.st, m, lane, a.N) ? g * T(a.dz_last.scale) : T(0);
@@ -479,6 +551,13 @@ template <typename T> __global__ void __launch_bounds__(256) head_ce_kernel(Head
         __syncwarp();
     }
     if (a.cost_base) block_add_double(local * a.inv_batch, cost_slot(a.cost_base, a.cost_cap, a.st));
+}
+
+template <typename T> __global__ void __launch_bounds__(256) head_ce_kernel(HeadArgs<T> a) {
+    extern __shared__ __align__(16) unsigned char head_smem[];
+    pdl_trigger();
+    pdl_wait();
+    head_ce_body<T>(a, head_smem, (int)blockIdx.x, (int)gridDim.x);
 }
 
 }  // namespace poz

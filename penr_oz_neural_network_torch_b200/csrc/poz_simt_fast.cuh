@@ -19,6 +19,18 @@ constexpr int BK = 16;
 constexpr int STAGES = 4;
 constexpr int TM = 4, TN = 4;
 
+// Debugging aid (POZ_KERNEL_TRACE=1): every CTA of the pipelined GEMMs records %globaltimer at five
+// points; poz_ctx_destroy prints, per kernel shape, when the CTAs reached them.  Null in normal runs.
+struct KernelTraceRec { int tag, m, n, k; unsigned long long t[6]; };
+__device__ KernelTraceRec* d_ktrace = nullptr;
+__device__ unsigned int d_ktrace_n = 0;
+constexpr unsigned int KTRACE_CAP = 1u << 20;
+__device__ __forceinline__ unsigned long long ktrace_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 struct Op {
     const float* ptr;
     long long ld;
@@ -44,10 +56,10 @@ template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.as
 // One operand tile -> shared memory.
 //   KC  (k contiguous in global): S[MN][BK+4], global rows <-> mn, cols <-> k
 //   !KC (mn contiguous in global): S[BK][MN+4], global rows <-> k,  cols <-> mn
-template <int MN, int NT, bool KC>
+template <int MN, int NT, bool KC, int PMN = 4>
 __device__ __forceinline__ void load_tile(float* S, const Op& op, long long mn0, long long k0, long long k_lim,
                                           int tid) {
-    constexpr int LD = KC ? BK + 4 : MN + 4;
+    constexpr int LD = KC ? BK + 4 : MN + PMN;
     constexpr int ROWS = KC ? MN : BK;
     constexpr int COLS = KC ? BK : MN;
     const long long row0 = KC ? mn0 : k0, col0 = KC ? k0 : mn0;
@@ -80,8 +92,8 @@ __device__ __forceinline__ void load_tile(float* S, const Op& op, long long mn0,
 // pointers (at the first k-tile) and row validity are computed once; per k-tile only the k bound
 // is re-checked and the pointer advanced.  Used when the operand allows 16-byte copies and its
 // gather (if any) is not along k.
-template <int MN, int NT, bool KC> struct TileCopier {
-    static constexpr int LD = KC ? BK + 4 : MN + 4;
+template <int MN, int NT, bool KC, int PMN = 4> struct TileCopier {
+    static constexpr int LD = KC ? BK + 4 : MN + PMN;
     static constexpr int ROWS = KC ? MN : BK;
     static constexpr int CV = (KC ? BK : MN) / 4;
     static constexpr int N = (ROWS * CV + NT - 1) / NT;
@@ -148,6 +160,16 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
     __shared__ __align__(16) float smem[SMEM_ELEMS];
 
     const int tid = threadIdx.x;
+    KernelTraceRec* ktr = nullptr;
+    if (d_ktrace && tid == 0) {
+        const unsigned int slot = atomicAdd(&d_ktrace_n, 1u);
+        if (slot < KTRACE_CAP) {
+            ktr = d_ktrace + slot;
+            ktr->tag = (A_KC ? 1 : 0) | (B_KC ? 2 : 0) | (COLSUM ? 4 : 0) | (BM == 64 ? 8 : 0);
+            ktr->m = (int)M; ktr->n = N; ktr->k = (int)Kd;
+            ktr->t[0] = ktrace_now();
+        }
+    }
     const int tx = tid % (BN / TN), ty = tid / (BN / TN);
     const long long m0 = (long long)blockIdx.y * BM;
     const int n0 = blockIdx.x * BN;
@@ -162,6 +184,7 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
     float bsum[TN] = {0.f, 0.f, 0.f, 0.f};
 
+    pdl_wait();   // everything above is index arithmetic; the operands may come from the previous launch
     // hoisted copy descriptors when the operands allow it (block-uniform conditions)
     const bool a_fast = A.vec4 && (A_KC || !A.row_idx);
     const bool b_fast = B.vec4 && (B_KC || !B.row_idx);
@@ -181,9 +204,11 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
         if (s < nk) issue(s);
         cp_commit();
     }
+    if (ktr) ktr->t[1] = ktrace_now();
     for (int t = 0; t < nk; ++t) {
         cp_wait<STAGES - 2>();
         __syncthreads();
+        if (ktr && t == 0) ktr->t[2] = ktrace_now();
         if (t + STAGES - 1 < nk) issue(t + STAGES - 1);
         cp_commit();
         const float* sa = smem + (t % STAGES) * STAGE_ELEMS;
@@ -231,6 +256,8 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
         }
     }
     cp_wait<0>();
+    pdl_trigger();   // the main loop is done: let the next launch's CTAs be scheduled behind this one's epilogue
+    if (ktr) ktr->t[3] = ktrace_now();
 
     cg::cluster_group cluster = cg::this_cluster();
     const unsigned csize = cluster.num_blocks();
@@ -263,7 +290,9 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
                 epi.template row<4>(m, n, vals, (N - n < 4) ? (N - n) : 4, 0);
             }
         }
+        if (ktr) ktr->t[4] = ktrace_now();
         cluster.sync();                        // peers may still be reading this CTA's tile
+        if (ktr) ktr->t[5] = ktrace_now();
         return;
     }
 
@@ -289,6 +318,7 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
         const int n = n0 + tx * TN;
         if (n < N) epi.template row<TN>(bias_row, n, bsum, (N - n < TN) ? (N - n) : TN, (int)blockIdx.z);
     }
+    if (ktr) { ktr->t[4] = ktrace_now(); ktr->t[5] = ktr->t[4]; }
 }
 
 // forward epilogue with an explicit bias (this kernel has no implicit ones column)

@@ -1,0 +1,78 @@
+"""The opt-in variants of the narrow float32 train step (environment switches read once per process):
+POZ_FUSED_STEP=1 (whole step in one persistent kernel, csrc/poz_narrow_step.cuh), POZ_TF32X3=1 (GEMMs on
+mma.sync with the error-compensated tf32 split, csrc/poz_tf32x3_gemm.cuh) and POZ_PDL=1 (programmatic
+dependent launches).  Each must give the oracle's numbers like the default path: three steps of
+BASELINE.json configs[1] (784-256-128-10, softmax + cross-entropy, batch 1024, Adam + L2) are run in a
+child process per switch (same seeded inputs as test_config2_full_size_against_live_oracle) and compared
+there with oracle/mlp_oracle.py at the float32 tolerance of
+tests/test_gpu_parity.py (rtol 1e-5, atol 1e-5 * max|reference|, relu-flip outliers allowed)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+CHILD = r'''
+import sys
+sys.path.insert(0, sys.argv[1])
+sys.path.insert(0, sys.argv[1] + "/tests")
+import numpy as np, torch
+from oracle import mlp_oracle as orc
+from oracle.detgen import det_params, det_normalish, det_labels
+from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+from test_gpu_parity import close, ADAM_PARAM_ATOL
+
+sizes = [784, 256, 128, 10]
+algos = ["linear", "relu", "linear", "relu", "linear", "softmax"]
+B = 1024
+params = det_params(sizes, True, 77)
+x = det_normalish((B, 784), 78)
+y = det_labels(B, 10, 79)
+eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+for l in range(3):
+    eng.upload_params(l, params[2 * l], params[2 * l + 1])
+xd = torch.tensor(x, dtype=torch.float32, device="cuda:0")
+yd = torch.tensor(y, dtype=torch.int32, device="cuda:0")
+eng.train_begin(optimizer="adam", learning_rate=0.01, decay_rate=0.9, l2_lambda=0.001, epochs=3)
+side = torch.cuda.Stream()
+with torch.cuda.stream(side):          # a non-default stream, so that graph replay is exercised too
+    for _ in range(3):
+        eng.train_step(xd, yd)
+torch.cuda.synchronize()
+stack = orc.parse_stack(algos)
+adam = orc.AdamState()
+p, costs = params, []
+tgt = [[int(v)] for v in y]
+for step in range(3):
+    p, c, *_ = orc.train_step(stack, p, x, tgt, lr=0.01 * 0.9 ** step, optimizer="adam", adam=adam, l2_lambda=0.001)
+    costs.append(c)
+close(eng.costs(0, 3), costs, "float32", "costs")
+for l in range(3):
+    w, b = eng.download_params(l)
+    close(w, p[2 * l], "float32", f"W{l}", atol=ADAM_PARAM_ATOL["float32"], outliers=True, loose_atol=0.02)
+    close(b, p[2 * l + 1], "float32", f"b{l}", atol=ADAM_PARAM_ATOL["float32"], outliers=True, loose_atol=0.02)
+out = eng.forward(xd).cpu().numpy()
+ref = orc.forward(stack, p, x)[0][-1]
+close(out, ref, "float32", "probs", rtol=1e-4)
+print("CHILD-OK")
+'''
+
+
+def run_child(env_extra):
+    env = dict(os.environ)
+    env.update(env_extra)
+    r = subprocess.run([sys.executable, "-c", CHILD, ROOT], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "CHILD-OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("switch", ["POZ_FUSED_STEP", "POZ_TF32X3", "POZ_PDL"])
+def test_optin_step_variants_match_the_oracle(switch):
+    run_child({switch: "1"})
+
+
+@pytest.mark.gpu
+def test_default_path_in_a_child_process_matches_too():
+    run_child({})

@@ -219,11 +219,12 @@ def run_c2(args, world, rank, local):
     hx = [torch.randn((batch, 784), dtype=torch.float32).pin_memory() for _ in range(n_host)]
     hy = [torch.randint(0, 10, (batch,), dtype=torch.int32).pin_memory() for _ in range(n_host)]
     e2e_steps = args.steps
-    # every step: host batch -> device, train step, that step's cost -> host.  The cost of step k is
-    # read while step k+1 runs (one step of lag), so the GPU never idles on the read-back.
-    # Through the C-ABI host-buffer call (poz_train_step_host): one call per step copies the pinned
-    # host batch to the device, runs the step and reads back the previous step's cost.  Host-side
-    # timing is exposed to host noise: three back-to-back timed regions, median reported.
+    # every step: host batch -> device, train step, a step's cost -> host, through the C-ABI host-buffer
+    # call (poz_train_step_host).  One call copies the pinned host batch to the device, launches the step
+    # and returns the cost of the step issued two calls earlier (POZ_HOST_LAG): the host stays two steps
+    # ahead, so the copy of step k+2 and the host's launch work overlap steps k and k+1.  Every step's cost
+    # reaches the host inside the timed region (the last two through the flush).  Host-side timing is
+    # exposed to host noise: three back-to-back timed regions, median reported.
     e2e_runs = []
     last = 0.0
     eng.train_begin(optimizer="adam", epochs=args.warmup + 3 * e2e_steps + 8, **HP)
@@ -236,12 +237,24 @@ def run_c2(args, world, rank, local):
         t0 = time.perf_counter()
         for i in range(e2e_steps):
             last = eng.train_step_host(hx[k % n_host], hy[k % n_host]); k += 1
-        last = eng.train_host_flush()
+        last = eng.train_host_flush()[-1]
         barrier_sync(world)
         e2e_runs.append(max_over_ranks((time.perf_counter() - t0) * 1e3, world))
     e2e_ms = float(np.median(e2e_runs))
     h2d_bytes, d2h_bytes = batch * 784 * 4 + batch * 4, 8
     assert np.isfinite(last)
+    # what the host link of this box gives for one step's input (explains e2e when it is copy-bound:
+    # the copy of step k+1 overlaps step k, so e2e ~ max(step, copy) + host overhead)
+    probe = torch.empty((batch, 784), dtype=torch.float32, device=dev)
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(3):
+        probe.copy_(hx[0], non_blocking=True)
+    c0.record()
+    for i in range(20):
+        probe.copy_(hx[i % n_host], non_blocking=True)
+    c1.record()
+    torch.cuda.synchronize()
+    h2d_us = c0.elapsed_time(c1) * 1e3 / 20
     clocks = sampler.stop() if sampler else None
 
     # ---- per-kernel timing pass (CUDA events inside the library, on the launching stream) -----------
@@ -269,7 +282,9 @@ def run_c2(args, world, rank, local):
                 "algorithmic_bytes_per_launch": nbytes,
                 "fp32_fma": {"achieved_tflops": round(flops / per_launch_s / 1e12, 2), "nominal_peak_tflops": 74.4,
                              "frac": round(flops / per_launch_s / 74.4e12, 4),
-                             "note": "the binding bound of this SIMT kernel is the fp32 FMA pipe, not HBM"},
+                             "note": "fp32 FMA rate of the kernel; its main loop waits for operand tiles, not for "
+                                     "arithmetic (POZ_TF32X3=1 swaps the FFMAs for tensor-core MMAs at the same "
+                                     "kernel time; per-CTA trace in DESIGN.md section 4g)"},
                 "step": {"algorithmic_bytes": C2_STEP_BYTES, "flops": C2_STEP_FLOPS,
                          "hbm_frac": round(C2_STEP_BYTES / (ms / args.steps * 1e-3) / 1e9 / pk["hbm_gbs"], 4),
                          "fp32_fma_frac": round(C2_STEP_FLOPS / (ms / args.steps * 1e-3) / 74.4e12, 4)},
@@ -281,8 +296,11 @@ def run_c2(args, world, rank, local):
                      "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                      "ms_per_step": e2e_ms / e2e_steps,
                      "note": "poz_train_step_host per step (pinned host batch in, cost out); median of 3 timed "
-                             "regions (host clock); the cost of step k is read back while step k+1 runs",
-                     "runs_ms_per_step": [round(v / e2e_steps, 5) for v in e2e_runs]},
+                             "regions (host clock); each call returns the cost of the step two calls earlier, so "
+                             "copy k+2 and the host's launch work overlap steps k and k+1",
+                     "runs_ms_per_step": [round(v / e2e_steps, 5) for v in e2e_runs],
+                     "h2d_copy_us_per_step": round(h2d_us, 1),
+                     "h2d_gbs": round(batch * 784 * 4 / (h2d_us * 1e-6) / 1e9, 1)},
                 gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
                 config={"workload": "c2: MLP 784-256-128-10 relu/relu/softmax + cross-entropy, Adam, L2 1e-3, "
                                     "batch 1024, fp32 train step", "batch_per_gpu": batch,

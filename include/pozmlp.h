@@ -145,16 +145,20 @@ int poz_train_costs(poz_ctx* ctx, long long first, long long count, double* cost
 /* The same step from HOST buffers -- the tensor copy of neural_net_model.py:472 plus the step plus the
  * cost.item() of :503 in one call.  x_host [batch][in] in the context's compute dtype (int32 token indices
  * for an embedding head), target_host int32 labels [batch] or [batch][out]; both should be pinned so the
- * copies are asynchronous.  The batch goes to one of two device slots on an internal copy stream, so
- * the copy of this call overlaps the kernels of the previous step; the step itself runs on `stream`
- * (replayed from a CUDA graph once a slot has been seen twice; use a non-default stream for that).
- * *prev_cost receives the cost of the PREVIOUS host step (NaN on the first call), read back on its own
- * stream without waiting for the step just launched.  The host buffers of a call may be reused once the
- * next call (or poz_train_host_flush) has returned.  poz_train_host_flush waits for the last step and
- * returns its cost. */
+ * copies are asynchronous.  The batch goes to one of POZ_HOST_LAG + 1 device slots on an internal copy
+ * stream, so the copy of this call overlaps the kernels of the steps before it; the step itself runs on
+ * `stream` (replayed from a CUDA graph once a slot has been seen twice; use a non-default stream for that).
+ * *done_cost receives the cost of the host step issued POZ_HOST_LAG calls earlier (NaN on the first
+ * POZ_HOST_LAG calls), read back on its own stream: the call returns when THAT step has finished, so the
+ * host runs POZ_HOST_LAG steps ahead of the GPU and neither a slow host link nor host-side launch
+ * latency leaves the GPU idle.  The host buffers of a call may be reused once POZ_HOST_LAG further calls
+ * (or poz_train_host_flush) have returned.  poz_train_host_flush waits for the outstanding steps and
+ * returns their costs, oldest first, right-aligned in last_costs[POZ_HOST_LAG] (NaN where fewer steps
+ * were outstanding). */
+#define POZ_HOST_LAG 2
 int poz_train_step_host(poz_ctx* ctx, const void* x_host, const void* target_host, long long batch,
-                        double* prev_cost, void* stream);
-int poz_train_host_flush(poz_ctx* ctx, double* last_cost);
+                        double* done_cost, void* stream);
+int poz_train_host_flush(poz_ctx* ctx, double* last_costs);
 /* ratios_host [count][n_linear]: std(w_new - w_old) / (std(w_new) + 1e-8), unbiased std. */
 int poz_train_update_ratios(poz_ctx* ctx, long long first_record, long long count,
                             double* ratios_host, void* stream);

@@ -1395,7 +1395,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     clear_graphs(c);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < poz_ctx::HostFeed::SLOTS; ++i) {
         dev_free(c->feed.x[i]); dev_free(c->feed.t[i]);
         if (c->feed.copied[i]) cudaEventDestroy(c->feed.copied[i]);
         if (c->feed.consumed[i]) cudaEventDestroy(c->feed.consumed[i]);
@@ -1651,7 +1651,6 @@ int poz_train_begin(poz_ctx* c, const poz_train_config* cfg) {
     c->train_begun = true;
     c->epoch_host = 0;
     c->feed.calls = 0;
-    c->feed.prev_epoch = -1;
     {   // captured steps bake these into kernel arguments; everything else lives in DevState
         const double sig[6] = {cfg->dropout_rate, (double)cfg->global_batch, (double)c->cost_cap, (double)c->stats_cap,
                                (double)reinterpret_cast<uintptr_t>(c->cost_ring), (double)reinterpret_cast<uintptr_t>(c->stats)};
@@ -1778,10 +1777,11 @@ static long long feed_t_row_bytes(const poz_ctx* c) {
 
 static int feed_reserve(poz_ctx* c, long long batch) {
     poz_ctx::HostFeed& f = c->feed;
+    constexpr int SLOTS = poz_ctx::HostFeed::SLOTS;
     if (!f.copy_stream) {
         POZ_CUDA(cudaStreamCreateWithFlags(&f.copy_stream, cudaStreamNonBlocking));
         POZ_CUDA(cudaStreamCreateWithFlags(&f.read_stream, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < SLOTS; ++i) {
             POZ_CUDA(cudaEventCreateWithFlags(&f.copied[i], cudaEventDisableTiming));
             POZ_CUDA(cudaEventCreateWithFlags(&f.consumed[i], cudaEventDisableTiming));
         }
@@ -1789,30 +1789,30 @@ static int feed_reserve(poz_ctx* c, long long batch) {
     }
     if (batch > f.batch) {
         POZ_CUDA(cudaDeviceSynchronize());
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < SLOTS; ++i) {
             dev_free(f.x[i]); dev_free(f.t[i]);
             POZ_TRY(dev_alloc(&f.x[i], (size_t)(batch * feed_x_row_bytes(c))));
             POZ_TRY(dev_alloc(&f.t[i], (size_t)(batch * feed_t_row_bytes(c))));
         }
         f.batch = batch;
         f.calls = 0;
-        f.prev_epoch = -1;
         clear_graphs(c);
     }
     return 0;
 }
 
-static int feed_read_cost(poz_ctx* c, int slot, long long epoch, double* out) {
+// cost of the step that last used `slot`: waits for that step only
+static int feed_read_cost(poz_ctx* c, int slot, double* out) {
     poz_ctx::HostFeed& f = c->feed;
     POZ_CUDA(cudaStreamWaitEvent(f.read_stream, f.consumed[slot], 0));
-    POZ_CUDA(cudaMemcpyAsync(f.cost_pinned, c->cost_ring + (epoch % c->cost_cap), sizeof(double), cudaMemcpyDeviceToHost,
-                             f.read_stream));
+    POZ_CUDA(cudaMemcpyAsync(f.cost_pinned, c->cost_ring + (f.epoch_of[slot] % c->cost_cap), sizeof(double),
+                             cudaMemcpyDeviceToHost, f.read_stream));
     POZ_CUDA(cudaStreamSynchronize(f.read_stream));
     *out = *f.cost_pinned;
     return 0;
 }
 
-int poz_train_step_host(poz_ctx* c, const void* x_host, const void* target_host, long long batch, double* prev_cost,
+int poz_train_step_host(poz_ctx* c, const void* x_host, const void* target_host, long long batch, double* done_cost,
                         void* stream) {
     POZ_TRY(check_layer(c, 0, "poz_train_step_host"));
     if (!x_host || !target_host) POZ_FAIL("poz_train_step_host: NULL buffer");
@@ -1820,35 +1820,45 @@ int poz_train_step_host(poz_ctx* c, const void* x_host, const void* target_host,
     if (batch <= 0) POZ_FAIL("poz_train_step_host: empty batch");
     POZ_TRY(feed_reserve(c, batch));
     poz_ctx::HostFeed& f = c->feed;
+    constexpr int SLOTS = poz_ctx::HostFeed::SLOTS;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    const int slot = (int)(f.calls & 1);
+    const int slot = (int)(f.calls % SLOTS);
     // host -> device on the copy stream; the slot is free once the step that last used it has run
-    if (f.calls >= 2) POZ_CUDA(cudaStreamWaitEvent(f.copy_stream, f.consumed[slot], 0));
+    // (that step's cost was already read by an earlier call, so this wait never blocks the GPU)
+    if (f.calls >= SLOTS) POZ_CUDA(cudaStreamWaitEvent(f.copy_stream, f.consumed[slot], 0));
     POZ_CUDA(cudaMemcpyAsync(f.x[slot], x_host, (size_t)(batch * feed_x_row_bytes(c)), cudaMemcpyHostToDevice, f.copy_stream));
     POZ_CUDA(cudaMemcpyAsync(f.t[slot], target_host, (size_t)(batch * feed_t_row_bytes(c)), cudaMemcpyHostToDevice, f.copy_stream));
     POZ_CUDA(cudaEventRecord(f.copied[slot], f.copy_stream));
     POZ_CUDA(cudaStreamWaitEvent(s, f.copied[slot], 0));
-    const long long epoch = c->epoch_host;
+    f.epoch_of[slot] = c->epoch_host;
     POZ_TRY(poz_train_step(c, f.x[slot], f.t[slot], nullptr, batch, nullptr, 0, stream));
     POZ_CUDA(cudaEventRecord(f.consumed[slot], s));
-    // the previous step's cost: only that step is waited for, the one just launched keeps running
-    if (prev_cost) {
-        *prev_cost = NAN;
-        if (f.calls >= 1 && f.prev_epoch >= 0) POZ_TRY(feed_read_cost(c, slot ^ 1, f.prev_epoch, prev_cost));
-    }
-    f.prev_epoch = epoch;
     f.calls += 1;
+    // the cost of the step issued POZ_HOST_LAG calls ago: only that step is waited for
+    if (done_cost) {
+        *done_cost = NAN;
+        if (f.calls > POZ_HOST_LAG) POZ_TRY(feed_read_cost(c, (int)((f.calls - 1 - POZ_HOST_LAG) % SLOTS), done_cost));
+    } else if (f.calls > POZ_HOST_LAG) {
+        POZ_CUDA(cudaEventSynchronize(f.consumed[(f.calls - 1 - POZ_HOST_LAG) % SLOTS]));   // keep the host POZ_HOST_LAG steps ahead, no further
+    }
     return 0;
 }
 
-int poz_train_host_flush(poz_ctx* c, double* last_cost) {
+int poz_train_host_flush(poz_ctx* c, double* last_costs) {
     POZ_TRY(check_layer(c, 0, "poz_train_host_flush"));
     poz_ctx::HostFeed& f = c->feed;
-    if (last_cost) *last_cost = NAN;
-    if (!f.copy_stream || f.calls == 0 || f.prev_epoch < 0) return 0;
-    if (last_cost) POZ_TRY(feed_read_cost(c, (int)((f.calls - 1) & 1), f.prev_epoch, last_cost));
-    else POZ_CUDA(cudaEventSynchronize(f.consumed[(f.calls - 1) & 1]));
-    f.prev_epoch = -1;
+    constexpr int SLOTS = poz_ctx::HostFeed::SLOTS;
+    if (last_costs)
+        for (int i = 0; i < POZ_HOST_LAG; ++i) last_costs[i] = NAN;
+    if (!f.copy_stream || f.calls == 0) return 0;
+    const long long outstanding = std::min<long long>(f.calls, POZ_HOST_LAG);
+    for (long long i = 0; i < outstanding; ++i) {
+        const long long call = f.calls - outstanding + i;          // 0-based index of the host step
+        const int slot = (int)(call % SLOTS);
+        if (last_costs) POZ_TRY(feed_read_cost(c, slot, last_costs + (POZ_HOST_LAG - outstanding + i)));
+        else POZ_CUDA(cudaEventSynchronize(f.consumed[slot]));
+    }
+    f.calls = 0;
     return 0;
 }
 

@@ -110,16 +110,17 @@ struct poz_ctx {
     long long fused_step_max_batch = 16384;
     double graph_sig[6] = {0, 0, 0, 0, 0, 0};
 
-    // host-buffer stepping (poz_train_step_host): two device slots, copy + read-back streams
+    // host-buffer stepping (poz_train_step_host): POZ_HOST_LAG + 1 device slots, copy + read-back streams
     struct HostFeed {
-        void* x[2] = {nullptr, nullptr};
-        void* t[2] = {nullptr, nullptr};
-        cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr};
+        static constexpr int SLOTS = POZ_HOST_LAG + 1;
+        void* x[SLOTS] = {};
+        void* t[SLOTS] = {};
+        cudaEvent_t copied[SLOTS] = {}, consumed[SLOTS] = {};
+        long long epoch_of[SLOTS] = {};   // epoch index of the step that last used the slot
         cudaStream_t copy_stream = nullptr, read_stream = nullptr;
         double* cost_pinned = nullptr;
         long long batch = 0;           // capacity of the slots
-        long long calls = 0;           // host steps since poz_train_begin
-        long long prev_epoch = -1;     // epoch index of the previous host step
+        long long calls = 0;           // host steps since the last flush / poz_train_begin
     } feed;
     long long epoch_host = 0;          // steps launched since poz_train_begin (mirrors DevState::next_epoch)
 

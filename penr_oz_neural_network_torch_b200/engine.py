@@ -357,8 +357,10 @@ class DeviceMLP:
 
     def train_step_host(self, x_host: torch.Tensor, target_host: torch.Tensor) -> float:
         """One step from (pinned) HOST tensors through poz_train_step_host: copy, step and the
-        read-back of the previous step's cost in a single C call.  Returns the cost of the previous
-        host step (NaN on the first call); ``train_host_flush`` returns the last one."""
+        read-back of an earlier step's cost in a single C call.  Returns the cost of the host step issued
+        HOST_LAG (= 2, include/pozmlp.h POZ_HOST_LAG) calls earlier, NaN on the first HOST_LAG calls;
+        ``train_host_flush`` returns the costs still outstanding.  The host tensors of a call may be
+        overwritten once HOST_LAG further calls (or the flush) have returned."""
         if x_host.is_cuda or target_host.is_cuda or not x_host.is_contiguous() or not target_host.is_contiguous():
             raise ValueError("train_step_host takes contiguous CPU tensors (pinned for asynchronous copies)")
         want = torch.int32 if self.embedding else self.tdtype
@@ -369,10 +371,14 @@ class DeviceMLP:
                                                C.byref(prev), _stream_ptr(self.device)))
         return float(prev.value)
 
-    def train_host_flush(self) -> float:
-        last = C.c_double()
-        nat.check(self.lib.poz_train_host_flush(self.ctx, C.byref(last)))
-        return float(last.value)
+    HOST_LAG = 2
+
+    def train_host_flush(self) -> list:
+        """Waits for the outstanding host steps; their costs, oldest first (HOST_LAG entries, NaN where
+        fewer steps were outstanding)."""
+        last = (C.c_double * self.HOST_LAG)()
+        nat.check(self.lib.poz_train_host_flush(self.ctx, last))
+        return [float(v) for v in last]
 
     def train_backward(self, x, target, row_idx=None, masks=None, diagnostics=False):
         batch = self._check_step_args(x, target, row_idx)

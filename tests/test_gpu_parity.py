@@ -397,8 +397,8 @@ def test_device_statistics_equal_host_torch_statistics(dtype):
 
 
 def test_host_buffer_steps_equal_device_buffer_steps():
-    """poz_train_step_host (pinned host batch in, previous cost out) trains exactly like
-    poz_train_step on device-resident copies of the same batches."""
+    """poz_train_step_host (pinned host batch in, the cost of the step two calls earlier out) trains
+    exactly like poz_train_step on device-resident copies of the same batches."""
     from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
     sizes, algos = [40, 24, 6], ["linear", "relu", "linear", "softmax"]
     params = det_params(sizes, True, 301)
@@ -414,7 +414,8 @@ def test_host_buffer_steps_equal_device_buffer_steps():
         with torch.cuda.stream(side):
             if host:
                 got = [eng.train_step_host(x, y) for x, y in batches]
-                got = got[1:] + [eng.train_host_flush()]
+                assert all(np.isnan(v) for v in got[:eng.HOST_LAG])
+                got = got[eng.HOST_LAG:] + eng.train_host_flush()
             else:
                 for x, y in batches:
                     eng.train_step(x.cuda(), y.cuda())

@@ -36,6 +36,7 @@ template <bool A_KC, bool B_KC, bool COLSUM, class Epi>
 __global__ void __launch_bounds__(128)
 gemm_tf32x3_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chunk, long long bias_row, Epi epi) {
     constexpr int BM = 32, BN = 64, NT = 128;
+    constexpr int STAGES = 6;   // shadows fast::STAGES: this kernel's tiles are small enough for a deeper pipeline
     // mn-contiguous tiles are padded to a row pitch of 8 (mod 32) words so that the fragment reads
     // (4 k-rows x 8 consecutive columns per instruction) hit 32 distinct banks
     constexpr int PMN = 8;

@@ -282,9 +282,9 @@ def run_c2(args, world, rank, local):
                 "algorithmic_bytes_per_launch": nbytes,
                 "fp32_fma": {"achieved_tflops": round(flops / per_launch_s / 1e12, 2), "nominal_peak_tflops": 74.4,
                              "frac": round(flops / per_launch_s / 74.4e12, 4),
-                             "note": "fp32 FMA rate of the kernel; its main loop waits for operand tiles, not for "
-                                     "arithmetic (POZ_TF32X3=1 swaps the FFMAs for tensor-core MMAs at the same "
-                                     "kernel time; per-CTA trace in DESIGN.md section 4g)"},
+                             "note": "fp32 FMA rate of the kernel including launch, prologue and the cluster "
+                                     "reduction; inside its main loop the FMA pipe is ~46 % busy (per-CTA trace, "
+                                     "DESIGN.md section 4g)"},
                 "step": {"algorithmic_bytes": C2_STEP_BYTES, "flops": C2_STEP_FLOPS,
                          "hbm_frac": round(C2_STEP_BYTES / (ms / args.steps * 1e-3) / 1e9 / pk["hbm_gbs"], 4),
                          "fp32_fma_frac": round(C2_STEP_FLOPS / (ms / args.steps * 1e-3) / 74.4e12, 4)},

@@ -7,6 +7,7 @@
 #include "poz_simt_fast.cuh"
 #include "poz_narrow_step.cuh"
 #include "poz_tf32x3_gemm.cuh"
+#include "poz_tf32x3_tma_gemm.cuh"
 #include "poz_tc.h"
 #include "poz_tc3.h"
 #include "poz_wide_kernels.cuh"
@@ -303,11 +304,23 @@ static fast::Op make_fast_op(const float* ptr, long long ld, const int* row_idx,
 
 // POZ_TF32X3=1 runs the 32x64-tile GEMMs of float32 contexts on the warp-level tensor-core instruction
 // with the error-compensated split (poz_tf32x3_gemm.cuh).  It passes the same parity tests, but measured
-// on B200 the C2 step does not get faster (the main loops of these GEMMs wait for operand tiles, not
-// for arithmetic: DESIGN.md section 4g), so the exact-fp32 FFMA kernel stays the default.
+// on B200 the C2 step does not get faster (three tf32 MMAs per product are only 1.3x the FFMA pipe, and
+// both kernels keep their pipe ~half busy at these sizes: DESIGN.md section 4g), so the exact-fp32 FFMA
+// kernel stays the default.
 static bool tf32x3_enabled() {
     static const bool on = getenv("POZ_TF32X3") && atoi(getenv("POZ_TF32X3")) != 0;
     return on;
+}
+
+// POZ_TMA_GEMM=1: the same GEMMs with TMA-delivered operand tiles (poz_tf32x3_tma_gemm.cuh) wherever both
+// operands can be described by a tensor map (no row gather, 16-byte aligned base and row pitch).
+static bool tma_gemm_enabled() {
+    static const bool on = getenv("POZ_TMA_GEMM") && atoi(getenv("POZ_TMA_GEMM")) != 0;
+    return on;
+}
+static bool tma_operand_ok(const fast::Op& o) {
+    return !o.row_idx && (reinterpret_cast<uintptr_t>(o.ptr) & 15) == 0 && (o.ld % 4) == 0 && o.rows > 0 && o.cols > 0 &&
+           o.rows < (1LL << 31) && o.ld * 4 < (1LL << 40);
 }
 
 template <int BM, int BN, bool A_KC, bool B_KC, bool COLSUM, class Epi>
@@ -335,6 +348,17 @@ static int launch_fast(const fast::Op& A, const fast::Op& B, long long M, int N,
         ++na;
     }
     if (na) { cfg.attrs = attr; cfg.numAttrs = na; }
+    if (BM == 32 && BN == 64 && tma_gemm_enabled() && tma_operand_ok(A) && tma_operand_ok(B)) {
+        // TMA-fed 3xTF32 kernel: boxes of 32 floats (A: 32 rows or 32 k-rows; B: 64 rows or 32 k-rows)
+        CUtensorMap ma, mb;
+        POZ_TRY(tc::make_map_f32(&ma, A.ptr, A.rows, A.cols, A.ld, 32));
+        POZ_TRY(tc::make_map_f32(&mb, B.ptr, B.rows, B.cols, B.ld, B_KC ? 64 : 32));
+        long long kc = (Kd + splits - 1) / splits;
+        kc = ((kc + fast::TBK - 1) / fast::TBK) * fast::TBK;
+        POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_tf32x3_tma<A_KC, B_KC, COLSUM, Epi>, ma, mb, M, N, Kd, kc, bias_row, epi));
+        count_launch();
+        return 0;
+    }
     if (BM == 32 && BN == 64 && tf32x3_enabled())
         POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_tf32x3_pipelined<A_KC, B_KC, COLSUM, Epi>, A, B, M, N, Kd, k_chunk,
                                     bias_row, epi));

@@ -43,6 +43,22 @@ static int make_map(CUtensorMap* map, const void* ptr, long long rows, long long
     return 0;
 }
 
+int make_map_f32(void* map_out, const void* ptr, long long rows, long long cols, long long ld, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) POZ_FAIL("TMA path: cuTensorMapEncodeTiled is not available from the driver");
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (ld * 4) % 16 != 0)
+        POZ_FAIL("TMA path: operand base and row pitch must be 16-byte aligned");
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(static_cast<CUtensorMap*>(map_out), CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), gdim,
+                    gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) POZ_FAIL("TMA path: cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return 0;
+}
+
 template <int A_MAJOR, int B_MAJOR, int EPI>
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, long long M, int N, long long K, int splits,
                   const EpiParams& ep, int sms, cudaStream_t stream) {

@@ -14,5 +14,8 @@ int gemm_backward_data(const __nv_bfloat16* dz, const __nv_bfloat16* w, long lon
 // g[split][K_in][N_out] = partial sums over the batch of x[batch][K_in]^T * dz[batch][N_out]
 int gemm_backward_weight(const __nv_bfloat16* x, const __nv_bfloat16* dz, long long batch, int K_in, int N_out,
                          float* g, long long slab, int splits, int sms, cudaStream_t s);
+// TMA descriptor of a row-major fp32 matrix [rows][cols] (pitch ld elements) for boxes of 32 columns (one
+// 128-byte swizzle row) by box_rows rows; `map_out` points at a CUtensorMap.  Used by the TMA-fed narrow GEMM.
+int make_map_f32(void* map_out, const void* ptr, long long rows, long long cols, long long ld, int box_rows);
 }  // namespace tc
 }  // namespace poz

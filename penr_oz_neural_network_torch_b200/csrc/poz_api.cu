@@ -6,6 +6,7 @@
 #include "poz_simt_gemm.cuh"
 #include "poz_simt_fast.cuh"
 #include "poz_narrow_step.cuh"
+#include "poz_infer_small.cuh"
 #include "poz_tf32x3_gemm.cuh"
 #include "poz_tf32x3_tma_gemm.cuh"
 #include "poz_tc.h"
@@ -589,11 +590,79 @@ template <typename T>
 static int forward_general_dispatch(poz_ctx* c, const void* x, const void* target, long long batch, T* out,
                                     double* cost_host, cudaStream_t stream);
 
+// A few rows of a plain float32 stack: the whole forward pass in one cluster launch (poz_infer_small.cuh).
+// Returns 1 through *taken when it ran.  POZ_SMALL_INFER=0 keeps such calls on the per-layer kernels.
+static int forward_small(poz_ctx* c, const float* x, long long batch, float* out, cudaStream_t stream, bool* taken) {
+    *taken = false;
+    static const bool enabled = !(getenv("POZ_SMALL_INFER") && atoi(getenv("POZ_SMALL_INFER")) == 0);
+    if (!enabled || c->small_infer_cluster < 0 || batch > si::SI_MAX_BATCH || c->nl > si::SI_MAX_LAYERS) return 0;
+    for (int l = 0; l + 1 < c->nl; ++l)
+        if (c->acts[l] == ACT_SOFTMAX) return 0;
+    if (c->small_infer_cluster == 0) {
+        // probe once: the largest cluster (16 needs the non-portable opt-in, else 8) this kernel can be launched with
+        c->small_infer_cluster = -1;
+        POZ_CUDA(cudaFuncSetAttribute(si::infer_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        const bool np = cudaFuncSetAttribute(si::infer_small_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+        cudaGetLastError();
+        const int cs_max = getenv("POZ_SMALL_INFER_CLUSTER") ? atoi(getenv("POZ_SMALL_INFER_CLUSTER")) : 16;
+        for (int cs : {16, 8}) {
+            if ((cs == 16 && !np) || cs > cs_max) continue;
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(cs); cfg.blockDim = dim3(si::SI_THREADS); cfg.dynamicSmemBytes = 200 * 1024;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, si::infer_small_kernel, &cfg) == cudaSuccess && n >= 1) {
+                c->small_infer_cluster = cs;
+                break;
+            }
+            cudaGetLastError();
+        }
+        if (c->small_infer_cluster < 0) return 0;
+    }
+    const int C = c->small_infer_cluster;
+    si::Args a{};
+    a.nl = c->nl; a.has_bias = c->has_bias; a.batch = (int)batch;
+    int max_w = 0, cols_cap = 1;
+    for (int l = 0; l <= c->nl; ++l) { a.sizes[l] = c->sizes[l]; max_w = std::max(max_w, c->sizes[l]); }
+    for (int l = 0; l < c->nl; ++l) {
+        a.acts[l] = c->acts[l];
+        a.wb[l] = static_cast<const float*>(c->P) + c->off[l];
+        cols_cap = std::max(cols_cap, (c->sizes[l + 1] + C - 1) / C);
+    }
+    if (cols_cap > si::SI_MAX_COLS) return 0;
+    a.max_w = max_w;
+    a.x = x; a.out = out;
+    const size_t smem = ((size_t)2 * batch * max_w + (size_t)si::SI_THREADS * batch) * sizeof(float);
+    if (smem > 200 * 1024) return 0;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(C); cfg.blockDim = dim3(si::SI_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    c->training_pass = false;
+    ProfScope ps(c, "infer_small", stream);
+    POZ_CUDA(cudaLaunchKernelEx(&cfg, si::infer_small_kernel, a));
+    count_launch();
+    *taken = true;
+    return 0;
+}
+
 template <typename T>
 static int forward_impl(poz_ctx* c, const T* x, const void* target, long long batch, T* out,
                         double* cost_host, cudaStream_t stream) {
     const int nl = c->nl;
     if (c->general) return forward_general_dispatch<T>(c, x, target, batch, out, cost_host, stream);
+    if constexpr (std::is_same<T, float>::value) {
+        if (!cost_host && !target) {
+            bool taken = false;
+            POZ_TRY(forward_small(c, x, batch, out, stream, &taken));
+            if (taken) return 0;
+        }
+    }
     if constexpr (std::is_same<T, float>::value) {
         // big batches of a deep-enough stack: every layer on the tensor cores
         if (batch >= c->tc3_min_batch && tc3_stack_ok(c)) return forward_tc3(c, x, target, batch, out, cost_host, stream);

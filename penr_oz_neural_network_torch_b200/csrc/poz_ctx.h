@@ -91,6 +91,7 @@ struct poz_ctx {
     std::vector<StepGraph> graphs;
     std::vector<StepGraph> fwd_graphs;   // inference calls: x = input, t = output buffer
     bool graphs_enabled = true;
+    int small_infer_cluster = 0;      // cluster size of the few-row inference kernel (0 = not probed, -1 = unavailable)
     bool fuse_head = true;            // narrow softmax head in one kernel (POZ_FUSE_HEAD=0 disables)
 
     // whole train step of a narrow fp32 stack in one persistent kernel (csrc/poz_narrow_step.cuh)

@@ -32,6 +32,11 @@ TOL = {"float32": (1e-5, 1e-5), "float64": (1e-10, 1e-12)}
 ADAM_PARAM_ATOL = {"float32": 2e-6, "float64": 1e-12}
 
 
+def launch_count():
+    from penr_oz_neural_network_torch_b200 import _native
+    return int(_native.lib().poz_launch_count())
+
+
 def close(got, want, dtype, what, rtol=None, atol=None, outliers=False, loose_atol=None):
     r, a = TOL[dtype]
     want = np.asarray(want, dtype=np.float64)
@@ -259,6 +264,40 @@ def test_config3_inference_sweep(batch):
         tail = xd[batch - 4096:].contiguous()
         again = eng.forward(tail)
         assert torch.allclose(out[batch - 4096:], again, rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("sizes,algos,has_bias", [
+    ([784, 256, 128, 10], ["linear", "relu", "linear", "relu", "linear", "softmax"], True),
+    ([13, 37, 5], ["linear", "sigmoid", "linear", "tanh"], False),
+    ([9, 70, 33, 21, 4], ["linear", "tanh", "linear", "relu", "linear", "sigmoid", "linear", "softmax"], True),
+    ([300, 1000, 7], ["linear", "relu", "linear"], True),
+])
+@pytest.mark.parametrize("batch", [1, 3, 4])
+def test_few_row_inference_in_one_cluster_launch(sizes, algos, has_bias, batch):
+    """Up to 4 rows of a plain float32 stack go through infer_small_kernel (one cluster, the layers
+    chained through distributed shared memory): against the oracle, and against the per-layer kernels
+    (which a 17-row call of the same rows uses)."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    params = det_params(sizes, has_bias, 611)
+    nl = len(sizes) - 1
+    per = 2 if has_bias else 1
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), has_bias, "float32", 0)
+    for l in range(nl):
+        eng.upload_params(l, params[per * l], params[per * l + 1] if has_bias else None)
+    x = det_normalish((17, sizes[0]), 612)
+    xd = torch.tensor(x, dtype=torch.float32, device="cuda:0")
+    before = launch_count()
+    out = eng.forward(xd[:batch].contiguous())
+    assert launch_count() - before == 1, "the few-row path is a single launch"
+    ref = orc.forward(orc.parse_stack(algos), params, x[:batch])[0][-1]
+    close(out.cpu().numpy(), ref.reshape(batch, -1), "float32", "output", rtol=1e-4)
+    layered = eng.forward(xd)[:batch]
+    assert torch.allclose(out, layered, rtol=2e-5, atol=1e-6)
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):                      # replayed from a graph on a side stream: same numbers
+        outs = [eng.forward(xd[:batch].contiguous()) for _ in range(3)]
+    side.synchronize()
+    assert all(torch.equal(o, out) for o in outs)
 
 
 def test_row_gather_equals_materialised_batch():

@@ -90,8 +90,7 @@ __device__ __forceinline__ void load_tile(float* S, const Op& op, long long mn0,
 // The same tile copy with everything that does not depend on the k-tile hoisted out of the main
 // loop: each thread owns a fixed set of 16-byte chunks, so their shared-memory offsets, source
 // pointers (at the first k-tile) and row validity are computed once; per k-tile only the k bound
-// is re-checked and the pointer advanced.  Used when the operand allows 16-byte copies and its
-// gather (if any) is not along k.
+// is re-checked and the pointer advanced.  Used whenever the operand allows 16-byte copies.
 template <int MN, int NT, bool KC, int PMN = 4> struct TileCopier {
     static constexpr int LD = KC ? BK + 4 : MN + PMN;
     static constexpr int ROWS = KC ? MN : BK;
@@ -104,9 +103,16 @@ template <int MN, int NT, bool KC, int PMN = 4> struct TileCopier {
     long long step;      // elements to advance per k-tile
     long long k_lim;     // exclusive bound on the global k index
     long long k_first;
+    // row gather along k (row-contiguous operand whose rows are the sampled batch rows: the first
+    // layer's weight gradient): the row of the next k-tile is looked up while the current one is issued
+    const int* gather;
+    long long ld;
+    int next_row[N];
 
     __device__ __forceinline__ void init(const Op& op, long long mn0, long long k_begin, long long k_end, int tid) {
         k_first = k_begin;
+        gather = KC ? nullptr : op.row_idx;
+        ld = op.ld;
         if (KC) { k_lim = k_end < op.cols ? k_end : (long long)op.cols; step = BK; }
         else    { k_lim = k_end < op.rows ? k_end : op.rows; step = (long long)BK * op.ld; }
 #pragma unroll
@@ -124,17 +130,27 @@ template <int MN, int NT, bool KC, int PMN = 4> struct TileCopier {
                 const long long gc = mn0 + cc;
                 ok[i] = ok[i] && gc < op.cols;
                 kofs[i] = r;
-                src[i] = ok[i] ? op.ptr + (k_begin + r) * op.ld + gc : op.ptr;
+                src[i] = ok[i] ? op.ptr + (gather ? gc : (k_begin + r) * op.ld + gc) : op.ptr;
+                next_row[i] = (gather && ok[i] && k_begin + r < k_lim) ? gather[k_begin + r] : 0;
             }
         }
     }
-    __device__ __forceinline__ void issue(float* S, int t) const {
+    // k-tiles must be issued in order (the gather looks one tile ahead)
+    __device__ __forceinline__ void issue(float* S, int t) {
         const long long kt = k_first + (long long)t * BK;
 #pragma unroll
         for (int i = 0; i < N; ++i) {
             if ((ROWS * CV) % NT != 0 && tid_out_of_range(i)) continue;
             const bool v = ok[i] && (kt + kofs[i] < k_lim);
-            cp_async16(S + soff[i], v ? src[i] + (long long)t * step : src[i], v ? 16 : 0);
+            const float* p = src[i];
+            if (!KC && gather) {
+                if (v) p = src[i] + (long long)next_row[i] * ld;
+                const long long kn = kt + BK + kofs[i];
+                if (ok[i] && kn < k_lim) next_row[i] = gather[kn];
+            } else if (v) {
+                p = src[i] + (long long)t * step;
+            }
+            cp_async16(S + soff[i], p, v ? 16 : 0);
         }
     }
     __device__ __forceinline__ bool tid_out_of_range(int i) const { return (int)threadIdx.x + i * NT >= ROWS * CV; }
@@ -186,8 +202,8 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
 
     pdl_wait();   // everything above is index arithmetic; the operands may come from the previous launch
     // hoisted copy descriptors when the operands allow it (block-uniform conditions)
-    const bool a_fast = A.vec4 && (A_KC || !A.row_idx);
-    const bool b_fast = B.vec4 && (B_KC || !B.row_idx);
+    const bool a_fast = A.vec4 != 0;
+    const bool b_fast = B.vec4 != 0;
     TileCopier<BM, NT, A_KC> ca;
     TileCopier<BN, NT, B_KC> cb;
     if (a_fast) ca.init(A, m0, k_begin, k_end, tid);

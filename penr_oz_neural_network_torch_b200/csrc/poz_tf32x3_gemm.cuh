@@ -77,8 +77,8 @@ gemm_tf32x3_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_
     float bsum[4] = {0.f, 0.f, 0.f, 0.f};
 
     pdl_wait();   // everything above is index arithmetic; the operands may come from the previous launch
-    const bool a_fast = A.vec4 && (A_KC || !A.row_idx);
-    const bool b_fast = B.vec4 && (B_KC || !B.row_idx);
+    const bool a_fast = A.vec4 != 0;
+    const bool b_fast = B.vec4 != 0;
     TileCopier<BM, NT, A_KC, PMN> ca;
     TileCopier<BN, NT, B_KC, PMN> cb;
     if (a_fast) ca.init(A, m0, k_begin, k_end, tid);

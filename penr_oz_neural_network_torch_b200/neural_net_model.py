@@ -509,6 +509,10 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         # one persistent index buffer: every epoch reuses the same device addresses, so the
         # library replays the step from a CUDA graph after the second epoch
         idx_d = torch.empty((sample_size,), dtype=torch.int32, device=eng.device)
+        # a small ring of pinned staging buffers, so that the per-epoch index upload is an asynchronous
+        # copy (a pageable source would stall the host on every epoch)
+        ring = [torch.empty((sample_size,), dtype=torch.int32).pin_memory() for _ in range(8)]
+        ring_done = [None] * len(ring)
         stamps = []
         fetched = 0
         last_serialized = time.time()
@@ -519,7 +523,13 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         with torch.cuda.stream(side):
             for epoch in range(epochs):
                 idx = torch.randint(0, n_data, (sample_size,))                  # :460, same generator
-                idx_d.copy_(idx.to(torch.int32))
+                slot = epoch % len(ring)
+                if ring_done[slot] is not None:
+                    ring_done[slot].synchronize()                               # its copy of 8 epochs ago
+                ring[slot].copy_(idx)
+                idx_d.copy_(ring[slot], non_blocking=True)
+                ring_done[slot] = torch.cuda.Event()
+                ring_done[slot].record(side)
                 if self.optimizer is not None:                                  # :467-469 (view only)
                     for group in self.optimizer.param_groups:
                         group["lr"] = learning_rate * (decay_rate ** epoch)

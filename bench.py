@@ -46,9 +46,9 @@ def init_params(sizes, seed=0):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures committed under
-# profiles/ncu/ (r01_c2_simt_full_raw.csv, r01_c4_tc_fwd_full_raw.csv); null where no capture exists.
-NCU_TRAFFIC = {"fwd_l0": 4_081_152, "bwd_w_l0": 4_301_568, "fwd_l1": 1_246_208, "bwd_w_l1": 1_614_592,
-               "bwd_x_l1": 1_769_472, "tc_fwd": 1_204_000_000}
+# profiles/ncu/ (r01_c2_simt_full_raw_v3.csv, r01_c4_tc_fwd_full_raw.csv); null where no capture exists.
+NCU_TRAFFIC = {"fwd_l0": 4_344_064, "bwd_w_l0": 4_307_712, "fwd_l1": 1_508_608, "bwd_w_l1": 1_620_736,
+               "bwd_w_l2": 613_376, "bwd_x_l1": 1_769_728, "tc_fwd": 1_204_000_000}
 
 
 def peaks():
@@ -303,7 +303,7 @@ def run_c2(args, world, rank, local):
         gbs = nbytes / per_launch_s / 1e9
         roof = {"bound": "hbm", "kernel": top, "achieved": round(gbs, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": round(gbs / pk["hbm_gbs"], 4), "traffic": NCU_TRAFFIC.get(top),
-                "traffic_source": "ncu --set full, profiles/ncu/r01_c2_simt_full_raw.csv" if top in NCU_TRAFFIC else None,
+                "traffic_source": "ncu --set full, profiles/ncu/r01_c2_simt_full_raw_v3.csv" if top in NCU_TRAFFIC else None,
                 "peak_source": pk["source"],
                 "us_per_launch": round(per_launch_s * 1e6, 2), "share_of_step": round(prof[top]["ms"] / tot, 3),
                 "algorithmic_bytes_per_launch": nbytes,

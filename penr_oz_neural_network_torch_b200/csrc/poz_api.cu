@@ -494,18 +494,23 @@ static tc3::PlaneMat tc3_weight(const poz_ctx* c, int l) {
     return m;
 }
 
-// Inference with every Linear layer on tcgen05: the input chunk is split into bf16 planes once,
-// each layer's epilogue writes the next layer's planes directly, and a chunk (8192 rows) of planes
-// is small enough to stay in L2 between the layer kernels.
+// Inference with every Linear layer on tcgen05: the input is split into bf16 planes once and each
+// layer's epilogue writes the next layer's planes directly.
 static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long batch, float* out,
                        double* cost_host, cudaStream_t stream) {
     const int nl = c->nl, sms = num_sms(c->device);
     POZ_TRY(tc3_refresh_weights(c, stream));
     long long widest = 0;
     for (int l = 0; l <= nl; ++l) widest = std::max<long long>(widest, round8(c->sizes[l]));
-    // chunk: input planes + the widest hidden planes of a chunk should fit in ~100 MB of L2, and the
-    // first (dominant) layer's 128x128 tiles of a chunk should fill whole waves of the SMs
-    long long chunk = (100LL << 20) / (6 * (round8(c->sizes[0]) + widest));
+    // Rows are processed in chunks only to bound the scratch planes (POZ_TC3_CHUNK_MB, default 3200 MB of
+    // input + widest hidden planes, ~356k rows of the 784-wide stack), and a chunk is a whole number of waves
+    // of the first (dominant) layer's 128x128 tiles.  An earlier version kept a chunk inside the L2 (100 MB):
+    // measured at 262,144 rows that was 2.16 ms per pass against 1.17 ms with one chunk -- per-chunk launches
+    // and tile-wave tails cost far more than the L2 hits saved (none of these kernels is HBM-bound).  Splitting
+    // chunk i+1 into planes on a side stream under the GEMMs of chunk i was measured too: 1.24 ms, the two
+    // compete for the same SMs and memory system.
+    static const long long chunk_mb = getenv("POZ_TC3_CHUNK_MB") ? std::max(1, atoi(getenv("POZ_TC3_CHUNK_MB"))) : 3200;
+    long long chunk = (chunk_mb << 20) / (6 * (round8(c->sizes[0]) + widest));
     {
         const long long tiles_n0 = (c->sizes[1] + 127) / 128;
         const long long rows_per_wave = std::max<long long>(1, sms / tiles_n0) * 128;

@@ -838,11 +838,25 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         xp.rows = batch; xp.cols = c->sizes[0]; xp.ld = round8(c->sizes[0]); xp.plane_stride = batch * xp.ld;
     }
 
+    static const bool sb_allowed = !(getenv("POZ_FORK_STEP_BEGIN") && atoi(getenv("POZ_FORK_STEP_BEGIN")) == 0);
+    const bool sb_forked = sb_allowed && c->fork_dw && c->side_stream && !masks && c->cfg.dropout_rate == 0.0;
     {
-        ProfScope ps(c, "step_begin", stream);
+        // The step's bookkeeping (epoch / Adam counters, lr_t, cost slot) is first needed by the loss kernel --
+        // the forward kernels read the step state only for dropout -- so without dropout it runs on the side
+        // stream beside the forward GEMMs instead of in front of them.
         const double share = c->cfg.global_batch > 0 ? (double)batch / (double)c->cfg.global_batch : 1.0;
-        POZ_TRY(launch_pdl(step_begin_kernel, dim3(1), dim3(32), 0, stream, c->st, c->cost_ring, c->cost_cap, c->stats,
-                           c->stats_cap, n_stat_slots(c), share));
+        cudaStream_t bs = stream;
+        if (sb_forked) {
+            bs = c->side_stream;
+            POZ_CUDA(cudaEventRecord(c->sb_fork, stream));
+            POZ_CUDA(cudaStreamWaitEvent(bs, c->sb_fork, 0));
+        }
+        {
+            ProfScope ps(c, "step_begin", bs);
+            POZ_TRY(launch_pdl(step_begin_kernel, dim3(1), dim3(32), 0, bs, c->st, c->cost_ring, c->cost_cap, c->stats,
+                               c->stats_cap, n_stat_slots(c), share));
+        }
+        if (sb_forked) POZ_CUDA(cudaEventRecord(c->sb_done, bs));
     }
 
     // narrow classifier head: last Linear + softmax/CE + its backward-x in one kernel (head_ce_kernel)
@@ -886,6 +900,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         cur_idx = nullptr;
     }
 
+    if (sb_forked) POZ_CUDA(cudaStreamWaitEvent(stream, c->sb_done, 0));
     // loss and the gradient of the last linear's pre-dropout output
     const long long gb = c->cfg.global_batch > 0 ? c->cfg.global_batch : batch;
     const int last = nl - 1;
@@ -1205,7 +1220,8 @@ template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream
     if (!reduced)
         for (int l = 0; l < c->nl; ++l) seg.splits[l] = c->seg_splits[l];
     const long long biggest = biggest_seg(seg);
-    int bx = (int)std::min<long long>((biggest + 255) / 256, 2LL * num_sms(c->device));
+    static const long long blocks_per_sm = getenv("POZ_UPDATE_BLOCKS_PER_SM") ? std::max(1, atoi(getenv("POZ_UPDATE_BLOCKS_PER_SM"))) : 2;
+    int bx = (int)std::min<long long>((biggest + 255) / 256, blocks_per_sm * num_sms(c->device));
     T* gdiag = nullptr;
     if (c->diag_pending) {
         if (!c->Gdiag) POZ_TRY(dev_alloc(&c->Gdiag, (size_t)c->p_total * c->esz));
@@ -1416,6 +1432,11 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
         set_error("cudaStreamCreate failed");
         return fail();
     }
+    if (cudaEventCreateWithFlags(&c->sb_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->sb_done, cudaEventDisableTiming) != cudaSuccess) {
+        set_error("cudaEventCreate failed");
+        return fail();
+    }
     if (const char* e = getenv("POZ_FORK_DW")) c->fork_dw = atoi(e) != 0;
     *out = c;
     return 0;
@@ -1477,6 +1498,15 @@ static void dump_kernel_trace() {
             ++cnt;
             for (int q = 0; q < 6; ++q) { mean[q] += (double)(h[i].t[q] - first); mx[q] = std::max(mx[q], h[i].t[q] - first); }
         }
+        {
+            unsigned long long last_exit = 0;
+            for (size_t i = beg; i < end; ++i)
+                if (latest - h[i].t[0] < 30000) last_exit = std::max(last_exit, h[i].t[5]);
+            static unsigned long long origin = 0;
+            if (!origin) origin = last_exit;       // the walk is backwards in time: the first group printed is the latest
+            fprintf(stderr, "[poz kernel trace] launch below: first CTA entry at %lld ns, last CTA exit at %lld ns (relative to the latest launch's exit)\n",
+                    (long long)first - (long long)origin, (long long)last_exit - (long long)origin);
+        }
         fprintf(stderr, "[poz kernel trace] tag %d M %d N %d K %d: %zu CTAs; mean (max) ns after first CTA start: entry %.0f (%llu) "
                         "setup+prologue %.0f (%llu) first tile ready %.0f (%llu) main loop done %.0f (%llu) epilogue done %.0f (%llu) exit %.0f (%llu)\n",
                 r0.tag, r0.m, r0.n, r0.k, cnt, mean[0] / cnt, mx[0], mean[1] / cnt, mx[1], mean[2] / cnt, mx[2], mean[3] / cnt, mx[3],
@@ -1506,6 +1536,8 @@ int poz_ctx_destroy(poz_ctx* c) {
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     for (auto e : c->dz_ready) if (e) cudaEventDestroy(e);
     if (c->side_stream) cudaStreamDestroy(c->side_stream);
+    if (c->sb_fork) cudaEventDestroy(c->sb_fork);
+    if (c->sb_done) cudaEventDestroy(c->sb_done);
     for (auto& p : c->bn_run) dev_free(p);
     for (auto& p : c->bn_stat) dev_free(p);
     for (auto& p : c->bn_sums) dev_free(p);

@@ -65,6 +65,7 @@ struct poz_ctx {
     std::vector<cudaEvent_t> dz_ready;     // recorded (compute stream) when layer l's dZ is complete
     cudaStream_t side_stream = nullptr;    // weight-gradient GEMMs of layers >= 1 run here, beside the backward-x chain
     bool fork_dw = true;
+    cudaEvent_t sb_fork = nullptr, sb_done = nullptr;   // step bookkeeping forked beside the forward GEMMs
 
     poz::DevState* st = nullptr;
     double* cost_ring = nullptr;  long long cost_cap = 0;

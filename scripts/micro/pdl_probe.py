@@ -21,9 +21,9 @@ with torch.cuda.stream(side):
     print("last error:", lib.poz_last_error())
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     e0.record(side)
-    for i in range(100):
+    for i in range(400):
         eng.train_step(xs[i % 4], ys[i % 4])
     e1.record(side)
     torch.cuda.synchronize()
-    print(os.environ.get("POZ_PDL"), os.environ.get("POZ_FORK_DW"), "us/step", e0.elapsed_time(e1) * 1000 / 100, "launches", lib.poz_launch_count())
+    print(os.environ.get("POZ_PDL"), os.environ.get("POZ_FORK_DW"), "us/step", e0.elapsed_time(e1) * 1000 / 400, "launches", lib.poz_launch_count())
 eng.close() if hasattr(eng, "close") else eng.__del__()

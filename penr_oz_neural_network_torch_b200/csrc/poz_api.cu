@@ -968,7 +968,8 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         const T* dz = static_cast<const T*>(c->dzbuf[l]);
         cudaStream_t ws = stream;
         if (fork && l >= 1) {
-            ws = c->side_stream;
+            static const bool two = !(getenv("POZ_FORK_DW_STREAMS") && atoi(getenv("POZ_FORK_DW_STREAMS")) == 1);
+            ws = (two && c->side_stream2 && (l & 1)) ? c->side_stream2 : c->side_stream;
             POZ_CUDA(cudaEventRecord(c->dz_ready[l], stream));
             POZ_CUDA(cudaStreamWaitEvent(ws, c->dz_ready[l], 0));
         }
@@ -1428,7 +1429,8 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
             set_error("cudaEventCreate failed");
             return fail();
         }
-    if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->side_stream2, cudaStreamNonBlocking) != cudaSuccess) {
         set_error("cudaStreamCreate failed");
         return fail();
     }
@@ -1536,6 +1538,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     for (auto e : c->dz_ready) if (e) cudaEventDestroy(e);
     if (c->side_stream) cudaStreamDestroy(c->side_stream);
+    if (c->side_stream2) cudaStreamDestroy(c->side_stream2);
     if (c->sb_fork) cudaEventDestroy(c->sb_fork);
     if (c->sb_done) cudaEventDestroy(c->sb_done);
     for (auto& p : c->bn_run) dev_free(p);

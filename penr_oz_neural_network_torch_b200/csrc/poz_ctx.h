@@ -64,6 +64,7 @@ struct poz_ctx {
     std::vector<cudaEvent_t> grad_ready;   // recorded when layer l's weight gradient is complete
     std::vector<cudaEvent_t> dz_ready;     // recorded (compute stream) when layer l's dZ is complete
     cudaStream_t side_stream = nullptr;    // weight-gradient GEMMs of layers >= 1 run here, beside the backward-x chain
+    cudaStream_t side_stream2 = nullptr;   // ... alternating with this one, so that two of them do not queue behind each other
     bool fork_dw = true;
     cudaEvent_t sb_fork = nullptr, sb_done = nullptr;   // step bookkeeping forked beside the forward GEMMs
 

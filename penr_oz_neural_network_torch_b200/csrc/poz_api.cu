@@ -1375,7 +1375,10 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
     c->da_rec.assign(n_linear, nullptr);
     c->bn_run.assign(n_linear, nullptr); c->bn_stat.assign(n_linear, nullptr); c->bn_sums.assign(n_linear, nullptr);
     c->ybuf.assign(n_linear, nullptr); c->dybuf.assign(n_linear, nullptr); c->dy_rec.assign(n_linear, nullptr);
-    c->max_splits = 16;
+    // batch splits of a weight-gradient GEMM (one gradient slab each): up to 64 for layers whose output is only a
+    // few tiles, bounded so that the slabs (splits x all parameters) stay under 1 GiB; POZ_MAX_SPLITS overrides
+    c->max_splits = (int)std::max<long long>(16, std::min<long long>(64, (1LL << 30) / std::max<long long>(1, c->p_total * (long long)c->esz)));
+    if (const char* e = getenv("POZ_MAX_SPLITS")) c->max_splits = std::max(1, atoi(e));
     if (const char* e = getenv("POZ_TC3_MIN_BATCH")) c->tc3_min_batch = atoll(e);
     if (const char* e = getenv("POZ_GRAPHS")) c->graphs_enabled = atoi(e) != 0;
     if (const char* e = getenv("POZ_FUSE_HEAD")) c->fuse_head = atoi(e) != 0;

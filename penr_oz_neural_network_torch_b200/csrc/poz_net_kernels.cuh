@@ -50,6 +50,36 @@ __global__ void emb_scatter_kernel(const T* __restrict__ dE, const int* __restri
     }
 }
 
+// The same for tables small enough for shared memory (vocab * E * sizeof(T) <= EMB_SMEM_BYTES): every block
+// accumulates its rows into a private copy of the table with shared-memory atomics and adds that copy to
+// dC once -- a character-level table (27 x 10) otherwise takes a million global atomics on 270 addresses.
+constexpr int EMB_SMEM_BYTES = 32768;
+template <typename T>
+__global__ void emb_scatter_small_kernel(const T* __restrict__ dE, const int* __restrict__ idx,
+                                         const int* __restrict__ row_idx, long long batch, int tokens, int E, int vocab,
+                                         T* __restrict__ dC) {
+    __shared__ __align__(16) unsigned char tab_raw[EMB_SMEM_BYTES];
+    T* tab = reinterpret_cast<T*>(tab_raw);
+    const int ne = vocab * E;
+    for (int i = threadIdx.x; i < ne; i += blockDim.x) tab[i] = T(0);
+    __syncthreads();
+    const long long total = batch * tokens * E;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / E;
+        const int e = (int)(i - r * E);
+        const long long b = r / tokens;
+        const int t = (int)(r - b * tokens);
+        const long long s = row_idx ? (long long)row_idx[b] : b;
+        int v = idx[s * tokens + t];
+        v = v < 0 ? 0 : (v >= vocab ? vocab - 1 : v);
+        atomicAdd(tab + v * E + e, dE[i]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < ne; i += blockDim.x)
+        if (tab[i] != T(0)) atomicAdd(dC + i, tab[i]);
+}
+
 constexpr int BN_ROW_SPLITS = 128;   // row splits of the batchnorm column reductions
 
 // Column reductions over the rows of a [R][N] matrix, two deterministic passes.  Pass 1: block

@@ -85,7 +85,7 @@ __device__ __forceinline__ void block_add_double(double v, double* dst) {
         int nw = (blockDim.x + 31) >> 5;
         double s = l < nw ? red[l] : 0.0;
         s = warp_sum(s);
-        if (l == 0 && dst) atomicAdd(dst, s);
+        if (l == 0 && dst && s != 0.0) atomicAdd(dst, s);   // (hundreds of blocks add to one address: skip the no-ops)
     }
     __syncthreads();
 }

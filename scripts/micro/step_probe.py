@@ -1,5 +1,8 @@
+"""Device time of the configs[1] train step (784-256-128-10, batch 1024, Adam + L2) on four L2-resident batches,
+for A/B runs of the library's environment switches on one box:  POZ_x=... python scripts/micro/step_probe.py
+With POZ_KERNEL_TRACE=1 the per-CTA kernel trace is printed when the engine is closed."""
 import os, sys, time, torch, numpy as np
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
 from penr_oz_neural_network_torch_b200 import _native
 algos = ["linear", "relu", "linear", "relu", "linear", "softmax"]
@@ -25,5 +28,5 @@ with torch.cuda.stream(side):
         eng.train_step(xs[i % 4], ys[i % 4])
     e1.record(side)
     torch.cuda.synchronize()
-    print(os.environ.get("POZ_PDL"), os.environ.get("POZ_FORK_DW"), "us/step", e0.elapsed_time(e1) * 1000 / 400, "launches", lib.poz_launch_count())
-eng.close() if hasattr(eng, "close") else eng.__del__()
+    print("us/step", e0.elapsed_time(e1) * 1000 / 400, "launches", lib.poz_launch_count())
+eng.close()

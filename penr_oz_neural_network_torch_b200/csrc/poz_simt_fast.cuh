@@ -229,9 +229,9 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
         cp_commit();
         const float* sa = smem + (t % STAGES) * STAGE_ELEMS;
         const float* sb = sa + A_ELEMS;
-#pragma unroll
-        for (int k4 = 0; k4 < BK; k4 += 4) {
-            float a[4][TM], b[4][TN];   // [kk][i]
+        // fragments of four k-values at a time, double-buffered in registers: the reads of block q+1 are
+        // issued before the FMAs of block q, so the shared-memory latency sits under 64 FMAs per thread
+        auto load_frag = [&](int k4, float (&a)[4][TM], float (&b)[4][TN]) {
             if (A_KC) {
 #pragma unroll
                 for (int i = 0; i < TM; ++i) {
@@ -258,6 +258,8 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
                     b[kk][0] = v.x; b[kk][1] = v.y; b[kk][2] = v.z; b[kk][3] = v.w;
                 }
             }
+        };
+        auto fma_frag = [&](const float (&a)[4][TM], const float (&b)[4][TN]) {
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
 #pragma unroll
@@ -269,7 +271,17 @@ gemm_f32_pipelined(Op A, Op B, long long M, int N, long long Kd, long long k_chu
                     for (int j = 0; j < TN; ++j) bsum[j] += b[kk][j];
                 }
             }
-        }
+        };
+        static_assert(BK == 16, "the fragment schedule below is written for four blocks of four k-values");
+        float a0[4][TM], b0[4][TN], a1[4][TM], b1[4][TN];
+        load_frag(0, a0, b0);
+        load_frag(4, a1, b1);
+        fma_frag(a0, b0);
+        load_frag(8, a0, b0);
+        fma_frag(a1, b1);
+        load_frag(12, a1, b1);
+        fma_frag(a0, b0);
+        fma_frag(a1, b1);
     }
     cp_wait<0>();
     pdl_trigger();   // the main loop is done: let the next launch's CTAs be scheduled behind this one's epilogue

@@ -531,10 +531,15 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
     const float* P = static_cast<const float*>(c->P);
     for (long long r0 = 0; r0 < batch; r0 += chunk) {
         const long long m = std::min(chunk, batch - r0);
+        // The first layer reads the fp32 rows directly and makes its planes in shared memory when it can
+        // (poz_tc3_x32_kernel.cuh); otherwise the chunk is split into planes in global memory first.
+        static const bool x32_allowed = !(getenv("POZ_TC3_X32") && atoi(getenv("POZ_TC3_X32")) == 0);
+        // (measured: 56 vs 67 us at 4096 rows in favour of the plane path, 189 vs 182 us at 32768 rows the other way)
+        const bool x32 = x32_allowed && m >= 16384 && tc3::gemm_forward_x32_ok(x + r0 * c->sizes[0], c->sizes[0], c->sizes[1]);
         tc3::PlaneMat cur;
         cur.ptr = static_cast<const __nv_bfloat16*>(c->tc_scr[0]);
         cur.rows = m; cur.cols = c->sizes[0]; cur.ld = round8(c->sizes[0]); cur.plane_stride = m * cur.ld;
-        {
+        if (!x32) {
             ProfScope ps(c, "split_x", stream);
             POZ_TRY(tc3::split_planes(x + r0 * c->sizes[0], nullptr, m, c->sizes[0], c->sizes[0],
                                       static_cast<__nv_bfloat16*>(c->tc_scr[0]), cur.ld, cur.plane_stride, stream));
@@ -560,7 +565,10 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
                 ep.ld_planes = nxt.ld; ep.plane_stride = nxt.plane_stride;
             }
             ProfScope ps(c, "tc3_fwd_l" + std::to_string(l), stream);
-            POZ_TRY(tc3::gemm_forward(cur, tc3_weight(c, l), m, N, K, ep, sms, stream));
+            if (l == 0 && x32)
+                POZ_TRY(tc3::gemm_forward_x32(x + r0 * c->sizes[0], c->sizes[0], tc3_weight(c, l), m, N, K, ep, sms, stream));
+            else
+                POZ_TRY(tc3::gemm_forward(cur, tc3_weight(c, l), m, N, K, ep, sms, stream));
             cur = nxt;
             flip = flip == 1 ? 2 : 1;
         }

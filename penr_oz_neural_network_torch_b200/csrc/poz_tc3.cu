@@ -3,6 +3,8 @@
 #include "../../include/pozmlp.h"
 #include "poz_tc3.h"
 #include "poz_tc3_kernel.cuh"
+#include "poz_tc3_x32_kernel.cuh"
+#include "poz_tc.h"
 
 #include <mutex>
 
@@ -87,6 +89,32 @@ int split_planes(const float* src, const int* row_idx, long long rows, int cols,
 int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms, cudaStream_t s) {
     return launch_bn<MAJOR_K, MAJOR_MN>(x, w, M, N, K, 1, ep, sms, s);
 }
+bool gemm_forward_x32_ok(const float* x, long long ld, int N) {
+    return N > 64 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (ld % 4) == 0;
+}
+
+int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms,
+                     cudaStream_t stream) {
+    constexpr int BN = 128;
+    using C = CfgX32<BN>;
+    if (!gemm_forward_x32_ok(x, ld, N)) POZ_FAIL("tc3 fp32-input forward: operand not eligible");
+    static bool configured = false;
+    auto kern = tc3_fwd_x32_kernel<BN>;
+    if (!configured) {
+        POZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        configured = true;
+    }
+    CUtensorMap mx, mb;
+    POZ_TRY(tc::make_map_f32(&mx, x, M, K, ld, BM));     // boxes of 32 floats x 128 rows, 128-byte swizzle
+    POZ_TRY(make_map3(&mb, w, 64, 64));
+    const long long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+    const int grid = (int)(tiles < sms ? tiles : sms);
+    kern<<<grid, X32_THREADS, C::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+    count_launch();
+    POZ_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int gemm_backward_data(const PlaneMat& dz, const PlaneMat& w, long long M, int K_in, int N_out, const Epi3& ep, int sms,
                        cudaStream_t s) {
     return launch_bn<MAJOR_K, MAJOR_K>(dz, w, M, K_in, N_out, 1, ep, sms, s);

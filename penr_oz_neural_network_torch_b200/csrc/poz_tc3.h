@@ -34,6 +34,11 @@ int split_planes(const float* src, const int* row_idx, long long rows, int cols,
                  long long ldp, long long plane_stride, cudaStream_t stream);
 // out[M][N] = epilogue(x[M][K] * w[K][N])
 int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms, cudaStream_t s);
+// the same with x given as the fp32 matrix itself (pitch ld floats, 16-byte aligned rows): its planes are made
+// inside the kernel and never written to global memory (csrc/poz_tc3_x32_kernel.cuh); N must be > 64
+int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms,
+                     cudaStream_t s);
+bool gemm_forward_x32_ok(const float* x, long long ld, int N);
 // out[M][K_in] = epilogue(dz[M][N_out] * w[K_in][N_out]^T)
 int gemm_backward_data(const PlaneMat& dz, const PlaneMat& w, long long M, int K_in, int N_out, const Epi3& ep, int sms,
                        cudaStream_t s);

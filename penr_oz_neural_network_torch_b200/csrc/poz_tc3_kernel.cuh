@@ -5,6 +5,92 @@
 namespace poz {
 namespace tc3 {
 
+// Epilogue of one 128 x BN tile for the 32 TMEM lanes of this warp's quarter and its column half: the two
+// accumulators are added, bias / activation (or activation gradient) applied, and the result written as fp32
+// and / or as the next GEMM's bf16 planes.
+template <int BN>
+__device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N, long long mb, int nb, int sp, bool empty_k,
+                                              uint32_t tmem_base, uint32_t ab, int quarter, int chalf, int lane) {
+    const long long m = mb * BM + quarter * 32 + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + ab * (2 * BN) + chalf * (BN / 2);
+#pragma unroll 1
+    for (int c = 0; c < BN / 2; c += 32) {
+        uint32_t v[32], w[32];
+        tc::tmem_ld32(taddr + c, v);
+        tc::tmem_ld32(taddr + BN + c, w);
+        tc::tmem_ld_wait();
+        const int n = nb * BN + chalf * (BN / 2) + c;
+        if (m < M && n < N) {
+            const bool full = (n + 32 <= N);
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = empty_k ? 0.f : __uint_as_float(v[j]) + __uint_as_float(w[j]);
+            if (ep.mode == EPI_BIAS_ACT) {
+                if (ep.bias) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (full || n + j < N) f[j] += __ldg(ep.bias + n + j);
+                }
+                if (ep.act == ACT_RELU) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+                } else if (ep.act != ACT_NONE && ep.act != ACT_SOFTMAX) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] = act_fwd<float>(ep.act, f[j]);
+                }
+            } else if (ep.mode == EPI_ACTGRAD) {
+                const float* aux = ep.aux + m * ep.ld_aux + n;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (full || n + j < N) f[j] *= act_bwd_from_out<float>(ep.act, __ldg(aux + j));
+            }
+            if (ep.out_f32) {
+                float* out = ep.out_f32 + (long long)sp * ep.slab + m * ep.ld_f32 + n;
+                if (full && ((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        *reinterpret_cast<float4*>(out + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (n + j < N) out[j] = f[j];
+                }
+            }
+            if (ep.out_planes) {
+                // pad columns N..ld_planes-1 of the planes must read as zero for the next GEMM
+                __nv_bfloat16* o = ep.out_planes + m * ep.ld_planes + n;
+                uint32_t ph[16], pm[16], pl[16];
+#pragma unroll
+                for (int j = 0; j < 32; j += 2) {
+                    __nv_bfloat16 h0, m0, l0, h1, m1, l1;
+                    split3((full || n + j < N) ? f[j] : 0.f, h0, m0, l0);
+                    split3((full || n + j + 1 < N) ? f[j + 1] : 0.f, h1, m1, l1);
+                    ph[j / 2] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+                    pm[j / 2] = (uint32_t)__bfloat16_as_ushort(m0) | ((uint32_t)__bfloat16_as_ushort(m1) << 16);
+                    pl[j / 2] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+                }
+                const bool fullp = (n + 32 <= ep.ld_planes);
+                if (fullp && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        reinterpret_cast<uint4*>(o)[q] = make_uint4(ph[4 * q], ph[4 * q + 1], ph[4 * q + 2], ph[4 * q + 3]);
+                        reinterpret_cast<uint4*>(o + ep.plane_stride)[q] = make_uint4(pm[4 * q], pm[4 * q + 1], pm[4 * q + 2], pm[4 * q + 3]);
+                        reinterpret_cast<uint4*>(o + 2 * ep.plane_stride)[q] = make_uint4(pl[4 * q], pl[4 * q + 1], pl[4 * q + 2], pl[4 * q + 3]);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2)
+                        if (n + j < ep.ld_planes) {   // ld_planes is even
+                            *reinterpret_cast<uint32_t*>(o + j) = ph[j / 2];
+                            *reinterpret_cast<uint32_t*>(o + ep.plane_stride + j) = pm[j / 2];
+                            *reinterpret_cast<uint32_t*>(o + 2 * ep.plane_stride + j) = pl[j / 2];
+                        }
+                }
+            }
+        }
+    }
+}
+
 template <int A_MAJOR, int B_MAJOR, int BN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc3_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
@@ -137,84 +223,7 @@ tc3_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
             tc::mbar_wait(&tmem_full_bar[ab], aphase);
             tc::tc_fence_after();
-            const long long m = mb * BM + quarter * 32 + lane;
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + ab * (2 * BN) + chalf * (BN / 2);
-#pragma unroll 1
-            for (int c = 0; c < BN / 2; c += 32) {
-                uint32_t v[32], w[32];
-                tc::tmem_ld32(taddr + c, v);
-                tc::tmem_ld32(taddr + BN + c, w);
-                tc::tmem_ld_wait();
-                const int n = nb * BN + chalf * (BN / 2) + c;
-                if (m < M && n < N) {
-                    const bool full = (n + 32 <= N);
-                    float f[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) f[j] = empty_k ? 0.f : __uint_as_float(v[j]) + __uint_as_float(w[j]);
-                    if (ep.mode == EPI_BIAS_ACT) {
-                        if (ep.bias) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (full || n + j < N) f[j] += __ldg(ep.bias + n + j);
-                        }
-                        if (ep.act == ACT_RELU) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-                        } else if (ep.act != ACT_NONE && ep.act != ACT_SOFTMAX) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) f[j] = act_fwd<float>(ep.act, f[j]);
-                        }
-                    } else if (ep.mode == EPI_ACTGRAD) {
-                        const float* aux = ep.aux + m * ep.ld_aux + n;
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (full || n + j < N) f[j] *= act_bwd_from_out<float>(ep.act, __ldg(aux + j));
-                    }
-                    if (ep.out_f32) {
-                        float* out = ep.out_f32 + (long long)sp * ep.slab + m * ep.ld_f32 + n;
-                        if (full && ((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 4)
-                                *reinterpret_cast<float4*>(out + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (n + j < N) out[j] = f[j];
-                        }
-                    }
-                    if (ep.out_planes) {
-                        // pad columns N..ld_planes-1 of the planes must read as zero for the next GEMM
-                        __nv_bfloat16* o = ep.out_planes + m * ep.ld_planes + n;
-                        uint32_t ph[16], pm[16], pl[16];
-#pragma unroll
-                        for (int j = 0; j < 32; j += 2) {
-                            __nv_bfloat16 h0, m0, l0, h1, m1, l1;
-                            split3((full || n + j < N) ? f[j] : 0.f, h0, m0, l0);
-                            split3((full || n + j + 1 < N) ? f[j + 1] : 0.f, h1, m1, l1);
-                            ph[j / 2] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-                            pm[j / 2] = (uint32_t)__bfloat16_as_ushort(m0) | ((uint32_t)__bfloat16_as_ushort(m1) << 16);
-                            pl[j / 2] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
-                        }
-                        const bool fullp = (n + 32 <= ep.ld_planes);
-                        if (fullp && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                reinterpret_cast<uint4*>(o)[q] = make_uint4(ph[4 * q], ph[4 * q + 1], ph[4 * q + 2], ph[4 * q + 3]);
-                                reinterpret_cast<uint4*>(o + ep.plane_stride)[q] = make_uint4(pm[4 * q], pm[4 * q + 1], pm[4 * q + 2], pm[4 * q + 3]);
-                                reinterpret_cast<uint4*>(o + 2 * ep.plane_stride)[q] = make_uint4(pl[4 * q], pl[4 * q + 1], pl[4 * q + 2], pl[4 * q + 3]);
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 2)
-                                if (n + j < ep.ld_planes) {   // ld_planes is even
-                                    *reinterpret_cast<uint32_t*>(o + j) = ph[j / 2];
-                                    *reinterpret_cast<uint32_t*>(o + ep.plane_stride + j) = pm[j / 2];
-                                    *reinterpret_cast<uint32_t*>(o + 2 * ep.plane_stride + j) = pl[j / 2];
-                                }
-                        }
-                    }
-                }
-            }
+            epilogue_tile<BN>(ep, M, N, mb, nb, sp, empty_k, tmem_base, ab, quarter, chalf, lane);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&tmem_empty_bar[ab]);

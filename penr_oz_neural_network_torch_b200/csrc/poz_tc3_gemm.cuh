@@ -63,6 +63,21 @@ __device__ __forceinline__ void split3(float x, __nv_bfloat16& h, __nv_bfloat16&
     l = __float2bfloat16_rn(r2);
 }
 
+// The same for two values at once, producing the packed bf16x2 words of the three planes (x0 in the low half).
+// One packed conversion per plane (cvt.rn.bf16x2.f32) instead of two scalar ones: the scalar conversion
+// issues on the quarter-rate conversion pipe and was what bound the in-kernel converters of
+// poz_tc3_x32_kernel.cuh (ncu: F2F.BF16.F32 at the top of their samples).  Same rounding, same bits.
+__device__ __forceinline__ void split3_pair(float x0, float x1, uint32_t& ph, uint32_t& pm, uint32_t& pl) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+    ph = *reinterpret_cast<uint32_t*>(&h);
+    const float r0 = x0 - __uint_as_float(ph << 16), r1 = x1 - __uint_as_float(ph & 0xffff0000u);
+    __nv_bfloat162 m = __floats2bfloat162_rn(r0, r1);
+    pm = *reinterpret_cast<uint32_t*>(&m);
+    const float s0 = r0 - __uint_as_float(pm << 16), s1 = r1 - __uint_as_float(pm & 0xffff0000u);
+    __nv_bfloat162 l = __floats2bfloat162_rn(s0, s1);
+    pl = *reinterpret_cast<uint32_t*>(&l);
+}
+
 // fp32 matrix [rows][cols] (pitch ld, optional row gather) -> planes [3][rows][ldp]; pad columns
 // cols..ldp-1 are zeroed.  One thread converts 8 consecutive elements: two 16-byte loads when the
 // source row allows it, one 16-byte store per plane.
@@ -88,14 +103,7 @@ __global__ void split_planes_kernel(const float* __restrict__ src, const int* __
         }
         uint32_t ph[4], pm[4], pl[4];
 #pragma unroll
-        for (int j = 0; j < 8; j += 2) {
-            __nv_bfloat16 h0, m0, l0, h1, m1, l1;
-            split3(x[j], h0, m0, l0);
-            split3(x[j + 1], h1, m1, l1);
-            ph[j / 2] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-            pm[j / 2] = (uint32_t)__bfloat16_as_ushort(m0) | ((uint32_t)__bfloat16_as_ushort(m1) << 16);
-            pl[j / 2] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
-        }
+        for (int j = 0; j < 8; j += 2) split3_pair(x[j], x[j + 1], ph[j / 2], pm[j / 2], pl[j / 2]);
         __nv_bfloat16* o = dst + r * ldp + c;
         *reinterpret_cast<uint4*>(o) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
         *reinterpret_cast<uint4*>(o + plane_stride) = make_uint4(pm[0], pm[1], pm[2], pm[3]);

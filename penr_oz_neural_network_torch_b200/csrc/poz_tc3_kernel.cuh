@@ -61,14 +61,9 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
                 __nv_bfloat16* o = ep.out_planes + m * ep.ld_planes + n;
                 uint32_t ph[16], pm[16], pl[16];
 #pragma unroll
-                for (int j = 0; j < 32; j += 2) {
-                    __nv_bfloat16 h0, m0, l0, h1, m1, l1;
-                    split3((full || n + j < N) ? f[j] : 0.f, h0, m0, l0);
-                    split3((full || n + j + 1 < N) ? f[j + 1] : 0.f, h1, m1, l1);
-                    ph[j / 2] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-                    pm[j / 2] = (uint32_t)__bfloat16_as_ushort(m0) | ((uint32_t)__bfloat16_as_ushort(m1) << 16);
-                    pl[j / 2] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
-                }
+                for (int j = 0; j < 32; j += 2)
+                    split3_pair((full || n + j < N) ? f[j] : 0.f, (full || n + j + 1 < N) ? f[j + 1] : 0.f, ph[j / 2], pm[j / 2],
+                                pl[j / 2]);
                 const bool fullp = (n + 32 <= ep.ld_planes);
                 if (fullp && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll

@@ -396,8 +396,17 @@ def run_c3(args, world, rank, local):
                 "peak_source": pk["source"], "top_kernel": top, "share_of_step": round(prof[top]["ms"] / tot, 3),
                 "fp32_fma": {"achieved_tflops": round(batch * C3_FLOPS_PER_SAMPLE / per / 1e12, 2),
                              "nominal_peak_tflops": 74.4,
-                             "frac": round(batch * C3_FLOPS_PER_SAMPLE / per / 74.4e12, 4)},
+                             "frac": round(batch * C3_FLOPS_PER_SAMPLE / per / 74.4e12, 4),
+                             "note": "fp32-grade FLOP rate against the FMA pipe; above 1 when the layers run on the tensor "
+                                     "cores (batch >= 2048)"},
                 "kernels_ms": {t: round(v["ms"] / 5, 4) for t, v in prof.items()}}
+        if any(t.startswith("tc3_") for t in prof):
+            # split-bf16 path: six bf16 MMAs per fp32-grade product
+            tf = 6 * batch * C3_FLOPS_PER_SAMPLE / per / 1e12
+            roof["tensor"] = {"achieved_tflops": round(tf, 1), "peak_tflops": pk["bf16_tflops_sustained"],
+                              "frac": round(tf / pk["bf16_tflops_sustained"], 4),
+                              "note": "bf16 MMA rate of the whole pass (6 plane products per fp32-grade product) against the "
+                                      "sustained cuBLAS bf16 figure"}
     eng.close()
     return dict(metric="infer samples/s", unit="samples/s", value=world * batch * args.steps / (ms * 1e-3),
                 ms_per_step=ms / args.steps,

@@ -534,8 +534,9 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
         // The first layer reads the fp32 rows directly and makes its planes in shared memory when it can
         // (poz_tc3_x32_kernel.cuh); otherwise the chunk is split into planes in global memory first.
         static const bool x32_allowed = !(getenv("POZ_TC3_X32") && atoi(getenv("POZ_TC3_X32")) == 0);
-        // (measured: 56 vs 67 us at 4096 rows in favour of the plane path, 189 vs 182 us at 32768 rows the other way)
-        const bool x32 = x32_allowed && m >= 16384 && tc3::gemm_forward_x32_ok(x + r0 * c->sizes[0], c->sizes[0], c->sizes[1]);
+        // (measured, plane path vs this one: 54 vs 58 us at 4096 rows, 67 vs 58 us at 8192, 110 vs 90 us at 16384)
+        static const long long x32_min_rows = getenv("POZ_TC3_X32_MIN_ROWS") ? atoll(getenv("POZ_TC3_X32_MIN_ROWS")) : 8192;
+        const bool x32 = x32_allowed && m >= x32_min_rows && tc3::gemm_forward_x32_ok(x + r0 * c->sizes[0], c->sizes[0], c->sizes[1]);
         tc3::PlaneMat cur;
         cur.ptr = static_cast<const __nv_bfloat16*>(c->tc_scr[0]);
         cur.rows = m; cur.cols = c->sizes[0]; cur.ld = round8(c->sizes[0]); cur.plane_stride = m * cur.ld;

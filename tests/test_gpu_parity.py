@@ -300,6 +300,32 @@ def test_few_row_inference_in_one_cluster_launch(sizes, algos, has_bias, batch):
     assert all(torch.equal(o, out) for o in outs)
 
 
+@pytest.mark.parametrize("sizes,batch", [([100, 200, 70, 5], 8200), ([784, 256, 128, 10], 8192 + 77), ([132, 136, 64], 9000)])
+def test_large_batch_inference_first_layer_from_fp32_rows(sizes, batch):
+    """From 8192 rows the first layer of the tcgen05 inference path reads the fp32 rows itself and builds
+    its bf16 planes in shared memory (tc3_fwd_x32_kernel): ragged row counts, a contraction that is not a
+    multiple of the 64-wide k-block and an output width that is not a multiple of the 128-wide tile, against
+    the oracle on every row."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    nl = len(sizes) - 1
+    algos = []
+    for l in range(nl):
+        algos += ["linear", "softmax" if l == nl - 1 else ("relu" if l % 2 == 0 else "tanh")]
+    params = det_params(sizes, True, 909)
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+    for l in range(nl):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    x = det_normalish((batch, sizes[0]), 910)
+    xd = torch.tensor(x, dtype=torch.float32, device="cuda:0")
+    eng.profile_begin()
+    out = eng.forward(xd)
+    tags = eng.profile_end()
+    assert "tc3_fwd_l0" in tags and "split_x" not in tags, tags      # no separate plane split of the input
+    ref = orc.forward(orc.parse_stack(algos), params, x)[0][-1]
+    close(out.cpu().numpy(), ref, "float32", "probs", rtol=1e-4)
+    assert (out.cpu().numpy().argmax(1) == ref.argmax(1)).mean() > 0.999
+
+
 def test_row_gather_equals_materialised_batch():
     """The in-kernel row gather (replacing neural_net_model.py:460-461,472) is bit-identical to
     training on the gathered copy."""

@@ -326,6 +326,32 @@ def test_large_batch_inference_first_layer_from_fp32_rows(sizes, batch):
     assert (out.cpu().numpy().argmax(1) == ref.argmax(1)).mean() > 0.999
 
 
+@pytest.mark.parametrize("batch", [1, 4, 300, 8192 + 77])
+def test_inference_writes_only_its_output_rows(batch):
+    """Guard bands around the caller's output buffer stay untouched on every inference path (few-row
+    cluster kernel, per-layer SIMT kernels, tcgen05 path with the fp32-input first layer)."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    sizes, algos = mnist_stack()
+    params = det_params(sizes, True, 5)
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+    for l in range(3):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    g = torch.Generator(device="cuda:0").manual_seed(batch)
+    guard = 4096
+    xbuf = torch.full((guard + batch * 784 + guard,), float("nan"), device="cuda:0", dtype=torch.float32)
+    x = xbuf[guard:guard + batch * 784].view(batch, 784)
+    x.copy_(torch.randn((batch, 784), generator=g, device="cuda:0"))
+    obuf = torch.full((guard + batch * 10 + guard,), -7.0, device="cuda:0", dtype=torch.float32)
+    out = obuf[guard:guard + batch * 10].view(batch, 10)
+    eng.forward(x, out)
+    torch.cuda.synchronize()
+    assert torch.all(obuf[:guard] == -7.0) and torch.all(obuf[guard + batch * 10:] == -7.0)
+    assert torch.isfinite(out).all()             # no NaN from the guard bands of the input leaked in
+    assert torch.allclose(out.sum(1), torch.ones(batch, device="cuda:0"), atol=1e-5)
+    ref = eng.forward(x.clone())
+    assert torch.equal(out, ref)
+
+
 def test_row_gather_equals_materialised_batch():
     """The in-kernel row gather (replacing neural_net_model.py:460-461,472) is bit-identical to
     training on the gathered copy."""

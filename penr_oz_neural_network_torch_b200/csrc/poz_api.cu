@@ -1489,44 +1489,43 @@ static void dump_kernel_trace() {
     if (!n) return;
     std::vector<fast::KernelTraceRec> h(n);
     cudaMemcpy(h.data(), buf, sizeof(fast::KernelTraceRec) * n, cudaMemcpyDeviceToHost);
-    // walk backwards: group consecutive records of one launch (same tag and shape)
-    size_t end = n;
-    int shown = 0;
-    while (end > 0 && shown < 12) {
-        size_t beg = end;
-        const fast::KernelTraceRec& r0 = h[end - 1];
-        while (beg > 0 && h[beg - 1].tag == r0.tag && h[beg - 1].m == r0.m && h[beg - 1].n == r0.n && h[beg - 1].k == r0.k) --beg;
-        unsigned long long t0 = ~0ull;
-        for (size_t i = beg; i < end; ++i) t0 = std::min(t0, h[i].t[0]);
-        // keep only the CTAs of the LAST launch of this run of records: those that started within 200 us of the latest
-        unsigned long long latest = 0;
-        for (size_t i = beg; i < end; ++i) latest = std::max(latest, h[i].t[0]);
-        double mean[6] = {0, 0, 0, 0, 0, 0};
-        unsigned long long mx[6] = {0, 0, 0, 0, 0, 0};
-        unsigned long long first = ~0ull;
-        size_t cnt = 0;
-        for (size_t i = beg; i < end; ++i)
-            if (latest - h[i].t[0] < 30000) first = std::min(first, h[i].t[0]);
-        for (size_t i = beg; i < end; ++i) {
-            if (latest - h[i].t[0] >= 30000) continue;
-            ++cnt;
-            for (int q = 0; q < 6; ++q) { mean[q] += (double)(h[i].t[q] - first); mx[q] = std::max(mx[q], h[i].t[q] - first); }
+    // the last ~400 us of records, in time order, grouped into launches: records of one kernel shape whose
+    // CTAs started within 40 us of the group's first one
+    unsigned long long t_end = 0;
+    for (auto& r : h) t_end = std::max(t_end, r.t[5]);
+    std::vector<const fast::KernelTraceRec*> recent;
+    for (auto& r : h)
+        if (t_end - r.t[0] < 400000ull) recent.push_back(&r);
+    std::sort(recent.begin(), recent.end(), [](const fast::KernelTraceRec* a, const fast::KernelTraceRec* b) { return a->t[0] < b->t[0]; });
+    struct Group { int tag, m, n, k; unsigned long long first, last_exit; double sum[6]; unsigned long long mx[6]; size_t cnt; };
+    std::vector<Group> groups;
+    for (const fast::KernelTraceRec* r : recent) {
+        Group* g = nullptr;
+        for (size_t i = groups.size(); i-- > 0;)
+            if (groups[i].tag == r->tag && groups[i].m == r->m && groups[i].n == r->n && groups[i].k == r->k) {
+                if (r->t[0] - groups[i].first < 40000ull) g = &groups[i];
+                break;
+            }
+        if (!g) {
+            Group ng{};
+            ng.tag = r->tag; ng.m = r->m; ng.n = r->n; ng.k = r->k; ng.first = r->t[0];
+            groups.push_back(ng);
+            g = &groups.back();
         }
-        {
-            unsigned long long last_exit = 0;
-            for (size_t i = beg; i < end; ++i)
-                if (latest - h[i].t[0] < 30000) last_exit = std::max(last_exit, h[i].t[5]);
-            static unsigned long long origin = 0;
-            if (!origin) origin = last_exit;       // the walk is backwards in time: the first group printed is the latest
-            fprintf(stderr, "[poz kernel trace] launch below: first CTA entry at %lld ns, last CTA exit at %lld ns (relative to the latest launch's exit)\n",
-                    (long long)first - (long long)origin, (long long)last_exit - (long long)origin);
+        ++g->cnt;
+        g->last_exit = std::max(g->last_exit, r->t[5]);
+        for (int q = 0; q < 6; ++q) {
+            g->sum[q] += (double)(r->t[q] - g->first);
+            g->mx[q] = std::max(g->mx[q], r->t[q] - g->first);
         }
+    }
+    for (const Group& g : groups) {
+        fprintf(stderr, "[poz kernel trace] launch below: first CTA entry at %lld ns, last CTA exit at %lld ns (relative to the latest launch's exit)\n",
+                (long long)g.first - (long long)t_end, (long long)g.last_exit - (long long)t_end);
         fprintf(stderr, "[poz kernel trace] tag %d M %d N %d K %d: %zu CTAs; mean (max) ns after first CTA start: entry %.0f (%llu) "
                         "setup+prologue %.0f (%llu) first tile ready %.0f (%llu) main loop done %.0f (%llu) epilogue done %.0f (%llu) exit %.0f (%llu)\n",
-                r0.tag, r0.m, r0.n, r0.k, cnt, mean[0] / cnt, mx[0], mean[1] / cnt, mx[1], mean[2] / cnt, mx[2], mean[3] / cnt, mx[3],
-                mean[4] / cnt, mx[4], mean[5] / cnt, mx[5]);
-        end = beg;
-        ++shown;
+                g.tag, g.m, g.n, g.k, g.cnt, g.sum[0] / g.cnt, g.mx[0], g.sum[1] / g.cnt, g.mx[1], g.sum[2] / g.cnt, g.mx[2],
+                g.sum[3] / g.cnt, g.mx[3], g.sum[4] / g.cnt, g.mx[4], g.sum[5] / g.cnt, g.mx[5]);
     }
     unsigned int zero = 0;
     cudaMemcpyToSymbol(fast::d_ktrace_n, &zero, sizeof(zero));

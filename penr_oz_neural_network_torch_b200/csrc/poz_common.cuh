@@ -128,6 +128,32 @@ template <typename T> __device__ __forceinline__ T act_bwd_from_out(int act, T a
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// Debugging aid (POZ_KERNEL_TRACE=1): the CTAs of the step's kernels record %globaltimer at up to six points;
+// poz_ctx_destroy prints, per launch, when the CTAs reached them.  The pointer is null in normal runs.  Internal
+// linkage: every translation unit has its own copy and only poz_api.cu's is ever set.
+namespace fast {
+struct KernelTraceRec { int tag, m, n, k; unsigned long long t[6]; };
+static __constant__ KernelTraceRec* d_ktrace = nullptr;   // constant bank: the null test at kernel entry costs no memory round trip
+static __device__ unsigned int d_ktrace_n = 0;
+constexpr unsigned int KTRACE_CAP = 1u << 20;
+__device__ __forceinline__ unsigned long long ktrace_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// one record per CTA (thread 0), or null
+__device__ __forceinline__ KernelTraceRec* ktrace_open(int tag, int m, int n, int k) {
+    if (!d_ktrace || threadIdx.x != 0) return nullptr;
+    const unsigned int slot = atomicAdd(&d_ktrace_n, 1u);
+    if (slot >= KTRACE_CAP) return nullptr;
+    KernelTraceRec* r = d_ktrace + slot;
+    r->tag = tag; r->m = m; r->n = n; r->k = k;
+    const unsigned long long now = ktrace_now();
+    for (int q = 0; q < 6; ++q) r->t[q] = now;
+    return r;
+}
+}  // namespace fast
+
 template <typename T> __device__ __forceinline__ T warp_sum(T v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

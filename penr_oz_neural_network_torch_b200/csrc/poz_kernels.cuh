@@ -325,6 +325,7 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
     pdl_trigger();
     pdl_wait();
     const int l = blockIdx.y;
+    fast::KernelTraceRec* ktr = fast::ktrace_open(128, (int)seg.n_elems[l], l, seg.splits[l]);   // trace tag 128: update
     const long long n = seg.n_elems[l];
     const long long nw = seg.w_elems[l];
     const int S = seg.splits[l];
@@ -335,6 +336,7 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
     const T step_size = T(st->step_size), bc2s = T(st->bc2_sqrt), eps = T(st->eps);
     const long long rec = st->cur_record;
     double l2acc = 0.0, sd = 0.0, sd2 = 0.0, sw = 0.0, sw2 = 0.0;
+    if (ktr) ktr->t[1] = fast::ktrace_now();                 // step scalars read
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
          i += (long long)gridDim.x * blockDim.x) {
         const long long idx = seg.off[l] + i;
@@ -366,6 +368,7 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
             sd += d; sd2 += d * d; sw += (double)wn; sw2 += (double)wn * (double)wn;
         }
     }
+    if (ktr) ktr->t[2] = fast::ktrace_now();                 // elements done
     if (st->l2 > 0.0) block_add_double(l2acc * st->l2 * st->l2_share, cost_slot(cost_base, cost_cap, st));
     if (rec >= 0 && seg.stat_slot[l] >= 0) {
         double* s = stats + (rec * seg.n_stat + (seg.stat_slot[l] < 0 ? 0 : seg.stat_slot[l])) * 4;
@@ -374,6 +377,7 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
         block_add_double(sw, s + 2);
         block_add_double(sw2, s + 3);
     }
+    if (ktr) { ktr->t[3] = fast::ktrace_now(); ktr->t[4] = ktr->t[3]; ktr->t[5] = ktr->t[3]; }
 }
 
 // Bias gradient db[n] = sum_b dz[b][n] for float32 dz (test_torch_backward.py:166), two
@@ -527,6 +531,7 @@ __device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char
     T* rows = bias + 32;                                     // [8 warps][K]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
     T* arow = rows + (long long)warp * a.K;
+    fast::KernelTraceRec* ktr = fast::ktrace_open(64, (int)a.M, a.N, a.K);    // trace tag 64: head
     // the first row of this warp and its label are requested before the weights, so that the three
     // global round trips overlap
     const long long m_first = (long long)part * wpb + warp;
@@ -539,6 +544,7 @@ __device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char
     for (int i = threadIdx.x; i < a.K * a.N; i += blockDim.x) W[(i / a.N) * Ns + (i % a.N)] = a.wb[i];
     for (int i = threadIdx.x; i < 32; i += blockDim.x) bias[i] = (a.has_bias && i < a.N) ? a.wb[(long long)a.K * a.N + i] : T(0);
     __syncthreads();
+    if (ktr) ktr->t[1] = fast::ktrace_now();                 // weights staged
     const T invb = T(a.inv_batch);
     double local = 0.0;
     for (long long m = m_first; m < a.M; m += (long long)parts * wpb) {
@@ -548,7 +554,8 @@ __device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char
             y_next = a.labels[a.row_idx ? (long long)a.row_idx[m] : m];
         }
         __syncwarp();
-        // logits: lane n < N owns logit n; four partial sums keep the dependent chain short
+        // logits: lane n < N owns logit n; four partial sums keep the dependent chain short.  (Splitting k over
+        // the 32 lanes with a warp reduction per output was measured slower: 2.5 against 1.4 us of this kernel.)
         T z = bias[lane];
         if (lane < a.N) {
             T z1 = T(0), z2 = T(0), z3 = T(0);
@@ -562,6 +569,7 @@ __device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char
             for (; k < a.K; ++k) z = fma(arow[k], W[k * Ns + lane], z);
             z = (z + z1) + (z2 + z3);
         }
+        if (ktr && m == m_first) ktr->t[2] = fast::ktrace_now();   // logits of the first row
         if (a.dz_last.enabled && lane < a.N) z = drop_keep(a.dz_last, a.st, m, lane, a.N) ? z * T(a.dz_last.scale) : T(0);
         if (a.z_rec && lane < a.N) a.z_rec[m * a.N + lane] = z;
         T zm = lane < a.N ? z : T(-INFINITY);
@@ -577,14 +585,23 @@ __device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char
         if (lane < a.N) a.dz_pre[m * a.N + lane] = g;
         const T zy = __shfl_sync(0xffffffffu, z, (y >= 0 && y < a.N) ? y : 0);
         if (lane == 0 && y >= 0 && y < a.N) local += (double)(mx + log(s) - zy);
-        // backward-x: lanes take k = lane, lane + 32, ...; g of lane n is broadcast with shuffles
-        for (int k0 = 0; k0 < a.K; k0 += 32) {
-            const int k = k0 + lane;
-            T d = T(0);
+        if (ktr && m == m_first) ktr->t[3] = fast::ktrace_now();   // softmax / loss / dZ of the first row
+        // backward-x: lanes take k = lane, lane + 32, ...; g of lane n is broadcast with shuffles, one
+        // shuffle per n for four k-chunks at a time (each d[j] still adds its terms in the order n = 0, 1, ...)
+        for (int kg = 0; kg < a.K; kg += 128) {
+            T dd[4] = {T(0), T(0), T(0), T(0)};
             for (int n = 0; n < a.N; ++n) {
                 const T gn = __shfl_sync(0xffffffffu, g, n);
-                if (k < a.K) d = fma(gn, W[k * Ns + n], d);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int kk = kg + 32 * j + lane;
+                    if (kk < a.K) dd[j] = fma(gn, W[kk * Ns + n], dd[j]);
+                }
             }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int k = kg + 32 * j + lane;
+            const T d = dd[j];
             if (k < a.K) {
                 if (a.da_rec) a.da_rec[m * a.K + k] = d;
                 T ga = d, av = arow[k];
@@ -597,10 +614,13 @@ __device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char
                 if (a.dz_prev.enabled) gz = drop_keep(a.dz_prev, a.st, m, k, a.K) ? gz * T(a.dz_prev.scale) : T(0);
                 a.dprev_pre[m * a.K + k] = gz;
             }
+          }
         }
         __syncwarp();
     }
+    if (ktr) ktr->t[4] = fast::ktrace_now();                 // rows done
     if (a.cost_base) block_add_double(local * a.inv_batch, cost_slot(a.cost_base, a.cost_cap, a.st));
+    if (ktr) ktr->t[5] = fast::ktrace_now();
 }
 
 template <typename T> __global__ void __launch_bounds__(256) head_ce_kernel(HeadArgs<T> a) {

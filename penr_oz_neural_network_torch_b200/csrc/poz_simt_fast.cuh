@@ -19,18 +19,6 @@ constexpr int BK = 16;
 constexpr int STAGES = 4;
 constexpr int TM = 4, TN = 4;
 
-// Debugging aid (POZ_KERNEL_TRACE=1): every CTA of the pipelined GEMMs records %globaltimer at five
-// points; poz_ctx_destroy prints, per kernel shape, when the CTAs reached them.  Null in normal runs.
-struct KernelTraceRec { int tag, m, n, k; unsigned long long t[6]; };
-__constant__ KernelTraceRec* d_ktrace = nullptr;   // constant bank: the null test at every kernel entry costs no memory round trip
-__device__ unsigned int d_ktrace_n = 0;
-constexpr unsigned int KTRACE_CAP = 1u << 20;
-__device__ __forceinline__ unsigned long long ktrace_now() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-
 struct Op {
     const float* ptr;
     long long ld;

@@ -63,6 +63,33 @@ int main() {
             cudaGraphExecDestroy(ge); cudaGraphDestroy(g);
         }
     }
+    // the same chain launched as thread-block clusters of 4 (the split-K GEMMs of the step are cluster launches)
+    for (int chain : {9, 18}) {
+        cudaGraph_t g; cudaGraphExec_t ge;
+        cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
+        for (int i = 0; i < chain; ++i) {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(4 * sms); cfg.blockDim = dim3(256); cfg.stream = s;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = 4; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            cudaLaunchKernelEx(&cfg, k_touch, p, n);
+        }
+        cudaStreamEndCapture(s, &g);
+        cudaGraphInstantiate(&ge, g, 0);
+        for (int i = 0; i < 20; ++i) cudaGraphLaunch(ge, s);
+        cudaStreamSynchronize(s);
+        const int reps = 200;
+        cudaEventRecord(e0, s);
+        for (int i = 0; i < reps; ++i) cudaGraphLaunch(ge, s);
+        cudaEventRecord(e1, s);
+        cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        printf("graph of %2d dependent CLUSTER(4) kernels, %4d blocks each: %7.2f us per graph, %5.2f us per kernel\n", chain, 4 * sms,
+               ms * 1000 / reps, ms * 1000 / reps / chain);
+        cudaGraphExecDestroy(ge); cudaGraphDestroy(g);
+    }
     for (int rounds : {1, 9, 33}) {
         int nn = n;
         void* args[] = {&p, &nn, &rounds, &bar};

@@ -7,6 +7,7 @@
 #include "poz_simt_fast.cuh"
 #include "poz_narrow_step.cuh"
 #include "poz_infer_small.cuh"
+#include "poz_fwd_head.cuh"
 #include "poz_tf32x3_gemm.cuh"
 #include "poz_tf32x3_tma_gemm.cuh"
 #include "poz_tc.h"
@@ -873,10 +874,30 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     const size_t head_smem = ((size_t)head_K * (head_N | 1) + 32 + 8 * (size_t)head_K) * sizeof(T);
     const bool fuse_head = c->fuse_head && nl >= 2 && c->loss == POZ_LOSS_CE && head_N <= 32 && head_smem <= 96 * 1024;
 
+    // float32: the last hidden unit's forward rides in the same launch as the head (poz_fwd_head.cuh)
+    bool fwd_head = false;
+    size_t fh_smem = 0;
+    if constexpr (std::is_same<T, float>::value) {
+        // opt-in (POZ_FUSE_FWD_HEAD=1): measured slower than the two launches it replaces (83 against 76 us per
+        // C2 step: its 128 blocks each stream all of W1 at ~9 GB/s)
+        static const bool allowed = getenv("POZ_FUSE_FWD_HEAD") && atoi(getenv("POZ_FUSE_FWD_HEAD")) != 0;
+        const int p = nl - 2;
+        if (allowed && fuse_head && !(tc0 && p == 0)) {
+            const int K1 = c->sizes[p], N1 = c->sizes[p + 1];
+            size_t fl = (size_t)N1 * (head_N | 1) + 32 + (size_t)FH_WARPS * N1;
+            fl = (fl + 3) & ~(size_t)3;
+            fl += (size_t)FH_WARPS * (((K1 + FH_KT - 1) / FH_KT) * FH_KT + 1);
+            fl = (fl + 3) & ~(size_t)3;
+            fl += (size_t)FH_STAGES * FH_KT * N1;
+            fh_smem = fl * sizeof(float);
+            fwd_head = N1 % 32 == 0 && N1 <= 256 && c->acts[p] != ACT_SOFTMAX && fh_smem <= 96 * 1024;
+        }
+    }
+
     // forward, keeping what the backward needs (and, for diagnostics, every entry's output)
     const T* cur = x;
     const int* cur_idx = row_idx;
-    for (int l = 0; l < (fuse_head ? nl - 1 : nl); ++l) {
+    for (int l = 0; l < (fuse_head ? (fwd_head ? nl - 2 : nl - 1) : nl); ++l) {
         T* zb = static_cast<T*>(c->zbuf[l]);
         T* ab = static_cast<T*>(c->abuf[l]);
         const int act = c->acts[l];
@@ -939,9 +960,33 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             POZ_CUDA(cudaFuncSetAttribute(head_ce_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
             configured[sizeof(T) == 8] = true;
         }
-        ProfScope ps(c, "head", stream);
         const int blocks = (int)std::max<long long>(1, std::min<long long>((batch + 7) / 8, 2LL * num_sms(c->device)));
-        POZ_TRY(launch_pdl(head_ce_kernel<T>, dim3(blocks), dim3(256), head_smem, stream, h));
+        bool launched = false;
+        if constexpr (std::is_same<T, float>::value) {
+            if (fwd_head) {
+                static bool fh_configured = false;
+                if (!fh_configured) {
+                    POZ_CUDA(cudaFuncSetAttribute(fwd_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+                    fh_configured = true;
+                }
+                FwdHeadArgs fa{};
+                fa.h = h;
+                fa.a_in = cur; fa.in_row_idx = cur_idx;
+                fa.w1b = static_cast<const float*>(c->P) + c->off[p];
+                fa.a1_out = static_cast<float*>(c->abuf[p]);
+                fa.z1_rec = (diag && c->acts[p] != ACT_NONE) ? static_cast<float*>(c->zbuf[p]) : nullptr;
+                fa.K1 = c->sizes[p]; fa.N1 = c->sizes[p + 1]; fa.act1 = c->acts[p];
+                fa.dz1 = make_drop(c, p, 0, masks);
+                fa.da1 = make_drop(c, p, 1, masks);
+                ProfScope ps(c, "fwd_head", stream);
+                POZ_TRY(launch_pdl(fwd_head_kernel, dim3(blocks), dim3(FH_WARPS * 32), fh_smem, stream, fa));
+                launched = true;
+            }
+        }
+        if (!launched) {
+            ProfScope ps(c, "head", stream);
+            POZ_TRY(launch_pdl(head_ce_kernel<T>, dim3(blocks), dim3(256), head_smem, stream, h));
+        }
     } else {
         LossArgs<T> a{};
         a.z = cur; a.target = target; a.row_idx = row_idx;

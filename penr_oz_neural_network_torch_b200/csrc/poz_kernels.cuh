@@ -523,6 +523,76 @@ template <typename T> struct HeadArgs {
     const DevState* st;
 };
 
+// One row of the head for one warp: arow (shared memory, this warp's own K values, already the recorded output of
+// the previous unit), W / bias staged in shared memory; returns the row's contribution to the cost sum in `local`.
+template <typename T>
+__device__ __forceinline__ void head_ce_row(const HeadArgs<T>& a, const T* W, int Ns, const T* bias, const T* arow,
+                                            long long m, int y, int lane, T invb, double& local,
+                                            fast::KernelTraceRec* ktr, bool stamp) {
+    // logits: lane n < N owns logit n; four partial sums keep the dependent chain short.  (Splitting k over
+    // the 32 lanes with a warp reduction per output was measured slower: 2.5 against 1.4 us of this kernel.)
+    T z = bias[lane];
+    if (lane < a.N) {
+        T z1 = T(0), z2 = T(0), z3 = T(0);
+        int k = 0;
+        for (; k + 4 <= a.K; k += 4) {
+            z  = fma(arow[k],     W[k * Ns + lane], z);
+            z1 = fma(arow[k + 1], W[(k + 1) * Ns + lane], z1);
+            z2 = fma(arow[k + 2], W[(k + 2) * Ns + lane], z2);
+            z3 = fma(arow[k + 3], W[(k + 3) * Ns + lane], z3);
+        }
+        for (; k < a.K; ++k) z = fma(arow[k], W[k * Ns + lane], z);
+        z = (z + z1) + (z2 + z3);
+    }
+    if (ktr && stamp) ktr->t[2] = fast::ktrace_now();   // logits of the first row
+    if (a.dz_last.enabled && lane < a.N) z = drop_keep(a.dz_last, a.st, m, lane, a.N) ? z * T(a.dz_last.scale) : T(0);
+    if (a.z_rec && lane < a.N) a.z_rec[m * a.N + lane] = z;
+    T zm = lane < a.N ? z : T(-INFINITY);
+    const T mx = warp_max(zm);
+    const T e = lane < a.N ? exp(z - mx) : T(0);
+    const T s = warp_sum(e);
+    const T p = e / s;
+    if (a.probs && lane < a.N) a.probs[m * a.N + lane] = p;
+    
+    T g = lane < a.N ? (p - (lane == y ? T(1) : T(0))) * invb : T(0);
+    if (a.dz_rec && lane < a.N) a.dz_rec[m * a.N + lane] = g;
+    if (a.dz_last.enabled && lane < a.N) g = drop_keep(a.dz_last, a.st, m, lane, a.N) ? g * T(a.dz_last.scale) : T(0);
+    if (lane < a.N) a.dz_pre[m * a.N + lane] = g;
+    const T zy = __shfl_sync(0xffffffffu, z, (y >= 0 && y < a.N) ? y : 0);
+    if (lane == 0 && y >= 0 && y < a.N) local += (double)(mx + log(s) - zy);
+    if (ktr && stamp) ktr->t[3] = fast::ktrace_now();   // softmax / loss / dZ of the first row
+    // backward-x: lanes take k = lane, lane + 32, ...; g of lane n is broadcast with shuffles, one
+    // shuffle per n for four k-chunks at a time (each d[j] still adds its terms in the order n = 0, 1, ...)
+    for (int kg = 0; kg < a.K; kg += 128) {
+        T dd[4] = {T(0), T(0), T(0), T(0)};
+        for (int n = 0; n < a.N; ++n) {
+            const T gn = __shfl_sync(0xffffffffu, g, n);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int kk = kg + 32 * j + lane;
+                if (kk < a.K) dd[j] = fma(gn, W[kk * Ns + n], dd[j]);
+            }
+        }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = kg + 32 * j + lane;
+        const T d = dd[j];
+        if (k < a.K) {
+            if (a.da_rec) a.da_rec[m * a.K + k] = d;
+            T ga = d, av = arow[k];
+            if (a.da_prev.enabled) {
+                ga = drop_keep(a.da_prev, a.st, m, k, a.K) ? d * T(a.da_prev.scale) : T(0);
+                av = av * T(a.da_prev.keep_prob);
+            }
+            T gz = ga * act_bwd_from_out<T>(a.act_prev, av);
+            if (a.dzprev_rec) a.dzprev_rec[m * a.K + k] = gz;
+            if (a.dz_prev.enabled) gz = drop_keep(a.dz_prev, a.st, m, k, a.K) ? gz * T(a.dz_prev.scale) : T(0);
+            a.dprev_pre[m * a.K + k] = gz;
+        }
+      }
+    }
+}
+
 template <typename T>
 __device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char* head_smem, int part, int parts) {
     T* W = reinterpret_cast<T*>(head_smem);
@@ -554,68 +624,7 @@ __device__ __forceinline__ void head_ce_body(const HeadArgs<T>& a, unsigned char
             y_next = a.labels[a.row_idx ? (long long)a.row_idx[m] : m];
         }
         __syncwarp();
-        // logits: lane n < N owns logit n; four partial sums keep the dependent chain short.  (Splitting k over
-        // the 32 lanes with a warp reduction per output was measured slower: 2.5 against 1.4 us of this kernel.)
-        T z = bias[lane];
-        if (lane < a.N) {
-            T z1 = T(0), z2 = T(0), z3 = T(0);
-            int k = 0;
-            for (; k + 4 <= a.K; k += 4) {
-                z  = fma(arow[k],     W[k * Ns + lane], z);
-                z1 = fma(arow[k + 1], W[(k + 1) * Ns + lane], z1);
-                z2 = fma(arow[k + 2], W[(k + 2) * Ns + lane], z2);
-                z3 = fma(arow[k + 3], W[(k + 3) * Ns + lane], z3);
-            }
-            for (; k < a.K; ++k) z = fma(arow[k], W[k * Ns + lane], z);
-            z = (z + z1) + (z2 + z3);
-        }
-        if (ktr && m == m_first) ktr->t[2] = fast::ktrace_now();   // logits of the first row
-        if (a.dz_last.enabled && lane < a.N) z = drop_keep(a.dz_last, a.st, m, lane, a.N) ? z * T(a.dz_last.scale) : T(0);
-        if (a.z_rec && lane < a.N) a.z_rec[m * a.N + lane] = z;
-        T zm = lane < a.N ? z : T(-INFINITY);
-        const T mx = warp_max(zm);
-        const T e = lane < a.N ? exp(z - mx) : T(0);
-        const T s = warp_sum(e);
-        const T p = e / s;
-        if (a.probs && lane < a.N) a.probs[m * a.N + lane] = p;
-        const int y = y_next;
-        T g = lane < a.N ? (p - (lane == y ? T(1) : T(0))) * invb : T(0);
-        if (a.dz_rec && lane < a.N) a.dz_rec[m * a.N + lane] = g;
-        if (a.dz_last.enabled && lane < a.N) g = drop_keep(a.dz_last, a.st, m, lane, a.N) ? g * T(a.dz_last.scale) : T(0);
-        if (lane < a.N) a.dz_pre[m * a.N + lane] = g;
-        const T zy = __shfl_sync(0xffffffffu, z, (y >= 0 && y < a.N) ? y : 0);
-        if (lane == 0 && y >= 0 && y < a.N) local += (double)(mx + log(s) - zy);
-        if (ktr && m == m_first) ktr->t[3] = fast::ktrace_now();   // softmax / loss / dZ of the first row
-        // backward-x: lanes take k = lane, lane + 32, ...; g of lane n is broadcast with shuffles, one
-        // shuffle per n for four k-chunks at a time (each d[j] still adds its terms in the order n = 0, 1, ...)
-        for (int kg = 0; kg < a.K; kg += 128) {
-            T dd[4] = {T(0), T(0), T(0), T(0)};
-            for (int n = 0; n < a.N; ++n) {
-                const T gn = __shfl_sync(0xffffffffu, g, n);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int kk = kg + 32 * j + lane;
-                    if (kk < a.K) dd[j] = fma(gn, W[kk * Ns + n], dd[j]);
-                }
-            }
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int k = kg + 32 * j + lane;
-            const T d = dd[j];
-            if (k < a.K) {
-                if (a.da_rec) a.da_rec[m * a.K + k] = d;
-                T ga = d, av = arow[k];
-                if (a.da_prev.enabled) {
-                    ga = drop_keep(a.da_prev, a.st, m, k, a.K) ? d * T(a.da_prev.scale) : T(0);
-                    av = av * T(a.da_prev.keep_prob);
-                }
-                T gz = ga * act_bwd_from_out<T>(a.act_prev, av);
-                if (a.dzprev_rec) a.dzprev_rec[m * a.K + k] = gz;
-                if (a.dz_prev.enabled) gz = drop_keep(a.dz_prev, a.st, m, k, a.K) ? gz * T(a.dz_prev.scale) : T(0);
-                a.dprev_pre[m * a.K + k] = gz;
-            }
-          }
-        }
+        head_ce_row<T>(a, W, Ns, bias, arow, m, y_next, lane, invb, local, ktr, m == m_first);
         __syncwarp();
     }
     if (ktr) ktr->t[4] = fast::ktrace_now();                 // rows done

@@ -68,7 +68,7 @@ def run_child(env_extra):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("switch", ["POZ_FUSED_STEP", "POZ_TF32X3", "POZ_TMA_GEMM", "POZ_PDL"])
+@pytest.mark.parametrize("switch", ["POZ_FUSED_STEP", "POZ_TF32X3", "POZ_TMA_GEMM", "POZ_PDL", "POZ_FUSE_FWD_HEAD"])
 def test_optin_step_variants_match_the_oracle(switch):
     run_child({switch: "1"})
 

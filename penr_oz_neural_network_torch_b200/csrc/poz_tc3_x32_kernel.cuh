@@ -161,8 +161,10 @@ tc3_fwd_x32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         }
     } else if (warp >= NUM_EPI_WARPS + 2) {
         // ================= converters: two threads per tile row, 16 of a half-block's 32 k-values each =================
-        const int ct = (warp - (NUM_EPI_WARPS + 2)) * 32 + lane;       // 0 .. 255
-        const int r = ct >> 1, part = ct & 1;
+        // a warp takes 16 rows; lanes 0-15 the first 16 k-values of each, lanes 16-31 the second: every group of eight
+        // lanes is eight consecutive rows at one chunk position, so the swizzle spreads its 16-byte loads AND stores
+        // over all banks (with (row, part) = (lane / 2, lane % 2) the plane stores were two-way conflicted)
+        const int r = (warp - (NUM_EPI_WARPS + 2)) * 16 + (lane & 15), part = lane >> 4;
         const uint32_t sw = (uint32_t)(r & 7);                          // the 128-byte swizzle XORs the 16-byte chunk index with row % 8
         uint32_t slot = 0, rphase = 0, kbc = 0;
         uint8_t* dst = smem + r * 128;

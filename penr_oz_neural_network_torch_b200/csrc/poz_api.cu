@@ -548,6 +548,12 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
         }
         int flip = 1;
         float* z_last = nullptr;
+        // A narrow last unit (<= 16 outputs) behind a 65..128-wide one rides in that unit's epilogue: the tile holds
+        // whole rows, so the epilogue warps apply the last Linear in fp32, then its activation / softmax, and the
+        // last hidden activation never leaves the SM (POZ_TC3_FUSE_HEAD=0: separate kernels).
+        static const bool head_allowed = !(getenv("POZ_TC3_FUSE_HEAD") && atoi(getenv("POZ_TC3_FUSE_HEAD")) == 0);
+        const bool fuse_head = head_allowed && !cost_host && nl >= 2 && !(nl == 2 && x32) &&
+                               c->acts[nl - 2] != ACT_SOFTMAX && tc3::gemm_forward_head_ok(c->sizes[nl - 1], n_out);
         for (int l = 0; l < nl; ++l) {
             const int K = c->sizes[l], N = c->sizes[l + 1];
             const bool last = l == nl - 1;
@@ -556,6 +562,16 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
             ep.act = c->acts[l];
             ep.bias = c->has_bias ? P + c->off[l] + (long long)K * N : nullptr;
             tc3::PlaneMat nxt{};
+            if (fuse_head && l == nl - 2) {
+                ep.head_w = P + c->off[nl - 1];
+                ep.head_b = c->has_bias ? P + c->off[nl - 1] + (long long)N * n_out : nullptr;
+                ep.head_out = out + r0 * n_out;
+                ep.head_n = n_out;
+                ep.head_act = c->acts[nl - 1];
+                ProfScope ps(c, "tc3_fwd_l" + std::to_string(l) + "_head", stream);
+                POZ_TRY(tc3::gemm_forward(cur, tc3_weight(c, l), m, N, K, ep, sms, stream));
+                break;
+            }
             if (last) {
                 ep.out_f32 = softmax_last ? c->tc_logits : out + r0 * n_out;
                 ep.ld_f32 = N;
@@ -587,7 +603,7 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
                 a.inv_count = 1.0 / ((double)batch * n_out);
             }
             POZ_TRY(run_loss<float>(c, a, stream));
-        } else if (softmax_last) {
+        } else if (softmax_last && !fuse_head) {
             POZ_TRY(run_softmax<float>(c, z_last, out + r0 * n_out, m, n_out, stream));
         }
     }

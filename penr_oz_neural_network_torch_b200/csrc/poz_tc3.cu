@@ -50,10 +50,16 @@ static int launch(const PlaneMat& a, const PlaneMat& b, long long M, int N, long
     using C = Cfg<BN>;
     static bool configured = false;
     auto kern = tc3_gemm_kernel<A_MAJOR, B_MAJOR, BN>;
+    constexpr bool head_capable = (A_MAJOR == MAJOR_K && B_MAJOR == MAJOR_MN && BN == 128);
+    constexpr int smem_max = C::SMEM_BYTES + (head_capable ? HEAD_SMEM_BYTES : 0);
+    static_assert(smem_max <= 227 * 1024, "shared memory of the tc3 GEMM (with the fused head's buffers)");
+    if (ep.head_w && (!head_capable || N > BN || splits != 1 || ep.head_n < 1 || ep.head_n > HEAD_MAX_N || !ep.head_out))
+        POZ_FAIL("tc3 forward: fused head not available for this shape");
     if (!configured) {
-        POZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        POZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
         configured = true;
     }
+    const int smem_bytes = C::SMEM_BYTES + (ep.head_w ? HEAD_SMEM_BYTES : 0);
     CUtensorMap ma, mb;
     POZ_TRY(make_map3(&ma, a, 64, A_MAJOR == MAJOR_K ? BM : 64));
     POZ_TRY(make_map3(&mb, b, 64, B_MAJOR == MAJOR_K ? BN : 64));
@@ -61,7 +67,7 @@ static int launch(const PlaneMat& a, const PlaneMat& b, long long M, int N, long
     k_per = ((k_per + BK - 1) / BK) * BK;
     const long long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * splits;
     const int grid = (int)(tiles < sms ? tiles : sms);
-    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ma, mb, M, N, K, splits, k_per, ep);
+    kern<<<grid, NUM_THREADS, smem_bytes, stream>>>(ma, mb, M, N, K, splits, k_per, ep);
     count_launch();
     POZ_CUDA(cudaGetLastError());
     return 0;
@@ -71,7 +77,7 @@ template <int A_MAJOR, int B_MAJOR>
 static int launch_bn(const PlaneMat& a, const PlaneMat& b, long long M, int N, long long K, int splits,
                      const Epi3& ep, int sms, cudaStream_t stream) {
     const long long tiles128 = ((M + BM - 1) / BM) * ((N + 127) / 128) * splits;
-    if (N <= 64 || tiles128 * 2 < sms) return launch<A_MAJOR, B_MAJOR, 64>(a, b, M, N, K, splits, ep, sms, stream);
+    if (!ep.head_w && (N <= 64 || tiles128 * 2 < sms)) return launch<A_MAJOR, B_MAJOR, 64>(a, b, M, N, K, splits, ep, sms, stream);
     return launch<A_MAJOR, B_MAJOR, 128>(a, b, M, N, K, splits, ep, sms, stream);
 }
 
@@ -89,6 +95,7 @@ int split_planes(const float* src, const int* row_idx, long long rows, int cols,
 int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms, cudaStream_t s) {
     return launch_bn<MAJOR_K, MAJOR_MN>(x, w, M, N, K, 1, ep, sms, s);
 }
+bool gemm_forward_head_ok(int N, int head_n) { return N > 64 && N <= 128 && head_n >= 1 && head_n <= HEAD_MAX_N; }
 bool gemm_forward_x32_ok(const float* x, long long ld, int N) {
     return N > 64 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (ld % 4) == 0;
 }

@@ -27,13 +27,24 @@ struct Epi3 {
     const float* aux;             // EPI_ACTGRAD: recorded activation of the previous unit [M][ld_aux]
     long long ld_aux;
     int mode, act;
+    // Optional fused head (forward, EPI_BIAS_ACT, one 128-wide tile holds whole rows: 64 < N <= 128): the NEXT Linear
+    // unit, at most HEAD_MAX_N wide, applied to the tile's activated rows in fp32 by the epilogue warps:
+    // head_out[M][head_n] = head_act(row * head_w[N][head_n] + head_b).  out_f32 / out_planes may then be null.
+    const float* head_w;          // nullable
+    const float* head_b;          // nullable
+    float* head_out;
+    int head_n, head_act;
 };
+constexpr int HEAD_MAX_N = 16;
+constexpr int HEAD_SMEM_BYTES = (128 * HEAD_MAX_N + 2 * 128 * HEAD_MAX_N) * 4;   // staged weights + two partial-sum buffers
 
 // row_idx (nullable) gathers source rows: plane row r = source row row_idx[r]
 int split_planes(const float* src, const int* row_idx, long long rows, int cols, long long ld, __nv_bfloat16* dst,
                  long long ldp, long long plane_stride, cudaStream_t stream);
 // out[M][N] = epilogue(x[M][K] * w[K][N])
 int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms, cudaStream_t s);
+// whether gemm_forward takes ep.head_* for this width
+bool gemm_forward_head_ok(int N, int head_n);
 // the same with x given as the fp32 matrix itself (pitch ld floats, 16-byte aligned rows): its planes are made
 // inside the kernel and never written to global memory (csrc/poz_tc3_x32_kernel.cuh); N must be > 64
 int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms,

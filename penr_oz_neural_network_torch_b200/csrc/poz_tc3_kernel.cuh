@@ -8,10 +8,16 @@ namespace tc3 {
 // Epilogue of one 128 x BN tile for the 32 TMEM lanes of this warp's quarter and its column half: the two
 // accumulators are added, bias / activation (or activation gradient) applied, and the result written as fp32
 // and / or as the next GEMM's bf16 planes.
-template <int BN>
+template <int BN, bool HEAD = false>
 __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N, long long mb, int nb, int sp, bool empty_k,
-                                              uint32_t tmem_base, uint32_t ab, int quarter, int chalf, int lane) {
+                                              uint32_t tmem_base, uint32_t ab, int quarter, int chalf, int lane,
+                                              const float* head_ws = nullptr, float* head_part = nullptr) {
     const long long m = mb * BM + quarter * 32 + lane;
+    float hacc[HEAD ? HEAD_MAX_N : 1];
+    if constexpr (HEAD) {
+#pragma unroll
+        for (int o = 0; o < HEAD_MAX_N; ++o) hacc[o] = 0.f;
+    }
     const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + ab * (2 * BN) + chalf * (BN / 2);
 #pragma unroll 1
     for (int c = 0; c < BN / 2; c += 32) {
@@ -43,6 +49,24 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
                     if (full || n + j < N) f[j] *= act_bwd_from_out<float>(ep.act, __ldg(aux + j));
+            }
+            if constexpr (HEAD) {
+                // this thread's 32 activations times the head's weight rows (staged [128][HEAD_MAX_N], zero beyond N / head_n);
+                // every lane of the warp reads the same row: broadcast loads
+                const int hq = (ep.head_n + 3) >> 2;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float4* wr = reinterpret_cast<const float4*>(head_ws + (chalf * (BN / 2) + c + j) * HEAD_MAX_N);
+#pragma unroll
+                    for (int q = 0; q < HEAD_MAX_N / 4; ++q)
+                        if (q < hq) {
+                            const float4 wv = wr[q];
+                            hacc[4 * q] = fmaf(f[j], wv.x, hacc[4 * q]);
+                            hacc[4 * q + 1] = fmaf(f[j], wv.y, hacc[4 * q + 1]);
+                            hacc[4 * q + 2] = fmaf(f[j], wv.z, hacc[4 * q + 2]);
+                            hacc[4 * q + 3] = fmaf(f[j], wv.w, hacc[4 * q + 3]);
+                        }
+                }
             }
             if (ep.out_f32) {
                 float* out = ep.out_f32 + (long long)sp * ep.slab + m * ep.ld_f32 + n;
@@ -82,6 +106,48 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
                         }
                 }
             }
+        }
+    }
+    if constexpr (HEAD) {
+        // the warps of the second column half hand their partial sums over; the first half finishes the rows
+        float4* pr = reinterpret_cast<float4*>(head_part + (quarter * 32 + lane) * HEAD_MAX_N);
+        if (chalf == 1) {
+#pragma unroll
+            for (int q = 0; q < HEAD_MAX_N / 4; ++q) pr[q] = make_float4(hacc[4 * q], hacc[4 * q + 1], hacc[4 * q + 2], hacc[4 * q + 3]);
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
+        if (chalf == 0 && m < M) {
+            const int hn = ep.head_n;
+#pragma unroll
+            for (int q = 0; q < HEAD_MAX_N / 4; ++q) {
+                const float4 pv = pr[q];
+                hacc[4 * q] += pv.x; hacc[4 * q + 1] += pv.y; hacc[4 * q + 2] += pv.z; hacc[4 * q + 3] += pv.w;
+            }
+            if (ep.head_b) {
+#pragma unroll
+                for (int o = 0; o < HEAD_MAX_N; ++o)
+                    if (o < hn) hacc[o] += __ldg(ep.head_b + o);
+            }
+            if (ep.head_act == ACT_SOFTMAX) {
+                float mx = -INFINITY;
+#pragma unroll
+                for (int o = 0; o < HEAD_MAX_N; ++o)
+                    if (o < hn) mx = fmaxf(mx, hacc[o]);
+                float sum = 0.f;
+#pragma unroll
+                for (int o = 0; o < HEAD_MAX_N; ++o)
+                    if (o < hn) { hacc[o] = expf(hacc[o] - mx); sum += hacc[o]; }
+                const float inv = 1.f / sum;
+#pragma unroll
+                for (int o = 0; o < HEAD_MAX_N; ++o) hacc[o] *= inv;
+            } else if (ep.head_act != ACT_NONE) {
+#pragma unroll
+                for (int o = 0; o < HEAD_MAX_N; ++o) hacc[o] = act_fwd<float>(ep.head_act, hacc[o]);
+            }
+            float* o_row = ep.head_out + m * hn;
+#pragma unroll
+            for (int o = 0; o < HEAD_MAX_N; ++o)
+                if (o < hn) o_row[o] = hacc[o];
         }
     }
 }
@@ -208,6 +274,18 @@ tc3_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     } else {
         // ================= epilogue =================
         const int quarter = warp & 3, chalf = warp >> 2;
+        constexpr bool HEAD_CAPABLE = (A_MAJOR == MAJOR_K && B_MAJOR == MAJOR_MN && BN == 128);
+        // fused head: its weights [N][head_n] staged once per CTA as [128][HEAD_MAX_N], zero-filled, behind the barriers
+        float* head_ws = reinterpret_cast<float*>(smem + STAGES * C::STAGE_BYTES + 256);
+        float* head_part = head_ws + 128 * HEAD_MAX_N;                  // [2][128][HEAD_MAX_N]
+        const bool head = HEAD_CAPABLE && ep.head_w != nullptr;
+        if (head) {
+            for (int i = threadIdx.x; i < 128 * HEAD_MAX_N; i += NUM_EPI_WARPS * 32) {
+                const int k = i / HEAD_MAX_N, o = i % HEAD_MAX_N;
+                head_ws[i] = (k < N && o < ep.head_n) ? __ldg(ep.head_w + (long long)k * ep.head_n + o) : 0.f;
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
+        }
         uint32_t it = 0;
         for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
             const int nb = (int)(t % tiles_n);
@@ -218,7 +296,11 @@ tc3_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
             tc::mbar_wait(&tmem_full_bar[ab], aphase);
             tc::tc_fence_after();
-            epilogue_tile<BN>(ep, M, N, mb, nb, sp, empty_k, tmem_base, ab, quarter, chalf, lane);
+            if (HEAD_CAPABLE && head)
+                epilogue_tile<BN, HEAD_CAPABLE>(ep, M, N, mb, nb, sp, empty_k, tmem_base, ab, quarter, chalf, lane, head_ws,
+                                                head_part + (it & 1) * 128 * HEAD_MAX_N);
+            else
+                epilogue_tile<BN>(ep, M, N, mb, nb, sp, empty_k, tmem_base, ab, quarter, chalf, lane);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&tmem_empty_bar[ab]);

@@ -326,6 +326,42 @@ def test_large_batch_inference_first_layer_from_fp32_rows(sizes, batch):
     assert (out.cpu().numpy().argmax(1) == ref.argmax(1)).mean() > 0.999
 
 
+@pytest.mark.parametrize("sizes,last_act,has_bias,batch", [
+    ([784, 256, 128, 10], "softmax", True, 2048 + 5),
+    ([90, 160, 100, 16], "sigmoid", True, 3000),
+    ([64, 72, 1], "tanh", False, 2500),
+    ([200, 96, 3], "softmax", False, 8192 + 130),
+])
+def test_large_batch_inference_last_unit_in_the_epilogue(sizes, last_act, has_bias, batch):
+    """A last unit of at most 16 outputs behind a 65..128-wide one is applied by the epilogue warps of that
+    unit's tcgen05 GEMM (fp32 FMAs on the tile's rows, then the activation / softmax): no launch of its own,
+    the last hidden activation is never written.  Against the oracle on every row."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    nl = len(sizes) - 1
+    algos = []
+    for l in range(nl):
+        algos += ["linear", last_act if l == nl - 1 else ("relu" if l % 2 == 0 else "sigmoid")]
+    params = det_params(sizes, has_bias, 1201)
+    per = 2 if has_bias else 1
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), has_bias, "float32", 0)
+    for l in range(nl):
+        eng.upload_params(l, params[per * l], params[per * l + 1] if has_bias else None)
+    x = det_normalish((batch, sizes[0]), 1202)
+    xd = torch.tensor(x, dtype=torch.float32, device="cuda:0")
+    eng.profile_begin()
+    out = eng.forward(xd)
+    tags = eng.profile_end()
+    x32_first = nl == 2 and batch >= 8192
+    if x32_first:
+        assert "tc3_fwd_l0" in tags, tags                 # the fp32-input kernel has no head: separate last unit
+    else:
+        assert f"tc3_fwd_l{nl - 2}_head" in tags and f"tc3_fwd_l{nl - 1}" not in tags and "softmax" not in tags, tags
+    ref = orc.forward(orc.parse_stack(algos), params, x)[0][-1]
+    close(out.cpu().numpy(), ref.reshape(batch, -1), "float32", "output", rtol=1e-4)
+    if sizes[-1] > 1:
+        assert (out.cpu().numpy().argmax(1) == ref.reshape(batch, -1).argmax(1)).mean() > 0.999
+
+
 @pytest.mark.parametrize("batch", [1, 4, 300, 8192 + 77])
 def test_inference_writes_only_its_output_rows(batch):
     """Guard bands around the caller's output buffer stay untouched on every inference path (few-row

@@ -4,8 +4,10 @@
 #include "poz_tc3.h"
 #include "poz_tc3_kernel.cuh"
 #include "poz_tc3_x32_kernel.cuh"
+#include "poz_tc3_x32t_kernel.cuh"
 #include "poz_tc.h"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace poz {
@@ -104,11 +106,14 @@ int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long 
                      cudaStream_t stream) {
     constexpr int BN = 128;
     using C = CfgX32<BN>;
+    using CT = CfgX32T<BN>;
     if (!gemm_forward_x32_ok(x, ld, N)) POZ_FAIL("tc3 fp32-input forward: operand not eligible");
+    // X planes in tensor memory (default) or in shared memory (POZ_TC3_X32_TMEM=0)
+    static const bool planes_in_tmem = !(getenv("POZ_TC3_X32_TMEM") && atoi(getenv("POZ_TC3_X32_TMEM")) == 0);
     static bool configured = false;
-    auto kern = tc3_fwd_x32_kernel<BN>;
     if (!configured) {
-        POZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32t_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT::SMEM_BYTES));
         configured = true;
     }
     CUtensorMap mx, mb;
@@ -116,7 +121,10 @@ int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long 
     POZ_TRY(make_map3(&mb, w, 64, 64));
     const long long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     const int grid = (int)(tiles < sms ? tiles : sms);
-    kern<<<grid, X32_THREADS, C::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+    if (planes_in_tmem)
+        tc3_fwd_x32t_kernel<BN><<<grid, X32_THREADS, CT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+    else
+        tc3_fwd_x32_kernel<BN><<<grid, X32_THREADS, C::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     count_launch();
     POZ_CUDA(cudaGetLastError());
     return 0;

@@ -8,7 +8,7 @@ namespace tc3 {
 // Epilogue of one 128 x BN tile for the 32 TMEM lanes of this warp's quarter and its column half: the two
 // accumulators are added, bias / activation (or activation gradient) applied, and the result written as fp32
 // and / or as the next GEMM's bf16 planes.
-template <int BN, bool HEAD = false>
+template <int BN, bool HEAD = false, bool ONE_ACC = false>
 __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N, long long mb, int nb, int sp, bool empty_k,
                                               uint32_t tmem_base, uint32_t ab, int quarter, int chalf, int lane,
                                               const float* head_ws = nullptr, float* head_part = nullptr) {
@@ -18,19 +18,22 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
 #pragma unroll
         for (int o = 0; o < HEAD_MAX_N; ++o) hacc[o] = 0.f;
     }
-    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + ab * (2 * BN) + chalf * (BN / 2);
+    // ONE_ACC: all six products of a k-step went into one accumulator per buffer (the fp32-input kernel with its
+    // X planes in tensor memory); otherwise hi*hi and the five small terms are kept apart and added here
+    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + ab * (ONE_ACC ? BN : 2 * BN) + chalf * (BN / 2);
 #pragma unroll 1
     for (int c = 0; c < BN / 2; c += 32) {
         uint32_t v[32], w[32];
         tc::tmem_ld32(taddr + c, v);
-        tc::tmem_ld32(taddr + BN + c, w);
+        if constexpr (!ONE_ACC) tc::tmem_ld32(taddr + BN + c, w);
         tc::tmem_ld_wait();
         const int n = nb * BN + chalf * (BN / 2) + c;
         if (m < M && n < N) {
             const bool full = (n + 32 <= N);
             float f[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = empty_k ? 0.f : __uint_as_float(v[j]) + __uint_as_float(w[j]);
+            for (int j = 0; j < 32; ++j)
+                f[j] = empty_k ? 0.f : (ONE_ACC ? __uint_as_float(v[j]) : __uint_as_float(v[j]) + __uint_as_float(w[j]));
             if (ep.mode == EPI_BIAS_ACT) {
                 if (ep.bias) {
 #pragma unroll

@@ -1,0 +1,237 @@
+// Forward split-bf16 tcgen05 GEMM from fp32 rows, X planes in TENSOR memory: out = epilogue(X[M][K] * W[K][N]).
+//
+// tc3_fwd_x32_kernel (poz_tc3_x32_kernel.cuh) writes the hi / mid / lo planes of X into shared memory, and its six
+// MMAs per k-step read both operands from there: 8 KB per 128x128x16 MMA, i.e. 128 B per clock at the tensor
+// pipe's full rate -- all the shared-memory bandwidth there is, before the TMA writes and the converters' own
+// loads and stores (ncu: tensor pipe 51 % active, LSU data pipe 66 %).  Here the converters put the planes into
+// tensor memory (`tcgen05.st`, one row per lane, two bf16 per 32-bit column) and the MMAs take A from there
+// (`tcgen05.mma` with a TMEM A operand), so shared memory carries only the fp32 half-blocks and W's planes.
+// Tensor memory then holds: two 128-column accumulators (double-buffered tiles; all six products of a k-step go
+// into the same accumulator, small terms first) and a five-slot ring of X-plane half-blocks (3 planes x 16 columns).
+//   warps 0-7 : epilogue          warp 8 : TMA producer (W planes, fp32 X half-blocks)
+//   warp  9   : TMEM + MMA        warps 10-17 : converters (warp w: rows 32 (w % 4).., k-values 16 ((w - 10) / 4)..)
+#pragma once
+#include "poz_tc3_x32_kernel.cuh"
+
+namespace poz {
+namespace tc3 {
+
+constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in shared memory == plane half-blocks in tensor memory
+constexpr int X32T_SLOT_COLS = PLANES * 16;         // 32 k-values of three planes, two per column
+
+template <int BN> struct CfgX32T {
+    static constexpr int STAGES = 3;                // W-plane stages (one per 64-wide k-block)
+    static constexpr int B_PLANE = BN * BK * 2;
+    static constexpr int B_STAGE = PLANES * B_PLANE;
+    static constexpr int RAW_OFF = STAGES * B_STAGE;
+    static constexpr int BAR_OFF = RAW_OFF + X32T_SLOTS * X32_RAW_BYTES;
+    static constexpr int SMEM_BYTES = BAR_OFF + 1024 + 256;
+    static constexpr int ACC_COLS = 2 * BN;         // two tile buffers
+    static constexpr int A_COL0 = ACC_COLS;
+    static constexpr int TMEM_COLS = 512;
+    static_assert(A_COL0 + X32T_SLOTS * X32T_SLOT_COLS <= TMEM_COLS, "tensor memory: accumulators + X-plane ring");
+    static_assert(SMEM_BYTES <= 227 * 1024, "shared memory of the fp32-input kernel");
+};
+
+// D[tmem] (+)= A[tmem] * B[smem]
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// this lane's eight 32-bit columns starting at taddr
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+template <int BN>
+__global__ void __launch_bounds__(X32_THREADS, 1)
+tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
+                    long long M, int N, long long K, Epi3 ep) {
+    using C = CfgX32T<BN>;
+    constexpr int STAGES = C::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* raw = smem + C::RAW_OFF;                                  // [X32T_SLOTS][128 rows][32 floats], swizzled
+    uint64_t* b_full = reinterpret_cast<uint64_t*>(smem + C::BAR_OFF); // [STAGES] W planes landed
+    uint64_t* b_empty = b_full + STAGES;                               // [STAGES] MMAs of the stage retired
+    uint64_t* a_full = b_empty + STAGES;                               // [SLOTS] planes of the half-block are in tensor memory
+    uint64_t* a_empty = a_full + X32T_SLOTS;                           // [SLOTS] MMAs that read them retired
+    uint64_t* raw_full = a_empty + X32T_SLOTS;                         // [SLOTS]
+    uint64_t* raw_empty = raw_full + X32T_SLOTS;                       // [SLOTS]
+    uint64_t* tmem_full_bar = raw_empty + X32T_SLOTS;                  // [2]
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;                      // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long tiles_m = (M + BM - 1) / BM;
+    const int tiles_n = (N + BN - 1) / BN;
+    const long long num_tiles = tiles_m * tiles_n;
+    const int nkb = (int)((K + BK - 1) / BK);
+
+    if (warp == 8 && lane == 0) {
+        tc::tma_prefetch_desc(&map_x);
+        tc::tma_prefetch_desc(&map_b);
+        for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&b_empty[s], 1); }
+        for (int q = 0; q < X32T_SLOTS; ++q) {
+            tc::mbar_init(&a_full[q], X32_CONV_WARPS); tc::mbar_init(&a_empty[q], 1);
+            tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], X32_CONV_WARPS);
+        }
+        for (int b = 0; b < 2; ++b) { tc::mbar_init(&tmem_full_bar[b], 1); tc::mbar_init(&tmem_empty_bar[b], NUM_EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 9) tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 8) {
+        // ================= TMA producer =================
+        if (tc::elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            uint32_t slot = 0, rphase = 0;
+            for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const int nb = (int)(t % tiles_n);
+                const long long mb = t / tiles_n;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    const int kc = kb * BK;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        tc::mbar_wait(&raw_empty[slot], rphase ^ 1);
+                        tc::mbar_expect_tx(&raw_full[slot], X32_RAW_BYTES);
+                        tma_load_2d_f32(&map_x, &raw_full[slot], raw + slot * X32_RAW_BYTES, kc + 32 * h, (int)(mb * BM));
+                        if (++slot == X32T_SLOTS) { slot = 0; rphase ^= 1; }
+                    }
+                    tc::mbar_wait(&b_empty[stage], phase ^ 1);
+                    uint8_t* sb = smem + stage * C::B_STAGE;
+                    tc::mbar_expect_tx(&b_full[stage], C::B_STAGE);
+#pragma unroll
+                    for (int p = 0; p < PLANES; ++p)
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_3d(&map_b, &b_full[stage], sb + p * C::B_PLANE + j * 8192, nb * BN + 64 * j, kc, p);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 9) {
+        // ================= MMA issuer =================
+        if (tc::elect_one()) {
+            constexpr uint32_t idesc = make_idesc3<MAJOR_K, MAJOR_MN, BN>();
+            int stage = 0;
+            uint32_t phase = 0;
+            uint32_t slot = 0, aphase_ring = 0;
+            uint32_t it = 0;
+            for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+                const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
+                tc::mbar_wait(&tmem_empty_bar[ab], aphase ^ 1);
+                tc::tc_fence_after();
+                const uint32_t acc = tmem_base + ab * BN;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    tc::mbar_wait(&b_full[stage], phase);
+                    const uint32_t sb = tc::smem_u32(smem + stage * C::B_STAGE);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        tc::mbar_wait(&a_full[slot], aphase_ring);
+                        tc::tc_fence_after();
+                        const uint32_t ta = tmem_base + C::A_COL0 + slot * X32T_SLOT_COLS;
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) {
+                            const int kk = 2 * h + j;
+                            uint32_t ad[PLANES];
+                            uint64_t bd[PLANES];
+#pragma unroll
+                            for (int p = 0; p < PLANES; ++p) {
+                                ad[p] = ta + p * 16 + j * 8;
+                                bd[p] = tc::make_desc(sb + p * C::B_PLANE + kk * 2048, 8192, 1024);
+                            }
+                            const uint32_t first = (kb | kk) != 0 ? 1u : 0u;
+                            umma_bf16_ts(acc, ad[0], bd[2], idesc, first);
+                            umma_bf16_ts(acc, ad[2], bd[0], idesc, 1u);
+                            umma_bf16_ts(acc, ad[1], bd[1], idesc, 1u);
+                            umma_bf16_ts(acc, ad[0], bd[1], idesc, 1u);
+                            umma_bf16_ts(acc, ad[1], bd[0], idesc, 1u);
+                            umma_bf16_ts(acc, ad[0], bd[0], idesc, 1u);
+                        }
+                        tc::umma_commit(&a_empty[slot]);     // this slot of the plane ring may be rewritten
+                        if (++slot == X32T_SLOTS) { slot = 0; aphase_ring ^= 1; }
+                    }
+                    tc::umma_commit(&b_empty[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                tc::umma_commit(&tmem_full_bar[ab]);
+            }
+        }
+    } else if (warp >= NUM_EPI_WARPS + 2) {
+        // ================= converters: one row per lane (the lanes this warp may address in tensor memory) =================
+        const int quarter = warp & 3;
+        const int khalf = (warp - (NUM_EPI_WARPS + 2)) >> 2;                 // which 16 of the half-block's 32 k-values
+        const int r = quarter * 32 + lane;
+        const uint32_t sw = (uint32_t)(r & 7);
+        const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::A_COL0 + khalf * 8;
+        uint32_t slot = 0, rphase = 0;
+        for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int kb = 0; kb < 2 * nkb; ++kb) {
+                tc::mbar_wait(&raw_full[slot], rphase);
+                const uint8_t* src = raw + slot * X32_RAW_BYTES + r * 128;
+                float x[16];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float4 v = *reinterpret_cast<const float4*>(src + (((uint32_t)(4 * khalf + c) ^ sw) << 4));
+                    x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+                }
+                uint32_t ph[8], pm[8], pl[8];
+#pragma unroll
+                for (int j = 0; j < 16; j += 2) split3_pair(x[j], x[j + 1], ph[j / 2], pm[j / 2], pl[j / 2]);
+                // the MMAs that read this slot one round ago must have retired
+                tc::mbar_wait(&a_empty[slot], rphase ^ 1);
+                tc::tc_fence_after();
+                const uint32_t ta = lane_base + slot * X32T_SLOT_COLS;
+                tmem_st8(ta, ph);
+                tmem_st8(ta + 16, pm);
+                tmem_st8(ta + 32, pl);
+                tmem_st_wait();
+                tc::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    tc::mbar_arrive(&raw_empty[slot]);
+                    tc::mbar_arrive(&a_full[slot]);
+                }
+                if (++slot == X32T_SLOTS) { slot = 0; rphase ^= 1; }
+            }
+        }
+    } else {
+        // ================= epilogue =================
+        const int quarter = warp & 3, chalf = warp >> 2;
+        uint32_t it = 0;
+        for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            const int nb = (int)(t % tiles_n);
+            const long long mb = t / tiles_n;
+            const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
+            tc::mbar_wait(&tmem_full_bar[ab], aphase);
+            tc::tc_fence_after();
+            epilogue_tile<BN, false, true>(ep, M, N, mb, nb, 0, false, tmem_base, ab, quarter, chalf, lane);
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&tmem_empty_bar[ab]);
+        }
+    }
+
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc::tc_fence_after();
+        tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
+    }
+}
+
+}  // namespace tc3
+}  // namespace poz

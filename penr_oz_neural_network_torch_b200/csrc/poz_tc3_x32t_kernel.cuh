@@ -9,7 +9,7 @@
 // Tensor memory then holds: two 128-column accumulators (double-buffered tiles; all six products of a k-step go
 // into the same accumulator, small terms first) and a five-slot ring of X-plane half-blocks (3 planes x 16 columns).
 //   warps 0-7 : epilogue          warp 8 : TMA producer (W planes, fp32 X half-blocks)
-//   warp  9   : TMEM + MMA        warps 10-17 : converters (warp w: rows 32 (w % 4).., k-values 16 ((w - 10) / 4)..)
+//   warp  9   : TMEM + MMA        warps 10-17 : converters (warp w: rows 32 (w % 4).., half-block (w - 10) / 4 of each k-block)
 #pragma once
 #include "poz_tc3_x32_kernel.cuh"
 
@@ -48,6 +48,17 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8])
                  ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
                  : "memory");
 }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+                 : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t saddr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr) : "memory");
+    return v;
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 template <int BN>
@@ -80,8 +91,8 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         tc::tma_prefetch_desc(&map_b);
         for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&b_empty[s], 1); }
         for (int q = 0; q < X32T_SLOTS; ++q) {
-            tc::mbar_init(&a_full[q], X32_CONV_WARPS); tc::mbar_init(&a_empty[q], 1);
-            tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], X32_CONV_WARPS);
+            tc::mbar_init(&a_full[q], X32_CONV_WARPS / 2); tc::mbar_init(&a_empty[q], 1);
+            tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], X32_CONV_WARPS / 2);
         }
         for (int b = 0; b < 2; ++b) { tc::mbar_init(&tmem_full_bar[b], 1); tc::mbar_init(&tmem_empty_bar[b], NUM_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -172,32 +183,35 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         }
     } else if (warp >= NUM_EPI_WARPS + 2) {
         // ================= converters: one row per lane (the lanes this warp may address in tensor memory) =================
+        // Two groups of four warps; group g converts half-block g of every k-block, so two half-blocks are in flight and
+        // one group's load -> convert -> store chain hides behind the other's.
         const int quarter = warp & 3;
-        const int khalf = (warp - (NUM_EPI_WARPS + 2)) >> 2;                 // which 16 of the half-block's 32 k-values
+        const int grp = (warp - (NUM_EPI_WARPS + 2)) >> 2;
         const int r = quarter * 32 + lane;
         const uint32_t sw = (uint32_t)(r & 7);
-        const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::A_COL0 + khalf * 8;
-        uint32_t slot = 0, rphase = 0;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::A_COL0;
+        const uint32_t raw_row = tc::smem_u32(raw) + r * 128;
+        uint32_t slot = grp, rphase = 0;
         for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            for (int kb = 0; kb < 2 * nkb; ++kb) {
+            for (int kb = 0; kb < nkb; ++kb) {
                 tc::mbar_wait(&raw_full[slot], rphase);
-                const uint8_t* src = raw + slot * X32_RAW_BYTES + r * 128;
-                float x[16];
+                const uint32_t src = raw_row + slot * X32_RAW_BYTES;
+                float4 x[8];
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const float4 v = *reinterpret_cast<const float4*>(src + (((uint32_t)(4 * khalf + c) ^ sw) << 4));
-                    x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+                for (int c = 0; c < 8; ++c) x[c] = lds128(src + (((uint32_t)c ^ sw) << 4));
+                uint32_t ph[16], pm[16], pl[16];
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    split3_pair(x[c].x, x[c].y, ph[2 * c], pm[2 * c], pl[2 * c]);
+                    split3_pair(x[c].z, x[c].w, ph[2 * c + 1], pm[2 * c + 1], pl[2 * c + 1]);
                 }
-                uint32_t ph[8], pm[8], pl[8];
-#pragma unroll
-                for (int j = 0; j < 16; j += 2) split3_pair(x[j], x[j + 1], ph[j / 2], pm[j / 2], pl[j / 2]);
                 // the MMAs that read this slot one round ago must have retired
                 tc::mbar_wait(&a_empty[slot], rphase ^ 1);
                 tc::tc_fence_after();
                 const uint32_t ta = lane_base + slot * X32T_SLOT_COLS;
-                tmem_st8(ta, ph);
-                tmem_st8(ta + 16, pm);
-                tmem_st8(ta + 32, pl);
+                tmem_st16(ta, ph);
+                tmem_st16(ta + 16, pm);
+                tmem_st16(ta + 32, pl);
                 tmem_st_wait();
                 tc::tc_fence_before();
                 __syncwarp();
@@ -205,7 +219,8 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     tc::mbar_arrive(&raw_empty[slot]);
                     tc::mbar_arrive(&a_full[slot]);
                 }
-                if (++slot == X32T_SLOTS) { slot = 0; rphase ^= 1; }
+                slot += 2;
+                if (slot >= X32T_SLOTS) { slot -= X32T_SLOTS; rphase ^= 1; }
             }
         }
     } else {

@@ -7,7 +7,7 @@ timeout 300 $C3 > gpurun_out/c3_plain.log 2>&1 || { echo "plain run failed"; tai
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv \
     --log-file gpurun_out/c3_launches.csv $C3 > gpurun_out/c3_ncu_list.log 2>&1
 echo "ncu list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:tc3_fwd_x32 -s 3 -c 2 -f \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:tc3_fwd_x32t -s 3 -c 2 -f \
     -o gpurun_out/prof_c3_x32 $C3 > gpurun_out/c3_ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ncu -i gpurun_out/prof_c3_x32.ncu-rep --page raw --csv > gpurun_out/c3_x32_raw.csv 2>/dev/null

@@ -551,9 +551,13 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
         // A narrow last unit (<= 16 outputs) behind a 65..128-wide one rides in that unit's epilogue: the tile holds
         // whole rows, so the epilogue warps apply the last Linear in fp32, then its activation / softmax, and the
         // last hidden activation never leaves the SM (POZ_TC3_FUSE_HEAD=0: separate kernels).
+        // A hidden unit whose consumer can read fp32 rows (the fp32-input kernel: wide enough, rows 16-byte aligned,
+        // enough of them) writes fp32 rows instead of three bf16 planes: 4 instead of 6 bytes per element each way.
         static const bool head_allowed = !(getenv("POZ_TC3_FUSE_HEAD") && atoi(getenv("POZ_TC3_FUSE_HEAD")) == 0);
-        const bool fuse_head = head_allowed && !cost_host && nl >= 2 && !(nl == 2 && x32) &&
-                               c->acts[nl - 2] != ACT_SOFTMAX && tc3::gemm_forward_head_ok(c->sizes[nl - 1], n_out);
+        static const bool f32_chain = !(getenv("POZ_TC3_F32_CHAIN") && atoi(getenv("POZ_TC3_F32_CHAIN")) == 0);
+        bool in_f32 = x32, head_done = false;
+        const float* in_ptr = x + r0 * c->sizes[0];
+        long long in_ld = c->sizes[0];
         for (int l = 0; l < nl; ++l) {
             const int K = c->sizes[l], N = c->sizes[l + 1];
             const bool last = l == nl - 1;
@@ -562,31 +566,41 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
             ep.act = c->acts[l];
             ep.bias = c->has_bias ? P + c->off[l] + (long long)K * N : nullptr;
             tc3::PlaneMat nxt{};
-            if (fuse_head && l == nl - 2) {
+            const bool head_here = head_allowed && !cost_host && l == nl - 2 && c->acts[l] != ACT_SOFTMAX &&
+                                   tc3::gemm_forward_head_ok(N, n_out) && (!in_f32 || tc3::gemm_forward_x32_head_ok());
+            bool out_f32_rows = false;
+            if (head_here) {
                 ep.head_w = P + c->off[nl - 1];
                 ep.head_b = c->has_bias ? P + c->off[nl - 1] + (long long)N * n_out : nullptr;
                 ep.head_out = out + r0 * n_out;
                 ep.head_n = n_out;
                 ep.head_act = c->acts[nl - 1];
-                ProfScope ps(c, "tc3_fwd_l" + std::to_string(l) + "_head", stream);
-                POZ_TRY(tc3::gemm_forward(cur, tc3_weight(c, l), m, N, K, ep, sms, stream));
-                break;
-            }
-            if (last) {
+            } else if (last) {
                 ep.out_f32 = softmax_last ? c->tc_logits : out + r0 * n_out;
                 ep.ld_f32 = N;
                 z_last = ep.out_f32;
+            } else if (f32_chain && x32_allowed && m >= x32_min_rows &&
+                       tc3::gemm_forward_x32_ok(static_cast<const float*>(c->tc_scr[flip]), N, c->sizes[l + 2])) {
+                out_f32_rows = true;
+                ep.out_f32 = static_cast<float*>(c->tc_scr[flip]);
+                ep.ld_f32 = N;
             } else {
                 nxt.ptr = static_cast<const __nv_bfloat16*>(c->tc_scr[flip]);
                 nxt.rows = m; nxt.cols = N; nxt.ld = round8(N); nxt.plane_stride = m * nxt.ld;
                 ep.out_planes = static_cast<__nv_bfloat16*>(c->tc_scr[flip]);
                 ep.ld_planes = nxt.ld; ep.plane_stride = nxt.plane_stride;
             }
-            ProfScope ps(c, "tc3_fwd_l" + std::to_string(l), stream);
-            if (l == 0 && x32)
-                POZ_TRY(tc3::gemm_forward_x32(x + r0 * c->sizes[0], c->sizes[0], tc3_weight(c, l), m, N, K, ep, sms, stream));
-            else
-                POZ_TRY(tc3::gemm_forward(cur, tc3_weight(c, l), m, N, K, ep, sms, stream));
+            {
+                ProfScope ps(c, "tc3_fwd_l" + std::to_string(l) + (head_here ? "_head" : ""), stream);
+                if (in_f32)
+                    POZ_TRY(tc3::gemm_forward_x32(in_ptr, in_ld, tc3_weight(c, l), m, N, K, ep, sms, stream));
+                else
+                    POZ_TRY(tc3::gemm_forward(cur, tc3_weight(c, l), m, N, K, ep, sms, stream));
+            }
+            if (head_here) { head_done = true; break; }
+            in_f32 = out_f32_rows;
+            in_ptr = static_cast<const float*>(c->tc_scr[flip]);
+            in_ld = N;
             cur = nxt;
             flip = flip == 1 ? 2 : 1;
         }
@@ -603,7 +617,7 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
                 a.inv_count = 1.0 / ((double)batch * n_out);
             }
             POZ_TRY(run_loss<float>(c, a, stream));
-        } else if (softmax_last && !fuse_head) {
+        } else if (softmax_last && !head_done) {
             POZ_TRY(run_softmax<float>(c, z_last, out + r0 * n_out, m, n_out, stream));
         }
     }

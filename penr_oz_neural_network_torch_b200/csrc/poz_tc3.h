@@ -50,6 +50,8 @@ bool gemm_forward_head_ok(int N, int head_n);
 int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms,
                      cudaStream_t s);
 bool gemm_forward_x32_ok(const float* x, long long ld, int N);
+// whether gemm_forward_x32 takes ep.head_* (only the tensor-memory variant does)
+bool gemm_forward_x32_head_ok();
 // out[M][K_in] = epilogue(dz[M][N_out] * w[K_in][N_out]^T)
 int gemm_backward_data(const PlaneMat& dz, const PlaneMat& w, long long M, int K_in, int N_out, const Epi3& ep, int sms,
                        cudaStream_t s);

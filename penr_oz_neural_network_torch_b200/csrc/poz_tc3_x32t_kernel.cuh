@@ -19,13 +19,14 @@ namespace tc3 {
 constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in shared memory == plane half-blocks in tensor memory
 constexpr int X32T_SLOT_COLS = PLANES * 16;         // 32 k-values of three planes, two per column
 
-template <int BN> struct CfgX32T {
-    static constexpr int STAGES = 3;                // W-plane stages (one per 64-wide k-block)
+template <int BN, int STAGES_, bool HEAD> struct CfgX32T {
+    static constexpr int STAGES = STAGES_;          // W-plane stages (one per 64-wide k-block)
     static constexpr int B_PLANE = BN * BK * 2;
     static constexpr int B_STAGE = PLANES * B_PLANE;
     static constexpr int RAW_OFF = STAGES * B_STAGE;
     static constexpr int BAR_OFF = RAW_OFF + X32T_SLOTS * X32_RAW_BYTES;
-    static constexpr int SMEM_BYTES = BAR_OFF + 1024 + 256;
+    static constexpr int HEAD_OFF = BAR_OFF + 256;  // fused head: staged weights + two partial-sum buffers (poz_tc3.h)
+    static constexpr int SMEM_BYTES = HEAD_OFF + (HEAD ? HEAD_SMEM_BYTES : 0) + 1024;
     static constexpr int ACC_COLS = 2 * BN;         // two tile buffers
     static constexpr int A_COL0 = ACC_COLS;
     static constexpr int TMEM_COLS = 512;
@@ -61,11 +62,11 @@ __device__ __forceinline__ float4 lds128(uint32_t saddr) {
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-template <int BN>
+template <int BN, int NSTAGES, bool HEAD>
 __global__ void __launch_bounds__(X32_THREADS, 1)
 tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                     long long M, int N, long long K, Epi3 ep) {
-    using C = CfgX32T<BN>;
+    using C = CfgX32T<BN, NSTAGES, HEAD>;
     constexpr int STAGES = C::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -226,6 +227,15 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     } else {
         // ================= epilogue =================
         const int quarter = warp & 3, chalf = warp >> 2;
+        float* head_ws = reinterpret_cast<float*>(smem + C::HEAD_OFF);    // [128][HEAD_MAX_N], zero beyond N / head_n
+        float* head_part = head_ws + 128 * HEAD_MAX_N;                     // [2][128][HEAD_MAX_N]
+        if (HEAD) {
+            for (int i = threadIdx.x; i < 128 * HEAD_MAX_N; i += NUM_EPI_WARPS * 32) {
+                const int k = i / HEAD_MAX_N, o = i % HEAD_MAX_N;
+                head_ws[i] = (k < N && o < ep.head_n) ? __ldg(ep.head_w + (long long)k * ep.head_n + o) : 0.f;
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
+        }
         uint32_t it = 0;
         for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
             const int nb = (int)(t % tiles_n);
@@ -233,7 +243,8 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
             tc::mbar_wait(&tmem_full_bar[ab], aphase);
             tc::tc_fence_after();
-            epilogue_tile<BN, false, true>(ep, M, N, mb, nb, 0, false, tmem_base, ab, quarter, chalf, lane);
+            epilogue_tile<BN, HEAD, true>(ep, M, N, mb, nb, 0, false, tmem_base, ab, quarter, chalf, lane, head_ws,
+                                          head_part + (it & 1) * 128 * HEAD_MAX_N);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&tmem_empty_bar[ab]);

@@ -263,7 +263,10 @@ def test_config3_inference_sweep(batch):
     if batch > 4096:
         tail = xd[batch - 4096:].contiguous()
         again = eng.forward(tail)
-        assert torch.allclose(out[batch - 4096:], again, rtol=1e-6, atol=1e-9)
+        # the re-run takes the plane path (two accumulators per tile), the large call the fp32-row kernels (one):
+        # both fp32-grade, not bit-identical
+        diff = ((out[batch - 4096:] - again).abs() / again.abs().clamp_min(1e-6)).max().item()
+        assert torch.allclose(out[batch - 4096:], again, rtol=1e-5, atol=1e-7), diff
 
 
 @pytest.mark.parametrize("sizes,algos,has_bias", [
@@ -330,7 +333,9 @@ def test_large_batch_inference_first_layer_from_fp32_rows(sizes, batch):
     ([784, 256, 128, 10], "softmax", True, 2048 + 5),
     ([90, 160, 100, 16], "sigmoid", True, 3000),
     ([64, 72, 1], "tanh", False, 2500),
-    ([200, 96, 3], "softmax", False, 8192 + 130),
+    ([200, 96, 3], "softmax", False, 8192 + 130),          # the head in the fp32-input kernel itself
+    ([784, 256, 128, 10], "softmax", True, 8192 + 300),    # fp32 rows from unit 0 to unit 1, head in unit 1
+    ([96, 130, 72, 100, 12], "tanh", True, 9000),          # 130 % 4 != 0: that hand-over stays bf16 planes
 ])
 def test_large_batch_inference_last_unit_in_the_epilogue(sizes, last_act, has_bias, batch):
     """A last unit of at most 16 outputs behind a 65..128-wide one is applied by the epilogue warps of that
@@ -351,11 +356,7 @@ def test_large_batch_inference_last_unit_in_the_epilogue(sizes, last_act, has_bi
     eng.profile_begin()
     out = eng.forward(xd)
     tags = eng.profile_end()
-    x32_first = nl == 2 and batch >= 8192
-    if x32_first:
-        assert "tc3_fwd_l0" in tags, tags                 # the fp32-input kernel has no head: separate last unit
-    else:
-        assert f"tc3_fwd_l{nl - 2}_head" in tags and f"tc3_fwd_l{nl - 1}" not in tags and "softmax" not in tags, tags
+    assert f"tc3_fwd_l{nl - 2}_head" in tags and f"tc3_fwd_l{nl - 1}" not in tags and "softmax" not in tags, tags
     ref = orc.forward(orc.parse_stack(algos), params, x)[0][-1]
     close(out.cpu().numpy(), ref.reshape(batch, -1), "float32", "output", rtol=1e-4)
     if sizes[-1] > 1:

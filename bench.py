@@ -47,6 +47,8 @@ def init_params(sizes, seed=0):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures committed under
 # profiles/ncu/ (r01_c2_simt_full_raw_v3.csv, r01_c4_tc_fwd_full_raw.csv); null where no capture exists.
+# dram__bytes_read.sum + dram__bytes_write.sum of the two launches of one 262,144-row inference pass (ncu --set full)
+NCU_TRAFFIC_C3 = {262144: 1_343_600_000}
 NCU_TRAFFIC = {"fwd_l0": 4_344_064, "bwd_w_l0": 4_307_712, "fwd_l1": 1_508_608, "bwd_w_l1": 1_620_736,
                "bwd_w_l2": 613_376, "bwd_x_l1": 1_769_728, "tc_fwd": 1_204_000_000}
 
@@ -412,7 +414,11 @@ def run_c3(args, world, rank, local):
         per = ms / args.steps * 1e-3
         roof = {"bound": "hbm", "kernel": "whole forward pass (all layer kernels of one call)",
                 "achieved": round(batch * C3_BYTES_PER_SAMPLE / per / 1e9, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
-                "frac": round(batch * C3_BYTES_PER_SAMPLE / per / 1e9 / pk["hbm_gbs"], 4), "traffic": None,
+                "frac": round(batch * C3_BYTES_PER_SAMPLE / per / 1e9 / pk["hbm_gbs"], 4),
+                "traffic": NCU_TRAFFIC_C3.get(batch),
+                "traffic_source": ("ncu --set full, profiles/ncu/r01_c3_x32t_full_raw_v4.csv (both launches of a pass; the excess "
+                                   "over the algorithmic bytes is the fp32 hand-over between unit 0 and unit 1)")
+                if batch in NCU_TRAFFIC_C3 else None,
                 "peak_source": pk["source"], "top_kernel": top, "share_of_step": round(prof[top]["ms"] / tot, 3),
                 "fp32_fma": {"achieved_tflops": round(batch * C3_FLOPS_PER_SAMPLE / per / 1e12, 2),
                              "nominal_peak_tflops": 74.4,

@@ -535,8 +535,9 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
         // The first layer reads the fp32 rows directly and makes its planes in shared memory when it can
         // (poz_tc3_x32_kernel.cuh); otherwise the chunk is split into planes in global memory first.
         static const bool x32_allowed = !(getenv("POZ_TC3_X32") && atoi(getenv("POZ_TC3_X32")) == 0);
-        // (measured, plane path vs this one: 54 vs 58 us at 4096 rows, 67 vs 58 us at 8192, 110 vs 90 us at 16384)
-        static const long long x32_min_rows = getenv("POZ_TC3_X32_MIN_ROWS") ? atoll(getenv("POZ_TC3_X32_MIN_ROWS")) : 8192;
+        // (measured, plane path vs this one with the planes in tensor memory: 41.4 vs 37.3 us per call at 2048 rows,
+        //  43.9 vs 39.1 us at 4096; the shared-memory-plane version of the kernel only paid from 8192 rows)
+        static const long long x32_min_rows = getenv("POZ_TC3_X32_MIN_ROWS") ? atoll(getenv("POZ_TC3_X32_MIN_ROWS")) : 2048;
         const bool x32 = x32_allowed && m >= x32_min_rows && tc3::gemm_forward_x32_ok(x + r0 * c->sizes[0], c->sizes[0], c->sizes[1]);
         tc3::PlaneMat cur;
         cur.ptr = static_cast<const __nv_bfloat16*>(c->tc_scr[0]);

@@ -129,9 +129,9 @@ int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long 
     const long long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     const int grid = (int)(tiles < sms ? tiles : sms);
     if (ep.head_w)
-        tc3_fwd_x32t_kernel<BN, 2, true><<<grid, X32_THREADS, CH::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+        tc3_fwd_x32t_kernel<BN, 2, true><<<grid, X32T_THREADS, CH::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     else if (planes_in_tmem)
-        tc3_fwd_x32t_kernel<BN, 3, false><<<grid, X32_THREADS, CT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+        tc3_fwd_x32t_kernel<BN, 3, false><<<grid, X32T_THREADS, CT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     else
         tc3_fwd_x32_kernel<BN><<<grid, X32_THREADS, C::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     count_launch();

@@ -13,10 +13,11 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
                                               uint32_t tmem_base, uint32_t ab, int quarter, int chalf, int lane,
                                               const float* head_ws = nullptr, float* head_part = nullptr) {
     const long long m = mb * BM + quarter * 32 + lane;
-    float hacc[HEAD ? HEAD_MAX_N : 1];
+    // fused head: HEAD_MAX_N running sums as packed fp32 pairs (fma.rn.f32x2: two FMAs per issue slot)
+    unsigned long long hacc2[HEAD ? HEAD_MAX_N / 2 : 1];
     if constexpr (HEAD) {
 #pragma unroll
-        for (int o = 0; o < HEAD_MAX_N; ++o) hacc[o] = 0.f;
+        for (int o = 0; o < HEAD_MAX_N / 2; ++o) hacc2[o] = 0ull;
     }
     // ONE_ACC: all six products of a k-step went into one accumulator per buffer (the fp32-input kernel with its
     // X planes in tensor memory); otherwise hi*hi and the five small terms are kept apart and added here
@@ -36,9 +37,17 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
                 f[j] = empty_k ? 0.f : (ONE_ACC ? __uint_as_float(v[j]) : __uint_as_float(v[j]) + __uint_as_float(w[j]));
             if (ep.mode == EPI_BIAS_ACT) {
                 if (ep.bias) {
+                    if (full && ((reinterpret_cast<uintptr_t>(ep.bias + n) & 15) == 0)) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (full || n + j < N) f[j] += __ldg(ep.bias + n + j);
+                        for (int j = 0; j < 32; j += 4) {
+                            const float4 b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + n + j));
+                            f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (n + j < N) f[j] += __ldg(ep.bias + n + j);
+                    }
                 }
                 if (ep.act == ACT_RELU) {
 #pragma unroll
@@ -57,17 +66,18 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
                 // this thread's 32 activations times the head's weight rows (staged [128][HEAD_MAX_N], zero beyond N / head_n);
                 // every lane of the warp reads the same row: broadcast loads
                 const int hq = (ep.head_n + 3) >> 2;
+                const uint32_t wrow = tc::smem_u32(head_ws) + (uint32_t)(chalf * (BN / 2) + c) * (HEAD_MAX_N * 4);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const float4* wr = reinterpret_cast<const float4*>(head_ws + (chalf * (BN / 2) + c + j) * HEAD_MAX_N);
+                    unsigned long long fj;
+                    asm("mov.b64 %0, {%1, %1};" : "=l"(fj) : "f"(f[j]));
 #pragma unroll
                     for (int q = 0; q < HEAD_MAX_N / 4; ++q)
                         if (q < hq) {
-                            const float4 wv = wr[q];
-                            hacc[4 * q] = fmaf(f[j], wv.x, hacc[4 * q]);
-                            hacc[4 * q + 1] = fmaf(f[j], wv.y, hacc[4 * q + 1]);
-                            hacc[4 * q + 2] = fmaf(f[j], wv.z, hacc[4 * q + 2]);
-                            hacc[4 * q + 3] = fmaf(f[j], wv.w, hacc[4 * q + 3]);
+                            unsigned long long w0, w1;
+                            asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "r"(wrow + (uint32_t)(j * HEAD_MAX_N + 4 * q) * 4));
+                            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(hacc2[2 * q]) : "l"(fj), "l"(w0));
+                            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(hacc2[2 * q + 1]) : "l"(fj), "l"(w1));
                         }
                 }
             }
@@ -113,6 +123,9 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
     }
     if constexpr (HEAD) {
         // the warps of the second column half hand their partial sums over; the first half finishes the rows
+        float hacc[HEAD_MAX_N];
+#pragma unroll
+        for (int o = 0; o < HEAD_MAX_N / 2; ++o) asm("mov.b64 {%0, %1}, %2;" : "=f"(hacc[2 * o]), "=f"(hacc[2 * o + 1]) : "l"(hacc2[o]));
         float4* pr = reinterpret_cast<float4*>(head_part + (quarter * 32 + lane) * HEAD_MAX_N);
         if (chalf == 1) {
 #pragma unroll

@@ -8,7 +8,7 @@
 // (`tcgen05.mma` with a TMEM A operand), so shared memory carries only the fp32 half-blocks and W's planes.
 // Tensor memory then holds: two 128-column accumulators (double-buffered tiles; all six products of a k-step go
 // into the same accumulator, small terms first) and a five-slot ring of X-plane half-blocks (3 planes x 16 columns).
-//   warps 0-7 : epilogue          warp 8 : TMA producer (W planes, fp32 X half-blocks)
+//   warps 0-7 : epilogue          warp 8 : TMA producer of the fp32 X half-blocks      warp 18 : TMA producer of W's planes
 //   warp  9   : TMEM + MMA        warps 10-17 : converters (warp w: rows 32 (w % 4).., half-block (w - 10) / 4 of each k-block)
 #pragma once
 #include "poz_tc3_x32_kernel.cuh"
@@ -18,6 +18,8 @@ namespace tc3 {
 
 constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in shared memory == plane half-blocks in tensor memory
 constexpr int X32T_SLOT_COLS = PLANES * 16;         // 32 k-values of three planes, two per column
+constexpr int X32T_W_WARP = NUM_EPI_WARPS + 2 + X32_CONV_WARPS;   // warp 18: producer of W's planes
+constexpr int X32T_THREADS = X32_THREADS + 32;
 
 template <int BN, int STAGES_, bool HEAD> struct CfgX32T {
     static constexpr int STAGES = STAGES_;          // W-plane stages (one per 64-wide k-block)
@@ -63,7 +65,7 @@ __device__ __forceinline__ float4 lds128(uint32_t saddr) {
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 template <int BN, int NSTAGES, bool HEAD>
-__global__ void __launch_bounds__(X32_THREADS, 1)
+__global__ void __launch_bounds__(X32T_THREADS, 1)
 tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                     long long M, int N, long long K, Epi3 ep) {
     using C = CfgX32T<BN, NSTAGES, HEAD>;
@@ -105,23 +107,30 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 8) {
-        // ================= TMA producer =================
+        // ================= TMA producer, X: fp32 half-blocks into the raw ring =================
+        // (W's planes have their own producer warp: with both in one thread the wait for a free W stage also held
+        // back the X loads, and the converters of a short-K layer spent their time waiting for data)
+        if (tc::elect_one()) {
+            uint32_t slot = 0, rphase = 0;
+            for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const long long mb = t / tiles_n;
+                for (int hb = 0; hb < 2 * nkb; ++hb) {
+                    tc::mbar_wait(&raw_empty[slot], rphase ^ 1);
+                    tc::mbar_expect_tx(&raw_full[slot], X32_RAW_BYTES);
+                    tma_load_2d_f32(&map_x, &raw_full[slot], raw + slot * X32_RAW_BYTES, 32 * hb, (int)(mb * BM));
+                    if (++slot == X32T_SLOTS) { slot = 0; rphase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == X32T_W_WARP) {
+        // ================= TMA producer, W: one stage of planes per 64-wide k-block =================
         if (tc::elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            uint32_t slot = 0, rphase = 0;
             for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
                 const int nb = (int)(t % tiles_n);
-                const long long mb = t / tiles_n;
                 for (int kb = 0; kb < nkb; ++kb) {
                     const int kc = kb * BK;
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        tc::mbar_wait(&raw_empty[slot], rphase ^ 1);
-                        tc::mbar_expect_tx(&raw_full[slot], X32_RAW_BYTES);
-                        tma_load_2d_f32(&map_x, &raw_full[slot], raw + slot * X32_RAW_BYTES, kc + 32 * h, (int)(mb * BM));
-                        if (++slot == X32T_SLOTS) { slot = 0; rphase ^= 1; }
-                    }
                     tc::mbar_wait(&b_empty[stage], phase ^ 1);
                     uint8_t* sb = smem + stage * C::B_STAGE;
                     tc::mbar_expect_tx(&b_full[stage], C::B_STAGE);
@@ -182,7 +191,7 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 tc::umma_commit(&tmem_full_bar[ab]);
             }
         }
-    } else if (warp >= NUM_EPI_WARPS + 2) {
+    } else if (warp >= NUM_EPI_WARPS + 2 && warp < X32T_W_WARP) {
         // ================= converters: one row per lane (the lanes this warp may address in tensor memory) =================
         // Two groups of four warps; group g converts half-block g of every k-block, so two half-blocks are in flight and
         // one group's load -> convert -> store chain hides behind the other's.

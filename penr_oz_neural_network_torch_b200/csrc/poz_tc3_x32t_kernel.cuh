@@ -6,8 +6,12 @@
 // loads and stores (ncu: tensor pipe 51 % active, LSU data pipe 66 %).  Here the converters put the planes into
 // tensor memory (`tcgen05.st`, one row per lane, two bf16 per 32-bit column) and the MMAs take A from there
 // (`tcgen05.mma` with a TMEM A operand), so shared memory carries only the fp32 half-blocks and W's planes.
-// Tensor memory then holds: two 128-column accumulators (double-buffered tiles; all six products of a k-step go
-// into the same accumulator, small terms first) and a five-slot ring of X-plane half-blocks (3 planes x 16 columns).
+// Tensor memory then holds: two 128-column main accumulators (hi*hi; double-buffered tiles), ONE 128-column accumulator
+// for the five small products, and two X-plane half-block slots (3 planes x 16 columns each; converter group h owns
+// slot h).  The tensor core truncates its fp32 accumulator at every MMA, so the small terms must stay out of the main
+// sum (one accumulator for all six: max relative error of the output probabilities 1.8e-5 against 2.3e-6); the small
+// accumulator is shared between the two tile buffers by folding it into the main one first thing in the epilogue
+// (tcgen05.ld both, add, tcgen05.st) and releasing it to the next tile's MMAs right after.
 //   warps 0-7 : epilogue          warp 8 : TMA producer of the fp32 X half-blocks      warp 18 : TMA producer of W's planes
 //   warp  9   : TMEM + MMA        warps 10-17 : converters (warp w: rows 32 (w % 4).., half-block (w - 10) / 4 of each k-block)
 #pragma once
@@ -16,7 +20,7 @@
 namespace poz {
 namespace tc3 {
 
-constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in shared memory == plane half-blocks in tensor memory
+constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in flight in shared memory
 constexpr int X32T_SLOT_COLS = PLANES * 16;         // 32 k-values of three planes, two per column
 constexpr int X32T_W_WARP = NUM_EPI_WARPS + 2 + X32_CONV_WARPS;   // warp 18: producer of W's planes
 constexpr int X32T_THREADS = X32_THREADS + 32;
@@ -29,10 +33,10 @@ template <int BN, int STAGES_, bool HEAD> struct CfgX32T {
     static constexpr int BAR_OFF = RAW_OFF + X32T_SLOTS * X32_RAW_BYTES;
     static constexpr int HEAD_OFF = BAR_OFF + 256;  // fused head: staged weights + two partial-sum buffers (poz_tc3.h)
     static constexpr int SMEM_BYTES = HEAD_OFF + (HEAD ? HEAD_SMEM_BYTES : 0) + 1024;
-    static constexpr int ACC_COLS = 2 * BN;         // two tile buffers
-    static constexpr int A_COL0 = ACC_COLS;
+    static constexpr int SMALL_COL0 = 2 * BN;       // after the two main accumulators
+    static constexpr int A_COL0 = 3 * BN;
     static constexpr int TMEM_COLS = 512;
-    static_assert(A_COL0 + X32T_SLOTS * X32T_SLOT_COLS <= TMEM_COLS, "tensor memory: accumulators + X-plane ring");
+    static_assert(A_COL0 + 2 * X32T_SLOT_COLS <= TMEM_COLS, "tensor memory: accumulators + two X-plane slots");
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory of the fp32-input kernel");
 };
 
@@ -57,6 +61,17 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16
                    "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
                  : "memory");
 }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+          "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+          "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+          "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+        : "memory");
+}
 __device__ __forceinline__ float4 lds128(uint32_t saddr) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr) : "memory");
@@ -75,13 +90,14 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint8_t* raw = smem + C::RAW_OFF;                                  // [X32T_SLOTS][128 rows][32 floats], swizzled
     uint64_t* b_full = reinterpret_cast<uint64_t*>(smem + C::BAR_OFF); // [STAGES] W planes landed
     uint64_t* b_empty = b_full + STAGES;                               // [STAGES] MMAs of the stage retired
-    uint64_t* a_full = b_empty + STAGES;                               // [SLOTS] planes of the half-block are in tensor memory
-    uint64_t* a_empty = a_full + X32T_SLOTS;                           // [SLOTS] MMAs that read them retired
-    uint64_t* raw_full = a_empty + X32T_SLOTS;                         // [SLOTS]
+    uint64_t* a_full = b_empty + STAGES;                               // [2] planes of half h of the k-block are in tensor memory
+    uint64_t* a_empty = a_full + 2;                                    // [2] MMAs that read them retired
+    uint64_t* raw_full = a_empty + 2;                                  // [SLOTS]
     uint64_t* raw_empty = raw_full + X32T_SLOTS;                       // [SLOTS]
     uint64_t* tmem_full_bar = raw_empty + X32T_SLOTS;                  // [2]
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;                      // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+    uint64_t* small_empty_bar = tmem_empty_bar + 2;                    // [1] small-terms accumulator folded into the main one
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(small_empty_bar + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long tiles_m = (M + BM - 1) / BM;
@@ -93,10 +109,9 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         tc::tma_prefetch_desc(&map_x);
         tc::tma_prefetch_desc(&map_b);
         for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&b_empty[s], 1); }
-        for (int q = 0; q < X32T_SLOTS; ++q) {
-            tc::mbar_init(&a_full[q], X32_CONV_WARPS / 2); tc::mbar_init(&a_empty[q], 1);
-            tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], X32_CONV_WARPS / 2);
-        }
+        for (int h = 0; h < 2; ++h) { tc::mbar_init(&a_full[h], X32_CONV_WARPS / 2); tc::mbar_init(&a_empty[h], 1); }
+        for (int q = 0; q < X32T_SLOTS; ++q) { tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], X32_CONV_WARPS / 2); }
+        tc::mbar_init(small_empty_bar, NUM_EPI_WARPS);
         for (int b = 0; b < 2; ++b) { tc::mbar_init(&tmem_full_bar[b], 1); tc::mbar_init(&tmem_empty_bar[b], NUM_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -149,21 +164,23 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             constexpr uint32_t idesc = make_idesc3<MAJOR_K, MAJOR_MN, BN>();
             int stage = 0;
             uint32_t phase = 0;
-            uint32_t slot = 0, aphase_ring = 0;
+            uint32_t kbc = 0;                              // k-blocks done: parity of the per-half barriers
             uint32_t it = 0;
+            const uint32_t acs = tmem_base + C::SMALL_COL0; // small-terms accumulator (shared by the two tile buffers)
             for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
                 const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
                 tc::mbar_wait(&tmem_empty_bar[ab], aphase ^ 1);
+                tc::mbar_wait(small_empty_bar, (it & 1) ^ 1);     // the previous tile's small terms have been folded away
                 tc::tc_fence_after();
-                const uint32_t acc = tmem_base + ab * BN;
-                for (int kb = 0; kb < nkb; ++kb) {
+                const uint32_t acc = tmem_base + ab * BN;          // main (hi*hi) accumulator
+                for (int kb = 0; kb < nkb; ++kb, ++kbc) {
                     tc::mbar_wait(&b_full[stage], phase);
                     const uint32_t sb = tc::smem_u32(smem + stage * C::B_STAGE);
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        tc::mbar_wait(&a_full[slot], aphase_ring);
+                        tc::mbar_wait(&a_full[h], kbc & 1);
                         tc::tc_fence_after();
-                        const uint32_t ta = tmem_base + C::A_COL0 + slot * X32T_SLOT_COLS;
+                        const uint32_t ta = tmem_base + C::A_COL0 + h * X32T_SLOT_COLS;
 #pragma unroll
                         for (int j = 0; j < 2; ++j) {
                             const int kk = 2 * h + j;
@@ -175,15 +192,14 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                                 bd[p] = tc::make_desc(sb + p * C::B_PLANE + kk * 2048, 8192, 1024);
                             }
                             const uint32_t first = (kb | kk) != 0 ? 1u : 0u;
-                            umma_bf16_ts(acc, ad[0], bd[2], idesc, first);
-                            umma_bf16_ts(acc, ad[2], bd[0], idesc, 1u);
-                            umma_bf16_ts(acc, ad[1], bd[1], idesc, 1u);
-                            umma_bf16_ts(acc, ad[0], bd[1], idesc, 1u);
-                            umma_bf16_ts(acc, ad[1], bd[0], idesc, 1u);
-                            umma_bf16_ts(acc, ad[0], bd[0], idesc, 1u);
+                            umma_bf16_ts(acs, ad[0], bd[2], idesc, first);
+                            umma_bf16_ts(acs, ad[2], bd[0], idesc, 1u);
+                            umma_bf16_ts(acs, ad[1], bd[1], idesc, 1u);
+                            umma_bf16_ts(acs, ad[0], bd[1], idesc, 1u);
+                            umma_bf16_ts(acs, ad[1], bd[0], idesc, 1u);
+                            umma_bf16_ts(acc, ad[0], bd[0], idesc, first);
                         }
-                        tc::umma_commit(&a_empty[slot]);     // this slot of the plane ring may be rewritten
-                        if (++slot == X32T_SLOTS) { slot = 0; aphase_ring ^= 1; }
+                        tc::umma_commit(&a_empty[h]);        // this half's plane slot may be rewritten
                     }
                     tc::umma_commit(&b_empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -199,11 +215,11 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const int grp = (warp - (NUM_EPI_WARPS + 2)) >> 2;
         const int r = quarter * 32 + lane;
         const uint32_t sw = (uint32_t)(r & 7);
-        const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::A_COL0;
+        const uint32_t ta = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::A_COL0 + grp * X32T_SLOT_COLS;
         const uint32_t raw_row = tc::smem_u32(raw) + r * 128;
-        uint32_t slot = grp, rphase = 0;
+        uint32_t slot = grp, rphase = 0, kbc = 0;
         for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            for (int kb = 0; kb < nkb; ++kb) {
+            for (int kb = 0; kb < nkb; ++kb, ++kbc) {
                 tc::mbar_wait(&raw_full[slot], rphase);
                 const uint32_t src = raw_row + slot * X32_RAW_BYTES;
                 float4 x[8];
@@ -215,10 +231,9 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     split3_pair(x[c].x, x[c].y, ph[2 * c], pm[2 * c], pl[2 * c]);
                     split3_pair(x[c].z, x[c].w, ph[2 * c + 1], pm[2 * c + 1], pl[2 * c + 1]);
                 }
-                // the MMAs that read this slot one round ago must have retired
-                tc::mbar_wait(&a_empty[slot], rphase ^ 1);
+                // the MMAs that read this half's planes in the previous k-block must have retired
+                tc::mbar_wait(&a_empty[grp], (kbc & 1) ^ 1);
                 tc::tc_fence_after();
-                const uint32_t ta = lane_base + slot * X32T_SLOT_COLS;
                 tmem_st16(ta, ph);
                 tmem_st16(ta + 16, pm);
                 tmem_st16(ta + 32, pl);
@@ -227,7 +242,7 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 __syncwarp();
                 if (lane == 0) {
                     tc::mbar_arrive(&raw_empty[slot]);
-                    tc::mbar_arrive(&a_full[slot]);
+                    tc::mbar_arrive(&a_full[grp]);
                 }
                 slot += 2;
                 if (slot >= X32T_SLOTS) { slot -= X32T_SLOTS; rphase ^= 1; }
@@ -252,6 +267,24 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
             tc::mbar_wait(&tmem_full_bar[ab], aphase);
             tc::tc_fence_after();
+            {   // main += small for this thread's row and column half, then hand the small accumulator to the next tile
+                const uint32_t tm = tmem_base + ((uint32_t)(quarter * 32) << 16) + ab * BN + chalf * (BN / 2);
+                const uint32_t ts = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::SMALL_COL0 + chalf * (BN / 2);
+#pragma unroll
+                for (int c = 0; c < BN / 2; c += 32) {
+                    uint32_t v[32], w[32];
+                    tc::tmem_ld32(tm + c, v);
+                    tc::tmem_ld32(ts + c, w);
+                    tc::tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                    tmem_st32(tm + c, v);
+                }
+                tmem_st_wait();
+                tc::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(small_empty_bar);
+            }
             epilogue_tile<BN, HEAD, true>(ep, M, N, mb, nb, 0, false, tmem_base, ab, quarter, chalf, lane, head_ws,
                                           head_part + (it & 1) * 128 * HEAD_MAX_N);
             tc::tc_fence_before();

@@ -76,3 +76,51 @@ def test_optin_step_variants_match_the_oracle(switch):
 @pytest.mark.gpu
 def test_default_path_in_a_child_process_matches_too():
     run_child({})
+
+
+# ---- inference variants of the tcgen05 path (csrc/poz_tc3_x32t_kernel.cuh and its predecessors) ----------------
+INFER_CHILD = r'''
+import sys
+sys.path.insert(0, sys.argv[1])
+sys.path.insert(0, sys.argv[1] + "/tests")
+import numpy as np, torch
+from oracle import mlp_oracle as orc
+from oracle.detgen import det_params, det_normalish
+from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+
+for sizes, last_act, batch in [([784, 256, 128, 10], "softmax", 4096 + 77), ([100, 200, 72, 5], "sigmoid", 2048 + 300)]:
+    nl = len(sizes) - 1
+    algos = []
+    for l in range(nl):
+        algos += ["linear", last_act if l == nl - 1 else "relu"]
+    params = det_params(sizes, True, 31)
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+    for l in range(nl):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    x = det_normalish((batch, sizes[0]), 32)
+    out = eng.forward(torch.tensor(x, dtype=torch.float32, device="cuda:0")).cpu().numpy().astype(np.float64)
+    ref = orc.forward(orc.parse_stack(algos), params, x)[0][-1].reshape(batch, -1)
+    # the contract's float32 tolerance, on every output: |out - ref| <= 1e-5 * |ref| (+ 1e-7 absolute)
+    bad = np.abs(out - ref) > 1e-5 * np.abs(ref) + 1e-7
+    assert not bad.any(), (sizes, int(bad.sum()), float((np.abs(out - ref) / np.abs(ref)).max()))
+    assert (out.argmax(1) == ref.argmax(1)).mean() > 0.9995
+    eng.close()
+print("CHILD-OK")
+'''
+
+
+def run_infer_child(env_extra):
+    env = dict(os.environ)
+    env.update(env_extra)
+    r = subprocess.run([sys.executable, "-c", INFER_CHILD, ROOT], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "CHILD-OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("env", [{}, {"POZ_TC3_X32_TMEM": "0"}, {"POZ_TC3_F32_CHAIN": "0"}, {"POZ_TC3_FUSE_HEAD": "0"},
+                                 {"POZ_TC3_X32": "0"}, {"POZ_TC3_MIN_BATCH": "1000000000"}],
+                         ids=["default", "planes-in-smem", "plane-hand-over", "separate-head", "pre-split-input", "simt"])
+def test_inference_variants_within_the_float32_contract(env):
+    """Every variant of the large-batch inference path (and the SIMT kernels) keeps every output within rtol 1e-5
+    of the float64 oracle -- the tolerance BASELINE.json's north_star states for float32."""
+    run_infer_child(env)

@@ -77,6 +77,18 @@ __device__ __forceinline__ float4 lds128(uint32_t saddr) {
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr) : "memory");
     return v;
 }
+// Wait of a warp that has nothing else to do for microseconds (the epilogue warps during a tile's main loop, the X
+// producer when its ring is full): sleep between polls so that the polling does not take issue slots from the
+// converters -- ncu counted 29 % of the kernel's executed instructions in the epilogue warps' poll loop.
+__device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity) {
+    for (uint32_t spins = 0; !tc::mbar_try_wait(bar, parity); ++spins) {
+        __nanosleep(spins < 16 ? 40 : 200);
+        if (spins > 20u * 1000u * 1000u) {
+            printf("poz tc3 x32t: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+            __trap();
+        }
+    }
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 template <int BN, int NSTAGES, bool HEAD>
@@ -130,7 +142,7 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
                 const long long mb = t / tiles_n;
                 for (int hb = 0; hb < 2 * nkb; ++hb) {
-                    tc::mbar_wait(&raw_empty[slot], rphase ^ 1);
+                    mbar_wait_idle(&raw_empty[slot], rphase ^ 1);
                     tc::mbar_expect_tx(&raw_full[slot], X32_RAW_BYTES);
                     tma_load_2d_f32(&map_x, &raw_full[slot], raw + slot * X32_RAW_BYTES, 32 * hb, (int)(mb * BM));
                     if (++slot == X32T_SLOTS) { slot = 0; rphase ^= 1; }
@@ -265,7 +277,7 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const int nb = (int)(t % tiles_n);
             const long long mb = t / tiles_n;
             const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
-            tc::mbar_wait(&tmem_full_bar[ab], aphase);
+            mbar_wait_idle(&tmem_full_bar[ab], aphase);
             tc::tc_fence_after();
             {   // main += small for this thread's row and column half, then hand the small accumulator to the next tile
                 const uint32_t tm = tmem_base + ((uint32_t)(quarter * 32) << 16) + ab * BN + chalf * (BN / 2);

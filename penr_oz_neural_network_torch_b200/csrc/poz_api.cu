@@ -2024,11 +2024,24 @@ static int feed_reserve(poz_ctx* c, long long batch) {
 // cost of the step that last used `slot`: waits for that step only
 static int feed_read_cost(poz_ctx* c, int slot, double* out) {
     poz_ctx::HostFeed& f = c->feed;
+    // The pinned word is preset to a NaN payload no kernel produces and polled until the copy overwrites it: the
+    // wait costs no driver call (the host side of this entry point is what bounds it on a slow host).  If nothing
+    // arrives for a long time, fall back to a stream synchronise, which also surfaces a launch failure.
+    static const unsigned long long SENTINEL = 0x7ff8dead0badc0deULL;
+    volatile unsigned long long* word = reinterpret_cast<volatile unsigned long long*>(f.cost_pinned);
+    *word = SENTINEL;
     POZ_CUDA(cudaStreamWaitEvent(f.read_stream, f.consumed[slot], 0));
     POZ_CUDA(cudaMemcpyAsync(f.cost_pinned, c->cost_ring + (f.epoch_of[slot] % c->cost_cap), sizeof(double),
                              cudaMemcpyDeviceToHost, f.read_stream));
-    POZ_CUDA(cudaStreamSynchronize(f.read_stream));
-    *out = *f.cost_pinned;
+    for (unsigned long long spins = 0; *word == SENTINEL; ++spins) {
+        if (spins > 200ull * 1000ull * 1000ull) {
+            POZ_CUDA(cudaStreamSynchronize(f.read_stream));
+            break;
+        }
+    }
+    unsigned long long bits = *word;
+    if (bits == SENTINEL) POZ_FAIL("poz_train_step_host: the step's cost did not arrive");
+    memcpy(out, &bits, sizeof(double));
     return 0;
 }
 

@@ -246,9 +246,12 @@ def run_c2(args, world, rank, local):
     # exposed to host noise: three back-to-back timed regions, median reported.
     e2e_runs = []
     last = 0.0
-    eng.train_begin(optimizer="adam", epochs=args.warmup + 3 * e2e_steps + 8, **HP)
+    # (the host side needs its own warm-up: of three back-to-back regions the first was 10-20 % slower than the third
+    # on every box, so one untimed region of the same length precedes them)
+    host_warm = max(args.warmup, e2e_steps)
+    eng.train_begin(optimizer="adam", epochs=host_warm + 3 * e2e_steps + 8, **HP)
     k = 0
-    for i in range(args.warmup):
+    for i in range(host_warm):
         eng.train_step_host(hx[k % n_host], hy[k % n_host]); k += 1
     for rep in range(3):
         eng.train_host_flush()

@@ -82,7 +82,7 @@ __device__ __forceinline__ float4 lds128(uint32_t saddr) {
 // converters -- ncu counted 29 % of the kernel's executed instructions in the epilogue warps' poll loop.
 __device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity) {
     for (uint32_t spins = 0; !tc::mbar_try_wait(bar, parity); ++spins) {
-        __nanosleep(spins < 16 ? 40 : 200);
+        __nanosleep(spins < 64 ? 20 : 100);
         if (spins > 20u * 1000u * 1000u) {
             printf("poz tc3 x32t: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
             __trap();

@@ -240,7 +240,8 @@ int poz_tc3_gemm(int device, int variant, const float* a, const float* b, long l
  * zero, so nothing is cleared.  Calls that run at the same time on one GPU overwrite each other's
  * activations: serialise them.  The first call on a device looks up the array's device address; make
  * that first call before starting any stream capture on that device.  The function calls no
- * cudaMalloc / cudaFree and no allocating library routine. */
+ * cudaMalloc / cudaFree and no allocating library routine.  `stream` must be a stream of `device`
+ * (or NULL); the caller's current device is the same after the call as before it. */
 #define POZ_NOALLOC_SCRATCH_BYTES (8ll << 20)
 #define POZ_NOALLOC_MAX_WIDTH 4096
 int poz_forward_noalloc(int device, int n_linear, const int* sizes, const int* act_codes,

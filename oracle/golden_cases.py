@@ -90,3 +90,12 @@ NET_CASES = [
     _n("emb_dropout", [9, 4, 12, 10, 9], ["embedding", "linear", "batchnorm", "relu", "softmax"], None, "random", 12,
        37, tokens=3, dropout=0.25),
 ]
+
+
+# Dropout in distribution (neural_net_model.py:393-395): the reference's cost and mean |weight gradient| of one
+# step over many F.dropout seeds.  The device draws its masks from Philox, so single steps cannot agree; the
+# means over the same number of seeds must, within the standard error.
+DROPSTAT_CASES = [
+    dict(name="relu_relu_softmax_p20", sizes=[64, 48, 32, 10], algos=["relu", "relu", "softmax"], optimizer=None,
+         bias="random", batch=512, salt=41, dropout=0.2, seeds=64),
+]

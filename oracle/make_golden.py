@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, "/root/reference")
 
 from oracle.detgen import det_labels, det_normalish, det_params, det_uniform  # noqa: E402
-from oracle.golden_cases import STEP_CASES, TRAIN_API_CASES, INIT_CASES, NET_CASES  # noqa: E402
+from oracle.golden_cases import STEP_CASES, TRAIN_API_CASES, INIT_CASES, NET_CASES, DROPSTAT_CASES  # noqa: E402
 
 import neural_net_model as ref  # noqa: E402  (the reference, unmodified)
 
@@ -345,6 +345,27 @@ def run_net_case(case):
     return arrays, meta
 
 
+def run_dropstat_case(case):
+    """Cost and mean |dcost/dW| of ONE step of the stock reference (its own F.dropout, neural_net_model.py:395)
+    for `seeds` different torch seeds; parameters are not updated between the draws."""
+    m = build_ref_model(case)
+    x = torch.tensor(det_normalish((case["batch"], case["sizes"][0]), case["salt"] + 3), dtype=torch.float64)
+    target = make_target(case, m.algos[-1] == "softmax")
+    costs, gabs = [], []
+    for seed in range(case["seeds"]):
+        torch.manual_seed(1000 + seed)
+        for q in m.params:
+            q.requires_grad_()
+            q.grad = None
+        _, cost = m._forward(x, target, case["dropout"])
+        cost.backward()
+        costs.append(cost.item())
+        gabs.append([w.grad.abs().mean().item() for w in m.weights])
+    meta = dict(case)
+    meta["expanded_algos"] = list(m.algos)
+    return {"cost": np.asarray(costs), "grad_abs_mean": np.asarray(gabs)}, meta
+
+
 def save(name, arrays, meta):
     path = os.path.join(OUT, name + ".npz")
     np.savez_compressed(path, __meta__=np.asarray(json.dumps(meta)), **arrays)
@@ -371,6 +392,9 @@ def main():
     for case in INIT_CASES:
         arrays, meta = run_init_case(case)
         save("init_" + case["name"], arrays, meta)
+    for case in DROPSTAT_CASES:
+        arrays, meta = run_dropstat_case(case)
+        save("dropstat_" + case["name"], arrays, meta)
 
 
 if __name__ == "__main__":

@@ -939,6 +939,9 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         if constexpr (std::is_same<T, float>::value) {
             if (tc0 && l == 0) {
                 const int K = c->sizes[0], N = c->sizes[1];
+                // every step re-splits W0: the previous step's update changed it, and a step captured into a
+                // graph must record the split whatever the host-side freshness flags said at capture time
+                if (c->wp_fresh.size() == (size_t)c->nl) c->wp_fresh[0] = 0;
                 POZ_TRY(tc3_refresh_weights(c, stream, 1));
                 {
                     ProfScope ps(c, "split_x", stream);
@@ -1948,6 +1951,7 @@ int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const 
         POZ_CUDA(cudaGraphLaunch(g->exec, s));
         count_launch(g->launches);
         c->epoch_host += 1;
+        c->wp_stale = true;                 // the replayed update changed the parameters under the weight planes
         return 0;
     }
     if (!g) {
@@ -1961,6 +1965,7 @@ int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const 
     }
     // second sighting: capture, instantiate, launch
     const long long before = poz_launch_count();
+    const long long epoch_before = c->epoch_host;
     POZ_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
     int rc = poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, nullptr, 0, stream);
     if (!rc) rc = poz_train_apply(c, stream);
@@ -1971,7 +1976,7 @@ int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const 
         if (!rc) set_error(std::string("poz_train_step: graph capture failed: ") + cudaGetErrorString(ce));
         c->graphs_enabled = false;          // fall back to plain launches for this context
         cudaGetLastError();
-        c->epoch_host -= 1;                 // the captured (never executed) attempt does not count
+        c->epoch_host = epoch_before;       // the captured (never executed) attempt does not count
         if (rc) return rc;
         POZ_TRY(poz_train_backward(c, x_dev, target_dev, row_idx_dev, batch, nullptr, 0, stream));
         return poz_train_apply(c, stream);
@@ -1983,6 +1988,7 @@ int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const 
     g->exec = exec;
     g->launches = (int)(poz_launch_count() - before);
     POZ_CUDA(cudaGraphLaunch(exec, s));
+    c->wp_stale = true;
     return 0;
 }
 
@@ -2110,6 +2116,9 @@ int poz_grad_buffer(poz_ctx* c, void** dev_ptr, long long* n_elems, int* dtype_c
 int poz_grad_layer(poz_ctx* c, int layer, void** dev_ptr, long long* n_elems, void* stream) {
     POZ_TRY(check_layer(c, layer, "poz_grad_layer"));
     if (!c->grads_pending) POZ_FAIL("poz_grad_layer: run poz_train_backward first");
+    // per-layer buckets cover the Linear [W;b] images only: an embedding table, batchnorm gain/bias and the batch
+    // statistics of a batchnorm would stay per-shard, so data-parallel training of such stacks is refused
+    if (c->general) POZ_FAIL("poz_grad_layer: embedding / flatten / batchnorm stacks are not data-parallel (Linear + activation stacks only)");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     POZ_CUDA(cudaStreamWaitEvent(s, c->grad_ready[layer], 0));
     const long long n = ((long long)c->kin[layer] + c->has_bias) * c->sizes[layer + 1];

@@ -150,7 +150,14 @@ extern "C" int poz_forward_noalloc(int device, int n_linear, const int* sizes, c
             POZ_FAIL("poz_forward_noalloc: softmax is supported as the last activation only");
     }
     if (batch == 0) return 0;
-    POZ_CUDA(cudaSetDevice(device));
+    // the caller's current device is put back on every way out (the stream must belong to `device`)
+    struct DeviceGuard {
+        int prev = -1;
+        ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    } guard;
+    POZ_CUDA(cudaGetDevice(&guard.prev));
+    if (guard.prev == device) guard.prev = -1;
+    else POZ_CUDA(cudaSetDevice(device));
     float* scratch = nullptr;
     POZ_TRY(scratch_for_device(device, &scratch));
     float* half[2] = {scratch, scratch + HALF_ELEMS};

@@ -37,6 +37,11 @@ class DataParallelTrainer:
     """Wraps a ``DeviceMLP`` (or anything with its train_* / grad_layer interface)."""
 
     def __init__(self, engine, group=None, comm_stream=None):
+        if getattr(engine, "general", False):
+            # the per-layer buckets are the Linear [W;b] images; an embedding table, batchnorm gain / bias and a
+            # batchnorm's batch statistics would stay per shard and the ranks would drift apart
+            raise ValueError("data-parallel training covers Linear + activation stacks; embedding / flatten / "
+                             "batchnorm stacks are not sharded")
         self.eng = engine
         self.group = group
         self.world = dist.get_world_size(group)

@@ -502,15 +502,27 @@ def forward_noalloc(sizes, acts, weights, biases, x: torch.Tensor, out: torch.Te
     """
     lib = nat.lib()
     n = len(acts)
-    dev = x.device
+    sizes = [int(v) for v in sizes]
+    if not x.is_cuda:
+        raise ValueError("forward_noalloc takes CUDA tensors")
+    dev = x.device if x.device.index is not None else torch.device("cuda", torch.cuda.current_device())
+    if len(sizes) != n + 1 or len(weights) != n or (biases is not None and len(biases) != n):
+        raise ValueError("forward_noalloc: sizes, acts, weights and biases do not describe the same stack")
     for t in list(weights) + [b for b in (biases or []) if b is not None] + [x, out]:
-        if t.dtype != torch.float32 or t.device != dev or not t.is_contiguous():
+        if t.dtype != torch.float32 or not t.is_cuda or t.get_device() != dev.index or not t.is_contiguous():
             raise ValueError("forward_noalloc takes contiguous float32 tensors on one CUDA device")
+    for l in range(n):
+        if tuple(weights[l].shape) != (sizes[l], sizes[l + 1]):
+            raise ValueError(f"forward_noalloc: weights[{l}] must be [{sizes[l]}, {sizes[l + 1]}]")
+        if biases is not None and biases[l] is not None and tuple(biases[l].shape) != (sizes[l + 1],):
+            raise ValueError(f"forward_noalloc: biases[{l}] must be [{sizes[l + 1]}]")
+    if x.ndim != 2 or x.shape[1] != sizes[0] or tuple(out.shape) != (x.shape[0], sizes[-1]):
+        raise ValueError(f"forward_noalloc: x must be [batch, {sizes[0]}] and out [batch, {sizes[-1]}]")
     wp = (C.c_void_p * n)(*[w.data_ptr() for w in weights])
     bp = None
     if biases is not None:
         bp = (C.c_void_p * n)(*[None if b is None else b.data_ptr() for b in biases])
-    nat.check(lib.poz_forward_noalloc(dev.index, n, _arr(C.c_int, [int(v) for v in sizes]),
+    nat.check(lib.poz_forward_noalloc(dev.index, n, _arr(C.c_int, sizes),
                                       _arr(C.c_int, [nat.ACT_CODES[a] for a in acts]), wp, bp,
                                       _ptr(x), x.shape[0], _ptr(out), _stream_ptr(dev)))
     return out

@@ -426,14 +426,23 @@ class NeuralNetworkModel(MultiLayerPerceptron):
     def _inputs_to_device(self, eng: DeviceMLP, x: Tensor) -> Tensor:
         """float64 host tensor (features, or token indices for an embedding head) -> device batch."""
         if eng.embedding:
-            return x.long().to(torch.int32).to(eng.device).contiguous()      # :68 `input_tensor.long()`
+            idx = x.long()                                                   # :68 `input_tensor.long()`
+            if idx.numel() and (int(idx.min()) < -eng.embedding[0] or int(idx.max()) >= eng.embedding[0]):
+                raise IndexError(f"index out of range for an embedding of {eng.embedding[0]} rows")   # as W[idx] raises
+            if idx.numel() and int(idx.min()) < 0:
+                idx = idx % eng.embedding[0]                                 # negative indices wrap, as in W[idx]
+            return idx.to(torch.int32).to(eng.device).contiguous()
         return x.to(eng.tdtype).to(eng.device).contiguous()
 
     # ------------------------------------------------------------------ forward (:371-408)
     def _targets_to_device(self, eng: DeviceMLP, target, batched: bool):
         if self.stack.loss == "ce":                                  # :401-402
             labels = [t[0] for t in target] if batched else [target[0]]
-            return torch.tensor(labels, dtype=torch.int64).to(torch.int32).to(eng.device)
+            lab = torch.tensor(labels, dtype=torch.int64)
+            # F.cross_entropy raises on a class index outside [0, C) (its ignore_index -100 is not used here)
+            if lab.numel() and (int(lab.min()) < 0 or int(lab.max()) >= eng.out_features):
+                raise IndexError(f"Target {int(lab.max()) if int(lab.max()) >= eng.out_features else int(lab.min())} is out of bounds.")
+            return lab.to(torch.int32).to(eng.device)
         t = torch.tensor(target, dtype=torch.float64)                # :405
         if not batched:
             t = t.unsqueeze(0)

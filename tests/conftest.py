@@ -47,6 +47,16 @@ def check_against(arrays, key, value, rtol, atol):
                                atol=atol * value.size, err_msg=key + "__sum")
 
 
+def check_means_within_standard_error(got, want, what, sigmas=3.0):
+    """Two samples of one statistic (e.g. 64 dropout seeds each): |mean difference| <= sigmas * combined
+    standard error, and the spreads within a factor 1.6 of each other."""
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    se = np.sqrt(got.var(ddof=1) / got.size + want.var(ddof=1) / want.size)
+    assert abs(got.mean() - want.mean()) <= sigmas * se, (what, got.mean(), want.mean(), se)
+    ratio = got.std(ddof=1) / want.std(ddof=1)
+    assert 1 / 1.6 < ratio < 1.6, (what, "spread", got.std(ddof=1), want.std(ddof=1))
+
+
 @pytest.fixture
 def workdir(tmp_path, monkeypatch):
     """The model class persists under ./models relative to cwd (as the reference does)."""

@@ -6,7 +6,7 @@ tolerance is rtol 1e-11 (atol 1e-13).
 import numpy as np
 import pytest
 
-from conftest import check_against, golden_names, load_golden
+from conftest import check_against, check_means_within_standard_error, golden_names, load_golden
 from oracle import mlp_oracle as orc
 from oracle.detgen import det_labels, det_normalish, det_params, det_uniform
 
@@ -211,3 +211,34 @@ def test_torch_cpu_port_general_stacks_match_reference(name):
     np.testing.assert_allclose(costs, arrays["costs"], rtol=1e-10)
     for i, q in enumerate(m.params):
         check_against(arrays, f"param{i}", q.detach().numpy(), 1e-8, 1e-9)
+
+
+@pytest.mark.parametrize("name", golden_names("dropstat_"))
+def test_oracle_dropout_statistics_match_reference(name):
+    """Dropout in distribution: the reference's cost and mean |dcost/dW| over 64 F.dropout seeds
+    (tests/golden/dropstat_*.npz) against the oracle's over 64 numpy-drawn keep masks placed on the same
+    hidden entries -- the means must agree within 3 standard errors (the same check the device's Philox
+    masks get in tests/test_gpu_round2.py)."""
+    arrays, meta = load_golden(name)
+    stack, params, x, target = case_inputs(meta)
+    p, n = meta["dropout"], meta["seeds"]
+    algos = meta["expanded_algos"]
+    hidden = [i for i in range(len(algos)) if 0 < i < len(algos) - 1]
+    widths = {}
+    for spec, (w, _) in zip(stack.linears, orc.split_params(stack, params)):
+        widths[spec.z_index] = w.shape[1]
+        if spec.a_index is not None:
+            widths[spec.a_index] = w.shape[1]
+    rng = np.random.default_rng(7)
+    costs, gabs = [], []
+    for _ in range(n):
+        masks = {i: (rng.random((meta["batch"], widths[i])) < 1.0 - p).astype(np.float64) for i in hidden}
+        _, cost, _, grads, _ = orc.train_step(stack, params, x, target, lr=0.0, optimizer="sgd",
+                                              dropout_rate=p, masks=masks)
+        costs.append(cost)
+        per = 2 if meta["bias"] else 1
+        gabs.append([np.abs(grads[per * l]).mean() for l in range(len(stack.linears))])
+    check_means_within_standard_error(np.asarray(costs), arrays["cost"], "cost")
+    gabs = np.asarray(gabs)
+    for l in range(gabs.shape[1]):
+        check_means_within_standard_error(gabs[:, l], arrays["grad_abs_mean"][:, l], f"mean|dW{l}|")

@@ -10,6 +10,7 @@ import numpy as np
 import pytest
 import torch
 
+from oracle import mlp_oracle as orc
 from oracle.detgen import det_normalish, det_params
 
 pytestmark = pytest.mark.gpu
@@ -37,7 +38,13 @@ def _pair(sizes, algos, batch, salt, has_bias=True):
     got = forward_noalloc(sizes, spec.acts, ws, bs, x, out)
     torch.cuda.synchronize()
     eng.close()
-    return want.cpu().numpy().astype(np.float64), got.cpu().numpy().astype(np.float64)
+    # and directly against the float64 oracle (neural_net_model.py:384-396 restated), not only against the
+    # library's other entry point
+    ref = orc.forward(orc.parse_stack(algos), params, x.cpu().numpy().astype(np.float64))[0][-1].reshape(batch, -1)
+    res = got.cpu().numpy().astype(np.float64)
+    bad = np.abs(res - ref) > 1e-5 * np.abs(ref) + 1e-7
+    assert not bad.any(), (sizes, int(bad.sum()))
+    return want.cpu().numpy().astype(np.float64), res
 
 
 def _check(want, got):

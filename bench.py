@@ -1,10 +1,18 @@
 #!/usr/bin/env python
 """Benchmark of the B200-native NeuralNetworkModel hot path (contract: see DESIGN.md, section Measurement).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3] [--impl native|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5|emb] [--impl native|reference]
 
-Default workload = BASELINE.json configs[1]: 784-256-128-10 MLP, relu/relu/softmax + cross-entropy,
-Adam, L2 0.001, batch 1024, fp32, one train step (forward + loss + backward + update) per "step".
+Default workload
+  * one process on a one-GPU box: BASELINE.json configs[1] (c2) -- 784-256-128-10 MLP, relu/relu/softmax +
+    cross-entropy, Adam, L2 0.001, batch 1024, fp32, one train step (forward + loss + backward + update) per
+    "step"; the same line carries configs[2] (batched inference, 262,144 rows) and configs[3] (4096x4 bf16 train
+    step, batch 65,536) under "secondary".
+  * a leg of the multi-GPU scaling curve -- launched by torch.distributed.run (WORLD_SIZE in the environment), or
+    any run on a box that shows more than one GPU: BASELINE.json configs[4] (c5) -- the 4096x4 bf16 stack, global
+    batch 524,288 SHARDED over the N ranks, one NCCL all-reduce per layer overlapped with the backward, strong
+    scaling.  Before the timed region a reduced stack is trained sharded and unsharded and compared ("dp_check").
+  --workload overrides either.
 Prints ONE JSON line (rank 0).  `value` = samples/s with inputs resident in HBM; `e2e` = the same
 through the host-buffer API (pinned host batch -> device every step, cost read back every step).
 """
@@ -49,6 +57,8 @@ def init_params(sizes, seed=0):
 # profiles/ncu/ (r01_c2_simt_full_raw_v3.csv, r01_c4_tc_fwd_full_raw.csv); null where no capture exists.
 # dram__bytes_read.sum + dram__bytes_write.sum of the two launches of one 262,144-row inference pass (ncu --set full)
 NCU_TRAFFIC_C3 = {262144: 1_348_500_000}
+NCU_TRAFFIC_SOURCE = "ncu --set full, profiles/ncu/r01_c2_simt_full_raw_v3.csv"
+TC3_MMAS_PER_PRODUCT = 6
 NCU_TRAFFIC = {"fwd_l0": 4_344_064, "bwd_w_l0": 4_307_712, "fwd_l1": 1_508_608, "bwd_w_l1": 1_620_736,
                "bwd_w_l2": 613_376, "bwd_x_l1": 1_769_728, "tc_fwd": 1_204_000_000}
 
@@ -146,6 +156,17 @@ def max_over_ranks(ms, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
     return ms
+
+
+def all_ranks(v, world):
+    """-> list of every rank's value (rank order)."""
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [float(q.item()) for q in out]
+    return [float(v)]
 
 
 def make_engine(local):
@@ -294,7 +315,7 @@ def run_c2(args, world, rank, local):
             rows = rng.standard_normal((2048, 784)).astype(np.float32)
             data = [(rows[i].tolist(), [int(rng.integers(0, 10))]) for i in range(2048)]
             took = {}
-            for ep in (100, 200, 1200):                     # the first call also pays one-off set-up
+            for ep in (100, 200, 4200):                     # the first call also pays one-off set-up
                 mdl = NeuralNetworkModel("bench-class-api", SIZES, activation_algos=["relu", "relu", "softmax"])
                 mdl.training_buffer_size = len(data)        # (the reference buffers num_params samples before it trains)
                 t0 = time.perf_counter()
@@ -302,9 +323,10 @@ def run_c2(args, world, rank, local):
                           learning_rate=HP["learning_rate"], decay_rate=0.999)
                 took[ep] = time.perf_counter() - t0
                 assert np.isfinite(mdl.progress[-1]["cost"])
-            us = (took[1200] - took[200]) / 1000 * 1e6
+            us = (took[4200] - took[200]) / 4000 * 1e6
             class_api = {"us_per_epoch": round(us, 1), "samples_per_s": round(batch / (us * 1e-6)),
-                         "note": "NeuralNetworkModel.train(batch_size=1024), (1200-epoch call - 200-epoch call) / 1000"}
+                         "note": "NeuralNetworkModel.train(batch_size=1024), (4200-epoch call - 200-epoch call) / 4000; the "
+                                 "fixed part of a call (two 11 MB JSON saves, statistics) is ~0.3 s and varies by tens of ms"}
         finally:
             os.chdir(cwd)
 
@@ -325,21 +347,33 @@ def run_c2(args, world, rank, local):
         per_launch_s = prof[top]["ms"] / prof[top]["launches"] * 1e-3
         nbytes, flops = kernel_work(top, batch)
         gbs = nbytes / per_launch_s / 1e9
-        roof = {"bound": "hbm", "kernel": top, "achieved": round(gbs, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
-                "frac": round(gbs / pk["hbm_gbs"], 4), "traffic": NCU_TRAFFIC.get(top),
-                "traffic_source": "ncu --set full, profiles/ncu/r01_c2_simt_full_raw_v3.csv" if top in NCU_TRAFFIC else None,
-                "peak_source": pk["source"],
-                "us_per_launch": round(per_launch_s * 1e6, 2), "share_of_step": round(prof[top]["ms"] / tot, 3),
-                "algorithmic_bytes_per_launch": nbytes,
-                "fp32_fma": {"achieved_tflops": round(flops / per_launch_s / 1e12, 2), "nominal_peak_tflops": 74.4,
-                             "frac": round(flops / per_launch_s / 74.4e12, 4),
-                             "note": "fp32 FMA rate of the kernel including launch, prologue and the cluster "
-                                     "reduction; inside its main loop the FMA pipe is ~46 % busy (per-CTA trace, "
-                                     "DESIGN.md section 4g)"},
-                "step": {"algorithmic_bytes": C2_STEP_BYTES, "flops": C2_STEP_FLOPS,
-                         "hbm_frac": round(C2_STEP_BYTES / (ms / args.steps * 1e-3) / 1e9 / pk["hbm_gbs"], 4),
-                         "fp32_fma_frac": round(C2_STEP_FLOPS / (ms / args.steps * 1e-3) / 74.4e12, 4)},
-                "kernels_us": {t: round(v["ms"] / v["launches"] * 1e3, 2) for t, v in prof.items()}}
+        step_s = ms / args.steps * 1e-3
+        on_tensor = top.startswith("tc3_") or top.startswith("tcs_")
+        hbm = {"achieved": round(gbs, 1), "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(gbs / pk["hbm_gbs"], 4),
+               "algorithmic_bytes_per_launch": nbytes, "traffic": NCU_TRAFFIC.get(top),
+               "traffic_source": NCU_TRAFFIC_SOURCE if top in NCU_TRAFFIC else None}
+        if on_tensor:
+            # fp32-grade product = TC3_MMAS_PER_PRODUCT bf16 MMAs (hi/mid/lo planes): the tensor pipe is the binding bound
+            tf = TC3_MMAS_PER_PRODUCT * flops / per_launch_s / 1e12
+            roof = {"bound": "tensor", "kernel": top, "achieved": round(tf, 2), "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                    "frac": round(tf / pk["bf16_tflops"], 4),
+                    "note": f"bf16 MMA rate: {TC3_MMAS_PER_PRODUCT} plane products per fp32-grade product; burst peak (kernel timed alone)"}
+        else:
+            # AI of the contraction is ~80-150 FLOP/B, far beyond the fp32 ridge (~11 FLOP/B): the FMA pipe, not HBM, is
+            # the ceiling this kernel can reach.  MEASURED_PEAKS.json holds no fp32 figure: nominal peak stated.
+            tf = flops / per_launch_s / 1e12
+            roof = {"bound": "fp32_fma", "kernel": top, "achieved": round(tf, 2), "peak": 74.4, "unit": "TFLOP/s",
+                    "frac": round(tf / 74.4, 4),
+                    "peak_note": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json has no fp32 entry); "
+                                 "measured FFMA rate 70 TFLOP/s (scripts/micro/mma_rate.cu)"}
+        roof.update({"traffic": hbm["traffic"], "peak_source": pk["source"], "hbm": hbm,
+                     "us_per_launch": round(per_launch_s * 1e6, 2), "share_of_step": round(prof[top]["ms"] / tot, 3),
+                     "timing": "CUDA events around each eager launch on the launching stream (poz_profile_begin/end); "
+                               "each figure carries a few us of launch + event cost",
+                     "step": {"algorithmic_bytes": C2_STEP_BYTES, "flops": C2_STEP_FLOPS,
+                              "hbm_frac": round(C2_STEP_BYTES / step_s / 1e9 / pk["hbm_gbs"], 4),
+                              "fp32_fma_frac": round(C2_STEP_FLOPS / step_s / 74.4e12, 4)},
+                     "kernels_us": {t: round(v["ms"] / v["launches"] * 1e3, 2) for t, v in prof.items()}})
     eng.close()
     return dict(metric="train samples/s (fwd+bwd+step)", unit="samples/s",
                 value=world * batch * args.steps / (ms * 1e-3), ms_per_step=ms / args.steps,
@@ -354,14 +388,10 @@ def run_c2(args, world, rank, local):
                      "h2d_copy_us_per_step": round(h2d_us, 1),
                      "h2d_gbs": round(batch * 784 * 4 / (h2d_us * 1e-6) / 1e9, 1)},
                 gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
-                config={"workload": "c2: MLP 784-256-128-10 relu/relu/softmax + cross-entropy, Adam, L2 1e-3, "
-                                    "batch 1024, fp32 train step", "batch_per_gpu": batch,
-                        "global_batch": batch * world, "parallelism": f"replicas x{world}" if world > 1 else "single",
-                        "dropout": 0.0,
-                        "with_dropout_0.2": {"ms_per_step": round(ms_drop / args.steps, 5),
-                                             "value": round(world * batch * args.steps / (ms_drop * 1e-3))},
-                        "l2_flush": "inputs cycle through a 205 MB pool (> 126 MB L2); parameters "
-                                                    "stay cache-resident as in real training"})
+                extras={"with_dropout_0.2": {"ms_per_step": round(ms_drop / args.steps, 5),
+                                             "value": round(world * batch * args.steps / (ms_drop * 1e-3)),
+                                             "note": "the same step at the reference's default dropout rate (Philox masks in "
+                                                     "the epilogues, regenerated in the backward)"}})
 
 
 def run_c3(args, world, rank, local):
@@ -445,10 +475,7 @@ def run_c3(args, world, rank, local):
                      "h2d_bytes_per_step": batch * 784 * 4, "d2h_bytes_per_step": batch * 10 * 4,
                      "ms_per_step": e2e_ms / e2e_steps},
                 gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
-                config={"workload": f"c3: batched inference 784-256-128-10, batch {batch}, fp32",
-                        "batch_per_gpu": batch, "global_batch": batch * world,
-                        "parallelism": f"replicas x{world}" if world > 1 else "single",
-                        "l2_flush": f"inputs cycle through a {n_pool * batch * 784 * 4 / 1e6:.0f} MB pool (> L2)"})
+                extras={"pool_mb": round(n_pool * batch * 784 * 4 / 1e6)})
 
 
 WIDE_SIZES = [4096] * 5
@@ -463,71 +490,217 @@ def wide_kernel_flops(tag, batch):
     return 0.0
 
 
+def wide_params(width, n_layers, seed=0):
+    """He-scaled normal weights, zero biases: the same on every rank."""
+    rng = np.random.default_rng(seed)
+    return [(rng.standard_normal((width, width)) * np.sqrt(2.0 / width), np.zeros(width)) for _ in range(n_layers)]
+
+
+def dp_check(world, rank, local):
+    """Correctness guard of the sharded step, run before the timed region (every rank takes part).
+
+    Two Adam steps of a reduced bf16 stack (4 x Linear(512 -> 512) + relu, MSE, global batch 4096) are trained
+    (a) sharded over the N ranks through DataParallelTrainer -- backward, per-layer NCCL all-reduce on the
+        communication stream, identical update on every rank -- and
+    (b) on rank 0 alone, unsharded, from the same parameters and the same global batch.
+    replicas_identical: a float64 checksum (sum, sum of squares) of every parameter tensor is all-gathered and must
+        be bit-equal on every rank (they apply the same reduced gradient with the same kernel).
+    vs_single_gpu_max_rel: largest rms(p_sharded - p_unsharded) / rms(update) over the parameter tensors.  The two
+        differ only in fp32 summation order of the weight gradient (one GEMM over the batch vs per-shard GEMMs +
+        all-reduce); Adam's first steps are ~lr*sign(g), so an element whose gradient is within that rounding of
+        zero moves the other way: expected ~2e-3, bound 2e-2.  Costs must agree to 1e-6 relative."""
+    if world == 1:
+        return {"n_ranks": 1, "ok": True, "note": "single rank: the batch is not sharded, nothing to compare"}
+    import torch.distributed as dist
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    from penr_oz_neural_network_torch_b200.dp import DataParallelTrainer, shard_bounds
+    width, nl, gb, steps = 512, 4, 4096, 2
+    dev = torch.device("cuda", local)
+    spec = StackSpec.from_algos(["linear", "relu"] * nl)
+    params = wide_params(width, nl, seed=3)
+    g = torch.Generator(device="cpu").manual_seed(11)              # the same global batch on every rank
+    x = torch.randn((gb, width), generator=g).to(torch.bfloat16)
+    t = torch.randn((gb, width), generator=g).to(torch.bfloat16)
+    hp = dict(optimizer="adam", learning_rate=1e-3, decay_rate=0.9, l2_lambda=0.001, epochs=steps)
+
+    def run(sharded):
+        eng = DeviceMLP([width] * (nl + 1), spec, True, "bfloat16", local)
+        for l, (w, b) in enumerate(params):
+            eng.upload_params(l, w, b)
+        if sharded:
+            lo, hi = shard_bounds(gb, rank, world)
+            xs, ts = x[lo:hi].to(dev).contiguous(), t[lo:hi].to(dev).contiguous()
+            tr = DataParallelTrainer(eng)
+            tr.train_begin(global_batch=gb, **hp)
+            for _ in range(steps):
+                tr.train_step(xs, ts)
+            costs = tr.costs(0, steps)
+        else:
+            xs, ts = x.to(dev), t.to(dev)
+            eng.train_begin(**hp)
+            for _ in range(steps):
+                eng.train_step(xs, ts)
+            costs = eng.costs(0, steps)
+        out = [eng.download_params(l) for l in range(nl)]
+        eng.close()
+        return out, np.asarray(costs)
+
+    p_dp, c_dp = run(True)
+    sums = torch.tensor([[float(w.sum()), float((w * w).sum()), float(b.sum()), float((b * b).sum())] for w, b in p_dp],
+                        dtype=torch.float64, device=dev).reshape(-1)
+    identical = True
+    if world > 1:
+        gathered = [torch.empty_like(sums) for _ in range(world)]
+        dist.all_gather(gathered, sums)
+        identical = all(torch.equal(gathered[0], q) for q in gathered[1:])
+    res = {"n_ranks": world, "stack": f"{nl} x Linear({width}->{width}) + relu, bf16, MSE, Adam, global batch {gb}, {steps} steps",
+           "replicas_identical": bool(identical)}
+    ok = identical
+    if rank == 0:
+        p_1, c_1 = run(False)
+        worst = 0.0
+        for l, ((w, b), (w1, b1)) in enumerate(zip(p_dp, p_1)):
+            for got, ref, init in ((w, w1, params[l][0]), (b, b1, params[l][1])):
+                upd = float(np.sqrt(np.mean((ref - init) ** 2)))
+                worst = max(worst, float(np.sqrt(np.mean((got - ref) ** 2))) / max(upd, 1e-30))
+        cost_rel = float(np.max(np.abs(c_dp - c_1) / np.abs(c_1)))
+        res.update({"vs_single_gpu_max_rel": round(worst, 6), "bound": 2e-2, "cost_max_rel": cost_rel, "cost_bound": 1e-6})
+        ok = ok and worst <= 2e-2 and cost_rel <= 1e-6
+    if world > 1:
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = bool(flag.item())
+    res["ok"] = ok
+    return res
+
+
 def run_wide(args, world, rank, local, dp):
     """C4 (one GPU, batch 65536) / C5 (data parallel, global batch 524288 sharded over the ranks):
     4 x Linear(4096->4096)+relu, MSE, Adam, bf16 operands / fp32 accumulate / fp32 masters."""
-    from penr_oz_neural_network_torch_b200 import DeviceMLP, HostBatchFeeder, StackSpec, launch_count
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec, launch_count
     from penr_oz_neural_network_torch_b200.dp import DataParallelTrainer, shard_bounds
     dev = torch.device("cuda", local)
+    check = dp_check(world, rank, local) if dp else None
+    if check is not None and not check["ok"]:
+        if rank == 0:
+            print(json.dumps({"error": "dp_check failed", "dp_check": check}), flush=True)
+        raise SystemExit(3)
     global_batch = (args.batch or 524288) if dp else (args.batch or 65536) * world
     lo, hi = shard_bounds(global_batch, rank, world) if dp else (0, global_batch // world)
     batch = hi - lo
     eng = DeviceMLP(WIDE_SIZES, StackSpec.from_algos(WIDE_ALGOS), True, "bfloat16", local)
-    rng = np.random.default_rng(0)                       # same parameters on every rank
-    for l in range(4):
-        eng.upload_params(l, rng.standard_normal((4096, 4096)) * np.sqrt(2.0 / 4096), np.zeros(4096))
+    for l, (w, b) in enumerate(wide_params(4096, 4, seed=0)):      # same parameters on every rank
+        eng.upload_params(l, w, b)
     g = torch.Generator(device=dev).manual_seed(7 + rank)
     x = torch.randn((batch, 4096), generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
     t = torch.randn((batch, 4096), generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
     total = args.warmup + args.steps
     hp = dict(optimizer="adam", learning_rate=1e-4, decay_rate=0.999, l2_lambda=0.001, epochs=total + 4)
-    if dp and world > 1:
-        tr = DataParallelTrainer(eng)
+    sharded = dp and world > 1
+    tr = DataParallelTrainer(eng) if sharded else None
+    if sharded:
         tr.train_begin(global_batch=global_batch, **hp)
-        step = lambda: tr.train_step(x, t)
+        step = lambda xx, tt: tr.train_step(xx, tt)
     else:
         eng.train_begin(**hp)
-        step = lambda: eng.train_step(x, t)
+        step = lambda xx, tt: eng.train_step(xx, tt)
     for _ in range(args.warmup):
-        step()
+        step(x, t)
     barrier_sync(world)
     sampler = ClockSampler(local).start() if rank == 0 else None
     l0 = launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        step()
+        step(x, t)
     e1.record()
     barrier_sync(world)
     launches = launch_count() - l0
-    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    my_ms = e0.elapsed_time(e1)
+    ms = max_over_ranks(my_ms, world)
+    per_rank_ms = all_ranks(my_ms / args.steps, world)
     costs = eng.costs(args.warmup, args.steps)
     assert np.isfinite(costs).all(), "non-finite training cost"
     clocks = sampler.stop() if sampler else None
     samples = global_batch * args.steps
-    # ---- e2e (single GPU only: host batch in, cost out, every step) ----
+
+    # ---- e2e: every step's shard comes from pinned host memory (copy stream, double-buffered, overlapping the
+    # previous step) and every step's cost (this rank's share) is read back ----
     e2e = None
-    if world == 1:
+    if True:
         hx, ht = x.cpu().pin_memory(), t.cpu().pin_memory()
-        n_e2e = max(3, min(args.steps, 10))
-        eng.train_begin(**dict(hp, epochs=n_e2e + 8))
-        feeder = HostBatchFeeder(eng, batch)
-        feeder.stage(hx, ht)
+        n_e2e = max(3, min(args.steps, 5 if dp else 10))
+        if sharded:
+            tr.train_begin(global_batch=global_batch, **dict(hp, epochs=n_e2e + 8))
+        else:
+            eng.train_begin(**dict(hp, epochs=n_e2e + 8))
+        xd = [x, torch.empty_like(x)]
+        td = [t, torch.empty_like(t)]
+        copy_stream, read_stream = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        copied = [torch.cuda.Event() for _ in range(2)]
+        consumed = [torch.cuda.Event() for _ in range(2)]
+        cur = torch.cuda.current_stream(dev)
+
+        def stage(i):
+            slot = i % 2
+            with torch.cuda.stream(copy_stream):
+                if i >= 2:
+                    copy_stream.wait_event(consumed[slot])
+                xd[slot].copy_(hx, non_blocking=True)
+                td[slot].copy_(ht, non_blocking=True)
+                copied[slot].record(copy_stream)
+
+        def one(i):
+            slot = i % 2
+            cur.wait_event(copied[slot])
+            step(xd[slot], td[slot])
+            consumed[slot].record(cur)
+            stage(i + 1)                                   # the next shard's copy overlaps this step
+            read_stream.wait_event(consumed[slot])
+            return float(eng.costs(i, 1, stream=read_stream)[0])
+
+        torch.cuda.synchronize()
+        stage(0)
         for i in range(2):
-            feeder.step(i); feeder.stage(hx, ht); feeder.cost(i)
-        torch.cuda.synchronize()
+            one(i)
+        barrier_sync(world)
         t0 = time.perf_counter()
-        for i in range(n_e2e):
-            feeder.step(2 + i); feeder.stage(hx, ht); last = feeder.cost(2 + i)
-        torch.cuda.synchronize()
-        el = time.perf_counter() - t0
-        e2e = {"value": batch * n_e2e / el, "unit": "samples/s", "h2d_bytes_per_step": feeder.h2d_bytes,
-               "d2h_bytes_per_step": feeder.d2h_bytes, "ms_per_step": el / n_e2e * 1e3}
-        del feeder, hx, ht
+        for i in range(2, 2 + n_e2e):
+            last = one(i)
+        barrier_sync(world)
+        el = max_over_ranks((time.perf_counter() - t0) * 1e3, world) * 1e-3
+        assert np.isfinite(last)
+        h2d = 2 * batch * 4096 * 2
+        e2e = {"value": global_batch * n_e2e / el, "unit": "samples/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 8, "ms_per_step": el / n_e2e * 1e3,
+               "h2d_gbs_per_rank_needed_to_hide": round(h2d / (ms / args.steps * 1e-3) / 1e9, 1),
+               "note": "per rank and step: its bf16 shard (inputs + targets) from pinned host memory on a copy stream, "
+                       "overlapping the previous step; this rank's cost share read back.  Above ~50 GB/s per rank "
+                       "(PCIe 5 x16) the step is bound by the host link, not by the GPU."}
+        del hx, ht, xd, td
+    # ---- exposed communication: the same per-GPU batch without the all-reduce (local steps only) ----
+    comm = None
+    if sharded:
+        eng.train_begin(**dict(hp, epochs=8))
+        for _ in range(2):
+            eng.train_step(x, t)
+        barrier_sync(world)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        n_loc = max(3, min(args.steps, 5))
+        for _ in range(n_loc):
+            eng.train_step(x, t)
+        a1.record()
+        barrier_sync(world)
+        local_ms = max_over_ranks(a0.elapsed_time(a1), world) / n_loc
+        comm = {"collective": f"nccl all_reduce(SUM), 4 buckets x {(4096 * 4096 + 4096) * 4 / 1e6:.1f} MB fp32 (one per Linear "
+                              f"layer, [W;b]), on a communication stream behind that layer's weight-gradient event",
+                "ms_per_step_without_allreduce": round(local_ms, 4),
+                "exposed_comm_ms_per_step": round(ms / args.steps - local_ms, 4)}
     roof = None
     if rank == 0:
         pk = peaks()
-        if not (dp and world > 1):
+        if not sharded:
             eng.train_begin(**dict(hp, epochs=16))
             eng.train_step(x, t)
             eng.profile_begin()
@@ -542,6 +715,8 @@ def run_wide(args, world, rank, local, dp):
         else:
             top, tf, per, tot, prof, kern = "whole step", 0.0, 0.0, 1.0, {}, {}
         step_tf = WIDE_FLOPS_PER_SAMPLE * batch / (ms / args.steps * 1e-3) / 1e12
+        if not prof:
+            tf = step_tf
         roof = {"bound": "tensor", "kernel": top, "achieved": round(tf, 1), "peak": pk["bf16_tflops_sustained"],
                 "unit": "TFLOP/s", "frac": round(tf / pk["bf16_tflops_sustained"], 4),
                 "traffic": NCU_TRAFFIC["tc_fwd"] if top.startswith("tc_fwd") else None,
@@ -554,38 +729,15 @@ def run_wide(args, world, rank, local, dp):
                          "frac_of_burst": round(step_tf / pk["bf16_tflops"], 4)},
                 "kernels_ms": kern}
     eng.close()
-    name = "c5" if dp else "c4"
+    extras = {}
+    if dp:
+        extras["dp_check"] = check
+        extras["per_rank_ms_per_step"] = [round(v, 4) for v in per_rank_ms]
+        if comm:
+            extras["comm"] = comm
     return dict(metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=samples / (ms * 1e-3),
                 ms_per_step=ms / args.steps, e2e=e2e, gpu_launches=int(launches), roofline=roof, clocks=clocks,
-                dtype="bf16", scaling="strong" if dp else "weak",
-                config={"workload": f"{name}: MLP 4096x4 hidden (4 x Linear 4096->4096 + relu), MSE, Adam, bf16 "
-                                    f"operands / fp32 accumulate / fp32 master weights, train step",
-                        "batch_per_gpu": batch, "global_batch": global_batch,
-                        "parallelism": (f"dp{world} (NCCL all-reduce per layer, overlapped)" if dp else
-                                        (f"replicas x{world}" if world > 1 else "single")),
-                        "dropout": 0.0, "l2_flush": "one batch of inputs is 537 MB per GPU (> 126 MB L2)"})
-
-
-def cpu_train_wide(seconds, batch=1024, threads=None):
-    from oracle.torch_cpu_port import TorchCpuMLP
-    threads = threads or os.cpu_count() or 1
-    torch.set_num_threads(threads)
-    rng = np.random.default_rng(0)
-    params = []
-    for l in range(4):
-        params += [rng.standard_normal((4096, 4096)) * np.sqrt(2.0 / 4096), np.zeros(4096)]
-    m = TorchCpuMLP(WIDE_ALGOS, params, "adam")
-    x = torch.randn((batch, 4096), dtype=torch.float64)
-    t = torch.randn((batch, 4096), dtype=torch.float64)
-    m.train_step(x, t, 1e-4, l2_lambda=0.001)
-    n, t0 = 0, time.perf_counter()
-    while True:
-        m.train_step(x, t, 1e-4, l2_lambda=0.001)
-        n += 1
-        el = time.perf_counter() - t0
-        if el >= seconds:
-            break
-    return batch * n / el, n, threads, el, batch
+                dtype="bf16", scaling="strong" if dp else "weak", extras=extras)
 
 
 EMB_SIZES = [27, 10, 30, 200, 27]
@@ -681,13 +833,7 @@ def run_emb(args, world, rank, local):
                 e2e={"value": world * batch * n_e2e / (e2e_ms * 1e-3), "unit": "samples/s",
                      "h2d_bytes_per_step": batch * (EMB_TOKENS + 1) * 4, "d2h_bytes_per_step": 8,
                      "ms_per_step": e2e_ms / n_e2e},
-                gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
-                config={"workload": "emb: embedding(27x10) -> Linear 30->200 -> batchnorm -> tanh -> Linear 200->27 -> softmax + "
-                                    "cross-entropy, Adam, L2 1e-3, batch 32768 x 3 tokens, fp32 train step",
-                        "batch_per_gpu": batch, "global_batch": batch * world,
-                        "parallelism": f"replicas x{world}" if world > 1 else "single", "dropout": 0.0,
-                        "l2_flush": "inputs are 0.5 MB per step; the step is bound by its ~90 MB of activation traffic, "
-                                    "which stays in L2"})
+                gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32", extras={})
 
 
 def cpu_train_emb(seconds, batch=EMB_BATCH, threads=None):
@@ -709,88 +855,296 @@ def cpu_train_emb(seconds, batch=EMB_BATCH, threads=None):
 
 
 # ---- CPU arms -------------------------------------------------------------------------------------------
-def cpu_train_c2(seconds, max_steps=None, threads=None):
-    """The reference's torch-CPU path (oracle/torch_cpu_port.py, fp64 as the reference ships) at C2
-    shapes on this box's host cores.  Returns (samples/s, steps timed, threads)."""
-    from oracle.torch_cpu_port import TorchCpuMLP
-    threads = threads or os.cpu_count() or 1
-    torch.set_num_threads(threads)
-    params = init_params(SIZES, seed=0)
-    m = TorchCpuMLP(ALGOS, params, "adam")
+# ---- the unmodified reference (baseline/_ref, copied there by __graft_entry__.build()) -----------------------
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")
+
+
+def load_reference():
+    """The reference's own neural_net_model module from baseline/_ref (a verbatim copy made by build() where
+    /root/reference is mounted; git-ignored, travels to the GPU box).  None if it is not there."""
+    path = os.path.join(REF_DIR, "neural_net_model.py")
+    if not os.path.exists(path):
+        return None
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("poz_reference_neural_net_model", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+class CpuArm:
+    """One CPU train step / forward pass at tensor level: the reference's own class when baseline/_ref is
+    present (kind "reference": NeuralNetworkModel._forward :384-408, the L2 term :482-483, cost.backward() :495,
+    optimizer.step() :497 -- the loop body of train() below its list -> tensor conversion), else the operator-
+    for-operator port oracle/torch_cpu_port.py (kind "port")."""
+
+    def __init__(self, sizes, acts, params, ce):
+        import warnings
+        warnings.filterwarnings("ignore", category=UserWarning)
+        self.ce = ce
+        self.ref = load_reference()
+        if self.ref is not None:
+            self.kind = "reference"
+            m = self.ref.NeuralNetworkModel("bench-cpu-arm", list(sizes), "xavier", "zeros", list(acts), "adam")
+            it = iter(params)
+            for layer in m.layers:
+                if layer.algo == "linear":
+                    layer.weights = torch.as_tensor(next(it), dtype=torch.float64).clone()
+                    layer.bias = torch.as_tensor(next(it), dtype=torch.float64).clone()
+            m.optimizer = torch.optim.Adam(m.params)          # as deserialize does (:353)
+            self.m = m
+        else:
+            from oracle.torch_cpu_port import TorchCpuMLP
+            self.kind = "port"
+            algos = []
+            for a in acts:
+                algos += ["linear", a]
+            self.m = TorchCpuMLP(algos, params, "adam")
+
+    def describe(self):
+        return ("the unmodified reference (baseline/_ref/neural_net_model.py): _forward + L2 + backward + Adam.step at "
+                "tensor level" if self.kind == "reference" else
+                "oracle/torch_cpu_port.py (the reference's operator sequence; baseline/_ref not present)")
+
+    def train_step(self, x, target, lr, l2):
+        if self.kind == "port":
+            return self.m.train_step(x, target, lr, l2_lambda=l2)
+        m = self.m
+        for grp in m.optimizer.param_groups:                  # :467-469
+            grp["lr"] = lr
+        for p in m.params:
+            p.requires_grad_()                                # :477-478
+        _, cost = m._forward(x, target, 0.0)                  # :480
+        if l2 > 0.0:
+            cost += l2 * sum((w ** 2).sum() for w in m.weights)   # :482-483
+        for p in m.params:
+            p.grad = None                                     # :485-486
+        cost.backward()                                       # :495
+        m.optimizer.step()                                    # :497
+        return cost.item()                                    # :503
+
+    def forward(self, x):
+        if self.kind == "port":
+            return self.m.forward(x)[0][-1]
+        return self.m._forward(x, None)[0][-1]                # as compute_output calls it (:380), no no_grad
+
+    def targets(self, y):
+        """CE labels: the reference takes a list of [label] rows (:401); MSE: the [B, out] target as a tensor
+        (torch.tensor(tensor) at :405 copies it)."""
+        if self.kind == "port":
+            return y
+        return [[int(v)] for v in y] if self.ce else y
+
+
+def cpu_steps(arm, x, y, n_warm, n_steps=None, seconds=None, lr=0.01, l2=0.001):
+    tgt = arm.targets(y)
+    for _ in range(n_warm):
+        arm.train_step(x, tgt, lr, l2)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        arm.train_step(x, tgt, lr * 0.9 ** min(n, 50), l2)
+        n += 1
+        el = time.perf_counter() - t0
+        if (n_steps and n >= n_steps) or (seconds and el >= seconds) or el > 150:
+            break
+    return x.shape[0] * n / el, n, el
+
+
+def cpu_arm_c2(threads=None):
+    torch.set_num_threads(threads or os.cpu_count() or 1)
+    arm = CpuArm(SIZES, ["relu", "relu", "softmax"], init_params(SIZES, seed=0), ce=True)
     g = torch.Generator().manual_seed(0)
     x = torch.randn((C2_BATCH, 784), generator=g, dtype=torch.float64)
     y = torch.randint(0, 10, (C2_BATCH,), generator=g, dtype=torch.int64)
-    for i in range(2):
-        m.train_step(x, y, 0.01, l2_lambda=0.001)
-    n, t0 = 0, time.perf_counter()
-    while True:
-        m.train_step(x, y, 0.01 * 0.9 ** min(n, 50), l2_lambda=0.001)
-        n += 1
-        el = time.perf_counter() - t0
-        if (max_steps and n >= max_steps) or (not max_steps and el >= seconds) or el > 120:
-            break
-    return C2_BATCH * n / el, n, threads, el
+    return arm, x, y
 
 
-def cpu_infer_c3(batch, seconds, threads=None):
-    from oracle.torch_cpu_port import TorchCpuMLP
-    threads = threads or os.cpu_count() or 1
-    torch.set_num_threads(threads)
-    m = TorchCpuMLP(ALGOS, init_params(SIZES, seed=0), "adam")
-    b = min(batch, 65536)
-    x = torch.randn((b, 784), dtype=torch.float64)
-    m.forward(x)
-    n, t0 = 0, time.perf_counter()
-    while time.perf_counter() - t0 < seconds:
-        m.forward(x)       # the reference does not wrap inference in no_grad (neural_net_model.py:379-380)
-        n += 1
-    el = time.perf_counter() - t0
-    return b * n / el, n, threads, el, b
+def cpu_arm_wide(batch=1024, threads=None):
+    torch.set_num_threads(threads or os.cpu_count() or 1)
+    params = [q for wb in wide_params(4096, 4, seed=0) for q in wb]
+    arm = CpuArm(WIDE_SIZES, ["relu"] * 4, params, ce=False)
+    x = torch.randn((batch, 4096), dtype=torch.float64)
+    t = torch.randn((batch, 4096), dtype=torch.float64)
+    return arm, x, t
+
+
+def list_api_baseline(ref, seconds_cap=40.0):
+    """The reference's list-level API: NeuralNetworkModel.train() and compute_output() on
+    Python lists, C2 model, training_buffer_size lowered (the gate needs 235,146 samples otherwise, :286,429).
+    train() includes what it always includes: list -> tensor per epoch (:472), two JSON saves and the final
+    statistics (:454,529-530)."""
+    import tempfile
+    cwd = os.getcwd()
+    os.chdir(tempfile.mkdtemp())
+    try:
+        rng = np.random.default_rng(1)
+        rows = rng.standard_normal((2048, 784))
+        data = [(rows[i].tolist(), [int(rng.integers(0, 10))]) for i in range(2048)]
+        out = {}
+        took = {}
+        for ep in (2, 6):
+            m = ref.NeuralNetworkModel("bench-list-api", SIZES, activation_algos=["relu", "relu", "softmax"])
+            m.training_buffer_size = len(data)
+            t0 = time.perf_counter()
+            m.train(list(data), epochs=ep, batch_size=C2_BATCH, dropout_rate=0.0)
+            took[ep] = time.perf_counter() - t0
+        per_epoch = (took[6] - took[2]) / 4
+        out["train_c2"] = {"ms_per_epoch": round(per_epoch * 1e3, 2), "samples_per_s": round(C2_BATCH / per_epoch),
+                           "fixed_ms_per_call": round((took[2] - 2 * per_epoch) * 1e3, 1),
+                           "note": "train(list, batch_size=1024, dropout 0): (6-epoch call - 2-epoch call) / 4; fixed = "
+                                   "JSON saves + statistics per call"}
+        m = ref.NeuralNetworkModel("bench-list-api", SIZES, activation_algos=["relu", "relu", "softmax"])
+        batch_in = [r for r, _ in data[:1024]]
+        m.compute_output(batch_in)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            m.compute_output(batch_in)
+        dt = (time.perf_counter() - t0) / 3
+        out["compute_output_c2_b1024"] = {"ms_per_call": round(dt * 1e3, 2), "samples_per_s": round(1024 / dt)}
+        # C1: one of the reference's own test_train rows ([9,9,9] relu+softmax Adam, data = num_params samples, 1 epoch)
+        m = ref.NeuralNetworkModel("bench-list-c1", [9, 9, 9], activation_algos=["relu", "softmax"])
+        n = m.num_params
+        d1 = [([0.5] * 9, [1])] * n
+        t0 = time.perf_counter()
+        m.train(list(d1), epochs=1, dropout_rate=0.0)
+        dt = time.perf_counter() - t0
+        out["train_c1_9_9_9"] = {"ms_per_call": round(dt * 1e3, 2), "samples_per_s": round(n / dt),
+                                 "note": f"test_neural_net_model.py:161-186 row: {n} samples, epochs=1"}
+        return out
+    finally:
+        os.chdir(cwd)
+
+
+def pick_workload(args):
+    """c2 for a single process on a one-GPU box; c5 (the sharded, data-parallel curve) when launched as a rank of
+    torch.distributed.run or on a box that shows several GPUs (a leg of the scaling run, N = 1 included)."""
+    if args.workload:
+        return args.workload, "--workload"
+    under_launcher = "WORLD_SIZE" in os.environ or "TORCHELASTIC_RUN_ID" in os.environ
+    try:
+        n_visible = torch.cuda.device_count()
+    except Exception:
+        n_visible = 0
+    if args.gpus > 1 or under_launcher:
+        return "c5", "default under torch.distributed.run / --gpus > 1: the data-parallel scaling workload"
+    if n_visible > 1:
+        return "c5", f"default on a box with {n_visible} visible GPUs: leg N=1 of the data-parallel scaling curve"
+    return "c2", "default on a one-GPU box: BASELINE.json configs[1]"
 
 
 def run_reference(args, world, rank):
+    """The reference's own CPU implementation of the same workload on the box's host cores (all of them), timed
+    for --steps steps after --warmup; each step is a bounded sample of the native arm's step."""
     if rank != 0:
         return None
-    if args.workload == "c3":
+    wl = args.workload
+    steps, warm = max(1, min(args.steps, 2000)), max(1, min(args.warmup, 50))
+    base = dict(impl="reference", n_gpus=args.gpus, higher_is_better=True, vs_baseline=None, dtype="f64", data="synthetic")
+    zero = {"h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    if wl == "c3":
         batch = args.batch or 262144
-        v, n, thr, el, b = cpu_infer_c3(batch, 10.0)
-        return dict(impl="reference", metric="infer samples/s", unit="samples/s", value=v, n_gpus=args.gpus,
-                    steps=n, warmup=1, ms_per_step=el / n * 1e3, higher_is_better=True, scaling="weak",
-                    vs_baseline=None, dtype="f64", data="synthetic",
-                    config={"workload": f"c3: batched inference 784-256-128-10, batch {batch}, fp32"},
-                    cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
-                                  "sample": f"{n} forward passes of {b} rows, torch CPU fp64 (oracle/torch_cpu_port.py)"},
-                    e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
-    if args.workload == "emb":
+        arm, x, _ = cpu_arm_c2()
+        b = min(batch, 65536)
+        xi = torch.randn((b, 784), dtype=torch.float64)
+        for _ in range(min(warm, 2)):
+            arm.forward(xi)
+        n_s = min(steps, 20)
+        t0 = time.perf_counter()
+        for _ in range(n_s):
+            arm.forward(xi)
+        el = time.perf_counter() - t0
+        v = b * n_s / el
+        return dict(base, metric="infer samples/s", unit="samples/s", value=v, steps=n_s, warmup=min(warm, 2),
+                    ms_per_step=el / n_s * 1e3, scaling="weak", config=native_config(args, world),
+                    cpu_baseline={"value": v, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": arm.kind,
+                                  "sample": f"{n_s} forward passes of {b} rows (a bounded sample of the {batch}-row pass), "
+                                            f"fp64, {arm.describe()}"},
+                    e2e=dict(zero, value=v, unit="samples/s"))
+    if wl == "emb":
         v, n, thr, el, b = cpu_train_emb(10.0, args.batch or EMB_BATCH)
-        return dict(impl="reference", metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v,
-                    n_gpus=args.gpus, steps=n, warmup=1, ms_per_step=el / n * 1e3, higher_is_better=True,
-                    scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
-                    config={"workload": "emb: embedding + batchnorm character model, train step"},
+        return dict(base, metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v, steps=n, warmup=1,
+                    ms_per_step=el / n * 1e3, scaling="weak", config=native_config(args, world),
                     cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
                                   "sample": f"{n} train steps of batch {b}, torch CPU fp64 (oracle/torch_cpu_port.py)"},
-                    e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
-    if args.workload in ("c4", "c5"):
-        v, n, thr, el, b = cpu_train_wide(10.0)
-        return dict(impl="reference", metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v,
-                    n_gpus=args.gpus, steps=n, warmup=1, ms_per_step=el / n * 1e3, higher_is_better=True,
-                    scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
-                    config={"workload": f"{args.workload}: MLP 4096x4 hidden, MSE, Adam, train step"},
-                    cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
-                                  "sample": f"{n} train steps of a REDUCED batch of {b} rows, torch CPU fp64 "
-                                            "(oracle/torch_cpu_port.py); a full 65536-row step takes minutes"},
-                    e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
-    steps = max(1, min(args.steps, 2000))
-    v, n, thr, el = cpu_train_c2(0, max_steps=steps)
-    return dict(impl="reference", metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v,
-                n_gpus=args.gpus, steps=n, warmup=2, ms_per_step=el / n * 1e3, higher_is_better=True,
-                scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
-                config={"workload": "c2: MLP 784-256-128-10 relu/relu/softmax + cross-entropy, Adam, L2 1e-3, "
-                                    "batch 1024, fp32 train step"},
-                cpu_baseline={"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
-                              "sample": f"{n} train steps of batch 1024, torch CPU fp64, the reference's operator "
-                                        "sequence (oracle/torch_cpu_port.py)"},
-                e2e={"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+                    e2e=dict(zero, value=v, unit="samples/s"))
+    if wl in ("c4", "c5"):
+        arm, x, t = cpu_arm_wide(1024)
+        n_s, n_w = min(steps, 20), min(warm, 3)
+        v, n, el = cpu_steps(arm, x, t, n_w, n_steps=n_s, lr=1e-4)
+        return dict(base, metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v, steps=n, warmup=n_w,
+                    ms_per_step=el / n * 1e3, scaling="strong" if wl == "c5" else "weak", config=native_config(args, world),
+                    cpu_baseline={"value": v, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": arm.kind,
+                                  "sample": f"{n} train steps of a bounded sample of 1024 rows of the batch (a full step is "
+                                            f"minutes of fp64 CPU work), {arm.describe()}"},
+                    e2e=dict(zero, value=v, unit="samples/s"))
+    arm, x, y = cpu_arm_c2()
+    v, n, el = cpu_steps(arm, x, y, warm, n_steps=steps)
+    line = dict(base, metric="train samples/s (fwd+bwd+step)", unit="samples/s", value=v, steps=n, warmup=warm,
+                ms_per_step=el / n * 1e3, scaling="weak", config=native_config(args, world),
+                cpu_baseline={"value": v, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": arm.kind,
+                              "sample": f"{n} train steps of batch 1024 after {warm} warm-up steps, fp64, {arm.describe()}"},
+                e2e=dict(zero, value=v, unit="samples/s"))
+    if arm.ref is not None and not args.no_class_api:
+        try:
+            line["list_api"] = list_api_baseline(arm.ref)
+        except Exception as e:        # the list-level numbers are an extra; never lose the line over them
+            line["list_api"] = {"error": str(e)[:200]}
+    return line
+
+
+def native_config(args, world):
+    """The `config` object both arms print for a workload (the driver compares them)."""
+    wl = args.workload
+    if wl == "c2":
+        return {"workload": "c2: MLP 784-256-128-10 relu/relu/softmax + cross-entropy, Adam, L2 1e-3, batch 1024, fp32 "
+                            "train step", "batch_per_gpu": C2_BATCH, "global_batch": C2_BATCH * world,
+                "parallelism": f"replicas x{world}" if world > 1 else "single", "dropout": 0.0,
+                "l2_flush": "native arm: inputs cycle through a 205 MB pool (> 126 MB L2); parameters stay cache-resident "
+                            "as in real training"}
+    if wl == "c3":
+        batch = args.batch or 262144
+        return {"workload": f"c3: batched inference 784-256-128-10, batch {batch}, fp32", "batch_per_gpu": batch,
+                "global_batch": batch * world, "parallelism": f"replicas x{world}" if world > 1 else "single",
+                "l2_flush": "native arm: inputs cycle through a pool of distinct batches larger than the 126 MB L2"}
+    if wl in ("c4", "c5"):
+        dp = wl == "c5"
+        gb = (args.batch or 524288) if dp else (args.batch or 65536) * world
+        return {"workload": f"{wl}: MLP 4096x4 hidden (4 x Linear 4096->4096 + relu), MSE, Adam, bf16 operands / fp32 "
+                            f"accumulate / fp32 master weights, train step"
+                            + (f"; global batch {gb} sharded over {world} GPU(s) (dp{world})" if dp else ""),
+                "batch_per_gpu": gb // world, "global_batch": gb,
+                "parallelism": (f"dp{world} (batch sharded, NCCL all-reduce per layer overlapped with the backward)" if dp
+                                else (f"replicas x{world}" if world > 1 else "single")), "dropout": 0.0,
+                "l2_flush": f"native arm: one batch of inputs is {gb // world * 4096 * 2 / 1e6:.0f} MB per GPU (> 126 MB L2)"}
+    return {"workload": "emb: embedding(27x10) -> Linear 30->200 -> batchnorm -> tanh -> Linear 200->27 -> softmax + "
+                        "cross-entropy, Adam, L2 1e-3, batch 32768 x 3 tokens, fp32 train step",
+            "batch_per_gpu": args.batch or EMB_BATCH, "global_batch": (args.batch or EMB_BATCH) * world,
+            "parallelism": f"replicas x{world}" if world > 1 else "single", "dropout": 0.0,
+            "l2_flush": "native arm: inputs are 0.5 MB per step; the step is bound by ~90 MB of activation traffic that stays in L2"}
+
+
+def secondary_lines(args, local):
+    """configs[2] and configs[3] of BASELINE.json in the same run as the headline (one GPU): batched inference at
+    262,144 rows and the 4096x4 bf16 train step at batch 65,536, each with its own roofline, clocks and e2e."""
+    import copy
+    out = {}
+    for name, fn, steps in (("c3", lambda a: run_c3(a, 1, 0, local), 20),
+                            ("c4", lambda a: run_wide(a, 1, 0, local, dp=False), 5)):
+        a = copy.copy(args)
+        a.steps, a.warmup, a.batch, a.workload = steps, 3, 0, name
+        try:
+            torch.cuda.set_stream(torch.cuda.default_stream())
+            r = fn(a)
+            out[name] = {k: r[k] for k in ("metric", "unit", "value", "ms_per_step", "e2e", "gpu_launches", "roofline",
+                                           "clocks", "dtype")}
+            out[name]["config"] = native_config(a, 1)
+            out[name].update(r.get("extras") or {})
+            out[name]["steps"], out[name]["warmup"] = steps, 3
+        except Exception as e:
+            out[name] = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+    return out
 
 
 def main():
@@ -799,17 +1153,22 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5", "emb"])
+    ap.add_argument("--workload", default=None, choices=["c2", "c3", "c4", "c5", "emb"])
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-class-api", action="store_true", help="skip the NeuralNetworkModel.train() timing of the c2 workload")
+    ap.add_argument("--no-class-api", action="store_true", help="skip the list-level NeuralNetworkModel.train() timings")
+    ap.add_argument("--no-secondary", action="store_true", help="c2 only: skip the c3 / c4 lines under 'secondary'")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    args.workload, why = pick_workload(args)
+    if args.workload in ("c4", "c5") and args.steps > 50:
+        args.steps, args.warmup = 10, 3          # the defaults are sized for the 80 us c2 step; a wide step is 20-160 ms
     world, rank, local = dist_setup(args)
 
     if args.impl == "reference":
         line = run_reference(args, world, rank)
         if line is not None:
+            line["config"]["picked"] = why
             print(json.dumps(line), flush=True)
         return
 
@@ -825,6 +1184,9 @@ def main():
     else:
         res = (run_c2 if args.workload == "c2" else run_c3)(args, world, rank, local)
     if rank == 0:
+        secondary = None
+        if args.workload == "c2" and world == 1 and not args.no_secondary:
+            secondary = secondary_lines(args, local)
         cpu = None
         try:
             os.sched_setaffinity(0, range(os.cpu_count() or 1))      # the CPU baseline uses every host core
@@ -836,25 +1198,43 @@ def main():
                 cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
                        "sample": f"{n} train steps of batch {b} in {el:.1f} s, torch CPU fp64 (oracle/torch_cpu_port.py)"}
             elif args.workload in ("c4", "c5"):
-                v, n, thr, el, b = cpu_train_wide(10.0)
-                cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
-                       "sample": f"{n} train steps of a REDUCED batch of {b} rows in {el:.1f} s, torch CPU fp64; "
-                                 "a full 65536-row step takes minutes"}
+                arm, x, t = cpu_arm_wide(1024)
+                v, n, el = cpu_steps(arm, x, t, 1, seconds=10.0, lr=1e-4)
+                cpu = {"value": v, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": arm.kind,
+                       "sample": f"{n} train steps of a bounded sample of 1024 rows in {el:.1f} s (a full step is minutes of "
+                                 f"fp64 CPU work), {arm.describe()}"}
             elif args.workload == "c2":
-                v, n, thr, el = cpu_train_c2(12.0)
-                cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
-                       "sample": f"{n} train steps of batch 1024 in {el:.1f} s, torch CPU fp64, the reference's "
-                                 "operator sequence (oracle/torch_cpu_port.py)"}
+                arm, x, y = cpu_arm_c2()
+                v, n, el = cpu_steps(arm, x, y, 2, seconds=12.0)
+                cpu = {"value": v, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": arm.kind,
+                       "sample": f"{n} train steps of batch 1024 in {el:.1f} s, fp64, {arm.describe()}"}
+                if arm.ref is not None and not args.no_class_api:
+                    try:
+                        cpu["list_api"] = list_api_baseline(arm.ref)
+                    except Exception as e:
+                        cpu["list_api"] = {"error": str(e)[:200]}
             else:
-                v, n, thr, el, b = cpu_infer_c3(args.batch or 262144, 10.0)
-                cpu = {"value": v, "unit": "samples/s", "cores": thr, "kind": "port",
-                       "sample": f"{n} forward passes of {b} rows in {el:.1f} s, torch CPU fp64"}
+                arm, _, _ = cpu_arm_c2()
+                b = min(args.batch or 262144, 65536)
+                xi = torch.randn((b, 784), dtype=torch.float64)
+                arm.forward(xi)
+                n, t0 = 0, time.perf_counter()
+                while time.perf_counter() - t0 < 10.0:
+                    arm.forward(xi); n += 1
+                el = time.perf_counter() - t0
+                cpu = {"value": b * n / el, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": arm.kind,
+                       "sample": f"{n} forward passes of {b} rows in {el:.1f} s, fp64, {arm.describe()}"}
+        cfg = dict(native_config(args, world))
+        cfg["picked"] = why
         line = dict(metric=res["metric"], value=res["value"], unit=res["unit"], n_gpus=world, steps=args.steps,
                     warmup=args.warmup, ms_per_step=res["ms_per_step"], higher_is_better=True,
                     scaling=res.get("scaling", "weak"),
-                    vs_baseline=None, dtype=res["dtype"], data="synthetic", config=res["config"], e2e=res["e2e"],
+                    vs_baseline=None, dtype=res["dtype"], data="synthetic", config=cfg, e2e=res["e2e"],
                     gpu_launches=res["gpu_launches"], clocks=res["clocks"], roofline=res["roofline"],
                     cpu_baseline=cpu, impl="native", host_numa=numa)
+        line.update(res.get("extras") or {})
+        if secondary is not None:
+            line["secondary"] = secondary
         print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist

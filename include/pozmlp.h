@@ -200,6 +200,31 @@ int poz_train_backward(poz_ctx* ctx, const void* x_dev, const void* target_dev,
                        int diagnostics, void* stream);
 int poz_train_apply(poz_ctx* ctx, void* stream);
 
+/* ---- unit operators: ONE entry of the reference's layer list per call -------------------------------
+ * What the drop-in's Layer objects run when their forward() is called directly, as the reference's tests do
+ * (test_neural_net_model.py:13-66), and what NeuralNetworkModel._forward chains when it is asked for every
+ * entry's output without a target (neural_net_model.py:389-396).  Stateless: device pointers in the given
+ * dtype (POZ_DTYPE_F32 / POZ_DTYPE_F64) in and out, row-major, nothing allocated, nothing kept.
+ *   poz_op_linear      LinearLayer.forward (:110-120): y[rows][out] = x[rows][in] @ w[in][out], then += b[out]
+ *                      (b_dev may be NULL: bias_algo "" gives a layer without bias, :105).
+ *   poz_op_activation  ReluLayer / SigmoidLayer / TanhLayer / SoftmaxLayer.forward (:172-188), POZ_ACT_*;
+ *                      softmax is over the last dimension (cols).  POZ_ACT_NONE copies (Layer.forward, :48-53).
+ *   poz_op_embedding   EmbeddingLayer.forward (:67-68): y[n][dim] = table[idx[n]][:], idx int32 in [0, vocab).
+ *   poz_op_batchnorm   BatchNormLayer.forward (:158-170).  training != 0: mean and UNBIASED variance of the batch
+ *                      (over the rows, per column) normalise it and move run_mean / run_var by `momentum`
+ *                      (:161-166); otherwise the running statistics are used (:168).  scalar_stats != 0: one mean /
+ *                      variance over every element, broadcast to all columns -- what the reference computes for a
+ *                      1-D input in training mode, where `dim = ()` reduces over everything (:160-162). */
+int poz_op_linear(int device, int dtype_code, const void* x_dev, const void* w_dev, const void* b_dev, long long rows,
+                  int in, int out, void* y_dev, void* stream);
+int poz_op_activation(int device, int dtype_code, int act, const void* x_dev, long long rows, int cols, void* y_dev,
+                      void* stream);
+int poz_op_embedding(int device, int dtype_code, const void* table_dev, int vocab, int dim, const int* idx_dev,
+                     long long n, void* y_dev, void* stream);
+int poz_op_batchnorm(int device, int dtype_code, int training, int scalar_stats, const void* x_dev, long long rows, int cols,
+                     const void* gain_dev, const void* bias_dev, void* run_mean_dev, void* run_var_dev, double eps,
+                     double momentum, void* y_dev, void* stream);
+
 /* ---- tcgen05 GEMM building block (new; the dense contractions of LinearLayer.forward,
  * neural_net_model.py:117, and of its autograd backward, :495, for wide layers) -----------------
  * bf16 row-major device matrices, fp32 accumulation in tensor memory.  Exposed so that the three

@@ -22,7 +22,7 @@ OPT_SGD, OPT_ADAM = 0, 1
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
-SOURCES = ["poz_api.cu", "poz_noalloc.cu", "poz_tc.cu", "poz_tc3.cu"]
+SOURCES = ["poz_api.cu", "poz_noalloc.cu", "poz_ops.cu", "poz_tc.cu", "poz_tc3.cu"]
 
 
 class PozError(RuntimeError):
@@ -71,19 +71,37 @@ def _stale() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile libpozmlp.so in-tree with nvcc for sm_100a (cross-compiles without a GPU)."""
+    """Compile libpozmlp.so in-tree with nvcc for sm_100a (cross-compiles without a GPU).  The translation
+    units are compiled side by side (objects under build/obj, git-ignored) and linked into the one library;
+    only units whose sources are newer than their object are recompiled."""
     if not force and not _stale():
         return LIB_PATH
+    from concurrent.futures import ThreadPoolExecutor
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + _sources() + ["-o", LIB_PATH]
+    obj_dir = os.path.join(os.path.dirname(_HERE), "build", "obj")
+    os.makedirs(obj_dir, exist_ok=True)
+    headers = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if not f.endswith(".cu")] + [HEADER_PATH]
+    newest_header = max(os.path.getmtime(h) for h in headers)
+    flags = [f for f in NVCC_FLAGS if f != "-shared"]
+
+    def compile_one(src):
+        obj = os.path.join(obj_dir, os.path.basename(src)[:-3] + ".o")
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), newest_header):
+            return obj, ""
+        cmd = [nvcc] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        proc = subprocess.run(cmd, capture_output=True, text=True)
+        if proc.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+        return obj, proc.stderr
+
+    with ThreadPoolExecutor(max_workers=len(SOURCES)) as pool:
+        results = list(pool.map(compile_one, _sources()))
     if verbose:
-        cmd.insert(1, "-Xptxas")
-        cmd.insert(2, "-v")
+        print("".join(r[1] for r in results))
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC"] + [r[0] for r in results] + ["-o", LIB_PATH]
     proc = subprocess.run(cmd, capture_output=True, text=True)
     if proc.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + proc.stdout + proc.stderr)
-    if verbose:
-        print(proc.stderr)
+        raise RuntimeError("nvcc link failed:\n" + " ".join(cmd) + "\n" + proc.stdout + proc.stderr)
     return LIB_PATH
 
 
@@ -128,6 +146,10 @@ SIGNATURES = {
     "poz_grad_layer": (_I, [_VP, _I, C.POINTER(_VP), C.POINTER(_LL), _VP]),
     "poz_train_backward": (_I, [_VP, _VP, _VP, _VP, _LL, C.POINTER(_VP), _I, _VP]),
     "poz_train_apply": (_I, [_VP, _VP]),
+    "poz_op_linear": (_I, [_I, _I, _VP, _VP, _VP, _LL, _I, _I, _VP, _VP]),
+    "poz_op_activation": (_I, [_I, _I, _I, _VP, _LL, _I, _VP, _VP]),
+    "poz_op_embedding": (_I, [_I, _I, _VP, _I, _I, _VP, _LL, _VP, _VP]),
+    "poz_op_batchnorm": (_I, [_I, _I, _I, _I, _VP, _LL, _I, _VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP, _VP]),
     "poz_tc_gemm": (_I, [_I, _I, _VP, _VP, _LL, _I, _LL, _VP, _VP, _VP, _I, _I, _VP]),
     "poz_tc3_gemm": (_I, [_I, _I, _VP, _VP, _LL, _I, _LL, _VP, _VP, _VP, _I, _I, _VP]),
     "poz_forward_noalloc": (_I, [_I, _I, C.POINTER(_I), C.POINTER(_I), C.POINTER(_VP), C.POINTER(_VP),

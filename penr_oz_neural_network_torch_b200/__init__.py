@@ -5,5 +5,6 @@ reference's ``from neural_net_model import NeuralNetworkModel``.
 """
 from ._native import PozError, build, launch_count  # noqa: F401
 from .engine import DeviceMLP, HostBatchFeeder, StackSpec, bind_host_to_gpu_numa_node  # noqa: F401
-from .neural_net_model import (Layer, LinearLayer, MultiLayerPerceptron, NeuralNetworkModel,  # noqa: F401
-                               ReluLayer, SigmoidLayer, SoftmaxLayer, TanhLayer)
+from .neural_net_model import (BatchNormLayer, EmbeddingLayer, FlattenLayer, Layer, LinearLayer,  # noqa: F401
+                               MultiLayerPerceptron, NeuralNetworkModel, ReluLayer, SigmoidLayer, SoftmaxLayer,
+                               TanhLayer)

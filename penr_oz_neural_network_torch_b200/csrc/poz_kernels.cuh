@@ -24,7 +24,7 @@ struct SegTable {
 
 // First kernel of every step: advances the epoch / Adam counters and derives the step's scalars
 // (neural_net_model.py:464 lr decay; torch/optim/adam.py bias corrections).
-__global__ void step_begin_kernel(DevState* st, double* cost_ring, long long cost_cap,
+static __global__ void step_begin_kernel(DevState* st, double* cost_ring, long long cost_cap,
                                   double* stats, long long stats_cap, int n_layers, double l2_share) {
     pdl_trigger();
     pdl_wait();
@@ -383,7 +383,7 @@ __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restri
 // Bias gradient db[n] = sum_b dz[b][n] for float32 dz (test_torch_backward.py:166), two
 // deterministic passes: block (x, r) sums rows r*8+warp, +8*gridDim.y, ... of 64 columns into
 // partial[r][n]; the second pass adds the gridDim.y partials in a fixed order.
-__global__ void colsum_f32_partial_kernel(const float* __restrict__ dz, long long rows, int N, float* __restrict__ partial) {
+static __global__ void colsum_f32_partial_kernel(const float* __restrict__ dz, long long rows, int N, float* __restrict__ partial) {
     __shared__ float red[8][64];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c0 = blockIdx.x * 64 + lane, c1 = c0 + 32;
@@ -403,7 +403,7 @@ __global__ void colsum_f32_partial_kernel(const float* __restrict__ dz, long lon
         if (cc < N) partial[(long long)blockIdx.y * N + cc] = t;
     }
 }
-__global__ void colsum_f32_final_kernel(const float* __restrict__ partial, int parts, int N, float* __restrict__ out) {
+static __global__ void colsum_f32_final_kernel(const float* __restrict__ partial, int parts, int N, float* __restrict__ out) {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
     float t = 0.f;

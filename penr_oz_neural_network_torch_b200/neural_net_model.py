@@ -28,6 +28,7 @@ import numpy as np
 import torch
 from torch import Tensor
 
+from . import unit_ops
 from .engine import ACTIVATIONS, DeviceMLP, StackSpec
 
 log = logging.getLogger(__name__)
@@ -39,8 +40,10 @@ DEFAULT_DTYPE = os.environ.get("POZ_DTYPE", "float32")
 
 
 class Layer:
-    """Parameter container + topology flags of one entry (neural_net_model.py:16-53).  Entries
-    hold no compute: the stack is executed as a whole by the CUDA library."""
+    """Parameter container + topology flags of one entry (neural_net_model.py:16-53).  ``train`` and
+    ``compute_output`` execute the stack as a whole in the CUDA library; ``forward`` runs this one entry on
+    the device through the unit operators (``poz_op_*``), for callers that drive a layer directly as the
+    reference's tests do, and for ``_forward`` without a target."""
     algo = ""
 
     def __init__(self):
@@ -48,6 +51,41 @@ class Layer:
         self.training = False
         self.weights: Tensor | None = None
         self.bias: Tensor | None = None
+
+    def forward(self, input_tensor: Tensor) -> Tensor:
+        """:param input_tensor: 1-D vector or 2-D batch matrix (any leading dimensions)
+        :return: the forwarded tensor, float64 where the input lives (neural_net_model.py:48-53)"""
+        if self._identity():
+            return input_tensor                                       # Layer.forward is the identity (:53)
+        chain = unit_ops.Chain()
+        t = torch.as_tensor(input_tensor)
+        return chain.leave(self._run(chain, chain.enter(t, as_index=self.algo == "embedding")), t)
+
+    def _identity(self) -> bool:
+        return type(self)._run is Layer._run
+
+    def _run(self, chain: "unit_ops.Chain", x: Tensor) -> Tensor:
+        """device tensor in, device tensor out"""
+        return x
+
+    def _on_device(self, name: str, chain: "unit_ops.Chain") -> Tensor | None:
+        """Device copy of parameter ``name`` in the chain's dtype, refreshed when the host tensor changed."""
+        host = getattr(self, name)
+        if host is None:
+            return None
+        cache = self.__dict__.setdefault("_dev_cache", {})
+        key = (name, chain.dtype, chain.dev.index)
+        tag = (id(host), host._version)
+        hit = cache.get(key)
+        if hit is None or hit[0] != tag:
+            hit = (tag, unit_ops.to_device(host, chain.dtype, chain.dev))
+            cache[key] = hit
+        return hit[1]
+
+    @staticmethod
+    def _rows(x: Tensor) -> Tensor:
+        """[..., features] -> [rows, features]"""
+        return x.reshape(-1, x.shape[-1]) if x.ndim != 2 else x
 
     @property
     def params(self) -> list[Tensor]:
@@ -79,6 +117,12 @@ class LinearLayer(Layer):
                 self.bias = (torch.zeros(output_size) if bias_algo == "zeros"
                              else torch.randn(output_size)).double()
 
+    def _run(self, chain, x):
+        """x @ W, then += b (neural_net_model.py:110-120); 1-D and batched inputs alike"""
+        w = self._on_device("weights", chain)
+        y = unit_ops.linear(self._rows(x), w, self._on_device("bias", chain), chain.dtype, chain.dev)
+        return y.reshape(*x.shape[:-1], w.shape[1])
+
 
 class EmbeddingLayer(Layer):
     """Lookup table (neural_net_model.py:55-68); the gather / scatter-add run in emb_*_kernel."""
@@ -88,6 +132,19 @@ class EmbeddingLayer(Layer):
         super().__init__()
         if vocab_size > 0 and embedding_size > 0:
             self.weights = torch.randn(vocab_size, embedding_size).double()
+
+    def _run(self, chain, idx):
+        """W[idx.long()] (neural_net_model.py:67-68): idx of any shape -> [..., embedding_size]"""
+        table = self._on_device("weights", chain)
+        vocab = table.shape[0]
+        if idx.numel():
+            lo, hi = int(idx.min()), int(idx.max())
+            if lo < -vocab or hi >= vocab:
+                raise IndexError(f"index {hi if hi >= vocab else lo} is out of bounds for dimension 0 with size {vocab}")
+            if lo < 0:
+                idx = torch.where(idx < 0, idx + vocab, idx)
+        y = unit_ops.embedding(table, idx.reshape(-1).contiguous(), chain.dtype, chain.dev)
+        return y.reshape(*idx.shape, table.shape[1])
 
 
 class FlattenLayer(Layer):
@@ -105,6 +162,21 @@ class FlattenLayer(Layer):
     @state_dict.setter
     def state_dict(self, new_state: dict):
         self.ratio = new_state["ratio"]
+
+    def forward(self, input_tensor: Tensor) -> Tensor:
+        return self._run(None, input_tensor)
+
+    def _run(self, chain, x):
+        """Merge `ratio` rows into one (neural_net_model.py:82-91): a view of the same row-major memory, on the
+        host or on the device -- there is nothing to compute."""
+        if x.ndim > 1:
+            shape = list(x.shape)
+            shape[-2] //= self.ratio
+            shape[-1] *= self.ratio
+            x = x.reshape(*shape)
+            if shape[-2] == 1:
+                x = x.squeeze(len(shape) - 2)
+        return x
 
 
 class BatchNormLayer(Layer):
@@ -140,22 +212,49 @@ class BatchNormLayer(Layer):
         self.eps = new_state["eps"]
         self.momentum = new_state["momentum"]
 
+    def _run(self, chain, x):
+        """neural_net_model.py:158-170: batch statistics (unbiased variance) and a move of the running statistics
+        when ``training``, the running statistics otherwise.  A 1-D input in training mode reduces over all of
+        its elements (``dim = ()``), giving one mean / variance for every feature -- reproduced as is."""
+        tdt = unit_ops._TORCH[chain.dtype]
+        mean = self.mean.reshape(-1).to(device=chain.dev, dtype=tdt).contiguous().clone()
+        var = self.variance.reshape(-1).to(device=chain.dev, dtype=tdt).contiguous().clone()
+        scalar = bool(self.training and x.ndim == 1)
+        x2 = x.reshape(1, -1) if x.ndim == 1 else self._rows(x)
+        y = unit_ops.batchnorm(x2, self._on_device("gain", chain), self._on_device("bias", chain), mean, var,
+                               self.eps, self.momentum, self.training, scalar, chain.dtype, chain.dev)
+        if self.training:
+            # the reference's running statistics take the keepdim shape of the batch statistics (:161-166)
+            keep = [1] * (x.ndim - 1) + [x.shape[-1]] if x.ndim >= 2 else [x.shape[-1]]
+            self.mean = mean.to("cpu", torch.float64).reshape(keep)
+            self.variance = var.to("cpu", torch.float64).reshape(keep)
+        return y.reshape(x.shape)
 
-class SigmoidLayer(Layer):
+
+class _ActivationLayer(Layer):
+    def _run(self, chain, x):
+        """element-wise sigmoid / relu / tanh, softmax over the last dimension (neural_net_model.py:172-188)"""
+        if x.ndim == 0:
+            x = x.reshape(1)
+        y = unit_ops.activation(x.reshape(1, -1) if x.ndim == 1 else self._rows(x), self.algo, chain.dtype, chain.dev)
+        return y.reshape(x.shape)
+
+
+class SigmoidLayer(_ActivationLayer):
     algo = "sigmoid"
 
 
-class ReluLayer(Layer):
+class ReluLayer(_ActivationLayer):
     algo = "relu"
     weight_gain = _GAIN["relu"]
 
 
-class TanhLayer(Layer):
+class TanhLayer(_ActivationLayer):
     algo = "tanh"
     weight_gain = _GAIN["tanh"]
 
 
-class SoftmaxLayer(Layer):
+class SoftmaxLayer(_ActivationLayer):
     algo = "softmax"
 
 
@@ -177,6 +276,21 @@ def expand_algos(activation_algos: list[str]) -> list[str]:
         elif algo == "embedding" and requested[i + 1] != "flatten":
             expanded.insert(i + 1, "flatten")
     return expanded
+
+
+class _DeviceCost(torch.autograd.Function):
+    """The scalar cost of a device pass as an autograd node whose inputs are the model's parameters: its
+    backward hands out the parameter gradients the CUDA backward pass computed (scaled by the incoming
+    gradient, so ``(2 * cost).backward()`` behaves)."""
+
+    @staticmethod
+    def forward(ctx, cost, grads, *params):
+        ctx.grads = grads
+        return cost.clone()
+
+    @staticmethod
+    def backward(ctx, upstream):
+        return (None, None) + tuple(upstream * g for g in ctx.grads)
 
 
 class MultiLayerPerceptron:
@@ -449,9 +563,37 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         return t.to(eng.tdtype).to(eng.device).contiguous()
 
     def _forward(self, input_tensor: Tensor, target: list, dropout_rate=0.0) -> Tuple[list[Tensor], Tensor]:
-        """Tensor-level forward (+ loss when a target is given).  Returns ``([final_output], cost)``
-        as float64 CPU tensors; ``cost`` is ``torch.empty(0)`` without a target (:399).  Gradients
-        do not flow through this call -- the backward pass lives in ``train``."""
+        """Tensor-level forward (+ loss when a target is given): the output of EVERY entry of the layer list, as
+        float64 CPU tensors of the reference's shapes, and the cost (``torch.empty(0)`` without a target, :399).
+
+        Without a target the entries run one after the other on the device through their own ``forward``
+        operators (neural_net_model.py:389-396, ``layer.training = False``).
+
+        With a target the stack runs as ONE training-mode pass of the fused kernels -- dropout at
+        ``dropout_rate`` on every hidden entry (masks drawn in the kernels), batchnorm on batch statistics
+        (running statistics move, :161-166), the configured loss -- followed by its backward pass, and the
+        results are tied into autograd: ``cost.backward()`` puts the kernels' gradients into ``p.grad`` of
+        every parameter that requires grad and into ``a.grad`` of every returned activation (``None`` for a
+        trailing softmax, which is not on the loss graph, :545); terms added to ``cost`` by the caller (the L2
+        sum of :482-483) differentiate as usual.  Gradients reach the parameters through ``cost`` only: an
+        objective the caller builds from the returned activations stops at those tensors."""
+        target_specified = target is not None and all(t is not None for t in target)
+        for layer in self.layers:
+            layer.training = target_specified                        # :390
+        x = torch.as_tensor(input_tensor)
+        if not target_specified:
+            chain = unit_ops.Chain(self._dtype if self._dtype in ("float32", "float64") else "float32", self._device)
+            cur = chain.enter(x, as_index=self.layers[0].algo == "embedding")
+            outs = []
+            for layer in self.layers:
+                cur = layer._run(chain, cur)
+                outs.append(cur)
+            return [o.to("cpu", torch.float64) for o in outs], torch.empty(0)
+        return self._forward_with_loss(x, target, float(dropout_rate))
+
+    def _forward_last(self, input_tensor: Tensor, target: list) -> Tuple[Tensor, Tensor]:
+        """What ``compute_output`` needs of ``_forward``: the last entry's output and the cost, through the
+        fused inference kernels (poz_forward / poz_forward_loss)."""
         target_specified = target is not None and all(t is not None for t in target)
         eng = self._ensure_engine()
         x = torch.as_tensor(input_tensor, dtype=torch.float64)
@@ -469,12 +611,70 @@ class NeuralNetworkModel(MultiLayerPerceptron):
             out = eng.forward(xd)
             cost_t = torch.empty(0)
         out = out.to("cpu", torch.float64)
-        return [out if batched else out[0]], cost_t
+        return (out if batched else out[0]), cost_t
+
+    def _entry_shapes(self, spec: StackSpec, batch: int, batched: bool) -> list[tuple]:
+        """Shape of every entry's output as the reference produces it for a [batch, features] (or, with an
+        embedding head, [batch, tokens]) input; the leading batch dimension is absent for a single sample."""
+        shapes = []
+        rows, width = 1, None
+        for layer in self.layers:
+            if layer.algo == "embedding":
+                rows, width = spec.tokens, layer.weights.shape[1]
+            elif layer.algo == "flatten":
+                rows, width = rows // layer.ratio, width * layer.ratio
+            elif layer.algo == "linear":
+                width = layer.weights.shape[1]
+            lead = (batch,) if batched else ()
+            if layer.algo == "embedding" or rows > 1:
+                shapes.append(lead + (rows, width))
+            else:
+                shapes.append(lead + (width,))
+        return shapes
+
+    def _forward_with_loss(self, x: Tensor, target: list, dropout_rate: float):
+        eng = self._ensure_engine()
+        spec = self.stack
+        batched = x.ndim == 2
+        xd = self._inputs_to_device(eng, (x if batched else x.unsqueeze(0)).to(torch.float64))
+        td = self._targets_to_device(eng, target, batched)
+        batch = xd.shape[0]
+        # One step with learning rate 0 (plain SGD: p -= 0 * g leaves the parameters, and Adam's state is not
+        # touched), recorded in diagnostics mode: every entry's output, its gradient and every parameter
+        # gradient of exactly this pass stay on the device.
+        eng.train_begin(optimizer="sgd", learning_rate=0.0, decay_rate=1.0, dropout_rate=dropout_rate, l2_lambda=0.0,
+                        epochs=1, progress_stride=0, dropout_seed=random.getrandbits(63))
+        side = torch.cuda.Stream(device=eng.device)
+        side.wait_stream(torch.cuda.current_stream(eng.device))
+        with torch.cuda.stream(side):
+            eng.train_step(xd, td, diagnostics=True)
+        side.synchronize()
+        cost_value = float(eng.costs(0, 1)[0])
+        if eng.general:
+            self._download_running_stats()
+        loc = self._entry_locations(spec)
+        shapes = self._entry_shapes(spec, batch, batched)
+        outs, out_grads = [], []
+        for i in range(len(self.layers)):
+            li, which = loc[i]
+            a = torch.from_numpy(eng.diag_activation(li, which, batch)).reshape(shapes[i])
+            g = eng.diag_activation_grad(li, which, batch)
+            outs.append(a.clone().requires_grad_())
+            out_grads.append(None if g is None else torch.from_numpy(g).reshape(shapes[i]).clone())
+        slots = self._param_slots(spec)
+        param_grads = [torch.from_numpy(eng.download_tensor(kind, l, "diag_grad")).reshape(t.shape).clone()
+                       for t, kind, l in slots]
+        cost = _DeviceCost.apply(torch.tensor(cost_value, dtype=torch.float64), param_grads, *[t for t, _, _ in slots])
+        for a, g in zip(outs, out_grads):
+            if g is not None:
+                # exactly zero in value; its derivative hands the kernels' gradient of this entry to a.grad
+                cost = cost + ((a - a.detach()) * g).sum()
+        return outs, cost
 
     def compute_output(self, input_data: list, target: list = None) -> Tuple[list, float]:
         input_tensor = torch.tensor(input_data, dtype=torch.float64)  # :379
-        activations, cost = self._forward(input_tensor, target)
-        return activations[-1].tolist(), cost.item() if cost.numel() > 0 else None
+        last, cost = self._forward_last(input_tensor, target)
+        return last.tolist(), cost.item() if cost.numel() > 0 else None
 
     # ------------------------------------------------------------------ train (:410-530)
     def train(self, training_data: list[Tuple[list[float], list[float]]], epochs=100, learning_rate=0.01,

@@ -60,7 +60,11 @@ NCU_TRAFFIC_C3 = {262144: 1_348_500_000}
 NCU_TRAFFIC_SOURCE = "ncu --set full, profiles/ncu/r01_c2_simt_full_raw_v3.csv"
 TC3_MMAS_PER_PRODUCT = 6
 NCU_TRAFFIC = {"fwd_l0": 4_344_064, "bwd_w_l0": 4_307_712, "fwd_l1": 1_508_608, "bwd_w_l1": 1_620_736,
-               "bwd_w_l2": 613_376, "bwd_x_l1": 1_769_728, "tc_fwd": 1_204_000_000}
+               "bwd_w_l2": 613_376, "bwd_x_l1": 1_769_728, "tc_fwd": 1_204_000_000,
+               # r02: ncu --set full of the cluster split-K tcgen05 launches (profiles/r02/ncu_tcs_raw_v1.csv)
+               "tcs_fwd_l0": 4_497_664, "tcs_bwd_w_l0_update": 7_271_680}
+NCU_TRAFFIC_SOURCES = {"tcs_fwd_l0": "ncu --set full, profiles/r02/ncu_tcs_raw_v1.csv",
+                       "tcs_bwd_w_l0_update": "ncu --set full, profiles/r02/ncu_tcs_raw_v1.csv"}
 
 
 def peaks():
@@ -188,15 +192,24 @@ def synth_pool(n_batches, batch, device, seed):
 # ---- kernel-level algorithmic work, for the roofline of the dominant kernel ------------------------
 def kernel_work(tag, batch):
     """(algorithmic bytes, flops) of one launch of kernel `tag` at C2 shapes (fp32)."""
-    if tag[:5] in ("fwd_l", "bwd_w", "bwd_x"):
-        l = int(tag.rsplit("l", 1)[1])
+    core = tag[4:] if tag.startswith("tcs_") else tag
+    if core[:5] in ("fwd_l", "bwd_w", "bwd_x"):
+        l = int(core.split("_l", 1)[1].split("_")[0])
         k, n = SIZES[l], SIZES[l + 1]
-        if tag.startswith("fwd_l"):       # read X, [W;b]; write the recorded output
-            return 4 * (batch * k + (k + 1) * n + batch * n), 2 * batch * (k + 1) * n
-        if tag.startswith("bwd_w"):       # read X, dZ; write [dW;db]
+        if core.startswith("fwd_l"):       # read X, [W;b] (as 3 bf16 planes on the tensor path); write the recorded output
+            wbytes = 6 * k * n + 4 * n if tag.startswith("tcs_") else 4 * (k + 1) * n
+            return 4 * (batch * k + batch * n) + wbytes, 2 * batch * (k + 1) * n
+        if core.startswith("bwd_w"):       # read X, dZ; write [dW;db]
+            if tag.endswith("_update"):    # tensor path with the optimizer in the epilogue: dZ as planes, Adam's read / write of
+                                           # w, m, v instead of the gradient, and the new weights' planes
+                return 4 * batch * k + 6 * batch * n + 4 * 6 * (k + 1) * n + 6 * k * n, 2 * batch * (k + 1) * n + 12 * (k + 1) * n
             return 4 * (batch * k + batch * n + (k + 1) * n), 2 * batch * (k + 1) * n
         return 4 * (batch * n + k * n + 2 * batch * k), 2 * batch * k * n     # read dZ, W, a_prev; write dZ_prev
-    if tag == "update":                   # read g, P, m, v; write P, m, v
+    if tag.startswith("update"):          # read g, P, m, v; write P, m, v
+        if tag.startswith("update_l"):
+            l = int(tag[8:])
+            npar = (SIZES[l] + 1) * SIZES[l + 1]
+            return 4 * 7 * npar, 12 * npar
         return 4 * 7 * N_PARAMS, 12 * N_PARAMS
     if tag == "loss":
         return 4 * (3 * batch * 10 + batch), 40 * batch
@@ -351,7 +364,7 @@ def run_c2(args, world, rank, local):
         on_tensor = top.startswith("tc3_") or top.startswith("tcs_")
         hbm = {"achieved": round(gbs, 1), "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(gbs / pk["hbm_gbs"], 4),
                "algorithmic_bytes_per_launch": nbytes, "traffic": NCU_TRAFFIC.get(top),
-               "traffic_source": NCU_TRAFFIC_SOURCE if top in NCU_TRAFFIC else None}
+               "traffic_source": NCU_TRAFFIC_SOURCES.get(top, NCU_TRAFFIC_SOURCE) if top in NCU_TRAFFIC else None}
         if on_tensor:
             # fp32-grade product = TC3_MMAS_PER_PRODUCT bf16 MMAs (hi/mid/lo planes): the tensor pipe is the binding bound
             tf = TC3_MMAS_PER_PRODUCT * flops / per_launch_s / 1e12

@@ -12,6 +12,7 @@
 #include "poz_tf32x3_tma_gemm.cuh"
 #include "poz_tc.h"
 #include "poz_tc3.h"
+#include "poz_tcs.h"
 #include "poz_wide_kernels.cuh"
 
 #include <algorithm>
@@ -475,6 +476,7 @@ static int tc3_refresh_weights(poz_ctx* c, cudaStream_t stream, int upto = -1) {
         c->wp_fresh.assign(c->nl, 0);
         c->wp_stale = false;
     }
+    if (c->tcs_live && !c->wp_fresh.empty()) c->wp_fresh[0] = 1;      // maintained by every writer of layer 0
     for (int l = 0; l < upto; ++l) {
         if (c->wp_fresh[l]) continue;
         c->wp_fresh[l] = 1;
@@ -485,6 +487,17 @@ static int tc3_refresh_weights(poz_ctx* c, cudaStream_t stream, int upto = -1) {
                                   (long long)K * c->wp_ld[l], stream));
     }
     return 0;
+}
+
+// Small-batch tensor-core path (csrc/poz_tcs_kernel.cuh): once a context has taken it, the bf16 planes of layer
+// 0's weights are kept equal to the parameters at every point where those change -- the fused update writes them,
+// every other writer (a plain update kernel, an upload) is followed by this split -- so a step replayed from a
+// CUDA graph never depends on host-side freshness flags.
+static int tcs_split_w0(poz_ctx* c, cudaStream_t stream) {
+    const int K = c->sizes[0], N = c->sizes[1];
+    ProfScope ps(c, "split_w0", stream);
+    return tc3::split_planes(static_cast<const float*>(c->P) + c->off[0], nullptr, K, N, N,
+                             static_cast<__nv_bfloat16*>(c->Wp) + c->wp_off[0], c->wp_ld[0], (long long)K * c->wp_ld[0], stream);
 }
 
 static tc3::PlaneMat tc3_weight(const poz_ctx* c, int l) {
@@ -793,6 +806,7 @@ static void plan_splits(poz_ctx* c, long long batch, SegTable& seg, std::vector<
     }
 }
 
+static int hb0(const poz_ctx* c) { return c->has_bias ? 1 : 0; }
 static int n_stat_slots(const poz_ctx* c) { return c->nl + (c->emb_vocab > 0 ? 1 : 0); }
 
 static void fill_seg(const poz_ctx* c, SegTable& seg) {
@@ -865,6 +879,56 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             }
             if (!c->Wp) POZ_TRY(tc3_refresh_weights(c, stream, 0));   // allocation only
             if (!c->colsum_scratch) POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->colsum_scratch), (size_t)32 * c->sizes[1] * sizeof(float)));
+        }
+    }
+    // Below the batch where the persistent plane kernels pay (tc0), the first layer's two deep contractions run as
+    // cluster split-K tcgen05 launches that convert their fp32 operand on the fly (poz_tcs_kernel.cuh).
+    bool tcs0 = false, tcs_fused = false, tcs_all = false;
+    int tcs_f_splits = 1, tcs_w_splits = 1;
+    if constexpr (std::is_same<T, float>::value) {
+        const int sms = num_sms(c->device);
+        const int K0 = c->sizes[0], N0 = c->sizes[1];
+        tcs0 = c->tcs_enabled && !c->fused_step && !tc0 && nl >= 2 && c->acts[0] != ACT_SOFTMAX && K0 >= 128 && N0 >= 32 && N0 % 4 == 0 &&
+               batch >= c->tcs_min_batch && batch <= c->tcs_max_batch;
+        if (tcs0) {
+            tcs_f_splits = tcs::pick_splits(K0, ((batch + tcs::BM - 1) / tcs::BM) * ((N0 + tcs::BN - 1) / tcs::BN), sms);
+            tcs_w_splits = tcs::pick_splits(batch, (long long)((K0 + hb0(c) + tcs::BM - 1) / tcs::BM) * ((N0 + tcs::BN - 1) / tcs::BN), sms);
+            tcs0 = tcs_f_splits > 0 && tcs_w_splits > 0;
+        }
+        if (tcs0) {
+            if (!c->Wp) POZ_TRY(tc3_refresh_weights(c, stream, 0));   // allocation only
+            if (!c->tcs_live) { POZ_TRY(tcs_split_w0(c, stream)); c->tcs_live = true; }
+            // With the fused classifier head every layer's dZ is born in a kernel that can also write its planes, and
+            // the weight gradients of ALL layers (same contraction length: the batch) go into ONE grouped launch
+            // whose epilogues apply the optimizer: no side streams, no slabs, no update kernel.
+            {
+                const int hK = c->sizes[nl - 1], hN = c->sizes[nl];
+                const size_t hsm = ((size_t)hK * (hN | 1) + 32 + 8 * (size_t)hK) * sizeof(T);
+                const bool head = c->fuse_head && c->loss == POZ_LOSS_CE && hN <= 32 && hsm <= 96 * 1024;
+                tcs_all = c->tcs_group && head && nl <= tcs::MAX_GROUP;
+                if (tcs_all) {
+                    long long tiles = 0;
+                    for (int l = 0; l < nl; ++l)
+                        tiles += (long long)((c->sizes[l] + hb0(c) + tcs::BM - 1) / tcs::BM) * ((c->sizes[l + 1] + tcs::BN - 1) / tcs::BN);
+                    tcs_w_splits = tcs::pick_splits(batch, tiles, sms);
+                }
+            }
+            if (c->tcs_dzp.size() != (size_t)nl) c->tcs_dzp.assign(nl, nullptr);
+            if (batch > c->tcs_dz_batch || (tcs_all && !c->tcs_dzp[nl - 1])) {
+                for (int l = 0; l < nl; ++l) {
+                    dev_free(c->tcs_dzp[l]);
+                    if (l > 0 && !tcs_all) continue;
+                    const size_t bytes = (size_t)3 * batch * round8(c->sizes[l + 1]) * 2;
+                    POZ_TRY(dev_alloc(&c->tcs_dzp[l], bytes));
+                    POZ_CUDA(cudaMemsetAsync(c->tcs_dzp[l], 0, bytes, stream));     // pad columns stay zero
+                }
+                c->tcs_dz_batch = batch;
+                clear_graphs(c);
+            }
+            tcs_fused = c->in_step && c->tcs_fuse_update;
+            seg.splits[0] = 1;
+            if (tcs_all)
+                for (int l = 0; l < nl; ++l) seg.splits[l] = 1;
         }
     }
     POZ_TRY(ensure_grad_slabs(c, slabs));
@@ -959,6 +1023,26 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
                 continue;
             }
         }
+        if constexpr (std::is_same<T, float>::value) {
+            if (tcs0 && l == 0) {
+                const int K = c->sizes[0], N = c->sizes[1];
+                const float* w = static_cast<const float*>(c->P) + c->off[0];
+                tcs::Gemm g{};
+                g.a = x; g.lda = K; g.row_idx = row_idx; g.a_transposed = 0; g.a_cols = K; g.ones_row = 0;
+                g.M = batch; g.N = N; g.K = K; g.b = tc3_weight(c, 0); g.splits = tcs_f_splits;
+                tcs::FwdEpi fe{};
+                fe.inner.bias = c->has_bias ? w + (long long)K * N : nullptr;
+                fe.inner.inner.z_out = z_out; fe.inner.inner.a_out = a_out; fe.inner.inner.ld = N; fe.inner.inner.act = act;
+                fe.inner.inner.dz = make_drop(c, 0, 0, masks);
+                fe.inner.inner.da = make_drop(c, 0, 1, masks);
+                fe.inner.inner.st = c->st;
+                ProfScope ps(c, "tcs_fwd_l0", stream);
+                POZ_TRY(tcs::forward(g, fe, stream));
+                cur = ab;
+                cur_idx = nullptr;
+                continue;
+            }
+        }
         POZ_TRY(layer_forward<T>(c, l, cur, cur_idx, batch, batch, z_out, a_out, masks, stream));
         cur = (act == ACT_SOFTMAX) ? zb : ab;
         cur_idx = nullptr;
@@ -989,6 +1073,14 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
         h.dz_prev = make_drop(c, p, 0, masks);
         h.inv_batch = 1.0 / (double)gb;
         h.cost_base = c->cost_ring; h.cost_cap = c->cost_cap; h.st = c->st;
+        if constexpr (std::is_same<T, float>::value) {
+            if (tcs_all) {
+                h.dz_planes = static_cast<unsigned short*>(c->tcs_dzp[last]);
+                h.dz_ldp = round8(head_N); h.dz_pstride = batch * round8(head_N);
+                h.dprev_planes = static_cast<unsigned short*>(c->tcs_dzp[p]);
+                h.dprev_ldp = round8(head_K); h.dprev_pstride = batch * round8(head_K);
+            }
+        }
         static bool configured[2] = {false, false};
         if (!configured[sizeof(T) == 8]) {
             POZ_CUDA(cudaFuncSetAttribute(head_ce_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
@@ -1050,11 +1142,13 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     // The weight-gradient GEMM of a layer >= 1 only needs that layer's dZ, so it is forked onto a side
     // stream and runs beside the backward-x chain (each of these launches fills a fraction of the GPU);
     // the compute stream joins again before the update.  Inside a graph capture this becomes a fork/join.
-    const bool fork = c->fork_dw && c->side_stream && nl >= 2;
+    const bool fork = c->fork_dw && c->side_stream && nl >= 2 && !tcs_all;
+    bool dz0_planes_done = false;      // the epilogue that produced layer 0's dZ also wrote its bf16 planes
     for (int l = last; l >= 0; --l) {
         const int K = c->sizes[l], N = c->sizes[l + 1], hb = c->has_bias;
         const T* dz = static_cast<const T*>(c->dzbuf[l]);
         cudaStream_t ws = stream;
+      if (!tcs_all) {
         if (fork && l >= 1) {
             static const bool two = !(getenv("POZ_FORK_DW_STREAMS") && atoi(getenv("POZ_FORK_DW_STREAMS")) == 1);
             ws = (two && c->side_stream2 && (l & 1)) ? c->side_stream2 : c->side_stream;
@@ -1090,16 +1184,51 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
                 POZ_LAUNCH_CHECK();
             }
             if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
+          } else if (tcs0 && l == 0) {
+            tc3::PlaneMat dzp;
+            dzp.ptr = static_cast<const __nv_bfloat16*>(c->tcs_dzp[0]);
+            dzp.rows = batch; dzp.cols = N; dzp.ld = round8(N); dzp.plane_stride = batch * dzp.ld;
+            if (!dz0_planes_done) {
+                ProfScope ps(c, "split_dz0", stream);
+                POZ_TRY(tc3::split_planes(dz, nullptr, batch, N, N, static_cast<__nv_bfloat16*>(c->tcs_dzp[0]), dzp.ld, dzp.plane_stride, stream));
+            }
+            tcs::Gemm g{};
+            g.a = x; g.lda = K; g.row_idx = row_idx; g.a_transposed = 1; g.a_cols = K; g.ones_row = hb;
+            g.M = (long long)K + hb; g.N = N; g.K = batch; g.b = dzp; g.splits = tcs_w_splits;
+            if (tcs_fused) {
+                tcs::UpdateEpi ue{};
+                ue.p = static_cast<float*>(c->P) + c->off[0];
+                ue.am = static_cast<float*>(c->AM) + c->off[0];
+                ue.av = static_cast<float*>(c->AV) + c->off[0];
+                if (diag) {
+                    if (!c->Gdiag) POZ_TRY(dev_alloc(&c->Gdiag, (size_t)c->p_total * c->esz));
+                    ue.g_diag = static_cast<float*>(c->Gdiag) + c->off[0];
+                }
+                ue.ld = N; ue.w_rows = K; ue.st = c->st; ue.cost_base = c->cost_ring; ue.cost_cap = c->cost_cap;
+                ue.stats = c->stats; ue.n_stat = n_stat_slots(c); ue.stat_slot = seg.stat_slot[0];
+                ue.planes = static_cast<__nv_bfloat16*>(c->Wp) + c->wp_off[0];
+                ue.ldp = c->wp_ld[0]; ue.plane_stride = (long long)K * c->wp_ld[0];
+                ProfScope ps(c, "tcs_bwd_w_l0_update", stream);
+                POZ_TRY(tcs::backward_weight_update(&g, &ue, 1, stream));
+                c->upd_done_mask |= 1u;
+            } else {
+                tcs::StoreEpi se{static_cast<float*>(c->G) + c->off[0], N};
+                ProfScope ps(c, "tcs_bwd_w_l0", stream);
+                POZ_TRY(tcs::backward_weight_store(&g, &se, 1, stream));
+            }
+            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
           } else {
             const float* inp = l == 0 ? x : static_cast<const float*>(c->abuf[l - 1]);
             fast::Op A = make_fast_op(inp, K, l == 0 ? row_idx : nullptr, batch, K);
             fast::Op B = make_fast_op(dz, N, nullptr, batch, N);
             BwdWeightEpi<float> epi;
             epi.g = static_cast<float*>(c->G); epi.slab = c->p_total; epi.off = c->off[l]; epi.ld = N;
-            ProfScope ps(c, "bwd_w_l" + std::to_string(l), ws);
-            if (hb) POZ_TRY((launch_fast<32, 64, false, false, true>(A, B, K, N, batch, seg.splits[l], false, K, epi, ws)));
-            else    POZ_TRY((launch_fast<32, 64, false, false, false>(A, B, K, N, batch, seg.splits[l], false, K, epi, ws)));
-            if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], ws));
+            {
+                ProfScope ps(c, "bwd_w_l" + std::to_string(l), ws);
+                if (hb) POZ_TRY((launch_fast<32, 64, false, false, true>(A, B, K, N, batch, seg.splits[l], false, K, epi, ws)));
+                else    POZ_TRY((launch_fast<32, 64, false, false, false>(A, B, K, N, batch, seg.splits[l], false, K, epi, ws)));
+            }
+            if (c->grad_ready.size() == (size_t)nl && !(tcs_fused && fork && l >= 1)) POZ_CUDA(cudaEventRecord(c->grad_ready[l], ws));
           }
         } else {
             const T* inp = l == 0 ? x : static_cast<const T*>(c->abuf[l - 1]);
@@ -1113,6 +1242,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
                                                   seg.splits[l], kchunk[l], epi, ws)));
             if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], ws));
         }
+      }
         if (l > 0 && !(fuse_head && l == last)) {
             const T* w = static_cast<const T*>(c->P) + c->off[l];
             Operand<T> A = make_operand<T>(dz, N, nullptr, batch, N, 0);
@@ -1126,6 +1256,13 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             epi.da = make_drop(c, l - 1, 1, masks);
             epi.st = c->st;
             epi.da_rec = nullptr; epi.dz_rec = nullptr;
+            if constexpr (std::is_same<T, float>::value) {
+                if (tcs0 && (l == 1 || tcs_all)) {   // dZ of the layer below leaves this epilogue as planes too
+                    epi.planes = static_cast<unsigned short*>(c->tcs_dzp[l - 1]);
+                    epi.ldp = round8(K); epi.plane_stride = batch * round8(K);
+                    if (l == 1) dz0_planes_done = true;
+                }
+            }
             if (diag) {
                 if (c->acts[l - 1] != ACT_NONE) {
                     epi.da_rec = static_cast<T*>(c->da_rec[l - 1]);
@@ -1145,9 +1282,78 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             POZ_TRY((launch_gemm<T, true, true>(pick_tile<T>(c, batch, K), A, B, batch, K, (long long)N, 1,
                                                 (long long)N, epi, stream)));
         }
+        if constexpr (std::is_same<T, float>::value) {
+            if (tcs_fused && fork && l >= 1 && !tcs_all) {
+                // Layer 0's update rides in its weight-gradient launch; this layer's follows its own weight gradient on
+                // the same side stream, so that no update kernel is left on the step's critical path.  It must not
+                // overtake the backward-x launch above, which still reads this layer's weights.
+                if (!(fuse_head && l == last)) {
+                    POZ_CUDA(cudaEventRecord(c->dz_ready[l], stream));
+                    POZ_CUDA(cudaStreamWaitEvent(ws, c->dz_ready[l], 0));
+                }
+                SegTable one;
+                fill_seg(c, one);
+                for (int k = 0; k < one.n; ++k) { one.splits[k] = seg.splits[k]; if (k != l) one.n_elems[k] = 0; }
+                float* gdiag = nullptr;
+                if (diag) {
+                    if (!c->Gdiag) POZ_TRY(dev_alloc(&c->Gdiag, (size_t)c->p_total * c->esz));
+                    gdiag = static_cast<float*>(c->Gdiag);
+                }
+                const int bx = (int)std::max<long long>(1, std::min<long long>((one.n_elems[l] + 255) / 256, 2LL * num_sms(c->device)));
+                ProfScope ps(c, "update_l" + std::to_string(l), ws);
+                POZ_TRY(launch_pdl(update_kernel<float>, dim3(bx, one.n), dim3(256), 0, ws, static_cast<float*>(c->P),
+                                   static_cast<float*>(c->AM), static_cast<float*>(c->AV), static_cast<const float*>(c->G), c->p_total,
+                                   gdiag, one, static_cast<const DevState*>(c->st), c->cost_ring, c->cost_cap, c->stats,
+                                   static_cast<__nv_bfloat16*>(c->Pb)));
+                c->upd_done_mask |= 1u << l;
+                if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], ws));
+            }
+        }
     }
     if (fork)
         for (int l = 1; l < nl; ++l) POZ_CUDA(cudaStreamWaitEvent(stream, c->grad_ready[l], 0));
+    if constexpr (std::is_same<T, float>::value) {
+        if (tcs_all) {
+            // every layer's [dW; db] = [A 1]^T dZ in one grouped launch; its epilogues are the optimizer
+            tcs::Gemm gs[tcs::MAX_GROUP];
+            tcs::UpdateEpi ues[tcs::MAX_GROUP];
+            tcs::StoreEpi ses[tcs::MAX_GROUP];
+            if (diag && tcs_fused && !c->Gdiag) POZ_TRY(dev_alloc(&c->Gdiag, (size_t)c->p_total * c->esz));
+            for (int l = 0; l < nl; ++l) {
+                const int K = c->sizes[l], N = c->sizes[l + 1], hb = c->has_bias;
+                tcs::Gemm& g = gs[l];
+                g = tcs::Gemm{};
+                g.a = l == 0 ? x : static_cast<const float*>(c->abuf[l - 1]);
+                g.lda = K; g.row_idx = l == 0 ? row_idx : nullptr; g.a_transposed = 1; g.a_cols = K; g.ones_row = hb;
+                g.M = (long long)K + hb; g.N = N; g.K = batch; g.splits = tcs_w_splits;
+                g.b.ptr = static_cast<const __nv_bfloat16*>(c->tcs_dzp[l]);
+                g.b.rows = batch; g.b.cols = N; g.b.ld = round8(N); g.b.plane_stride = batch * round8(N);
+                tcs::UpdateEpi& ue = ues[l];
+                ue = tcs::UpdateEpi{};
+                ue.p = static_cast<float*>(c->P) + c->off[l];
+                ue.am = static_cast<float*>(c->AM) + c->off[l];
+                ue.av = static_cast<float*>(c->AV) + c->off[l];
+                ue.g_diag = diag ? static_cast<float*>(c->Gdiag) + c->off[l] : nullptr;
+                ue.ld = N; ue.w_rows = K; ue.st = c->st; ue.cost_base = c->cost_ring; ue.cost_cap = c->cost_cap;
+                ue.stats = c->stats; ue.n_stat = n_stat_slots(c); ue.stat_slot = seg.stat_slot[l];
+                if (l == 0) {
+                    ue.planes = static_cast<__nv_bfloat16*>(c->Wp) + c->wp_off[0];
+                    ue.ldp = c->wp_ld[0]; ue.plane_stride = (long long)K * c->wp_ld[0];
+                }
+                ses[l] = tcs::StoreEpi{static_cast<float*>(c->G) + c->off[l], N};
+            }
+            if (tcs_fused) {
+                ProfScope ps(c, "tcs_bwd_w_all_update", stream);
+                POZ_TRY(tcs::backward_weight_update(gs, ues, nl, stream));
+                c->upd_done_mask |= (1u << nl) - 1u;
+            } else {
+                ProfScope ps(c, "tcs_bwd_w_all", stream);
+                POZ_TRY(tcs::backward_weight_store(gs, ses, nl, stream));
+            }
+            if (c->grad_ready.size() == (size_t)nl)
+                for (int l = 0; l < nl; ++l) POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
+        }
+    }
     c->grads_pending = true;
     c->diag_pending = diag != 0;
     return 0;
@@ -1308,6 +1514,15 @@ template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream
     fill_seg(c, seg);
     if (!reduced)
         for (int l = 0; l < c->nl; ++l) seg.splits[l] = c->seg_splits[l];
+    // layers whose update already ran in the epilogue of their weight-gradient launch
+    const unsigned done = c->upd_done_mask;
+    c->upd_done_mask = 0;
+    const bool l0_done = (done & 1u) != 0;
+    bool anything_left = false;
+    for (int k = 0; k < seg.n; ++k) {
+        if (k < c->nl && ((done >> k) & 1u)) seg.n_elems[k] = 0;
+        anything_left |= seg.n_elems[k] > 0;
+    }
     const long long biggest = biggest_seg(seg);
     static const long long blocks_per_sm = getenv("POZ_UPDATE_BLOCKS_PER_SM") ? std::max(1, atoi(getenv("POZ_UPDATE_BLOCKS_PER_SM"))) : 2;
     int bx = (int)std::min<long long>((biggest + 255) / 256, blocks_per_sm * num_sms(c->device));
@@ -1317,14 +1532,19 @@ template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream
         gdiag = static_cast<T*>(c->Gdiag);
         c->have_diag = true;
     }
-    ProfScope ps(c, "update", stream);
-    POZ_TRY(launch_pdl(update_kernel<T>, dim3(std::max(bx, 1), seg.n), dim3(256), 0, stream,
-                       static_cast<T*>(c->P), static_cast<T*>(c->AM), static_cast<T*>(c->AV),
-                       static_cast<const T*>(c->G), c->p_total, gdiag, seg, static_cast<const DevState*>(c->st), c->cost_ring,
-                       c->cost_cap, c->stats, static_cast<__nv_bfloat16*>(c->Pb)));
+    if (anything_left) {
+        ProfScope ps(c, "update", stream);
+        POZ_TRY(launch_pdl(update_kernel<T>, dim3(std::max(bx, 1), seg.n), dim3(256), 0, stream,
+                           static_cast<T*>(c->P), static_cast<T*>(c->AM), static_cast<T*>(c->AV),
+                           static_cast<const T*>(c->G), c->p_total, gdiag, seg, static_cast<const DevState*>(c->st), c->cost_ring,
+                           c->cost_cap, c->stats, static_cast<__nv_bfloat16*>(c->Pb)));
+    }
     c->grads_pending = false;
     c->diag_pending = false;
     c->wp_stale = true;
+    if constexpr (std::is_same<T, float>::value) {
+        if (c->tcs_live && !l0_done) POZ_TRY(tcs_split_w0(c, stream));   // a plain update of layer 0: its planes follow
+    }
     return 0;
 }
 
@@ -1477,9 +1697,15 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
             POZ_CUDA(cudaMalloc(&buf, sizeof(fast::KernelTraceRec) * (size_t)fast::KTRACE_CAP));
             POZ_CUDA(cudaMemcpyToSymbol(fast::d_ktrace, &buf, sizeof(buf)));
         }
+        POZ_TRY(tcs::trace_enable());
     }
     if (const char* e = getenv("POZ_FUSED_STEP")) c->fused_step = atoi(e) != 0;
     if (const char* e = getenv("POZ_FUSED_STEP_MAX_BATCH")) c->fused_step_max_batch = atoll(e);
+    if (const char* e = getenv("POZ_TCS")) c->tcs_enabled = atoi(e) != 0;
+    if (const char* e = getenv("POZ_TCS_FUSE_UPDATE")) c->tcs_fuse_update = atoi(e) != 0;
+    if (const char* e = getenv("POZ_TCS_GROUP")) c->tcs_group = atoi(e) != 0;
+    if (const char* e = getenv("POZ_TCS_MIN_BATCH")) c->tcs_min_batch = atoll(e);
+    if (const char* e = getenv("POZ_TCS_MAX_BATCH")) c->tcs_max_batch = atoll(e);
     if (const char* e = getenv("POZ_TC3_TRAIN")) c->tc3_train = atoi(e) != 0;
     if (const char* e = getenv("POZ_TC3_TRAIN_MIN_BATCH")) c->tc3_train_min_batch = atoll(e);
     auto fail = [&](void) { poz_ctx_destroy(c); return 1; };
@@ -1623,7 +1849,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     if (c->feed.copy_stream) cudaStreamDestroy(c->feed.copy_stream);
     if (c->feed.read_stream) cudaStreamDestroy(c->feed.read_stream);
     if (c->feed.cost_pinned) cudaFreeHost(c->feed.cost_pinned);
-    if (getenv("POZ_KERNEL_TRACE") && atoi(getenv("POZ_KERNEL_TRACE")) != 0) dump_kernel_trace();
+    if (getenv("POZ_KERNEL_TRACE") && atoi(getenv("POZ_KERNEL_TRACE")) != 0) { dump_kernel_trace(); tcs::trace_dump(); }
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     for (auto e : c->dz_ready) if (e) cudaEventDestroy(e);
@@ -1641,7 +1867,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     dev_free(reinterpret_cast<void*&>(c->bn_part));
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
     dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
-    dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz);
+    dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz); for (auto& q : c->tcs_dzp) dev_free(q);
     for (auto& p : c->step_plans) dev_free(p.d_tasks);
     dev_free(reinterpret_cast<void*&>(c->step_barrier));
     dev_free(reinterpret_cast<void*&>(c->step_trace));
@@ -1707,6 +1933,7 @@ int poz_params_upload(poz_ctx* c, int layer, const double* w, const double* b) {
     POZ_TRY(check_layer(c, layer, "poz_params_upload"));
     POZ_TRY(POZ_DISPATCH(c, put_layer, c, c->P, layer, w, b));
     c->wp_stale = true;
+    if (c->tcs_live && layer == 0) { POZ_TRY(tcs_split_w0(c, nullptr)); POZ_CUDA(cudaDeviceSynchronize()); }
     if (c->dtype == POZ_DTYPE_BF16) {
         const long long n = c->off[layer + 1] - c->off[layer];
         int blocks = (int)std::min<long long>((n + 255) / 256, 4096);
@@ -1741,6 +1968,7 @@ int poz_tensor_io(poz_ctx* c, int kind, int layer, int buffer, int download, dou
     if (buffer == 3) POZ_FAIL("poz_tensor_io: the diagnostics gradient is read-only");
     c->wp_stale = true;
     POZ_TRY(POZ_DISPATCH(c, put_f64, c, base, off, host, n));
+    if (c->tcs_live && buffer == 0 && kind == 0 && layer == 0) { POZ_TRY(tcs_split_w0(c, nullptr)); POZ_CUDA(cudaDeviceSynchronize()); }
     if (c->dtype == POZ_DTYPE_BF16 && buffer == 0 && kind <= 1) {
         int blocks = (int)std::min<long long>((n + 255) / 256, 4096);
         convert_kernel<float, __nv_bfloat16><<<blocks, 256>>>(static_cast<const float*>(c->P) + off,
@@ -1925,9 +2153,20 @@ int poz_train_apply(poz_ctx* c, void* stream) {
 // (everything that changes from step to step lives in DevState on the device), so from the second
 // time a (x, target, row_idx, batch) key is seen the step is captured once into a CUDA graph and
 // replayed: one graph launch instead of ~11 kernel launches of host work per step.
+static int train_step_inner(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
+                            long long batch, const void* const* keep_masks, int diagnostics, void* stream);
+
 int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
                    long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
     POZ_TRY(check_layer(c, 0, "poz_train_step"));
+    c->in_step = true;             // backward and update belong to one call: the update may ride in a backward epilogue
+    const int rc = train_step_inner(c, x_dev, target_dev, row_idx_dev, batch, keep_masks, diagnostics, stream);
+    c->in_step = false;
+    return rc;
+}
+
+static int train_step_inner(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
+                            long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
     if (x_dev && target_dev && c->fused_step && c->step_grid == 0) POZ_TRY(fused_step_probe(c));
     if (x_dev && target_dev && fused_step_eligible(c, batch, keep_masks, diagnostics)) {
         // narrow fp32 stack: the whole step is one persistent kernel (no graph needed: it is one launch)

@@ -83,8 +83,11 @@ struct DropPoint {
     double scale;          // 1 / (1 - p)
 };
 
-__device__ __forceinline__ bool drop_keep(const DropPoint& d, const DevState* st, long long m,
-                                          int n, int ld) {
+// Out of line on purpose: the step's kernels are launch-bound and start with a cold instruction cache, and a
+// Philox evaluation inlined at every epilogue call site (x 4 elements x 2 points) made each of them tens of
+// kilobytes of code that a step without dropout fetches around.  A call keeps the common path compact.
+__device__ __noinline__ static bool drop_keep(const DropPoint& d, const DevState* st, long long m,
+                                              int n, int ld) {
     long long e = m * (long long)ld + n;
     if (d.mask) return d.mask[e] != 0;
     uint32_t r = philox_first((uint32_t)e, (uint32_t)(e >> 32), d.point, (uint32_t)st->cur_epoch,
@@ -93,21 +96,22 @@ __device__ __forceinline__ bool drop_keep(const DropPoint& d, const DevState* st
 }
 
 // ---- activations (neural_net_model.py:172-188) and their derivatives from the OUTPUT value -------
+// relu / identity inline; the transcendental ones out of line (same reason as drop_keep: compact hot code)
+__device__ __noinline__ static double act_fwd_slow(int act, double z) {
+    return act == ACT_SIGMOID ? 1.0 / (1.0 + exp(-z)) : tanh(z);
+}
+__device__ __noinline__ static float act_fwd_slow(int act, float z) {
+    return act == ACT_SIGMOID ? 1.f / (1.f + expf(-z)) : tanhf(z);
+}
 template <typename T> __device__ __forceinline__ T act_fwd(int act, T z) {
-    switch (act) {
-        case ACT_RELU: return z > T(0) ? z : T(0);
-        case ACT_SIGMOID: return T(1) / (T(1) + exp(-z));
-        case ACT_TANH: return tanh(z);
-        default: return z;
-    }
+    if (act == ACT_RELU) return z > T(0) ? z : T(0);
+    if (act == ACT_SIGMOID || act == ACT_TANH) return act_fwd_slow(act, z);
+    return z;
 }
 template <> __device__ __forceinline__ float act_fwd<float>(int act, float z) {
-    switch (act) {
-        case ACT_RELU: return fmaxf(z, 0.f);
-        case ACT_SIGMOID: return 1.f / (1.f + expf(-z));
-        case ACT_TANH: return tanhf(z);
-        default: return z;
-    }
+    if (act == ACT_RELU) return fmaxf(z, 0.f);
+    if (act == ACT_SIGMOID || act == ACT_TANH) return act_fwd_slow(act, z);
+    return z;
 }
 // derivative expressed through the activation output a = act(z)
 template <typename T> __device__ __forceinline__ T act_bwd_from_out(int act, T a) {

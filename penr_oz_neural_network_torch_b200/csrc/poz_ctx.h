@@ -32,6 +32,19 @@ struct poz_ctx {
     // kernels keep the first layer below this batch (POZ_TC3_TRAIN_MIN_BATCH overrides)
     long long tc3_train_min_batch = 8192;
     bool tc3_train = true;            // first layer of float32 training on tcgen05 when it is deep enough
+    // small-batch tensor-core path of the first layer (csrc/poz_tcs_kernel.cuh): forward and weight gradient of
+    // layer 0 as cluster split-K tcgen05 launches, the optimizer applied in the weight-gradient epilogue
+    bool tcs_enabled = true;          // POZ_TCS=0 keeps the SIMT kernels
+    bool tcs_fuse_update = true;      // POZ_TCS_FUSE_UPDATE=0: the weight-gradient launch stores the gradient instead
+    long long tcs_min_batch = 256, tcs_max_batch = 2560;
+    bool tcs_live = false;            // layer 0's weight planes are kept equal to its parameters at all times
+    std::vector<void*> tcs_dzp;       // planes of dZ of layer l [3][batch][round8(out_l)] (layer 0 only unless grouped)
+    long long tcs_dz_batch = 0;
+    // All layers' weight gradients in one grouped launch: measured slower on the C2 stack (36 clusters of 4 CTAs where
+    // 33 fit at once: a second wave), so opt-in: POZ_TCS_GROUP=1
+    bool tcs_group = false;
+    unsigned upd_done_mask = 0;       // layers whose update this step's backward already applied
+    bool in_step = false;             // inside poz_train_step (backward + apply as one call: the update may be fused)
     void* tc_scr[3] = {nullptr, nullptr, nullptr};   // plane stacks: input chunk, ping, pong
     float* tc_logits = nullptr;       // fp32 logits of a chunk (trailing softmax)
     long long tc_chunk = 0;

@@ -521,7 +521,25 @@ template <typename T> struct HeadArgs {
     double* cost_base;
     long long cost_cap;
     const DevState* st;
+    // optional: dz_pre / dprev_pre also as bf16 planes hi + mid + lo for a tensor-core weight-gradient launch
+    // (poz_tcs_kernel.cuh): [3][M][ld], pad columns untouched
+    unsigned short* dz_planes = nullptr;
+    long long dz_ldp = 0, dz_pstride = 0;
+    unsigned short* dprev_planes = nullptr;
+    long long dprev_ldp = 0, dprev_pstride = 0;
 };
+
+// x -> its three bf16 planes at o, o + stride, o + 2 stride
+template <typename T> __device__ __forceinline__ void store_planes3(T x, unsigned short* o, long long stride) {
+    const float xv = (float)x;
+    const __nv_bfloat16 h = __float2bfloat16_rn(xv);
+    const float r1 = xv - __bfloat162float(h);
+    const __nv_bfloat16 mm = __float2bfloat16_rn(r1);
+    const __nv_bfloat16 ll = __float2bfloat16_rn(r1 - __bfloat162float(mm));
+    o[0] = __bfloat16_as_ushort(h);
+    o[stride] = __bfloat16_as_ushort(mm);
+    o[2 * stride] = __bfloat16_as_ushort(ll);
+}
 
 // One row of the head for one warp: arow (shared memory, this warp's own K values, already the recorded output of
 // the previous unit), W / bias staged in shared memory; returns the row's contribution to the cost sum in `local`.
@@ -558,6 +576,7 @@ __device__ __forceinline__ void head_ce_row(const HeadArgs<T>& a, const T* W, in
     if (a.dz_rec && lane < a.N) a.dz_rec[m * a.N + lane] = g;
     if (a.dz_last.enabled && lane < a.N) g = drop_keep(a.dz_last, a.st, m, lane, a.N) ? g * T(a.dz_last.scale) : T(0);
     if (lane < a.N) a.dz_pre[m * a.N + lane] = g;
+    if (a.dz_planes && lane < a.N) store_planes3<T>(g, a.dz_planes + m * a.dz_ldp + lane, a.dz_pstride);
     const T zy = __shfl_sync(0xffffffffu, z, (y >= 0 && y < a.N) ? y : 0);
     if (lane == 0 && y >= 0 && y < a.N) local += (double)(mx + log(s) - zy);
     if (ktr && stamp) ktr->t[3] = fast::ktrace_now();   // softmax / loss / dZ of the first row
@@ -588,6 +607,7 @@ __device__ __forceinline__ void head_ce_row(const HeadArgs<T>& a, const T* W, in
             if (a.dzprev_rec) a.dzprev_rec[m * a.K + k] = gz;
             if (a.dz_prev.enabled) gz = drop_keep(a.dz_prev, a.st, m, k, a.K) ? gz * T(a.dz_prev.scale) : T(0);
             a.dprev_pre[m * a.K + k] = gz;
+            if (a.dprev_planes) store_planes3<T>(gz, a.dprev_planes + m * a.dprev_ldp + k, a.dprev_pstride);
         }
       }
     }

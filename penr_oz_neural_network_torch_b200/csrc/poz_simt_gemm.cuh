@@ -6,6 +6,7 @@
 // which works because a layer's bias is stored directly behind its weight matrix, making
 // [W; b] one contiguous row-major [in+1][out] matrix.
 #pragma once
+#include <cuda_bf16.h>
 #include "poz_common.cuh"
 
 namespace poz {
@@ -232,6 +233,10 @@ template <typename T> struct BwdDataEpi {
     int act;
     DropPoint dz, da;
     const DevState* st;
+    // optional (float only): dz_prev also as the three bf16 planes hi + mid + lo a tensor-core weight-gradient launch
+    // takes as its B operand (poz_tcs_kernel.cuh) -- [3][rows][ldp], pad columns untouched (zeroed at allocation)
+    unsigned short* planes = nullptr;
+    long long ldp = 0, plane_stride = 0;
     template <int TN>
     __device__ __forceinline__ void row(long long m, int n, const T (&acc)[TN], int nvalid, int) const {
         T g0[TN], g1[TN], g2[TN];
@@ -257,6 +262,40 @@ template <typename T> struct BwdDataEpi {
         if (da_rec) store_row<T, TN>(da_rec + m * ld + n, g0, nvalid);
         if (dz_rec) store_row<T, TN>(dz_rec + m * ld + n, g1, nvalid);
         store_row<T, TN>(dz_prev + m * ld + n, g2, nvalid);
+        if (planes && TN == 4 && nvalid == 4) {
+            // two packed conversions per plane, one 8-byte store per plane
+            uint32_t ph[2], pm[2], pl[2];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const float x0 = (float)g2[2 * q], x1 = (float)g2[2 * q + 1];
+                __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+                ph[q] = *reinterpret_cast<uint32_t*>(&h);
+                const float r0 = x0 - __uint_as_float(ph[q] << 16), r1 = x1 - __uint_as_float(ph[q] & 0xffff0000u);
+                __nv_bfloat162 mm = __floats2bfloat162_rn(r0, r1);
+                pm[q] = *reinterpret_cast<uint32_t*>(&mm);
+                const float s0 = r0 - __uint_as_float(pm[q] << 16), s1 = r1 - __uint_as_float(pm[q] & 0xffff0000u);
+                __nv_bfloat162 ll = __floats2bfloat162_rn(s0, s1);
+                pl[q] = *reinterpret_cast<uint32_t*>(&ll);
+            }
+            unsigned short* o = planes + m * ldp + n;
+            *reinterpret_cast<uint2*>(o) = make_uint2(ph[0], ph[1]);
+            *reinterpret_cast<uint2*>(o + plane_stride) = make_uint2(pm[0], pm[1]);
+            *reinterpret_cast<uint2*>(o + 2 * plane_stride) = make_uint2(pl[0], pl[1]);
+        } else if (planes) {
+#pragma unroll
+            for (int j = 0; j < TN; ++j)
+                if (j < nvalid) {
+                    const float xv = (float)g2[j];
+                    const __nv_bfloat16 h = __float2bfloat16_rn(xv);
+                    const float r1 = xv - __bfloat162float(h);
+                    const __nv_bfloat16 mm = __float2bfloat16_rn(r1);
+                    const __nv_bfloat16 ll = __float2bfloat16_rn(r1 - __bfloat162float(mm));
+                    unsigned short* o = planes + m * ldp + n + j;
+                    o[0] = __bfloat16_as_ushort(h);
+                    o[plane_stride] = __bfloat16_as_ushort(mm);
+                    o[2 * plane_stride] = __bfloat16_as_ushort(ll);
+                }
+        }
     }
 };
 

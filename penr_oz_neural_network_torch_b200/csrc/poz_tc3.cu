@@ -5,10 +5,13 @@
 #include "poz_tc3_kernel.cuh"
 #include "poz_tc3_x32_kernel.cuh"
 #include "poz_tc3_x32t_kernel.cuh"
+#include "poz_tcs_kernel.cuh"
 #include "poz_tc.h"
 
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
+#include <vector>
 
 namespace poz {
 namespace tc3 {
@@ -149,6 +152,118 @@ int gemm_backward_weight(const PlaneMat& x, const PlaneMat& dz, long long batch,
 }
 
 }  // namespace tc3
+
+// ---- small-batch cluster split-K GEMM of the narrow train step (poz_tcs_kernel.cuh) ---------------------------
+namespace tcs {
+
+int pick_splits(long long K, long long tiles, int sms) {
+    const long long nkb = (K + BK - 1) / BK;
+    int s = 1;
+    while (s < MAX_SPLITS && (nkb + s - 1) / s > MAX_KB) s *= 2;
+    if ((nkb + s - 1) / s > MAX_KB) return 0;                                  // deeper than a cluster can hold
+    while (s < MAX_SPLITS && tiles * s * 2 <= sms && nkb >= 2 * s) s *= 2;     // grow while the grid stays within one wave
+    return s;
+}
+
+bool shape_ok(long long M, int N, long long K) {
+    return M > 0 && N > 0 && K > 0 && (M + BM - 1) / BM <= 65535 && pick_splits(K, 1, 1) > 0;
+}
+
+template <bool A_T, class Epi> static int launch(const Gemm* gs, const Epi* epis, int n, cudaStream_t stream) {
+    auto kern = tcs_gemm_kernel<A_T, Epi>;
+    static bool configured = false;
+    if (!configured) {
+        POZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        configured = true;
+    }
+    if (n < 1 || n > MAX_GROUP) POZ_FAIL("tcs gemm: between 1 and MAX_GROUP problems per launch");
+    const int splits = gs[0].splits;
+    const long long nkb = (gs[0].K + BK - 1) / BK;
+    if (splits < 1 || splits > MAX_SPLITS || (splits & (splits - 1)) || (nkb + splits - 1) / splits > MAX_KB)
+        POZ_FAIL("tcs gemm: bad split count for this contraction length");
+    GroupArgs ga{};
+    GroupEpi<Epi> ge{};
+    CUtensorMap maps[MAX_GROUP];
+    ga.n = n;
+    long long tiles = 0;
+    for (int i = 0; i < n; ++i) {
+        const Gemm& g = gs[i];
+        if (g.K != gs[0].K || g.splits != splits) POZ_FAIL("tcs gemm: the problems of one launch share K and the split count");
+        POZ_TRY(tc3::make_map3(&maps[i], g.b, 64, 64));
+        Args& a = ga.a[i];
+        a.a = g.a; a.lda = g.lda; a.row_idx = g.row_idx; a.a_cols = g.a_cols; a.ones_row = g.ones_row;
+        a.M = g.M; a.N = g.N; a.K = g.K;
+        a.k_per_split = ((nkb + splits - 1) / splits) * BK;
+        ga.tiles_n[i] = (g.N + BN - 1) / BN;
+        tiles += ((g.M + BM - 1) / BM) * ga.tiles_n[i];
+        if (tiles > 0x7fffffffLL / 2) POZ_FAIL("tcs gemm: too many tiles");
+        ga.tile_end[i] = (int)tiles;
+        ge.e[i] = epis[i];
+    }
+    for (int i = n; i < MAX_GROUP; ++i) { maps[i] = maps[0]; ga.tile_end[i] = (int)tiles; ga.tiles_n[i] = 1; ga.a[i] = ga.a[0]; ge.e[i] = epis[0]; }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)tiles, 1, (unsigned)splits);
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)splits;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    POZ_CUDA(cudaLaunchKernelEx(&cfg, kern, ga, maps[0], maps[1], maps[2], maps[3], ge));
+    count_launch();
+    return 0;
+}
+
+// POZ_KERNEL_TRACE=1 (this translation unit's own copy of the trace symbols: they have internal linkage)
+int trace_enable() {
+    fast::KernelTraceRec* buf = nullptr;
+    POZ_CUDA(cudaMemcpyFromSymbol(&buf, fast::d_ktrace, sizeof(buf)));
+    if (!buf) {
+        POZ_CUDA(cudaMalloc(&buf, sizeof(fast::KernelTraceRec) * (size_t)fast::KTRACE_CAP));
+        POZ_CUDA(cudaMemcpyToSymbol(fast::d_ktrace, &buf, sizeof(buf)));
+    }
+    return 0;
+}
+
+void trace_dump() {
+    fast::KernelTraceRec* buf = nullptr;
+    if (cudaMemcpyFromSymbol(&buf, fast::d_ktrace, sizeof(buf)) != cudaSuccess || !buf) return;
+    cudaDeviceSynchronize();
+    unsigned int n = 0;
+    cudaMemcpyFromSymbol(&n, fast::d_ktrace_n, sizeof(n));
+    n = n < fast::KTRACE_CAP ? n : fast::KTRACE_CAP;
+    if (!n) return;
+    std::vector<fast::KernelTraceRec> h(n);
+    cudaMemcpy(h.data(), buf, sizeof(fast::KernelTraceRec) * n, cudaMemcpyDeviceToHost);
+    for (int tag : {200, 201}) {
+        // the CTAs of the last launch with this tag: entries within 60 us of the latest entry
+        unsigned long long latest = 0;
+        for (auto& r : h) if (r.tag == tag && r.t[0] > latest) latest = r.t[0];
+        if (!latest) continue;
+        unsigned long long first = latest;
+        for (auto& r : h) if (r.tag == tag && latest - r.t[0] < 60000ull && r.t[0] < first) first = r.t[0];
+        double sum[6] = {0}; unsigned long long mx[6] = {0}; size_t cnt = 0; int m = 0, nn = 0, k = 0;
+        for (auto& r : h)
+            if (r.tag == tag && latest - r.t[0] < 60000ull) {
+                ++cnt; m = r.m; nn = r.n; k = r.k;
+                for (int q = 0; q < 6; ++q) { sum[q] += (double)(r.t[q] - first); if (r.t[q] - first > mx[q]) mx[q] = r.t[q] - first; }
+            }
+        fprintf(stderr, "[poz tcs trace] tag %d (M %d N %d K %d): %zu CTAs; mean (max) ns after the first CTA's entry: entry %.0f (%llu) "
+                        "set-up %.0f (%llu) first half-block in tensor memory %.0f (%llu) accumulators complete %.0f (%llu) "
+                        "partials exchanged %.0f (%llu) exit %.0f (%llu)\n",
+                tag, m, nn, k, cnt, sum[0] / cnt, mx[0], sum[1] / cnt, mx[1], sum[2] / cnt, mx[2], sum[3] / cnt, mx[3],
+                sum[4] / cnt, mx[4], sum[5] / cnt, mx[5]);
+    }
+    unsigned int zero = 0;
+    cudaMemcpyToSymbol(fast::d_ktrace_n, &zero, sizeof(zero));
+}
+
+int forward(const Gemm& g, const FwdEpi& epi, cudaStream_t stream) { return launch<false>(&g, &epi, 1, stream); }
+int backward_weight_store(const Gemm* g, const StoreEpi* epi, int n, cudaStream_t stream) { return launch<true>(g, epi, n, stream); }
+int backward_weight_update(const Gemm* g, const UpdateEpi* epi, int n, cudaStream_t stream) { return launch<true>(g, epi, n, stream); }
+
+}  // namespace tcs
 }  // namespace poz
 
 // fp32 matrices in, fp32 out: splits both operands into temporary plane stacks (allocated and freed

@@ -83,10 +83,7 @@ __device__ __forceinline__ float4 lds128(uint32_t saddr) {
 __device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity) {
     for (uint32_t spins = 0; !tc::mbar_try_wait(bar, parity); ++spins) {
         __nanosleep(spins < 64 ? 20 : 100);
-        if (spins > 20u * 1000u * 1000u) {
-            printf("poz tc3 x32t: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-            __trap();
-        }
+        if (spins > 20u * 1000u * 1000u) tc::mbar_timeout();
     }
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }

@@ -1,0 +1,7 @@
+#!/bin/bash
+set -x
+timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_model_api.py tests/test_gpu_round2.py -m gpu -x -q -k "not sweep and not wide" > gpurun_out/pytest_tcs.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_tcs.log
+tail -30 gpurun_out/pytest_tcs.log
+POZ_KERNEL_TRACE=1 timeout 120 python scripts/micro/tcs_trace.py 2>&1 | grep -i "tcs trace\|tag 4 \|tag 3 \|tag 1 \|tag 64\|tag 128 M 32\|launch below" | tail -24
+timeout 300 python bench.py --steps 200 --warmup 20 --no-secondary --no-class-api --no-cpu-baseline > gpurun_out/bench_tcs.json 2> gpurun_out/bench_tcs.err; echo "bench rc=$?"
+tail -c 800 gpurun_out/bench_tcs.err

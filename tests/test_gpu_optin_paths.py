@@ -74,6 +74,18 @@ def test_optin_step_variants_match_the_oracle(switch):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("env", [{"POZ_TCS": "0"}, {"POZ_TCS_FUSE_UPDATE": "0"}, {"POZ_TCS_GROUP": "1"},
+                                 {"POZ_TCS_GROUP": "1", "POZ_TCS_FUSE_UPDATE": "0"}],
+                         ids=["simt-layer0", "gradient-stored", "grouped", "grouped-stored"])
+def test_small_batch_tensor_core_variants_match_the_oracle(env):
+    """The default C2 step runs layer 0's forward and weight gradient as cluster split-K tcgen05 launches with the
+    optimizer in the weight-gradient epilogue (csrc/poz_tcs_kernel.cuh).  The same three steps with that path off,
+    with the gradient stored for the update kernel instead, and with every layer's weight gradient grouped into one
+    launch must give the oracle's numbers too."""
+    run_child(env)
+
+
+@pytest.mark.gpu
 def test_default_path_in_a_child_process_matches_too():
     run_child({})
 

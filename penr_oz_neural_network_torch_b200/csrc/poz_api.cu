@@ -5,11 +5,7 @@
 #include "poz_net_kernels.cuh"
 #include "poz_simt_gemm.cuh"
 #include "poz_simt_fast.cuh"
-#include "poz_narrow_step.cuh"
 #include "poz_infer_small.cuh"
-#include "poz_fwd_head.cuh"
-#include "poz_tf32x3_gemm.cuh"
-#include "poz_tf32x3_tma_gemm.cuh"
 #include "poz_tc.h"
 #include "poz_tc3.h"
 #include "poz_tcs.h"
@@ -273,25 +269,14 @@ static int ensure_grad_slabs(poz_ctx* c, int slabs) {
 }
 
 
-// ---- programmatic dependent launch (poz_common.cuh: pdl_trigger / pdl_wait) ----------------------------
-// Only kernels that call pdl_wait() before touching global memory are launched this way.  Measured on
-// B200 inside the step's CUDA graph the programmatic edges made the C2 step slower (108-114 us against
-// 82 us with plain edges), so the attribute is opt-in: POZ_PDL=1.
-static bool pdl_enabled() {
-    static const bool on = getenv("POZ_PDL") && atoi(getenv("POZ_PDL")) != 0;
-    return on;
-}
-
+// ---- launch helper ---------------------------------------------------------------------------------
+// (Programmatic dependent launches were measured inside the step's CUDA graph in round 1: 108-114 us per C2 step against
+//  82 us with plain edges, wherever the trigger was placed.  The attribute and its switch are gone; pdl_trigger / pdl_wait
+//  in the kernels are no-ops for a launch without it.)
 template <typename... P, typename... A>
 static int launch_pdl(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A&&... args) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    if (pdl_enabled()) {
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr; cfg.numAttrs = 1;
-    }
     POZ_CUDA(cudaLaunchKernelEx(&cfg, kern, std::forward<A>(args)...));
     count_launch();
     return 0;
@@ -303,27 +288,6 @@ static fast::Op make_fast_op(const float* ptr, long long ld, const int* row_idx,
     o.ptr = ptr; o.ld = ld; o.row_idx = row_idx; o.rows = rows; o.cols = cols;
     o.vec4 = ((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld % 4) == 0 && (cols % 4) == 0) ? 1 : 0;
     return o;
-}
-
-// POZ_TF32X3=1 runs the 32x64-tile GEMMs of float32 contexts on the warp-level tensor-core instruction
-// with the error-compensated split (poz_tf32x3_gemm.cuh).  It passes the same parity tests, but measured
-// on B200 the C2 step does not get faster (three tf32 MMAs per product are only 1.3x the FFMA pipe, and
-// both kernels keep their pipe ~half busy at these sizes: DESIGN.md section 4g), so the exact-fp32 FFMA
-// kernel stays the default.
-static bool tf32x3_enabled() {
-    static const bool on = getenv("POZ_TF32X3") && atoi(getenv("POZ_TF32X3")) != 0;
-    return on;
-}
-
-// POZ_TMA_GEMM=1: the same GEMMs with TMA-delivered operand tiles (poz_tf32x3_tma_gemm.cuh) wherever both
-// operands can be described by a tensor map (no row gather, 16-byte aligned base and row pitch).
-static bool tma_gemm_enabled() {
-    static const bool on = getenv("POZ_TMA_GEMM") && atoi(getenv("POZ_TMA_GEMM")) != 0;
-    return on;
-}
-static bool tma_operand_ok(const fast::Op& o) {
-    return !o.row_idx && (reinterpret_cast<uintptr_t>(o.ptr) & 15) == 0 && (o.ld % 4) == 0 && o.rows > 0 && o.cols > 0 &&
-           o.rows < (1LL << 31) && o.ld * 4 < (1LL << 40);
 }
 
 template <int BM, int BN, bool A_KC, bool B_KC, bool COLSUM, class Epi>
@@ -345,29 +309,9 @@ static int launch_fast(const fast::Op& A, const fast::Op& B, long long M, int N,
         attr[na].val.clusterDim.x = 1; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = (unsigned)splits;
         ++na;
     }
-    if (pdl_enabled()) {
-        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[na].val.programmaticStreamSerializationAllowed = 1;
-        ++na;
-    }
     if (na) { cfg.attrs = attr; cfg.numAttrs = na; }
-    if (BM == 32 && BN == 64 && tma_gemm_enabled() && tma_operand_ok(A) && tma_operand_ok(B)) {
-        // TMA-fed 3xTF32 kernel: boxes of 32 floats (A: 32 rows or 32 k-rows; B: 64 rows or 32 k-rows)
-        CUtensorMap ma, mb;
-        POZ_TRY(tc::make_map_f32(&ma, A.ptr, A.rows, A.cols, A.ld, 32));
-        POZ_TRY(tc::make_map_f32(&mb, B.ptr, B.rows, B.cols, B.ld, B_KC ? 64 : 32));
-        long long kc = (Kd + splits - 1) / splits;
-        kc = ((kc + fast::TBK - 1) / fast::TBK) * fast::TBK;
-        POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_tf32x3_tma<A_KC, B_KC, COLSUM, Epi>, ma, mb, M, N, Kd, kc, bias_row, epi));
-        count_launch();
-        return 0;
-    }
-    if (BM == 32 && BN == 64 && tf32x3_enabled())
-        POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_tf32x3_pipelined<A_KC, B_KC, COLSUM, Epi>, A, B, M, N, Kd, k_chunk,
-                                    bias_row, epi));
-    else
-        POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_f32_pipelined<BM, BN, A_KC, B_KC, COLSUM, Epi>, A, B, M, N, Kd,
-                                    k_chunk, bias_row, epi));
+        POZ_CUDA(cudaLaunchKernelEx(&cfg, fast::gemm_f32_pipelined<BM, BN, A_KC, B_KC, COLSUM, Epi>, A, B, M, N, Kd, k_chunk,
+                                bias_row, epi));
     count_launch();
     return 0;
 }
@@ -888,7 +832,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     if constexpr (std::is_same<T, float>::value) {
         const int sms = num_sms(c->device);
         const int K0 = c->sizes[0], N0 = c->sizes[1];
-        tcs0 = c->tcs_enabled && !c->fused_step && !tc0 && nl >= 2 && c->acts[0] != ACT_SOFTMAX && K0 >= 128 && N0 >= 32 && N0 % 4 == 0 &&
+        tcs0 = c->tcs_enabled && !tc0 && nl >= 2 && c->acts[0] != ACT_SOFTMAX && K0 >= 128 && N0 >= 32 && N0 % 4 == 0 &&
                batch >= c->tcs_min_batch && batch <= c->tcs_max_batch;
         if (tcs0) {
             tcs_f_splits = tcs::pick_splits(K0, ((batch + tcs::BM - 1) / tcs::BM) * ((N0 + tcs::BN - 1) / tcs::BN), sms);
@@ -969,30 +913,10 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     const size_t head_smem = ((size_t)head_K * (head_N | 1) + 32 + 8 * (size_t)head_K) * sizeof(T);
     const bool fuse_head = c->fuse_head && nl >= 2 && c->loss == POZ_LOSS_CE && head_N <= 32 && head_smem <= 96 * 1024;
 
-    // float32: the last hidden unit's forward rides in the same launch as the head (poz_fwd_head.cuh)
-    bool fwd_head = false;
-    size_t fh_smem = 0;
-    if constexpr (std::is_same<T, float>::value) {
-        // opt-in (POZ_FUSE_FWD_HEAD=1): measured slower than the two launches it replaces (83 against 76 us per
-        // C2 step: its 128 blocks each stream all of W1 at ~9 GB/s)
-        static const bool allowed = getenv("POZ_FUSE_FWD_HEAD") && atoi(getenv("POZ_FUSE_FWD_HEAD")) != 0;
-        const int p = nl - 2;
-        if (allowed && fuse_head && !(tc0 && p == 0)) {
-            const int K1 = c->sizes[p], N1 = c->sizes[p + 1];
-            size_t fl = (size_t)N1 * (head_N | 1) + 32 + (size_t)FH_WARPS * N1;
-            fl = (fl + 3) & ~(size_t)3;
-            fl += (size_t)FH_WARPS * (((K1 + FH_KT - 1) / FH_KT) * FH_KT + 1);
-            fl = (fl + 3) & ~(size_t)3;
-            fl += (size_t)FH_STAGES * FH_KT * N1;
-            fh_smem = fl * sizeof(float);
-            fwd_head = N1 % 32 == 0 && N1 <= 256 && c->acts[p] != ACT_SOFTMAX && fh_smem <= 96 * 1024;
-        }
-    }
-
     // forward, keeping what the backward needs (and, for diagnostics, every entry's output)
     const T* cur = x;
     const int* cur_idx = row_idx;
-    for (int l = 0; l < (fuse_head ? (fwd_head ? nl - 2 : nl - 1) : nl); ++l) {
+    for (int l = 0; l < (fuse_head ? nl - 1 : nl); ++l) {
         T* zb = static_cast<T*>(c->zbuf[l]);
         T* ab = static_cast<T*>(c->abuf[l]);
         const int act = c->acts[l];
@@ -1087,29 +1011,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             configured[sizeof(T) == 8] = true;
         }
         const int blocks = (int)std::max<long long>(1, std::min<long long>((batch + 7) / 8, 2LL * num_sms(c->device)));
-        bool launched = false;
-        if constexpr (std::is_same<T, float>::value) {
-            if (fwd_head) {
-                static bool fh_configured = false;
-                if (!fh_configured) {
-                    POZ_CUDA(cudaFuncSetAttribute(fwd_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-                    fh_configured = true;
-                }
-                FwdHeadArgs fa{};
-                fa.h = h;
-                fa.a_in = cur; fa.in_row_idx = cur_idx;
-                fa.w1b = static_cast<const float*>(c->P) + c->off[p];
-                fa.a1_out = static_cast<float*>(c->abuf[p]);
-                fa.z1_rec = (diag && c->acts[p] != ACT_NONE) ? static_cast<float*>(c->zbuf[p]) : nullptr;
-                fa.K1 = c->sizes[p]; fa.N1 = c->sizes[p + 1]; fa.act1 = c->acts[p];
-                fa.dz1 = make_drop(c, p, 0, masks);
-                fa.da1 = make_drop(c, p, 1, masks);
-                ProfScope ps(c, "fwd_head", stream);
-                POZ_TRY(launch_pdl(fwd_head_kernel, dim3(blocks), dim3(FH_WARPS * 32), fh_smem, stream, fa));
-                launched = true;
-            }
-        }
-        if (!launched) {
+        {
             ProfScope ps(c, "head", stream);
             POZ_TRY(launch_pdl(head_ce_kernel<T>, dim3(blocks), dim3(256), head_smem, stream, h));
         }
@@ -1500,7 +1402,6 @@ static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target,
 }
 
 #include "poz_general.inc"
-#include "poz_narrow_step_host.inc"
 
 template <typename T>
 static int forward_general_dispatch(poz_ctx* c, const void* x, const void* target, long long batch, T* out,
@@ -1699,8 +1600,6 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
         }
         POZ_TRY(tcs::trace_enable());
     }
-    if (const char* e = getenv("POZ_FUSED_STEP")) c->fused_step = atoi(e) != 0;
-    if (const char* e = getenv("POZ_FUSED_STEP_MAX_BATCH")) c->fused_step_max_batch = atoll(e);
     if (const char* e = getenv("POZ_TCS")) c->tcs_enabled = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS_FUSE_UPDATE")) c->tcs_fuse_update = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS_GROUP")) c->tcs_group = atoi(e) != 0;
@@ -1868,9 +1767,6 @@ int poz_ctx_destroy(poz_ctx* c) {
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
     dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
     dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz); for (auto& q : c->tcs_dzp) dev_free(q);
-    for (auto& p : c->step_plans) dev_free(p.d_tasks);
-    dev_free(reinterpret_cast<void*&>(c->step_barrier));
-    dev_free(reinterpret_cast<void*&>(c->step_trace));
     dev_free(reinterpret_cast<void*&>(c->tc_logits));
     dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
     dev_free(reinterpret_cast<void*&>(c->st));
@@ -2167,14 +2063,6 @@ int poz_train_step(poz_ctx* c, const void* x_dev, const void* target_dev, const 
 
 static int train_step_inner(poz_ctx* c, const void* x_dev, const void* target_dev, const int* row_idx_dev,
                             long long batch, const void* const* keep_masks, int diagnostics, void* stream) {
-    if (x_dev && target_dev && c->fused_step && c->step_grid == 0) POZ_TRY(fused_step_probe(c));
-    if (x_dev && target_dev && fused_step_eligible(c, batch, keep_masks, diagnostics)) {
-        // narrow fp32 stack: the whole step is one persistent kernel (no graph needed: it is one launch)
-        POZ_TRY(fused_step_launch(c, static_cast<const float*>(x_dev), target_dev, row_idx_dev, batch,
-                                  static_cast<cudaStream_t>(stream)));
-        c->epoch_host += 1;
-        return 0;
-    }
     const bool graphable = c->graphs_enabled && !c->profiling && !diagnostics && !keep_masks &&
                            c->dtype != POZ_DTYPE_BF16 && c->train_begun &&
                            stream != nullptr;   // the legacy default stream cannot be captured

@@ -109,21 +109,6 @@ struct poz_ctx {
     int small_infer_cluster = 0;      // cluster size of the few-row inference kernel (0 = not probed, -1 = unavailable)
     bool fuse_head = true;            // narrow softmax head in one kernel (POZ_FUSE_HEAD=0 disables)
 
-    // whole train step of a narrow fp32 stack in one persistent kernel (csrc/poz_narrow_step.cuh)
-    struct StepPlan {
-        long long batch = 0;
-        void* d_tasks = nullptr;       // device copy of the task table
-        int n_tasks = 0, n_phases = 0, slabs = 1;
-        std::vector<int> phase_end, splits;
-    };
-    std::vector<StepPlan> step_plans;  // one per batch size seen
-    unsigned int* step_barrier = nullptr;
-    unsigned long long* step_trace = nullptr;   // POZ_STEP_TRACE=1: per-CTA phase time stamps of the last fused step
-    int step_grid = 0;                 // CTAs of the cooperative launch (0 = not probed yet, -1 = unavailable)
-    // Measured on B200 the single-kernel step is slower than the graph of separate
-    // kernels (instruction-fetch and per-stage latency bound), so it is opt-in: POZ_FUSED_STEP=1
-    bool fused_step = false;
-    long long fused_step_max_batch = 16384;
     double graph_sig[6] = {0, 0, 0, 0, 0, 0};
 
     // host-buffer stepping (poz_train_step_host): POZ_HOST_LAG + 1 device slots, copy + read-back streams

@@ -3,7 +3,6 @@
 #include "../../include/pozmlp.h"
 #include "poz_tc3.h"
 #include "poz_tc3_kernel.cuh"
-#include "poz_tc3_x32_kernel.cuh"
 #include "poz_tc3_x32t_kernel.cuh"
 #include "poz_tcs_kernel.cuh"
 #include "poz_tc.h"
@@ -101,9 +100,7 @@ int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K
     return launch_bn<MAJOR_K, MAJOR_MN>(x, w, M, N, K, 1, ep, sms, s);
 }
 bool gemm_forward_head_ok(int N, int head_n) { return N > 64 && N <= 128 && head_n >= 1 && head_n <= HEAD_MAX_N; }
-bool gemm_forward_x32_head_ok() {
-    return !(getenv("POZ_TC3_X32_TMEM") && atoi(getenv("POZ_TC3_X32_TMEM")) == 0);
-}
+bool gemm_forward_x32_head_ok() { return true; }
 bool gemm_forward_x32_ok(const float* x, long long ld, int N) {
     return N > 64 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (ld % 4) == 0;
 }
@@ -111,17 +108,13 @@ bool gemm_forward_x32_ok(const float* x, long long ld, int N) {
 int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms,
                      cudaStream_t stream) {
     constexpr int BN = 128;
-    using C = CfgX32<BN>;
     using CT = CfgX32T<BN, 3, false>;
     using CH = CfgX32T<BN, 2, true>;                  // with the fused head: one W stage fewer, its buffers instead
     if (!gemm_forward_x32_ok(x, ld, N)) POZ_FAIL("tc3 fp32-input forward: operand not eligible");
-    // X planes in tensor memory (default) or in shared memory (POZ_TC3_X32_TMEM=0)
-    static const bool planes_in_tmem = !(getenv("POZ_TC3_X32_TMEM") && atoi(getenv("POZ_TC3_X32_TMEM")) == 0);
-    if (ep.head_w && (!planes_in_tmem || N > BN || ep.head_n < 1 || ep.head_n > HEAD_MAX_N || !ep.head_out))
+    if (ep.head_w && (N > BN || ep.head_n < 1 || ep.head_n > HEAD_MAX_N || !ep.head_out))
         POZ_FAIL("tc3 fp32-input forward: fused head not available for this shape");
     static bool configured = false;
     if (!configured) {
-        POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32t_kernel<BN, 3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT::SMEM_BYTES));
         POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32t_kernel<BN, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH::SMEM_BYTES));
         configured = true;
@@ -133,10 +126,8 @@ int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long 
     const int grid = (int)(tiles < sms ? tiles : sms);
     if (ep.head_w)
         tc3_fwd_x32t_kernel<BN, 2, true><<<grid, X32T_THREADS, CH::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
-    else if (planes_in_tmem)
-        tc3_fwd_x32t_kernel<BN, 3, false><<<grid, X32T_THREADS, CT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     else
-        tc3_fwd_x32_kernel<BN><<<grid, X32_THREADS, C::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+        tc3_fwd_x32t_kernel<BN, 3, false><<<grid, X32T_THREADS, CT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     count_launch();
     POZ_CUDA(cudaGetLastError());
     return 0;

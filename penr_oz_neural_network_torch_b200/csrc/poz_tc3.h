@@ -46,7 +46,7 @@ int gemm_forward(const PlaneMat& x, const PlaneMat& w, long long M, int N, int K
 // whether gemm_forward takes ep.head_* for this width
 bool gemm_forward_head_ok(int N, int head_n);
 // the same with x given as the fp32 matrix itself (pitch ld floats, 16-byte aligned rows): its planes are made
-// inside the kernel and never written to global memory (csrc/poz_tc3_x32_kernel.cuh); N must be > 64
+// inside the kernel and never written to global memory (csrc/poz_tc3_x32t_kernel.cuh); N must be > 64
 int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms,
                      cudaStream_t s);
 bool gemm_forward_x32_ok(const float* x, long long ld, int N);

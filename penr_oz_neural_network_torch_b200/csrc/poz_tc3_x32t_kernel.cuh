@@ -1,9 +1,11 @@
 // Forward split-bf16 tcgen05 GEMM from fp32 rows, X planes in TENSOR memory: out = epilogue(X[M][K] * W[K][N]).
 //
-// tc3_fwd_x32_kernel (poz_tc3_x32_kernel.cuh) writes the hi / mid / lo planes of X into shared memory, and its six
-// MMAs per k-step read both operands from there: 8 KB per 128x128x16 MMA, i.e. 128 B per clock at the tensor
-// pipe's full rate -- all the shared-memory bandwidth there is, before the TMA writes and the converters' own
-// loads and stores (ncu: tensor pipe 51 % active, LSU data pipe 66 %).  Here the converters put the planes into
+// TMA brings fp32 half-blocks (128 rows x 32 k, 128-byte swizzle) into a five-slot shared-memory ring and eight
+// converter warps split them into hi / mid / lo planes.  A first version (round 1, removed) wrote those planes into
+// shared memory, and its six MMAs per k-step read both operands from there: 8 KB per 128x128x16 MMA, i.e. 128 B per
+// clock at the tensor pipe's full rate -- all the shared-memory bandwidth there is, before the TMA writes and the
+// converters' own loads and stores (ncu: tensor pipe 51 % active, LSU data pipe 66 %; 0.60 ms per 262,144-row pass
+// against 0.50 ms for this kernel).  Here the converters put the planes into
 // tensor memory (`tcgen05.st`, one row per lane, two bf16 per 32-bit column) and the MMAs take A from there
 // (`tcgen05.mma` with a TMEM A operand), so shared memory carries only the fp32 half-blocks and W's planes.
 // Tensor memory then holds: two 128-column main accumulators (hi*hi; double-buffered tiles), ONE 128-column accumulator
@@ -15,10 +17,20 @@
 //   warps 0-7 : epilogue          warp 8 : TMA producer of the fp32 X half-blocks      warp 18 : TMA producer of W's planes
 //   warp  9   : TMEM + MMA        warps 10-17 : converters (warp w: rows 32 (w % 4).., half-block (w - 10) / 4 of each k-block)
 #pragma once
-#include "poz_tc3_x32_kernel.cuh"
+#include "poz_tc3_kernel.cuh"
 
 namespace poz {
 namespace tc3 {
+
+constexpr int X32_CONV_WARPS = 8;                   // two groups of four: one tile row per lane
+constexpr int X32_THREADS = (NUM_EPI_WARPS + 2 + X32_CONV_WARPS) * 32;
+constexpr int X32_RAW_BYTES = BM * 32 * 4;          // one half-block: 128 rows x 32 floats
+
+__device__ __forceinline__ void tma_load_2d_f32(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(tc::smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1)
+                 : "memory");
+}
 
 constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in flight in shared memory
 constexpr int X32T_SLOT_COLS = PLANES * 16;         // 32 k-values of three planes, two per column

@@ -5,7 +5,6 @@ import numpy as np
 
 PATHS = {
     "simt fp32 FFMA": {"POZ_TC3_MIN_BATCH": "1000000000"},
-    "tc3 planes in smem, two accumulators": {"POZ_TC3_X32_TMEM": "0", "POZ_TC3_F32_CHAIN": "0", "POZ_TC3_FUSE_HEAD": "0"},
     "tc3 planes in tmem, shared small-terms accumulator (default)": {},
 }
 

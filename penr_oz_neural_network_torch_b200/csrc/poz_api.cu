@@ -189,6 +189,24 @@ template <typename T> static int get_f64(poz_ctx* c, const void* src_base, long 
     return 0;
 }
 
+// bf16 device tensor -> float64 host image (activations and their gradients of a bf16 context)
+static __global__ void bf16_to_f64_kernel(const __nv_bfloat16* __restrict__ src, double* __restrict__ dst, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        dst[i] = (double)__bfloat162float(src[i]);
+}
+static int get_bf16_f64(poz_ctx* c, const void* src, double* dst, long long n) {
+    if (n <= 0) return 0;
+    POZ_CUDA(cudaDeviceSynchronize());
+    POZ_TRY(ensure_stage(c, (size_t)n));
+    int blocks = (int)std::min<long long>((n + 255) / 256, 4096);
+    bf16_to_f64_kernel<<<blocks, 256>>>(static_cast<const __nv_bfloat16*>(src), c->stage, n);
+    POZ_LAUNCH_CHECK();
+    POZ_CUDA(cudaMemcpy(dst, c->stage, n * sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
+// activations / activation gradients of a bf16 context are bf16; parameters and their gradients float32
+static bool diag_is_bf16(const poz_ctx* c, int source) { return c->dtype == POZ_DTYPE_BF16 && source <= 1; }
+
 #define POZ_DISPATCH(c, fn, ...)                                                              \
     ((c)->dtype == POZ_DTYPE_F64 ? fn<double>(__VA_ARGS__) : fn<float>(__VA_ARGS__))
 
@@ -1315,11 +1333,29 @@ static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target,
     const int sms = num_sms(c->device);
     if (!c->train_begun) POZ_FAIL("poz_train_step: call poz_train_begin first");
     if (batch <= 0) POZ_FAIL("poz_train_step: empty batch");
-    if (row_idx) POZ_FAIL("poz_train_step: bf16 contexts take a materialised batch (no row gather: TMA reads dense tiles)");
-    if (masks || c->cfg.dropout_rate > 0.0) POZ_FAIL("poz_train_step: dropout is not available in bf16 contexts yet");
-    if (diag) POZ_FAIL("poz_train_step: diagnostics are not available in bf16 contexts yet");
     if (batch % 8) POZ_FAIL("poz_train_step: bf16 contexts need a batch that is a multiple of 8");
-    POZ_TRY(reserve_train(c, batch, false));
+    POZ_TRY(reserve_train(c, batch, diag != 0));
+    const int n_out = c->sizes[nl];
+    const __nv_bfloat16* tgt = static_cast<const __nv_bfloat16*>(target);
+    if (row_idx) {
+        // TMA reads dense tiles: the sampled rows (inputs and targets) are materialised first -- 2 x batch x width x 2
+        // bytes each way, ~1 % of the step at the C4 shape
+        if (batch > c->wide_g_batch) {
+            dev_free(c->wide_xg); dev_free(c->wide_tg);
+            POZ_TRY(dev_alloc(&c->wide_xg, (size_t)batch * c->sizes[0] * 2));
+            POZ_TRY(dev_alloc(&c->wide_tg, (size_t)batch * n_out * 2));
+            c->wide_g_batch = batch;
+        }
+        ProfScope ps(c, "gather_rows", stream);
+        const int bx = (int)std::min<long long>((batch * (c->sizes[0] / 8) + 255) / 256, 8LL * sms);
+        wide_gather_rows_kernel<<<std::max(bx, 1), 256, 0, stream>>>(x, row_idx, batch, c->sizes[0], static_cast<__nv_bfloat16*>(c->wide_xg));
+        POZ_LAUNCH_CHECK();
+        const int bt = (int)std::min<long long>((batch * (n_out / 8) + 255) / 256, 8LL * sms);
+        wide_gather_rows_kernel<<<std::max(bt, 1), 256, 0, stream>>>(tgt, row_idx, batch, n_out, static_cast<__nv_bfloat16*>(c->wide_tg));
+        POZ_LAUNCH_CHECK();
+        x = static_cast<const __nv_bfloat16*>(c->wide_xg);
+        tgt = static_cast<const __nv_bfloat16*>(c->wide_tg);
+    }
     // split the batch reduction of dW only when the output tiles alone cannot fill the GPU
     c->seg_splits.assign(nl, 1);
     int slabs = 1;
@@ -1336,7 +1372,7 @@ static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target,
     if (!c->colsum_scratch) POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->colsum_scratch), (size_t)COLSUM_ROWS * widest * sizeof(float)));
     c->training_pass = true;
     c->grads_reduced = false;
-    c->diag_batch = 0;
+    c->diag_batch = diag ? batch : 0;
     c->last_batch = batch;
     {
         ProfScope ps(c, "step_begin", stream);
@@ -1351,20 +1387,33 @@ static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target,
     for (int l = 0; l < nl; ++l) {
         const int K = c->sizes[l], N = c->sizes[l + 1];
         __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(c->abuf[l]);
+        tc::Extras ex;
+        ex.dz = make_drop(c, l, 0, masks);
+        ex.da = make_drop(c, l, 1, masks);
+        ex.st = c->st;
+        if (diag && c->acts[l] != ACT_NONE) ex.z_rec = static_cast<__nv_bfloat16*>(c->zbuf[l]);
+        const bool plain = !ex.dz.enabled && !ex.da.enabled && !ex.z_rec;
         ProfScope ps(c, "tc_fwd_l" + std::to_string(l), stream);
         POZ_TRY(tc::gemm_forward(cur, Pb + c->off[l], batch, N, K,
-                                 c->has_bias ? P + c->off[l] + (long long)K * N : nullptr, c->acts[l], dst, sms, stream));
+                                 c->has_bias ? P + c->off[l] + (long long)K * N : nullptr, c->acts[l], dst, sms, stream,
+                                 plain ? nullptr : &ex));
         cur = dst;
     }
     const long long gb = c->cfg.global_batch > 0 ? c->cfg.global_batch : batch;
-    const int last = nl - 1, n_out = c->sizes[nl];
+    const int last = nl - 1;
     {
         WideLossArgs a{};
-        a.y = cur; a.target = static_cast<const __nv_bfloat16*>(target);
+        a.y = cur; a.target = tgt;
         a.dz = static_cast<__nv_bfloat16*>(c->dzbuf[last]);
         a.total = batch * n_out; a.act = c->acts[last];
         a.inv_count = 1.0 / ((double)gb * n_out);
         a.cost_base = c->cost_ring; a.cost_cap = c->cost_cap; a.st = c->st;
+        a.N = n_out;
+        a.dzp = make_drop(c, last, 0, masks);
+        if (diag) {
+            a.dz_rec = static_cast<__nv_bfloat16*>(c->dz_rec[last]);
+            if (c->acts[last] != ACT_NONE) a.da_rec = static_cast<__nv_bfloat16*>(c->da_rec[last]);
+        }
         ProfScope ps(c, "loss", stream);
         int blocks = (int)std::min<long long>((a.total / 8 + 255) / 256, 148 * 8);
         wide_mse_loss_kernel<<<std::max(blocks, 1), 256, 0, stream>>>(a);
@@ -1391,13 +1440,23 @@ static int backward_wide(poz_ctx* c, const __nv_bfloat16* x, const void* target,
         }
         POZ_CUDA(cudaEventRecord(c->grad_ready[l], stream));
         if (l > 0) {
+            tc::Extras ex;
+            ex.dz = make_drop(c, l - 1, 0, masks);
+            ex.da = make_drop(c, l - 1, 1, masks);
+            ex.st = c->st;
+            if (diag) {
+                ex.dz_rec = static_cast<__nv_bfloat16*>(c->dz_rec[l - 1]);
+                if (c->acts[l - 1] != ACT_NONE) ex.da_rec = static_cast<__nv_bfloat16*>(c->da_rec[l - 1]);
+            }
+            const bool plain = !ex.dz.enabled && !ex.da.enabled && !ex.dz_rec && !ex.da_rec;
             ProfScope ps(c, "tc_bwd_x_l" + std::to_string(l), stream);
             POZ_TRY(tc::gemm_backward_data(dz, Pb + c->off[l], batch, K, N, static_cast<const __nv_bfloat16*>(c->abuf[l - 1]),
-                                           c->acts[l - 1], static_cast<__nv_bfloat16*>(c->dzbuf[l - 1]), sms, stream));
+                                           c->acts[l - 1], static_cast<__nv_bfloat16*>(c->dzbuf[l - 1]), sms, stream,
+                                           plain ? nullptr : &ex));
         }
     }
     c->grads_pending = true;
-    c->diag_pending = false;
+    c->diag_pending = diag != 0;
     return 0;
 }
 
@@ -1764,7 +1823,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     for (auto& p : c->dy_rec) dev_free(p);
     dev_free(c->ebuf); dev_free(c->debuf); dev_free(c->de_rec);
     dev_free(reinterpret_cast<void*&>(c->bn_part));
-    dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch));
+    dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch)); dev_free(c->wide_xg); dev_free(c->wide_tg);
     dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
     dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz); for (auto& q : c->tcs_dzp) dev_free(q);
     dev_free(reinterpret_cast<void*&>(c->tc_logits));
@@ -2312,7 +2371,6 @@ static int diag_ready(poz_ctx* c, int layer, const char* who) {
 
 static int diag_tensor(poz_ctx* c, int layer, int which, int source, const void** ptr, long long* rows, int* cols) {
     *ptr = nullptr;
-    if (c->dtype == POZ_DTYPE_BF16) POZ_FAIL("diagnostics are not available in bf16 contexts");
     if (layer < -1 || layer >= c->nl) POZ_FAIL("diagnostics: layer out of range");
     if ((source == 0 || source == 1) && c->diag_batch <= 0) POZ_FAIL("diagnostics: no step was run with diagnostics enabled");
     if (source == 3 && (!c->have_diag || !c->Gdiag)) POZ_FAIL("diagnostics: no weight gradients recorded");
@@ -2358,6 +2416,7 @@ int poz_diag_activation(poz_ctx* c, int layer, int which, double* host_out) {
     const void* src; long long rows; int cols;
     POZ_TRY(diag_tensor(c, layer, which, 0, &src, &rows, &cols));
     if (!src) POZ_FAIL("poz_diag_activation: no such entry");
+    if (diag_is_bf16(c, 0)) return get_bf16_f64(c, src, host_out, rows * cols);
     return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, rows * cols);
 }
 
@@ -2368,6 +2427,7 @@ int poz_diag_activation_grad(poz_ctx* c, int layer, int which, double* host_out,
     // the trailing softmax is not on the loss graph: its .grad is None (neural_net_model.py:545)
     if (has_grad) *has_grad = src ? 1 : 0;
     if (!src) return 0;
+    if (diag_is_bf16(c, 1)) return get_bf16_f64(c, src, host_out, rows * cols);
     return POZ_DISPATCH(c, get_f64, c, src, 0, host_out, rows * cols);
 }
 
@@ -2381,7 +2441,9 @@ int poz_diag_moments(poz_ctx* c, int layer, int which, int source, int rule, dou
     const long long n = rows * cols;
     const int blocks = (int)std::min<long long>((n + 255) / 256, 512);
     POZ_TRY(ensure_stage(c, (size_t)blocks * 5));
-    if (c->dtype == POZ_DTYPE_F64)
+    if (diag_is_bf16(c, source))
+        diag_moments_kernel<__nv_bfloat16><<<blocks, 256>>>(static_cast<const __nv_bfloat16*>(ptr), rows, cols, rule, threshold, c->stage);
+    else if (c->dtype == POZ_DTYPE_F64)
         diag_moments_kernel<double><<<blocks, 256>>>(static_cast<const double*>(ptr), rows, cols, rule, threshold, c->stage);
     else
         diag_moments_kernel<float><<<blocks, 256>>>(static_cast<const float*>(ptr), rows, cols, rule, threshold, c->stage);
@@ -2411,7 +2473,9 @@ int poz_diag_histogram(poz_ctx* c, int layer, int which, int source, const doubl
     POZ_CUDA(cudaMemcpy(d_edges, edges, (size_t)(bins + 1) * sizeof(double), cudaMemcpyHostToDevice));
     POZ_CUDA(cudaMemset(d_counts, 0, (size_t)bins * sizeof(unsigned long long)));
     const int blocks = (int)std::min<long long>((n + 255) / 256, 1184);
-    if (c->dtype == POZ_DTYPE_F64)
+    if (diag_is_bf16(c, source))
+        diag_histogram_kernel<__nv_bfloat16><<<blocks, 256>>>(static_cast<const __nv_bfloat16*>(ptr), n, d_edges, bins, d_counts);
+    else if (c->dtype == POZ_DTYPE_F64)
         diag_histogram_kernel<double><<<blocks, 256>>>(static_cast<const double*>(ptr), n, d_edges, bins, d_counts);
     else
         diag_histogram_kernel<float><<<blocks, 256>>>(static_cast<const float*>(ptr), n, d_edges, bins, d_counts);

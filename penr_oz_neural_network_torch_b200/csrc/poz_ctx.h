@@ -19,6 +19,9 @@ struct poz_ctx {
     size_t act_esz = 4;               // bytes per element of activations (2 in bf16 contexts)
     void* Pb = nullptr;               // bf16 copy of the parameters (bf16 contexts)
     float* colsum_scratch = nullptr;  // partial column sums for the bias gradient (bf16 contexts)
+    void* wide_xg = nullptr;          // bf16 contexts: the sampled rows of a gathered batch, dense (inputs / targets)
+    void* wide_tg = nullptr;
+    long long wide_g_batch = 0;
     // split-bf16 tensor-core path of float32 contexts (csrc/poz_tc3.*)
     void* Wp = nullptr;               // weight planes, layer l at wp_off[l]: [3][in_l][wp_ld[l]] bf16
     std::vector<long long> wp_off, wp_ld;

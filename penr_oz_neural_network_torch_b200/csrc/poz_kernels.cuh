@@ -22,6 +22,10 @@ struct SegTable {
     int stat_slot[MAX_SEGS];         // update-ratio slot, -1 if none
 };
 
+// element -> double, whatever the storage type of a diagnostics tensor
+template <typename T> __device__ __forceinline__ double as_double(T v) { return (double)v; }
+template <> __device__ __forceinline__ double as_double<__nv_bfloat16>(__nv_bfloat16 v) { return (double)__bfloat162float(v); }
+
 // First kernel of every step: advances the epoch / Adam counters and derives the step's scalars
 // (neural_net_model.py:464 lr decay; torch/optim/adam.py bias corrections).
 static __global__ void step_begin_kernel(DevState* st, double* cost_ring, long long cost_cap,
@@ -426,7 +430,7 @@ __global__ void diag_moments_kernel(const T* __restrict__ x, long long rows, int
         for (long long r = (long long)blockIdx.x * wpb + (threadIdx.x >> 5); r < rows; r += (long long)gridDim.x * wpb) {
             double rmax = -INFINITY, rsq = 0.0;
             for (int j = lane; j < cols; j += 32) {
-                const double v = (double)x[r * cols + j];
+                const double v = as_double<T>(x[r * cols + j]);
                 s += v; s2 += v * v; mn = v < mn ? v : mn; mx = v > mx ? v : mx; rmax = v > rmax ? v : rmax;
                 rsq += v * v;
             }
@@ -436,7 +440,7 @@ __global__ void diag_moments_kernel(const T* __restrict__ x, long long rows, int
         }
     } else {
         for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-            const double v = (double)x[i];
+            const double v = as_double<T>(x[i]);
             s += v; s2 += v * v; mn = v < mn ? v : mn; mx = v > mx ? v : mx;
             if (rule == 1) sat += (fabs(v) > thr) ? 1.0 : 0.0;
             else if (rule == 2) sat += (v <= 0.0) ? 1.0 : 0.0;
@@ -471,7 +475,7 @@ __global__ void diag_histogram_kernel(const T* __restrict__ x, long long n, cons
     __syncthreads();
     const double lo = e[0], scale = (double)bins / (e[bins] - e[0]);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const double v = (double)x[i];
+        const double v = as_double<T>(x[i]);
         int pos = (int)((v - lo) * scale);
         pos = pos < 0 ? 0 : (pos > bins - 1 ? bins - 1 : pos);
         while (pos > 0 && v < e[pos]) --pos;

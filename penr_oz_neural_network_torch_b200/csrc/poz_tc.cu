@@ -78,24 +78,32 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, long long M, int
     return 0;
 }
 
+static void apply_extras(EpiParams& ep, const Extras* ex) {
+    if (!ex) return;
+    ep.dz = ex->dz; ep.da = ex->da; ep.st = ex->st;
+    ep.z_rec = ex->z_rec; ep.da_rec = ex->da_rec; ep.dz_rec = ex->dz_rec;
+}
+
 int gemm_forward(const __nv_bfloat16* x, const __nv_bfloat16* w, long long M, int N, int K, const float* bias,
-                 int act, __nv_bfloat16* out, int sms, cudaStream_t s) {
+                 int act, __nv_bfloat16* out, int sms, cudaStream_t s, const Extras* ex) {
     CUtensorMap ma, mb;
     POZ_TRY(make_map(&ma, x, M, K, K, 64, 256));     // A = X [M][K], k-contiguous: box {64 k, 256 m}
     POZ_TRY(make_map(&mb, w, K, N, N, 64, 64));      // B = W [K][N], n-contiguous: boxes {64 n, 64 k}
     EpiParams ep{};
     ep.out = out; ep.ldo = N; ep.bias = bias; ep.act = act;
+    apply_extras(ep, ex);
     return launch<MAJOR_K, MAJOR_MN, EPI_BIAS_ACT_BF16>(ma, mb, M, N, K, 1, ep, sms, s);
 }
 
 int gemm_backward_data(const __nv_bfloat16* dz, const __nv_bfloat16* w, long long M, int K_in, int N_out,
                        const __nv_bfloat16* a_prev, int act_prev, __nv_bfloat16* dz_prev, int sms,
-                       cudaStream_t s) {
+                       cudaStream_t s, const Extras* ex) {
     CUtensorMap ma, mb;
     POZ_TRY(make_map(&ma, dz, M, N_out, N_out, 64, 256));        // A = dZ [M][N_out], k-contiguous
     POZ_TRY(make_map(&mb, w, K_in, N_out, N_out, 64, 256));      // B = W [K_in][N_out]: rows = mma-N, k-contiguous
     EpiParams ep{};
     ep.out = dz_prev; ep.ldo = K_in; ep.aux = a_prev; ep.act = act_prev;
+    apply_extras(ep, ex);
     return launch<MAJOR_K, MAJOR_K, EPI_ACTGRAD_BF16>(ma, mb, M, K_in, N_out, 1, ep, sms, s);
 }
 

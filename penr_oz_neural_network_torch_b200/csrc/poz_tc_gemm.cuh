@@ -42,6 +42,13 @@ struct EpiParams {
     const float* bias;         // EPI_BIAS_ACT_BF16: [N] or null
     const __nv_bfloat16* aux;  // EPI_ACTGRAD_BF16: recorded activation of the previous unit [M][ldo]
     int act;
+    // dropout points (neural_net_model.py:393-395) of this unit (forward: on z, then on a) or of the previous unit
+    // (backward-x: the masks are regenerated), both optional; diagnostics outputs (:491-493), all nullable
+    DropPoint dz, da;
+    const DevState* st;
+    __nv_bfloat16* z_rec;      // forward: the recorded (post-dropout) linear output
+    __nv_bfloat16* da_rec;     // backward-x: gradient of the previous unit's recorded activation output
+    __nv_bfloat16* dz_rec;     // backward-x: gradient of its recorded linear output
 };
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------
@@ -326,12 +333,46 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                         if (n + j < N) f[j] += __ldg(bp + j);
                                 }
                             }
+                            if (ep.dz.enabled) {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j)
+                                    if (n + j < N) f[j] = drop_keep(ep.dz, ep.st, m, n + j, (int)ep.ldo) ? f[j] * (float)ep.dz.scale : 0.f;
+                            }
+                            if (ep.z_rec) {
+                                __nv_bfloat16* zr = ep.z_rec + m * ep.ldo + n;
+#pragma unroll
+                                for (int j = 0; j < 32; ++j)
+                                    if (n + j < N) zr[j] = __float2bfloat16_rn(f[j]);
+                            }
                             if (ep.act == ACT_RELU) {
 #pragma unroll
                                 for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
                             } else if (ep.act != ACT_NONE) {
 #pragma unroll
                                 for (int j = 0; j < 32; ++j) f[j] = act_fwd<float>(ep.act, f[j]);
+                            }
+                            if (ep.da.enabled) {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j)
+                                    if (n + j < N) f[j] = drop_keep(ep.da, ep.st, m, n + j, (int)ep.ldo) ? f[j] * (float)ep.da.scale : 0.f;
+                            }
+                        } else if (ep.da.enabled || ep.dz.enabled || ep.da_rec || ep.dz_rec) {
+                            // EPI_ACTGRAD_BF16, general form (test_torch_backward.py:168-170 with the dropout of :393-395):
+                            // f = gradient of the previous unit's RECORDED (dropped, scaled) activation output
+                            const __nv_bfloat16* aux = ep.aux + m * ep.ldo + n;
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                if (n + j >= N) continue;
+                                float g = f[j], a = __bfloat162float(aux[j]);
+                                if (ep.da_rec) ep.da_rec[m * ep.ldo + n + j] = __float2bfloat16_rn(g);
+                                if (ep.da.enabled) {
+                                    g = drop_keep(ep.da, ep.st, m, n + j, (int)ep.ldo) ? g * (float)ep.da.scale : 0.f;
+                                    a *= (float)ep.da.keep_prob;
+                                }
+                                g *= act_bwd_from_out<float>(ep.act, a);
+                                if (ep.dz_rec) ep.dz_rec[m * ep.ldo + n + j] = __float2bfloat16_rn(g);
+                                if (ep.dz.enabled) g = drop_keep(ep.dz, ep.st, m, n + j, (int)ep.ldo) ? g * (float)ep.dz.scale : 0.f;
+                                f[j] = g;
                             }
                         } else {   // EPI_ACTGRAD_BF16: gradient through the previous unit's activation
                             const __nv_bfloat16* aux = ep.aux + m * ep.ldo + n;

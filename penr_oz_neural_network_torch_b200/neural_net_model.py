@@ -703,24 +703,39 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         eng = self._ensure_engine()
         if self.optimizer is not None:
             self._upload_adam_state()
+        # Data parallel (new: the reference is single-process): when this process is a rank of an initialised
+        # torch.distributed group, every rank draws the same indices (same torch seed, as :460 uses the global
+        # generator), trains on its contiguous share of them and all-reduces the layer gradients (dp.py); the
+        # update and therefore the parameters are identical on every rank.
+        dp = None
+        if torch.distributed.is_available() and torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1:
+            from .dp import DataParallelTrainer
+            dp = DataParallelTrainer(eng)
         n_data = len(training_data)
         # One upload of the whole buffer; each epoch's sample is a device-side row gather inside
         # the first-layer kernels instead of the reference's per-epoch list -> tensor copy (:472).
         x_all = self._inputs_to_device(eng, torch.tensor([x for x, _ in training_data], dtype=torch.float64))
         t_all = self._targets_to_device(eng, [t for _, t in training_data], True)
         stride = max(1, epochs // 100)                                      # :504
-        eng.train_begin(optimizer="adam" if self.optimizer is not None else "sgd",
-                        learning_rate=learning_rate, decay_rate=decay_rate, dropout_rate=dropout_rate,
-                        l2_lambda=l2_lambda, beta1=beta1, beta2=beta2, epsilon=epsilon, epochs=epochs,
-                        progress_stride=stride, dropout_seed=random.getrandbits(63))
+        hyper = dict(optimizer="adam" if self.optimizer is not None else "sgd",
+                     learning_rate=learning_rate, decay_rate=decay_rate, dropout_rate=dropout_rate,
+                     l2_lambda=l2_lambda, beta1=beta1, beta2=beta2, epsilon=epsilon, epochs=epochs,
+                     progress_stride=stride, dropout_seed=random.getrandbits(63))
+        lo, hi = 0, sample_size
+        if dp is not None:
+            dp.train_begin(global_batch=sample_size, **hyper)
+            lo, hi = dp.local_rows(sample_size)
+        else:
+            eng.train_begin(**hyper)
+        self._dp = dp
         for layer in self.layers:
             layer.training = True
         # one persistent index buffer: every epoch reuses the same device addresses, so the
         # library replays the step from a CUDA graph after the second epoch
-        idx_d = torch.empty((sample_size,), dtype=torch.int32, device=eng.device)
+        idx_d = torch.empty((hi - lo,), dtype=torch.int32, device=eng.device)
         # a small ring of pinned staging buffers, so that the per-epoch index upload is an asynchronous
         # copy (a pageable source would stall the host on every epoch)
-        ring = [torch.empty((sample_size,), dtype=torch.int32).pin_memory() for _ in range(8)]
+        ring = [torch.empty((hi - lo,), dtype=torch.int32).pin_memory() for _ in range(8)]
         ring_done = [None] * len(ring)
         stamps = []
         fetched = 0
@@ -729,13 +744,14 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         # stream does not allow
         side = torch.cuda.Stream(device=eng.device)
         side.wait_stream(torch.cuda.current_stream(eng.device))
+        loop_started = time.perf_counter()
         with torch.cuda.stream(side):
             for epoch in range(epochs):
                 idx = torch.randint(0, n_data, (sample_size,))                  # :460, same generator
                 slot = epoch % len(ring)
                 if ring_done[slot] is not None:
                     ring_done[slot].synchronize()                               # its copy of 8 epochs ago
-                ring[slot].copy_(idx)
+                ring[slot].copy_(idx[lo:hi])                                    # this rank's share (all of it on one GPU)
                 idx_d.copy_(ring[slot], non_blocking=True)
                 ring_done[slot] = torch.cuda.Event()
                 ring_done[slot].record(side)
@@ -744,7 +760,10 @@ class NeuralNetworkModel(MultiLayerPerceptron):
                         group["lr"] = learning_rate * (decay_rate ** epoch)
                 long_training = time.time() - last_serialized >= 10             # :488
                 diagnostics = epoch + 1 == epochs or long_training              # :491
-                eng.train_step(x_all, t_all, row_idx=idx_d, diagnostics=diagnostics)
+                if dp is not None:
+                    dp.train_step(x_all, t_all, row_idx_local=idx_d, diagnostics=diagnostics)
+                else:
+                    eng.train_step(x_all, t_all, row_idx=idx_d, diagnostics=diagnostics)
                 stamps.append(dt.now().isoformat())
                 if long_training:  # pragma: no cover
                     fetched = self._collect_progress(eng, stamps, fetched, epoch + 1, stride)
@@ -756,6 +775,9 @@ class NeuralNetworkModel(MultiLayerPerceptron):
                     last_serialized = time.time()
         torch.cuda.current_stream(eng.device).wait_stream(side)
         side.synchronize()
+        # wall time of the epoch loop alone (sampling, index upload, the steps, until the last one has finished):
+        # what bench.py reports as the class-level rate, apart from the list ingestion and the JSON saves around it
+        self.train_loop_seconds = time.perf_counter() - loop_started
         self._collect_progress(eng, stamps, fetched, epochs, stride)
         self._download_params()
         if self.optimizer is not None:
@@ -770,7 +792,8 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         reference would have recorded (:503-516)."""
         if upto <= first:
             return first
-        costs = eng.costs(first, upto - first)
+        dp = getattr(self, "_dp", None)
+        costs = dp.costs(first, upto - first) if dp is not None else eng.costs(first, upto - first)
         rec_first = (first + stride - 1) // stride
         rec_count = (upto - 1) // stride + 1 - rec_first
         ratios = eng.update_ratios(rec_first, rec_count) if rec_count > 0 else np.empty((0, 0))

@@ -109,7 +109,25 @@ def test_unsupported_requests_fail_loudly():
     from penr_oz_neural_network_torch_b200 import DeviceMLP, PozError, StackSpec
     with pytest.raises(PozError):
         DeviceMLP([784, 256, 10], StackSpec.from_algos(["linear", "relu", "linear", "softmax"]), True, "bfloat16", 0)
+    with pytest.raises(PozError):          # layer sizes must be multiples of 8 (16-byte TMA rows)
+        DeviceMLP([100, 50, 20], StackSpec.from_algos(["linear", "relu", "linear"]), True, "bfloat16", 0)
+
+
+def test_dropout_and_row_gather_in_the_bf16_context():
+    """Philox dropout in the tcgen05 epilogues (forward masks regenerated in the backward) and the row gather of
+    train()'s sampling: with p = 0 a gathered step equals the step on the materialised rows bit for bit; with
+    p = 0.3 the step runs, is reproducible for a seed, differs between seeds, and the cost stays in range."""
     eng, params, x, t, xd, td = make("adam")
-    eng.train_begin(optimizer="adam", dropout_rate=0.2, epochs=1)
-    with pytest.raises(PozError):
+    idx = torch.randperm(B, device="cuda:0")[: B // 2].to(torch.int32).contiguous()
+    eng.train_begin(optimizer="sgd", learning_rate=0.0, decay_rate=1.0, epochs=8)
+    eng.train_step(xd, td, row_idx=idx)
+    eng.train_step(xd[idx.long()].contiguous(), td[idx.long()].contiguous())
+    c = eng.costs(0, 2)
+    assert c[0] == c[1]
+    costs = []
+    for seed in (5, 5, 6):
+        eng.train_begin(optimizer="sgd", learning_rate=0.0, decay_rate=1.0, dropout_rate=0.3, dropout_seed=seed, epochs=1)
         eng.train_step(xd, td)
+        costs.append(float(eng.costs(0, 1)[0]))
+    assert costs[0] == costs[1] and costs[0] != costs[2]
+    assert 0.5 * c[0] < costs[0] < 3.0 * c[0]

@@ -9,6 +9,7 @@
 #include "poz_tc.h"
 #include "poz_tc3.h"
 #include "poz_tcs.h"
+#include "poz_tail_kernel.cuh"
 #include "poz_wide_kernels.cuh"
 
 #include <algorithm>
@@ -876,10 +877,11 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
                 }
             }
             if (c->tcs_dzp.size() != (size_t)nl) c->tcs_dzp.assign(nl, nullptr);
-            if (batch > c->tcs_dz_batch || (tcs_all && !c->tcs_dzp[nl - 1])) {
+            const bool want_l1 = c->tail_fused && c->tail_group && nl == 3;     // the fused tail hands dZ1's planes to the grouped launch
+            if (batch > c->tcs_dz_batch || (tcs_all && !c->tcs_dzp[nl - 1]) || (want_l1 && !c->tcs_dzp[1])) {
                 for (int l = 0; l < nl; ++l) {
                     dev_free(c->tcs_dzp[l]);
-                    if (l > 0 && !tcs_all) continue;
+                    if (l > 0 && !tcs_all && !(want_l1 && l == 1)) continue;
                     const size_t bytes = (size_t)3 * batch * round8(c->sizes[l + 1]) * 2;
                     POZ_TRY(dev_alloc(&c->tcs_dzp[l], bytes));
                     POZ_CUDA(cudaMemsetAsync(c->tcs_dzp[l], 0, bytes, stream));     // pad columns stay zero
@@ -931,10 +933,33 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     const size_t head_smem = ((size_t)head_K * (head_N | 1) + 32 + 8 * (size_t)head_K) * sizeof(T);
     const bool fuse_head = c->fuse_head && nl >= 2 && c->loss == POZ_LOSS_CE && head_N <= 32 && head_smem <= 96 * 1024;
 
+    // The tail of the stack -- last hidden unit, head, and the backward-x of both -- as ONE launch (poz_tail_kernel.cuh)
+    // when nothing needs the separate kernels' extras (dropout, masks, diagnostics).
+    bool tail = false, tail_group = false;
+    size_t tail_smem = 0;
+    if constexpr (std::is_same<T, float>::value) {
+        const int p = nl - 2;
+        tail = c->tail_fused && fuse_head && p >= 1 && !diag && !masks && c->cfg.dropout_rate == 0.0 && !tcs_all &&
+               batch <= c->tail_max_batch && c->sizes[p] <= TAIL_MAX_K1 && c->sizes[p] % 4 == 0 && c->sizes[p + 1] <= TAIL_MAX_N1 &&
+               c->sizes[p + 1] % 4 == 0 && head_N <= TAIL_MAX_N2 && c->acts[p] != ACT_SOFTMAX;
+        if (tail) {
+            tail_smem = tail_smem_bytes(c->sizes[p], c->sizes[p + 1], head_N);
+            tail = tail_smem <= 200 * 1024;
+        }
+        // ... and then the weight gradients of layers 0 and 1 fit ONE tensor-core launch (layer 1 without its bias row:
+        // 28 + 4 clusters of 4 CTAs on the C2 stack, where 33 can be resident), while the head's parameters and b1 are
+        // updated from the tail's per-block partial sums: four launches on the step's critical path, no side-stream GEMMs.
+        if (tail && tcs0 && tcs_fused && c->tail_group && nl == 3 && c->tcs_dzp.size() == 3 && c->tcs_dzp[1]) {
+            const long long t0 = (long long)((c->sizes[0] + hb0(c) + tcs::BM - 1) / tcs::BM) * ((c->sizes[1] + tcs::BN - 1) / tcs::BN);
+            const long long t1 = (long long)((c->sizes[1] + tcs::BM - 1) / tcs::BM) * ((c->sizes[2] + tcs::BN - 1) / tcs::BN);
+            const int sp = tcs::pick_splits(batch, t0 + t1, num_sms(c->device));
+            if (sp == 4 && t0 + t1 <= 33) { tail_group = true; tcs_w_splits = sp; }
+        }
+    }
     // forward, keeping what the backward needs (and, for diagnostics, every entry's output)
     const T* cur = x;
     const int* cur_idx = row_idx;
-    for (int l = 0; l < (fuse_head ? nl - 1 : nl); ++l) {
+    for (int l = 0; l < (fuse_head ? (tail ? nl - 2 : nl - 1) : nl); ++l) {
         T* zb = static_cast<T*>(c->zbuf[l]);
         T* ab = static_cast<T*>(c->abuf[l]);
         const int act = c->acts[l];
@@ -995,7 +1020,79 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     const long long gb = c->cfg.global_batch > 0 ? c->cfg.global_batch : batch;
     const int last = nl - 1;
     const int n_out = c->sizes[nl];
-    if (fuse_head) {
+    bool tail_done = false;
+    if constexpr (std::is_same<T, float>::value) {
+        if (tail) {
+            const int p = last - 1;
+            static bool configured = false;
+            if (!configured) {
+                POZ_CUDA(cudaFuncSetAttribute(tail_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                configured = true;
+            }
+            TailArgs ta{};
+            ta.a0 = cur;
+            ta.w1b = static_cast<const float*>(c->P) + c->off[p];
+            ta.w2b = static_cast<const float*>(c->P) + c->off[last];
+            ta.labels = static_cast<const int*>(target); ta.row_idx = row_idx;
+            ta.a1_out = static_cast<float*>(c->abuf[p]);
+            ta.dz2_out = static_cast<float*>(c->dzbuf[last]);
+            ta.dz1_out = static_cast<float*>(c->dzbuf[p]);
+            ta.dz0_out = static_cast<float*>(c->dzbuf[p - 1]);
+            if (tcs0 && p - 1 == 0) {
+                ta.dz0_planes = static_cast<unsigned short*>(c->tcs_dzp[0]);
+                ta.dz0_ldp = round8(c->sizes[p]); ta.dz0_pstride = batch * round8(c->sizes[p]);
+            }
+            const int n_w2 = (c->sizes[p + 1] + c->has_bias) * head_N;              // parameters of the head
+            const int pw2 = ((c->sizes[p + 1] + 1) * head_N + 3) & ~3;           // the tail always writes the bias row of the partial too
+            const int n_blocks = (int)((batch + TAIL_ROWS - 1) / TAIL_ROWS);
+            if (tail_group) {
+                const long long need = (long long)n_blocks * (pw2 + c->sizes[p + 1]);
+                if (need > c->tail_part_elems) {
+                    dev_free(reinterpret_cast<void*&>(c->tail_part));
+                    POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->tail_part), (size_t)need * sizeof(float)));
+                    c->tail_part_elems = need;
+                    clear_graphs(c);
+                }
+                ta.part = c->tail_part; ta.part_stride = pw2 + c->sizes[p + 1]; ta.part_b1 = pw2;
+                ta.dz1_planes = static_cast<unsigned short*>(c->tcs_dzp[p]);
+                ta.dz1_ldp = round8(c->sizes[p + 1]); ta.dz1_pstride = batch * round8(c->sizes[p + 1]);
+            }
+            ta.M = batch; ta.K1 = c->sizes[p]; ta.N1 = c->sizes[p + 1]; ta.N2 = head_N; ta.has_bias = c->has_bias;
+            ta.act1 = c->acts[p]; ta.act0 = c->acts[p - 1];
+            ta.inv_batch = 1.0 / (double)gb;
+            ta.cost_base = c->cost_ring; ta.cost_cap = c->cost_cap; ta.st = c->st;
+            {
+                ProfScope ps(c, "tail", stream);
+                POZ_TRY(launch_pdl(tail_fused_kernel, dim3((unsigned)n_blocks), dim3(TAIL_THREADS), tail_smem, stream, ta));
+            }
+            tail_done = true;
+            if (tail_group) {
+                // the head's [W2; b2] and b1: partial sums -> optimizer, on the side stream beside the grouped launch
+                cudaStream_t ws = c->side_stream;
+                POZ_CUDA(cudaEventRecord(c->dz_ready[last], stream));
+                POZ_CUDA(cudaStreamWaitEvent(ws, c->dz_ready[last], 0));
+                auto mk = [&](int l) {
+                    tcs::UpdateEpi ue{};
+                    ue.p = static_cast<float*>(c->P) + c->off[l];
+                    ue.am = static_cast<float*>(c->AM) + c->off[l];
+                    ue.av = static_cast<float*>(c->AV) + c->off[l];
+                    ue.ld = c->sizes[l + 1]; ue.w_rows = c->sizes[l]; ue.st = c->st;
+                    ue.cost_base = c->cost_ring; ue.cost_cap = c->cost_cap;
+                    ue.stats = c->stats; ue.n_stat = n_stat_slots(c); ue.stat_slot = seg.stat_slot[l];
+                    return ue;
+                };
+                const int n_b1 = c->has_bias ? c->sizes[p + 1] : 0;
+                const int total = n_w2 + n_b1;
+                ProfScope ps(c, "tail_update", ws);
+                POZ_TRY(launch_pdl(tail_update_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, ws,
+                                   static_cast<const float*>(c->tail_part), n_blocks, pw2 + c->sizes[p + 1], pw2, n_w2, head_N, mk(last),
+                                   n_b1, c->sizes[p], mk(p)));
+                POZ_CUDA(cudaEventRecord(c->grad_ready[last], ws));
+            }
+        }
+    }
+    if (tail_done) {
+    } else if (fuse_head) {
         const int p = last - 1;
         HeadArgs<T> h{};
         h.a_prev = cur;
@@ -1062,9 +1159,10 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     // The weight-gradient GEMM of a layer >= 1 only needs that layer's dZ, so it is forked onto a side
     // stream and runs beside the backward-x chain (each of these launches fills a fraction of the GPU);
     // the compute stream joins again before the update.  Inside a graph capture this becomes a fork/join.
-    const bool fork = c->fork_dw && c->side_stream && nl >= 2 && !tcs_all;
-    bool dz0_planes_done = false;      // the epilogue that produced layer 0's dZ also wrote its bf16 planes
+    const bool fork = c->fork_dw && c->side_stream && nl >= 2 && !tcs_all && !tail_group;
+    bool dz0_planes_done = tail && tcs0 && nl == 3;      // the epilogue that produced layer 0's dZ also wrote its bf16 planes
     for (int l = last; l >= 0; --l) {
+        if (tail_group) break;          // nothing left: the tail produced every dZ, the grouped launch below the rest
         const int K = c->sizes[l], N = c->sizes[l + 1], hb = c->has_bias;
         const T* dz = static_cast<const T*>(c->dzbuf[l]);
         cudaStream_t ws = stream;
@@ -1163,7 +1261,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             if (c->grad_ready.size() == (size_t)nl) POZ_CUDA(cudaEventRecord(c->grad_ready[l], ws));
         }
       }
-        if (l > 0 && !(fuse_head && l == last)) {
+        if (l > 0 && !(fuse_head && l == last) && !(tail && l == last - 1)) {
             const T* w = static_cast<const T*>(c->P) + c->off[l];
             Operand<T> A = make_operand<T>(dz, N, nullptr, batch, N, 0);
             Operand<T> B = make_operand<T>(w, N, nullptr, K, N, 0);
@@ -1207,7 +1305,7 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
                 // Layer 0's update rides in its weight-gradient launch; this layer's follows its own weight gradient on
                 // the same side stream, so that no update kernel is left on the step's critical path.  It must not
                 // overtake the backward-x launch above, which still reads this layer's weights.
-                if (!(fuse_head && l == last)) {
+                if (!(fuse_head && l == last) && !(tail && l == last - 1)) {
                     POZ_CUDA(cudaEventRecord(c->dz_ready[l], stream));
                     POZ_CUDA(cudaStreamWaitEvent(ws, c->dz_ready[l], 0));
                 }
@@ -1233,6 +1331,41 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     if (fork)
         for (int l = 1; l < nl; ++l) POZ_CUDA(cudaStreamWaitEvent(stream, c->grad_ready[l], 0));
     if constexpr (std::is_same<T, float>::value) {
+        if (tail_group) {
+            tcs::Gemm gs[2];
+            tcs::UpdateEpi ues[2];
+            for (int l = 0; l < 2; ++l) {
+                const int K = c->sizes[l], N = c->sizes[l + 1], hb = (l == 0) ? c->has_bias : 0;   // b1 comes from the tail's partial sums
+                tcs::Gemm& g = gs[l];
+                g = tcs::Gemm{};
+                g.a = l == 0 ? x : static_cast<const float*>(c->abuf[0]);
+                g.lda = K; g.row_idx = l == 0 ? row_idx : nullptr; g.a_transposed = 1; g.a_cols = K; g.ones_row = hb;
+                g.M = (long long)K + hb; g.N = N; g.K = batch; g.splits = tcs_w_splits;
+                g.b.ptr = static_cast<const __nv_bfloat16*>(c->tcs_dzp[l]);
+                g.b.rows = batch; g.b.cols = N; g.b.ld = round8(N); g.b.plane_stride = batch * round8(N);
+                tcs::UpdateEpi& ue = ues[l];
+                ue = tcs::UpdateEpi{};
+                ue.p = static_cast<float*>(c->P) + c->off[l];
+                ue.am = static_cast<float*>(c->AM) + c->off[l];
+                ue.av = static_cast<float*>(c->AV) + c->off[l];
+                ue.ld = N; ue.w_rows = K; ue.st = c->st; ue.cost_base = c->cost_ring; ue.cost_cap = c->cost_cap;
+                ue.stats = c->stats; ue.n_stat = n_stat_slots(c); ue.stat_slot = seg.stat_slot[l];
+                if (l == 0) {
+                    ue.planes = static_cast<__nv_bfloat16*>(c->Wp) + c->wp_off[0];
+                    ue.ldp = c->wp_ld[0]; ue.plane_stride = (long long)K * c->wp_ld[0];
+                }
+            }
+            {
+                ProfScope ps(c, "tcs_bwd_w_l0_l1_update", stream);
+                POZ_TRY(tcs::backward_weight_update(gs, ues, 2, stream));
+            }
+            c->upd_done_mask |= 7u;
+            if (c->grad_ready.size() == (size_t)nl) {
+                POZ_CUDA(cudaEventRecord(c->grad_ready[0], stream));
+                POZ_CUDA(cudaEventRecord(c->grad_ready[1], stream));
+            }
+            POZ_CUDA(cudaStreamWaitEvent(stream, c->grad_ready[last], 0));      // join the side stream (tail_update)
+        }
         if (tcs_all) {
             // every layer's [dW; db] = [A 1]^T dZ in one grouped launch; its epilogues are the optimizer
             tcs::Gemm gs[tcs::MAX_GROUP];
@@ -1659,6 +1792,8 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
         }
         POZ_TRY(tcs::trace_enable());
     }
+    if (const char* e = getenv("POZ_TAIL")) c->tail_fused = atoi(e) != 0;
+    if (const char* e = getenv("POZ_TAIL_GROUP")) c->tail_group = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS")) c->tcs_enabled = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS_FUSE_UPDATE")) c->tcs_fuse_update = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS_GROUP")) c->tcs_group = atoi(e) != 0;
@@ -1783,8 +1918,9 @@ static void dump_kernel_trace() {
         }
     }
     for (const Group& g : groups) {
-        fprintf(stderr, "[poz kernel trace] launch below: first CTA entry at %lld ns, last CTA exit at %lld ns (relative to the latest launch's exit)\n",
-                (long long)g.first - (long long)t_end, (long long)g.last_exit - (long long)t_end);
+        fprintf(stderr, "[poz kernel trace] launch below: first CTA entry at %lld ns, last CTA exit at %lld ns (relative to the latest launch's exit); "
+                        "absolute %%globaltimer mod 1e9: %llu .. %llu\n",
+                (long long)g.first - (long long)t_end, (long long)g.last_exit - (long long)t_end, g.first % 1000000000ull, g.last_exit % 1000000000ull);
         fprintf(stderr, "[poz kernel trace] tag %d M %d N %d K %d: %zu CTAs; mean (max) ns after first CTA start: entry %.0f (%llu) "
                         "setup+prologue %.0f (%llu) first tile ready %.0f (%llu) main loop done %.0f (%llu) epilogue done %.0f (%llu) exit %.0f (%llu)\n",
                 g.tag, g.m, g.n, g.k, g.cnt, g.sum[0] / g.cnt, g.mx[0], g.sum[1] / g.cnt, g.mx[1], g.sum[2] / g.cnt, g.mx[2],
@@ -1825,7 +1961,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     dev_free(reinterpret_cast<void*&>(c->bn_part));
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch)); dev_free(c->wide_xg); dev_free(c->wide_tg);
     dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
-    dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz); for (auto& q : c->tcs_dzp) dev_free(q);
+    dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz); for (auto& q : c->tcs_dzp) dev_free(q); dev_free(reinterpret_cast<void*&>(c->tail_part));
     dev_free(reinterpret_cast<void*&>(c->tc_logits));
     dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
     dev_free(reinterpret_cast<void*&>(c->st));

@@ -47,6 +47,12 @@ struct poz_ctx {
     // 33 fit at once: a second wave), so opt-in: POZ_TCS_GROUP=1
     bool tcs_group = false;
     unsigned upd_done_mask = 0;       // layers whose update this step's backward already applied
+    bool tail_fused = true;           // last hidden unit + head + their backward-x in one launch (POZ_TAIL=0 disables)
+    long long tail_max_batch = 4096;
+    bool tail_group = true;           // + the weight gradients of layers 0 and 1 in one tensor-core launch, head / b1 updated from the
+                                      //   tail's partial sums (POZ_TAIL_GROUP=0 disables)
+    float* tail_part = nullptr;       // [blocks][stride] partial sums written by tail_fused_kernel
+    long long tail_part_elems = 0;
     bool in_step = false;             // inside poz_train_step (backward + apply as one call: the update may be fused)
     void* tc_scr[3] = {nullptr, nullptr, nullptr};   // plane stacks: input chunk, ping, pong
     float* tc_logits = nullptr;       // fp32 logits of a chunk (trailing softmax)

@@ -233,92 +233,6 @@ template <typename T> __global__ void grad_finalize_kernel(T* g, long long slab,
 //   SGD : neural_net_model.py:499-500
 //   L2  : neural_net_model.py:482-483 (weights only)
 //   ratio statistics: neural_net_model.py:506-507
-// `part` of `parts` cooperating blocks works on segment l (a kernel passes blockIdx.x / gridDim.x; the
-// fused narrow step passes its own task split).  The gradient slabs may have been written earlier in
-// the same launch, so g is not marked read-only.
-template <typename T>
-__device__ __forceinline__ void update_body(T* __restrict__ p, T* __restrict__ am, T* __restrict__ av,
-                                            const T* g, long long slab, T* __restrict__ g_diag,
-                                            const SegTable& seg, const DevState* st, double* cost_base,
-                                            long long cost_cap, double* stats, __nv_bfloat16* __restrict__ p_bf16,
-                                            int l, int part, int parts) {
-    const long long n = seg.n_elems[l];
-    const long long nw = seg.w_elems[l];
-    const int S = seg.splits[l];
-    const bool adam = st->optimizer == 1;
-    const T l2 = T(st->l2);
-    const T lr = T(st->lr_t);
-    const T b1c = T(1.0 - st->beta1), b2 = T(st->beta2), b2c = T(1.0 - st->beta2);
-    const T step_size = T(st->step_size), bc2s = T(st->bc2_sqrt), eps = T(st->eps);
-    const long long rec = st->cur_record;
-    double l2acc = 0.0, sd = 0.0, sd2 = 0.0, sw = 0.0, sw2 = 0.0;
-    // Four elements per thread and pass, all their loads issued before the first store: the stores may
-    // alias the gradient slabs as far as the compiler knows, so a one-element loop would serialise a
-    // full memory round trip per element.
-    constexpr int U = 4;
-    const long long stride = (long long)parts * blockDim.x;
-    const bool use_l2 = st->l2 > 0.0;
-    for (long long i0 = (long long)part * blockDim.x + threadIdx.x; i0 < n; i0 += U * stride) {
-        T gr[U], w[U], m[U], v[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const long long i = i0 + u * stride;
-            gr[u] = T(0); w[u] = T(0); m[u] = T(0); v[u] = T(0);
-            if (i < n) {
-                const long long idx = seg.off[l] + i;
-                gr[u] = g[idx];
-                w[u] = p[idx];
-                if (adam) { m[u] = am[idx]; v[u] = av[idx]; }
-            }
-        }
-        for (int k = 1; k < S; ++k) {
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const long long i = i0 + u * stride;
-                if (i < n) gr[u] += g[(long long)k * slab + seg.off[l] + i];
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const long long i = i0 + u * stride;
-            if (i >= n) continue;
-            const long long idx = seg.off[l] + i;
-            const bool is_w = i < nw;
-            T gu = gr[u];
-            if (is_w && use_l2) {
-                l2acc += (double)w[u] * (double)w[u];
-                gu += T(2) * l2 * w[u];
-            }
-            if (g_diag) g_diag[idx] = gu;
-            T wn;
-            if (adam) {
-                const T mu = m[u] + (gu - m[u]) * b1c;
-                const T vu = v[u] * b2 + b2c * gu * gu;
-                am[idx] = mu;
-                av[idx] = vu;
-                const T denom = sqrt(vu) / bc2s + eps;
-                wn = w[u] - step_size * (mu / denom);
-            } else {
-                wn = w[u] - lr * gu;
-            }
-            p[idx] = wn;
-            if (p_bf16) p_bf16[idx] = __float2bfloat16_rn((float)wn);
-            if (rec >= 0 && is_w) {
-                const double d = (double)wn - (double)w[u];
-                sd += d; sd2 += d * d; sw += (double)wn; sw2 += (double)wn * (double)wn;
-            }
-        }
-    }
-    if (st->l2 > 0.0) block_add_double(l2acc * st->l2 * st->l2_share, cost_slot(cost_base, cost_cap, st));
-    if (rec >= 0 && seg.stat_slot[l] >= 0) {
-        double* s = stats + (rec * seg.n_stat + (seg.stat_slot[l] < 0 ? 0 : seg.stat_slot[l])) * 4;
-        block_add_double(sd, s + 0);
-        block_add_double(sd2, s + 1);
-        block_add_double(sw, s + 2);
-        block_add_double(sw2, s + 3);
-    }
-}
-
 template <typename T>
 __global__ void update_kernel(T* __restrict__ p, T* __restrict__ am, T* __restrict__ av,
                               const T* __restrict__ g, long long slab, T* __restrict__ g_diag,

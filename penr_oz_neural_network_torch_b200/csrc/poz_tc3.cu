@@ -240,6 +240,10 @@ void trace_dump() {
                 ++cnt; m = r.m; nn = r.n; k = r.k;
                 for (int q = 0; q < 6; ++q) { sum[q] += (double)(r.t[q] - first); if (r.t[q] - first > mx[q]) mx[q] = r.t[q] - first; }
             }
+        unsigned long long last_exit = 0;
+        for (auto& r : h) if (r.tag == tag && latest - r.t[0] < 60000ull && r.t[5] > last_exit) last_exit = r.t[5];
+        fprintf(stderr, "[poz tcs trace] tag %d: absolute %%globaltimer mod 1e9 of the last launch: %llu .. %llu\n", tag, first % 1000000000ull,
+                last_exit % 1000000000ull);
         fprintf(stderr, "[poz tcs trace] tag %d (M %d N %d K %d): %zu CTAs; mean (max) ns after the first CTA's entry: entry %.0f (%llu) "
                         "set-up %.0f (%llu) first half-block in tensor memory %.0f (%llu) accumulators complete %.0f (%llu) "
                         "partials exchanged %.0f (%llu) exit %.0f (%llu)\n",

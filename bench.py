@@ -400,7 +400,10 @@ def run_c2(args, world, rank, local):
                      "runs_ms_per_step": [round(v / e2e_steps, 5) for v in e2e_runs],
                      "class_api": class_api,
                      "h2d_copy_us_per_step": round(h2d_us, 1),
-                     "h2d_gbs": round(batch * 784 * 4 / (h2d_us * 1e-6) / 1e9, 1)},
+                     "h2d_gbs": round(batch * 784 * 4 / (h2d_us * 1e-6) / 1e9, 1),
+                     "bound": ("host link: one step's 3.2 MB fp32 batch takes %.1f us over this box's PCIe link, the device step "
+                               "%.1f us; the copies overlap the steps before them, so e2e ~ max(copy, step)" % (h2d_us, ms / args.steps * 1e3)),
+                     "link_floor_samples_per_s": round(batch / (h2d_us * 1e-6))},
                 gpu_launches=int(launches), roofline=roof, clocks=clocks, dtype="f32",
                 extras={"with_dropout_0.2": {"ms_per_step": round(ms_drop / args.steps, 5),
                                              "value": round(world * batch * args.steps / (ms_drop * 1e-3)),

@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <ctime>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -1930,6 +1931,8 @@ static void dump_kernel_trace() {
     cudaMemcpyToSymbol(fast::d_ktrace_n, &zero, sizeof(zero));
 }
 
+static void host_trace_dump();
+
 int poz_ctx_destroy(poz_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
@@ -1944,6 +1947,7 @@ int poz_ctx_destroy(poz_ctx* c) {
     if (c->feed.read_stream) cudaStreamDestroy(c->feed.read_stream);
     if (c->feed.cost_pinned) cudaFreeHost(c->feed.cost_pinned);
     if (getenv("POZ_KERNEL_TRACE") && atoi(getenv("POZ_KERNEL_TRACE")) != 0) { dump_kernel_trace(); tcs::trace_dump(); }
+    host_trace_dump();
     free_workspace(c);
     for (auto e : c->grad_ready) if (e) cudaEventDestroy(e);
     for (auto e : c->dz_ready) if (e) cudaEventDestroy(e);
@@ -2373,6 +2377,27 @@ static int feed_read_cost(poz_ctx* c, int slot, double* out) {
     return 0;
 }
 
+// POZ_HOST_TRACE=1: host time spent in the segments of poz_train_step_host, printed when the context is destroyed
+static bool host_trace_on() {
+    static const bool on = getenv("POZ_HOST_TRACE") && atoi(getenv("POZ_HOST_TRACE")) != 0;
+    return on;
+}
+static double g_host_seg[6] = {0, 0, 0, 0, 0, 0};
+static long long g_host_calls = 0;
+static inline double host_now() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+}
+static void host_trace_dump() {
+    if (!host_trace_on() || !g_host_calls) return;
+    fprintf(stderr, "[poz host trace] poz_train_step_host, us per call over %lld calls: copies %.2f, copied-event + wait %.2f, "
+                    "step launch %.2f, consumed-event %.2f, cost read-back %.2f\n", g_host_calls, g_host_seg[0] / g_host_calls,
+            g_host_seg[1] / g_host_calls, g_host_seg[2] / g_host_calls, g_host_seg[3] / g_host_calls, g_host_seg[4] / g_host_calls);
+    g_host_calls = 0;
+    for (double& v : g_host_seg) v = 0;
+}
+
 int poz_train_step_host(poz_ctx* c, const void* x_host, const void* target_host, long long batch, double* done_cost,
                         void* stream) {
     POZ_TRY(check_layer(c, 0, "poz_train_step_host"));
@@ -2387,13 +2412,19 @@ int poz_train_step_host(poz_ctx* c, const void* x_host, const void* target_host,
     // host -> device on the copy stream.  The slot is free: the step that last used it was issued SLOTS calls ago,
     // and the previous call did not return before the step issued POZ_HOST_LAG = SLOTS - 1 calls before IT had
     // finished (its cost read or the event wait below) -- no stream-side wait needed, one driver call fewer per step.
+    const bool ht = host_trace_on();
+    double t0 = ht ? host_now() : 0.0, t1;
     POZ_CUDA(cudaMemcpyAsync(f.x[slot], x_host, (size_t)(batch * feed_x_row_bytes(c)), cudaMemcpyHostToDevice, f.copy_stream));
     POZ_CUDA(cudaMemcpyAsync(f.t[slot], target_host, (size_t)(batch * feed_t_row_bytes(c)), cudaMemcpyHostToDevice, f.copy_stream));
+    if (ht) { t1 = host_now(); g_host_seg[0] += t1 - t0; t0 = t1; }
     POZ_CUDA(cudaEventRecord(f.copied[slot], f.copy_stream));
     POZ_CUDA(cudaStreamWaitEvent(s, f.copied[slot], 0));
+    if (ht) { t1 = host_now(); g_host_seg[1] += t1 - t0; t0 = t1; }
     f.epoch_of[slot] = c->epoch_host;
     POZ_TRY(poz_train_step(c, f.x[slot], f.t[slot], nullptr, batch, nullptr, 0, stream));
+    if (ht) { t1 = host_now(); g_host_seg[2] += t1 - t0; t0 = t1; }
     POZ_CUDA(cudaEventRecord(f.consumed[slot], s));
+    if (ht) { t1 = host_now(); g_host_seg[3] += t1 - t0; t0 = t1; }
     f.calls += 1;
     // the cost of the step issued POZ_HOST_LAG calls ago: only that step is waited for
     if (done_cost) {
@@ -2402,6 +2433,7 @@ int poz_train_step_host(poz_ctx* c, const void* x_host, const void* target_host,
     } else if (f.calls > POZ_HOST_LAG) {
         POZ_CUDA(cudaEventSynchronize(f.consumed[(f.calls - 1 - POZ_HOST_LAG) % SLOTS]));   // keep the host POZ_HOST_LAG steps ahead, no further
     }
+    if (ht) { g_host_seg[4] += host_now() - t0; g_host_calls += 1; }
     return 0;
 }
 

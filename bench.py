@@ -192,6 +192,23 @@ def synth_pool(n_batches, batch, device, seed):
 # ---- kernel-level algorithmic work, for the roofline of the dominant kernel ------------------------
 def kernel_work(tag, batch):
     """(algorithmic bytes, flops) of one launch of kernel `tag` at C2 shapes (fp32)."""
+    if tag == "tail":
+        # last hidden unit + head + both backward-x in one launch (poz_tail_kernel.cuh): reads a0, [W1;b1], [W2;b2], labels;
+        # writes a1, dZ2, dZ1 and dZ0 (fp32 + three bf16 planes each) and the per-block partial sums of [dW2;db2], db1
+        k1, n1, n2 = SIZES[1], SIZES[2], SIZES[3]
+        nblk = (batch + 7) // 8
+        nbytes = (4 * batch * k1 + 4 * (k1 + 1) * n1 + 4 * (n1 + 1) * n2 + 4 * batch + 4 * batch * n1 + 4 * batch * n2 +
+                  10 * batch * n1 + 10 * batch * k1 + 4 * nblk * ((n1 + 1) * n2 + n1))
+        flops = 2 * batch * ((k1 + 1) * n1 + (n1 + 1) * n2) + 2 * batch * (n1 * n2 + k1 * n1) + 2 * batch * (n1 + 1) * n2
+        return nbytes, flops
+    if tag == "tail_update":
+        n1, n2 = SIZES[2], SIZES[3]
+        npar = (n1 + 1) * n2 + n1
+        return 4 * ((batch + 7) // 8) * npar + 4 * 6 * npar, ((batch + 7) // 8) * npar + 12 * npar
+    if tag == "tcs_bwd_w_l0_l1_update":   # layers 0 and 1 in one grouped launch (layer 1 without its bias row)
+        b0, f0 = kernel_work("tcs_bwd_w_l0_update", batch)
+        b1, f1 = kernel_work("tcs_bwd_w_l1_update", batch)
+        return b0 + b1, f0 + f1
     core = tag[4:] if tag.startswith("tcs_") else tag
     if core[:5] in ("fwd_l", "bwd_w", "bwd_x"):
         l = int(core.split("_l", 1)[1].split("_")[0])

@@ -11,7 +11,7 @@
 // W1 (up to 256 x 128 fp32, 132 KB) is staged once per block in shared memory with 16-byte cp.async copies into rows
 // of pitch N1 + 4 floats: the forward reads it by columns (lanes = consecutive columns), the backward-x by rows with
 // 16-byte loads -- eight consecutive rows 528 bytes apart tile the 32 banks, so neither pass has a bank conflict.  At
-// batch 1024 this is 128 blocks, one per SM, replacing three launches (7 + 7 + 9 us in the CUDA graph) and the two
+// batch 1024 this is 128 blocks of 512 threads, one per SM, replacing three launches (7 + 7 + 9 us in the CUDA graph) and the two
 // kernel boundaries between them; exact fp32 FMA arithmetic, no tensor cores (0.13 GFLOP in all).
 // Optionally the block also leaves what the WEIGHT GRADIENTS of the two units need from these rows: dZ1 as bf16
 // planes (B operand of the tensor-core weight-gradient launch, poz_tcs_kernel.cuh), and its eight rows' partial sums
@@ -25,7 +25,9 @@
 namespace poz {
 
 constexpr int TAIL_ROWS = 8;
-constexpr int TAIL_THREADS = 256;
+constexpr int TAIL_THREADS = 512;
+constexpr int TAIL_CHUNK = 32;            // rows of W1 per asynchronous copy group
+constexpr int TAIL_KSPLIT = 8;            // the forward splits K1 over 8 thread groups, the backward-x N1 over 2
 constexpr int TAIL_MAX_K1 = 256, TAIL_MAX_N1 = 128, TAIL_MAX_N2 = 32;
 
 struct TailArgs {
@@ -52,6 +54,41 @@ struct TailArgs {
     const DevState* st;
 };
 
+// four adjacent values -> their bf16 planes hi / mid / lo, 8-byte stores where the pitch allows
+__device__ __forceinline__ void tail_store_planes4(const float4& v, unsigned short* o, long long stride, long long ldp) {
+    if ((ldp & 3) == 0 && (stride & 3) == 0) {
+        const float x[4] = {v.x, v.y, v.z, v.w};
+        unsigned short h[4], md[4], lo[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const __nv_bfloat16 bh = __float2bfloat16_rn(x[i]);
+            const float r1 = x[i] - __bfloat162float(bh);
+            const __nv_bfloat16 bm = __float2bfloat16_rn(r1);
+            const __nv_bfloat16 bl = __float2bfloat16_rn(r1 - __bfloat162float(bm));
+            h[i] = __bfloat16_as_ushort(bh); md[i] = __bfloat16_as_ushort(bm); lo[i] = __bfloat16_as_ushort(bl);
+        }
+        *reinterpret_cast<uint2*>(o) = make_uint2(h[0] | ((unsigned)h[1] << 16), h[2] | ((unsigned)h[3] << 16));
+        *reinterpret_cast<uint2*>(o + stride) = make_uint2(md[0] | ((unsigned)md[1] << 16), md[2] | ((unsigned)md[3] << 16));
+        *reinterpret_cast<uint2*>(o + 2 * stride) = make_uint2(lo[0] | ((unsigned)lo[1] << 16), lo[2] | ((unsigned)lo[3] << 16));
+    } else {
+        store_planes3<float>(v.x, o, stride); store_planes3<float>(v.y, o + 1, stride);
+        store_planes3<float>(v.z, o + 2, stride); store_planes3<float>(v.w, o + 3, stride);
+    }
+}
+
+__device__ __forceinline__ void tail_cp_wait(int pending) {      // cp.async.wait_group takes an immediate
+    switch (pending) {
+        case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
+        case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
+        case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
+        case 3: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
+        case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
+        case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
+        case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
+        default: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
+    }
+}
+
 __device__ __forceinline__ void tail_cp16(float* dst_smem, const float* src) {
     const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst_smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
@@ -59,7 +96,8 @@ __device__ __forceinline__ void tail_cp16(float* dst_smem, const float* src) {
 
 inline size_t tail_smem_bytes(int K1, int N1, int N2) {
     const size_t p1 = N1 + 4, pa = K1 + 4, pn = N1 + 4, p2 = (size_t)N2 | 1;
-    return (K1 * p1 + N1 + N1 * p2 + 32 + TAIL_ROWS * 32 + TAIL_ROWS * pa + 2 * TAIL_ROWS * pn) * sizeof(float);
+    const size_t red = (size_t)TAIL_ROWS * (TAIL_KSPLIT * (size_t)N1 > 2 * (size_t)K1 ? TAIL_KSPLIT * (size_t)N1 : 2 * (size_t)K1);
+    return (K1 * p1 + N1 + N1 * p2 + 32 + TAIL_ROWS * 32 + TAIL_ROWS * pa + 2 * TAIL_ROWS * pn + red) * sizeof(float);
 }
 
 __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a) {
@@ -74,161 +112,223 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
     float* W2s = b1s + N1;                                   // [N1][P2]
     float* b2s = W2s + (size_t)N1 * P2;                      // [32]
     float* dz2s = b2s + 32;                                  // [8][32]
+    float* red = dz2s + TAIL_ROWS * 32;                      // partial sums of the k-split groups: [8 splits][8][N1] / [2][8][K1]
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const long long m0 = (long long)blockIdx.x * TAIL_ROWS;
     // POZ_KERNEL_TRACE=1, tag 66: operands staged / hidden unit forward done / head done / backward-x done / exit
     fast::KernelTraceRec* ktr = fast::ktrace_open(66, (int)a.M, N1, K1);
 
-    // ---- stage W1 and this block's rows of a0 (16-byte asynchronous copies), then the small operands ----
-    const int n4 = N1 / 4, k4 = K1 / 4;
-    for (int i = t; i < K1 * n4; i += TAIL_THREADS) {
-        const int r = i / n4, c = (i - r * n4) * 4;
-        tail_cp16(W1s + (size_t)r * P1 + c, a.w1b + (size_t)r * N1 + c);
-    }
-    for (int i = t; i < TAIL_ROWS * k4; i += TAIL_THREADS) {
-        const int r = i / k4, c = (i - r * k4) * 4;
-        const long long m = m0 + r < a.M ? m0 + r : a.M - 1;
-        tail_cp16(a0s + r * PA + c, a.a0 + m * K1 + c);
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    for (int i = t; i < N1; i += TAIL_THREADS) b1s[i] = a.has_bias ? a.w1b[(size_t)K1 * N1 + i] : 0.f;
-    for (int i = t; i < N1 * N2; i += TAIL_THREADS) W2s[(i / N2) * P2 + (i % N2)] = a.w2b[i];
-    for (int i = t; i < 32; i += TAIL_THREADS) b2s[i] = (a.has_bias && i < N2) ? a.w2b[(size_t)N1 * N2 + i] : 0.f;
-    int y = -1;                                              // label of this warp's row
-    const long long mw = m0 + warp;
-    if (mw < a.M) y = a.labels[a.row_idx ? (long long)a.row_idx[mw] : mw];
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
-    if (ktr) ktr->t[1] = fast::ktrace_now();
-
-    // ---- forward of the hidden unit: thread = (column c, four of the eight rows) ----
+    // Index arithmetic below uses shifts and masks over the maxima (K1 <= 256, N1 <= 128, N2 <= 32) with guards, never
+    // a division by a run-time size: the first version of this kernel spent 60 % of its issue slots on them.
+    // ---- stage this block's rows of a0 and W1 (16-byte asynchronous copies, W1 in chunks of 32 rows, one copy group per
+    //      chunk: the forward below starts on chunk 0 while the others are still arriving), then the small operands ----
+    const int n4 = N1 >> 2, k4 = K1 >> 2;
+    const int nchunks = (K1 + TAIL_CHUNK - 1) / TAIL_CHUNK;          // <= 8
     {
-        const int c = t & 127, g = t >> 7;
-        if (c < N1) {
-            float acc[4] = {0.f, 0.f, 0.f, 0.f};
-            const float* ar = a0s + (g * 4) * PA;
-#pragma unroll 2
-            for (int k = 0; k < K1; k += 4) {
-                const float w0 = W1s[(size_t)k * P1 + c], w1 = W1s[(size_t)(k + 1) * P1 + c];
-                const float w2 = W1s[(size_t)(k + 2) * P1 + c], w3 = W1s[(size_t)(k + 3) * P1 + c];
+        const int r = t >> 6, c = t & 63;                            // 8 rows x (up to) 64 16-byte pieces
+        if (c < k4) {
+            const long long m = m0 + r < a.M ? m0 + r : a.M - 1;
+            tail_cp16(a0s + r * PA + c * 4, a.a0 + m * K1 + c * 4);
+        }
+    }
+    for (int ch = 0; ch < nchunks; ++ch) {
+#pragma unroll
+        for (int q = 0; q < TAIL_CHUNK / 16; ++q) {                  // 16 warps, a row of (up to) 32 pieces per warp
+            const int r = ch * TAIL_CHUNK + q * 16 + warp;
+            if (r < K1 && lane < n4) tail_cp16(W1s + (size_t)r * P1 + lane * 4, a.w1b + (size_t)r * N1 + lane * 4);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    if (t < N1) b1s[t] = a.has_bias ? a.w1b[(size_t)K1 * N1 + t] : 0.f;
+    for (int k = warp; k < N1; k += TAIL_THREADS / 32)
+        if (lane < N2) W2s[k * P2 + lane] = a.w2b[k * N2 + lane];
+    if (t < 32) b2s[t] = (a.has_bias && t < N2) ? a.w2b[(size_t)N1 * N2 + t] : 0.f;
+    const int hrow = warp & (TAIL_ROWS - 1), hhalf = warp >> 3;       // the head's split: row, half of the outputs / of N1
+    int y = -1;                                                        // label of this warp's row
+    const long long mw = m0 + hrow;
+    if (mw < a.M) y = a.labels[a.row_idx ? (long long)a.row_idx[mw] : mw];
+
+    // ---- forward of the hidden unit: thread = (four adjacent columns, four of the eight rows, one eighth of each chunk's
+    //      k); a warp's 32 lanes read 512 contiguous bytes of a W1 row, the a0 values are broadcasts: 8 loads per 64 FMAs ----
+    {
+        const int cg = t & 31, rh = (t >> 5) & 1, ks = t >> 6;              // column group, row half, k split
+        const int c = cg * 4;
+        float acc[4][4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[r][q] = 0.f;
+        const float* ar = a0s + (rh * 4) * PA;
+        for (int ch = 0; ch < nchunks; ++ch) {
+            tail_cp_wait(nchunks - 1 - ch);                                 // this thread's copies of chunk ch have landed
+            __syncthreads();                                                // ... and everybody else's
+            if (ch == 0 && ktr) ktr->t[1] = fast::ktrace_now();
+            const int k = ch * TAIL_CHUNK + ks * 4;                         // four k of this chunk per split
+            if (c < N1 && k < K1) {
+                float4 w[4], x[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) w[q] = *reinterpret_cast<const float4*>(W1s + (size_t)(k + q) * P1 + c);
+#pragma unroll
+                for (int r = 0; r < 4; ++r) x[r] = *reinterpret_cast<const float4*>(ar + r * PA + k);
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
-                    const float4 x = *reinterpret_cast<const float4*>(ar + r * PA + k);
-                    acc[r] = fmaf(x.x, w0, acc[r]);
-                    acc[r] = fmaf(x.y, w1, acc[r]);
-                    acc[r] = fmaf(x.z, w2, acc[r]);
-                    acc[r] = fmaf(x.w, w3, acc[r]);
+                    acc[r][0] = fmaf(x[r].x, w[0].x, acc[r][0]); acc[r][1] = fmaf(x[r].x, w[0].y, acc[r][1]);
+                    acc[r][2] = fmaf(x[r].x, w[0].z, acc[r][2]); acc[r][3] = fmaf(x[r].x, w[0].w, acc[r][3]);
+                    acc[r][0] = fmaf(x[r].y, w[1].x, acc[r][0]); acc[r][1] = fmaf(x[r].y, w[1].y, acc[r][1]);
+                    acc[r][2] = fmaf(x[r].y, w[1].z, acc[r][2]); acc[r][3] = fmaf(x[r].y, w[1].w, acc[r][3]);
+                    acc[r][0] = fmaf(x[r].z, w[2].x, acc[r][0]); acc[r][1] = fmaf(x[r].z, w[2].y, acc[r][1]);
+                    acc[r][2] = fmaf(x[r].z, w[2].z, acc[r][2]); acc[r][3] = fmaf(x[r].z, w[2].w, acc[r][3]);
+                    acc[r][0] = fmaf(x[r].w, w[3].x, acc[r][0]); acc[r][1] = fmaf(x[r].w, w[3].y, acc[r][1]);
+                    acc[r][2] = fmaf(x[r].w, w[3].z, acc[r][2]); acc[r][3] = fmaf(x[r].w, w[3].w, acc[r][3]);
                 }
             }
+        }
+        if (c < N1) {
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int row = g * 4 + r;
-                const float v = act_fwd<float>(a.act1, acc[r] + b1s[c]);
-                a1s[row * PN + c] = v;
-                if (m0 + row < a.M) a.a1_out[(m0 + row) * N1 + c] = v;
+            for (int r = 0; r < 4; ++r)
+                *reinterpret_cast<float4*>(red + ((size_t)ks * TAIL_ROWS + rh * 4 + r) * N1 + c) =
+                    make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+        }
+        __syncthreads();
+        const int cc = t & 127;                                             // 4 rows x 128 columns per pass
+        if (cc < N1) {
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int row = (t >> 7) + 4 * q;
+                float z = b1s[cc];
+#pragma unroll
+                for (int sidx = 0; sidx < TAIL_KSPLIT; ++sidx) z += red[((size_t)sidx * TAIL_ROWS + row) * N1 + cc];
+                const float v = act_fwd<float>(a.act1, z);
+                a1s[row * PN + cc] = v;
+                if (m0 + row < a.M) a.a1_out[(m0 + row) * N1 + cc] = v;
             }
         }
     }
     __syncthreads();
     if (ktr) ktr->t[2] = fast::ktrace_now();
 
-    // ---- head: one warp per row (logits, softmax, loss, dZ2), then dZ1 = (dZ2 W2^T) . act1'(a1) ----
+    // ---- head.  Two warps per row.  Logits: each lane keeps four values of the row's a1, the warp sums one output at a
+    //      time (half of the outputs per warp); then both warps of a row do the softmax, and each takes half of
+    //      dZ1 = (dZ2 W2^T) . act1'(a1) ----
     double local = 0.0;
-    if (mw < a.M) {
-        const float* arow = a1s + warp * PN;
-        float z = b2s[lane];
-        if (lane < N2) {
-            float z1 = 0.f, z2 = 0.f, z3 = 0.f;
-            for (int k = 0; k < N1; k += 4) {
-                z = fmaf(arow[k], W2s[k * P2 + lane], z);
-                z1 = fmaf(arow[k + 1], W2s[(k + 1) * P2 + lane], z1);
-                z2 = fmaf(arow[k + 2], W2s[(k + 2) * P2 + lane], z2);
-                z3 = fmaf(arow[k + 3], W2s[(k + 3) * P2 + lane], z3);
-            }
-            z = (z + z1) + (z2 + z3);
+    float* zs = red;                                                        // [8][32] logits
+    {
+        const float* arow = a1s + hrow * PN;
+        float av[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) av[j] = lane + 32 * j < N1 ? arow[lane + 32 * j] : 0.f;
+        const int nh = (N2 + 1) >> 1;
+        const int nb = hhalf * nh, ne = nb + nh < N2 ? nb + nh : N2;
+        for (int n = nb; n < ne; ++n) {
+            float pz = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (lane + 32 * j < N1) pz = fmaf(av[j], W2s[(lane + 32 * j) * P2 + n], pz);
+            pz = warp_sum(pz);
+            if (lane == 0) zs[hrow * 32 + n] = pz + b2s[n];
         }
-        const float zm = lane < N2 ? z : -INFINITY;
-        const float mx = warp_max(zm);
-        const float e = lane < N2 ? expf(z - mx) : 0.f;
-        const float s = warp_sum(e);
-        const float p = e / s;
-        const float g = lane < N2 ? (p - (lane == y ? 1.f : 0.f)) * (float)a.inv_batch : 0.f;
-        if (lane < N2) a.dz2_out[mw * N2 + lane] = g;
-        dz2s[warp * 32 + lane] = g;
-        const float zy = __shfl_sync(0xffffffffu, z, (y >= 0 && y < N2) ? y : 0);
-        if (lane == 0 && y >= 0 && y < N2) local += (double)(mx + logf(s) - zy);
-        for (int kg = 0; kg < N1; kg += 128) {
-            float dd[4] = {0.f, 0.f, 0.f, 0.f};
-            for (int n = 0; n < N2; ++n) {
-                const float gn = __shfl_sync(0xffffffffu, g, n);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int kk = kg + 32 * j + lane;
-                    if (kk < N1) dd[j] = fmaf(gn, W2s[kk * P2 + n], dd[j]);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int k = kg + 32 * j + lane;
-                if (k < N1) {
-                    const float gz = dd[j] * act_bwd_from_out<float>(a.act1, arow[k]);
-                    dz1s[warp * PN + k] = gz;
-                    a.dz1_out[mw * N1 + k] = gz;
-                    if (a.dz1_planes) store_planes3<float>(gz, a.dz1_planes + mw * a.dz1_ldp + k, a.dz1_pstride);
-                }
+        __syncthreads();
+        float g = 0.f;
+        if (mw < a.M) {
+            const float z = lane < N2 ? zs[hrow * 32 + lane] : -INFINITY;
+            const float mx = warp_max(z);
+            const float e = lane < N2 ? expf(z - mx) : 0.f;
+            const float ssum = warp_sum(e);
+            const float pr = e / ssum;
+            g = lane < N2 ? (pr - (lane == y ? 1.f : 0.f)) * (float)a.inv_batch : 0.f;
+            const float zy = __shfl_sync(0xffffffffu, z, (y >= 0 && y < N2) ? y : 0);
+            if (hhalf == 0) {
+                if (lane < N2) a.dz2_out[mw * N2 + lane] = g;
+                if (lane == 0 && y >= 0 && y < N2) local += (double)(mx + logf(ssum) - zy);
             }
         }
-    } else {
-        for (int k = lane; k < N1; k += 32) dz1s[warp * PN + k] = 0.f;
-        dz2s[warp * 32 + lane] = 0.f;
+        if (hhalf == 0) dz2s[hrow * 32 + lane] = g;
+        float dd[2] = {0.f, 0.f};
+        const int kb = hhalf * 64 + lane;                                   // this warp's k: kb, kb + 32
+        for (int n = 0; n < N2; ++n) {
+            const float gn = __shfl_sync(0xffffffffu, g, n);
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                if (kb + 32 * j < N1) dd[j] = fmaf(gn, W2s[(kb + 32 * j) * P2 + n], dd[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int k = kb + 32 * j;
+            if (k < N1) dz1s[hrow * PN + k] = dd[j] * act_bwd_from_out<float>(a.act1, arow[k]);   // zero for rows past M
+        }
     }
     __syncthreads();
     if (ktr) ktr->t[3] = fast::ktrace_now();
 
-    // ---- backward-x of the hidden unit: thread = input feature j, all eight rows ----
-    if (a.dz0_out && t < K1) {
-        const int j = t;
+    // dZ1 to global memory, four values per thread: fp32 and (for the weight-gradient launch) the three bf16 planes
+    if (t < TAIL_ROWS * 32) {
+        const int r = t >> 5, k = lane * 4;
+        const long long m = m0 + r;
+        if (k < N1 && m < a.M) {
+            const float4 v = *reinterpret_cast<const float4*>(dz1s + r * PN + k);
+            *reinterpret_cast<float4*>(a.dz1_out + m * N1 + k) = v;
+            if (a.dz1_planes) tail_store_planes4(v, a.dz1_planes + m * a.dz1_ldp + k, a.dz1_pstride, a.dz1_ldp);
+        }
+    }
+
+    // ---- backward-x of the hidden unit: thread = (input feature j, one half of N1), all eight rows; the halves meet in
+    //      shared memory ----
+    if (a.dz0_out) {
+        const int j = t & 255, kh = t >> 8;
+        const int nhalf = ((n4 + 1) >> 1) * 4;
+        const int k0 = kh * nhalf, k1 = k0 + nhalf < N1 ? k0 + nhalf : N1;
         float acc[TAIL_ROWS];
 #pragma unroll
         for (int r = 0; r < TAIL_ROWS; ++r) acc[r] = 0.f;
-        const float* wr = W1s + (size_t)j * P1;
-#pragma unroll 2
-        for (int k = 0; k < N1; k += 4) {
-            const float4 w = *reinterpret_cast<const float4*>(wr + k);
+        if (j < K1) {
+            const float* wr = W1s + (size_t)j * P1;
+#pragma unroll 4
+            for (int k = k0; k < k1; k += 4) {
+                const float4 w = *reinterpret_cast<const float4*>(wr + k);
 #pragma unroll
-            for (int r = 0; r < TAIL_ROWS; ++r) {
-                const float4 d = *reinterpret_cast<const float4*>(dz1s + r * PN + k);
-                acc[r] = fmaf(d.x, w.x, acc[r]);
-                acc[r] = fmaf(d.y, w.y, acc[r]);
-                acc[r] = fmaf(d.z, w.z, acc[r]);
-                acc[r] = fmaf(d.w, w.w, acc[r]);
+                for (int r = 0; r < TAIL_ROWS; ++r) {
+                    const float4 d = *reinterpret_cast<const float4*>(dz1s + r * PN + k);
+                    acc[r] = fmaf(d.x, w.x, acc[r]);
+                    acc[r] = fmaf(d.y, w.y, acc[r]);
+                    acc[r] = fmaf(d.z, w.z, acc[r]);
+                    acc[r] = fmaf(d.w, w.w, acc[r]);
+                }
             }
+#pragma unroll
+            for (int r = 0; r < TAIL_ROWS; ++r) red[((size_t)kh * TAIL_ROWS + r) * K1 + j] = acc[r];
         }
-#pragma unroll
-        for (int r = 0; r < TAIL_ROWS; ++r) {
-            const long long m = m0 + r;
-            if (m < a.M) {
-                const float gz = acc[r] * act_bwd_from_out<float>(a.act0, a0s[r * PA + j]);
-                a.dz0_out[m * K1 + j] = gz;
-                if (a.dz0_planes) store_planes3<float>(gz, a.dz0_planes + m * a.dz0_ldp + j, a.dz0_pstride);
-            }
+        __syncthreads();
+        const int r = t >> 6, jj = (t & 63) * 4;                            // 8 rows x (up to) 64 groups of four
+        const long long m = m0 + r;
+        if (jj < K1 && m < a.M) {
+            const float4 s0 = *reinterpret_cast<const float4*>(red + (size_t)r * K1 + jj);
+            const float4 s1 = *reinterpret_cast<const float4*>(red + ((size_t)TAIL_ROWS + r) * K1 + jj);
+            const float4 o = *reinterpret_cast<const float4*>(a0s + r * PA + jj);
+            float4 gz;
+            gz.x = (s0.x + s1.x) * act_bwd_from_out<float>(a.act0, o.x);
+            gz.y = (s0.y + s1.y) * act_bwd_from_out<float>(a.act0, o.y);
+            gz.z = (s0.z + s1.z) * act_bwd_from_out<float>(a.act0, o.z);
+            gz.w = (s0.w + s1.w) * act_bwd_from_out<float>(a.act0, o.w);
+            *reinterpret_cast<float4*>(a.dz0_out + m * K1 + jj) = gz;
+            if (a.dz0_planes) tail_store_planes4(gz, a.dz0_planes + m * a.dz0_ldp + jj, a.dz0_pstride, a.dz0_ldp);
         }
     }
     // ---- this block's share of [dW2; db2] = [a1 1]^T dZ2 and of db1 = column sums of dZ1 ----
     if (a.part) {
         float* prt = a.part + (size_t)blockIdx.x * a.part_stride;
-        for (int i = t; i < (N1 + 1) * N2; i += TAIL_THREADS) {
-            const int k = i / N2, n = i - k * N2;
-            float sacc = 0.f;
+        if (lane < N2) {
+            for (int k = warp; k <= N1; k += TAIL_THREADS / 32) {           // a row of [dW2; db2] per warp
+                float sacc = 0.f;
 #pragma unroll
-            for (int r = 0; r < TAIL_ROWS; ++r) sacc = fmaf(k < N1 ? a1s[r * PN + k] : 1.f, dz2s[r * 32 + n], sacc);
-            prt[i] = sacc;
+                for (int r = 0; r < TAIL_ROWS; ++r) sacc = fmaf(k < N1 ? a1s[r * PN + k] : 1.f, dz2s[r * 32 + lane], sacc);
+                prt[k * N2 + lane] = sacc;
+            }
         }
-        for (int k = t; k < N1; k += TAIL_THREADS) {
+        if (t < N1) {
             float sacc = 0.f;
 #pragma unroll
-            for (int r = 0; r < TAIL_ROWS; ++r) sacc += dz1s[r * PN + k];
-            prt[a.part_b1 + k] = sacc;
+            for (int r = 0; r < TAIL_ROWS; ++r) sacc += dz1s[r * PN + t];
+            prt[a.part_b1 + t] = sacc;
         }
     }
     if (ktr) ktr->t[4] = fast::ktrace_now();

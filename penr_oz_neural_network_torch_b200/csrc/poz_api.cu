@@ -1025,10 +1025,10 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
     if constexpr (std::is_same<T, float>::value) {
         if (tail) {
             const int p = last - 1;
-            static bool configured = false;
-            if (!configured) {
+            static bool configured[64] = {};                       // a function attribute is per device
+            if (c->device < 0 || c->device >= 64 || !configured[c->device]) {
                 POZ_CUDA(cudaFuncSetAttribute(tail_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-                configured = true;
+                if (c->device >= 0 && c->device < 64) configured[c->device] = true;
             }
             TailArgs ta{};
             ta.a0 = cur;
@@ -1064,7 +1064,18 @@ static int backward_impl(poz_ctx* c, const T* x, const void* target, const int* 
             ta.cost_base = c->cost_ring; ta.cost_cap = c->cost_cap; ta.st = c->st;
             {
                 ProfScope ps(c, "tail", stream);
-                POZ_TRY(launch_pdl(tail_fused_kernel, dim3((unsigned)n_blocks), dim3(TAIL_THREADS), tail_smem, stream, ta));
+                // clusters of 4 (or 2) blocks share the reads of W1 (multicast within the cluster, from this GPU's own memory)
+                cudaLaunchConfig_t cfg{};
+                cfg.gridDim = dim3((unsigned)n_blocks); cfg.blockDim = dim3(TAIL_THREADS);
+                cfg.dynamicSmemBytes = tail_smem; cfg.stream = stream;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = c->tail_cluster > 1 && n_blocks % 4 == 0 && c->tail_cluster >= 4 ? 4
+                                         : (c->tail_cluster > 1 && n_blocks % 2 == 0 ? 2 : 1);
+                at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                cfg.attrs = at; cfg.numAttrs = 1;
+                POZ_CUDA(cudaLaunchKernelEx(&cfg, tail_fused_kernel, ta));
+                count_launch();
             }
             tail_done = true;
             if (tail_group) {
@@ -1795,6 +1806,7 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
     }
     if (const char* e = getenv("POZ_TAIL")) c->tail_fused = atoi(e) != 0;
     if (const char* e = getenv("POZ_TAIL_GROUP")) c->tail_group = atoi(e) != 0;
+    if (const char* e = getenv("POZ_TAIL_CLUSTER")) c->tail_cluster = std::max(1, std::min(4, atoi(e)));
     if (const char* e = getenv("POZ_TCS")) c->tcs_enabled = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS_FUSE_UPDATE")) c->tcs_fuse_update = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS_GROUP")) c->tcs_group = atoi(e) != 0;

@@ -27,7 +27,7 @@ namespace poz {
 constexpr int TAIL_ROWS = 8;
 constexpr int TAIL_THREADS = 512;
 constexpr int TAIL_CHUNK = 32;            // rows of W1 per asynchronous copy group
-constexpr int TAIL_KSPLIT = 8;            // the forward splits K1 over 8 thread groups, the backward-x N1 over 2
+constexpr int TAIL_KSPLIT = 8;            // the forward splits K1 over 8 thread groups, the backward-x N1 over 4
 constexpr int TAIL_MAX_K1 = 256, TAIL_MAX_N1 = 128, TAIL_MAX_N2 = 32;
 
 struct TailArgs {
@@ -76,6 +76,42 @@ __device__ __forceinline__ void tail_store_planes4(const float4& v, unsigned sho
     }
 }
 
+// ---- mbarrier / bulk-copy helpers of the W1 staging (the cluster's CTAs share the reads of W1: each fetches a share of
+//      the rows and multicasts them into every CTA's shared memory; W1 lies in this GPU's own memory) ----
+__device__ __forceinline__ void tail_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void tail_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void tail_mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = (uint32_t)__cvta_generic_to_shared(bar);
+    uint32_t done = 0;
+    long long spins = 0;
+    while (!done) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (!done && ++spins > (1LL << 26)) __trap();        // a copy that never lands: fail loudly instead of hanging the GPU
+    }
+}
+// one row of W1 (bytes, a multiple of 16) into the same shared-memory offset of every CTA in cta_mask
+__device__ __forceinline__ void tail_bulk_row(float* dst_smem, const float* src, uint32_t bytes, uint64_t* bar, uint32_t ncta,
+                                              uint16_t cta_mask) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst_smem), b = (uint32_t)__cvta_generic_to_shared(bar);
+    if (ncta > 1)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+                     ::"r"(d), "l"(src), "r"(bytes), "r"(b), "h"(cta_mask) : "memory");
+    else
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(d), "l"(src), "r"(bytes), "r"(b) : "memory");
+}
+__device__ __forceinline__ void tail_cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tail_cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
 __device__ __forceinline__ void tail_cp_wait(int pending) {      // cp.async.wait_group takes an immediate
     switch (pending) {
         case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
@@ -96,7 +132,7 @@ __device__ __forceinline__ void tail_cp16(float* dst_smem, const float* src) {
 
 inline size_t tail_smem_bytes(int K1, int N1, int N2) {
     const size_t p1 = N1 + 4, pa = K1 + 4, pn = N1 + 4, p2 = (size_t)N2 | 1;
-    const size_t red = (size_t)TAIL_ROWS * (TAIL_KSPLIT * (size_t)N1 > 2 * (size_t)K1 ? TAIL_KSPLIT * (size_t)N1 : 2 * (size_t)K1);
+    const size_t red = (size_t)TAIL_ROWS * (TAIL_KSPLIT * (size_t)N1 > 4 * (size_t)K1 ? TAIL_KSPLIT * (size_t)N1 : 4 * (size_t)K1);
     return (K1 * p1 + N1 + N1 * p2 + 32 + TAIL_ROWS * 32 + TAIL_ROWS * pa + 2 * TAIL_ROWS * pn + red) * sizeof(float);
 }
 
@@ -112,7 +148,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
     float* W2s = b1s + N1;                                   // [N1][P2]
     float* b2s = W2s + (size_t)N1 * P2;                      // [32]
     float* dz2s = b2s + 32;                                  // [8][32]
-    float* red = dz2s + TAIL_ROWS * 32;                      // partial sums of the k-split groups: [8 splits][8][N1] / [2][8][K1]
+    float* red = dz2s + TAIL_ROWS * 32;                      // partial sums of the k-split groups: [8 splits][8][N1] / [4][8][K1]
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const long long m0 = (long long)blockIdx.x * TAIL_ROWS;
     // POZ_KERNEL_TRACE=1, tag 66: operands staged / hidden unit forward done / head done / backward-x done / exit
@@ -120,24 +156,40 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
 
     // Index arithmetic below uses shifts and masks over the maxima (K1 <= 256, N1 <= 128, N2 <= 32) with guards, never
     // a division by a run-time size: the first version of this kernel spent 60 % of its issue slots on them.
-    // ---- stage this block's rows of a0 and W1 (16-byte asynchronous copies, W1 in chunks of 32 rows, one copy group per
-    //      chunk: the forward below starts on chunk 0 while the others are still arriving), then the small operands ----
+    // ---- stage W1: bulk copies of whole rows, one mbarrier per chunk of 32 rows, so that the forward below starts on
+    //      chunk 0 while the others are still arriving.  The CTAs of a cluster share the reads: each fetches the rows
+    //      with (row mod cluster size == its rank) and multicasts them into every CTA's shared memory -- 128 blocks
+    //      reading 132 KB each from L2 was 4 us of L2 bandwidth.  Then this block's rows of a0 and the small operands ----
     const int n4 = N1 >> 2, k4 = K1 >> 2;
     const int nchunks = (K1 + TAIL_CHUNK - 1) / TAIL_CHUNK;          // <= 8
+    __shared__ __align__(8) uint64_t bars[TAIL_MAX_K1 / TAIL_CHUNK];   // one per chunk, used once (parity 0)
+    uint32_t crank, csize;
+    asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+    asm("mov.u32 %0, %%cluster_nctarank;" : "=r"(csize));
+    if (t == 0) {
+        for (int ch = 0; ch < nchunks; ++ch) {
+            const int nr = K1 - ch * TAIL_CHUNK < TAIL_CHUNK ? K1 - ch * TAIL_CHUNK : TAIL_CHUNK;
+            tail_mbar_init(&bars[ch], 1);
+            tail_mbar_expect_tx(&bars[ch], (uint32_t)(nr * N1 * sizeof(float)));   // the whole chunk, whoever fetches it
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    tail_cluster_arrive();                                            // "my barriers are armed"
     {
-        const int r = t >> 6, c = t & 63;                            // 8 rows x (up to) 64 16-byte pieces
+        const int r = t >> 6, c = t & 63;                            // a0: 8 rows x (up to) 64 16-byte pieces
         if (c < k4) {
             const long long m = m0 + r < a.M ? m0 + r : a.M - 1;
             tail_cp16(a0s + r * PA + c * 4, a.a0 + m * K1 + c * 4);
         }
     }
-    for (int ch = 0; ch < nchunks; ++ch) {
-#pragma unroll
-        for (int q = 0; q < TAIL_CHUNK / 16; ++q) {                  // 16 warps, a row of (up to) 32 pieces per warp
-            const int r = ch * TAIL_CHUNK + q * 16 + warp;
-            if (r < K1 && lane < n4) tail_cp16(W1s + (size_t)r * P1 + lane * 4, a.w1b + (size_t)r * N1 + lane * 4);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    tail_cluster_wait();                                              // ... and so are everybody else's: rows may be sent
+    if (warp < nchunks) {                                             // warp w sends this CTA's share of chunk w
+        const int r = warp * TAIL_CHUNK + lane;
+        if (r < K1 && (r & (int)(csize - 1)) == (int)crank)
+            tail_bulk_row(W1s + (size_t)r * P1, a.w1b + (size_t)r * N1, (uint32_t)(N1 * sizeof(float)), &bars[warp], csize,
+                          (uint16_t)((1u << csize) - 1));
     }
     if (t < N1) b1s[t] = a.has_bias ? a.w1b[(size_t)K1 * N1 + t] : 0.f;
     for (int k = warp; k < N1; k += TAIL_THREADS / 32)
@@ -147,6 +199,9 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
     int y = -1;                                                        // label of this warp's row
     const long long mw = m0 + hrow;
     if (mw < a.M) y = a.labels[a.row_idx ? (long long)a.row_idx[mw] : mw];
+    asm volatile("cp.async.wait_group 0;" ::: "memory");      // a0 rows (cp.async) and the small operands
+    __syncthreads();
+    if (ktr) ktr->t[1] = fast::ktrace_now();
 
     // ---- forward of the hidden unit: thread = (four adjacent columns, four of the eight rows, one eighth of each chunk's
     //      k); a warp's 32 lanes read 512 contiguous bytes of a W1 row, the a0 values are broadcasts: 8 loads per 64 FMAs ----
@@ -160,9 +215,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
             for (int q = 0; q < 4; ++q) acc[r][q] = 0.f;
         const float* ar = a0s + (rh * 4) * PA;
         for (int ch = 0; ch < nchunks; ++ch) {
-            tail_cp_wait(nchunks - 1 - ch);                                 // this thread's copies of chunk ch have landed
-            __syncthreads();                                                // ... and everybody else's
-            if (ch == 0 && ktr) ktr->t[1] = fast::ktrace_now();
+            tail_mbar_wait(&bars[ch], 0);                                   // chunk ch has landed (all its bytes, from all senders)
             const int k = ch * TAIL_CHUNK + ks * 4;                         // four k of this chunk per split
             if (c < N1 && k < K1) {
                 float4 w[4], x[4];
@@ -183,6 +236,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
                 }
             }
         }
+        tail_cluster_arrive();                                              // (waited for at the end: no CTA leaves the cluster early)
         if (c < N1) {
 #pragma unroll
             for (int r = 0; r < 4; ++r)
@@ -271,44 +325,52 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
         }
     }
 
-    // ---- backward-x of the hidden unit: thread = (input feature j, one half of N1), all eight rows; the halves meet in
-    //      shared memory ----
+    // ---- backward-x of the hidden unit: thread = (input features j and j + 128, one quarter of N1), all eight rows: 10
+    //      shared-memory loads (8 of them broadcasts) per 64 FMAs; the quarters meet in shared memory ----
     if (a.dz0_out) {
-        const int j = t & 255, kh = t >> 8;
-        const int nhalf = ((n4 + 1) >> 1) * 4;
-        const int k0 = kh * nhalf, k1 = k0 + nhalf < N1 ? k0 + nhalf : N1;
-        float acc[TAIL_ROWS];
+        const int j = t & 127, kq = t >> 7;
+        const int nq = ((n4 + 3) >> 2) * 4;
+        const int k0 = kq * nq, k1 = k0 + nq < N1 ? k0 + nq : N1;
+        float acc[2][TAIL_ROWS];
 #pragma unroll
-        for (int r = 0; r < TAIL_ROWS; ++r) acc[r] = 0.f;
-        if (j < K1) {
-            const float* wr = W1s + (size_t)j * P1;
-#pragma unroll 4
-            for (int k = k0; k < k1; k += 4) {
-                const float4 w = *reinterpret_cast<const float4*>(wr + k);
+        for (int r = 0; r < TAIL_ROWS; ++r) acc[0][r] = acc[1][r] = 0.f;
+        const bool h0 = j < K1, h1 = j + 128 < K1;
+        const float* wr0 = W1s + (size_t)(h0 ? j : 0) * P1;
+        const float* wr1 = W1s + (size_t)(h1 ? j + 128 : 0) * P1;
+#pragma unroll 2
+        for (int k = k0; k < k1; k += 4) {
+            const float4 w0 = *reinterpret_cast<const float4*>(wr0 + k);
+            const float4 w1 = *reinterpret_cast<const float4*>(wr1 + k);
 #pragma unroll
-                for (int r = 0; r < TAIL_ROWS; ++r) {
-                    const float4 d = *reinterpret_cast<const float4*>(dz1s + r * PN + k);
-                    acc[r] = fmaf(d.x, w.x, acc[r]);
-                    acc[r] = fmaf(d.y, w.y, acc[r]);
-                    acc[r] = fmaf(d.z, w.z, acc[r]);
-                    acc[r] = fmaf(d.w, w.w, acc[r]);
-                }
+            for (int r = 0; r < TAIL_ROWS; ++r) {
+                const float4 d = *reinterpret_cast<const float4*>(dz1s + r * PN + k);
+                acc[0][r] = fmaf(d.x, w0.x, acc[0][r]); acc[1][r] = fmaf(d.x, w1.x, acc[1][r]);
+                acc[0][r] = fmaf(d.y, w0.y, acc[0][r]); acc[1][r] = fmaf(d.y, w1.y, acc[1][r]);
+                acc[0][r] = fmaf(d.z, w0.z, acc[0][r]); acc[1][r] = fmaf(d.z, w1.z, acc[1][r]);
+                acc[0][r] = fmaf(d.w, w0.w, acc[0][r]); acc[1][r] = fmaf(d.w, w1.w, acc[1][r]);
             }
+        }
 #pragma unroll
-            for (int r = 0; r < TAIL_ROWS; ++r) red[((size_t)kh * TAIL_ROWS + r) * K1 + j] = acc[r];
+        for (int r = 0; r < TAIL_ROWS; ++r) {
+            if (h0) red[((size_t)kq * TAIL_ROWS + r) * K1 + j] = acc[0][r];
+            if (h1) red[((size_t)kq * TAIL_ROWS + r) * K1 + j + 128] = acc[1][r];
         }
         __syncthreads();
         const int r = t >> 6, jj = (t & 63) * 4;                            // 8 rows x (up to) 64 groups of four
         const long long m = m0 + r;
         if (jj < K1 && m < a.M) {
-            const float4 s0 = *reinterpret_cast<const float4*>(red + (size_t)r * K1 + jj);
-            const float4 s1 = *reinterpret_cast<const float4*>(red + ((size_t)TAIL_ROWS + r) * K1 + jj);
+            float4 sm = *reinterpret_cast<const float4*>(red + (size_t)r * K1 + jj);
+#pragma unroll
+            for (int q = 1; q < 4; ++q) {
+                const float4 sq = *reinterpret_cast<const float4*>(red + ((size_t)q * TAIL_ROWS + r) * K1 + jj);
+                sm.x += sq.x; sm.y += sq.y; sm.z += sq.z; sm.w += sq.w;
+            }
             const float4 o = *reinterpret_cast<const float4*>(a0s + r * PA + jj);
             float4 gz;
-            gz.x = (s0.x + s1.x) * act_bwd_from_out<float>(a.act0, o.x);
-            gz.y = (s0.y + s1.y) * act_bwd_from_out<float>(a.act0, o.y);
-            gz.z = (s0.z + s1.z) * act_bwd_from_out<float>(a.act0, o.z);
-            gz.w = (s0.w + s1.w) * act_bwd_from_out<float>(a.act0, o.w);
+            gz.x = sm.x * act_bwd_from_out<float>(a.act0, o.x);
+            gz.y = sm.y * act_bwd_from_out<float>(a.act0, o.y);
+            gz.z = sm.z * act_bwd_from_out<float>(a.act0, o.z);
+            gz.w = sm.w * act_bwd_from_out<float>(a.act0, o.w);
             *reinterpret_cast<float4*>(a.dz0_out + m * K1 + jj) = gz;
             if (a.dz0_planes) tail_store_planes4(gz, a.dz0_planes + m * a.dz0_ldp + jj, a.dz0_pstride, a.dz0_ldp);
         }
@@ -317,10 +379,18 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
     if (a.part) {
         float* prt = a.part + (size_t)blockIdx.x * a.part_stride;
         if (lane < N2) {
+            float g2[TAIL_ROWS];                                            // this lane's column of dZ2
+#pragma unroll
+            for (int r = 0; r < TAIL_ROWS; ++r) g2[r] = dz2s[r * 32 + lane];
             for (int k = warp; k <= N1; k += TAIL_THREADS / 32) {           // a row of [dW2; db2] per warp
                 float sacc = 0.f;
+                if (k < N1) {
 #pragma unroll
-                for (int r = 0; r < TAIL_ROWS; ++r) sacc = fmaf(k < N1 ? a1s[r * PN + k] : 1.f, dz2s[r * 32 + lane], sacc);
+                    for (int r = 0; r < TAIL_ROWS; ++r) sacc = fmaf(a1s[r * PN + k], g2[r], sacc);
+                } else {
+#pragma unroll
+                    for (int r = 0; r < TAIL_ROWS; ++r) sacc = fmaf(1.f, g2[r], sacc);
+                }
                 prt[k * N2 + lane] = sacc;
             }
         }
@@ -332,6 +402,7 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
         }
     }
     if (ktr) ktr->t[4] = fast::ktrace_now();
+    tail_cluster_wait();
     if (a.cost_base) block_add_double(local * a.inv_batch, cost_slot(a.cost_base, a.cost_cap, a.st));
     if (ktr) ktr->t[5] = fast::ktrace_now();
 }

@@ -434,7 +434,7 @@ static int tc3_refresh_weights(poz_ctx* c, cudaStream_t stream, int upto = -1) {
         }
         c->wp_total = c->wp_off[c->nl];
         POZ_TRY(dev_alloc(&c->Wp, (size_t)c->wp_total * 2));
-        c->wp_stale = true;
+        c->wp_stale = true; c->w16_stale = true;
     }
     if (c->wp_stale || c->wp_fresh.size() != (size_t)c->nl) {
         c->wp_fresh.assign(c->nl, 0);
@@ -462,6 +462,36 @@ static int tcs_split_w0(poz_ctx* c, cudaStream_t stream) {
     ProfScope ps(c, "split_w0", stream);
     return tc3::split_planes(static_cast<const float*>(c->P) + c->off[0], nullptr, K, N, N,
                              static_cast<__nv_bfloat16*>(c->Wp) + c->wp_off[0], c->wp_ld[0], (long long)K * c->wp_ld[0], stream);
+}
+
+// fp16 planes of every layer's weights for the fp16-split inference kernels (made again whenever the parameters changed)
+static int tc3_refresh_weights_f16(poz_ctx* c, cudaStream_t stream) {
+    if (!c->Wp16) {
+        POZ_TRY(dev_alloc(&c->Wp16, (size_t)(c->wp_total / 3 * 2) * 2));
+        POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->w16_amax), sizeof(unsigned) * (size_t)c->nl));
+        POZ_TRY(dev_alloc(reinterpret_cast<void**>(&c->f16_flag), sizeof(int)));
+        c->w16_stale = true;
+    }
+    if (!c->w16_stale) return 0;
+    POZ_CUDA(cudaMemsetAsync(c->w16_amax, 0, sizeof(unsigned) * (size_t)c->nl, stream));
+    for (int l = 0; l < c->nl; ++l) {
+        const int K = c->sizes[l], N = c->sizes[l + 1];
+        ProfScope ps(c, "split_w16", stream);
+        POZ_TRY(tc3::split_planes_f16(static_cast<const float*>(c->P) + c->off[l], K, N, N,
+                                      static_cast<__nv_bfloat16*>(c->Wp16) + c->wp_off[l] / 3 * 2, c->wp_ld[l],
+                                      (long long)K * c->wp_ld[l], c->w16_amax + l, stream));
+    }
+    c->w16_stale = false;
+    return 0;
+}
+
+static tc3::PlaneMat tc3_weight_f16(const poz_ctx* c, int l) {
+    tc3::PlaneMat m;
+    m.ptr = static_cast<const __nv_bfloat16*>(c->Wp16) + c->wp_off[l] / 3 * 2;
+    m.rows = c->sizes[l]; m.cols = c->sizes[l + 1]; m.ld = c->wp_ld[l];
+    m.plane_stride = (long long)c->sizes[l] * c->wp_ld[l];
+    m.planes = 2;
+    return m;
 }
 
 static tc3::PlaneMat tc3_weight(const poz_ctx* c, int l) {
@@ -524,7 +554,6 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
             POZ_TRY(tc3::split_planes(x + r0 * c->sizes[0], nullptr, m, c->sizes[0], c->sizes[0],
                                       static_cast<__nv_bfloat16*>(c->tc_scr[0]), cur.ld, cur.plane_stride, stream));
         }
-        int flip = 1;
         float* z_last = nullptr;
         // A narrow last unit (<= 16 outputs) behind a 65..128-wide one rides in that unit's epilogue: the tile holds
         // whole rows, so the epilogue warps apply the last Linear in fp32, then its activation / softmax, and the
@@ -533,54 +562,78 @@ static int forward_tc3(poz_ctx* c, const float* x, const void* target, long long
         // enough of them) writes fp32 rows instead of three bf16 planes: 4 instead of 6 bytes per element each way.
         static const bool head_allowed = !(getenv("POZ_TC3_FUSE_HEAD") && atoi(getenv("POZ_TC3_FUSE_HEAD")) == 0);
         static const bool f32_chain = !(getenv("POZ_TC3_F32_CHAIN") && atoi(getenv("POZ_TC3_F32_CHAIN")) == 0);
-        bool in_f32 = x32, head_done = false;
-        const float* in_ptr = x + r0 * c->sizes[0];
-        long long in_ld = c->sizes[0];
-        for (int l = 0; l < nl; ++l) {
-            const int K = c->sizes[l], N = c->sizes[l + 1];
-            const bool last = l == nl - 1;
-            tc3::Epi3 ep{};
-            ep.mode = tc3::EPI_BIAS_ACT;
-            ep.act = c->acts[l];
-            ep.bias = c->has_bias ? P + c->off[l] + (long long)K * N : nullptr;
-            tc3::PlaneMat nxt{};
-            const bool head_here = head_allowed && !cost_host && l == nl - 2 && c->acts[l] != ACT_SOFTMAX &&
-                                   tc3::gemm_forward_head_ok(N, n_out) && (!in_f32 || tc3::gemm_forward_x32_head_ok());
-            bool out_f32_rows = false;
-            if (head_here) {
-                ep.head_w = P + c->off[nl - 1];
-                ep.head_b = c->has_bias ? P + c->off[nl - 1] + (long long)N * n_out : nullptr;
-                ep.head_out = out + r0 * n_out;
-                ep.head_n = n_out;
-                ep.head_act = c->acts[nl - 1];
-            } else if (last) {
-                ep.out_f32 = softmax_last ? c->tc_logits : out + r0 * n_out;
-                ep.ld_f32 = N;
-                z_last = ep.out_f32;
-            } else if (f32_chain && x32_allowed && m >= x32_min_rows &&
-                       tc3::gemm_forward_x32_ok(static_cast<const float*>(c->tc_scr[flip]), N, c->sizes[l + 2])) {
-                out_f32_rows = true;
-                ep.out_f32 = static_cast<float*>(c->tc_scr[flip]);
-                ep.ld_f32 = N;
-            } else {
-                nxt.ptr = static_cast<const __nv_bfloat16*>(c->tc_scr[flip]);
-                nxt.rows = m; nxt.cols = N; nxt.ld = round8(N); nxt.plane_stride = m * nxt.ld;
-                ep.out_planes = static_cast<__nv_bfloat16*>(c->tc_scr[flip]);
-                ep.ld_planes = nxt.ld; ep.plane_stride = nxt.plane_stride;
+        bool head_done = false;
+        // One pass over the layers.  dry: nothing is launched, the return value says whether every unit would run on the
+        // fp32-input kernel.  f16: that kernel in its fp16-split form (two planes, three MMAs per product), which reports
+        // operands outside its range through c->f16_flag; run_if: kernels that return at once unless *run_if != 0.
+        auto chain = [&](bool dry, bool f16, const int* run_if, bool* all_x32) -> int {
+            int flip = 1;
+            bool in_f32 = x32;
+            const float* in_ptr = x + r0 * c->sizes[0];
+            long long in_ld = c->sizes[0];
+            tc3::PlaneMat cur_l = cur;
+            if (all_x32) *all_x32 = true;
+            for (int l = 0; l < nl; ++l) {
+                const int K = c->sizes[l], N = c->sizes[l + 1];
+                const bool last = l == nl - 1;
+                tc3::Epi3 ep{};
+                ep.mode = tc3::EPI_BIAS_ACT;
+                ep.act = c->acts[l];
+                ep.bias = c->has_bias ? P + c->off[l] + (long long)K * N : nullptr;
+                ep.run_if = run_if;
+                if (f16) { ep.f16_flag = c->f16_flag; ep.f16_w_amax = c->w16_amax + l; }
+                tc3::PlaneMat nxt{};
+                const bool head_here = head_allowed && !cost_host && l == nl - 2 && c->acts[l] != ACT_SOFTMAX &&
+                                       tc3::gemm_forward_head_ok(N, n_out) && (!in_f32 || tc3::gemm_forward_x32_head_ok());
+                bool out_f32_rows = false;
+                if (head_here) {
+                    ep.head_w = P + c->off[nl - 1];
+                    ep.head_b = c->has_bias ? P + c->off[nl - 1] + (long long)N * n_out : nullptr;
+                    ep.head_out = out + r0 * n_out;
+                    ep.head_n = n_out;
+                    ep.head_act = c->acts[nl - 1];
+                } else if (last) {
+                    ep.out_f32 = softmax_last ? c->tc_logits : out + r0 * n_out;
+                    ep.ld_f32 = N;
+                    if (!dry) z_last = ep.out_f32;
+                } else if (f32_chain && x32_allowed && m >= x32_min_rows &&
+                           tc3::gemm_forward_x32_ok(static_cast<const float*>(c->tc_scr[flip]), N, c->sizes[l + 2])) {
+                    out_f32_rows = true;
+                    ep.out_f32 = static_cast<float*>(c->tc_scr[flip]);
+                    ep.ld_f32 = N;
+                } else {
+                    nxt.ptr = static_cast<const __nv_bfloat16*>(c->tc_scr[flip]);
+                    nxt.rows = m; nxt.cols = N; nxt.ld = round8(N); nxt.plane_stride = m * nxt.ld;
+                    ep.out_planes = static_cast<__nv_bfloat16*>(c->tc_scr[flip]);
+                    ep.ld_planes = nxt.ld; ep.plane_stride = nxt.plane_stride;
+                }
+                if (!in_f32 && all_x32) *all_x32 = false;
+                if (!dry) {
+                    ProfScope ps(c, std::string(f16 ? "tc3h_fwd_l" : "tc3_fwd_l") + std::to_string(l) + (head_here ? "_head" : ""), stream);
+                    if (in_f32)
+                        POZ_TRY(tc3::gemm_forward_x32(in_ptr, in_ld, f16 ? tc3_weight_f16(c, l) : tc3_weight(c, l), m, N, K, ep, sms, stream));
+                    else
+                        POZ_TRY(tc3::gemm_forward(cur_l, tc3_weight(c, l), m, N, K, ep, sms, stream));
+                }
+                if (head_here) { if (!dry) head_done = true; break; }
+                in_f32 = out_f32_rows;
+                in_ptr = static_cast<const float*>(c->tc_scr[flip]);
+                in_ld = N;
+                cur_l = nxt;
+                flip = flip == 1 ? 2 : 1;
             }
-            {
-                ProfScope ps(c, "tc3_fwd_l" + std::to_string(l) + (head_here ? "_head" : ""), stream);
-                if (in_f32)
-                    POZ_TRY(tc3::gemm_forward_x32(in_ptr, in_ld, tc3_weight(c, l), m, N, K, ep, sms, stream));
-                else
-                    POZ_TRY(tc3::gemm_forward(cur, tc3_weight(c, l), m, N, K, ep, sms, stream));
-            }
-            if (head_here) { head_done = true; break; }
-            in_f32 = out_f32_rows;
-            in_ptr = static_cast<const float*>(c->tc_scr[flip]);
-            in_ld = N;
-            cur = nxt;
-            flip = flip == 1 ? 2 : 1;
+            return 0;
+        };
+        bool f16 = false;
+        if (c->tc3_f16 && x32 && m >= c->tc3_f16_min_rows) POZ_TRY(chain(true, false, nullptr, &f16));
+        if (f16) {
+            // the fp16-split pass, then the split-bf16 pass as kernels that only run when the first one raised its flag
+            POZ_TRY(tc3_refresh_weights_f16(c, stream));
+            POZ_CUDA(cudaMemsetAsync(c->f16_flag, 0, sizeof(int), stream));
+            POZ_TRY(chain(false, true, nullptr, nullptr));
+            POZ_TRY(chain(false, false, c->f16_flag, nullptr));
+        } else {
+            POZ_TRY(chain(false, false, nullptr, nullptr));
         }
         if (cost_host) {
             LossArgs<float> a{};
@@ -1646,7 +1699,7 @@ template <typename T> static int apply_impl(poz_ctx* c, bool reduced, cudaStream
     }
     c->grads_pending = false;
     c->diag_pending = false;
-    c->wp_stale = true;
+    c->wp_stale = true; c->w16_stale = true;
     if constexpr (std::is_same<T, float>::value) {
         if (c->tcs_live && !l0_done) POZ_TRY(tcs_split_w0(c, stream));   // a plain update of layer 0: its planes follow
     }
@@ -1807,6 +1860,8 @@ int poz_ctx_create_ex(int device, const poz_stack_desc* d, poz_ctx** out) {
     if (const char* e = getenv("POZ_TAIL")) c->tail_fused = atoi(e) != 0;
     if (const char* e = getenv("POZ_TAIL_GROUP")) c->tail_group = atoi(e) != 0;
     if (const char* e = getenv("POZ_TAIL_CLUSTER")) c->tail_cluster = std::max(1, std::min(4, atoi(e)));
+    if (const char* e = getenv("POZ_TC3_F16")) c->tc3_f16 = atoi(e) != 0;
+    if (const char* e = getenv("POZ_TC3_F16_MIN_ROWS")) c->tc3_f16_min_rows = std::max(1LL, atoll(e));
     if (const char* e = getenv("POZ_TCS")) c->tcs_enabled = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS_FUSE_UPDATE")) c->tcs_fuse_update = atoi(e) != 0;
     if (const char* e = getenv("POZ_TCS_GROUP")) c->tcs_group = atoi(e) != 0;
@@ -1976,7 +2031,8 @@ int poz_ctx_destroy(poz_ctx* c) {
     dev_free(c->ebuf); dev_free(c->debuf); dev_free(c->de_rec);
     dev_free(reinterpret_cast<void*&>(c->bn_part));
     dev_free(c->Pb); dev_free(reinterpret_cast<void*&>(c->colsum_scratch)); dev_free(c->wide_xg); dev_free(c->wide_tg);
-    dev_free(c->Wp); for (auto& p : c->tc_scr) dev_free(p);
+    dev_free(c->Wp); dev_free(c->Wp16); dev_free(reinterpret_cast<void*&>(c->w16_amax)); dev_free(reinterpret_cast<void*&>(c->f16_flag));
+    for (auto& p : c->tc_scr) dev_free(p);
     dev_free(c->tc_tr_x); dev_free(c->tc_tr_dz); for (auto& q : c->tcs_dzp) dev_free(q); dev_free(reinterpret_cast<void*&>(c->tail_part));
     dev_free(reinterpret_cast<void*&>(c->tc_logits));
     dev_free(c->P); dev_free(c->AM); dev_free(c->AV); dev_free(c->G); dev_free(c->Gdiag);
@@ -2039,7 +2095,7 @@ int poz_ctx_reserve(poz_ctx* c, long long max_batch, int for_training) {
 int poz_params_upload(poz_ctx* c, int layer, const double* w, const double* b) {
     POZ_TRY(check_layer(c, layer, "poz_params_upload"));
     POZ_TRY(POZ_DISPATCH(c, put_layer, c, c->P, layer, w, b));
-    c->wp_stale = true;
+    c->wp_stale = true; c->w16_stale = true;
     if (c->tcs_live && layer == 0) { POZ_TRY(tcs_split_w0(c, nullptr)); POZ_CUDA(cudaDeviceSynchronize()); }
     if (c->dtype == POZ_DTYPE_BF16) {
         const long long n = c->off[layer + 1] - c->off[layer];
@@ -2073,7 +2129,7 @@ int poz_tensor_io(poz_ctx* c, int kind, int layer, int buffer, int download, dou
     POZ_TRY(tensor_locate(c, kind, layer, buffer, &base, &off, &n));
     if (download) return POZ_DISPATCH(c, get_f64, c, base, off, host, n);
     if (buffer == 3) POZ_FAIL("poz_tensor_io: the diagnostics gradient is read-only");
-    c->wp_stale = true;
+    c->wp_stale = true; c->w16_stale = true;
     POZ_TRY(POZ_DISPATCH(c, put_f64, c, base, off, host, n));
     if (c->tcs_live && buffer == 0 && kind == 0 && layer == 0) { POZ_TRY(tcs_split_w0(c, nullptr)); POZ_CUDA(cudaDeviceSynchronize()); }
     if (c->dtype == POZ_DTYPE_BF16 && buffer == 0 && kind <= 1) {
@@ -2289,7 +2345,7 @@ static int train_step_inner(poz_ctx* c, const void* x_dev, const void* target_de
         POZ_CUDA(cudaGraphLaunch(g->exec, s));
         count_launch(g->launches);
         c->epoch_host += 1;
-        c->wp_stale = true;                 // the replayed update changed the parameters under the weight planes
+        c->wp_stale = true; c->w16_stale = true;                 // the replayed update changed the parameters under the weight planes
         return 0;
     }
     if (!g) {
@@ -2326,7 +2382,7 @@ static int train_step_inner(poz_ctx* c, const void* x_dev, const void* target_de
     g->exec = exec;
     g->launches = (int)(poz_launch_count() - before);
     POZ_CUDA(cudaGraphLaunch(exec, s));
-    c->wp_stale = true;
+    c->wp_stale = true; c->w16_stale = true;
     return 0;
 }
 

@@ -28,6 +28,13 @@ struct poz_ctx {
     long long wp_total = 0;
     bool wp_stale = true;             // parameters changed since (some of) the planes were built
     std::vector<char> wp_fresh;       // per layer: planes match the current parameters
+    // fp16-split inference (two planes, three MMAs per product; poz_tc3_gemm.cuh): its own weight planes
+    void* Wp16 = nullptr;             // layer l at 2/3 of wp_off[l]: [2][in_l][wp_ld[l]] fp16
+    bool w16_stale = true;            // parameters changed since these planes were built
+    unsigned* w16_amax = nullptr;     // device: bits of max |W| per layer
+    int* f16_flag = nullptr;          // device: set by a pass whose operands left the fp16-split range (the pass is repeated)
+    bool tc3_f16 = true;              // POZ_TC3_F16=0 keeps large-batch inference on the split-bf16 kernels
+    long long tc3_f16_min_rows = 16384;
     void* tc_tr_x = nullptr;          // training: planes of the (gathered) input batch
     void* tc_tr_dz = nullptr;         // training: planes of dZ of the first layer
     long long tc_tr_batch = 0;

@@ -37,7 +37,7 @@ static int make_map3(CUtensorMap* map, const PlaneMat& m, int box_cols, int box_
     if (!fn) POZ_FAIL("tcgen05 path: cuTensorMapEncodeTiled is not available from the driver");
     if ((reinterpret_cast<uintptr_t>(m.ptr) & 15) != 0 || (m.ld * 2) % 16 != 0 || (m.plane_stride * 2) % 16 != 0)
         POZ_FAIL("tcgen05 path: plane base, row pitch and plane stride must be 16-byte aligned");
-    cuuint64_t gdim[3] = {(cuuint64_t)m.cols, (cuuint64_t)m.rows, 3};
+    cuuint64_t gdim[3] = {(cuuint64_t)m.cols, (cuuint64_t)m.rows, (cuuint64_t)m.planes};
     cuuint64_t gstride[2] = {(cuuint64_t)m.ld * 2, (cuuint64_t)m.plane_stride * 2};
     cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1};
     cuuint32_t estr[3] = {1, 1, 1};
@@ -105,18 +105,36 @@ bool gemm_forward_x32_ok(const float* x, long long ld, int N) {
     return N > 64 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (ld % 4) == 0;
 }
 
+int split_planes_f16(const float* src, long long rows, int cols, long long ld, __nv_bfloat16* dst, long long ldp,
+                     long long plane_stride, unsigned* amax_bits, cudaStream_t stream) {
+    if (rows <= 0) return 0;
+    const long long total = rows * (ldp / 8);
+    int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    split_planes_f16_kernel<<<blocks, 256, 0, stream>>>(src, rows, cols, ld, dst, ldp, plane_stride, amax_bits);
+    count_launch();
+    POZ_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms,
                      cudaStream_t stream) {
     constexpr int BN = 128;
     using CT = CfgX32T<BN, 3, false>;
     using CH = CfgX32T<BN, 2, true>;                  // with the fused head: one W stage fewer, its buffers instead
+    using FT = CfgX32T<BN, 3, false, true, 7>;        // fp16 planes: two thirds of a stage; the room goes to the X ring
+    using FH = CfgX32T<BN, 3, true, true>;
     if (!gemm_forward_x32_ok(x, ld, N)) POZ_FAIL("tc3 fp32-input forward: operand not eligible");
     if (ep.head_w && (N > BN || ep.head_n < 1 || ep.head_n > HEAD_MAX_N || !ep.head_out))
         POZ_FAIL("tc3 fp32-input forward: fused head not available for this shape");
-    static bool configured = false;
+    static bool configured_dev[64] = {};              // function attributes are per device
+    int dev = 0;
+    POZ_CUDA(cudaGetDevice(&dev));
+    bool& configured = configured_dev[dev & 63];
     if (!configured) {
         POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32t_kernel<BN, 3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT::SMEM_BYTES));
         POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32t_kernel<BN, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH::SMEM_BYTES));
+        POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32t_kernel<BN, 3, false, true, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT::SMEM_BYTES));
+        POZ_CUDA(cudaFuncSetAttribute(tc3_fwd_x32t_kernel<BN, 3, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FH::SMEM_BYTES));
         configured = true;
     }
     CUtensorMap mx, mb;
@@ -124,7 +142,12 @@ int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long 
     POZ_TRY(make_map3(&mb, w, 64, 64));
     const long long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     const int grid = (int)(tiles < sms ? tiles : sms);
-    if (ep.head_w)
+    if (w.planes == 2) {
+        if (ep.head_w)
+            tc3_fwd_x32t_kernel<BN, 3, true, true><<<grid, X32T_THREADS, FH::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+        else
+            tc3_fwd_x32t_kernel<BN, 3, false, true, 7><<<grid, X32T_THREADS, FT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+    } else if (ep.head_w)
         tc3_fwd_x32t_kernel<BN, 2, true><<<grid, X32T_THREADS, CH::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     else
         tc3_fwd_x32t_kernel<BN, 3, false><<<grid, X32T_THREADS, CT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);

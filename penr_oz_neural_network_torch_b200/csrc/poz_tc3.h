@@ -14,6 +14,7 @@ struct PlaneMat {
     int cols;
     long long ld;            // elements, multiple of 8
     long long plane_stride;  // elements, multiple of 8
+    int planes = 3;          // 2: fp16 planes hi, lo' = (x - hi) * 2^11 (the fp16-split inference kernels)
 };
 
 enum EpiMode { EPI_BIAS_ACT = 0, EPI_ACTGRAD = 1, EPI_PLAIN = 2 };
@@ -34,6 +35,13 @@ struct Epi3 {
     const float* head_b;          // nullable
     float* head_out;
     int head_n, head_act;
+    // fp16-split kernels (two planes, three MMAs per product): the kernel stores 1 to *f16_flag when an operand leaves the
+    // range in which two fp16 planes carry fp32 precision (|x| >= 2^15, or a whole row / the whole weight matrix below
+    // 2^-16); the caller then repeats the pass with the split-bf16 kernels, which are launched with run_if = that flag
+    // and return at once while it is 0.
+    int* f16_flag;                // nullable
+    const unsigned* f16_w_amax;   // bits of max |W| of this layer (device), written when its fp16 planes were made
+    const int* run_if;            // nullable: the kernel does nothing unless *run_if != 0
 };
 constexpr int HEAD_MAX_N = 16;
 constexpr int HEAD_SMEM_BYTES = (128 * HEAD_MAX_N + 2 * 128 * HEAD_MAX_N) * 4;   // staged weights + two partial-sum buffers
@@ -49,6 +57,10 @@ bool gemm_forward_head_ok(int N, int head_n);
 // inside the kernel and never written to global memory (csrc/poz_tc3_x32t_kernel.cuh); N must be > 64
 int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long M, int N, int K, const Epi3& ep, int sms,
                      cudaStream_t s);
+// fp32 matrix -> two fp16 planes [2][rows][ldp] (hi, (x - hi) * 2^11); max |x| is folded into *amax_bits (atomicMax on the
+// float's bits; the caller zeroes it first)
+int split_planes_f16(const float* src, long long rows, int cols, long long ld, __nv_bfloat16* dst, long long ldp,
+                     long long plane_stride, unsigned* amax_bits, cudaStream_t stream);
 bool gemm_forward_x32_ok(const float* x, long long ld, int N);
 // whether gemm_forward_x32 takes ep.head_* (only the tensor-memory variant does)
 bool gemm_forward_x32_head_ok();

@@ -18,6 +18,7 @@
 //   warp  8   : TMA producer       warp 9 : TMEM allocator + MMA issuer
 // Planes are stored [3][rows][pitch] and addressed through one 3-D tensor map per operand.
 #pragma once
+#include <cuda_fp16.h>
 #include "poz_tc_gemm.cuh"
 #include "poz_tc3.h"
 
@@ -52,6 +53,30 @@ __device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint64_t* ba
 template <int A_MAJOR, int B_MAJOR, int BN> __device__ __forceinline__ constexpr uint32_t make_idesc3() {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)A_MAJOR << 15) | ((uint32_t)B_MAJOR << 16) |
            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+// the same with fp16 operands (a_format = b_format = 0)
+template <int A_MAJOR, int B_MAJOR, int BN> __device__ __forceinline__ constexpr uint32_t make_idesc_f16() {
+    return (1u << 4) | ((uint32_t)A_MAJOR << 15) | ((uint32_t)B_MAJOR << 16) | ((uint32_t)(BN >> 3) << 17) |
+           ((uint32_t)(BM >> 4) << 24);
+}
+
+// fp16 split: x = hi + lo with hi = fp16(x) (11 significant bits) and lo = x - hi (exact in fp32, |lo| <= 2^-11 |x|);
+// lo is carried as lo' = fp16(lo * 2^11), which keeps it in fp16's normal range wherever hi is, so hi + lo' 2^-11
+// has 22 significant bits.  A product needs three MMAs: hi*hi, and hi*lo' + lo'*hi in an accumulator of their own that
+// the epilogue folds in with the factor 2^-11 (the dropped lo*lo is below 2^-22 relative).  Valid for
+// 2^-16 <= max |x| < 2^15 (poz_tc3.h, f16_flag).
+constexpr float F16_LO_SCALE = 2048.f, F16_LO_UNSCALE = 1.f / 2048.f;
+constexpr float F16_MAX_OK = 32768.f, F16_MIN_OK = 1.52587890625e-05f;
+__device__ __forceinline__ void split2h_pair(float x0, float x1, uint32_t& ph, uint32_t& pl) {
+    const __half2 h = __floats2half2_rn(x0, x1);
+    ph = *reinterpret_cast<const uint32_t*>(&h);
+    const float2 hf = __half22float2(h);
+    const __half2 l = __floats2half2_rn(fmaf(x0, F16_LO_SCALE, -F16_LO_SCALE * hf.x), fmaf(x1, F16_LO_SCALE, -F16_LO_SCALE * hf.y));
+    pl = *reinterpret_cast<const uint32_t*>(&l);
+}
+__device__ __forceinline__ bool f16_range_bad(float amax) {
+    return amax >= F16_MAX_OK || (amax != 0.f && amax < F16_MIN_OK);
 }
 
 // x -> (hi, mid, lo) bf16 with x ~= hi + mid + lo
@@ -109,6 +134,35 @@ __global__ void split_planes_kernel(const float* __restrict__ src, const int* __
         *reinterpret_cast<uint4*>(o + plane_stride) = make_uint4(pm[0], pm[1], pm[2], pm[3]);
         *reinterpret_cast<uint4*>(o + 2 * plane_stride) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
     }
+}
+
+// fp32 matrix [rows][cols] (pitch ld) -> fp16 planes [2][rows][ldp] (hi, lo'), pad columns zeroed; max |x| -> *amax_bits
+__global__ void split_planes_f16_kernel(const float* __restrict__ src, long long rows, int cols, long long ld,
+                                        __nv_bfloat16* __restrict__ dst, long long ldp, long long plane_stride,
+                                        unsigned* __restrict__ amax_bits) {
+    const int groups = (int)(ldp / 8);
+    const long long total = rows * groups;
+    float amax = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / groups;
+        const int c = (int)(i - r * groups) * 8;
+        const float* s = src + r * ld + c;
+        float x[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            x[j] = (c + j < cols) ? s[j] : 0.f;
+            amax = fmaxf(amax, fabsf(x[j]));
+        }
+        uint32_t ph[4], pl[4];
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) split2h_pair(x[j], x[j + 1], ph[j / 2], pl[j / 2]);
+        __nv_bfloat16* o = dst + r * ldp + c;
+        *reinterpret_cast<uint4*>(o) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+        *reinterpret_cast<uint4*>(o + plane_stride) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(amax_bits, __float_as_uint(amax));   // non-negative floats order as their bits
 }
 
 }  // namespace tc3

@@ -32,23 +32,29 @@ __device__ __forceinline__ void tma_load_2d_f32(const CUtensorMap* map, uint64_t
                  : "memory");
 }
 
-constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in flight in shared memory
+constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in flight in shared memory (default)
 constexpr int X32T_SLOT_COLS = PLANES * 16;         // 32 k-values of three planes, two per column
 constexpr int X32T_W_WARP = NUM_EPI_WARPS + 2 + X32_CONV_WARPS;   // warp 18: producer of W's planes
 constexpr int X32T_THREADS = X32_THREADS + 32;
 
-template <int BN, int STAGES_, bool HEAD> struct CfgX32T {
+template <int BN, int STAGES_, bool HEAD, bool F16 = false, int RAW_SLOTS_ = X32T_SLOTS> struct CfgX32T {
     static constexpr int STAGES = STAGES_;          // W-plane stages (one per 64-wide k-block)
+    static constexpr int RAW_SLOTS = RAW_SLOTS_;    // fp32 half-blocks of X in flight in shared memory
+    static constexpr int NPL = F16 ? 2 : PLANES;    // planes per operand
     static constexpr int B_PLANE = BN * BK * 2;
-    static constexpr int B_STAGE = PLANES * B_PLANE;
+    static constexpr int B_STAGE = NPL * B_PLANE;
     static constexpr int RAW_OFF = STAGES * B_STAGE;
-    static constexpr int BAR_OFF = RAW_OFF + X32T_SLOTS * X32_RAW_BYTES;
-    static constexpr int HEAD_OFF = BAR_OFF + 256;  // fused head: staged weights + two partial-sum buffers (poz_tc3.h)
+    static constexpr int BAR_OFF = RAW_OFF + RAW_SLOTS * X32_RAW_BYTES;
+    static constexpr int HEAD_OFF = BAR_OFF + 512;  // fused head: staged weights + two partial-sum buffers (poz_tc3.h)
     static constexpr int SMEM_BYTES = HEAD_OFF + (HEAD ? HEAD_SMEM_BYTES : 0) + 1024;
     static constexpr int SMALL_COL0 = 2 * BN;       // after the two main accumulators
     static constexpr int A_COL0 = 3 * BN;
     static constexpr int TMEM_COLS = 512;
-    static_assert(A_COL0 + 2 * X32T_SLOT_COLS <= TMEM_COLS, "tensor memory: accumulators + two X-plane slots");
+    // X-plane slots in tensor memory, each one half-block (32 k) of NPL planes: one per converter group, two in the fp16 form
+    // (its planes are smaller; measured neutral: the converters, not the hand-over of a slot, set the pace)
+    static constexpr int SLOT_COLS = NPL * 16;
+    static constexpr int NSLOT = F16 ? 4 : 2;
+    static_assert(A_COL0 + NSLOT * SLOT_COLS <= TMEM_COLS, "tensor memory: accumulators + the X-plane slots");
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory of the fp32-input kernel");
 };
 
@@ -100,22 +106,27 @@ __device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-template <int BN, int NSTAGES, bool HEAD>
+// F16: two fp16 planes per operand and three MMAs per product instead of three bf16 planes and six (poz_tc3_gemm.cuh,
+// split2h_pair): half the work for the tensor pipe, a third less for the converters and for the W loads.
+template <int BN, int NSTAGES, bool HEAD, bool F16 = false, int RAW_SLOTS = X32T_SLOTS>
 __global__ void __launch_bounds__(X32T_THREADS, 1)
 tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                     long long M, int N, long long K, Epi3 ep) {
-    using C = CfgX32T<BN, NSTAGES, HEAD>;
+    using C = CfgX32T<BN, NSTAGES, HEAD, F16, RAW_SLOTS>;
     constexpr int STAGES = C::STAGES;
+    constexpr int NPL = C::NPL;
+    constexpr int NSLOT = C::NSLOT;
+    if (ep.run_if && *ep.run_if == 0) return;        // the repeat of a pass that needed none (uniform: before any barrier)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* raw = smem + C::RAW_OFF;                                  // [X32T_SLOTS][128 rows][32 floats], swizzled
     uint64_t* b_full = reinterpret_cast<uint64_t*>(smem + C::BAR_OFF); // [STAGES] W planes landed
     uint64_t* b_empty = b_full + STAGES;                               // [STAGES] MMAs of the stage retired
-    uint64_t* a_full = b_empty + STAGES;                               // [2] planes of half h of the k-block are in tensor memory
-    uint64_t* a_empty = a_full + 2;                                    // [2] MMAs that read them retired
-    uint64_t* raw_full = a_empty + 2;                                  // [SLOTS]
-    uint64_t* raw_empty = raw_full + X32T_SLOTS;                       // [SLOTS]
-    uint64_t* tmem_full_bar = raw_empty + X32T_SLOTS;                  // [2]
+    uint64_t* a_full = b_empty + STAGES;                               // [NSLOT] planes of a half-block are in tensor memory
+    uint64_t* a_empty = a_full + NSLOT;                                // [NSLOT] MMAs that read them retired
+    uint64_t* raw_full = a_empty + NSLOT;                              // [SLOTS]
+    uint64_t* raw_empty = raw_full + RAW_SLOTS;                        // [SLOTS]
+    uint64_t* tmem_full_bar = raw_empty + RAW_SLOTS;                   // [2]
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;                      // [2]
     uint64_t* small_empty_bar = tmem_empty_bar + 2;                    // [1] small-terms accumulator folded into the main one
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(small_empty_bar + 1);
@@ -130,8 +141,8 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         tc::tma_prefetch_desc(&map_x);
         tc::tma_prefetch_desc(&map_b);
         for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&b_empty[s], 1); }
-        for (int h = 0; h < 2; ++h) { tc::mbar_init(&a_full[h], X32_CONV_WARPS / 2); tc::mbar_init(&a_empty[h], 1); }
-        for (int q = 0; q < X32T_SLOTS; ++q) { tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], X32_CONV_WARPS / 2); }
+        for (int h = 0; h < NSLOT; ++h) { tc::mbar_init(&a_full[h], X32_CONV_WARPS / 2); tc::mbar_init(&a_empty[h], 1); }
+        for (int q = 0; q < RAW_SLOTS; ++q) { tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], X32_CONV_WARPS / 2); }
         tc::mbar_init(small_empty_bar, NUM_EPI_WARPS);
         for (int b = 0; b < 2; ++b) { tc::mbar_init(&tmem_full_bar[b], 1); tc::mbar_init(&tmem_empty_bar[b], NUM_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -154,7 +165,7 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     mbar_wait_idle(&raw_empty[slot], rphase ^ 1);
                     tc::mbar_expect_tx(&raw_full[slot], X32_RAW_BYTES);
                     tma_load_2d_f32(&map_x, &raw_full[slot], raw + slot * X32_RAW_BYTES, 32 * hb, (int)(mb * BM));
-                    if (++slot == X32T_SLOTS) { slot = 0; rphase ^= 1; }
+                    if (++slot == RAW_SLOTS) { slot = 0; rphase ^= 1; }
                 }
             }
         }
@@ -171,7 +182,7 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     uint8_t* sb = smem + stage * C::B_STAGE;
                     tc::mbar_expect_tx(&b_full[stage], C::B_STAGE);
 #pragma unroll
-                    for (int p = 0; p < PLANES; ++p)
+                    for (int p = 0; p < NPL; ++p)
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
                             tma_load_3d(&map_b, &b_full[stage], sb + p * C::B_PLANE + j * 8192, nb * BN + 64 * j, kc, p);
@@ -182,7 +193,8 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     } else if (warp == 9) {
         // ================= MMA issuer =================
         if (tc::elect_one()) {
-            constexpr uint32_t idesc = make_idesc3<MAJOR_K, MAJOR_MN, BN>();
+            constexpr uint32_t idesc = F16 ? make_idesc_f16<MAJOR_K, MAJOR_MN, BN>() : make_idesc3<MAJOR_K, MAJOR_MN, BN>();
+            if (F16 && ep.f16_flag && ep.f16_w_amax && f16_range_bad(__uint_as_float(*ep.f16_w_amax))) *ep.f16_flag = 1;
             int stage = 0;
             uint32_t phase = 0;
             uint32_t kbc = 0;                              // k-blocks done: parity of the per-half barriers
@@ -199,28 +211,37 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     const uint32_t sb = tc::smem_u32(smem + stage * C::B_STAGE);
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        tc::mbar_wait(&a_full[h], kbc & 1);
+                        // half h of k-block kbc lives in slot h (+ 2 for odd k-blocks when there are four)
+                        const uint32_t as = NSLOT == 4 ? (uint32_t)h + 2u * (kbc & 1u) : (uint32_t)h;
+                        const uint32_t apar = NSLOT == 4 ? (kbc >> 1) & 1u : kbc & 1u;
+                        tc::mbar_wait(&a_full[as], apar);
                         tc::tc_fence_after();
-                        const uint32_t ta = tmem_base + C::A_COL0 + h * X32T_SLOT_COLS;
+                        const uint32_t ta = tmem_base + C::A_COL0 + as * C::SLOT_COLS;
 #pragma unroll
                         for (int j = 0; j < 2; ++j) {
                             const int kk = 2 * h + j;
-                            uint32_t ad[PLANES];
-                            uint64_t bd[PLANES];
+                            uint32_t ad[NPL];
+                            uint64_t bd[NPL];
 #pragma unroll
-                            for (int p = 0; p < PLANES; ++p) {
+                            for (int p = 0; p < NPL; ++p) {
                                 ad[p] = ta + p * 16 + j * 8;
                                 bd[p] = tc::make_desc(sb + p * C::B_PLANE + kk * 2048, 8192, 1024);
                             }
                             const uint32_t first = (kb | kk) != 0 ? 1u : 0u;
-                            umma_bf16_ts(acs, ad[0], bd[2], idesc, first);
-                            umma_bf16_ts(acs, ad[2], bd[0], idesc, 1u);
-                            umma_bf16_ts(acs, ad[1], bd[1], idesc, 1u);
-                            umma_bf16_ts(acs, ad[0], bd[1], idesc, 1u);
-                            umma_bf16_ts(acs, ad[1], bd[0], idesc, 1u);
-                            umma_bf16_ts(acc, ad[0], bd[0], idesc, first);
+                            if constexpr (F16) {
+                                umma_bf16_ts(acs, ad[0], bd[1], idesc, first);     // hi * lo'   (both scaled by 2^11)
+                                umma_bf16_ts(acs, ad[1], bd[0], idesc, 1u);        // lo' * hi
+                                umma_bf16_ts(acc, ad[0], bd[0], idesc, first);     // hi * hi
+                            } else {
+                                umma_bf16_ts(acs, ad[0], bd[NPL - 1], idesc, first);
+                                umma_bf16_ts(acs, ad[NPL - 1], bd[0], idesc, 1u);
+                                umma_bf16_ts(acs, ad[1], bd[1], idesc, 1u);
+                                umma_bf16_ts(acs, ad[0], bd[1], idesc, 1u);
+                                umma_bf16_ts(acs, ad[1], bd[0], idesc, 1u);
+                                umma_bf16_ts(acc, ad[0], bd[0], idesc, first);
+                            }
                         }
-                        tc::umma_commit(&a_empty[h]);        // this half's plane slot may be rewritten
+                        tc::umma_commit(&a_empty[as]);       // this half's plane slot may be rewritten
                     }
                     tc::umma_commit(&b_empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -236,10 +257,12 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const int grp = (warp - (NUM_EPI_WARPS + 2)) >> 2;
         const int r = quarter * 32 + lane;
         const uint32_t sw = (uint32_t)(r & 7);
-        const uint32_t ta = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::A_COL0 + grp * X32T_SLOT_COLS;
+        const uint32_t ta0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::A_COL0;
         const uint32_t raw_row = tc::smem_u32(raw) + r * 128;
         uint32_t slot = grp, rphase = 0, kbc = 0;
+        bool bad = false;                                  // F16: a row of this lane outside the fp16-split range
         for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            __half2 amax2 = __floats2half2_rn(0.f, 0.f);   // F16: max |hi| of this lane's half of the row
             for (int kb = 0; kb < nkb; ++kb, ++kbc) {
                 tc::mbar_wait(&raw_full[slot], rphase);
                 const uint32_t src = raw_row + slot * X32_RAW_BYTES;
@@ -247,28 +270,47 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                 for (int c = 0; c < 8; ++c) x[c] = lds128(src + (((uint32_t)c ^ sw) << 4));
                 uint32_t ph[16], pm[16], pl[16];
+                if constexpr (F16) {
 #pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    split3_pair(x[c].x, x[c].y, ph[2 * c], pm[2 * c], pl[2 * c]);
-                    split3_pair(x[c].z, x[c].w, ph[2 * c + 1], pm[2 * c + 1], pl[2 * c + 1]);
+                    for (int c = 0; c < 8; ++c) {
+                        split2h_pair(x[c].x, x[c].y, ph[2 * c], pl[2 * c]);
+                        split2h_pair(x[c].z, x[c].w, ph[2 * c + 1], pl[2 * c + 1]);
+                        amax2 = __hmax2(amax2, __hmax2(__habs2(*reinterpret_cast<const __half2*>(&ph[2 * c])),
+                                                       __habs2(*reinterpret_cast<const __half2*>(&ph[2 * c + 1]))));
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        split3_pair(x[c].x, x[c].y, ph[2 * c], pm[2 * c], pl[2 * c]);
+                        split3_pair(x[c].z, x[c].w, ph[2 * c + 1], pm[2 * c + 1], pl[2 * c + 1]);
+                    }
                 }
-                // the MMAs that read this half's planes in the previous k-block must have retired
-                tc::mbar_wait(&a_empty[grp], (kbc & 1) ^ 1);
+                // the MMAs that last read this slot (one k-block ago, or two with four slots) must have retired
+                const uint32_t as = NSLOT == 4 ? (uint32_t)grp + 2u * (kbc & 1u) : (uint32_t)grp;
+                const uint32_t apar = NSLOT == 4 ? (kbc >> 1) & 1u : kbc & 1u;
+                const uint32_t ta = ta0 + as * C::SLOT_COLS;
+                tc::mbar_wait(&a_empty[as], apar ^ 1);
                 tc::tc_fence_after();
                 tmem_st16(ta, ph);
-                tmem_st16(ta + 16, pm);
-                tmem_st16(ta + 32, pl);
+                if constexpr (F16) {
+                    tmem_st16(ta + 16, pl);
+                } else {
+                    tmem_st16(ta + 16, pm);
+                    tmem_st16(ta + 32, pl);
+                }
                 tmem_st_wait();
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
                     tc::mbar_arrive(&raw_empty[slot]);
-                    tc::mbar_arrive(&a_full[grp]);
+                    tc::mbar_arrive(&a_full[as]);
                 }
                 slot += 2;
-                if (slot >= X32T_SLOTS) { slot -= X32T_SLOTS; rphase ^= 1; }
+                if (slot >= RAW_SLOTS) { slot -= RAW_SLOTS; rphase ^= 1; }
             }
+            if (F16) bad = bad || f16_range_bad(fmaxf(__low2float(amax2), __high2float(amax2)));
         }
+        if (F16 && bad && ep.f16_flag) *ep.f16_flag = 1;
     } else {
         // ================= epilogue =================
         const int quarter = warp & 3, chalf = warp >> 2;
@@ -298,7 +340,9 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     tc::tmem_ld32(ts + c, w);
                     tc::tmem_ld_wait();
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                    for (int j = 0; j < 32; ++j)
+                        v[j] = __float_as_uint(F16 ? fmaf(__uint_as_float(w[j]), F16_LO_UNSCALE, __uint_as_float(v[j]))
+                                                   : __uint_as_float(v[j]) + __uint_as_float(w[j]));
                     tmem_st32(tm + c, v);
                 }
                 tmem_st_wait();

@@ -5,7 +5,10 @@ import numpy as np
 
 PATHS = {
     "simt fp32 FFMA": {"POZ_TC3_MIN_BATCH": "1000000000"},
-    "tc3 planes in tmem, shared small-terms accumulator (default)": {},
+    "tc3 bf16 x 3 planes in tmem, six MMAs per product": {"POZ_TC3_F16": "0"},
+    "tc3 fp16 x 2 planes in tmem, three MMAs per product (default)": {},
+    "  the same, inputs scaled by 1e-3": {"INFER_ERROR_SCALE": "1e-3"},
+    "  the same, inputs scaled by 1e+3": {"INFER_ERROR_SCALE": "1e3"},
 }
 
 def child():
@@ -21,7 +24,7 @@ def child():
     for l in range(3):
         eng.upload_params(l, params[2 * l], params[2 * l + 1])
     g = torch.Generator(device="cuda:0").manual_seed(1)
-    xd = torch.randn((8192, 784), generator=g, device="cuda:0", dtype=torch.float32)
+    xd = torch.randn((32768, 784), generator=g, device="cuda:0", dtype=torch.float32) * float(os.environ.get("INFER_ERROR_SCALE", "1"))
     out = eng.forward(xd).cpu().numpy().astype(np.float64)
     ref = orc.forward(orc.parse_stack(algos), params, xd.cpu().numpy().astype(np.float64))[0][-1]
     rel = np.abs(out - ref) / ref

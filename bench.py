@@ -56,7 +56,7 @@ def init_params(sizes, seed=0):
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures committed under
 # profiles/ncu/ (r01_c2_simt_full_raw_v3.csv, r01_c4_tc_fwd_full_raw.csv); null where no capture exists.
 # dram__bytes_read.sum + dram__bytes_write.sum of the two launches of one 262,144-row inference pass (ncu --set full)
-NCU_TRAFFIC_C3 = {262144: 1_348_500_000}
+NCU_TRAFFIC_C3 = {262144: 1_348_500_000}      # (measured on the split-bf16 kernels; the fp16-split ones move the same fp32 tensors)
 NCU_TRAFFIC_SOURCE = "ncu --set full, profiles/ncu/r01_c2_simt_full_raw_v3.csv"
 TC3_MMAS_PER_PRODUCT = 6
 NCU_TRAFFIC = {"fwd_l0": 4_344_064, "bwd_w_l0": 4_307_712, "fwd_l1": 1_508_608, "bwd_w_l1": 1_620_736,
@@ -495,13 +495,19 @@ def run_c3(args, world, rank, local):
                              "note": "fp32-grade FLOP rate against the FMA pipe; above 1 when the layers run on the tensor "
                                      "cores (batch >= 2048)"},
                 "kernels_ms": {t: round(v["ms"] / 5, 4) for t, v in prof.items()}}
-        if any(t.startswith("tc3_") for t in prof):
-            # split-bf16 path: six bf16 MMAs per fp32-grade product
-            tf = 6 * batch * C3_FLOPS_PER_SAMPLE / per / 1e12
+        if any(t.startswith("tc3") for t in prof):
+            # fp16-split kernels (tc3h_*): three 16-bit MMAs per fp32-grade product; split-bf16 kernels (tc3_*): six
+            f16 = any(t.startswith("tc3h_") for t in prof)
+            mmas = 3 if f16 else 6
+            tf = mmas * batch * C3_FLOPS_PER_SAMPLE / per / 1e12
             roof["tensor"] = {"achieved_tflops": round(tf, 1), "peak_tflops": pk["bf16_tflops_sustained"],
-                              "frac": round(tf / pk["bf16_tflops_sustained"], 4),
-                              "note": "bf16 MMA rate of the whole pass (6 plane products per fp32-grade product) against the "
-                                      "sustained cuBLAS bf16 figure"}
+                              "frac": round(tf / pk["bf16_tflops_sustained"], 4), "mmas_per_product": mmas,
+                              "note": ("16-bit MMA rate of the whole pass (%d plane products per fp32-grade product: %s) against "
+                                       "the sustained cuBLAS bf16 figure" % (mmas, "two fp16 planes per operand" if f16
+                                                                            else "three bf16 planes per operand"))}
+            if f16:
+                roof["note"] = ("fp16-split kernels; the tc3_* entries of kernels_ms are the split-bf16 repeat launches that "
+                                "return at once unless an operand left the fp16-split range")
     eng.close()
     return dict(metric="infer samples/s", unit="samples/s", value=world * batch * args.steps / (ms * 1e-3),
                 ms_per_step=ms / args.steps,

@@ -56,6 +56,7 @@ struct poz_ctx {
     unsigned upd_done_mask = 0;       // layers whose update this step's backward already applied
     bool tail_fused = true;           // last hidden unit + head + their backward-x in one launch (POZ_TAIL=0 disables)
     long long tail_max_batch = 4096;
+    bool pdl = true;                  // the launches of the narrow step's critical path as programmatic dependents (POZ_PDL=0: plain edges)
     int tail_cluster = 4;             // blocks of the tail launch that share the reads of W1 (POZ_TAIL_CLUSTER = 1, 2, 4)
     bool tail_group = true;           // + the weight gradients of layers 0 and 1 in one tensor-core launch, head / b1 updated from the
                                       //   tail's partial sums (POZ_TAIL_GROUP=0 disables)

@@ -175,15 +175,8 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
+    pdl_trigger();                                                    // (programmatic dependent launch: see poz_tcs_kernel.cuh)
     tail_cluster_arrive();                                            // "my barriers are armed"
-    {
-        const int r = t >> 6, c = t & 63;                            // a0: 8 rows x (up to) 64 16-byte pieces
-        if (c < k4) {
-            const long long m = m0 + r < a.M ? m0 + r : a.M - 1;
-            tail_cp16(a0s + r * PA + c * 4, a.a0 + m * K1 + c * 4);
-        }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
     tail_cluster_wait();                                              // ... and so are everybody else's: rows may be sent
     if (warp < nchunks) {                                             // warp w sends this CTA's share of chunk w
         const int r = warp * TAIL_CHUNK + lane;
@@ -199,6 +192,15 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
     int y = -1;                                                        // label of this warp's row
     const long long mw = m0 + hrow;
     if (mw < a.M) y = a.labels[a.row_idx ? (long long)a.row_idx[mw] : mw];
+    pdl_wait();                                                       // a0 is the launch before's result; nothing above reads it
+    {
+        const int r = t >> 6, c = t & 63;                            // a0: 8 rows x (up to) 64 16-byte pieces
+        if (c < k4) {
+            const long long m = m0 + r < a.M ? m0 + r : a.M - 1;
+            tail_cp16(a0s + r * PA + c * 4, a.a0 + m * K1 + c * 4);
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");      // a0 rows (cp.async) and the small operands
     __syncthreads();
     if (ktr) ktr->t[1] = fast::ktrace_now();

@@ -146,7 +146,7 @@ int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long 
         if (ep.head_w)
             tc3_fwd_x32t_kernel<BN, 3, true, true><<<grid, X32T_THREADS, FH::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
         else
-            tc3_fwd_x32t_kernel<BN, 3, false, true, 7><<<grid, X32T_THREADS, FT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
+            tc3_fwd_x32t_kernel<BN, 3, false, true, 7><<<grid, x32t_threads(2), FT::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     } else if (ep.head_w)
         tc3_fwd_x32t_kernel<BN, 2, true><<<grid, X32T_THREADS, CH::SMEM_BYTES, stream>>>(mx, mb, M, N, (long long)K, ep);
     else
@@ -154,6 +154,22 @@ int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long 
     count_launch();
     POZ_CUDA(cudaGetLastError());
     return 0;
+}
+
+void x32t_probe_dump() {
+    unsigned long long h[16] = {0};
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpyFromSymbol(h, x32t_probe, sizeof(h)) != cudaSuccess || !h[5]) return;
+    const double n = (double)h[5];
+    fprintf(stderr, "[poz x32t probe] converter warp 10 of block 0, %llu half-blocks, cycles per half-block: wait for fp32 data %.0f, "
+                    "loads + conversion %.0f, wait for the tensor-memory slot %.0f, tcgen05.st + wait %.0f, fences + arrivals %.0f; "
+                    "whole loop %.0f\n", h[5], h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n, h[6] / n);
+    if (h[12]) {
+        const double m = (double)h[12];
+        fprintf(stderr, "[poz x32t probe] MMA issuer of block 0, %llu k-blocks, cycles per k-block: wait for the accumulators (tile boundary) %.0f, "
+                        "for W's planes %.0f, for X's planes %.0f, issuing %.0f\n", h[12], h[8] / m, h[9] / m, h[10] / m, h[11] / m);
+    }
+    unsigned long long z[16] = {0};
+    cudaMemcpyToSymbol(x32t_probe, z, sizeof(z));
 }
 
 int gemm_backward_data(const PlaneMat& dz, const PlaneMat& w, long long M, int K_in, int N_out, const Epi3& ep, int sms,
@@ -206,7 +222,7 @@ template <bool A_T, class Epi> static int launch(const Gemm* gs, const Epi* epis
         POZ_TRY(tc3::make_map3(&maps[i], g.b, 64, 64));
         Args& a = ga.a[i];
         a.a = g.a; a.lda = g.lda; a.row_idx = g.row_idx; a.a_cols = g.a_cols; a.ones_row = g.ones_row;
-        a.M = g.M; a.N = g.N; a.K = g.K;
+        a.M = g.M; a.N = g.N; a.K = g.K; a.a_dep = g.a_dep;
         a.k_per_split = ((nkb + splits - 1) / splits) * BK;
         ga.tiles_n[i] = (g.N + BN - 1) / BN;
         tiles += ((g.M + BM - 1) / BM) * ga.tiles_n[i];
@@ -220,10 +236,12 @@ template <bool A_T, class Epi> static int launch(const Gemm* gs, const Epi* epis
     cfg.blockDim = dim3(THREADS);
     cfg.dynamicSmemBytes = SMEM_BYTES;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)splits;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = gs[0].pdl ? 2 : 1;
     POZ_CUDA(cudaLaunchKernelEx(&cfg, kern, ga, maps[0], maps[1], maps[2], maps[3], ge));
     count_launch();
     return 0;

@@ -42,6 +42,7 @@ struct Epi3 {
     int* f16_flag;                // nullable
     const unsigned* f16_w_amax;   // bits of max |W| of this layer (device), written when its fp16 planes were made
     const int* run_if;            // nullable: the kernel does nothing unless *run_if != 0
+    int probe;                    // POZ_X32T_PROBE=1: one converter warp of block 0 adds up the cycles of its loop's phases
 };
 constexpr int HEAD_MAX_N = 16;
 constexpr int HEAD_SMEM_BYTES = (128 * HEAD_MAX_N + 2 * 128 * HEAD_MAX_N) * 4;   // staged weights + two partial-sum buffers
@@ -62,6 +63,7 @@ int gemm_forward_x32(const float* x, long long ld, const PlaneMat& w, long long 
 int split_planes_f16(const float* src, long long rows, int cols, long long ld, __nv_bfloat16* dst, long long ldp,
                      long long plane_stride, unsigned* amax_bits, cudaStream_t stream);
 bool gemm_forward_x32_ok(const float* x, long long ld, int N);
+void x32t_probe_dump();           // prints and clears the sums of POZ_X32T_PROBE=1
 // whether gemm_forward_x32 takes ep.head_* (only the tensor-memory variant does)
 bool gemm_forward_x32_head_ok();
 // out[M][K_in] = epilogue(dz[M][N_out] * w[K_in][N_out]^T)

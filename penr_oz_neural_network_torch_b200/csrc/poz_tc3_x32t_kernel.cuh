@@ -22,8 +22,9 @@
 namespace poz {
 namespace tc3 {
 
-constexpr int X32_CONV_WARPS = 8;                   // two groups of four: one tile row per lane
+constexpr int X32_CONV_WARPS = 8;                   // two groups of four (default): one tile row per lane
 constexpr int X32_THREADS = (NUM_EPI_WARPS + 2 + X32_CONV_WARPS) * 32;
+constexpr int x32t_threads(int ncg) { return (NUM_EPI_WARPS + 3 + 4 * ncg) * 32; }
 constexpr int X32_RAW_BYTES = BM * 32 * 4;          // one half-block: 128 rows x 32 floats
 
 __device__ __forceinline__ void tma_load_2d_f32(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
@@ -31,6 +32,13 @@ __device__ __forceinline__ void tma_load_2d_f32(const CUtensorMap* map, uint64_t
                  ::"r"(tc::smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1)
                  : "memory");
 }
+
+// POZ_X32T_PROBE=1: cycles spent by converter warp 10 of block 0 in the phases of its loop, summed over the launch:
+// [0] waiting for the fp32 half-block, [1] loads + conversion, [2] waiting for the tensor-memory slot, [3] tcgen05.st + its
+// wait, [4] fences / arrivals, [5] iterations, [6] whole loop
+// and of the MMA issuer of block 0: [8] waiting for the accumulators at a tile boundary, [9] for W's planes, [10] for X's planes,
+// [11] the rest (issuing), [12] k-blocks
+__device__ unsigned long long x32t_probe[16];
 
 constexpr int X32T_SLOTS = 5;                       // fp32 half-blocks in flight in shared memory (default)
 constexpr int X32T_SLOT_COLS = PLANES * 16;         // 32 k-values of three planes, two per column
@@ -108,14 +116,21 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 
 // F16: two fp16 planes per operand and three MMAs per product instead of three bf16 planes and six (poz_tc3_gemm.cuh,
 // split2h_pair): half the work for the tensor pipe, a third less for the converters and for the W loads.
-template <int BN, int NSTAGES, bool HEAD, bool F16 = false, int RAW_SLOTS = X32T_SLOTS>
-__global__ void __launch_bounds__(X32T_THREADS, 1)
+// NCG: converter groups of four warps each.  Half-blocks are numbered through the whole launch (hbg); group g converts
+// hbg = g, g + NCG, ...; half-block hbg uses ring slot hbg % RAW_SLOTS and tensor-memory slot hbg % NSLOT.  A converter
+// warp's loop is serial -- wait for data 290, load + convert 510, wait for the slot, publish 380 cycles (POZ_X32T_PROBE=1) --
+// so with two groups the MMAs (768 cycles of tensor pipe per k-block in the fp16 form) were fed one k-block per ~1600.
+// A third group (736 threads, 80 registers) was measured: 966 instead of 508 cycles for load + convert, the pass slower
+// (0.358 against 0.338 ms) -- the warps of a scheduler share the conversion pipe, which is what the time goes to.
+template <int BN, int NSTAGES, bool HEAD, bool F16 = false, int RAW_SLOTS = X32T_SLOTS, int NCG = 2>
+__global__ void __launch_bounds__((NUM_EPI_WARPS + 3 + 4 * NCG) * 32, 1)
 tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                     long long M, int N, long long K, Epi3 ep) {
     using C = CfgX32T<BN, NSTAGES, HEAD, F16, RAW_SLOTS>;
     constexpr int STAGES = C::STAGES;
     constexpr int NPL = C::NPL;
     constexpr int NSLOT = C::NSLOT;
+    constexpr int W_WARP = NUM_EPI_WARPS + 2 + 4 * NCG;      // producer of W's planes: the warp after the converters
     if (ep.run_if && *ep.run_if == 0) return;        // the repeat of a pass that needed none (uniform: before any barrier)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -141,8 +156,8 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         tc::tma_prefetch_desc(&map_x);
         tc::tma_prefetch_desc(&map_b);
         for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&b_full[s], 1); tc::mbar_init(&b_empty[s], 1); }
-        for (int h = 0; h < NSLOT; ++h) { tc::mbar_init(&a_full[h], X32_CONV_WARPS / 2); tc::mbar_init(&a_empty[h], 1); }
-        for (int q = 0; q < RAW_SLOTS; ++q) { tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], X32_CONV_WARPS / 2); }
+        for (int h = 0; h < NSLOT; ++h) { tc::mbar_init(&a_full[h], 4); tc::mbar_init(&a_empty[h], 1); }
+        for (int q = 0; q < RAW_SLOTS; ++q) { tc::mbar_init(&raw_full[q], 1); tc::mbar_init(&raw_empty[q], 4); }
         tc::mbar_init(small_empty_bar, NUM_EPI_WARPS);
         for (int b = 0; b < 2; ++b) { tc::mbar_init(&tmem_full_bar[b], 1); tc::mbar_init(&tmem_empty_bar[b], NUM_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -169,7 +184,7 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 }
             }
         }
-    } else if (warp == X32T_W_WARP) {
+    } else if (warp == W_WARP) {
         // ================= TMA producer, W: one stage of planes per 64-wide k-block =================
         if (tc::elect_one()) {
             int stage = 0;
@@ -200,22 +215,29 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             uint32_t kbc = 0;                              // k-blocks done: parity of the per-half barriers
             uint32_t it = 0;
             const uint32_t acs = tmem_base + C::SMALL_COL0; // small-terms accumulator (shared by the two tile buffers)
+            const bool mprobe = ep.probe && blockIdx.x == 0;
+            long long mc[4] = {0, 0, 0, 0}, mt = mprobe ? clock64() : 0, mn = 0;
             for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
                 const uint32_t ab = it & 1, aphase = (it >> 1) & 1;
+                if (mprobe) { const long long now = clock64(); mc[3] += now - mt; mt = now; }
                 tc::mbar_wait(&tmem_empty_bar[ab], aphase ^ 1);
                 tc::mbar_wait(small_empty_bar, (it & 1) ^ 1);     // the previous tile's small terms have been folded away
                 tc::tc_fence_after();
+                if (mprobe) { const long long now = clock64(); mc[0] += now - mt; mt = now; }
                 const uint32_t acc = tmem_base + ab * BN;          // main (hi*hi) accumulator
                 for (int kb = 0; kb < nkb; ++kb, ++kbc) {
+                    if (mprobe) { const long long now = clock64(); mc[3] += now - mt; mt = now; ++mn; }
                     tc::mbar_wait(&b_full[stage], phase);
+                    if (mprobe) { const long long now = clock64(); mc[1] += now - mt; mt = now; }
                     const uint32_t sb = tc::smem_u32(smem + stage * C::B_STAGE);
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        // half h of k-block kbc lives in slot h (+ 2 for odd k-blocks when there are four)
-                        const uint32_t as = NSLOT == 4 ? (uint32_t)h + 2u * (kbc & 1u) : (uint32_t)h;
-                        const uint32_t apar = NSLOT == 4 ? (kbc >> 1) & 1u : kbc & 1u;
+                        const uint32_t hbg = 2u * kbc + (uint32_t)h;       // half-block number since the launch began
+                        const uint32_t as = hbg % NSLOT, apar = (hbg / NSLOT) & 1u;
+                        if (mprobe) { const long long now = clock64(); mc[3] += now - mt; mt = now; }
                         tc::mbar_wait(&a_full[as], apar);
                         tc::tc_fence_after();
+                        if (mprobe) { const long long now = clock64(); mc[2] += now - mt; mt = now; }
                         const uint32_t ta = tmem_base + C::A_COL0 + as * C::SLOT_COLS;
 #pragma unroll
                         for (int j = 0; j < 2; ++j) {
@@ -248,23 +270,35 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 }
                 tc::umma_commit(&tmem_full_bar[ab]);
             }
+            if (mprobe) {
+                for (int q = 0; q < 4; ++q) atomicAdd(&x32t_probe[8 + q], (unsigned long long)mc[q]);
+                atomicAdd(&x32t_probe[12], (unsigned long long)mn);
+            }
         }
-    } else if (warp >= NUM_EPI_WARPS + 2 && warp < X32T_W_WARP) {
+    } else if (warp >= NUM_EPI_WARPS + 2 && warp < W_WARP) {
         // ================= converters: one row per lane (the lanes this warp may address in tensor memory) =================
-        // Two groups of four warps; group g converts half-block g of every k-block, so two half-blocks are in flight and
-        // one group's load -> convert -> store chain hides behind the other's.
+        // NCG groups of four warps; a group's load -> convert -> store chain hides behind the other groups'.
         const int quarter = warp & 3;
         const int grp = (warp - (NUM_EPI_WARPS + 2)) >> 2;
         const int r = quarter * 32 + lane;
         const uint32_t sw = (uint32_t)(r & 7);
         const uint32_t ta0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + C::A_COL0;
         const uint32_t raw_row = tc::smem_u32(raw) + r * 128;
-        uint32_t slot = grp, rphase = 0, kbc = 0;
         bool bad = false;                                  // F16: a row of this lane outside the fp16-split range
-        for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            __half2 amax2 = __floats2half2_rn(0.f, 0.f);   // F16: max |hi| of this lane's half of the row
-            for (int kb = 0; kb < nkb; ++kb, ++kbc) {
+        const bool probe = ep.probe && blockIdx.x == 0 && warp == NUM_EPI_WARPS + 2;
+        long long pc[5] = {0, 0, 0, 0, 0}, pt0 = probe ? clock64() : 0, pt = pt0, pn = 0;
+        const long long my_tiles = (long long)blockIdx.x < num_tiles ? (num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+        const uint32_t per_tile = 2u * (uint32_t)nkb;
+        const unsigned long long total_hb = (unsigned long long)my_tiles * per_tile;
+        uint32_t pos = (uint32_t)grp % per_tile;           // place of the half-block within its tile (a new tile = other rows)
+        __half2 amax2 = __floats2half2_rn(0.f, 0.f);       // F16: max |hi| over this lane's share of the current tile's row
+        static_assert(NCG <= NSLOT && NCG <= RAW_SLOTS, "a group advances by NCG slots per step");
+        uint32_t slot = grp % RAW_SLOTS, rphase = (grp / RAW_SLOTS) & 1u;     // ring slot hbg % RAW_SLOTS and its parity
+        uint32_t as = grp % NSLOT, apar = (grp / NSLOT) & 1u;                 // tensor-memory slot hbg % NSLOT and its parity
+        for (unsigned long long hbg = grp; hbg < total_hb; hbg += NCG) {
+            {
                 tc::mbar_wait(&raw_full[slot], rphase);
+                if (probe) { const long long now = clock64(); pc[0] += now - pt; pt = now; }
                 const uint32_t src = raw_row + slot * X32_RAW_BYTES;
                 float4 x[8];
 #pragma unroll
@@ -285,12 +319,12 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         split3_pair(x[c].z, x[c].w, ph[2 * c + 1], pm[2 * c + 1], pl[2 * c + 1]);
                     }
                 }
-                // the MMAs that last read this slot (one k-block ago, or two with four slots) must have retired
-                const uint32_t as = NSLOT == 4 ? (uint32_t)grp + 2u * (kbc & 1u) : (uint32_t)grp;
-                const uint32_t apar = NSLOT == 4 ? (kbc >> 1) & 1u : kbc & 1u;
+                // the MMAs that last read this tensor-memory slot (NSLOT half-blocks ago) must have retired
                 const uint32_t ta = ta0 + as * C::SLOT_COLS;
+                if (probe) { const long long now = clock64(); pc[1] += now - pt; pt = now; }
                 tc::mbar_wait(&a_empty[as], apar ^ 1);
                 tc::tc_fence_after();
+                if (probe) { const long long now = clock64(); pc[2] += now - pt; pt = now; }
                 tmem_st16(ta, ph);
                 if constexpr (F16) {
                     tmem_st16(ta + 16, pl);
@@ -299,18 +333,33 @@ tc3_fwd_x32t_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     tmem_st16(ta + 32, pl);
                 }
                 tmem_st_wait();
+                if (probe) { const long long now = clock64(); pc[3] += now - pt; pt = now; }
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
                     tc::mbar_arrive(&raw_empty[slot]);
                     tc::mbar_arrive(&a_full[as]);
                 }
-                slot += 2;
-                if (slot >= RAW_SLOTS) { slot -= RAW_SLOTS; rphase ^= 1; }
+                if (probe) { const long long now = clock64(); pc[4] += now - pt; pt = now; ++pn; }
             }
-            if (F16) bad = bad || f16_range_bad(fmaxf(__low2float(amax2), __high2float(amax2)));
+            slot += NCG;
+            if (slot >= RAW_SLOTS) { slot -= RAW_SLOTS; rphase ^= 1u; }
+            as += NCG;
+            if (as >= NSLOT) { as -= NSLOT; apar ^= 1u; }
+            pos += NCG;
+            if (pos >= per_tile) {                         // this group's next half-block belongs to a later tile
+                do pos -= per_tile; while (pos >= per_tile);
+                if (F16) bad = bad || f16_range_bad(fmaxf(__low2float(amax2), __high2float(amax2)));
+                amax2 = __floats2half2_rn(0.f, 0.f);
+            }
         }
+        if (F16) bad = bad || f16_range_bad(fmaxf(__low2float(amax2), __high2float(amax2)));
         if (F16 && bad && ep.f16_flag) *ep.f16_flag = 1;
+        if (probe && lane == 0) {
+            for (int q = 0; q < 5; ++q) atomicAdd(&x32t_probe[q], (unsigned long long)pc[q]);
+            atomicAdd(&x32t_probe[5], (unsigned long long)pn);
+            atomicAdd(&x32t_probe[6], (unsigned long long)(clock64() - pt0));
+        }
     } else {
         // ================= epilogue =================
         const int quarter = warp & 3, chalf = warp >> 2;

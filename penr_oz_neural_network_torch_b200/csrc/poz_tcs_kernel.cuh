@@ -58,6 +58,7 @@ struct Args {
     long long M;
     int N;
     long long K, k_per_split;
+    int a_dep;                    // A is written by an earlier launch of the same step: read it only after pdl_wait()
 };
 
 // Up to MAX_GROUP problems of one kind in one launch (the weight gradients of ALL layers of a narrow stack: same
@@ -144,6 +145,10 @@ tcs_gemm_kernel(const __grid_constant__ GroupArgs ga, const __grid_constant__ CU
     // half-block in tensor memory, accumulators complete, partial tiles exchanged, epilogue done
     fast::KernelTraceRec* ktr = fast::ktrace_open(A_T ? 201 : 200, (int)g.M, g.N, (int)g.K);
 
+    // Programmatic dependent launch (when the launch carries the attribute; no-ops otherwise): the next launch's CTAs may
+    // be scheduled as soon as every CTA of this one has got here, and this launch's own reads of what its predecessors
+    // wrote -- B's planes, and A where a_dep says so -- come after pdl_wait().
+    pdl_trigger();
     cg::cluster_group cluster = cg::this_cluster();
     const unsigned csize = cluster.num_blocks(), rank = cluster.block_rank();
     const int rows_per = BM / (int)csize;                                // rows of the tile this CTA finishes
@@ -167,6 +172,7 @@ tcs_gemm_kernel(const __grid_constant__ GroupArgs ga, const __grid_constant__ CU
     if (warp == CONV_WARPS) {
         // ================= TMA producer: every k-block of B's planes, up front =================
         if (tc::elect_one()) {
+            pdl_wait();
             for (int kb = 0; kb < nkb; ++kb) {
                 tc::mbar_expect_tx(&b_full[kb], B_KBLOCK);
 #pragma unroll
@@ -220,6 +226,7 @@ tcs_gemm_kernel(const __grid_constant__ GroupArgs ga, const __grid_constant__ CU
         const uint32_t ta0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + COL_A;
         const int nhb = 2 * nkb;
         float xa[32], xb[32];
+        if (g.a_dep) pdl_wait();
         if (grp < nhb) load_a<A_T>(g, m, k_beg + 32LL * grp, lane, xa);
         if (grp + 4 < nhb) load_a<A_T>(g, m, k_beg + 32LL * (grp + 4), lane, xb);
         auto convert_store = [&](const float (&x)[32], int hb) {

@@ -69,9 +69,10 @@ def run_child(env_extra):
 @pytest.mark.parametrize("env", [{"POZ_TCS": "0"}, {"POZ_TCS_FUSE_UPDATE": "0"}, {"POZ_TCS_GROUP": "1"},
                                  {"POZ_TCS_GROUP": "1", "POZ_TCS_FUSE_UPDATE": "0"}, {"POZ_TAIL": "0"},
                                  {"POZ_TAIL": "0", "POZ_TCS": "0"}, {"POZ_TAIL_GROUP": "0"},
-                                 {"POZ_TAIL_CLUSTER": "1"}, {"POZ_TAIL_CLUSTER": "2"}],
+                                 {"POZ_TAIL_CLUSTER": "1"}, {"POZ_TAIL_CLUSTER": "2"}, {"POZ_PDL": "0"}],
                          ids=["simt-layer0", "gradient-stored", "grouped", "grouped-stored", "separate-tail", "round-1-step",
-                              "tail-without-grouped-weight-gradients", "tail-without-cluster", "tail-cluster-of-2"])
+                              "tail-without-grouped-weight-gradients", "tail-without-cluster", "tail-cluster-of-2",
+                              "plain-edges-instead-of-programmatic-launches"])
 def test_small_batch_tensor_core_variants_match_the_oracle(env):
     """The default C2 step runs layer 0's forward and weight gradient as cluster split-K tcgen05 launches with the
     optimizer in the weight-gradient epilogue (csrc/poz_tcs_kernel.cuh).  The same three steps with that path off,

@@ -17,7 +17,8 @@
 // planes (B operand of the tensor-core weight-gradient launch, poz_tcs_kernel.cuh), and its eight rows' partial sums
 // of [dW2; db2] = [a1 1]^T dZ2 and of db1 = sum dZ1 -- tail_update_kernel adds the blocks' partials in a fixed order and
 // applies the optimizer to the head's parameters and to b1, so neither needs a GEMM launch of its own.
-// Not here (the step falls back to the separate kernels): dropout, recorded masks, diagnostics.
+// Dropout: the same Philox keys (or recorded masks) as the separate kernels; the hidden unit's two masks are kept in shared
+// memory for its backward.  Not here (the step falls back to the separate kernels): diagnostics.
 #pragma once
 #include "poz_kernels.cuh"
 #include "poz_tcs.h"
@@ -52,6 +53,10 @@ struct TailArgs {
     double* cost_base;
     long long cost_cap;
     const DevState* st;
+    // dropout points (neural_net_model.py:393-395), as in the separate kernels: on the linear output (z) and on the
+    // activation output (a) of the hidden unit, on the head's logits, and -- for the backward-x only -- of the unit before
+    DropPoint dz1p, da1p, dz2p, dz0p, da0p;
+    int any_drop;
 };
 
 // four adjacent values -> their bf16 planes hi / mid / lo, 8-byte stores where the pitch allows
@@ -133,10 +138,11 @@ __device__ __forceinline__ void tail_cp16(float* dst_smem, const float* src) {
 inline size_t tail_smem_bytes(int K1, int N1, int N2) {
     const size_t p1 = N1 + 4, pa = K1 + 4, pn = N1 + 4, p2 = (size_t)N2 | 1;
     const size_t red = (size_t)TAIL_ROWS * (TAIL_KSPLIT * (size_t)N1 > 4 * (size_t)K1 ? TAIL_KSPLIT * (size_t)N1 : 4 * (size_t)K1);
-    return (K1 * p1 + N1 + N1 * p2 + 32 + TAIL_ROWS * 32 + TAIL_ROWS * pa + 2 * TAIL_ROWS * pn + red) * sizeof(float);
+    return (K1 * p1 + N1 + N1 * p2 + 32 + TAIL_ROWS * 32 + TAIL_ROWS * pa + 2 * TAIL_ROWS * pn + red) * sizeof(float) +
+           2 * TAIL_ROWS * (size_t)N1;          // keep flags of the hidden unit's two dropout points
 }
 
-__global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a) {
+__global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(const __grid_constant__ TailArgs a) {
     extern __shared__ __align__(16) unsigned char tail_smem[];
     const int K1 = a.K1, N1 = a.N1, N2 = a.N2;
     const int P1 = N1 + 4, PA = K1 + 4, PN = N1 + 4, P2 = N2 | 1;
@@ -149,6 +155,9 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
     float* b2s = W2s + (size_t)N1 * P2;                      // [32]
     float* dz2s = b2s + 32;                                  // [8][32]
     float* red = dz2s + TAIL_ROWS * 32;                      // partial sums of the k-split groups: [8 splits][8][N1] / [4][8][K1]
+    const int red_elems = TAIL_ROWS * (TAIL_KSPLIT * N1 > 4 * K1 ? TAIL_KSPLIT * N1 : 4 * K1);
+    unsigned char* kz1 = reinterpret_cast<unsigned char*>(red + red_elems);   // [8][N1] keep flags: dropout on z1
+    unsigned char* ka1 = kz1 + TAIL_ROWS * N1;                                // [8][N1] ... on a1
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const long long m0 = (long long)blockIdx.x * TAIL_ROWS;
     // POZ_KERNEL_TRACE=1, tag 66: operands staged / hidden unit forward done / head done / backward-x done / exit
@@ -254,7 +263,17 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
                 float z = b1s[cc];
 #pragma unroll
                 for (int sidx = 0; sidx < TAIL_KSPLIT; ++sidx) z += red[((size_t)sidx * TAIL_ROWS + row) * N1 + cc];
-                const float v = act_fwd<float>(a.act1, z);
+                if (a.dz1p.enabled) {
+                    const bool keep = drop_keep(a.dz1p, a.st, m0 + row, cc, N1);
+                    kz1[row * N1 + cc] = keep;
+                    z = keep ? z * (float)a.dz1p.scale : 0.f;
+                }
+                float v = act_fwd<float>(a.act1, z);
+                if (a.da1p.enabled) {
+                    const bool keep = drop_keep(a.da1p, a.st, m0 + row, cc, N1);
+                    ka1[row * N1 + cc] = keep;
+                    v = keep ? v * (float)a.da1p.scale : 0.f;
+                }
                 a1s[row * PN + cc] = v;
                 if (m0 + row < a.M) a.a1_out[(m0 + row) * N1 + cc] = v;
             }
@@ -286,12 +305,18 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
         __syncthreads();
         float g = 0.f;
         if (mw < a.M) {
-            const float z = lane < N2 ? zs[hrow * 32 + lane] : -INFINITY;
+            float z = lane < N2 ? zs[hrow * 32 + lane] : -INFINITY;
+            bool keep2 = true;                                              // dropout on the logits (and back through it)
+            if (a.dz2p.enabled && lane < N2) {
+                keep2 = drop_keep(a.dz2p, a.st, mw, lane, N2);
+                z = keep2 ? z * (float)a.dz2p.scale : 0.f;
+            }
             const float mx = warp_max(z);
             const float e = lane < N2 ? expf(z - mx) : 0.f;
             const float ssum = warp_sum(e);
             const float pr = e / ssum;
             g = lane < N2 ? (pr - (lane == y ? 1.f : 0.f)) * (float)a.inv_batch : 0.f;
+            if (a.dz2p.enabled) g = keep2 ? g * (float)a.dz2p.scale : 0.f;
             const float zy = __shfl_sync(0xffffffffu, z, (y >= 0 && y < N2) ? y : 0);
             if (hhalf == 0) {
                 if (lane < N2) a.dz2_out[mw * N2 + lane] = g;
@@ -310,7 +335,16 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
             const int k = kb + 32 * j;
-            if (k < N1) dz1s[hrow * PN + k] = dd[j] * act_bwd_from_out<float>(a.act1, arow[k]);   // zero for rows past M
+            if (k < N1) {                                                    // (zero for rows past M)
+                float ga = dd[j], av = arow[k];
+                if (a.da1p.enabled) {
+                    ga = ka1[hrow * N1 + k] ? ga * (float)a.da1p.scale : 0.f;
+                    av = av * (float)a.da1p.keep_prob;
+                }
+                float gz = ga * act_bwd_from_out<float>(a.act1, av);
+                if (a.dz1p.enabled) gz = kz1[hrow * N1 + k] ? gz * (float)a.dz1p.scale : 0.f;
+                dz1s[hrow * PN + k] = gz;
+            }
         }
     }
     __syncthreads();
@@ -369,10 +403,27 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(TailArgs a)
             }
             const float4 o = *reinterpret_cast<const float4*>(a0s + r * PA + jj);
             float4 gz;
-            gz.x = sm.x * act_bwd_from_out<float>(a.act0, o.x);
-            gz.y = sm.y * act_bwd_from_out<float>(a.act0, o.y);
-            gz.z = sm.z * act_bwd_from_out<float>(a.act0, o.z);
-            gz.w = sm.w * act_bwd_from_out<float>(a.act0, o.w);
+            if (!a.any_drop) {
+                gz.x = sm.x * act_bwd_from_out<float>(a.act0, o.x);
+                gz.y = sm.y * act_bwd_from_out<float>(a.act0, o.y);
+                gz.z = sm.z * act_bwd_from_out<float>(a.act0, o.z);
+                gz.w = sm.w * act_bwd_from_out<float>(a.act0, o.w);
+            } else {
+                const float dv[4] = {sm.x, sm.y, sm.z, sm.w}, ov[4] = {o.x, o.y, o.z, o.w};
+                float gv[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float ga = dv[i], av = ov[i];
+                    if (a.da0p.enabled) {
+                        ga = drop_keep(a.da0p, a.st, m, jj + i, K1) ? ga * (float)a.da0p.scale : 0.f;
+                        av = av * (float)a.da0p.keep_prob;
+                    }
+                    float gq = ga * act_bwd_from_out<float>(a.act0, av);
+                    if (a.dz0p.enabled) gq = drop_keep(a.dz0p, a.st, m, jj + i, K1) ? gq * (float)a.dz0p.scale : 0.f;
+                    gv[i] = gq;
+                }
+                gz = make_float4(gv[0], gv[1], gv[2], gv[3]);
+            }
             *reinterpret_cast<float4*>(a.dz0_out + m * K1 + jj) = gz;
             if (a.dz0_planes) tail_store_planes4(gz, a.dz0_planes + m * a.dz0_ldp + jj, a.dz0_pstride, a.dz0_ldp);
         }

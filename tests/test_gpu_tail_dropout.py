@@ -1,0 +1,116 @@
+"""Dropout in the fused tail launch of the narrow train step (csrc/poz_tail_kernel.cuh): the reference applies
+F.dropout to every hidden entry's output (neural_net_model.py:393-395), i.e. on BASELINE.json configs[1] to relu0,
+linear1, relu1 and linear2 (the logits).
+
+* with recorded keep masks the step must give the oracle's numbers (same masks in oracle/mlp_oracle.py);
+* with the in-kernel Philox masks it must give what the separate kernels (POZ_TAIL=0) give for the same seed: the keys
+  (seed, epoch, point, element) are the same, only the summation order differs."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import mlp_oracle as orc
+from oracle.detgen import det_params, det_normalish, det_labels
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SIZES = [784, 256, 128, 10]
+ALGOS = ["linear", "relu", "linear", "relu", "linear", "softmax"]
+B = 1024
+P = 0.2
+
+
+def test_recorded_masks_through_the_tail_launch_match_the_oracle():
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    from test_gpu_parity import close, ADAM_PARAM_ATOL
+    params = det_params(SIZES, True, 177)
+    x = det_normalish((B, 784), 178)
+    y = det_labels(B, 10, 179)
+    rng = np.random.default_rng(5)
+    widths = {1: 256, 2: 128, 3: 128, 4: 10}                     # algos index of the hidden entries -> width
+    eng = DeviceMLP(SIZES, StackSpec.from_algos(ALGOS), True, "float32", 0)
+    for l in range(3):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    xd = torch.tensor(x, dtype=torch.float32, device="cuda:0")
+    yd = torch.tensor(y, dtype=torch.int32, device="cuda:0")
+    eng.train_begin(optimizer="adam", learning_rate=0.01, decay_rate=0.9, l2_lambda=0.001, dropout_rate=P, epochs=3)
+    stack = orc.parse_stack(ALGOS)
+    adam = orc.AdamState()
+    p, costs = params, []
+    tgt = [[int(v)] for v in y]
+    side = torch.cuda.Stream()
+    for step in range(3):
+        masks = {i: (rng.random((B, w)) >= P).astype(np.float64) for i, w in widths.items()}
+        dev = {i: torch.tensor(masks[i].astype(np.uint8), device="cuda:0").contiguous() for i in widths}   # slot 2l + {z: 0, a: 1} = algos index
+        with torch.cuda.stream(side):
+            eng.train_step(xd, yd, masks={i: dev.get(i) for i in range(6)})
+        side.synchronize()
+        p, c, *_ = orc.train_step(stack, p, x, tgt, lr=0.01 * 0.9 ** step, optimizer="adam", adam=adam, l2_lambda=0.001,
+                                  dropout_rate=P, masks=masks)
+        costs.append(c)
+    close(eng.costs(0, 3), costs, "float32", "costs")
+    for l in range(3):
+        w, b = eng.download_params(l)
+        close(w, p[2 * l], "float32", f"W{l}", atol=ADAM_PARAM_ATOL["float32"], outliers=True, loose_atol=0.02)
+        close(b, p[2 * l + 1], "float32", f"b{l}", atol=ADAM_PARAM_ATOL["float32"], outliers=True, loose_atol=0.02)
+    eng.close()
+
+
+CHILD = r'''
+import sys
+sys.path.insert(0, sys.argv[1])
+import numpy as np, torch
+from oracle.detgen import det_params, det_normalish, det_labels
+from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+sizes = [784, 256, 128, 10]
+algos = ["linear", "relu", "linear", "relu", "linear", "softmax"]
+B = 1024
+params = det_params(sizes, True, 277)
+x = det_normalish((B, 784), 278)
+y = det_labels(B, 10, 279)
+eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+for l in range(3):
+    eng.upload_params(l, params[2 * l], params[2 * l + 1])
+xd = torch.tensor(x, dtype=torch.float32, device="cuda:0")
+yd = torch.tensor(y, dtype=torch.int32, device="cuda:0")
+eng.train_begin(optimizer="adam", learning_rate=0.01, decay_rate=0.9, l2_lambda=0.001, dropout_rate=0.2, dropout_seed=4321, epochs=6)
+side = torch.cuda.Stream()
+with torch.cuda.stream(side):          # a non-default stream: eager, captured, then replayed steps
+    for _ in range(6):
+        eng.train_step(xd, yd)
+torch.cuda.synchronize()
+out = {"costs": np.asarray(eng.costs(0, 6))}
+for l in range(3):
+    w, b = eng.download_params(l)
+    out[f"w{l}"] = w; out[f"b{l}"] = b
+np.savez(sys.argv[2], **out)
+print("CHILD-OK")
+'''
+
+
+def _run(env_extra, path):
+    env = dict(os.environ)
+    env.update(env_extra)
+    r = subprocess.run([sys.executable, "-c", CHILD, ROOT, path], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "CHILD-OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+    return dict(np.load(path))
+
+
+def test_philox_dropout_same_through_the_tail_launch_and_the_separate_kernels(tmp_path):
+    a = _run({}, str(tmp_path / "tail.npz"))
+    b = _run({"POZ_TAIL": "0"}, str(tmp_path / "separate.npz"))
+    assert np.isfinite(a["costs"]).all()
+    np.testing.assert_allclose(a["costs"], b["costs"], rtol=2e-6)
+    for k in a:
+        if k == "costs":
+            continue
+        # six Adam steps: identical masks, fp32 sums in another order; an element whose relu flips on a rounding may differ
+        diff = np.abs(a[k] - b[k])
+        tol = 1e-5 * np.abs(b[k]).max() + 1e-5 * np.abs(b[k])
+        assert (diff > tol).mean() < 2e-3, (k, float(diff.max()), float((diff > tol).mean()))
+        assert diff.max() < 0.02 * np.abs(b[k]).max() + 1e-3, (k, float(diff.max()))

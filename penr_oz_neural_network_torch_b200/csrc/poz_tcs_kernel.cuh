@@ -278,6 +278,7 @@ tcs_gemm_kernel(const __grid_constant__ GroupArgs ga, const __grid_constant__ CU
     // ================= one cluster barrier: every partial row has arrived where it is finished =================
     tc::tc_fence_before();
     cluster.sync();
+    pdl_wait();      // the epilogue may read the step state that the launch before wrote (dropout keys)
     if (ktr) ktr->t[4] = fast::ktrace_now();
     if (warp < CONV_WARPS) {
         // 512 threads, rows_per x 16 four-wide pieces: piece i of this thread is its prefetch slot i

@@ -62,9 +62,13 @@ TC3_MMAS_PER_PRODUCT = 6
 NCU_TRAFFIC = {"fwd_l0": 4_344_064, "bwd_w_l0": 4_307_712, "fwd_l1": 1_508_608, "bwd_w_l1": 1_620_736,
                "bwd_w_l2": 613_376, "bwd_x_l1": 1_769_728, "tc_fwd": 1_204_000_000,
                # r02: ncu --set full of the cluster split-K tcgen05 launches (profiles/r02/ncu_tcs_raw_v1.csv)
-               "tcs_fwd_l0": 4_497_664, "tcs_bwd_w_l0_update": 7_271_680}
-NCU_TRAFFIC_SOURCES = {"tcs_fwd_l0": "ncu --set full, profiles/r02/ncu_tcs_raw_v1.csv",
-                       "tcs_bwd_w_l0_update": "ncu --set full, profiles/r02/ncu_tcs_raw_v1.csv"}
+               "tcs_fwd_l0": 4_477_952, "tcs_bwd_w_l0_update": 7_271_680,
+               # final step of round 2 (profiles/r02/ncu_c2_final_raw_v1.csv; writes stay in the L2 within the capture)
+               "tail": 1_249_792, "tcs_bwd_w_l0_l1_update": 9_495_552}
+NCU_TRAFFIC_SOURCES = {"tcs_fwd_l0": "ncu --set full, profiles/r02/ncu_c2_final_raw_v1.csv",
+                       "tcs_bwd_w_l0_update": "ncu --set full, profiles/r02/ncu_tcs_raw_v1.csv",
+                       "tail": "ncu --set full, profiles/r02/ncu_c2_final_raw_v1.csv",
+                       "tcs_bwd_w_l0_l1_update": "ncu --set full, profiles/r02/ncu_c2_final_raw_v1.csv"}
 
 
 def peaks():

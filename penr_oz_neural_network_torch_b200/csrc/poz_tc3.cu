@@ -222,7 +222,7 @@ template <bool A_T, class Epi> static int launch(const Gemm* gs, const Epi* epis
         POZ_TRY(tc3::make_map3(&maps[i], g.b, 64, 64));
         Args& a = ga.a[i];
         a.a = g.a; a.lda = g.lda; a.row_idx = g.row_idx; a.a_cols = g.a_cols; a.ones_row = g.ones_row;
-        a.M = g.M; a.N = g.N; a.K = g.K; a.a_dep = g.a_dep;
+        a.M = g.M; a.N = g.N; a.K = g.K; a.a_dep = g.a_dep; a.b_dep = g.b_dep;
         a.k_per_split = ((nkb + splits - 1) / splits) * BK;
         ga.tiles_n[i] = (g.N + BN - 1) / BN;
         tiles += ((g.M + BM - 1) / BM) * ga.tiles_n[i];

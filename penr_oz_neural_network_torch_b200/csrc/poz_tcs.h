@@ -28,7 +28,7 @@ struct Gemm {
     long long K;
     tc3::PlaneMat b;
     int splits;                            // 1, 2, 4 or 8; ceil(ceil(K / 64) / splits) <= MAX_KB
-    int a_dep = 0;                         // a is written by an earlier launch of the same step (see pdl below)
+    int a_dep = 0, b_dep = 0;              // a / b are written by an earlier launch of the same step (see pdl below)
     int pdl = 0;                           // (first problem of a launch) launch with programmatic stream serialization: the CTAs
                                            // may start while the launch before is finishing; they wait before reading its results
 };

@@ -58,7 +58,7 @@ struct Args {
     long long M;
     int N;
     long long K, k_per_split;
-    int a_dep;                    // A is written by an earlier launch of the same step: read it only after pdl_wait()
+    int a_dep, b_dep;             // A / B's planes are written by an earlier launch of the same step: read only after pdl_wait()
 };
 
 // Up to MAX_GROUP problems of one kind in one launch (the weight gradients of ALL layers of a narrow stack: same
@@ -172,7 +172,7 @@ tcs_gemm_kernel(const __grid_constant__ GroupArgs ga, const __grid_constant__ CU
     if (warp == CONV_WARPS) {
         // ================= TMA producer: every k-block of B's planes, up front =================
         if (tc::elect_one()) {
-            pdl_wait();
+            if (g.b_dep) pdl_wait();
             for (int kb = 0; kb < nkb; ++kb) {
                 tc::mbar_expect_tx(&b_full[kb], B_KBLOCK);
 #pragma unroll

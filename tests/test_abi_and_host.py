@@ -148,3 +148,19 @@ def test_missing_model_is_key_error_and_delete_is_silent(workdir):
     NeuralNetworkModel.delete("test")
     with pytest.raises(KeyError):
         NeuralNetworkModel.deserialize("test")
+
+
+def test_randint_hands_out_the_same_indices_in_one_call_or_many():
+    """NeuralNetworkModel.train() draws the row indices of up to 16 epochs in one torch.randint call (the reference draws
+    them epoch by epoch from the same global generator, neural_net_model.py:460): the numbers, and the generator's state
+    afterwards, must not depend on how the draws are grouped."""
+    import torch
+    for batch, epochs, n in [(1024, 16, 2048), (5, 7, 9), (201, 3, 201), (180, 16, 1 << 20)]:
+        torch.manual_seed(1234)
+        one_by_one = torch.cat([torch.randint(0, n, (batch,)) for _ in range(epochs)])
+        after_a = torch.randint(0, 1 << 30, (4,))
+        torch.manual_seed(1234)
+        at_once = torch.randint(0, n, (epochs * batch,))
+        after_b = torch.randint(0, 1 << 30, (4,))
+        assert torch.equal(one_by_one, at_once)
+        assert torch.equal(after_a, after_b)

@@ -732,15 +732,14 @@ class NeuralNetworkModel(MultiLayerPerceptron):
             layer.training = True
         # The indices of K epochs are drawn in ONE torch.randint call -- the generator hands out the same numbers
         # whether asked for K x batch at once or batch at a time (tests/test_abi_and_host.py pins that), so the sampled
-        # rows are exactly the reference's (:460) -- and uploaded in one asynchronous copy: per epoch the host then only
-        # launches the step.  Three device blocks and three pinned staging blocks rotate; every epoch's slice has a
-        # fixed device address, so the library replays its step from a CUDA graph once it has seen the slice twice.
+        # rows are exactly the reference's (:460) -- and converted into a pinned staging block; per epoch the host then
+        # only issues one small asynchronous copy into the ONE device index buffer (a fixed address: the library replays
+        # the step from a single CUDA graph after the second epoch) and launches the step.
         m_local = hi - lo
         K = max(1, min(16, epochs))
-        n_blocks = 3
-        idx_dev = torch.empty((n_blocks, K, m_local), dtype=torch.int32, device=eng.device)
-        ring = [torch.empty((K, m_local), dtype=torch.int32).pin_memory() for _ in range(n_blocks)]
-        ring_done = [None] * n_blocks
+        idx_d = torch.empty((m_local,), dtype=torch.int32, device=eng.device)
+        ring = [torch.empty((K, m_local), dtype=torch.int32).pin_memory() for _ in range(3)]
+        ring_done = [None] * len(ring)
         stamps = []
         fetched = 0
         last_serialized = time.time()
@@ -752,17 +751,17 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         with torch.cuda.stream(side):
             for epoch in range(epochs):
                 j = epoch % K
-                blk = (epoch // K) % n_blocks
+                blk = (epoch // K) % len(ring)
                 if j == 0:
                     k_now = min(K, epochs - epoch)
                     idx = torch.randint(0, n_data, (k_now * sample_size,)).view(k_now, sample_size)   # :460, same generator
                     if ring_done[blk] is not None:
-                        ring_done[blk].synchronize()                            # its upload of three blocks ago
+                        ring_done[blk].synchronize()                            # the copies out of this block, three blocks ago
                     ring[blk][:k_now].copy_(idx[:, lo:hi])                       # this rank's share (all of it on one GPU)
-                    idx_dev[blk].copy_(ring[blk], non_blocking=True)             # (ordered behind the steps that read the block)
+                idx_d.copy_(ring[blk][j], non_blocking=True)
+                if j == K - 1 or epoch + 1 == epochs:
                     ring_done[blk] = torch.cuda.Event()
                     ring_done[blk].record(side)
-                idx_d = idx_dev[blk, j]
                 if self.optimizer is not None:                                  # :467-469 (view only)
                     for group in self.optimizer.param_groups:
                         group["lr"] = learning_rate * (decay_rate ** epoch)

@@ -769,9 +769,11 @@ int poz_ctx_destroy(poz_ctx* c) {
     for (int i = 0; i < poz_ctx::HostFeed::SLOTS; ++i) {
         dev_free(c->feed.x[i]); dev_free(c->feed.t[i]);
         if (c->feed.copied[i]) cudaEventDestroy(c->feed.copied[i]);
+        if (c->feed.copied_t[i]) cudaEventDestroy(c->feed.copied_t[i]);
         if (c->feed.consumed[i]) cudaEventDestroy(c->feed.consumed[i]);
     }
     if (c->feed.copy_stream) cudaStreamDestroy(c->feed.copy_stream);
+    if (c->feed.t_stream) cudaStreamDestroy(c->feed.t_stream);
     if (c->feed.read_stream) cudaStreamDestroy(c->feed.read_stream);
     if (c->feed.cost_pinned) cudaFreeHost(c->feed.cost_pinned);
     if (getenv("POZ_KERNEL_TRACE") && atoi(getenv("POZ_KERNEL_TRACE")) != 0) { dump_kernel_trace(); tcs::trace_dump(); }

@@ -134,9 +134,9 @@ struct poz_ctx {
         static constexpr int SLOTS = POZ_HOST_LAG + 1;
         void* x[SLOTS] = {};
         void* t[SLOTS] = {};
-        cudaEvent_t copied[SLOTS] = {}, consumed[SLOTS] = {};
+        cudaEvent_t copied[SLOTS] = {}, copied_t[SLOTS] = {}, consumed[SLOTS] = {};
         long long epoch_of[SLOTS] = {};   // epoch index of the step that last used the slot
-        cudaStream_t copy_stream = nullptr, read_stream = nullptr;
+        cudaStream_t copy_stream = nullptr, t_stream = nullptr, read_stream = nullptr;   // inputs, targets, cost read-back
         double* cost_pinned = nullptr;
         long long batch = 0;           // capacity of the slots
         long long calls = 0;           // host steps since the last flush / poz_train_begin

@@ -104,12 +104,12 @@ __device__ __noinline__ static float act_fwd_slow(int act, float z) {
     return act == ACT_SIGMOID ? 1.f / (1.f + expf(-z)) : tanhf(z);
 }
 template <typename T> __device__ __forceinline__ T act_fwd(int act, T z) {
-    if (act == ACT_RELU) return z > T(0) ? z : T(0);
+    if (act == ACT_RELU) return z < T(0) ? T(0) : z;   // a NaN stays a NaN, as in torch.relu
     if (act == ACT_SIGMOID || act == ACT_TANH) return act_fwd_slow(act, z);
     return z;
 }
 template <> __device__ __forceinline__ float act_fwd<float>(int act, float z) {
-    if (act == ACT_RELU) return fmaxf(z, 0.f);
+    if (act == ACT_RELU) return z < 0.f ? 0.f : z;      // (not fmaxf: a NaN must stay a NaN, as in torch.relu)
     if (act == ACT_SIGMOID || act == ACT_TANH) return act_fwd_slow(act, z);
     return z;
 }

@@ -51,7 +51,7 @@ __device__ __forceinline__ void epilogue_tile(const Epi3& ep, long long M, int N
                 }
                 if (ep.act == ACT_RELU) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+                    for (int j = 0; j < 32; ++j) f[j] = f[j] < 0.f ? 0.f : f[j];     // (keeps a NaN a NaN, as torch.relu does)
                 } else if (ep.act != ACT_NONE && ep.act != ACT_SOFTMAX) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) f[j] = act_fwd<float>(ep.act, f[j]);

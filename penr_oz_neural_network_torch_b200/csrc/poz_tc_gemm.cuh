@@ -346,7 +346,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             }
                             if (ep.act == ACT_RELU) {
 #pragma unroll
-                                for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+                                for (int j = 0; j < 32; ++j) f[j] = f[j] < 0.f ? 0.f : f[j];   // (keeps a NaN a NaN)
                             } else if (ep.act != ACT_NONE) {
 #pragma unroll
                                 for (int j = 0; j < 32; ++j) f[j] = act_fwd<float>(ep.act, f[j]);

@@ -566,3 +566,24 @@ def test_host_buffer_steps_equal_device_buffer_steps():
         runs.append((got, eng.costs(0, 5), [eng.download_params(l) for l in range(2)]))
     np.testing.assert_allclose(runs[0][0], runs[1][0], rtol=1e-12)
     np.testing.assert_allclose(runs[0][1], runs[1][1], rtol=1e-12)
+
+
+@pytest.mark.parametrize("batch", [3, 300, 4096 + 5])
+def test_a_nan_input_row_gives_a_nan_output_row_as_in_the_reference(batch):
+    """torch.relu keeps a NaN (neural_net_model.py:179): a row with a NaN in it comes out all NaN -- through the few-row
+    cluster launch, the SIMT kernels and the tensor-core kernels alike -- and the other rows are untouched."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    sizes, algos = mnist_stack()
+    params = det_params(sizes, True, 5)
+    eng = DeviceMLP(sizes, StackSpec.from_algos(algos), True, "float32", 0)
+    for l in range(3):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    x = det_normalish((batch, 784), 61)
+    bad = batch // 2
+    x[bad, 17] = np.nan
+    out = eng.forward(torch.tensor(x, dtype=torch.float32, device="cuda:0")).cpu().numpy()
+    ref = orc.forward(orc.parse_stack(algos), params, x)[0][-1].reshape(batch, -1)
+    assert np.isnan(ref[bad]).all() and np.isnan(out[bad]).all()
+    ok = np.arange(batch) != bad
+    close(out[ok], ref[ok], "float32", "probs", rtol=1e-4)
+    eng.close()

@@ -271,6 +271,8 @@ def run_c2(args, world, rank, local):
     costs = eng.costs(pre + args.warmup, args.steps)
     assert np.isfinite(costs).all(), "non-finite training cost"
 
+    torch.cuda.synchronize()
+    phase("c2: timed region done; dropout variant")
     # ---- the same step with the reference's default dropout (0.2, neural_net_model.py:410): Philox masks in the
     # epilogues, regenerated in the backward.  Reported beside the headline (which is measured at 0.0, the
     # setting the parity tests pin).
@@ -336,6 +338,8 @@ def run_c2(args, world, rank, local):
     h2d_us = c0.elapsed_time(c1) * 1e3 / 20
     clocks = sampler.stop() if sampler else None
 
+    torch.cuda.synchronize()
+    phase("c2: host-buffer regions done; class API")
     # ---- the drop-in class itself: NeuralNetworkModel.train() per epoch (index sampling on the host as in the
     # reference, row gather on the device); the one-off ingestion of the Python lists is removed by differencing
     class_api = None
@@ -369,6 +373,8 @@ def run_c2(args, world, rank, local):
         finally:
             os.chdir(cwd)
 
+    torch.cuda.synchronize()
+    phase("c2: class API done; per-kernel timing")
     # ---- per-kernel timing pass (CUDA events inside the library, on the launching stream) -----------
     roof = None
     if rank == 0:
@@ -1199,6 +1205,11 @@ def native_config(args, world):
             "l2_flush": "native arm: inputs are 0.5 MB per step; the step is bound by ~90 MB of activation traffic that stays in L2"}
 
 
+def phase(name):
+    """progress marker on stderr: a failure inside a kernel surfaces at some later call, this says how far the run got"""
+    print(f"[bench] {name}", file=sys.stderr, flush=True)
+
+
 def secondary_lines(args, local):
     """configs[2] and configs[3] of BASELINE.json in the same run as the headline (one GPU): batched inference at
     262,144 rows and the 4096x4 bf16 train step at batch 65,536, each with its own roofline, clocks and e2e."""
@@ -1209,6 +1220,7 @@ def secondary_lines(args, local):
         a = copy.copy(args)
         a.steps, a.warmup, a.batch, a.workload = steps, 3, 0, name
         try:
+            phase(f"secondary {name}")
             torch.cuda.set_stream(torch.cuda.default_stream())
             r = fn(a)
             out[name] = {k: r[k] for k in ("metric", "unit", "value", "ms_per_step", "e2e", "gpu_launches", "roofline",
@@ -1217,6 +1229,8 @@ def secondary_lines(args, local):
             out[name].update(r.get("extras") or {})
             out[name]["steps"], out[name]["warmup"] = steps, 3
         except Exception as e:
+            if "CUDA" in str(e) or "launch failure" in str(e):
+                raise                       # a sticky device error: nothing measured after it would mean anything
             out[name] = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
         torch.cuda.synchronize()
         torch.cuda.empty_cache()
@@ -1234,6 +1248,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-class-api", action="store_true", help="skip the list-level NeuralNetworkModel.train() timings")
     ap.add_argument("--no-secondary", action="store_true", help="c2 only: skip the c3 / c4 lines under 'secondary'")
+    ap.add_argument("--in-child", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     args.workload, why = pick_workload(args)
@@ -1258,7 +1273,10 @@ def main():
     elif args.workload in ("c4", "c5"):
         res = run_wide(args, world, rank, local, dp=args.workload == "c5")
     else:
+        phase(f"workload {args.workload}")
         res = (run_c2 if args.workload == "c2" else run_c3)(args, world, rank, local)
+        torch.cuda.synchronize()
+        phase(f"workload {args.workload} done")
     if rank == 0:
         secondary = None
         if args.workload == "c2" and world == 1 and not args.no_secondary:
@@ -1317,5 +1335,37 @@ def main():
         dist.destroy_process_group()
 
 
+def supervised():
+    """One process on one box, native arm: the measurement runs in a child process and is repeated once if the child dies.
+    (One `python bench.py` in 27 of round 2 ended in "unspecified launch failure", a sticky CUDA error nothing in the
+    process survives; 13 repeats, a 10-run loop and 800,000 stress steps did not reproduce it.  The line says how many
+    attempts it took.)  Ranks of a torch.distributed.run launch, the reference arm and the child itself run main() directly."""
+    import subprocess
+    argv = sys.argv[1:]
+    if "--in-child" in argv or "RANK" in os.environ or "--impl" in argv and "reference" in argv:
+        return main()
+    try:                                   # this process also loads the library (nothing of CUDA is touched here)
+        from penr_oz_neural_network_torch_b200 import _native
+        _native.lib()
+    except Exception as e:                 # the child will say why in full
+        print(f"[bench] parent could not load the library: {e}", file=sys.stderr, flush=True)
+    rc = 1
+    for attempt in (1, 2):
+        proc = subprocess.run([sys.executable, os.path.abspath(__file__)] + argv + ["--in-child"], stdout=subprocess.PIPE, text=True)
+        rc = proc.returncode
+        lines = [ln for ln in proc.stdout.splitlines() if ln.startswith("{")]
+        if rc == 0 and lines:
+            try:
+                line = json.loads(lines[-1])
+                line["attempts"] = attempt
+                print(json.dumps(line), flush=True)
+            except Exception:
+                print(lines[-1], flush=True)
+            return
+        print(f"[bench] attempt {attempt} ended with exit code {rc}" + ("; repeating once" if attempt == 1 else ""),
+              file=sys.stderr, flush=True)
+    raise SystemExit(rc or 1)
+
+
 if __name__ == "__main__":
-    main()
+    supervised()

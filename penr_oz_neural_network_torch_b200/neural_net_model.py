@@ -732,12 +732,13 @@ class NeuralNetworkModel(MultiLayerPerceptron):
             layer.training = True
         # The indices of K epochs are drawn in ONE torch.randint call -- the generator hands out the same numbers
         # whether asked for K x batch at once or batch at a time (tests/test_abi_and_host.py pins that), so the sampled
-        # rows are exactly the reference's (:460) -- and converted into a pinned staging block; per epoch the host then
-        # only issues one small asynchronous copy into the ONE device index buffer (a fixed address: the library replays
-        # the step from a single CUDA graph after the second epoch) and launches the step.
+        # rows are exactly the reference's (:460) -- and converted into a pinned staging block.  Per epoch the host then
+        # issues one small asynchronous copy, on a copy stream, into one of TWO device index buffers (fixed addresses:
+        # the library replays the step from two CUDA graphs) -- the copy for epoch e + 1 runs under the step of epoch e --
+        # and launches the step.
         m_local = hi - lo
         K = max(1, min(16, epochs))
-        idx_d = torch.empty((m_local,), dtype=torch.int32, device=eng.device)
+        idx_bufs = [torch.empty((m_local,), dtype=torch.int32, device=eng.device) for _ in range(2)]
         ring = [torch.empty((K, m_local), dtype=torch.int32).pin_memory() for _ in range(3)]
         ring_done = [None] * len(ring)
         stamps = []
@@ -747,6 +748,9 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         # stream does not allow
         side = torch.cuda.Stream(device=eng.device)
         side.wait_stream(torch.cuda.current_stream(eng.device))
+        copier = torch.cuda.Stream(device=eng.device)
+        copied = [torch.cuda.Event() for _ in idx_bufs]
+        consumed = [None for _ in idx_bufs]
         loop_started = time.perf_counter()
         with torch.cuda.stream(side):
             for epoch in range(epochs):
@@ -758,10 +762,17 @@ class NeuralNetworkModel(MultiLayerPerceptron):
                     if ring_done[blk] is not None:
                         ring_done[blk].synchronize()                            # the copies out of this block, three blocks ago
                     ring[blk][:k_now].copy_(idx[:, lo:hi])                       # this rank's share (all of it on one GPU)
-                idx_d.copy_(ring[blk][j], non_blocking=True)
-                if j == K - 1 or epoch + 1 == epochs:
-                    ring_done[blk] = torch.cuda.Event()
-                    ring_done[blk].record(side)
+                buf = epoch & 1
+                idx_d = idx_bufs[buf]
+                with torch.cuda.stream(copier):
+                    if consumed[buf] is not None:
+                        copier.wait_event(consumed[buf])                        # the step of two epochs ago has read this buffer
+                    idx_d.copy_(ring[blk][j], non_blocking=True)
+                    copied[buf].record(copier)
+                    if j == K - 1 or epoch + 1 == epochs:
+                        ring_done[blk] = torch.cuda.Event()
+                        ring_done[blk].record(copier)
+                side.wait_event(copied[buf])
                 if self.optimizer is not None:                                  # :467-469 (view only)
                     for group in self.optimizer.param_groups:
                         group["lr"] = learning_rate * (decay_rate ** epoch)
@@ -771,6 +782,9 @@ class NeuralNetworkModel(MultiLayerPerceptron):
                     dp.train_step(x_all, t_all, row_idx_local=idx_d, diagnostics=diagnostics)
                 else:
                     eng.train_step(x_all, t_all, row_idx=idx_d, diagnostics=diagnostics)
+                if consumed[buf] is None:
+                    consumed[buf] = torch.cuda.Event()
+                consumed[buf].record(side)
                 stamps.append(dt.now().isoformat())
                 if long_training:  # pragma: no cover
                     fetched = self._collect_progress(eng, stamps, fetched, epoch + 1, stride)

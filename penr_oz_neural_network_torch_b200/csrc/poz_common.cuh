@@ -59,8 +59,9 @@ struct DevState {
 };
 
 // ---- Philox4x32-10 (counter-based RNG for in-kernel dropout) -------------------------------------
-__device__ __forceinline__ uint32_t philox_first(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                                 uint32_t k0, uint32_t k1) {
+// One evaluation yields four 32-bit words: element e of a dropout point takes word e & 3 of the block with counter e >> 2,
+// so an epilogue that holds four consecutive elements pays for one evaluation, not four.
+__device__ __forceinline__ uint4 philox4(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
     const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
@@ -70,7 +71,7 @@ __device__ __forceinline__ uint32_t philox_first(uint32_t c0, uint32_t c1, uint3
         c0 = n0; c1 = n1; c2 = n2; c3 = n3;
         k0 += W0; k1 += W1;
     }
-    return c0;
+    return make_uint4(c0, c1, c2, c3);
 }
 
 // One dropout point (the output of one hidden entry).  keep(m, n) is a pure function of
@@ -86,13 +87,32 @@ struct DropPoint {
 // Out of line on purpose: the step's kernels are launch-bound and start with a cold instruction cache, and a
 // Philox evaluation inlined at every epilogue call site (x 4 elements x 2 points) made each of them tens of
 // kilobytes of code that a step without dropout fetches around.  A call keeps the common path compact.
+__device__ __noinline__ static uint4 drop_block(const DropPoint& d, const DevState* st, long long q) {
+    return philox4((uint32_t)q, (uint32_t)(q >> 32), d.point, (uint32_t)st->cur_epoch, (uint32_t)st->seed,
+                   (uint32_t)(st->seed >> 32));
+}
+__device__ __forceinline__ bool drop_word_keeps(const DropPoint& d, uint32_t r) {
+    return (r * 2.3283064365386963e-10f) < (float)d.keep_prob;
+}
 __device__ __noinline__ static bool drop_keep(const DropPoint& d, const DevState* st, long long m,
                                               int n, int ld) {
     long long e = m * (long long)ld + n;
     if (d.mask) return d.mask[e] != 0;
-    uint32_t r = philox_first((uint32_t)e, (uint32_t)(e >> 32), d.point, (uint32_t)st->cur_epoch,
-                              (uint32_t)st->seed, (uint32_t)(st->seed >> 32));
-    return (r * 2.3283064365386963e-10f) < (float)d.keep_prob;
+    const uint4 b = drop_block(d, st, e >> 2);
+    const int w = (int)(e & 3);
+    return drop_word_keeps(d, w == 0 ? b.x : w == 1 ? b.y : w == 2 ? b.z : b.w);
+}
+// the same for four consecutive elements (m, n .. n + 3): one Philox evaluation when they are one aligned block
+__device__ __forceinline__ void drop_keep4(const DropPoint& d, const DevState* st, long long m, int n, int ld, bool (&keep)[4]) {
+    const long long e = m * (long long)ld + n;
+    if (!d.mask && (e & 3) == 0) {
+        const uint4 b = drop_block(d, st, e >> 2);
+        keep[0] = drop_word_keeps(d, b.x); keep[1] = drop_word_keeps(d, b.y);
+        keep[2] = drop_word_keeps(d, b.z); keep[3] = drop_word_keeps(d, b.w);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) keep[j] = drop_keep(d, st, m, n + j, ld);
+    }
 }
 
 // ---- activations (neural_net_model.py:172-188) and their derivatives from the OUTPUT value -------

@@ -196,6 +196,25 @@ __device__ __forceinline__ void store_row(T* p, const T (&v)[TN], int nvalid) {
 
 // ---- epilogues --------------------------------------------------------------------------------
 
+// keep flags of TN consecutive elements of one dropout point (all true when the point is off): one Philox evaluation
+// for an aligned group of four (poz_common.cuh)
+template <int TN>
+__device__ __forceinline__ void drop_flags(const DropPoint& d, const DevState* st, long long m, int n, int ld, int nvalid,
+                                           bool (&keep)[TN]) {
+#pragma unroll
+    for (int j = 0; j < TN; ++j) keep[j] = true;
+    if (!d.enabled) return;
+    if constexpr (TN == 4) {
+        if (nvalid == 4) {
+            drop_keep4(d, st, m, n, ld, keep);
+            return;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < TN; ++j)
+        if (j < nvalid) keep[j] = drop_keep(d, st, m, n + j, ld);
+}
+
 // forward: dropout on z, activation, dropout on a (neural_net_model.py:117-119,172-188,393-395)
 template <typename T> struct FwdEpi {
     T* z_out;          // recorded (post-dropout) linear output, nullable
@@ -207,13 +226,16 @@ template <typename T> struct FwdEpi {
     template <int TN>
     __device__ __forceinline__ void row(long long m, int n, const T (&acc)[TN], int nvalid, int) const {
         T z[TN], a[TN];
+        bool kz[TN], ka[TN];
+        drop_flags<TN>(dz, st, m, n, ld, nvalid, kz);
+        drop_flags<TN>(da, st, m, n, ld, nvalid, ka);
 #pragma unroll
         for (int j = 0; j < TN; ++j) {
             T v = acc[j];
-            if (dz.enabled && j < nvalid) v = drop_keep(dz, st, m, n + j, ld) ? v * T(dz.scale) : T(0);
+            if (dz.enabled && j < nvalid) v = kz[j] ? v * T(dz.scale) : T(0);
             z[j] = v;
             T w = act_fwd<T>(act, v);
-            if (da.enabled && j < nvalid) w = drop_keep(da, st, m, n + j, ld) ? w * T(da.scale) : T(0);
+            if (da.enabled && j < nvalid) w = ka[j] ? w * T(da.scale) : T(0);
             a[j] = w;
         }
         if (z_out) store_row<T, TN>(z_out + m * ld + n, z, nvalid);
@@ -240,6 +262,9 @@ template <typename T> struct BwdDataEpi {
     template <int TN>
     __device__ __forceinline__ void row(long long m, int n, const T (&acc)[TN], int nvalid, int) const {
         T g0[TN], g1[TN], g2[TN];
+        bool kz[TN], ka[TN];
+        drop_flags<TN>(dz, st, m, n, ld, nvalid, kz);
+        drop_flags<TN>(da, st, m, n, ld, nvalid, ka);
 #pragma unroll
         for (int j = 0; j < TN; ++j) {
             T g = acc[j];
@@ -249,14 +274,13 @@ template <typename T> struct BwdDataEpi {
                 T ga = g;
                 T a = a_prev[m * ld + n + j];
                 if (da.enabled) {
-                    bool keep = drop_keep(da, st, m, n + j, ld);
-                    ga = keep ? g * T(da.scale) : T(0);
+                    ga = ka[j] ? g * T(da.scale) : T(0);
                     a = a * T(da.keep_prob);
                 }
                 gz = ga * act_bwd_from_out<T>(act, a);
             }
             g1[j] = gz;
-            if (dz.enabled && j < nvalid) gz = drop_keep(dz, st, m, n + j, ld) ? gz * T(dz.scale) : T(0);
+            if (dz.enabled && j < nvalid) gz = kz[j] ? gz * T(dz.scale) : T(0);
             g2[j] = gz;
         }
         if (da_rec) store_row<T, TN>(da_rec + m * ld + n, g0, nvalid);

@@ -255,27 +255,33 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(const __gri
                     make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
         }
         __syncthreads();
-        const int cc = t & 127;                                             // 4 rows x 128 columns per pass
-        if (cc < N1) {
+        if (t < TAIL_ROWS * 32) {                                           // 8 rows x (up to) 32 groups of four columns
+            const int row = t >> 5, c4 = (t & 31) * 4;
+            if (c4 < N1) {
+                float4 z4 = *reinterpret_cast<const float4*>(b1s + c4);
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                const int row = (t >> 7) + 4 * q;
-                float z = b1s[cc];
-#pragma unroll
-                for (int sidx = 0; sidx < TAIL_KSPLIT; ++sidx) z += red[((size_t)sidx * TAIL_ROWS + row) * N1 + cc];
+                for (int sidx = 0; sidx < TAIL_KSPLIT; ++sidx) {
+                    const float4 pq = *reinterpret_cast<const float4*>(red + ((size_t)sidx * TAIL_ROWS + row) * N1 + c4);
+                    z4.x += pq.x; z4.y += pq.y; z4.z += pq.z; z4.w += pq.w;
+                }
+                float z[4] = {z4.x, z4.y, z4.z, z4.w}, v[4];
                 if (a.dz1p.enabled) {
-                    const bool keep = drop_keep(a.dz1p, a.st, m0 + row, cc, N1);
-                    kz1[row * N1 + cc] = keep;
-                    z = keep ? z * (float)a.dz1p.scale : 0.f;
+                    bool keep[4];
+                    drop_keep4(a.dz1p, a.st, m0 + row, c4, N1, keep);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { kz1[row * N1 + c4 + i] = keep[i]; z[i] = keep[i] ? z[i] * (float)a.dz1p.scale : 0.f; }
                 }
-                float v = act_fwd<float>(a.act1, z);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) v[i] = act_fwd<float>(a.act1, z[i]);
                 if (a.da1p.enabled) {
-                    const bool keep = drop_keep(a.da1p, a.st, m0 + row, cc, N1);
-                    ka1[row * N1 + cc] = keep;
-                    v = keep ? v * (float)a.da1p.scale : 0.f;
+                    bool keep[4];
+                    drop_keep4(a.da1p, a.st, m0 + row, c4, N1, keep);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { ka1[row * N1 + c4 + i] = keep[i]; v[i] = keep[i] ? v[i] * (float)a.da1p.scale : 0.f; }
                 }
-                a1s[row * PN + cc] = v;
-                if (m0 + row < a.M) a.a1_out[(m0 + row) * N1 + cc] = v;
+                const float4 v4 = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4*>(a1s + row * PN + c4) = v4;
+                if (m0 + row < a.M) *reinterpret_cast<float4*>(a.a1_out + (m0 + row) * N1 + c4) = v4;
             }
         }
     }
@@ -411,15 +417,18 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tail_fused_kernel(const __gri
             } else {
                 const float dv[4] = {sm.x, sm.y, sm.z, sm.w}, ov[4] = {o.x, o.y, o.z, o.w};
                 float gv[4];
+                bool ka0[4] = {true, true, true, true}, kz0[4] = {true, true, true, true};
+                if (a.da0p.enabled) drop_keep4(a.da0p, a.st, m, jj, K1, ka0);
+                if (a.dz0p.enabled) drop_keep4(a.dz0p, a.st, m, jj, K1, kz0);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     float ga = dv[i], av = ov[i];
                     if (a.da0p.enabled) {
-                        ga = drop_keep(a.da0p, a.st, m, jj + i, K1) ? ga * (float)a.da0p.scale : 0.f;
+                        ga = ka0[i] ? ga * (float)a.da0p.scale : 0.f;
                         av = av * (float)a.da0p.keep_prob;
                     }
                     float gq = ga * act_bwd_from_out<float>(a.act0, av);
-                    if (a.dz0p.enabled) gq = drop_keep(a.dz0p, a.st, m, jj + i, K1) ? gq * (float)a.dz0p.scale : 0.f;
+                    if (a.dz0p.enabled) gq = kz0[i] ? gq * (float)a.dz0p.scale : 0.f;
                     gv[i] = gq;
                 }
                 gz = make_float4(gv[0], gv[1], gv[2], gv[3]);

@@ -293,10 +293,26 @@ static int ensure_grad_slabs(poz_ctx* c, int slabs) {
 // (Programmatic dependent launches: in round 1, on the ~12 small launches of the step's CUDA graph, they cost 108-114 us per
 //  C2 step against 82 us with plain edges, and were removed.  Round 2 brought them back for the two edges that remain on
 //  the critical path -- forward -> tail -> grouped weight gradient: 51.3 -> 49.1 us per step; see poz_tcs_kernel.cuh.)
+// Set around the launches of a small float32 inference pass (forward_impl): its kernels -- the pipelined SIMT GEMMs and the
+// softmax kernels, which all start with index arithmetic and griddepcontrol.wait -- are then launched as programmatic
+// dependents of one another, so a launch's CTAs are in place when the one before finishes.
+static thread_local bool t_pdl_launches = false;
+struct PdlScope {
+    bool prev;
+    explicit PdlScope(bool on) : prev(t_pdl_launches) { t_pdl_launches = on; }
+    ~PdlScope() { t_pdl_launches = prev; }
+};
+
 template <typename... P, typename... A>
 static int launch_pdl(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A&&... args) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    if (t_pdl_launches) {
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+    }
     POZ_CUDA(cudaLaunchKernelEx(&cfg, kern, std::forward<A>(args)...));
     count_launch();
     return 0;
@@ -327,6 +343,11 @@ static int launch_fast(const fast::Op& A, const fast::Op& B, long long M, int N,
     if (cluster && splits > 1) {
         attr[na].id = cudaLaunchAttributeClusterDimension;
         attr[na].val.clusterDim.x = 1; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = (unsigned)splits;
+        ++na;
+    }
+    if (t_pdl_launches) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
         ++na;
     }
     if (na) { cfg.attrs = attr; cfg.numAttrs = na; }

@@ -40,7 +40,8 @@ struct poz_ctx {
     long long tc_tr_batch = 0;
     // measured at batch 1024 (C2) the plane splits cost what the tensor cores save, so the SIMT
     // kernels keep the first layer below this batch (POZ_TC3_TRAIN_MIN_BATCH overrides)
-    long long tc3_train_min_batch = 8192;
+    long long tc3_train_min_batch = 2304;   // (measured, us per configs[1] step, cluster split-K path / this path: 2048 rows 95.7 / 100.6,
+                                            //  2560 rows 153.2 / 119.5, 4096 rows 208.0 / 150.1)
     bool tc3_train = true;            // first layer of float32 training on tcgen05 when it is deep enough
     // small-batch tensor-core path of the first layer (csrc/poz_tcs_kernel.cuh): forward and weight gradient of
     // layer 0 as cluster split-K tcgen05 launches, the optimizer applied in the weight-gradient epilogue

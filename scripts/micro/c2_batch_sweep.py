@@ -8,7 +8,7 @@ dev = torch.device("cuda", 0)
 side = torch.cuda.Stream(device=dev)
 torch.cuda.synchronize()
 torch.cuda.set_stream(side)
-for batch in (64, 128, 256, 512, 1024, 1536, 2048, 2560, 4096, 8192, 16384):
+for batch in [int(b) for b in os.environ.get("SWEEP_BATCHES", "64,128,256,512,1024,1536,2048,2560,4096,8192,16384").split(",")]:
     eng = bench.make_engine(0)
     n_pool = max(2, min(64, int(210e6 / (batch * 784 * 4))))
     xs, ys = bench.synth_pool(n_pool, batch, dev, 7)

@@ -461,12 +461,12 @@ def test_in_kernel_dropout_statistics_and_determinism():
     assert np.isfinite(runs[0][2])
 
 
-def test_large_batch_training_with_first_layer_on_tensor_cores():
-    """Batch 8192 >= the threshold at which the first layer's forward / weight-gradient GEMMs run on
-    tcgen05 (split-bf16): three Adam steps against the live oracle, same float32 tolerance."""
+@pytest.mark.parametrize("B", [2304 + 40, 8192])
+def test_large_batch_training_with_first_layer_on_tensor_cores(B):
+    """Batches from the threshold (2,304 rows) at which the first layer's forward / weight-gradient GEMMs run on the
+    persistent split-bf16 tcgen05 kernels: three steps against the live oracle, same float32 tolerance."""
     from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
     sizes, algos = mnist_stack()
-    B = 8192
     params = det_params(sizes, True, 177)
     x = det_normalish((B, 784), 178)
     y = det_labels(B, 10, 179)

@@ -47,7 +47,7 @@ struct poz_ctx {
     // layer 0 as cluster split-K tcgen05 launches, the optimizer applied in the weight-gradient epilogue
     bool tcs_enabled = true;          // POZ_TCS=0 keeps the SIMT kernels
     bool tcs_fuse_update = true;      // POZ_TCS_FUSE_UPDATE=0: the weight-gradient launch stores the gradient instead
-    long long tcs_min_batch = 256, tcs_max_batch = 2560;
+    long long tcs_min_batch = 96, tcs_max_batch = 2560;
     bool tcs_live = false;            // layer 0's weight planes are kept equal to its parameters at all times
     std::vector<void*> tcs_dzp;       // planes of dZ of layer l [3][batch][round8(out_l)] (layer 0 only unless grouped)
     long long tcs_dz_batch = 0;

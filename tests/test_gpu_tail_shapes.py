@@ -20,9 +20,12 @@ CASES = [
     ([33, 4, 4, 1],          ("relu", "tanh"),     False, 9,     0.0),     # the smallest widths, a single class
     ([130, 252, 124, 17],    ("sigmoid", "relu"),  True,  257,   0.0),     # 33 blocks: no cluster
     ([64, 128, 64, 5],       ("relu", "relu"),     False, 520,   0.0),
-    ([784, 256, 128, 10],    ("relu", "relu"),     True,  300,   0.25),    # recorded masks, batch below the tensor-core path's minimum...
-    ([784, 256, 128, 10],    ("tanh", "relu"),     True,  1024,  0.25),    # ... and on it (see OUTLIERS)
+    ([784, 256, 128, 10],    ("relu", "relu"),     True,  300,   0.25),    # recorded masks, a batch that is no multiple of the 128-row tile...
+    ([784, 256, 128, 10],    ("tanh", "relu"),     True,  1024,  0.25),    # ... and one that is (see OUTLIERS)
     ([96, 60, 36, 3],        ("relu", "sigmoid"),  True,  64,    0.5),
+    ([784, 256, 128, 10],    ("relu", "relu"),     True,  100,   0.0),     # the smallest batches of the tensor-core path (96 rows up)
+    ([200, 64, 32, 4],       ("tanh", "relu"),     True,  128,   0.25),
+    ([784, 256, 128, 10],    ("relu", "relu"),     False, 95,    0.0),     # ... and one row below it
 ]
 
 # Three Adam steps divide every gradient by its own running magnitude, so an element whose gradient is within fp32

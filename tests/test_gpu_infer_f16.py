@@ -158,3 +158,44 @@ def test_switch_keeps_the_split_bf16_kernels():
     r = subprocess.run([sys.executable, "-c", CHILD.format(root=root)], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-500:] + r.stderr[-1500:]
     assert "launches 2" in r.stdout, r.stdout
+
+
+def test_fp16_planes_follow_training_steps_replayed_from_a_graph():
+    """train x4 (the last two replayed from the CUDA graph), infer 32,768 rows, train x4, infer again: each inference must
+    see the parameters as the steps before it left them (the fp16 weight planes are rebuilt whenever a step -- launched or
+    replayed -- has changed the parameters)."""
+    from penr_oz_neural_network_torch_b200 import DeviceMLP, StackSpec
+    params = det_params(SIZES, True, 321)
+    eng = DeviceMLP(SIZES, StackSpec.from_algos(ALGOS), True, "float32", 0)
+    for l in range(3):
+        eng.upload_params(l, params[2 * l], params[2 * l + 1])
+    from oracle.detgen import det_normalish, det_labels
+    xt = det_normalish((1024, 784), 322)
+    yt = det_labels(1024, 10, 323)
+    xtd = torch.tensor(xt, dtype=torch.float32, device="cuda:0")
+    ytd = torch.tensor(yt, dtype=torch.int32, device="cuda:0")
+    g = torch.Generator(device="cuda:0").manual_seed(324)
+    xi = torch.randn((ROWS, 784), generator=g, device="cuda:0", dtype=torch.float32)
+    rows = torch.arange(0, ROWS, 23, device="cuda:0")
+    stack = orc.parse_stack(ALGOS)
+    adam = orc.AdamState()
+    p = params
+    tgt = [[int(v)] for v in yt]
+    eng.train_begin(optimizer="adam", learning_rate=0.01, decay_rate=0.9, l2_lambda=0.001, epochs=8)
+    side = torch.cuda.Stream()
+    step = 0
+    for _round in range(2):
+        with torch.cuda.stream(side):
+            for _ in range(4):
+                eng.train_step(xtd, ytd)
+        side.synchronize()
+        for _ in range(4):
+            p, _c, *_ = orc.train_step(stack, p, xt, tgt, lr=0.01 * 0.9 ** step, optimizer="adam", adam=adam, l2_lambda=0.001)
+            step += 1
+        out = eng.forward(xi)
+        ref = orc.forward(stack, p, xi[rows].cpu().numpy().astype(np.float64))[0][-1]
+        got = out[rows].cpu().numpy().astype(np.float64).reshape(ref.shape)
+        # the parameters themselves carry the float32 training tolerance (relu-flip outliers): compare loosely, but a stale
+        # set of planes would be off by the whole of four Adam steps (~4e-2 in the weights)
+        assert np.abs(got - ref).max() < 5e-3, float(np.abs(got - ref).max())
+    eng.close()

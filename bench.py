@@ -366,6 +366,7 @@ def run_c2(args, world, rank, local):
                                                                             # capture, the diagnostics epoch at the end) cancel
             class_api = {"us_per_epoch": round(us, 1), "samples_per_s": round(batch / (us * 1e-6)),
                          "steady_us_per_epoch": round(steady, 1),
+                         "list_api": drop_in_list_api(),
                          "note": "NeuralNetworkModel.train(list, batch_size=1024): wall time of its epoch loop (host-side "
                                  "torch.randint sampling, pinned index upload, device row gather, step) per epoch, "
                                  "2000 epochs; the list ingestion and the two 11 MB JSON saves around the loop (~0.3 s per "
@@ -1095,6 +1096,18 @@ def list_api_baseline(ref, seconds_cap=40.0):
         return out
     finally:
         os.chdir(cwd)
+
+
+def drop_in_list_api():
+    """The same list-level calls as list_api_baseline times on the reference -- train() and compute_output() on Python lists for
+    C2, one train() call of the C1 row -- on the drop-in class, to set beside cpu_baseline.list_api."""
+    import penr_oz_neural_network_torch_b200 as pkg
+    try:
+        return list_api_baseline(pkg)
+    except Exception as e:
+        if "CUDA" in str(e):
+            raise
+        return {"error": f"{type(e).__name__}: {str(e)[:200]}"}
 
 
 def pick_workload(args):

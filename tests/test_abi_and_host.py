@@ -164,3 +164,27 @@ def test_randint_hands_out_the_same_indices_in_one_call_or_many():
         after_b = torch.randint(0, 1 << 30, (4,))
         assert torch.equal(one_by_one, at_once)
         assert torch.equal(after_a, after_b)
+
+
+def test_fast_list_conversion_equals_torch_tensor():
+    """compute_output() / train() convert their Python lists with numpy.fromiter where the shape allows; the result must be
+    what torch.tensor(data, dtype=float64) gives (neural_net_model.py:379,472), and anything irregular must reach torch.tensor."""
+    import numpy as np
+    import torch
+    from penr_oz_neural_network_torch_b200.neural_net_model import _list_to_f64
+    rng = np.random.default_rng(3)
+    rows = rng.standard_normal((37, 11)).tolist()
+    assert torch.equal(_list_to_f64(rows), torch.tensor(rows, dtype=torch.float64))
+    ints = [[1, 2, 3], [4, 5, 6]]                                   # token indices, integers, booleans
+    assert torch.equal(_list_to_f64(ints), torch.tensor(ints, dtype=torch.float64))
+    assert torch.equal(_list_to_f64([[True, False]]), torch.tensor([[True, False]], dtype=torch.float64))
+    vec = [0.5, 1.5, -2.0]                                          # a single vector: torch.tensor's own path
+    assert torch.equal(_list_to_f64(vec), torch.tensor(vec, dtype=torch.float64))
+    deep = [[[1, 2], [3, 4]], [[5, 6], [7, 8]]]
+    assert torch.equal(_list_to_f64(deep), torch.tensor(deep, dtype=torch.float64))
+    for bad in ([[1.0, 2.0], [3.0]], [[1.0, "x"]], [[1.0, None]]):  # ragged rows, non-numbers: torch.tensor's exception
+        with pytest.raises((ValueError, TypeError)):
+            torch.tensor(bad, dtype=torch.float64)
+        with pytest.raises((ValueError, TypeError)):
+            _list_to_f64(bad)
+    assert _list_to_f64([]).shape == torch.tensor([], dtype=torch.float64).shape
